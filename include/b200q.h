@@ -1,0 +1,151 @@
+/*
+ * b200q.h — the thin C-ABI of the B200-native quantized matmul kernels (libb200q.so).
+ *
+ * Plain pointers and sizes only: no ggml, torch or C++ types cross this boundary.  The ggml backend
+ * plugin (include/ggml-b200.h, libggml-b200.so) is the C++ host code that sits above it; tests and
+ * bench.py bind it with ctypes.
+ *
+ * Each entry point replaces one piece of the reference's CUDA hot path (paths relative to
+ * /root/reference/ggml/src/ggml-cuda/ unless stated):
+ *
+ *   b200q_dequantize      <- dequantize_block_* / ggml_get_to_fp32_cuda       convert.cu:82-290,661-760
+ *                            (oracle: dequantize_row_* ggml-quants.c:307-1800, bit-exact)
+ *   b200q_get_rows        <- k_get_rows / ggml_cuda_op_get_rows               getrows.cu:5-67,206-252
+ *   b200q_mul_mat         <- ggml_cuda_mul_mat (GEMV: mul_mat_vec_q mmvq.cu:139-226,500-570 +
+ *                            quantize_q8_1 quantize.cu:4-48;  MMQ: mul_mat_q mmq.cuh:3134-3370 +
+ *                            quantize_mmq_q8_1 quantize.cu:50-146)            ggml-cuda.cu:2002-2085
+ *   b200q_mul_mat_id      <- ggml_cuda_mul_mat_id + host routing              ggml-cuda.cu:2087-2228, mmq.cu:145-227
+ *   b200q_*_host          <- the set_tensor / graph_compute / get_tensor round trip a ggml caller
+ *                            makes (ggml-backend.cpp:327-376) — used for end-to-end timing
+ *   b200q_rowsplit_*      <- ggml_cuda_op_mul_mat row-split orchestration     ggml-cuda.cu:1436-1754
+ *
+ * Tensor conventions are ggml's (ggml/include/ggml.h:614-646): ne[0] is the contiguous dimension,
+ * nb[] are byte strides.  `type` values are ggml_type numbers (ggml.h:371-411).
+ * All pointers are DEVICE pointers unless the function name ends in _host.
+ * `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ * Every function returns 0 on success, a negative B200Q_E* code otherwise; b200q_last_error() gives text.
+ * There is no CPU fallback anywhere behind this header: without a CUDA device the calls fail.
+ */
+#ifndef B200Q_H
+#define B200Q_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define B200Q_API
+#else
+#define B200Q_API __attribute__((visibility("default")))
+#endif
+
+/* ggml_type numbers accepted as weight types */
+enum b200q_type {
+    B200Q_TYPE_F32   = 0,
+    B200Q_TYPE_Q4_0  = 2,
+    B200Q_TYPE_Q4_1  = 3,
+    B200Q_TYPE_Q5_0  = 6,
+    B200Q_TYPE_Q5_1  = 7,
+    B200Q_TYPE_Q8_0  = 8,
+    B200Q_TYPE_Q4_K  = 12,
+    B200Q_TYPE_Q5_K  = 13,
+    B200Q_TYPE_Q6_K  = 14,
+    B200Q_TYPE_MXFP4 = 39,
+};
+
+enum b200q_status {
+    B200Q_OK            = 0,
+    B200Q_EINVAL        = -1, /* bad argument / unsupported layout */
+    B200Q_ENOTSUP       = -2, /* type or shape not supported by the kernels */
+    B200Q_ECUDA         = -3, /* CUDA runtime error (see b200q_last_error) */
+    B200Q_ENOMEM        = -4,
+    B200Q_ENODEVICE     = -5,
+    B200Q_EWORKSPACE    = -6, /* workspace too small */
+};
+
+/* b200q_mul_mat flags */
+#define B200Q_FLAG_WEIGHTS_IMMUTABLE 1u /* src0 is never written by stream work => weight prefetch may start before the
+                                            previous kernel finishes (programmatic dependent launch) */
+#define B200Q_FLAG_FORCE_GEMV        2u /* debugging / measurement: always take the GEMV kernel (n <= 8 required) */
+#define B200Q_FLAG_FORCE_MMQ         4u /* debugging / measurement: always take the tensor-core kernel */
+#define B200Q_FLAG_NO_PDL            8u /* launch without programmatic stream serialization */
+
+/* ---- library / device ---------------------------------------------------------------------- */
+B200Q_API int          b200q_version(void);
+B200Q_API const char * b200q_last_error(void);
+B200Q_API int          b200q_device_count(void);
+/* name may be NULL; any out pointer may be NULL */
+B200Q_API int b200q_device_info(int device, char * name, size_t name_len, size_t * total_mem, size_t * free_mem,
+                                int * cc_major, int * cc_minor, int * sm_count, size_t * l2_bytes);
+
+/* ---- type table (mirrors ggml_blck_size / ggml_type_size, ggml.c:586-876) -------------------- */
+B200Q_API int64_t b200q_blck_size(int type);
+B200Q_API size_t  b200q_type_size(int type);
+B200Q_API size_t  b200q_row_size(int type, int64_t ne0);
+B200Q_API int     b200q_type_supported(int type); /* 1 if usable as MUL_MAT/GET_ROWS weight type */
+
+/* ---- dequantize / GET_ROWS (bit-exact vs dequantize_row_*) ----------------------------------- */
+/* contiguous: n_elems % blck_size == 0 */
+B200Q_API int b200q_dequantize(int type, const void * src, float * dst, int64_t n_elems, void * stream);
+
+typedef struct b200q_get_rows_args {
+    int     type;              /* src0 type (quantized or F32) */
+    int64_t ne00;              /* row length */
+    int64_t ne10, ne11, ne12;  /* index tensor shape; dst = [ne00, ne10, ne11, ne12] */
+    size_t  nb01, nb02, nb03;  /* src0 byte strides (row, plane, batch) */
+    size_t  nb10, nb11, nb12;  /* ids byte strides */
+    size_t  nb1, nb2, nb3;     /* dst byte strides (dst rows contiguous f32) */
+} b200q_get_rows_args;
+B200Q_API int b200q_get_rows(const b200q_get_rows_args * a, const void * src0, const int32_t * ids, float * dst,
+                             void * stream);
+
+/* ---- MUL_MAT --------------------------------------------------------------------------------- */
+/* dst[i13][i12][j][i] = sum_l W[i13/r3][i12/r2][i][l] * act[i13][i12][j][l]   (ggml_mul_mat, ggml.c:3015-3030) */
+typedef struct b200q_mul_mat_args {
+    int      type;             /* weight type */
+    int64_t  k, m, n;          /* ne00 (= ne10), ne01, ne11 */
+    int64_t  ne02, ne03;       /* weight batch dims */
+    int64_t  ne12, ne13;       /* activation batch dims (multiples of ne02 / ne03) */
+    size_t   nb01, nb02, nb03; /* weight byte strides */
+    size_t   nb11, nb12, nb13; /* activation byte strides (f32, nb10 == 4) */
+    size_t   nb1, nb2, nb3;    /* dst byte strides (f32, nb0 == 4) */
+    uint32_t flags;
+} b200q_mul_mat_args;
+B200Q_API size_t b200q_mul_mat_workspace(const b200q_mul_mat_args * a);
+B200Q_API int    b200q_mul_mat(const b200q_mul_mat_args * a, const void * w, const float * act, float * dst,
+                               void * workspace, size_t workspace_bytes, void * stream);
+
+/* ---- MUL_MAT_ID (MoE) ------------------------------------------------------------------------ */
+/* dst[t][s][:] = W[ids[t][s]] . b[t][s or 0][:]     (ggml_mul_mat_id, ggml.c:3056-3080) */
+typedef struct b200q_mul_mat_id_args {
+    int      type;
+    int64_t  k, m;             /* expert matrix [m][k] */
+    int64_t  n_expert;         /* as->ne[2] */
+    int64_t  n_used;           /* ids->ne[0] */
+    int64_t  n_tokens;         /* ids->ne[1] */
+    int64_t  b_ne1;            /* 1 (broadcast) or n_used */
+    size_t   nb01, nb02;       /* expert weights byte strides (row, expert) */
+    size_t   nb11, nb12;       /* b byte strides (slot, token) */
+    size_t   ids_nb1;          /* ids byte stride between tokens */
+    size_t   nb1, nb2;         /* dst byte strides (slot, token) */
+    uint32_t flags;
+} b200q_mul_mat_id_args;
+B200Q_API size_t b200q_mul_mat_id_workspace(const b200q_mul_mat_id_args * a);
+B200Q_API int    b200q_mul_mat_id(const b200q_mul_mat_id_args * a, const void * as, const float * b,
+                                  const int32_t * ids, float * dst, void * workspace, size_t workspace_bytes,
+                                  void * stream);
+
+/* ---- host-buffer round trip (what a ggml caller does: tensor_set -> graph_compute -> tensor_get) --- */
+/* Weights stay resident on the device (w_dev); activations and results are HOST buffers (pinned or pageable).
+ * act_host: n*k floats contiguous, dst_host: n*m floats contiguous.  Synchronous. */
+B200Q_API int b200q_mul_mat_host(int type, const void * w_dev, const float * act_host, float * dst_host, int64_t m,
+                                 int64_t k, int64_t n, void * act_dev_scratch, void * dst_dev_scratch,
+                                 void * workspace, size_t workspace_bytes, void * stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200Q_H */

@@ -1,0 +1,417 @@
+// api.cu — the C-ABI of libb200q.so (include/b200q.h): argument checking, kernel selection, launches.
+// No compute happens on the host and nothing here falls back to a CPU path.
+#include "../../include/b200q.h"
+
+#include "blocks.cuh"
+#include "dequant.cuh"
+#include "gemv.cuh"
+#include "mmq.cuh"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <set>
+#include <string>
+
+using namespace b200q;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char * fmt, ...) {
+    char    buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                                     \
+    do {                                                                                                   \
+        cudaError_t e_ = (expr);                                                                           \
+        if (e_ != cudaSuccess) {                                                                           \
+            return fail(B200Q_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
+        }                                                                                                  \
+    } while (0)
+
+struct DevInfo {
+    bool   ok = false;
+    int    sms = 0;
+    int    max_smem = 0;
+    int    cc = 0;
+};
+
+DevInfo & dev_info() {
+    static DevInfo    info[64];
+    static std::mutex mu;
+    int               dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    std::lock_guard<std::mutex> lk(mu);
+    DevInfo & d = info[dev];
+    if (!d.ok) {
+        int major = 0, minor = 0;
+        cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaDeviceGetAttribute(&d.max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+        cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+        cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev);
+        d.cc = major * 10 + minor;
+        d.ok = d.sms > 0;
+    }
+    return d;
+}
+
+// opt every kernel in to the full dynamic shared memory carve-out once per (device, function)
+int ensure_smem_attr(const void * fn, int bytes) {
+    static std::mutex                            mu;
+    static std::set<std::pair<int, const void *>> done;
+    int                                          dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lk(mu);
+    if (done.count({ dev, fn })) return 0;
+    CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    done.insert({ dev, fn });
+    return 0;
+}
+
+inline int round_up(int x, int a) { return (x + a - 1) / a * a; }
+
+// ---- GEMV configuration ------------------------------------------------------------------------------
+struct GemvPlan {
+    GemvParams p;
+    int        grid = 0;
+    int        smem = 0;
+};
+
+// fills the tiling fields of plan.p for `ncols` activation columns; false if it cannot fit in shared memory
+bool plan_gemv(GemvPlan & plan, int type, int ncols, const DevInfo & di) {
+    GemvParams & p = plan.p;
+    p.row_bytes    = (int) ((long long) p.k / blck_elems(type) * blck_bytes(type));
+    p.contiguous   = p.w_nb1 == p.row_bytes;
+    p.smem_pitch   = p.contiguous ? (int) p.w_nb1 : round_up(p.row_bytes + 31, 16);
+    const int pitch  = p.smem_pitch;
+    const int budget = 24 * 1024;
+    p.wpr            = 8;
+    for (int wpr = 1; wpr <= 8; wpr *= 2) {
+        if ((long long) gemv_pass_rows(wpr) * pitch <= budget) {
+            p.wpr = wpr;
+            break;
+        }
+    }
+    const int       pass_rows  = gemv_pass_rows(p.wpr);
+    const long long pass_bytes = (long long) pass_rows * pitch;
+    p.passes                   = (int) std::max<long long>(1, budget / pass_bytes);
+    // keep a few stages of work per CTA so the ring actually pipelines
+    const long long rows_total   = (long long) p.nch * p.m;
+    const long long rows_per_cta = std::max<long long>(1, rows_total / std::max(1, di.sms * 2));
+    while (p.passes > 1 && (long long) p.passes * pass_rows * 3 > rows_per_cta) {
+        --p.passes;
+    }
+    const long long stage_bytes = 16 + (long long) p.passes * pass_bytes + 48;
+    if (stage_bytes > di.max_smem) return false;
+    p.stage_bytes             = round_up((int) stage_bytes, 128);
+    const long long act_bytes = (long long) ncols * (p.k + p.k / 4);
+    const long long stage_off = round_up((int) std::min<long long>(gemv_fixed_smem() + act_bytes, 1 << 30), 128);
+    if (stage_off > di.max_smem) return false;
+    p.stage_off = (int) stage_off;
+
+    const int half = (di.max_smem - 2048) / 2;  // two resident CTAs per SM
+    int       S    = (int) ((half - stage_off) / p.stage_bytes);
+    int       ctas = 2;
+    if (S < 3 || ncols > 4) {
+        ctas = 1;
+        S    = (int) ((di.max_smem - stage_off) / p.stage_bytes);
+    }
+    if (S < 2) return false;
+    p.nstages = std::min(S, ctas == 2 ? 6 : 8);
+    plan.smem = p.stage_off + p.nstages * p.stage_bytes;
+    const long long want = (rows_total + pass_rows - 1) / pass_rows;
+    plan.grid            = (int) std::max<long long>(1, std::min<long long>((long long) di.sms * ctas, want));
+    return true;
+}
+
+int launch_gemv(GemvPlan & plan, int type, int ncols, uint32_t flags, cudaStream_t st) {
+    gemv_kernel_t fn = gemv_kernel_for(type, ncols);
+    if (!fn) return fail(B200Q_ENOTSUP, "gemv: unsupported type %d / ncols %d", type, ncols);
+    const DevInfo & di = dev_info();
+    if (int rc = ensure_smem_attr((const void *) fn, di.max_smem)) return rc;
+    const bool pdl        = !(flags & B200Q_FLAG_NO_PDL);
+    plan.p.early_prefetch = pdl && (flags & B200Q_FLAG_WEIGHTS_IMMUTABLE) ? 1 : 0;
+
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim          = dim3(plan.grid);
+    cfg.blockDim         = dim3(gemv_threads());
+    cfg.dynamicSmemBytes = plan.smem;
+    cfg.stream           = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs                                          = attr;
+    cfg.numAttrs                                       = pdl ? 1 : 0;
+    CUDA_TRY(cudaLaunchKernelEx(&cfg, fn, plan.p));
+    return 0;
+}
+
+bool aligned16(const void * p, long long stride) { return ((uintptr_t) p & 15) == 0 && (stride & 15) == 0; }
+
+}  // namespace
+
+// ======================================================================================================
+extern "C" {
+
+int          b200q_version(void) { return 100; }
+const char * b200q_last_error(void) { return g_err.c_str(); }
+
+int b200q_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+int b200q_device_info(int device, char * name, size_t name_len, size_t * total_mem, size_t * free_mem, int * cc_major,
+                      int * cc_minor, int * sm_count, size_t * l2_bytes) {
+    int n = b200q_device_count();
+    if (device < 0 || device >= n) return fail(B200Q_ENODEVICE, "no CUDA device %d (count %d)", device, n);
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (name && name_len) {
+        snprintf(name, name_len, "%s", prop.name);
+    }
+    if (cc_major) *cc_major = prop.major;
+    if (cc_minor) *cc_minor = prop.minor;
+    if (sm_count) *sm_count = prop.multiProcessorCount;
+    if (l2_bytes) *l2_bytes = (size_t) prop.l2CacheSize;
+    if (total_mem || free_mem) {
+        int cur = 0;
+        CUDA_TRY(cudaGetDevice(&cur));
+        CUDA_TRY(cudaSetDevice(device));
+        size_t f = 0, t = 0;
+        CUDA_TRY(cudaMemGetInfo(&f, &t));
+        CUDA_TRY(cudaSetDevice(cur));
+        if (total_mem) *total_mem = t;
+        if (free_mem) *free_mem = f;
+    }
+    return 0;
+}
+
+int64_t b200q_blck_size(int type) { return blck_elems(type); }
+size_t  b200q_type_size(int type) { return (size_t) blck_bytes(type); }
+size_t  b200q_row_size(int type, int64_t ne0) {
+    const int be = blck_elems(type);
+    return be ? (size_t) (ne0 / be) * (size_t) blck_bytes(type) : 0;
+}
+int b200q_type_supported(int type) { return type != T_F32 && blck_elems(type) > 0; }
+
+// ---- dequantize / GET_ROWS -----------------------------------------------------------------------------
+static int launch_get_rows(const GetRowsParams & p, int type, cudaStream_t st) {
+    get_rows_kernel_t fn = get_rows_kernel_for(type);
+    if (!fn) return fail(B200Q_ENOTSUP, "get_rows: unsupported type %d", type);
+    const long long total = ((p.ne00 + 3) / 4) * p.n_rows;
+    if (total <= 0) return 0;
+    const DevInfo & di   = dev_info();
+    const long long want = (total + 255) / 256;
+    const int       grid = (int) std::min<long long>(want, (long long) di.sms * 16);
+    fn<<<grid, 256, 0, st>>>(p);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int b200q_dequantize(int type, const void * src, float * dst, int64_t n_elems, void * stream) {
+    const int be = blck_elems(type);
+    if (!be || type == T_F32) return fail(B200Q_ENOTSUP, "dequantize: unsupported type %d", type);
+    if (n_elems % be) return fail(B200Q_EINVAL, "dequantize: n_elems %lld not a multiple of the block size %d", (long long) n_elems, be);
+    GetRowsParams p{};
+    p.src      = (const uint8_t *) src;
+    p.ids      = nullptr;
+    p.dst      = dst;
+    p.ne00     = n_elems;
+    p.n_rows   = 1;
+    p.ne10     = 1;
+    p.ne11     = 1;
+    p.nb01     = 0;
+    p.nb1      = 0;
+    p.dst_vec4 = ((uintptr_t) dst & 15) == 0;
+    return launch_get_rows(p, type, (cudaStream_t) stream);
+}
+
+int b200q_get_rows(const b200q_get_rows_args * a, const void * src0, const int32_t * ids, float * dst, void * stream) {
+    if (!a || !src0 || !ids || !dst) return fail(B200Q_EINVAL, "get_rows: null argument");
+    const int be = blck_elems(a->type);
+    if (!be) return fail(B200Q_ENOTSUP, "get_rows: unsupported type %d", a->type);
+    if (a->ne00 % be) return fail(B200Q_EINVAL, "get_rows: ne00 not a multiple of the block size");
+    GetRowsParams p{};
+    p.src      = (const uint8_t *) src0;
+    p.ids      = ids;
+    p.dst      = dst;
+    p.ne00     = a->ne00;
+    p.ne10     = a->ne10;
+    p.ne11     = a->ne11;
+    p.n_rows   = a->ne10 * a->ne11 * a->ne12;
+    p.nb01     = (int64_t) a->nb01;
+    p.nb02     = (int64_t) a->nb02;
+    p.nb03     = (int64_t) a->nb03;
+    p.nb10     = (int64_t) a->nb10;
+    p.nb11     = (int64_t) a->nb11;
+    p.nb12     = (int64_t) a->nb12;
+    p.nb1      = (int64_t) a->nb1;
+    p.nb2      = (int64_t) a->nb2;
+    p.nb3      = (int64_t) a->nb3;
+    p.dst_vec4 = ((uintptr_t) dst & 15) == 0 && (a->nb1 & 15) == 0 && (a->nb2 & 15) == 0 && (a->nb3 & 15) == 0;
+    return launch_get_rows(p, a->type, (cudaStream_t) stream);
+}
+
+// ---- MUL_MAT -------------------------------------------------------------------------------------------
+static int check_mm(const b200q_mul_mat_args * a) {
+    if (!a) return fail(B200Q_EINVAL, "mul_mat: null args");
+    const int be = blck_elems(a->type);
+    if (!be || a->type == T_F32) return fail(B200Q_ENOTSUP, "mul_mat: unsupported weight type %d", a->type);
+    if (a->k <= 0 || a->k % be) return fail(B200Q_EINVAL, "mul_mat: k=%lld not a positive multiple of %d", (long long) a->k, be);
+    if (a->m < 0 || a->n < 0) return fail(B200Q_EINVAL, "mul_mat: negative dimension");
+    if (a->ne02 <= 0 || a->ne03 <= 0 || a->ne12 <= 0 || a->ne13 <= 0 || a->ne12 % a->ne02 || a->ne13 % a->ne03) {
+        return fail(B200Q_EINVAL, "mul_mat: bad batch dims");
+    }
+    return 0;
+}
+
+static bool use_mmq(const b200q_mul_mat_args * a) {
+    if (a->flags & B200Q_FLAG_FORCE_GEMV) return false;
+    if (a->flags & B200Q_FLAG_FORCE_MMQ) return mmq_supported(a->type, a->k);
+    return a->n > 8 && mmq_supported(a->type, a->k);
+}
+
+size_t b200q_mul_mat_workspace(const b200q_mul_mat_args * a) {
+    if (!a || check_mm(a)) return 0;
+    if (!use_mmq(a)) return 0;
+    return mmq_workspace_bytes(a->k, a->n, a->ne12 * a->ne13);
+}
+
+int b200q_mul_mat(const b200q_mul_mat_args * a, const void * w, const float * act, float * dst, void * workspace,
+                  size_t workspace_bytes, void * stream) {
+    if (int rc = check_mm(a)) return rc;
+    if (!w || !act || !dst) return fail(B200Q_EINVAL, "mul_mat: null pointer");
+    if (a->m == 0 || a->n == 0) return 0;
+    cudaStream_t    st = (cudaStream_t) stream;
+    const DevInfo & di = dev_info();
+    if (!di.ok) return fail(B200Q_ENODEVICE, "mul_mat: no CUDA device");
+
+    if (use_mmq(a)) {
+        MmqArgs q{};
+        q.type = a->type; q.k = a->k; q.m = a->m; q.n = a->n;
+        q.ne02 = a->ne02; q.ne03 = a->ne03; q.ne12 = a->ne12; q.ne13 = a->ne13;
+        q.w_nb1 = (long long) a->nb01; q.w_nb2 = (long long) a->nb02; q.w_nb3 = (long long) a->nb03;
+        q.a_nb1 = (long long) a->nb11; q.a_nb2 = (long long) a->nb12; q.a_nb3 = (long long) a->nb13;
+        q.d_nb1 = (long long) a->nb1;  q.d_nb2 = (long long) a->nb2;  q.d_nb3 = (long long) a->nb3;
+        q.w = (const uint8_t *) w; q.act = act; q.dst = dst;
+        const size_t need = mmq_workspace_bytes(a->k, a->n, a->ne12 * a->ne13);
+        if (workspace_bytes < need || !workspace) {
+            return fail(B200Q_EWORKSPACE, "mul_mat: workspace %zu < required %zu", workspace_bytes, need);
+        }
+        std::string err;
+        const int   rc = mmq_launch(q, workspace, st, di.sms, err);
+        if (rc) return fail(rc, "%s", err.c_str());
+        return 0;
+    }
+
+    // GEMV path: up to 8 activation columns per launch (more columns = several passes over the weights)
+    GemvPlan plan{};
+    GemvParams & p = plan.p;
+    p.w            = (const uint8_t *) w;
+    p.ids          = nullptr;
+    p.k            = (int) a->k;
+    p.m            = (int) a->m;
+    p.nch          = (int) (a->ne12 * a->ne13);
+    p.mode         = GEMV_MODE_BATCH;
+    p.ne12         = (int) a->ne12;
+    p.r2           = (int) (a->ne12 / a->ne02);
+    p.r3           = (int) (a->ne13 / a->ne03);
+    p.n_used = 1; p.n_expert = 1; p.b_bcast = 0; p.ids_nb1 = 0;
+    p.w_nb1 = (long long) a->nb01; p.w_nb2 = (long long) a->nb02; p.w_nb3 = (long long) a->nb03;
+    p.a_nb1 = (long long) a->nb11; p.a_nb2 = (long long) a->nb12; p.a_nb3 = (long long) a->nb13;
+    p.d_nb1 = (long long) a->nb1;  p.d_nb2 = (long long) a->nb2;  p.d_nb3 = (long long) a->nb3;
+    p.act_vec4 = aligned16(act, p.a_nb1) && (p.a_nb2 & 15) == 0 && (p.a_nb3 & 15) == 0;
+
+    int ncols = (int) std::min<int64_t>(a->n, 8);
+    while (ncols >= 1 && !plan_gemv(plan, a->type, ncols, di)) {
+        ncols = ncols > 1 ? (ncols + 1) / 2 : 0;
+    }
+    if (ncols < 1) return fail(B200Q_ENOTSUP, "mul_mat: k=%lld too large for the GEMV shared-memory plan", (long long) a->k);
+    for (int64_t j0 = 0; j0 < a->n; j0 += ncols) {
+        const int nc = (int) std::min<int64_t>(ncols, a->n - j0);
+        if (nc != ncols && !plan_gemv(plan, a->type, nc, di)) return fail(B200Q_ENOTSUP, "mul_mat: plan failed");
+        p.act = (const float *) ((const char *) act + j0 * (long long) a->nb11);
+        p.dst = (float *) ((char *) dst + j0 * (long long) a->nb1);
+        if (int rc = launch_gemv(plan, a->type, nc, a->flags, st)) return rc;
+    }
+    return 0;
+}
+
+// ---- MUL_MAT_ID ----------------------------------------------------------------------------------------
+size_t b200q_mul_mat_id_workspace(const b200q_mul_mat_id_args * a) {
+    (void) a;
+    return 0;
+}
+
+int b200q_mul_mat_id(const b200q_mul_mat_id_args * a, const void * as, const float * b, const int32_t * ids, float * dst,
+                     void * workspace, size_t workspace_bytes, void * stream) {
+    (void) workspace;
+    (void) workspace_bytes;
+    if (!a || !as || !b || !ids || !dst) return fail(B200Q_EINVAL, "mul_mat_id: null argument");
+    const int be = blck_elems(a->type);
+    if (!be || a->type == T_F32) return fail(B200Q_ENOTSUP, "mul_mat_id: unsupported weight type %d", a->type);
+    if (a->k <= 0 || a->k % be) return fail(B200Q_EINVAL, "mul_mat_id: bad k");
+    if (a->b_ne1 != 1 && a->b_ne1 != a->n_used) return fail(B200Q_EINVAL, "mul_mat_id: b->ne[1] must be 1 or n_used");
+    if (a->m == 0 || a->n_tokens == 0 || a->n_used == 0) return 0;
+    const DevInfo & di = dev_info();
+    if (!di.ok) return fail(B200Q_ENODEVICE, "mul_mat_id: no CUDA device");
+
+    // one GEMV channel per (token, slot); expert ids are read on the device (no host round trip, cf. mmq.cu:161)
+    GemvPlan plan{};
+    GemvParams & p = plan.p;
+    p.w = (const uint8_t *) as; p.act = b; p.dst = dst; p.ids = ids;
+    p.k = (int) a->k; p.m = (int) a->m;
+    p.nch  = (int) (a->n_tokens * a->n_used);
+    p.mode = GEMV_MODE_MOE;
+    p.ne12 = 1; p.r2 = 1; p.r3 = 1;
+    p.n_used = (int) a->n_used; p.n_expert = (int) a->n_expert; p.b_bcast = a->b_ne1 == 1;
+    p.w_nb1 = (long long) a->nb01; p.w_nb2 = (long long) a->nb02; p.w_nb3 = 0;
+    p.a_nb1 = (long long) a->nb11; p.a_nb2 = (long long) a->nb12; p.a_nb3 = 0;
+    p.d_nb1 = (long long) a->nb1;  p.d_nb2 = (long long) a->nb2;  p.d_nb3 = 0;
+    p.ids_nb1  = (long long) a->ids_nb1;
+    p.act_vec4 = aligned16(b, p.a_nb1) && (p.a_nb2 & 15) == 0;
+    if (!plan_gemv(plan, a->type, 1, di)) return fail(B200Q_ENOTSUP, "mul_mat_id: k too large");
+    return launch_gemv(plan, a->type, 1, a->flags, (cudaStream_t) stream);
+}
+
+// ---- host round trip -----------------------------------------------------------------------------------
+int b200q_mul_mat_host(int type, const void * w_dev, const float * act_host, float * dst_host, int64_t m, int64_t k,
+                       int64_t n, void * act_dev_scratch, void * dst_dev_scratch, void * workspace,
+                       size_t workspace_bytes, void * stream) {
+    cudaStream_t st = (cudaStream_t) stream;
+    CUDA_TRY(cudaMemcpyAsync(act_dev_scratch, act_host, (size_t) (n * k) * sizeof(float), cudaMemcpyHostToDevice, st));
+    b200q_mul_mat_args a{};
+    a.type = type; a.k = k; a.m = m; a.n = n;
+    a.ne02 = a.ne03 = a.ne12 = a.ne13 = 1;
+    a.nb01 = b200q_row_size(type, k); a.nb02 = a.nb01 * (size_t) m; a.nb03 = a.nb02;
+    a.nb11 = (size_t) k * 4; a.nb12 = a.nb11 * (size_t) n; a.nb13 = a.nb12;
+    a.nb1  = (size_t) m * 4; a.nb2 = a.nb1 * (size_t) n; a.nb3 = a.nb2;
+    a.flags = B200Q_FLAG_WEIGHTS_IMMUTABLE;
+    if (int rc = b200q_mul_mat(&a, w_dev, (const float *) act_dev_scratch, (float *) dst_dev_scratch, workspace,
+                               workspace_bytes, stream)) {
+        return rc;
+    }
+    CUDA_TRY(cudaMemcpyAsync(dst_host, dst_dev_scratch, (size_t) (n * m) * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return 0;
+}
+
+}  // extern "C"

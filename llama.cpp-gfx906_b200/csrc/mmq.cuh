@@ -1,0 +1,26 @@
+// mmq.cuh — host interface of the tensor-core (tcgen05) prompt-processing kernel (mmq.cu)
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+namespace b200q {
+
+struct MmqArgs {
+    int             type;
+    int64_t         k, m, n;
+    int64_t         ne02, ne03, ne12, ne13;
+    long long       w_nb1, w_nb2, w_nb3;
+    long long       a_nb1, a_nb2, a_nb3;
+    long long       d_nb1, d_nb2, d_nb3;
+    const uint8_t * w;
+    const float *   act;
+    float *         dst;
+};
+
+bool   mmq_supported(int type, int64_t k);
+size_t mmq_workspace_bytes(int64_t k, int64_t n, int64_t nbatch);
+int    mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, std::string & err);
+
+}  // namespace b200q

@@ -1,0 +1,350 @@
+// units.cuh — integer-dot "units" for the decode GEMV.
+//
+// A unit is the smallest piece of a quantized row that one lane decodes on its own:
+//   * 32-element block formats (q4_0 q4_1 q5_0 q5_1 q8_0 mxfp4): one block            -> 1 group of 8 words
+//   * q4_K / q5_K: one 64-element pair of sub-blocks sharing 32 nibble bytes           -> 2 groups of 8 words
+//   * q6_K: 4 x 16 elements that share 4 ql words (lo) + 4 ql words (hi) + 4 qh words  -> 4 groups of 4 words
+// decode() turns the unit into int8x4 words `wq` (in activation order), one fp32 scale `ws` per group and
+// one fp32 offset `wm` per group such that
+//      sum_{i in group} w_i * x_i  ~=  ws * d_x * dot(wq, q_x)  +  wm * s_x ,    s_x = d_x * sum(q_x)
+// with (q_x, d_x) the q8 quantization of the activation block the group lies in.  This is the arithmetic of the
+// reference's vec_dot_*_q8_1 device functions (ggml-cuda/vecdotq.cuh:51-70 q4_0, :179-191 q8_0, :243-262 mxfp4,
+// :409-431 q4_K, :528-548 q6_K), restated; it is NOT bit-comparable with ggml-cpu (which uses q8_0/q8_K
+// activations) and is gated by NMSE <= 5e-4 like the reference CUDA backend (tests/test-backend-ops.cpp:3106).
+//
+// Rows are byte streams: `p` may have ANY byte alignment (17/18/34/210-byte blocks), so all weight
+// loads go through ldw(), an aligned 32-bit load pair + funnel shift.  The caller guarantees 8 readable bytes of
+// slack behind the row.
+#pragma once
+
+#include "blocks.cuh"
+
+namespace b200q {
+
+// ---- intrinsic shims so the same code runs in csrc/selftest on the host ----------------------------------
+B200Q_HD int dp4a_(int a, int b, int c) {
+#ifdef __CUDA_ARCH__
+    return __dp4a(a, b, c);
+#else
+    for (int i = 0; i < 4; ++i) {
+        c += (int) (int8_t) (a >> (8 * i)) * (int) (int8_t) (b >> (8 * i));
+    }
+    return c;
+#endif
+}
+B200Q_HD uint32_t funnel_r(uint32_t lo, uint32_t hi, int shift_bits) {
+#ifdef __CUDA_ARCH__
+    return __funnelshift_r(lo, hi, shift_bits);
+#else
+    return shift_bits ? (lo >> shift_bits) | (hi << (32 - shift_bits)) : lo;
+#endif
+}
+B200Q_HD uint32_t vsub4_(uint32_t a, uint32_t b) {
+#ifdef __CUDA_ARCH__
+    return __vsub4(a, b);
+#else
+    uint32_t r = 0;
+    for (int i = 0; i < 4; ++i) {
+        r |= (uint32_t) (uint8_t) ((uint8_t) (a >> (8 * i)) - (uint8_t) (b >> (8 * i))) << (8 * i);
+    }
+    return r;
+#endif
+}
+B200Q_HD uint32_t byte_perm_(uint32_t a, uint32_t b, uint32_t s) {
+#ifdef __CUDA_ARCH__
+    return __byte_perm(a, b, s);
+#else
+    uint64_t v = ((uint64_t) b << 32) | a;
+    uint32_t r = 0;
+    for (int i = 0; i < 4; ++i) {
+        r |= (uint32_t) ((v >> (8 * ((s >> (4 * i)) & 7))) & 0xff) << (8 * i);
+    }
+    return r;
+#endif
+}
+
+// 32-bit little-endian word at an arbitrary byte address (reads the two aligned words that cover it)
+B200Q_HD uint32_t ldw(const uint8_t * p) {
+    const uintptr_t   a  = (uintptr_t) p;
+    const uint32_t *  w  = (const uint32_t *) (a & ~(uintptr_t) 3);
+    const int         sh = (int) (a & 3) * 8;
+    return funnel_r(w[0], w[1], sh);
+}
+// N consecutive words starting at an arbitrary byte address: N+1 aligned loads, N funnel shifts
+template <int N> B200Q_HD void ldw_n(const uint8_t * p, uint32_t (&out)[N]) {
+    const uintptr_t  a  = (uintptr_t) p;
+    const uint32_t * w  = (const uint32_t *) (a & ~(uintptr_t) 3);
+    const int        sh = (int) (a & 3) * 8;
+    uint32_t         prev = w[0];
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        const uint32_t next = w[i + 1];
+        out[i]              = funnel_r(prev, next, sh);
+        prev                = next;
+    }
+}
+
+// spread 4 bits (bit i -> bit 8*i) : used for the 5th bit of q5_0 / q5_1 / q5_K
+B200Q_HD uint32_t spread4(uint32_t b) { return ((b & 0xFu) * 0x00204081u) & 0x01010101u; }
+
+// 8 nibbles (one word) -> two int8x4 words through the mxfp4 code-point table, lo nibbles and hi nibbles
+B200Q_HD void mxfp4_lut(uint32_t q, uint32_t & lo, uint32_t & hi) {
+    // table bytes 0..15: 0,1,2,3 | 4,6,8,12 | 0,-1,-2,-3 | -4,-6,-8,-12
+    const uint32_t t0 = 0x03020100u, t1 = 0x0C080604u, t2 = 0xFDFEFF00u, t3 = 0xF4F8FAFCu;
+    uint32_t       r[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const uint32_t n   = (q >> (4 * h)) & 0x0F0F0F0Fu;      // 4 nibble indices, one per byte
+        const uint32_t sel = n & 0x07070707u;                    // index within the selected 8-entry half
+        // prmt selector nibbles: byte i of sel goes to selector nibble i
+        const uint32_t s   = (sel & 0xF) | ((sel >> 4) & 0xF0) | ((sel >> 8) & 0xF00) | ((sel >> 12) & 0xF000);
+        const uint32_t pos = byte_perm_(t0, t1, s);              // table[idx & 7]        (non-negative half)
+        const uint32_t neg = byte_perm_(t2, t3, s);              // table[8 + (idx & 7)]  (negative half)
+        // per-byte select on bit 3 of the nibble
+        const uint32_t m   = ((n >> 3) & 0x01010101u) * 0xFFu;
+        r[h]               = (pos & ~m) | (neg & m);
+    }
+    lo = r[0];
+    hi = r[1];
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Unit<T>
+//   ELEMS        elements covered by one unit
+//   NG, GW       groups per unit, activation words per group
+//   act_word(u,g) index of the first int8x4 activation word of group g of unit u
+//   act_blk(u,g)  index of the 32-element activation block (for d_x, s_x)
+//   decode(row, u, wq, ws, wm)
+// ---------------------------------------------------------------------------------------------------------
+template <int T> struct Unit;
+
+template <int T, int BYTES> struct UnitBlock32 {
+    static constexpr int ELEMS = 32, NG = 1, GW = 8;
+    static B200Q_HD int  act_word(int u, int) { return u * 8; }
+    static B200Q_HD int  act_blk(int u, int) { return u; }
+};
+
+template <> struct Unit<T_Q4_0> : UnitBlock32<T_Q4_0, 18> {
+    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
+        const uint8_t * b = row + (size_t) u * 18;
+        uint32_t        w[5];
+        ldw_n<5>(b, w);  // [d | qs0 qs1] [qs2..5] [qs6..9] [qs10..13] [qs14 qs15 | next]
+        const float d = half_bits_to_float((uint16_t) (w[0] & 0xffff));
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t q = funnel_r(w[i], w[i + 1], 16);
+            wq[i]            = (int) (q & 0x0F0F0F0Fu);
+            wq[4 + i]        = (int) ((q >> 4) & 0x0F0F0F0Fu);
+        }
+        ws[0] = d;
+        wm[0] = -8.0f * d;
+    }
+};
+template <> struct Unit<T_Q4_1> : UnitBlock32<T_Q4_1, 20> {
+    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
+        const uint8_t * b = row + (size_t) u * 20;
+        uint32_t        w[5];
+        ldw_n<5>(b, w);  // [d m] [qs x4]
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            wq[i]     = (int) (w[1 + i] & 0x0F0F0F0Fu);
+            wq[4 + i] = (int) ((w[1 + i] >> 4) & 0x0F0F0F0Fu);
+        }
+        ws[0] = half_bits_to_float((uint16_t) (w[0] & 0xffff));
+        wm[0] = half_bits_to_float((uint16_t) (w[0] >> 16));
+    }
+};
+template <> struct Unit<T_Q5_0> : UnitBlock32<T_Q5_0, 22> {
+    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
+        const uint8_t * b = row + (size_t) u * 22;
+        uint32_t        w[6];
+        ldw_n<6>(b, w);  // [d | qh0 qh1] [qh2 qh3 | qs0 qs1] [qs2..5] [qs6..9] [qs10..13] [qs14 qs15 | next]
+        const float    d  = half_bits_to_float((uint16_t) (w[0] & 0xffff));
+        const uint32_t qh = funnel_r(w[0], w[1], 16);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t q = funnel_r(w[1 + i], w[2 + i], 16);
+            wq[i]            = (int) ((q & 0x0F0F0F0Fu) | (spread4(qh >> (4 * i)) << 4));
+            wq[4 + i]        = (int) (((q >> 4) & 0x0F0F0F0Fu) | (spread4(qh >> (16 + 4 * i)) << 4));
+        }
+        ws[0] = d;
+        wm[0] = -16.0f * d;
+    }
+};
+template <> struct Unit<T_Q5_1> : UnitBlock32<T_Q5_1, 24> {
+    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
+        const uint8_t * b = row + (size_t) u * 24;
+        uint32_t        w[6];
+        ldw_n<6>(b, w);  // [d m] [qh] [qs x4]
+        const uint32_t qh = w[1];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            wq[i]     = (int) ((w[2 + i] & 0x0F0F0F0Fu) | (spread4(qh >> (4 * i)) << 4));
+            wq[4 + i] = (int) (((w[2 + i] >> 4) & 0x0F0F0F0Fu) | (spread4(qh >> (16 + 4 * i)) << 4));
+        }
+        ws[0] = half_bits_to_float((uint16_t) (w[0] & 0xffff));
+        wm[0] = half_bits_to_float((uint16_t) (w[0] >> 16));
+    }
+};
+template <> struct Unit<T_Q8_0> : UnitBlock32<T_Q8_0, 34> {
+    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
+        const uint8_t * b = row + (size_t) u * 34;
+        uint32_t        w[9];
+        ldw_n<9>(b, w);  // [d | q0 q1] ... [q30 q31 | next]
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            wq[i] = (int) funnel_r(w[i], w[i + 1], 16);
+        }
+        ws[0] = half_bits_to_float((uint16_t) (w[0] & 0xffff));
+        wm[0] = 0.0f;
+    }
+};
+template <> struct Unit<T_MXFP4> : UnitBlock32<T_MXFP4, 17> {
+    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
+        const uint8_t * b = row + (size_t) u * 17;
+        uint32_t        w[5];
+        ldw_n<5>(b, w);  // [e | qs0 qs1 qs2] ... [qs15 | next]
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t q = funnel_r(w[i], w[i + 1], 8);
+            uint32_t       lo, hi;
+            mxfp4_lut(q, lo, hi);
+            wq[i]     = (int) lo;
+            wq[4 + i] = (int) hi;
+        }
+        ws[0] = e8m0_half_to_float((uint8_t) (w[0] & 0xff));
+        wm[0] = 0.0f;
+    }
+};
+
+// scale/min bytes j (0..7) of a K-quant super-block from the three scale words (get_scale_min_k4 in word form)
+B200Q_HD void k4_scale_min_words(const uint32_t (&s)[3], int j, int & sc, int & mn) {
+    // bytes: s[0] = q[0..3], s[1] = q[4..7], s[2] = q[8..11]
+    if (j < 4) {
+        sc = (int) ((s[0] >> (8 * j)) & 63);
+        mn = (int) ((s[1] >> (8 * j)) & 63);
+    } else {
+        const int      jj = j - 4;
+        const uint32_t hi = (s[2] >> (8 * jj)) & 0xff;  // q[j+4]
+        sc                = (int) ((hi & 0xF) | (((s[0] >> (8 * jj + 6)) & 3) << 4));
+        mn                = (int) ((hi >> 4) | (((s[1] >> (8 * jj + 6)) & 3) << 4));
+    }
+}
+
+template <> struct Unit<T_Q4_K> {
+    static constexpr int ELEMS = 64, NG = 2, GW = 8;
+    static B200Q_HD int  act_word(int u, int g) { return u * 16 + g * 8; }
+    static B200Q_HD int  act_blk(int u, int g) { return u * 2 + g; }
+    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[16], float (&ws)[2], float (&wm)[2]) {
+        const int       p = u & 3;
+        const uint8_t * b = row + (size_t) (u >> 2) * 144;
+        uint32_t        h[4];
+        ldw_n<4>(b, h);  // [d dmin] [scales x3]
+        uint32_t q[8];
+        ldw_n<8>(b + 16 + 32 * p, q);
+        const float    d    = half_bits_to_float((uint16_t) (h[0] & 0xffff));
+        const float    dmin = half_bits_to_float((uint16_t) (h[0] >> 16));
+        const uint32_t s[3] = { h[1], h[2], h[3] };
+        int            sc0, mn0, sc1, mn1;
+        k4_scale_min_words(s, 2 * p, sc0, mn0);
+        k4_scale_min_words(s, 2 * p + 1, sc1, mn1);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            wq[i]     = (int) (q[i] & 0x0F0F0F0Fu);
+            wq[8 + i] = (int) ((q[i] >> 4) & 0x0F0F0F0Fu);
+        }
+        ws[0] = d * (float) sc0;
+        ws[1] = d * (float) sc1;
+        wm[0] = -dmin * (float) mn0;
+        wm[1] = -dmin * (float) mn1;
+    }
+};
+template <> struct Unit<T_Q5_K> {
+    static constexpr int ELEMS = 64, NG = 2, GW = 8;
+    static B200Q_HD int  act_word(int u, int g) { return u * 16 + g * 8; }
+    static B200Q_HD int  act_blk(int u, int g) { return u * 2 + g; }
+    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[16], float (&ws)[2], float (&wm)[2]) {
+        const int       p = u & 3;
+        const uint8_t * b = row + (size_t) (u >> 2) * 176;
+        uint32_t        h[4];
+        ldw_n<4>(b, h);
+        uint32_t qh[8];
+        ldw_n<8>(b + 16, qh);
+        uint32_t q[8];
+        ldw_n<8>(b + 48 + 32 * p, q);
+        const float    d    = half_bits_to_float((uint16_t) (h[0] & 0xffff));
+        const float    dmin = half_bits_to_float((uint16_t) (h[0] >> 16));
+        const uint32_t s[3] = { h[1], h[2], h[3] };
+        int            sc0, mn0, sc1, mn1;
+        k4_scale_min_words(s, 2 * p, sc0, mn0);
+        k4_scale_min_words(s, 2 * p + 1, sc1, mn1);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t hb0 = (qh[i] >> (2 * p)) & 0x01010101u;
+            const uint32_t hb1 = (qh[i] >> (2 * p + 1)) & 0x01010101u;
+            wq[i]              = (int) ((q[i] & 0x0F0F0F0Fu) | (hb0 << 4));
+            wq[8 + i]          = (int) (((q[i] >> 4) & 0x0F0F0F0Fu) | (hb1 << 4));
+        }
+        ws[0] = d * (float) sc0;
+        ws[1] = d * (float) sc1;
+        wm[0] = -dmin * (float) mn0;
+        wm[1] = -dmin * (float) mn1;
+    }
+};
+template <> struct Unit<T_Q6_K> {
+    // unit u = (super-block sb, half n, 16-lane half h): elements 256 sb + 128 n + 32 quad + 16 h + [0,16), quad = 0..3
+    static constexpr int ELEMS = 64, NG = 4, GW = 4;
+    static B200Q_HD int  elem0(int u, int g) { return (u >> 2) * 256 + ((u >> 1) & 1) * 128 + g * 32 + (u & 1) * 16; }
+    static B200Q_HD int  act_word(int u, int g) { return elem0(u, g) >> 2; }
+    static B200Q_HD int  act_blk(int u, int g) { return elem0(u, g) >> 5; }
+    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[16], float (&ws)[4], float (&wm)[4]) {
+        const int       n = (u >> 1) & 1, h = u & 1;
+        const uint8_t * b = row + (size_t) (u >> 2) * 210;
+        uint32_t        l0[4], l1[4], qh[4];
+        ldw_n<4>(b + 64 * n + 16 * h, l0);        // ql[l],      l = 16h .. 16h+15
+        ldw_n<4>(b + 64 * n + 32 + 16 * h, l1);   // ql[l + 32]
+        ldw_n<4>(b + 128 + 32 * n + 16 * h, qh);  // qh[l]
+        // scales: sc[8n + 2*quad + h], d at +208
+        const uint32_t sw0 = ldw(b + 192 + 8 * n);      // sc[8n+0..3]
+        const uint32_t sw1 = ldw(b + 192 + 8 * n + 4);  // sc[8n+4..7]
+        const float    d   = half_bits_to_float((uint16_t) (ldw(b + 208) & 0xffff));
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t q0 = (l0[i] & 0x0F0F0F0Fu) | (((qh[i] >> 0) & 0x03030303u) << 4);
+            const uint32_t q1 = (l1[i] & 0x0F0F0F0Fu) | (((qh[i] >> 2) & 0x03030303u) << 4);
+            const uint32_t q2 = ((l0[i] >> 4) & 0x0F0F0F0Fu) | (((qh[i] >> 4) & 0x03030303u) << 4);
+            const uint32_t q3 = ((l1[i] >> 4) & 0x0F0F0F0Fu) | (((qh[i] >> 6) & 0x03030303u) << 4);
+            wq[0 + i]         = (int) vsub4_(q0, 0x20202020u);
+            wq[4 + i]         = (int) vsub4_(q1, 0x20202020u);
+            wq[8 + i]         = (int) vsub4_(q2, 0x20202020u);
+            wq[12 + i]        = (int) vsub4_(q3, 0x20202020u);
+        }
+        ws[0] = d * (float) (int8_t) (sw0 >> (8 * h));
+        ws[1] = d * (float) (int8_t) (sw0 >> (16 + 8 * h));
+        ws[2] = d * (float) (int8_t) (sw1 >> (8 * h));
+        ws[3] = d * (float) (int8_t) (sw1 >> (16 + 8 * h));
+        wm[0] = wm[1] = wm[2] = wm[3] = 0.0f;
+    }
+};
+
+// acc += sum over groups of  ws*d_x*dot + wm*s_x   against one activation column held as
+// int8x4 words `qa` and (d, s) pairs `ds`
+template <int T> B200Q_HD float unit_dot(const int (&wq)[Unit<T>::NG * Unit<T>::GW], const float (&ws)[Unit<T>::NG],
+                                         const float (&wm)[Unit<T>::NG], int u, const int * qa, const float2 * ds) {
+    using U   = Unit<T>;
+    float acc = 0.0f;
+#pragma unroll
+    for (int g = 0; g < U::NG; ++g) {
+        const int * a    = qa + U::act_word(u, g);
+        int         sumi = 0;
+#pragma unroll
+        for (int i = 0; i < U::GW; ++i) {
+            sumi = dp4a_(wq[g * U::GW + i], a[i], sumi);
+        }
+        const float2 x = ds[U::act_blk(u, g)];
+        acc += ws[g] * (x.x * (float) sumi) + wm[g] * x.y;
+    }
+    return acc;
+}
+
+}  // namespace b200q

@@ -113,6 +113,7 @@ int ref_dequantize(int type, const void * src, float * dst, int64_t n) {
 
 // activation row -> the CPU backend's vec_dot_type for `wtype` (q8_0 / q8_1 / q8_K)
 int ref_act_quantize(int wtype, const float * src, void * dst, int64_t n) {
+    ggml_cpu_init();  // fp16 lookup tables used by the CPU kernels
     const ggml_type_traits_cpu * tc = ggml_get_type_traits_cpu((ggml_type) wtype);
     if (!tc) return -1;
     const ggml_type_traits_cpu * tv = ggml_get_type_traits_cpu(tc->vec_dot_type);
@@ -123,6 +124,7 @@ int ref_act_quantize(int wtype, const float * src, void * dst, int64_t n) {
 
 // one dot product, exactly as mul_mat_one_chunk calls it (nrc = 1)
 int ref_vec_dot(int wtype, int64_t n, const void * w_row, const void * act_q, float * out) {
+    ggml_cpu_init();
     const ggml_type_traits_cpu * tc = ggml_get_type_traits_cpu((ggml_type) wtype);
     if (!tc || !tc->vec_dot) return -1;
     tc->vec_dot((int) n, out, 0, w_row, 0, act_q, 0, 1);

@@ -1,0 +1,51 @@
+"""The C-ABI library loads and exports every symbol include/b200q.h declares (no compute without a GPU)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared(header):
+    src = open(os.path.join(ROOT, "include", header)).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"B200Q_API[^;(]*?\b(b200q_\w+)\s*\(", src)))
+
+
+def test_header_declares_the_expected_entry_points():
+    names = declared("b200q.h")
+    for must in ("b200q_mul_mat", "b200q_mul_mat_id", "b200q_get_rows", "b200q_dequantize", "b200q_mul_mat_host"):
+        assert must in names
+
+
+def test_library_exports_every_declared_symbol():
+    import b200q
+    if not os.path.exists(b200q.LIB_PATH):
+        import __graft_entry__ as g
+        g.build()
+    L = ctypes.CDLL(b200q.LIB_PATH)
+    missing = [n for n in declared("b200q.h") if not hasattr(L, n)]
+    assert not missing, missing
+    assert sorted(b200q.EXPORTS) == [n for n in declared("b200q.h") if n in b200q.EXPORTS]
+    assert set(declared("b200q.h")) - set(b200q.EXPORTS) <= set(n for n in declared("b200q.h") if "rowsplit" in n or "graph" in n or "route" in n)
+
+
+def test_type_table_matches_ggml_block_sizes():
+    import b200q
+    L = b200q.lib()
+    for t, (be, bb) in b200q.BLCK.items():
+        assert L.b200q_blck_size(t) == be
+        assert L.b200q_type_size(t) == bb
+    assert L.b200q_row_size(b200q.Q4_K, 4096) == 2304
+    assert L.b200q_row_size(b200q.MXFP4, 2880) == 1530
+
+
+def test_compute_fails_loudly_without_a_gpu():
+    import torch
+    import b200q
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(RuntimeError):
+        b200q.dequantize(b200q.QTensor(b200q.Q4_0, (1, 32), None))
