@@ -12,6 +12,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <set>
@@ -81,6 +82,8 @@ int ensure_smem_attr(const void * fn, int bytes) {
     return 0;
 }
 
+unsigned long long * g_ts = nullptr;  // debug timestamps (b200q_debug_timestamps)
+
 inline int round_up(int x, int a) { return (x + a - 1) / a * a; }
 
 // ---- GEMV configuration ------------------------------------------------------------------------------
@@ -90,50 +93,74 @@ struct GemvPlan {
     int        smem = 0;
 };
 
-// fills the tiling fields of plan.p for `ncols` activation columns; false if it cannot fit in shared memory
+// fills the tiling fields of plan.p for `ncols` activation columns; false if it cannot fit in shared memory.
+// One CTA per SM and (when it fits) <= ~100 KB of shared memory so that the next GEMV's CTAs can become
+// co-resident under programmatic dependent launch and prefetch their weights.
 bool plan_gemv(GemvPlan & plan, int type, int ncols, const DevInfo & di) {
     GemvParams & p = plan.p;
     p.row_bytes    = (int) ((long long) p.k / blck_elems(type) * blck_bytes(type));
     p.contiguous   = p.w_nb1 == p.row_bytes;
     p.smem_pitch   = p.contiguous ? (int) p.w_nb1 : round_up(p.row_bytes + 31, 16);
-    const int pitch  = p.smem_pitch;
-    const int budget = 24 * 1024;
-    p.wpr            = 8;
+    const int pitch = p.smem_pitch;
+    const int nu    = p.k / gemv_unit_elems(type);
+    int       lpr   = 1;
+    while (lpr < 32 && lpr < nu) lpr *= 2;
+    p.lpr        = lpr;
+    const int RW = 32 / lpr, RB = 2, NW = 8;
+
+    // activations: int8 columns (padded to 128 B so the chunk swizzle stays inside a column) + (d, s) pairs
+    p.act_col_bytes        = round_up(p.k, 128);
+    p.ds_off               = gemv_act_off() + ncols * p.act_col_bytes;
+    const long long act_end = (long long) p.ds_off + (long long) ncols * (p.k / 32) * 8;
+    if (act_end > di.max_smem - 4096) return false;
+    p.stage_off = round_up((int) act_end, 128);
+
+    // pick (wpr, groups): stage = one pass of the owning group, aim for ~16 KB
+    const double target = 16.0 * 1024;
+    double       best   = 1e30;
+    int          bw = 1, bg = 1;
     for (int wpr = 1; wpr <= 8; wpr *= 2) {
-        if ((long long) gemv_pass_rows(wpr) * pitch <= budget) {
-            p.wpr = wpr;
-            break;
+        if (wpr > 1 && (lpr < 32 || nu < 32 * wpr)) break;
+        for (int g = 1; g * wpr <= NW; g *= 2) {
+            if (g > 1 && p.nch > 1) break;
+            const long long bytes = (long long) (NW / g / wpr) * RW * RB * pitch;
+            double          cost  = bytes > target ? bytes / target : target / bytes;
+            cost *= 1.0 + 0.08 * (wpr > 1 ? wpr : 0) + 0.02 * g;  // prefer no cross-warp reduction, fewer groups
+            if (cost < best) {
+                best = cost;
+                bw   = wpr;
+                bg   = g;
+            }
         }
     }
-    const int       pass_rows  = gemv_pass_rows(p.wpr);
-    const long long pass_bytes = (long long) pass_rows * pitch;
-    p.passes                   = (int) std::max<long long>(1, budget / pass_bytes);
-    // keep a few stages of work per CTA so the ring actually pipelines
-    const long long rows_total   = (long long) p.nch * p.m;
-    const long long rows_per_cta = std::max<long long>(1, rows_total / std::max(1, di.sms * 2));
-    while (p.passes > 1 && (long long) p.passes * pass_rows * 3 > rows_per_cta) {
-        --p.passes;
+    p.wpr    = bw;
+    p.groups = bg;
+    const long long rows_total = (long long) p.nch * p.m;
+    for (;;) {
+        const int       pass_rows  = (NW / p.groups / p.wpr) * RW * RB;
+        const long long pass_bytes = (long long) pass_rows * pitch;
+        p.passes                   = (int) std::max<long long>(1, (long long) (20 * 1024) / pass_bytes);
+        // keep a few stages of work per CTA so the ring actually pipelines
+        const long long rows_per_cta = std::max<long long>(1, rows_total / std::max(1, di.sms));
+        while (p.passes > 1 && (long long) p.passes * pass_rows * 3 > rows_per_cta) --p.passes;
+        p.stage_rows                = pass_rows * p.passes;
+        const long long stage_bytes = 16 + (long long) p.stage_rows * pitch + 48;
+        p.stage_bytes               = round_up((int) std::min<long long>(stage_bytes, 1 << 28), 128);
+        const int soft              = 100 * 1024;  // two kernels co-resident
+        int       S                 = (int) ((soft - p.stage_off) / p.stage_bytes);
+        if (S < std::max(3, p.groups + 1)) S = (int) ((di.max_smem - p.stage_off) / p.stage_bytes);
+        if (S >= std::max(2, p.groups + 1)) {
+            p.nstages = std::min(S, 8);
+            break;
+        }
+        if (p.groups > 1) { p.groups /= 2; continue; }   // fewer, larger stages cannot help; fewer groups can
+        if (p.wpr < 8 && lpr == 32 && nu >= 64 * p.wpr) { p.wpr *= 2; continue; }
+        return false;
     }
-    const long long stage_bytes = 16 + (long long) p.passes * pass_bytes + 48;
-    if (stage_bytes > di.max_smem) return false;
-    p.stage_bytes             = round_up((int) stage_bytes, 128);
-    const long long act_bytes = (long long) ncols * (p.k + p.k / 4);
-    const long long stage_off = round_up((int) std::min<long long>(gemv_fixed_smem() + act_bytes, 1 << 30), 128);
-    if (stage_off > di.max_smem) return false;
-    p.stage_off = (int) stage_off;
-
-    const int half = (di.max_smem - 2048) / 2;  // two resident CTAs per SM
-    int       S    = (int) ((half - stage_off) / p.stage_bytes);
-    int       ctas = 2;
-    if (S < 3 || ncols > 4) {
-        ctas = 1;
-        S    = (int) ((di.max_smem - stage_off) / p.stage_bytes);
-    }
-    if (S < 2) return false;
-    p.nstages = std::min(S, ctas == 2 ? 6 : 8);
     plan.smem = p.stage_off + p.nstages * p.stage_bytes;
-    const long long want = (rows_total + pass_rows - 1) / pass_rows;
-    plan.grid            = (int) std::max<long long>(1, std::min<long long>((long long) di.sms * ctas, want));
+    const int       pass_rows = p.stage_rows / p.passes;
+    const long long want      = (rows_total + pass_rows - 1) / pass_rows;
+    plan.grid                 = (int) std::max<long long>(1, std::min<long long>((long long) di.sms, want));
     return true;
 }
 
@@ -144,7 +171,15 @@ int launch_gemv(GemvPlan & plan, int type, int ncols, uint32_t flags, cudaStream
     if (int rc = ensure_smem_attr((const void *) fn, di.max_smem)) return rc;
     const bool pdl        = !(flags & B200Q_FLAG_NO_PDL);
     plan.p.early_prefetch = pdl && (flags & B200Q_FLAG_WEIGHTS_IMMUTABLE) ? 1 : 0;
+    plan.p.ts             = g_ts;
 
+    static const bool debug = getenv("B200Q_DEBUG") != nullptr;
+    if (debug) {
+        fprintf(stderr, "[b200q] gemv type=%d n=%d k=%d m=%d nch=%d grid=%d smem=%d lpr=%d wpr=%d groups=%d passes=%d stage_rows=%d stage_bytes=%d S=%d contiguous=%d pdl=%d early=%d\n",
+                type, ncols, plan.p.k, plan.p.m, plan.p.nch, plan.grid, plan.smem, plan.p.lpr, plan.p.wpr, plan.p.groups,
+                plan.p.passes, plan.p.stage_rows, plan.p.stage_bytes, plan.p.nstages, plan.p.contiguous, (int) pdl,
+                plan.p.early_prefetch);
+    }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim          = dim3(plan.grid);
     cfg.blockDim         = dim3(gemv_threads());
@@ -167,6 +202,8 @@ bool aligned16(const void * p, long long stride) { return ((uintptr_t) p & 15) =
 extern "C" {
 
 int          b200q_version(void) { return 100; }
+// development aid: device buffer of [grid][8] u64 that GEMV CTAs fill with %globaltimer stamps (NULL = off)
+B200Q_API void b200q_debug_timestamps(void * dev_buf) { g_ts = (unsigned long long *) dev_buf; }
 const char * b200q_last_error(void) { return g_err.c_str(); }
 
 int b200q_device_count(void) {

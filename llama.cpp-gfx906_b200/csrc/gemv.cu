@@ -9,18 +9,20 @@
 //     SASS UBLKCP) into a ring of mbarrier-guarded stages, evict-first in L2.  17/18/34/210-byte blocks
 //     never see a misaligned global access; lanes decode at arbitrary byte offsets from smem.
 //   * the q8 activation quantization (per 32 values: int8 + fp32 scale + fp32 scale*sum) is fused into the
-//     prologue: each CTA quantizes the activation columns once into shared memory, no second launch,
-//     no global scratch buffer.
-//   * consumer warps run integer dots with dp4a (units.cuh), two rows per warp pass so every activation
-//     word read from shared memory is used twice, warp-shuffle reduction, fixed summation order
-//     (bit-reproducible, which the row-split parity test relies on).
-//   * launched with programmatic stream serialization: griddepcontrol.launch_dependents is issued at once
-//     and, when the caller marks the weights immutable, the producer starts streaming weights BEFORE
-//     griddepcontrol.wait, so the HBM pipe stays busy across back-to-back GEMVs of a decode step.
+//     prologue: each CTA quantizes the activation columns once into shared memory (16-byte chunks XOR-swizzled
+//     so the strided per-lane reads are bank-conflict free), no second launch, no global scratch buffer.
+//   * 8 consumer warps run integer dots with dp4a (units.cuh), two rows per lane so every activation word
+//     read from shared memory is used twice; fixed summation order (bit-reproducible, which the row-split
+//     parity test relies on).  Short rows put several rows in one warp (lpr lanes per row), long rows put
+//     several warps on one row pair (wpr), medium rows split the warps into groups that own alternate stages.
+//   * one CTA per SM and <= ~100 KB of shared memory, launched with programmatic stream serialization:
+//     griddepcontrol.launch_dependents is issued at once, the NEXT GEMV's CTAs become co-resident and — when
+//     the caller marks the weights immutable — start streaming their weights BEFORE griddepcontrol.wait, so
+//     the HBM pipe stays busy across the back-to-back GEMVs of a decode step.
 //
-// Work decomposition: the (channel, row) space is cut into contiguous ranges, one per CTA (grid = a multiple
-// of the SM count); a channel is one (i12, i13) batch element of MUL_MAT or one (token, slot) pair of
-// MUL_MAT_ID (expert id read on the device from `ids`, no host round trip).
+// Work decomposition: the (channel, row) space is cut into contiguous ranges, one per CTA; a channel is one
+// (i12, i13) batch element of MUL_MAT or one (token, slot) pair of MUL_MAT_ID (expert id read on the device
+// from `ids`, no host round trip).  All shared-memory addressing is by 32-bit offset into b200q_smem.
 #include "gemv.cuh"
 #include "units.cuh"
 
@@ -30,25 +32,28 @@ namespace b200q {
 
 namespace {
 
-constexpr int NW          = 8;   // consumer warps
-constexpr int RB          = 2;   // rows per warp pass
-constexpr int NTHREADS    = (NW + 1) * 32;
-constexpr int MAX_STAGES  = 8;
-constexpr int RED_FLOATS  = 2 * NW * RB * 8;
+constexpr int NW         = 8;  // consumer warps
+constexpr int RB         = 2;  // rows per lane
+constexpr int NTHREADS   = (NW + 1) * 32;
+constexpr int MAX_STAGES = 8;
+// shared memory map (byte offsets)
+constexpr uint32_t OFF_FULL  = 0;     // MAX_STAGES mbarriers
+constexpr uint32_t OFF_EMPTY = 64;    // MAX_STAGES mbarriers
+constexpr uint32_t OFF_RED   = 128;   // [2][NW][RB*8] floats for the cross-warp reduction
+constexpr uint32_t OFF_ACT   = 128 + 2 * NW * RB * 8 * 4;  // quantized activations
 
-__device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t smem_base_u32() { return (uint32_t) __cvta_generic_to_shared(b200q_smem); }
 
-__device__ __forceinline__ void mbar_init(uint64_t * bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
-__device__ __forceinline__ void mbar_arrive(uint64_t * bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void mbar_expect_tx(uint64_t * bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint64_t * bar, uint32_t parity) {
-    const uint32_t a = smem_u32(bar);
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
@@ -57,7 +62,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t * bar, uint32_t parity) {
         "@p bra DONE_%=;\n"
         "bra WAIT_%=;\n"
         "DONE_%=:\n"
-        "}\n" ::"r"(a),
+        "}\n" ::"r"(bar),
         "r"(parity)
         : "memory");
 }
@@ -67,17 +72,26 @@ __device__ __forceinline__ uint64_t l2_evict_first_policy() {
     return pol;
 }
 // 1-D bulk copy global -> shared, completion signalled on an mbarrier (TMA, UBLKCP in SASS)
-__device__ __forceinline__ void bulk_g2s(void * dst_smem, const void * src_gmem, uint32_t bytes, uint64_t * bar,
+__device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void * src_gmem, uint32_t bytes, uint32_t bar,
                                          uint64_t policy) {
     asm volatile(
         "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::
-            "r"(smem_u32(dst_smem)),
-        "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+            "r"(dst_smem),
+        "l"(src_gmem), "r"(bytes), "r"(bar), "l"(policy)
         : "memory");
 }
-__device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(NW * 32) : "memory"); }
+__device__ __forceinline__ void named_bar(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void stamp(const GemvParams & p, int slot) {
+    if (p.ts) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        p.ts[blockIdx.x * 8 + slot] = t;
+    }
+}
 
 struct ChannelOff {
     long long w, a, d;
@@ -93,6 +107,8 @@ __device__ __forceinline__ ChannelOff channel_offsets(const GemvParams & p, int 
         o.w         = (long long) e * p.w_nb2;
         o.a         = (long long) t * p.a_nb2 + (p.b_bcast ? 0 : (long long) s * p.a_nb1);
         o.d         = (long long) t * p.d_nb2 + (long long) s * p.d_nb1;
+    } else if (p.nch == 1) {
+        o.w = o.a = o.d = 0;
     } else {
         const int i13 = c / p.ne12;
         const int i12 = c - i13 * p.ne12;
@@ -103,30 +119,39 @@ __device__ __forceinline__ ChannelOff channel_offsets(const GemvParams & p, int 
     return o;
 }
 
+// physical word index of logical activation word `widx` inside one column: 16-byte chunks are XOR-swizzled
+// within aligned groups of 8 so that lanes reading chunks at a stride of 2 or 4 hit 8 different bank groups
+__device__ __forceinline__ uint32_t act_swz_chunk(uint32_t chunk) { return chunk ^ ((chunk >> 3) & 7u); }
+
 // quantize NCOLS activation columns of length k (f32, global) into shared memory:
-//   qa  int8  [NCOLS][k]          (as int8x4 words)
-//   ds  float2[NCOLS][k/32]       (d, d * sum(q))
+//   int8x4 words at OFF_ACT + j * act_col_bytes (swizzled), (d, d*sum(q)) float2 at ds_off + (j*k/32 + blk)*8
 // 8 lanes share one 32-value block (float4 each); executed by the NW consumer warps only.
 template <int NCOLS>
-__device__ __forceinline__ void quantize_activations(const GemvParams & p, const char * act_base, int * qa, float2 * ds,
-                                                     int tid) {
-    const int chunks_per_col = p.k >> 2;
+__device__ __forceinline__ void quantize_activations(const GemvParams & p, const char * act_base, int tid) {
+    const int chunks_per_col = p.k >> 2;  // float4 chunks == int8x4 words
     const int total          = NCOLS * chunks_per_col;
+    const int nblk           = p.k >> 5;
     for (int base = 0; base < total; base += NW * 32) {
         const int  q      = base + tid;
         const bool active = q < total;
-        const int  j      = active ? q / chunks_per_col : 0;
-        const int  pos    = active ? q - j * chunks_per_col : 0;
-        float4     v      = make_float4(0.f, 0.f, 0.f, 0.f);
+        int        j      = 0;
+        int        pos    = active ? q : 0;
+        if (NCOLS > 1) {
+            while (pos >= chunks_per_col) {
+                pos -= chunks_per_col;
+                ++j;
+            }
+        }
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
         if (active) {
             const float * src = (const float *) (act_base + (long long) j * p.a_nb1) + 4 * pos;
             if (p.act_vec4) {
-                v = *(const float4 *) src;
+                v = __ldg((const float4 *) src);
             } else {
-                v.x = src[0];
-                v.y = src[1];
-                v.z = src[2];
-                v.w = src[3];
+                v.x = __ldg(src);
+                v.y = __ldg(src + 1);
+                v.z = __ldg(src + 2);
+                v.w = __ldg(src + 3);
             }
         }
         float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
@@ -144,44 +169,66 @@ __device__ __forceinline__ void quantize_activations(const GemvParams & p, const
         s += __shfl_xor_sync(0xffffffffu, s, 2);
         s += __shfl_xor_sync(0xffffffffu, s, 4);
         if (active) {
-            qa[q] = (q0 & 0xff) | ((q1 & 0xff) << 8) | ((q2 & 0xff) << 16) | ((q3 & 0xff) << 24);
+            const uint32_t word = (act_swz_chunk((uint32_t) pos >> 2) << 2) | ((uint32_t) pos & 3u);
+            *(int *) (b200q_smem + OFF_ACT + (uint32_t) j * p.act_col_bytes + word * 4) =
+                (q0 & 0xff) | ((q1 & 0xff) << 8) | ((q2 & 0xff) << 16) | ((q3 & 0xff) << 24);
             if ((pos & 7) == 0) {
-                ds[j * (p.k >> 5) + (pos >> 3)] = make_float2(d, d * (float) s);
+                *(float2 *) (b200q_smem + p.ds_off + (uint32_t) (j * nblk + (pos >> 3)) * 8) =
+                    make_float2(d, d * (float) s);
             }
         }
     }
 }
 
-template <int T, int NCOLS>
-__global__ void __launch_bounds__(NTHREADS, NCOLS <= 4 ? 2 : 1) gemv_stream_kernel(const GemvParams p) {
-    using U = Unit<T>;
-    extern __shared__ __align__(128) uint8_t smem[];
-    uint64_t * full   = (uint64_t *) smem;
-    uint64_t * empty  = full + MAX_STAGES;
-    float *    red    = (float *) (smem + 128);
-    int *      qa     = (int *) (smem + 128 + RED_FLOATS * 4);
-    float2 *   ds     = (float2 *) ((uint8_t *) qa + (size_t) NCOLS * p.k);
-    uint8_t *  stages = smem + p.stage_off;
+// the stage walk shared by producer and consumers: (channel, first row, row count) of consecutive stages
+struct StageWalk {
+    long long cur, end;
+    int       c, r, m, stage_rows;
+    __device__ __forceinline__ void init(long long R0, long long R1, int m_, int stage_rows_) {
+        cur = R0; end = R1; m = m_; stage_rows = stage_rows_;
+        c = (int) (R0 / m_);
+        r = (int) (R0 - (long long) c * m_);
+    }
+    __device__ __forceinline__ bool done() const { return cur >= end; }
+    __device__ __forceinline__ int  nrows() const {
+        int       n    = m - r < stage_rows ? m - r : stage_rows;
+        long long left = end - cur;
+        return left < n ? (int) left : n;
+    }
+    __device__ __forceinline__ void advance(int n) {
+        cur += n;
+        r += n;
+        if (r >= m) { r = 0; ++c; }
+    }
+};
 
-    const int warp = threadIdx.x >> 5;
-    const int lane = threadIdx.x & 31;
+template <int T, int NCOLS>
+__global__ void __launch_bounds__(NTHREADS, 2) gemv_stream_kernel(const GemvParams p) {
+    using U = Unit<T>;
+    const uint32_t sb   = smem_base_u32();
+    const int      warp = threadIdx.x >> 5;
+    const int      lane = threadIdx.x & 31;
+    const int      S    = p.nstages;
+    const int      G    = p.groups;
+    const int      WS   = NW / G;  // warps per group
 
     const long long rows_total = (long long) p.nch * p.m;
     const long long R0         = rows_total * blockIdx.x / gridDim.x;
     const long long R1         = rows_total * (blockIdx.x + 1) / gridDim.x;
-    const int       pass_rows  = (NW * RB) / p.wpr;
-    const int       stage_rows = pass_rows * p.passes;
-    const int       S          = p.nstages;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < S; ++s) {
-            mbar_init(&full[s], 1);
-            mbar_init(&empty[s], NW);
+            mbar_init(sb + OFF_FULL + 8 * s, 1);
+            mbar_init(sb + OFF_EMPTY + 8 * s, WS);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+    if (threadIdx.x == 0) stamp(p, 0);
     pdl_launch_dependents();
+
+    StageWalk walk;
+    walk.init(R0, R1, p.m, p.stage_rows);
 
     if (warp == NW) {
         // ------------------------------------------------------------------ producer: one elected lane
@@ -190,40 +237,40 @@ __global__ void __launch_bounds__(NTHREADS, NCOLS <= 4 ? 2 : 1) gemv_stream_kern
                 pdl_wait();
             }
             const uint64_t pol = l2_evict_first_policy();
-            long long      cur = R0;
-            for (int it = 0; cur < R1; ++it) {
-                const int c     = (int) (cur / p.m);
-                const int r     = (int) (cur - (long long) c * p.m);
-                long long left  = R1 - cur;
-                int       nrows = p.m - r < stage_rows ? p.m - r : stage_rows;
-                nrows           = left < nrows ? (int) left : nrows;
-                const int s     = it % S;
-                if (it >= S) {
-                    mbar_wait(&empty[s], ((it / S) & 1) ^ 1);
+            int            s = 0, round = 0;
+            while (!walk.done()) {
+                const int nrows = walk.nrows();
+                if (round > 0) {
+                    mbar_wait(sb + OFF_EMPTY + 8 * s, (round & 1) ^ 1);
                 }
-                const ChannelOff o   = channel_offsets(p, c);
-                const uint8_t *  src = p.w + o.w + (long long) r * p.w_nb1;
-                uint8_t *        dst = stages + (size_t) s * p.stage_bytes;
+                const ChannelOff o    = channel_offsets(p, walk.c);
+                const uint8_t *  src  = p.w + o.w + (long long) walk.r * p.w_nb1;
+                const uint32_t   dst  = sb + p.stage_off + (uint32_t) s * p.stage_bytes;
+                const uint32_t   full = sb + OFF_FULL + 8 * s;
                 if (p.contiguous) {
                     const uint32_t lead  = (uint32_t) ((uintptr_t) src & 15);
                     const uint32_t bytes = (lead + (uint32_t) nrows * (uint32_t) p.w_nb1 + 15u) & ~15u;
-                    mbar_expect_tx(&full[s], bytes);
-                    bulk_g2s(dst, src - lead, bytes, &full[s], pol);
+                    mbar_expect_tx(full, bytes);
+                    bulk_g2s(dst, src - lead, bytes, full, pol);
                 } else {
                     uint32_t total = 0;
                     for (int rr = 0; rr < nrows; ++rr) {
                         const uint32_t lead = (uint32_t) ((uintptr_t) (src + (long long) rr * p.w_nb1) & 15);
                         total += (lead + (uint32_t) p.row_bytes + 15u) & ~15u;
                     }
-                    mbar_expect_tx(&full[s], total);
+                    mbar_expect_tx(full, total);
                     for (int rr = 0; rr < nrows; ++rr) {
                         const uint8_t * a     = src + (long long) rr * p.w_nb1;
                         const uint32_t  lead  = (uint32_t) ((uintptr_t) a & 15);
                         const uint32_t  bytes = (lead + (uint32_t) p.row_bytes + 15u) & ~15u;
-                        bulk_g2s(dst + (size_t) rr * p.smem_pitch, a - lead, bytes, &full[s], pol);
+                        bulk_g2s(dst + (uint32_t) rr * p.smem_pitch, a - lead, bytes, full, pol);
                     }
                 }
-                cur += nrows;
+                walk.advance(nrows);
+                if (++s == S) {
+                    s = 0;
+                    ++round;
+                }
             }
         }
         return;
@@ -231,157 +278,189 @@ __global__ void __launch_bounds__(NTHREADS, NCOLS <= 4 ? 2 : 1) gemv_stream_kern
 
     // ---------------------------------------------------------------------- consumers
     pdl_wait();  // activations (and dst) belong to the previous kernels of the stream
+    if (threadIdx.x == 0) stamp(p, 1);
 
-    const int tid  = threadIdx.x;  // 0 .. NW*32-1
-    const int g    = warp / p.wpr;
-    const int part = warp - g * p.wpr;
-    const int nu   = p.k / U::ELEMS;
+    const int tid   = threadIdx.x;       // 0 .. NW*32-1
+    const int gi    = warp / WS;         // group
+    const int wi    = warp - gi * WS;    // warp inside the group
+    const int slot  = wi / p.wpr;        // row-pair slot inside a pass
+    const int part  = wi - slot * p.wpr; // which slice of the row this warp sums
+    const int lpr   = p.lpr;
+    const int RW    = 32 / lpr;          // rows per warp step (per rr)
+    const int sub   = lane & (lpr - 1);
+    const int lrow  = lane / lpr;
+    const int nu    = p.k / U::ELEMS;
+    const int ustep = lpr * p.wpr;
+    const int pass_rows = (WS / p.wpr) * RW * RB;
+    const int nblk  = p.k >> 5;
 
-    int       cur_ch = -1;
-    long long d_off  = 0;
+    int       cur_ch  = -1;
+    long long d_off   = 0;
+    uint32_t  lead0   = 0;
     int       red_buf = 0;
-    long long cur     = R0;
-    for (int it = 0; cur < R1; ++it) {
-        const int c     = (int) (cur / p.m);
-        const int r     = (int) (cur - (long long) c * p.m);
-        long long left  = R1 - cur;
-        int       nrows = p.m - r < stage_rows ? p.m - r : stage_rows;
-        nrows           = left < nrows ? (int) left : nrows;
-        const int s     = it % S;
-
-        const ChannelOff o = channel_offsets(p, c);
+    int       s = 0, round = 0, gsel = 0;
+    while (!walk.done()) {
+        const int nrows = walk.nrows();
+        const int c = walk.c, r = walk.r;
         if (c != cur_ch) {
+            const ChannelOff o = channel_offsets(p, c);
             if (cur_ch >= 0) {
-                consumer_bar();  // everyone is done reading the previous channel's activations
+                named_bar(9, NW * 32);  // everyone is done reading the previous channel's activations
             }
-            quantize_activations<NCOLS>(p, (const char *) p.act + o.a, qa, ds, tid);
-            consumer_bar();
+            quantize_activations<NCOLS>(p, (const char *) p.act + o.a, tid);
+            named_bar(9, NW * 32);
+            if (threadIdx.x == 0 && cur_ch < 0) stamp(p, 2);
             cur_ch = c;
             d_off  = o.d;
+            lead0  = (uint32_t) ((uintptr_t) (p.w + o.w) & 15);
         }
+        if (gsel == gi) {
+            mbar_wait(sb + OFF_FULL + 8 * s, round & 1);
+            if (threadIdx.x == 0 && round == 0 && s == 0) stamp(p, 3);
+            const uint32_t stage = p.stage_off + (uint32_t) s * p.stage_bytes;
+            // byte offset (inside b200q_smem) of row `row` of this stage
+            const uint32_t row_lead = (lead0 + (uint32_t) (((long long) r * p.w_nb1) & 15)) & 15u;
 
-        mbar_wait(&full[s], (it / S) & 1);
-
-        const uint8_t * src0  = p.w + o.w + (long long) r * p.w_nb1;
-        const uint8_t * sbase = stages + (size_t) s * p.stage_bytes;
-
-        for (int pass = 0; pass * pass_rows < nrows; ++pass) {
-            const int row0 = pass * pass_rows + g * RB;
-            float     acc[RB][NCOLS];
+            for (int pass = 0; pass * pass_rows < nrows; ++pass) {
+                const int row_a = pass * pass_rows + slot * (RW * RB) + lrow;  // rr = 0; rr = 1 is RW rows further
+                float     acc[RB][NCOLS];
 #pragma unroll
-            for (int rr = 0; rr < RB; ++rr) {
-#pragma unroll
-                for (int j = 0; j < NCOLS; ++j) {
-                    acc[rr][j] = 0.0f;
-                }
-            }
-            const uint8_t * rowp[RB];
-            bool            valid[RB];
-#pragma unroll
-            for (int rr = 0; rr < RB; ++rr) {
-                const int row = row0 + rr;
-                valid[rr]     = row < nrows;
-                if (p.contiguous) {
-                    rowp[rr] = sbase + ((uintptr_t) src0 & 15) + (size_t) row * p.w_nb1;
-                } else {
-                    rowp[rr] = sbase + (size_t) row * p.smem_pitch + ((uintptr_t) (src0 + (long long) row * p.w_nb1) & 15);
-                }
-            }
-            if (valid[0]) {
-                for (int u = part * 32 + lane; u < nu; u += 32 * p.wpr) {
-                    int   wq[RB][U::NG * U::GW];
-                    float ws[RB][U::NG], wm[RB][U::NG];
-                    U::decode(rowp[0], u, wq[0], ws[0], wm[0]);
-                    if (valid[1]) {
-                        U::decode(rowp[1], u, wq[1], ws[1], wm[1]);
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < U::NG * U::GW; ++i) {
-                            wq[1][i] = 0;
-                        }
-#pragma unroll
-                        for (int i = 0; i < U::NG; ++i) {
-                            ws[1][i] = 0.0f;
-                            wm[1][i] = 0.0f;
-                        }
-                    }
+                for (int rr = 0; rr < RB; ++rr) {
 #pragma unroll
                     for (int j = 0; j < NCOLS; ++j) {
-                        const int *    qaj = qa + j * (p.k >> 2);
-                        const float2 * dsj = ds + j * (p.k >> 5);
+                        acc[rr][j] = 0.0f;
+                    }
+                }
+                const bool v0 = row_a < nrows;
+                const bool v1 = row_a + RW < nrows;
+                uint32_t   rowp0, rowp1;
+                if (p.contiguous) {
+                    rowp0 = stage + row_lead + (uint32_t) row_a * (uint32_t) p.smem_pitch;
+                    rowp1 = rowp0 + (uint32_t) RW * (uint32_t) p.smem_pitch;
+                } else {
+                    const uint32_t l0 = (lead0 + (uint32_t) (((long long) (r + row_a) * p.w_nb1) & 15)) & 15u;
+                    const uint32_t l1 = (lead0 + (uint32_t) (((long long) (r + row_a + RW) * p.w_nb1) & 15)) & 15u;
+                    rowp0             = stage + (uint32_t) row_a * (uint32_t) p.smem_pitch + l0;
+                    rowp1             = stage + (uint32_t) (row_a + RW) * (uint32_t) p.smem_pitch + l1;
+                }
+                if (v0) {
+                    for (int u = part * lpr + sub; u < nu; u += ustep) {
+                        int   wq[RB][U::NG * U::GW];
+                        float ws[RB][U::NG], wm[RB][U::NG];
+                        U::decode(rowp0, u, wq[0], ws[0], wm[0]);
+                        if (v1) {
+                            U::decode(rowp1, u, wq[1], ws[1], wm[1]);
+                        } else {
 #pragma unroll
-                        for (int gi = 0; gi < U::NG; ++gi) {
-                            const int * a = qaj + U::act_word(u, gi);
-                            int         aw[U::GW];
-#pragma unroll
-                            for (int i4 = 0; i4 < U::GW / 4; ++i4) {
-                                const int4 t  = *(const int4 *) (a + 4 * i4);
-                                aw[4 * i4 + 0] = t.x;
-                                aw[4 * i4 + 1] = t.y;
-                                aw[4 * i4 + 2] = t.z;
-                                aw[4 * i4 + 3] = t.w;
+                            for (int i = 0; i < U::NG * U::GW; ++i) {
+                                wq[1][i] = 0;
                             }
-                            const float2 x = dsj[U::act_blk(u, gi)];
 #pragma unroll
-                            for (int rr = 0; rr < RB; ++rr) {
-                                int sumi = 0;
+                            for (int i = 0; i < U::NG; ++i) {
+                                ws[1][i] = 0.0f;
+                                wm[1][i] = 0.0f;
+                            }
+                        }
 #pragma unroll
-                                for (int i = 0; i < U::GW; ++i) {
-                                    sumi = dp4a_(wq[rr][gi * U::GW + i], aw[i], sumi);
+                        for (int j = 0; j < NCOLS; ++j) {
+                            const uint32_t colb = OFF_ACT + (uint32_t) j * p.act_col_bytes;
+#pragma unroll
+                            for (int g = 0; g < U::NG; ++g) {
+                                const uint32_t chunk0 = (uint32_t) U::act_word(u, g) >> 2;
+                                int            aw[U::GW];
+#pragma unroll
+                                for (int i4 = 0; i4 < U::GW / 4; ++i4) {
+                                    const int4 t   = lds128(colb + act_swz_chunk(chunk0 + i4) * 16);
+                                    aw[4 * i4 + 0] = t.x;
+                                    aw[4 * i4 + 1] = t.y;
+                                    aw[4 * i4 + 2] = t.z;
+                                    aw[4 * i4 + 3] = t.w;
                                 }
-                                acc[rr][j] += ws[rr][gi] * (x.x * (float) sumi) + wm[rr][gi] * x.y;
+                                const float2 x = lds64f(p.ds_off + (uint32_t) (j * nblk + U::act_blk(u, g)) * 8);
+#pragma unroll
+                                for (int rr = 0; rr < RB; ++rr) {
+                                    int s0 = 0, s1 = 0;
+#pragma unroll
+                                    for (int i = 0; i < U::GW; i += 2) {
+                                        s0 = dp4a_(wq[rr][g * U::GW + i], aw[i], s0);
+                                        s1 = dp4a_(wq[rr][g * U::GW + i + 1], aw[i + 1], s1);
+                                    }
+                                    acc[rr][j] += ws[rr][g] * (x.x * (float) (s0 + s1)) + wm[rr][g] * x.y;
+                                }
                             }
                         }
                     }
                 }
-            }
-            // warp all-reduce, then lane (rr*NCOLS + j) owns output (row0+rr, column j)
-            float mine = 0.0f;
+                // reduce over the lpr lanes of each row
 #pragma unroll
-            for (int rr = 0; rr < RB; ++rr) {
+                for (int rr = 0; rr < RB; ++rr) {
 #pragma unroll
-                for (int j = 0; j < NCOLS; ++j) {
-                    float v = acc[rr][j];
-                    v += __shfl_xor_sync(0xffffffffu, v, 16);
-                    v += __shfl_xor_sync(0xffffffffu, v, 8);
-                    v += __shfl_xor_sync(0xffffffffu, v, 4);
-                    v += __shfl_xor_sync(0xffffffffu, v, 2);
-                    v += __shfl_xor_sync(0xffffffffu, v, 1);
-                    if (lane == rr * NCOLS + j) {
-                        mine = v;
+                    for (int j = 0; j < NCOLS; ++j) {
+                        float v = acc[rr][j];
+                        for (int o = lpr >> 1; o > 0; o >>= 1) {
+                            v += __shfl_xor_sync(0xffffffffu, v, o);
+                        }
+                        acc[rr][j] = v;
                     }
                 }
-            }
-            const int my_rr = lane / NCOLS;
-            const int my_j  = lane - my_rr * NCOLS;
-            if (p.wpr == 1) {
-                if (lane < RB * NCOLS && row0 + my_rr < nrows) {
-                    float * out = (float *) ((char *) p.dst + d_off + (long long) my_j * p.d_nb1) + (r + row0 + my_rr);
-                    *out        = mine;
-                }
-            } else {
-                float * rb = red + red_buf * (NW * RB * 8);
-                if (lane < RB * NCOLS) {
-                    rb[warp * (RB * 8) + lane] = mine;
-                }
-                consumer_bar();
-                if (part == 0 && lane < RB * NCOLS && row0 + my_rr < nrows) {
-                    float v = 0.0f;
-                    for (int pp = 0; pp < p.wpr; ++pp) {
-                        v += rb[(warp + pp) * (RB * 8) + lane];
+                if (p.wpr == 1) {
+                    if (sub == 0) {
+#pragma unroll
+                        for (int rr = 0; rr < RB; ++rr) {
+                            const int row = row_a + rr * RW;
+                            if (row < nrows) {
+#pragma unroll
+                                for (int j = 0; j < NCOLS; ++j) {
+                                    float * out = (float *) ((char *) p.dst + d_off + (long long) j * p.d_nb1) + (r + row);
+                                    *out        = acc[rr][j];
+                                }
+                            }
+                        }
                     }
-                    float * out = (float *) ((char *) p.dst + d_off + (long long) my_j * p.d_nb1) + (r + row0 + my_rr);
-                    *out        = v;
+                } else {
+                    // lpr == 32: lane 0 holds the warp's partial sums; the group's warps exchange them through smem
+                    float * rb = (float *) (b200q_smem + OFF_RED) + red_buf * (NW * RB * 8);
+                    if (lane == 0) {
+#pragma unroll
+                        for (int rr = 0; rr < RB; ++rr) {
+#pragma unroll
+                            for (int j = 0; j < NCOLS; ++j) {
+                                rb[warp * (RB * 8) + rr * 8 + j] = acc[rr][j];
+                            }
+                        }
+                    }
+                    named_bar(1 + gi, WS * 32);
+                    if (part == 0 && lane < RB * 8) {
+                        const int rr  = lane >> 3;
+                        const int j   = lane & 7;
+                        const int row = row_a + rr * RW;
+                        if (j < NCOLS && row < nrows) {
+                            float v = 0.0f;
+                            for (int pp = 0; pp < p.wpr; ++pp) {
+                                v += rb[(warp + pp) * (RB * 8) + lane];
+                            }
+                            float * out = (float *) ((char *) p.dst + d_off + (long long) j * p.d_nb1) + (r + row);
+                            *out        = v;
+                        }
+                    }
+                    red_buf ^= 1;
                 }
-                red_buf ^= 1;
+            }
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(sb + OFF_EMPTY + 8 * s);
             }
         }
-        __syncwarp();
-        if (lane == 0) {
-            mbar_arrive(&empty[s]);
+        walk.advance(nrows);
+        if (++s == S) {
+            s = 0;
+            ++round;
         }
-        cur += nrows;
+        if (++gsel == G) {
+            gsel = 0;
+        }
     }
+    if (threadIdx.x == 0) stamp(p, 4);
 }
 
 template <int T> gemv_kernel_t pick_ncols(int ncols) {
@@ -416,7 +495,12 @@ gemv_kernel_t gemv_kernel_for(int type, int ncols) {
 }
 
 int gemv_threads() { return NTHREADS; }
-int gemv_fixed_smem() { return 128 + RED_FLOATS * 4; }
-int gemv_pass_rows(int wpr) { return (NW * RB) / wpr; }
+int gemv_act_off() { return (int) OFF_ACT; }
+int gemv_unit_elems(int type) {
+    switch (type) {
+        case T_Q4_K: case T_Q5_K: case T_Q6_K: return 64;
+        default: return 32;
+    }
+}
 
 }  // namespace b200q

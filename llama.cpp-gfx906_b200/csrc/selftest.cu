@@ -90,7 +90,7 @@ template <int T> static int check_type(const char * name) {
             for (int u = 0; u < k / U::ELEMS; ++u) {
                 int   wq[U::NG * U::GW];
                 float ws[U::NG], wm[U::NG];
-                U::decode(base + mis, u, wq, ws, wm);
+                U::decode((const uint8_t *) (base + mis), u, wq, ws, wm);
                 got += unit_dot<T>(wq, ws, wm, u, qa_words, ds.data());
             }
             for (int i = 0; i < k; ++i) {

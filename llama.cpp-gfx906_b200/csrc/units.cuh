@@ -63,22 +63,38 @@ B200Q_HD uint32_t byte_perm_(uint32_t a, uint32_t b, uint32_t s) {
 #endif
 }
 
+// ---- address abstraction ----------------------------------------------------------------------------------
+// The decoders are templates on the address type A so the SAME code runs
+//   * on the device with A = uint32_t: a byte offset into the CTA's dynamic shared memory (b200q_smem) — loads
+//     are emitted as LDS because the base is the __shared__ symbol itself (no generic-pointer LD), and all
+//     address arithmetic is 32-bit;
+//   * on the host (selftest) with A = const uint8_t *.
+#ifdef __CUDACC__
+extern __shared__ __align__(128) uint8_t b200q_smem[];
+__device__ __forceinline__ uint32_t lds32(uint32_t off) { return *(const uint32_t *) (b200q_smem + off); }
+__device__ __forceinline__ int4     lds128(uint32_t off) { return *(const int4 *) (b200q_smem + off); }
+__device__ __forceinline__ float2   lds64f(uint32_t off) { return *(const float2 *) (b200q_smem + off); }
+__device__ __forceinline__ uint32_t addr_align4(uint32_t a) { return a & ~3u; }
+__device__ __forceinline__ int      addr_shift(uint32_t a) { return (int) (a & 3u) * 8; }
+#endif
+B200Q_HD uint32_t        lds32(const uint8_t * p) { return *(const uint32_t *) p; }
+B200Q_HD const uint8_t * addr_align4(const uint8_t * p) { return (const uint8_t *) ((uintptr_t) p & ~(uintptr_t) 3); }
+B200Q_HD int             addr_shift(const uint8_t * p) { return (int) ((uintptr_t) p & 3) * 8; }
+
 // 32-bit little-endian word at an arbitrary byte address (reads the two aligned words that cover it)
-B200Q_HD uint32_t ldw(const uint8_t * p) {
-    const uintptr_t   a  = (uintptr_t) p;
-    const uint32_t *  w  = (const uint32_t *) (a & ~(uintptr_t) 3);
-    const int         sh = (int) (a & 3) * 8;
-    return funnel_r(w[0], w[1], sh);
+template <class A> B200Q_HD uint32_t ldw(A p) {
+    const A   w  = addr_align4(p);
+    const int sh = addr_shift(p);
+    return funnel_r(lds32(w), lds32(w + 4), sh);
 }
 // N consecutive words starting at an arbitrary byte address: N+1 aligned loads, N funnel shifts
-template <int N> B200Q_HD void ldw_n(const uint8_t * p, uint32_t (&out)[N]) {
-    const uintptr_t  a  = (uintptr_t) p;
-    const uint32_t * w  = (const uint32_t *) (a & ~(uintptr_t) 3);
-    const int        sh = (int) (a & 3) * 8;
-    uint32_t         prev = w[0];
+template <int N, class A> B200Q_HD void ldw_n(A p, uint32_t (&out)[N]) {
+    const A   w    = addr_align4(p);
+    const int sh   = addr_shift(p);
+    uint32_t  prev = lds32(w);
 #pragma unroll
     for (int i = 0; i < N; ++i) {
-        const uint32_t next = w[i + 1];
+        const uint32_t next = lds32(w + 4 * (i + 1));
         out[i]              = funnel_r(prev, next, sh);
         prev                = next;
     }
@@ -125,8 +141,8 @@ template <int T, int BYTES> struct UnitBlock32 {
 };
 
 template <> struct Unit<T_Q4_0> : UnitBlock32<T_Q4_0, 18> {
-    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
-        const uint8_t * b = row + (size_t) u * 18;
+    template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
+        const A b = row + u * 18;
         uint32_t        w[5];
         ldw_n<5>(b, w);  // [d | qs0 qs1] [qs2..5] [qs6..9] [qs10..13] [qs14 qs15 | next]
         const float d = half_bits_to_float((uint16_t) (w[0] & 0xffff));
@@ -141,8 +157,8 @@ template <> struct Unit<T_Q4_0> : UnitBlock32<T_Q4_0, 18> {
     }
 };
 template <> struct Unit<T_Q4_1> : UnitBlock32<T_Q4_1, 20> {
-    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
-        const uint8_t * b = row + (size_t) u * 20;
+    template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
+        const A b = row + u * 20;
         uint32_t        w[5];
         ldw_n<5>(b, w);  // [d m] [qs x4]
 #pragma unroll
@@ -155,8 +171,8 @@ template <> struct Unit<T_Q4_1> : UnitBlock32<T_Q4_1, 20> {
     }
 };
 template <> struct Unit<T_Q5_0> : UnitBlock32<T_Q5_0, 22> {
-    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
-        const uint8_t * b = row + (size_t) u * 22;
+    template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
+        const A b = row + u * 22;
         uint32_t        w[6];
         ldw_n<6>(b, w);  // [d | qh0 qh1] [qh2 qh3 | qs0 qs1] [qs2..5] [qs6..9] [qs10..13] [qs14 qs15 | next]
         const float    d  = half_bits_to_float((uint16_t) (w[0] & 0xffff));
@@ -172,8 +188,8 @@ template <> struct Unit<T_Q5_0> : UnitBlock32<T_Q5_0, 22> {
     }
 };
 template <> struct Unit<T_Q5_1> : UnitBlock32<T_Q5_1, 24> {
-    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
-        const uint8_t * b = row + (size_t) u * 24;
+    template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
+        const A b = row + u * 24;
         uint32_t        w[6];
         ldw_n<6>(b, w);  // [d m] [qh] [qs x4]
         const uint32_t qh = w[1];
@@ -187,8 +203,8 @@ template <> struct Unit<T_Q5_1> : UnitBlock32<T_Q5_1, 24> {
     }
 };
 template <> struct Unit<T_Q8_0> : UnitBlock32<T_Q8_0, 34> {
-    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
-        const uint8_t * b = row + (size_t) u * 34;
+    template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
+        const A b = row + u * 34;
         uint32_t        w[9];
         ldw_n<9>(b, w);  // [d | q0 q1] ... [q30 q31 | next]
 #pragma unroll
@@ -200,8 +216,8 @@ template <> struct Unit<T_Q8_0> : UnitBlock32<T_Q8_0, 34> {
     }
 };
 template <> struct Unit<T_MXFP4> : UnitBlock32<T_MXFP4, 17> {
-    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
-        const uint8_t * b = row + (size_t) u * 17;
+    template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
+        const A b = row + u * 17;
         uint32_t        w[5];
         ldw_n<5>(b, w);  // [e | qs0 qs1 qs2] ... [qs15 | next]
 #pragma unroll
@@ -235,9 +251,9 @@ template <> struct Unit<T_Q4_K> {
     static constexpr int ELEMS = 64, NG = 2, GW = 8;
     static B200Q_HD int  act_word(int u, int g) { return u * 16 + g * 8; }
     static B200Q_HD int  act_blk(int u, int g) { return u * 2 + g; }
-    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[16], float (&ws)[2], float (&wm)[2]) {
+    template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[16], float (&ws)[2], float (&wm)[2]) {
         const int       p = u & 3;
-        const uint8_t * b = row + (size_t) (u >> 2) * 144;
+        const A b = row + (u >> 2) * 144;
         uint32_t        h[4];
         ldw_n<4>(b, h);  // [d dmin] [scales x3]
         uint32_t q[8];
@@ -263,9 +279,9 @@ template <> struct Unit<T_Q5_K> {
     static constexpr int ELEMS = 64, NG = 2, GW = 8;
     static B200Q_HD int  act_word(int u, int g) { return u * 16 + g * 8; }
     static B200Q_HD int  act_blk(int u, int g) { return u * 2 + g; }
-    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[16], float (&ws)[2], float (&wm)[2]) {
+    template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[16], float (&ws)[2], float (&wm)[2]) {
         const int       p = u & 3;
-        const uint8_t * b = row + (size_t) (u >> 2) * 176;
+        const A b = row + (u >> 2) * 176;
         uint32_t        h[4];
         ldw_n<4>(b, h);
         uint32_t qh[8];
@@ -297,9 +313,9 @@ template <> struct Unit<T_Q6_K> {
     static B200Q_HD int  elem0(int u, int g) { return (u >> 2) * 256 + ((u >> 1) & 1) * 128 + g * 32 + (u & 1) * 16; }
     static B200Q_HD int  act_word(int u, int g) { return elem0(u, g) >> 2; }
     static B200Q_HD int  act_blk(int u, int g) { return elem0(u, g) >> 5; }
-    static B200Q_HD void decode(const uint8_t * row, int u, int (&wq)[16], float (&ws)[4], float (&wm)[4]) {
+    template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[16], float (&ws)[4], float (&wm)[4]) {
         const int       n = (u >> 1) & 1, h = u & 1;
-        const uint8_t * b = row + (size_t) (u >> 2) * 210;
+        const A b = row + (u >> 2) * 210;
         uint32_t        l0[4], l1[4], qh[4];
         ldw_n<4>(b + 64 * n + 16 * h, l0);        // ql[l],      l = 16h .. 16h+15
         ldw_n<4>(b + 64 * n + 32 + 16 * h, l1);   // ql[l + 32]

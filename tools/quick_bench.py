@@ -1,0 +1,76 @@
+"""quick GEMV timing sweep (development aid; bench.py is the contract).  Cold-HBM numbers: rotates over enough
+distinct weight copies to exceed 4x L2."""
+import sys, os, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "llama.cpp-gfx906_b200")); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import numpy as np, torch
+import b200q, refs
+
+def bench(t, m, k, n, copies=None, iters=200, flags=b200q.FLAG_WEIGHTS_IMMUTABLE):
+    rs = refs.row_size(t, k)
+    wbytes = m * rs
+    if copies is None:
+        copies = max(2, int(600e6 // wbytes) + 1)
+    base = refs.random_blocks(t, min(m, 512), k, seed=1)
+    reps = (m + base.shape[0] - 1) // base.shape[0]
+    host = np.tile(base, (reps, 1))[:m]
+    ws = [b200q.upload(t, (m, k), host) for _ in range(copies)]
+    act = torch.rand(n, k, device="cuda") * 2 - 1
+    out = torch.empty(n, m, device="cuda")
+    for i in range(3 * copies):
+        b200q.mul_mat(ws[i % copies], act, out=out, flags=flags)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for i in range(copies):
+            b200q.mul_mat(ws[i], act, out=out, flags=flags)
+    g.replay(); torch.cuda.synchronize()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    reps = max(1, iters // copies)
+    e0.record()
+    for _ in range(reps):
+        g.replay()
+    e1.record(); torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) * 1e3 / (reps * copies)
+    algo = wbytes + 4 * n * k + 4 * n * m
+    print(f"{refs.NAMES[t]:6s} m={m:6d} k={k:6d} n={n} copies={copies:3d}: {us:8.2f} us  {algo / us / 1e3:8.1f} GB/s  ({algo/us/1e3/6547.8*100:5.1f}% of measured HBM)", flush=True)
+    return us
+
+if __name__ == "__main__":
+    torch.cuda.set_device(0)
+    which = sys.argv[1] if len(sys.argv) > 1 else "basic"
+    if which == "basic":
+        for (m, k) in [(4096, 4096), (14336, 4096), (4096, 14336), (1024, 4096), (128256, 4096)]:
+            bench(refs.Q4_K, m, k, 1)
+        bench(refs.Q4_0, 4096, 4096, 1)
+        bench(refs.Q6_K, 128256, 4096, 1, copies=3)
+        bench(refs.Q8_0, 14336, 4096, 1)
+        bench(refs.MXFP4, 2880 * 4, 2880, 1)
+        for n in (2, 4, 8):
+            bench(refs.Q4_K, 14336, 4096, n)
+        bench(refs.Q4_K, 14336, 4096, 1, flags=b200q.FLAG_NO_PDL)
+    elif which == "one":
+        t = {"q4_K": refs.Q4_K, "q6_K": refs.Q6_K, "q8_0": refs.Q8_0, "q4_0": refs.Q4_0, "mxfp4": refs.MXFP4}[sys.argv[2]]
+        m, k, n = int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5])
+        bench(t, m, k, n, copies=4, iters=16)
+    elif which == "ts":
+        # per-CTA timeline of the GEMV kernel inside a back-to-back chain (ns relative to the CTA's start stamp)
+        t = {"q4_K": refs.Q4_K, "q6_K": refs.Q6_K, "q8_0": refs.Q8_0}[sys.argv[2]]
+        m, k, n = int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5])
+        host = np.tile(refs.random_blocks(t, 256, k, seed=1), ((m + 255) // 256, 1))[:m]
+        ws = [b200q.upload(t, (m, k), host) for _ in range(8)]
+        act = torch.rand(n, k, device="cuda"); out = torch.empty(n, m, device="cuda")
+        L = b200q.lib()
+        bufs = [torch.zeros(148 * 8, dtype=torch.int64, device="cuda") for _ in range(8)]
+        for rep in range(3):
+            for i in range(8):
+                L.b200q_debug_timestamps(__import__("ctypes").c_void_p(bufs[i].data_ptr()))
+                b200q.mul_mat(ws[i], act, out=out)
+        torch.cuda.synchronize()
+        L.b200q_debug_timestamps(None)
+        T = torch.stack(bufs).cpu().numpy().reshape(8, 148, 8)
+        t0 = T[:, :, 0].min()
+        for i in range(3, 8):
+            a = T[i]
+            names = ["start", "pdl_wait", "quant", "first_full", "end"]
+            print(f"kernel {i}: " + "  ".join(f"{names[j]}: min {int(a[:, j].min() - t0):6d} med {int(np.median(a[:, j]) - t0):6d} max {int(a[:, j].max() - t0):6d}" for j in range(5)))
