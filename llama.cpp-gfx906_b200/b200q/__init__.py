@@ -17,7 +17,7 @@ from typing import Optional
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libb200q.so")
+LIB_PATH = os.environ.get("B200Q_LIB", os.path.join(os.path.dirname(_HERE), "lib", "libb200q.so"))
 
 # ggml_type numbers
 F32, Q4_0, Q4_1, Q5_0, Q5_1, Q8_0, Q4_K, Q5_K, Q6_K, MXFP4 = 0, 2, 3, 6, 7, 8, 12, 13, 14, 39

@@ -106,7 +106,7 @@ bool plan_gemv(GemvPlan & plan, int type, int ncols, const DevInfo & di) {
     int       lpr   = 1;
     while (lpr < 32 && lpr < nu) lpr *= 2;
     p.lpr        = lpr;
-    const int RW = 32 / lpr, RB = 2, NW = 8;
+    const int RW = 32 / lpr, RB = 2, NW = gemv_consumer_warps();
 
     // activations: int8 columns (padded to 128 B so the chunk swizzle stays inside a column) + (d, s) pairs
     p.act_col_bytes        = round_up(p.k, 128);
@@ -119,9 +119,9 @@ bool plan_gemv(GemvPlan & plan, int type, int ncols, const DevInfo & di) {
     const double target = 16.0 * 1024;
     double       best   = 1e30;
     int          bw = 1, bg = 1;
-    for (int wpr = 1; wpr <= 8; wpr *= 2) {
+    for (int wpr = 1; wpr <= NW; wpr *= 2) {
         if (wpr > 1 && (lpr < 32 || nu < 32 * wpr)) break;
-        for (int g = 1; g * wpr <= NW; g *= 2) {
+        for (int g = 1; g * wpr <= NW && g <= 8; g *= 2) {
             if (g > 1 && p.nch > 1) break;
             const long long bytes = (long long) (NW / g / wpr) * RW * RB * pitch;
             double          cost  = bytes > target ? bytes / target : target / bytes;
@@ -154,7 +154,7 @@ bool plan_gemv(GemvPlan & plan, int type, int ncols, const DevInfo & di) {
             break;
         }
         if (p.groups > 1) { p.groups /= 2; continue; }   // fewer, larger stages cannot help; fewer groups can
-        if (p.wpr < 8 && lpr == 32 && nu >= 64 * p.wpr) { p.wpr *= 2; continue; }
+        if (p.wpr < NW && lpr == 32 && nu >= 64 * p.wpr) { p.wpr *= 2; continue; }
         return false;
     }
     plan.smem = p.stage_off + p.nstages * p.stage_bytes;
@@ -172,6 +172,8 @@ int launch_gemv(GemvPlan & plan, int type, int ncols, uint32_t flags, cudaStream
     const bool pdl        = !(flags & B200Q_FLAG_NO_PDL);
     plan.p.early_prefetch = pdl && (flags & B200Q_FLAG_WEIGHTS_IMMUTABLE) ? 1 : 0;
     plan.p.ts             = g_ts;
+    static const int early = getenv("B200Q_EARLY") ? atoi(getenv("B200Q_EARLY")) : 8;
+    plan.p.early_stages   = early;
 
     static const bool debug = getenv("B200Q_DEBUG") != nullptr;
     if (debug) {

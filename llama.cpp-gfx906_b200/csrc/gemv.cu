@@ -32,15 +32,19 @@ namespace b200q {
 
 namespace {
 
-constexpr int NW         = 8;  // consumer warps
+#ifndef B200Q_GEMV_NW
+#define B200Q_GEMV_NW 16
+#endif
+constexpr int NW         = B200Q_GEMV_NW;  // consumer warps
 constexpr int RB         = 2;  // rows per lane
 constexpr int NTHREADS   = (NW + 1) * 32;
 constexpr int MAX_STAGES = 8;
 // shared memory map (byte offsets)
 constexpr uint32_t OFF_FULL  = 0;     // MAX_STAGES mbarriers
 constexpr uint32_t OFF_EMPTY = 64;    // MAX_STAGES mbarriers
-constexpr uint32_t OFF_RED   = 128;   // [2][NW][RB*8] floats for the cross-warp reduction
-constexpr uint32_t OFF_ACT   = 128 + 2 * NW * RB * 8 * 4;  // quantized activations
+constexpr uint32_t OFF_ARDY  = 128;   // mbarrier: the consumers have issued their first activation loads
+constexpr uint32_t OFF_RED   = 144;   // [2][NW][RB*8] floats for the cross-warp reduction
+constexpr uint32_t OFF_ACT   = 144 + 2 * NW * RB * 8 * 4;  // quantized activations
 
 __device__ __forceinline__ uint32_t smem_base_u32() { return (uint32_t) __cvta_generic_to_shared(b200q_smem); }
 
@@ -127,54 +131,74 @@ __device__ __forceinline__ uint32_t act_swz_chunk(uint32_t chunk) { return chunk
 //   int8x4 words at OFF_ACT + j * act_col_bytes (swizzled), (d, d*sum(q)) float2 at ds_off + (j*k/32 + blk)*8
 // 8 lanes share one 32-value block (float4 each); executed by the NW consumer warps only.
 template <int NCOLS>
-__device__ __forceinline__ void quantize_activations(const GemvParams & p, const char * act_base, int tid) {
+__device__ __forceinline__ void quantize_activations(const GemvParams & p, const char * act_base, int tid, bool signal) {
+    constexpr int QB         = 4;         // iterations whose global loads are issued together (latency paid once)
     const int chunks_per_col = p.k >> 2;  // float4 chunks == int8x4 words
     const int total          = NCOLS * chunks_per_col;
     const int nblk           = p.k >> 5;
-    for (int base = 0; base < total; base += NW * 32) {
-        const int  q      = base + tid;
-        const bool active = q < total;
-        int        j      = 0;
-        int        pos    = active ? q : 0;
-        if (NCOLS > 1) {
-            while (pos >= chunks_per_col) {
-                pos -= chunks_per_col;
-                ++j;
+    for (int base = 0; base < total; base += QB * NW * 32) {
+        float4 v[QB];
+        int    jj[QB], pp[QB];
+#pragma unroll
+        for (int b = 0; b < QB; ++b) {
+            const int  q      = base + b * NW * 32 + tid;
+            const bool active = q < total;
+            int        j      = 0;
+            int        pos    = active ? q : 0;
+            if (NCOLS > 1) {
+                j   = pos / chunks_per_col;
+                pos = pos - j * chunks_per_col;
+            }
+            jj[b] = active ? j : -1;
+            pp[b] = pos;
+            v[b]  = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (active) {
+                const float * src = (const float *) (act_base + (long long) j * p.a_nb1) + 4 * pos;
+                if (p.act_vec4) {
+                    v[b] = __ldg((const float4 *) src);
+                } else {
+                    v[b].x = __ldg(src);
+                    v[b].y = __ldg(src + 1);
+                    v[b].z = __ldg(src + 2);
+                    v[b].w = __ldg(src + 3);
+                }
             }
         }
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (active) {
-            const float * src = (const float *) (act_base + (long long) j * p.a_nb1) + 4 * pos;
-            if (p.act_vec4) {
-                v = __ldg((const float4 *) src);
-            } else {
-                v.x = __ldg(src);
-                v.y = __ldg(src + 1);
-                v.z = __ldg(src + 2);
-                v.w = __ldg(src + 3);
-            }
+        if (signal && base == 0 && (tid & 31) == 0) {
+            // the first activation loads are in flight: the producer may now queue the rest of the weight stream
+            mbar_arrive(smem_base_u32() + OFF_ARDY);
         }
-        float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
-        amax       = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
-        amax       = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
-        amax       = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
-        const float d  = amax * (1.0f / 127.0f);
-        const float id = amax > 0.0f ? 127.0f / amax : 0.0f;
-        const int   q0 = __float2int_rn(v.x * id);
-        const int   q1 = __float2int_rn(v.y * id);
-        const int   q2 = __float2int_rn(v.z * id);
-        const int   q3 = __float2int_rn(v.w * id);
-        int         s  = q0 + q1 + q2 + q3;
-        s += __shfl_xor_sync(0xffffffffu, s, 1);
-        s += __shfl_xor_sync(0xffffffffu, s, 2);
-        s += __shfl_xor_sync(0xffffffffu, s, 4);
-        if (active) {
-            const uint32_t word = (act_swz_chunk((uint32_t) pos >> 2) << 2) | ((uint32_t) pos & 3u);
-            *(int *) (b200q_smem + OFF_ACT + (uint32_t) j * p.act_col_bytes + word * 4) =
-                (q0 & 0xff) | ((q1 & 0xff) << 8) | ((q2 & 0xff) << 16) | ((q3 & 0xff) << 24);
-            if ((pos & 7) == 0) {
-                *(float2 *) (b200q_smem + p.ds_off + (uint32_t) (j * nblk + (pos >> 3)) * 8) =
-                    make_float2(d, d * (float) s);
+        if (p.ts && tid == 0 && base == 0) {
+            // debug: time at which the first activation value is usable
+            if (v[0].x == 123456.0f) stamp(p, 7);
+            stamp(p, 5);
+        }
+#pragma unroll
+        for (int b = 0; b < QB; ++b) {
+            if (base + b * NW * 32 >= total) break;  // warp-uniform
+            float amax = fmaxf(fmaxf(fabsf(v[b].x), fabsf(v[b].y)), fmaxf(fabsf(v[b].z), fabsf(v[b].w)));
+            amax       = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+            amax       = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+            amax       = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
+            const float d  = amax * (1.0f / 127.0f);
+            const float id = amax > 0.0f ? 127.0f / amax : 0.0f;
+            const int   q0 = __float2int_rn(v[b].x * id);
+            const int   q1 = __float2int_rn(v[b].y * id);
+            const int   q2 = __float2int_rn(v[b].z * id);
+            const int   q3 = __float2int_rn(v[b].w * id);
+            int         s  = q0 + q1 + q2 + q3;
+            s += __shfl_xor_sync(0xffffffffu, s, 1);
+            s += __shfl_xor_sync(0xffffffffu, s, 2);
+            s += __shfl_xor_sync(0xffffffffu, s, 4);
+            if (jj[b] >= 0) {
+                const int      pos  = pp[b];
+                const uint32_t word = (act_swz_chunk((uint32_t) pos >> 2) << 2) | ((uint32_t) pos & 3u);
+                *(int *) (b200q_smem + OFF_ACT + (uint32_t) jj[b] * p.act_col_bytes + word * 4) =
+                    (q0 & 0xff) | ((q1 & 0xff) << 8) | ((q2 & 0xff) << 16) | ((q3 & 0xff) << 24);
+                if ((pos & 7) == 0) {
+                    *(float2 *) (b200q_smem + p.ds_off + (uint32_t) (jj[b] * nblk + (pos >> 3)) * 8) =
+                        make_float2(d, d * (float) s);
+                }
             }
         }
     }
@@ -203,7 +227,7 @@ struct StageWalk {
 };
 
 template <int T, int NCOLS>
-__global__ void __launch_bounds__(NTHREADS, 2) gemv_stream_kernel(const GemvParams p) {
+__global__ void __launch_bounds__(NTHREADS, NW <= 8 ? 2 : 1) gemv_stream_kernel(const GemvParams p) {
     using U = Unit<T>;
     const uint32_t sb   = smem_base_u32();
     const int      warp = threadIdx.x >> 5;
@@ -221,6 +245,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) gemv_stream_kernel(const GemvPara
             mbar_init(sb + OFF_FULL + 8 * s, 1);
             mbar_init(sb + OFF_EMPTY + 8 * s, WS);
         }
+        mbar_init(sb + OFF_ARDY, NW);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -237,9 +262,16 @@ __global__ void __launch_bounds__(NTHREADS, 2) gemv_stream_kernel(const GemvPara
                 pdl_wait();
             }
             const uint64_t pol = l2_evict_first_policy();
-            int            s = 0, round = 0;
+            int            s = 0, round = 0, issued = 0;
             while (!walk.done()) {
                 const int nrows = walk.nrows();
+                if (issued == p.early_stages) {
+                    // only `early_stages` stages are queued ahead of the activation loads (a deeper queue would
+                    // delay them by the time the SM needs to ingest it); the rest follows once those are issued
+                    pdl_wait();
+                    mbar_wait(sb + OFF_ARDY, 0);
+                }
+                ++issued;
                 if (round > 0) {
                     mbar_wait(sb + OFF_EMPTY + 8 * s, (round & 1) ^ 1);
                 }
@@ -277,6 +309,15 @@ __global__ void __launch_bounds__(NTHREADS, 2) gemv_stream_kernel(const GemvPara
     }
 
     // ---------------------------------------------------------------------- consumers
+    if (p.mode == GEMV_MODE_BATCH && !walk.done()) {
+        // warm the TLB / L2 path of the activation vector while the previous kernel is still running
+        // (L2 is the point of coherence, so a line fetched early is still correct after griddepcontrol.wait)
+        const ChannelOff o0  = channel_offsets(p, walk.c);
+        const int        idx = threadIdx.x * 32;  // one 128-byte line per thread
+        if (idx < p.k) {
+            asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *) p.act + o0.a + (long long) idx * 4));
+        }
+    }
     pdl_wait();  // activations (and dst) belong to the previous kernels of the stream
     if (threadIdx.x == 0) stamp(p, 1);
 
@@ -307,7 +348,8 @@ __global__ void __launch_bounds__(NTHREADS, 2) gemv_stream_kernel(const GemvPara
             if (cur_ch >= 0) {
                 named_bar(9, NW * 32);  // everyone is done reading the previous channel's activations
             }
-            quantize_activations<NCOLS>(p, (const char *) p.act + o.a, tid);
+            quantize_activations<NCOLS>(p, (const char *) p.act + o.a, tid, cur_ch < 0);
+            if (threadIdx.x == 0 && cur_ch < 0) stamp(p, 6);
             named_bar(9, NW * 32);
             if (threadIdx.x == 0 && cur_ch < 0) stamp(p, 2);
             cur_ch = c;
@@ -382,8 +424,13 @@ __global__ void __launch_bounds__(NTHREADS, 2) gemv_stream_kernel(const GemvPara
                                     int s0 = 0, s1 = 0;
 #pragma unroll
                                     for (int i = 0; i < U::GW; i += 2) {
-                                        s0 = dp4a_(wq[rr][g * U::GW + i], aw[i], s0);
-                                        s1 = dp4a_(wq[rr][g * U::GW + i + 1], aw[i + 1], s1);
+                                        if (U::UNSIGNED_W) {
+                                            s0 = dp4a_us((uint32_t) wq[rr][g * U::GW + i], aw[i], s0);
+                                            s1 = dp4a_us((uint32_t) wq[rr][g * U::GW + i + 1], aw[i + 1], s1);
+                                        } else {
+                                            s0 = dp4a_(wq[rr][g * U::GW + i], aw[i], s0);
+                                            s1 = dp4a_(wq[rr][g * U::GW + i + 1], aw[i + 1], s1);
+                                        }
                                     }
                                     acc[rr][j] += ws[rr][g] * (x.x * (float) (s0 + s1)) + wm[rr][g] * x.y;
                                 }
@@ -397,8 +444,16 @@ __global__ void __launch_bounds__(NTHREADS, 2) gemv_stream_kernel(const GemvPara
 #pragma unroll
                     for (int j = 0; j < NCOLS; ++j) {
                         float v = acc[rr][j];
-                        for (int o = lpr >> 1; o > 0; o >>= 1) {
-                            v += __shfl_xor_sync(0xffffffffu, v, o);
+                        if (lpr == 32) {
+                            v += __shfl_xor_sync(0xffffffffu, v, 16);
+                            v += __shfl_xor_sync(0xffffffffu, v, 8);
+                            v += __shfl_xor_sync(0xffffffffu, v, 4);
+                            v += __shfl_xor_sync(0xffffffffu, v, 2);
+                            v += __shfl_xor_sync(0xffffffffu, v, 1);
+                        } else {
+                            for (int o = lpr >> 1; o > 0; o >>= 1) {
+                                v += __shfl_xor_sync(0xffffffffu, v, o);
+                            }
                         }
                         acc[rr][j] = v;
                     }
@@ -495,6 +550,7 @@ gemv_kernel_t gemv_kernel_for(int type, int ncols) {
 }
 
 int gemv_threads() { return NTHREADS; }
+int gemv_consumer_warps() { return NW; }
 int gemv_act_off() { return (int) OFF_ACT; }
 int gemv_unit_elems(int type) {
     switch (type) {

@@ -33,6 +33,7 @@ struct GemvParams {
     int act_col_bytes;     // bytes between quantized activation columns in smem (k rounded up to 128)
     int ds_off;            // smem offset of the (d, s) pairs
     int act_vec4;          // activation columns are 16-byte aligned in global memory
+    int early_stages;      // stages queued before the consumers' activation loads are in flight
     int early_prefetch;    // weights immutable: stream them before griddepcontrol.wait
     unsigned long long * ts;  // debug: per-CTA %globaltimer stamps [grid][8] (NULL in production)
 };
@@ -41,6 +42,7 @@ typedef void (*gemv_kernel_t)(const GemvParams);
 
 gemv_kernel_t gemv_kernel_for(int type, int ncols);
 int           gemv_threads();
+int           gemv_consumer_warps();
 int           gemv_act_off();        // smem offset where the quantized activations start
 int           gemv_unit_elems(int type);
 

@@ -32,6 +32,19 @@ B200Q_HD int dp4a_(int a, int b, int c) {
     return c;
 #endif
 }
+// a: four UNSIGNED bytes, b: four signed bytes (dp4a.u32.s32)
+B200Q_HD int dp4a_us(uint32_t a, int b, int c) {
+#ifdef __CUDA_ARCH__
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+#else
+    for (int i = 0; i < 4; ++i) {
+        c += (int) (uint8_t) (a >> (8 * i)) * (int) (int8_t) (b >> (8 * i));
+    }
+    return c;
+#endif
+}
 B200Q_HD uint32_t funnel_r(uint32_t lo, uint32_t hi, int shift_bits) {
 #ifdef __CUDA_ARCH__
     return __funnelshift_r(lo, hi, shift_bits);
@@ -78,6 +91,36 @@ __device__ __forceinline__ uint32_t addr_align4(uint32_t a) { return a & ~3u; }
 __device__ __forceinline__ int      addr_shift(uint32_t a) { return (int) (a & 3u) * 8; }
 #endif
 B200Q_HD uint32_t        lds32(const uint8_t * p) { return *(const uint32_t *) p; }
+struct Words4 { uint32_t x, y, z, w; };
+#ifdef __CUDACC__
+__device__ __forceinline__ Words4 ldq(uint32_t off) {  // one LDS.128, `off` 16-byte aligned
+    const int4 t = *(const int4 *) (b200q_smem + off);
+    return Words4{ (uint32_t) t.x, (uint32_t) t.y, (uint32_t) t.z, (uint32_t) t.w };
+}
+__device__ __forceinline__ bool addr_is16(uint32_t a) { return (a & 15u) == 0; }
+#endif
+B200Q_HD Words4 ldq(const uint8_t * p) {
+    const uint32_t * w = (const uint32_t *) p;
+    return Words4{ w[0], w[1], w[2], w[3] };
+}
+B200Q_HD bool addr_is16(const uint8_t * p) { return ((uintptr_t) p & 15) == 0; }
+template <int N, class A> B200Q_HD void ldw_n(A p, uint32_t (&out)[N]);
+// N words (N % 4 == 0) from a byte address: LDS.128s when the address is 16-byte aligned (warp-uniform in
+// practice: row pitch and block size of the K-quants are multiples of 16), else the funnel-shift path
+template <int N, class A> B200Q_HD void ldw_n_fast(A p, uint32_t (&out)[N]) {
+    if (addr_is16(p)) {
+#pragma unroll
+        for (int i = 0; i < N / 4; ++i) {
+            const Words4 t = ldq(p + 16 * i);
+            out[4 * i + 0] = t.x;
+            out[4 * i + 1] = t.y;
+            out[4 * i + 2] = t.z;
+            out[4 * i + 3] = t.w;
+        }
+    } else {
+        ldw_n<N>(p, out);
+    }
+}
 B200Q_HD const uint8_t * addr_align4(const uint8_t * p) { return (const uint8_t *) ((uintptr_t) p & ~(uintptr_t) 3); }
 B200Q_HD int             addr_shift(const uint8_t * p) { return (int) ((uintptr_t) p & 3) * 8; }
 
@@ -135,7 +178,8 @@ B200Q_HD void mxfp4_lut(uint32_t q, uint32_t & lo, uint32_t & hi) {
 template <int T> struct Unit;
 
 template <int T, int BYTES> struct UnitBlock32 {
-    static constexpr int ELEMS = 32, NG = 1, GW = 8;
+    static constexpr int  ELEMS = 32, NG = 1, GW = 8;
+    static constexpr bool UNSIGNED_W = false;
     static B200Q_HD int  act_word(int u, int) { return u * 8; }
     static B200Q_HD int  act_blk(int u, int) { return u; }
 };
@@ -247,69 +291,80 @@ B200Q_HD void k4_scale_min_words(const uint32_t (&s)[3], int j, int & sc, int & 
     }
 }
 
+// (scale, min) pairs 2p and 2p+1 of a K-quant super-block as packed 16-bit pairs (byte 0: pair 2p, byte 1: pair 2p+1)
+B200Q_HD void k4_scale_min_pair(uint32_t s0, uint32_t s1, uint32_t s2, int p, uint32_t & scp, uint32_t & mnp) {
+    const int      sh = 16 * (p & 1);
+    const uint32_t a0 = s0 >> sh, a1 = s1 >> sh, a2 = s2 >> sh;
+    if (p < 2) {
+        scp = a0 & 0x3F3Fu;
+        mnp = a1 & 0x3F3Fu;
+    } else {
+        scp = (a2 & 0x0F0Fu) | ((a0 >> 2) & 0x3030u);
+        mnp = ((a2 >> 4) & 0x0F0Fu) | ((a1 >> 2) & 0x3030u);
+    }
+}
+
 template <> struct Unit<T_Q4_K> {
-    static constexpr int ELEMS = 64, NG = 2, GW = 8;
+    static constexpr int  ELEMS = 64, NG = 2, GW = 8;
+    static constexpr bool UNSIGNED_W = true;  // wq bytes are unsigned; group 1 holds 16 * nibble (scale pre-divided)
     static B200Q_HD int  act_word(int u, int g) { return u * 16 + g * 8; }
     static B200Q_HD int  act_blk(int u, int g) { return u * 2 + g; }
     template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[16], float (&ws)[2], float (&wm)[2]) {
-        const int       p = u & 3;
-        const A b = row + (u >> 2) * 144;
-        uint32_t        h[4];
-        ldw_n<4>(b, h);  // [d dmin] [scales x3]
+        const int p = u & 3;
+        const A   b = row + (u >> 2) * 144;
+        uint32_t  h[4];
+        ldw_n_fast<4>(b, h);  // [d dmin] [scales x3]
         uint32_t q[8];
-        ldw_n<8>(b + 16 + 32 * p, q);
-        const float    d    = half_bits_to_float((uint16_t) (h[0] & 0xffff));
-        const float    dmin = half_bits_to_float((uint16_t) (h[0] >> 16));
-        const uint32_t s[3] = { h[1], h[2], h[3] };
-        int            sc0, mn0, sc1, mn1;
-        k4_scale_min_words(s, 2 * p, sc0, mn0);
-        k4_scale_min_words(s, 2 * p + 1, sc1, mn1);
+        ldw_n_fast<8>(b + 16 + 32 * p, q);
+        const float d    = half_bits_to_float((uint16_t) (h[0] & 0xffff));
+        const float dmin = half_bits_to_float((uint16_t) (h[0] >> 16));
+        uint32_t    scp, mnp;
+        k4_scale_min_pair(h[1], h[2], h[3], p, scp, mnp);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             wq[i]     = (int) (q[i] & 0x0F0F0F0Fu);
-            wq[8 + i] = (int) ((q[i] >> 4) & 0x0F0F0F0Fu);
+            wq[8 + i] = (int) (q[i] & 0xF0F0F0F0u);  // 16 * high nibble, consumed by the unsigned dp4a
         }
-        ws[0] = d * (float) sc0;
-        ws[1] = d * (float) sc1;
-        wm[0] = -dmin * (float) mn0;
-        wm[1] = -dmin * (float) mn1;
+        ws[0] = d * (float) (scp & 0xff);
+        ws[1] = d * (float) (scp >> 8) * 0.0625f;
+        wm[0] = -dmin * (float) (mnp & 0xff);
+        wm[1] = -dmin * (float) (mnp >> 8);
     }
 };
 template <> struct Unit<T_Q5_K> {
-    static constexpr int ELEMS = 64, NG = 2, GW = 8;
+    static constexpr int  ELEMS = 64, NG = 2, GW = 8;
+    static constexpr bool UNSIGNED_W = true;
     static B200Q_HD int  act_word(int u, int g) { return u * 16 + g * 8; }
     static B200Q_HD int  act_blk(int u, int g) { return u * 2 + g; }
     template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[16], float (&ws)[2], float (&wm)[2]) {
-        const int       p = u & 3;
-        const A b = row + (u >> 2) * 176;
-        uint32_t        h[4];
-        ldw_n<4>(b, h);
+        const int p = u & 3;
+        const A   b = row + (u >> 2) * 176;
+        uint32_t  h[4];
+        ldw_n_fast<4>(b, h);
         uint32_t qh[8];
-        ldw_n<8>(b + 16, qh);
+        ldw_n_fast<8>(b + 16, qh);
         uint32_t q[8];
-        ldw_n<8>(b + 48 + 32 * p, q);
-        const float    d    = half_bits_to_float((uint16_t) (h[0] & 0xffff));
-        const float    dmin = half_bits_to_float((uint16_t) (h[0] >> 16));
-        const uint32_t s[3] = { h[1], h[2], h[3] };
-        int            sc0, mn0, sc1, mn1;
-        k4_scale_min_words(s, 2 * p, sc0, mn0);
-        k4_scale_min_words(s, 2 * p + 1, sc1, mn1);
+        ldw_n_fast<8>(b + 48 + 32 * p, q);
+        const float d    = half_bits_to_float((uint16_t) (h[0] & 0xffff));
+        const float dmin = half_bits_to_float((uint16_t) (h[0] >> 16));
+        uint32_t    scp, mnp;
+        k4_scale_min_pair(h[1], h[2], h[3], p, scp, mnp);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const uint32_t hb0 = (qh[i] >> (2 * p)) & 0x01010101u;
-            const uint32_t hb1 = (qh[i] >> (2 * p + 1)) & 0x01010101u;
-            wq[i]              = (int) ((q[i] & 0x0F0F0F0Fu) | (hb0 << 4));
-            wq[8 + i]          = (int) (((q[i] >> 4) & 0x0F0F0F0Fu) | (hb1 << 4));
+            const uint32_t hb = qh[i] >> (2 * p);
+            wq[i]             = (int) ((q[i] & 0x0F0F0F0Fu) | ((hb & 0x01010101u) << 4));
+            wq[8 + i]         = (int) (((q[i] >> 4) & 0x0F0F0F0Fu) | ((hb & 0x02020202u) << 3));
         }
-        ws[0] = d * (float) sc0;
-        ws[1] = d * (float) sc1;
-        wm[0] = -dmin * (float) mn0;
-        wm[1] = -dmin * (float) mn1;
+        ws[0] = d * (float) (scp & 0xff);
+        ws[1] = d * (float) (scp >> 8);
+        wm[0] = -dmin * (float) (mnp & 0xff);
+        wm[1] = -dmin * (float) (mnp >> 8);
     }
 };
 template <> struct Unit<T_Q6_K> {
     // unit u = (super-block sb, half n, 16-lane half h): elements 256 sb + 128 n + 32 quad + 16 h + [0,16), quad = 0..3
-    static constexpr int ELEMS = 64, NG = 4, GW = 4;
+    static constexpr int  ELEMS = 64, NG = 4, GW = 4;
+    static constexpr bool UNSIGNED_W = false;
     static B200Q_HD int  elem0(int u, int g) { return (u >> 2) * 256 + ((u >> 1) & 1) * 128 + g * 32 + (u & 1) * 16; }
     static B200Q_HD int  act_word(int u, int g) { return elem0(u, g) >> 2; }
     static B200Q_HD int  act_blk(int u, int g) { return elem0(u, g) >> 5; }
@@ -355,7 +410,7 @@ template <int T> B200Q_HD float unit_dot(const int (&wq)[Unit<T>::NG * Unit<T>::
         int         sumi = 0;
 #pragma unroll
         for (int i = 0; i < U::GW; ++i) {
-            sumi = dp4a_(wq[g * U::GW + i], a[i], sumi);
+            sumi = U::UNSIGNED_W ? dp4a_us((uint32_t) wq[g * U::GW + i], a[i], sumi) : dp4a_(wq[g * U::GW + i], a[i], sumi);
         }
         const float2 x = ds[U::act_blk(u, g)];
         acc += ws[g] * (x.x * (float) sumi) + wm[g] * x.y;

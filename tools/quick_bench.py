@@ -62,15 +62,26 @@ if __name__ == "__main__":
         act = torch.rand(n, k, device="cuda"); out = torch.empty(n, m, device="cuda")
         L = b200q.lib()
         bufs = [torch.zeros(148 * 8, dtype=torch.int64, device="cuda") for _ in range(8)]
-        for rep in range(3):
+        import ctypes
+        def chain():
             for i in range(8):
-                L.b200q_debug_timestamps(__import__("ctypes").c_void_p(bufs[i].data_ptr()))
-                b200q.mul_mat(ws[i], act, out=out)
+                L.b200q_debug_timestamps(ctypes.c_void_p(bufs[i].data_ptr()))
+                b200q.mul_mat(ws[i], act, out=out, flags=int(os.environ.get('QB_FLAGS', '1')))
+        chain(); torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            chain()
+        for rep in range(3):
+            g.replay()
         torch.cuda.synchronize()
         L.b200q_debug_timestamps(None)
         T = torch.stack(bufs).cpu().numpy().reshape(8, 148, 8)
         t0 = T[:, :, 0].min()
         for i in range(3, 8):
             a = T[i]
-            names = ["start", "pdl_wait", "quant", "first_full", "end"]
-            print(f"kernel {i}: " + "  ".join(f"{names[j]}: min {int(a[:, j].min() - t0):6d} med {int(np.median(a[:, j]) - t0):6d} max {int(a[:, j].max() - t0):6d}" for j in range(5)))
+            names = ["start", "pdl_wait", "quant", "first_full", "end", "act_loaded", "q_done_t0"]
+            order = [0, 1, 5, 6, 2, 3, 4]
+            print(f"kernel {i}: " + "  ".join(f"{names[j]}: med {int(np.median(a[:, j]) - t0):6d} max {int(a[:, j].max() - t0):6d}" for j in order))
+    elif which == "small":
+        for (m, k) in [(4096, 4096), (14336, 4096), (4096, 14336), (1024, 4096)]:
+            bench(refs.Q4_K, m, k, 1)
