@@ -81,6 +81,22 @@ B200Q_API int          b200q_device_count(void);
 B200Q_API int b200q_device_info(int device, char * name, size_t name_len, size_t * total_mem, size_t * free_mem,
                                 int * cc_major, int * cc_minor, int * sm_count, size_t * l2_bytes);
 
+/* ---- device memory / streams (thin wrappers so that hosts above this ABI need no CUDA headers; they replace the
+ *      cudaMalloc / cudaMemcpyAsync / cudaStream calls of ggml-cuda.cu:551-664, 2525-2618) ------------------------- */
+B200Q_API int b200q_set_device(int device);
+B200Q_API int b200q_malloc(void ** ptr, size_t bytes);             /* B200Q_ENOMEM when the device is out of memory */
+B200Q_API int b200q_free(void * ptr);
+B200Q_API int b200q_memset(void * ptr, int value, size_t bytes, void * stream);
+#define B200Q_H2D 1
+#define B200Q_D2H 2
+#define B200Q_D2D 3
+B200Q_API int b200q_memcpy(void * dst, const void * src, size_t bytes, int kind, void * stream); /* asynchronous */
+B200Q_API int b200q_stream_create(void ** stream);
+B200Q_API int b200q_stream_destroy(void * stream);
+B200Q_API int b200q_stream_synchronize(void * stream);
+B200Q_API int b200q_host_alloc(void ** ptr, size_t bytes);         /* pinned host memory */
+B200Q_API int b200q_host_free(void * ptr);
+
 /* ---- type table (mirrors ggml_blck_size / ggml_type_size, ggml.c:586-876) -------------------- */
 B200Q_API int64_t b200q_blck_size(int type);
 B200Q_API size_t  b200q_type_size(int type);

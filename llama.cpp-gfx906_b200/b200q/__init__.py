@@ -32,7 +32,8 @@ EXPORTS = [
     "b200q_version", "b200q_last_error", "b200q_device_count", "b200q_device_info", "b200q_blck_size",
     "b200q_type_size", "b200q_row_size", "b200q_type_supported", "b200q_dequantize", "b200q_get_rows",
     "b200q_mul_mat_workspace", "b200q_mul_mat", "b200q_mul_mat_id_workspace", "b200q_mul_mat_id",
-    "b200q_mul_mat_host",
+    "b200q_mul_mat_host", "b200q_set_device", "b200q_malloc", "b200q_free", "b200q_memset", "b200q_memcpy",
+    "b200q_stream_create", "b200q_stream_destroy", "b200q_stream_synchronize", "b200q_host_alloc", "b200q_host_free",
 ]
 
 

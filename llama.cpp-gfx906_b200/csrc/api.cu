@@ -243,6 +243,39 @@ int b200q_device_info(int device, char * name, size_t name_len, size_t * total_m
     return 0;
 }
 
+// ---- memory / streams ----------------------------------------------------------------------------------
+int b200q_set_device(int device) { CUDA_TRY(cudaSetDevice(device)); return 0; }
+int b200q_malloc(void ** ptr, size_t bytes) {
+    cudaError_t e = cudaMalloc(ptr, bytes);
+    if (e == cudaErrorMemoryAllocation) {
+        cudaGetLastError();
+        return fail(B200Q_ENOMEM, "cudaMalloc(%zu) out of memory", bytes);
+    }
+    CUDA_TRY(e);
+    return 0;
+}
+int b200q_free(void * ptr) { CUDA_TRY(cudaFree(ptr)); return 0; }
+int b200q_memset(void * ptr, int value, size_t bytes, void * stream) {
+    CUDA_TRY(cudaMemsetAsync(ptr, value, bytes, (cudaStream_t) stream));
+    return 0;
+}
+int b200q_memcpy(void * dst, const void * src, size_t bytes, int kind, void * stream) {
+    const cudaMemcpyKind k = kind == B200Q_H2D ? cudaMemcpyHostToDevice
+                           : kind == B200Q_D2H ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
+    CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, k, (cudaStream_t) stream));
+    return 0;
+}
+int b200q_stream_create(void ** stream) {
+    cudaStream_t s;
+    CUDA_TRY(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    *stream = (void *) s;
+    return 0;
+}
+int b200q_stream_destroy(void * stream) { CUDA_TRY(cudaStreamDestroy((cudaStream_t) stream)); return 0; }
+int b200q_stream_synchronize(void * stream) { CUDA_TRY(cudaStreamSynchronize((cudaStream_t) stream)); return 0; }
+int b200q_host_alloc(void ** ptr, size_t bytes) { CUDA_TRY(cudaMallocHost(ptr, bytes)); return 0; }
+int b200q_host_free(void * ptr) { CUDA_TRY(cudaFreeHost(ptr)); return 0; }
+
 int64_t b200q_blck_size(int type) { return blck_elems(type); }
 size_t  b200q_type_size(int type) { return (size_t) blck_bytes(type); }
 size_t  b200q_row_size(int type, int64_t ne0) {

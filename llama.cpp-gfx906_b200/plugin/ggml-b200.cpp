@@ -1,0 +1,517 @@
+// ggml-b200.cpp — the ggml backend plugin ("B200" backend): C++ host code behind the reference's own
+// plugin API (ggml/src/ggml-backend-impl.h:17-207, GGML_BACKEND_API_VERSION 1) that routes the quantized
+// MUL_MAT / MUL_MAT_ID / GET_ROWS hot path to the hand-written sm_100a kernels behind include/b200q.h.
+//
+// It plays the role ggml-cuda.cu plays in the reference (reg :3751-3790, device :3148-3649, buffer type
+// :672-756, buffer :566-664, backend :2525-3077) but is NOT derived from it: no op besides the hot path is
+// claimed (supports_op is exact, so the scheduler leaves everything else on ggml-cpu), buffers are plain
+// device allocations with tail slack instead of per-row padding, MoE routing never touches the host, and
+// all CUDA calls go through the single runtime inside libb200q.so.
+//
+// Loading: dlopen'ed by the reference's registry (GGML_BACKEND_PATH=.../libggml-b200.so or
+// ggml_backend_load(), ggml-backend-reg.cpp:232-276,588-592).  The ggml-base symbols used here
+// (ggml_backend_buffer_init, ggml_nbytes, ...) are resolved from the host process at load time — the plugin
+// is deliberately not linked against any ggml library (and never against anything under oracle/).
+#include "ggml-backend-impl.h"
+#include "ggml-backend.h"
+#include "ggml.h"
+
+#include "../../include/b200q.h"
+#include "../../include/ggml-b200.h"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+namespace {
+
+[[noreturn]] void b200_abort(const char * what, int rc, const char * file, int line) {
+    fprintf(stderr, "ggml-b200: %s failed (%d): %s  [%s:%d]\n", what, rc, b200q_last_error(), file, line);
+    abort();  // same convention as CUDA_CHECK -> ggml_cuda_error -> GGML_ABORT (ggml-cuda.cu:85-96)
+}
+#define B200_CHECK(expr)                                           \
+    do {                                                           \
+        int rc_ = (expr);                                          \
+        if (rc_ != 0) b200_abort(#expr, rc_, __FILE__, __LINE__);  \
+    } while (0)
+
+constexpr size_t TENSOR_ALIGNMENT = 128;
+constexpr size_t BUFFER_SLACK     = 256;  // the kernels' 16-byte aligned bulk windows may over-read up to 15 bytes
+
+struct b200_device_ctx {
+    int         device;       // CUDA ordinal
+    std::string name;         // "B2000", "B2001", ... (what `test-backend-ops -b` matches)
+    std::string description;  // "NVIDIA B200"
+    void *      xfer_stream = nullptr;  // stream for the synchronous buffer operations
+    std::mutex  mu;
+};
+
+struct b200_buffer_ctx {
+    int    device;
+    void * base;
+};
+
+struct b200_backend_ctx {
+    int         device;
+    std::string name;
+    void *      stream    = nullptr;
+    void *      workspace = nullptr;
+    size_t      ws_bytes  = 0;
+};
+
+void * device_xfer_stream(b200_device_ctx * d) {
+    std::lock_guard<std::mutex> lk(d->mu);
+    if (!d->xfer_stream) {
+        B200_CHECK(b200q_set_device(d->device));
+        B200_CHECK(b200q_stream_create(&d->xfer_stream));
+    }
+    return d->xfer_stream;
+}
+
+// ------------------------------------------------------------------------------------------------ buffer
+void buffer_free(ggml_backend_buffer_t buffer) {
+    auto * ctx = (b200_buffer_ctx *) buffer->context;
+    b200q_set_device(ctx->device);
+    b200q_free(ctx->base);
+    delete ctx;
+}
+void * buffer_get_base(ggml_backend_buffer_t buffer) { return ((b200_buffer_ctx *) buffer->context)->base; }
+
+ggml_status buffer_init_tensor(ggml_backend_buffer_t, ggml_tensor *) { return GGML_STATUS_SUCCESS; }
+
+b200_device_ctx * buffer_device(ggml_backend_buffer_t buffer) {
+    return (b200_device_ctx *) buffer->buft->device->context;
+}
+
+void buffer_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, uint8_t value, size_t offset, size_t size) {
+    b200_device_ctx * d = buffer_device(buffer);
+    void *            s = device_xfer_stream(d);
+    B200_CHECK(b200q_set_device(d->device));
+    B200_CHECK(b200q_memset((char *) tensor->data + offset, value, size, s));
+    B200_CHECK(b200q_stream_synchronize(s));
+}
+void buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
+    b200_device_ctx * d = buffer_device(buffer);
+    void *            s = device_xfer_stream(d);
+    B200_CHECK(b200q_set_device(d->device));
+    B200_CHECK(b200q_memcpy((char *) tensor->data + offset, data, size, B200Q_H2D, s));
+    B200_CHECK(b200q_stream_synchronize(s));
+}
+void buffer_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * tensor, void * data, size_t offset, size_t size) {
+    b200_device_ctx * d = buffer_device(buffer);
+    void *            s = device_xfer_stream(d);
+    B200_CHECK(b200q_set_device(d->device));
+    B200_CHECK(b200q_memcpy(data, (const char *) tensor->data + offset, size, B200Q_D2H, s));
+    B200_CHECK(b200q_stream_synchronize(s));
+}
+bool buffer_is_b200(ggml_backend_buffer_t buffer);
+
+bool buffer_cpy_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * src, ggml_tensor * dst) {
+    if (!src->buffer || !buffer_is_b200(src->buffer)) return false;
+    auto * sctx = (b200_buffer_ctx *) src->buffer->context;
+    auto * dctx = (b200_buffer_ctx *) buffer->context;
+    if (sctx->device != dctx->device) return false;  // cross-device copies go through the host path of ggml-backend
+    b200_device_ctx * d = buffer_device(buffer);
+    void *            s = device_xfer_stream(d);
+    B200_CHECK(b200q_set_device(d->device));
+    B200_CHECK(b200q_memcpy(dst->data, src->data, ggml_nbytes(src), B200Q_D2D, s));
+    B200_CHECK(b200q_stream_synchronize(s));
+    return true;
+}
+void buffer_clear(ggml_backend_buffer_t buffer, uint8_t value) {
+    b200_device_ctx * d = buffer_device(buffer);
+    void *            s = device_xfer_stream(d);
+    B200_CHECK(b200q_set_device(d->device));
+    B200_CHECK(b200q_memset(((b200_buffer_ctx *) buffer->context)->base, value, buffer->size, s));
+    B200_CHECK(b200q_stream_synchronize(s));
+}
+
+const ggml_backend_buffer_i buffer_iface = {
+    /* .free_buffer   = */ buffer_free,
+    /* .get_base      = */ buffer_get_base,
+    /* .init_tensor   = */ buffer_init_tensor,
+    /* .memset_tensor = */ buffer_memset_tensor,
+    /* .set_tensor    = */ buffer_set_tensor,
+    /* .get_tensor    = */ buffer_get_tensor,
+    /* .cpy_tensor    = */ buffer_cpy_tensor,
+    /* .clear         = */ buffer_clear,
+    /* .reset         = */ nullptr,
+};
+bool buffer_is_b200(ggml_backend_buffer_t buffer) { return buffer->iface.free_buffer == buffer_free; }
+
+// ------------------------------------------------------------------------------------------- buffer type
+const char * buft_get_name(ggml_backend_buffer_type_t buft) {
+    return ((b200_device_ctx *) buft->device->context)->name.c_str();
+}
+ggml_backend_buffer_t buft_alloc_buffer(ggml_backend_buffer_type_t buft, size_t size) {
+    auto * d = (b200_device_ctx *) buft->device->context;
+    if (b200q_set_device(d->device) != 0) return nullptr;
+    void * base = nullptr;
+    if (b200q_malloc(&base, size + BUFFER_SLACK) != 0) {
+        fprintf(stderr, "ggml-b200: allocating %.2f MiB on device %d failed: %s\n", size / 1048576.0, d->device,
+                b200q_last_error());
+        return nullptr;  // OOM -> NULL, as the reference does (ggml-cuda.cu:689-694)
+    }
+    return ggml_backend_buffer_init(buft, buffer_iface, new b200_buffer_ctx{ d->device, base }, size);
+}
+size_t buft_get_alignment(ggml_backend_buffer_type_t) { return TENSOR_ALIGNMENT; }
+size_t buft_get_alloc_size(ggml_backend_buffer_type_t, const ggml_tensor * tensor) {
+    // quantized rows are read through 16-byte aligned windows: keep 16 bytes of slack behind every such tensor so a
+    // window never touches another tensor's bytes that a concurrent copy might be writing
+    return ggml_nbytes(tensor) + (ggml_is_quantized(tensor->type) ? 16 : 0);
+}
+bool buft_is_host(ggml_backend_buffer_type_t) { return false; }
+
+const ggml_backend_buffer_type_i buft_iface = {
+    /* .get_name       = */ buft_get_name,
+    /* .alloc_buffer   = */ buft_alloc_buffer,
+    /* .get_alignment  = */ buft_get_alignment,
+    /* .get_max_size   = */ nullptr,
+    /* .get_alloc_size = */ buft_get_alloc_size,
+    /* .is_host        = */ buft_is_host,
+};
+
+// ------------------------------------------------------------------------------------------------ ops
+bool type_ok(ggml_type t) { return b200q_type_supported((int) t) != 0; }
+
+bool rows_dense(const ggml_tensor * t) { return t->nb[0] == ggml_type_size(t->type); }
+
+// exactly what the kernels take; anything else is declined so the scheduler keeps it on another backend
+// (north_star: no CPU fallback for supported ops; cf. the reference's rules at ggml-cuda.cu:3265-3348)
+bool supports_mul_mat(const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0];
+    const ggml_tensor * b = op->src[1];
+    if (!type_ok(a->type) || b->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
+    if (!rows_dense(a) || !rows_dense(b) || !rows_dense(op)) return false;  // dims 1..3 may be permuted / broadcast
+    if (a->ne[0] != b->ne[0] || a->ne[0] % ggml_blck_size(a->type)) return false;
+    if (b->ne[2] % a->ne[2] || b->ne[3] % a->ne[3]) return false;
+    if (a->ne[0] > (1 << 17)) return false;  // one row must fit a shared-memory stage
+    return true;
+}
+bool supports_mul_mat_id(const ggml_tensor * op) {
+    const ggml_tensor * as  = op->src[0];
+    const ggml_tensor * b   = op->src[1];
+    const ggml_tensor * ids = op->src[2];
+    if (!type_ok(as->type) || b->type != GGML_TYPE_F32 || ids->type != GGML_TYPE_I32 || op->type != GGML_TYPE_F32) return false;
+    if (!rows_dense(as) || !rows_dense(b) || !rows_dense(op) || ids->nb[0] != sizeof(int32_t)) return false;
+    if (as->ne[3] != 1 || b->ne[3] != 1 || ids->ne[2] != 1 || ids->ne[3] != 1) return false;
+    if (as->ne[0] % ggml_blck_size(as->type) || as->ne[0] > (1 << 17)) return false;
+    if (b->ne[1] != 1 && b->ne[1] != ids->ne[0]) return false;
+    return true;
+}
+bool supports_get_rows(const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0];
+    const ggml_tensor * r = op->src[1];
+    if (!(type_ok(a->type) || a->type == GGML_TYPE_F32) || r->type != GGML_TYPE_I32 || op->type != GGML_TYPE_F32) return false;
+    if (!rows_dense(a) || !rows_dense(op) || r->ne[3] != 1) return false;
+    return true;
+}
+
+bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
+    switch (op->op) {
+        case GGML_OP_NONE:
+        case GGML_OP_VIEW:
+        case GGML_OP_RESHAPE:
+        case GGML_OP_PERMUTE:
+        case GGML_OP_TRANSPOSE:
+            return true;  // no-ops; the harness probes every tensor of the graph (test-backend-ops.cpp:1108-1115)
+        case GGML_OP_MUL_MAT:    return supports_mul_mat(op);
+        case GGML_OP_MUL_MAT_ID: return supports_mul_mat_id(op);
+        case GGML_OP_GET_ROWS:   return supports_get_rows(op);
+        default: return false;
+    }
+}
+
+void * backend_workspace(b200_backend_ctx * ctx, size_t need) {
+    if (need > ctx->ws_bytes) {
+        if (ctx->workspace) {
+            B200_CHECK(b200q_stream_synchronize(ctx->stream));
+            B200_CHECK(b200q_free(ctx->workspace));
+        }
+        const size_t bytes = need + need / 4;
+        B200_CHECK(b200q_malloc(&ctx->workspace, bytes));
+        ctx->ws_bytes = bytes;
+    }
+    return ctx->workspace;
+}
+
+uint32_t weight_flags(const ggml_tensor * w) {
+    const ggml_tensor * root = w->view_src ? w->view_src : w;
+    const bool immutable = root->buffer && ggml_backend_buffer_get_usage(root->buffer) == GGML_BACKEND_BUFFER_USAGE_WEIGHTS;
+    return immutable ? B200Q_FLAG_WEIGHTS_IMMUTABLE : 0;
+}
+
+int compute_mul_mat(b200_backend_ctx * ctx, const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0];
+    const ggml_tensor * b = op->src[1];
+    b200q_mul_mat_args  q{};
+    q.type = (int) a->type;
+    q.k = a->ne[0]; q.m = a->ne[1]; q.n = b->ne[1];
+    q.ne02 = a->ne[2]; q.ne03 = a->ne[3]; q.ne12 = b->ne[2]; q.ne13 = b->ne[3];
+    q.nb01 = a->nb[1]; q.nb02 = a->nb[2]; q.nb03 = a->nb[3];
+    q.nb11 = b->nb[1]; q.nb12 = b->nb[2]; q.nb13 = b->nb[3];
+    q.nb1 = op->nb[1]; q.nb2 = op->nb[2]; q.nb3 = op->nb[3];
+    q.flags = weight_flags(a);
+    const size_t need = b200q_mul_mat_workspace(&q);
+    void *       ws   = need ? backend_workspace(ctx, need) : nullptr;
+    return b200q_mul_mat(&q, a->data, (const float *) b->data, (float *) op->data, ws, ctx->ws_bytes, ctx->stream);
+}
+int compute_mul_mat_id(b200_backend_ctx * ctx, const ggml_tensor * op) {
+    const ggml_tensor *   as  = op->src[0];
+    const ggml_tensor *   b   = op->src[1];
+    const ggml_tensor *   ids = op->src[2];
+    b200q_mul_mat_id_args q{};
+    q.type = (int) as->type;
+    q.k = as->ne[0]; q.m = as->ne[1]; q.n_expert = as->ne[2];
+    q.n_used = ids->ne[0]; q.n_tokens = ids->ne[1]; q.b_ne1 = b->ne[1];
+    q.nb01 = as->nb[1]; q.nb02 = as->nb[2];
+    q.nb11 = b->nb[1]; q.nb12 = b->nb[2];
+    q.ids_nb1 = ids->nb[1];
+    q.nb1 = op->nb[1]; q.nb2 = op->nb[2];
+    q.flags = weight_flags(as);
+    const size_t need = b200q_mul_mat_id_workspace(&q);
+    void *       ws   = need ? backend_workspace(ctx, need) : nullptr;
+    return b200q_mul_mat_id(&q, as->data, (const float *) b->data, (const int32_t *) ids->data, (float *) op->data, ws,
+                            ctx->ws_bytes, ctx->stream);
+}
+int compute_get_rows(b200_backend_ctx * ctx, const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0];
+    const ggml_tensor * r = op->src[1];
+    b200q_get_rows_args q{};
+    q.type = (int) a->type;
+    q.ne00 = a->ne[0];
+    q.ne10 = r->ne[0]; q.ne11 = r->ne[1]; q.ne12 = r->ne[2];
+    q.nb01 = a->nb[1]; q.nb02 = a->nb[2]; q.nb03 = a->nb[3];
+    q.nb10 = r->nb[0]; q.nb11 = r->nb[1]; q.nb12 = r->nb[2];
+    q.nb1 = op->nb[1]; q.nb2 = op->nb[2]; q.nb3 = op->nb[3];
+    return b200q_get_rows(&q, a->data, (const int32_t *) r->data, (float *) op->data, ctx->stream);
+}
+
+// ------------------------------------------------------------------------------------------------ backend
+const char * backend_get_name(ggml_backend_t backend) { return ((b200_backend_ctx *) backend->context)->name.c_str(); }
+
+void backend_free(ggml_backend_t backend) {
+    auto * ctx = (b200_backend_ctx *) backend->context;
+    b200q_set_device(ctx->device);
+    if (ctx->stream) {
+        b200q_stream_synchronize(ctx->stream);
+        if (ctx->workspace) b200q_free(ctx->workspace);
+        b200q_stream_destroy(ctx->stream);
+    }
+    delete ctx;
+    delete backend;
+}
+void backend_synchronize(ggml_backend_t backend) {
+    auto * ctx = (b200_backend_ctx *) backend->context;
+    B200_CHECK(b200q_set_device(ctx->device));
+    B200_CHECK(b200q_stream_synchronize(ctx->stream));
+}
+void backend_set_tensor_async(ggml_backend_t backend, ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
+    auto * ctx = (b200_backend_ctx *) backend->context;
+    B200_CHECK(b200q_set_device(ctx->device));
+    B200_CHECK(b200q_memcpy((char *) tensor->data + offset, data, size, B200Q_H2D, ctx->stream));
+}
+void backend_get_tensor_async(ggml_backend_t backend, const ggml_tensor * tensor, void * data, size_t offset, size_t size) {
+    auto * ctx = (b200_backend_ctx *) backend->context;
+    B200_CHECK(b200q_set_device(ctx->device));
+    B200_CHECK(b200q_memcpy(data, (const char *) tensor->data + offset, size, B200Q_D2H, ctx->stream));
+}
+
+// asynchronous: kernels are enqueued on the backend's stream, the caller follows with synchronize()
+// (ggml-backend.cpp:327-335).  Graph and tensor pointers are not retained (they may be stack temporaries).
+ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
+    auto * ctx = (b200_backend_ctx *) backend->context;
+    B200_CHECK(b200q_set_device(ctx->device));
+    const int n_nodes = ggml_graph_n_nodes(cgraph);
+    for (int i = 0; i < n_nodes; ++i) {
+        ggml_tensor * node = ggml_graph_node(cgraph, i);
+        if (ggml_is_empty(node)) continue;
+        int rc = 0;
+        switch (node->op) {
+            case GGML_OP_NONE:
+            case GGML_OP_VIEW:
+            case GGML_OP_RESHAPE:
+            case GGML_OP_PERMUTE:
+            case GGML_OP_TRANSPOSE:
+                continue;
+            case GGML_OP_MUL_MAT:    rc = compute_mul_mat(ctx, node); break;
+            case GGML_OP_MUL_MAT_ID: rc = compute_mul_mat_id(ctx, node); break;
+            case GGML_OP_GET_ROWS:   rc = compute_get_rows(ctx, node); break;
+            default:
+                fprintf(stderr, "ggml-b200: op %s reached graph_compute but is not supported\n", ggml_op_name(node->op));
+                return GGML_STATUS_FAILED;
+        }
+        if (rc != 0) {
+            fprintf(stderr, "ggml-b200: %s (%s) failed (%d): %s\n", ggml_op_name(node->op), node->name, rc, b200q_last_error());
+            return rc == B200Q_ENOMEM ? GGML_STATUS_ALLOC_FAILED : GGML_STATUS_FAILED;
+        }
+    }
+    return GGML_STATUS_SUCCESS;
+}
+
+const ggml_backend_i backend_iface = {
+    /* .get_name           = */ backend_get_name,
+    /* .free               = */ backend_free,
+    /* .set_tensor_async   = */ backend_set_tensor_async,
+    /* .get_tensor_async   = */ backend_get_tensor_async,
+    /* .cpy_tensor_async   = */ nullptr,
+    /* .synchronize        = */ backend_synchronize,
+    /* .graph_plan_create  = */ nullptr,
+    /* .graph_plan_free    = */ nullptr,
+    /* .graph_plan_update  = */ nullptr,
+    /* .graph_plan_compute = */ nullptr,
+    /* .graph_compute      = */ backend_graph_compute,
+    /* .event_record       = */ nullptr,
+    /* .event_wait         = */ nullptr,
+};
+
+ggml_guid_t backend_guid() {
+    static ggml_guid guid = { 0xb2, 0x00, 0x71, 0x5e, 0x10, 0x0a, 0x4c, 0x0d, 0x9e, 0x51, 0x67, 0x67, 0x6d, 0x6c, 0x62, 0x32 };
+    return &guid;
+}
+
+// ------------------------------------------------------------------------------------------------ device
+struct b200_device {
+    ggml_backend_device      dev;
+    ggml_backend_buffer_type buft;
+    b200_device_ctx          ctx;
+};
+
+const char * device_get_name(ggml_backend_dev_t dev) { return ((b200_device_ctx *) dev->context)->name.c_str(); }
+const char * device_get_description(ggml_backend_dev_t dev) { return ((b200_device_ctx *) dev->context)->description.c_str(); }
+void device_get_memory(ggml_backend_dev_t dev, size_t * free, size_t * total) {
+    auto * d = (b200_device_ctx *) dev->context;
+    *free = *total = 0;
+    b200q_device_info(d->device, nullptr, 0, total, free, nullptr, nullptr, nullptr, nullptr);
+}
+enum ggml_backend_dev_type device_get_type(ggml_backend_dev_t) { return GGML_BACKEND_DEVICE_TYPE_GPU; }
+void device_get_props(ggml_backend_dev_t dev, ggml_backend_dev_props * props) {
+    props->name        = device_get_name(dev);
+    props->description = device_get_description(dev);
+    props->type        = device_get_type(dev);
+    device_get_memory(dev, &props->memory_free, &props->memory_total);
+    props->caps = { /* async */ true, /* host_buffer */ false, /* buffer_from_host_ptr */ false, /* events */ false };
+}
+ggml_backend_t device_init_backend(ggml_backend_dev_t dev, const char *) {
+    auto * d   = (b200_device_ctx *) dev->context;
+    auto * ctx = new b200_backend_ctx{ d->device, d->name };
+    if (b200q_set_device(d->device) != 0 || b200q_stream_create(&ctx->stream) != 0) {
+        fprintf(stderr, "ggml-b200: cannot initialise device %d: %s\n", d->device, b200q_last_error());
+        delete ctx;
+        return nullptr;
+    }
+    return new ggml_backend{ backend_guid(), backend_iface, dev, ctx };
+}
+ggml_backend_buffer_type_t device_get_buffer_type(ggml_backend_dev_t dev) {
+    return &((b200_device *) ((char *) dev - offsetof(b200_device, dev)))->buft;
+}
+bool device_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) {
+    return buft->iface.get_name == buft_get_name && buft->device == dev;
+}
+bool device_offload_op(ggml_backend_dev_t, const ggml_tensor * op) {
+    // weights living in host memory are worth shipping to the device for batches, as in the reference
+    // (ggml-cuda.cu offload_op: batch >= 32)
+    const int64_t batch = op->op == GGML_OP_MUL_MAT_ID ? op->ne[2] : op->ne[1];
+    return (op->op == GGML_OP_MUL_MAT || op->op == GGML_OP_MUL_MAT_ID) && batch >= 32;
+}
+
+const ggml_backend_device_i device_iface = {
+    /* .get_name             = */ device_get_name,
+    /* .get_description      = */ device_get_description,
+    /* .get_memory           = */ device_get_memory,
+    /* .get_type             = */ device_get_type,
+    /* .get_props            = */ device_get_props,
+    /* .init_backend         = */ device_init_backend,
+    /* .get_buffer_type      = */ device_get_buffer_type,
+    /* .get_host_buffer_type = */ nullptr,
+    /* .buffer_from_host_ptr = */ nullptr,
+    /* .supports_op          = */ device_supports_op,
+    /* .supports_buft        = */ device_supports_buft,
+    /* .offload_op           = */ device_offload_op,
+    /* .event_new            = */ nullptr,
+    /* .event_free           = */ nullptr,
+    /* .event_synchronize    = */ nullptr,
+};
+
+// ------------------------------------------------------------------------------------------------ registry
+struct b200_reg_ctx {
+    std::vector<b200_device *> devices;
+};
+
+const char * reg_get_name(ggml_backend_reg_t) { return "B200"; }
+size_t       reg_get_device_count(ggml_backend_reg_t reg) { return ((b200_reg_ctx *) reg->context)->devices.size(); }
+ggml_backend_dev_t reg_get_device(ggml_backend_reg_t reg, size_t index) {
+    auto * ctx = (b200_reg_ctx *) reg->context;
+    return index < ctx->devices.size() ? &ctx->devices[index]->dev : nullptr;
+}
+
+ggml_backend_feature * get_features(ggml_backend_reg_t) {
+    static ggml_backend_feature features[] = {
+        { "ARCHS", "1000a" }, { "TMA_BULK", "1" }, { "PDL", "1" }, { "DP4A", "1" }, { nullptr, nullptr },
+    };
+    return features;
+}
+void * reg_get_proc_address(ggml_backend_reg_t, const char * name) {
+    if (strcmp(name, "ggml_backend_get_features") == 0) return (void *) get_features;
+    return nullptr;
+}
+
+const ggml_backend_reg_i reg_iface = {
+    /* .get_name         = */ reg_get_name,
+    /* .get_device_count = */ reg_get_device_count,
+    /* .get_device       = */ reg_get_device,
+    /* .get_proc_address = */ reg_get_proc_address,
+};
+
+int count_blackwell_devices(std::vector<int> * ordinals) {
+    int n = b200q_device_count(), found = 0;
+    for (int i = 0; i < n; ++i) {
+        int major = 0, minor = 0;
+        if (b200q_device_info(i, nullptr, 0, nullptr, nullptr, &major, &minor, nullptr, nullptr) == 0 && major == 10) {
+            if (ordinals) ordinals->push_back(i);
+            ++found;
+        }
+    }
+    return found;
+}
+
+}  // namespace
+
+extern "C" {
+
+// named entry point for static registration (the reference's ggml_backend_cuda_reg, ggml-cuda.cu:3751-3790)
+ggml_backend_reg_t ggml_backend_b200_reg(void) {
+    static std::mutex       mu;
+    static ggml_backend_reg reg;
+    static bool             initialised = false;
+    std::lock_guard<std::mutex> lk(mu);
+    if (!initialised) {
+        auto *           ctx = new b200_reg_ctx;
+        std::vector<int> ordinals;
+        count_blackwell_devices(&ordinals);
+        for (size_t i = 0; i < ordinals.size(); ++i) {
+            auto * d            = new b200_device;
+            d->ctx.device       = ordinals[i];
+            d->ctx.name         = "B200" + std::to_string(i);
+            char name[128]      = "B200";
+            b200q_device_info(ordinals[i], name, sizeof(name), nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+            d->ctx.description  = name;
+            d->dev              = ggml_backend_device{ device_iface, &reg, &d->ctx };
+            d->buft             = ggml_backend_buffer_type{ buft_iface, &d->dev, nullptr };
+            ctx->devices.push_back(d);
+        }
+        reg         = ggml_backend_reg{ GGML_BACKEND_API_VERSION, reg_iface, ctx };
+        initialised = true;
+    }
+    return &reg;
+}
+
+// dlopen entry points (ggml-backend-impl.h:215-251; looked up by name in ggml-backend-reg.cpp:232-276)
+ggml_backend_reg_t ggml_backend_init(void) { return ggml_backend_b200_reg(); }
+int                ggml_backend_score(void) { return count_blackwell_devices(nullptr) > 0 ? 100 : 0; }
+
+}  // extern "C"
