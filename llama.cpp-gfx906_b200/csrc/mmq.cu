@@ -1,7 +1,550 @@
-// mmq.cu — placeholder until the tcgen05 kernel lands (n > 8 currently runs as repeated GEMV passes)
+// mmq.cu — prompt-processing matmul (n > 8 activation columns) for GGUF block formats on the 5th-generation
+// tensor cores of sm_100a (tcgen05.mma, accumulators in TMEM, operands fed by 1-D TMA bulk copies).
+//
+// Replaces the reference's quantize_mmq_q8_1 + mul_mat_q pair (ggml-cuda/quantize.cu:50-146, mmq.cuh:3134-3370,
+// tile loaders mmq.cuh:277-336 q4_0, :637-697 q8_0, :699-762 mxfp4, :1726-1833 q4_K, :2027-2111 q6_K, stream-K fixup
+// :3373-3522, host side mmq.cu:71-143).  It is NOT a port: the reference multiplies int8 tiles with mma.sync and pays an
+// fp32 scale FMA per accumulator per 32-element block in registers (mmq.cuh:923-926).  On tcgen05 the accumulator lives
+// in TMEM and a kind::i8 MMA consumes exactly one 32-block per instruction, so per-block scales would force a TMEM
+// read-out + 2 CUDA-core ops per accumulator element per block (4x over the FP32-pipe budget at the i8 MMA rate, DESIGN.md
+// "H2").  Instead the per-block scales are folded into the A operand where they are exact to 2^-9: weight tiles are
+// dequantized on the fly by CUDA-core warps to bf16 (d * q computed in fp32, one rounding) into the canonical
+// 128-byte-swizzled K-major UMMA layout, activations are rounded f32 -> bf16 once (no q8_1 quantization at all, which
+// is MORE accurate than the reference's int8 activations), and kind::f16 MMAs accumulate the whole K extent in fp32 in
+// TMEM with no per-block epilogue.
+//
+// CTA = 15 warps, one CTA per SM, persistent over output tiles of 128 weight rows x 256 activation columns:
+//   warps 0-3   epilogue: tcgen05.ld of the finished accumulator (TMEM lane = weight row, column = token) and
+//               coalesced stores to dst (ggml layout: rows contiguous); overlaps the next tile's main loop because
+//               the 512 TMEM columns hold two 256-column accumulators
+//   warp  4     W producer: per stage one bulk copy per weight row of the raw quantized bytes of 256 k-elements,
+//               16-byte-aligned windows around arbitrarily aligned 17/18/34/210-byte blocks
+//   warp  5     B producer: one bulk copy per 64-wide k-chunk of the bf16 activation tile, which mmq_pack_act has
+//               already written in the exact swizzled shared-memory image (so no tensor map is needed)
+//   warp  6     MMA issuer: one thread, 4 x tcgen05.mma (M=128, N<=256, K=16) per k-chunk, tcgen05.commit to free stages
+//   warps 7-14  dequantizers: thread = (row, 32-element block); raw bytes -> fp32 -> bf16 -> 4 x STS.128 (conflict-free
+//               under the 128B swizzle), fence.proxy.async, arrive
 #include "mmq.cuh"
+
+#include "../../include/b200q.h"
+#include "blocks.cuh"
+#include "sm100.cuh"
+
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <mutex>
+#include <set>
+
 namespace b200q {
-bool   mmq_supported(int, int64_t) { return false; }
-size_t mmq_workspace_bytes(int64_t, int64_t, int64_t) { return 0; }
-int    mmq_launch(const MmqArgs &, void *, cudaStream_t, int, std::string & err) { err = "mmq not built"; return -2; }
+
+namespace {
+
+using namespace sm100;
+
+constexpr int TILE_M  = 128;  // weight rows per tile (UMMA M)
+constexpr int TILE_N  = 256;  // activation columns per tile (UMMA N, <= 256)
+constexpr int CHUNK_K = 64;   // bf16 elements per 128-byte swizzled row
+constexpr int WSTAGE_K = 256; // k-elements of raw weights per W stage
+constexpr int AB_STAGES = 3;
+constexpr int W_STAGES  = 2;
+constexpr int A_STAGE_BYTES = TILE_M * 128;  // 16 KB
+constexpr int B_STAGE_BYTES = TILE_N * 128;  // 32 KB
+constexpr int N_EPI_WARPS = 4, N_DQ_WARPS = 8;
+constexpr int WARP_WPROD = 4, WARP_BPROD = 5, WARP_MMA = 6, WARP_DQ0 = 7;
+constexpr int NTHREADS = (WARP_DQ0 + N_DQ_WARPS) * 32;  // 480
+constexpr int TMEM_COLS = 512;
+
+// barrier slots (8 bytes each) inside the barrier block
+enum {
+    BAR_W_FULL  = 0,                       // [W_STAGES]  count 32 (producer lanes) + tx bytes
+    BAR_W_EMPTY = BAR_W_FULL + W_STAGES,   // [W_STAGES]  count N_DQ_WARPS
+    BAR_A_FULL  = BAR_W_EMPTY + W_STAGES,  // [AB_STAGES] count N_DQ_WARPS
+    BAR_B_FULL  = BAR_A_FULL + AB_STAGES,  // [AB_STAGES] count 1 + tx bytes
+    BAR_AB_EMPTY = BAR_B_FULL + AB_STAGES, // [AB_STAGES] count 1 (tcgen05.commit)
+    BAR_ACC_FULL = BAR_AB_EMPTY + AB_STAGES,  // [2] count 1 (tcgen05.commit)
+    BAR_ACC_EMPTY = BAR_ACC_FULL + 2,         // [2] count N_EPI_WARPS
+    BAR_COUNT = BAR_ACC_EMPTY + 2,
+};
+
+struct MmqParams {
+    const uint8_t * w;
+    const uint8_t * actp;  // packed bf16 activation tiles (mmq_pack_act)
+    float *         dst;
+    int   k, m, n;
+    int   ne12, r2, r3, nbatch;
+    long long w_nb1, w_nb2, w_nb3;
+    long long d_nb1, d_nb2, d_nb3;
+    int   m_tiles, n_tiles, k_chunks, w_stages_per_tile;
+    int   piece_bytes;   // raw bytes of WSTAGE_K elements of one row
+    int   blk_bytes;     // bytes per 32 elements (32-block types) — used for the ragged last stage
+    int   w_pitch;       // shared-memory pitch of one row piece
+    int   w_stage_bytes; // TILE_M * w_pitch
+    uint32_t off_b, off_w, off_bar;  // shared-memory offsets from the 1024-aligned base
+};
+
+struct PackParams {
+    const float * act;
+    uint8_t *     out;
+    int   k, n, ne12, nbatch, n_tiles, k_chunks;
+    long long a_nb1, a_nb2, a_nb3;
+    int   vec4;
+};
+
+// f32 activations [n][k] (byte strides) -> bf16 tiles in the shared-memory image the MMA reads:
+//   block (batch, n_tile, k_chunk) = TILE_N rows x 128 bytes; 16-byte chunk c of row j sits at chunk (c ^ (j & 7)).
+// One thread = one 16-byte chunk (8 elements).  Rows >= n are written as zeros.
+__global__ void __launch_bounds__(256) mmq_pack_act(const PackParams p) {
+    const long long chunks_per_block = TILE_N * 8;
+    const long long total = (long long) p.nbatch * p.n_tiles * p.k_chunks * chunks_per_block;
+    for (long long idx = (long long) blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+         idx += (long long) gridDim.x * blockDim.x) {
+        const int       c    = (int) (idx & 7);
+        const int       j    = (int) ((idx >> 3) & (TILE_N - 1));
+        const long long blk  = idx / chunks_per_block;
+        const int       kc   = (int) (blk % p.k_chunks);
+        const long long rest = blk / p.k_chunks;
+        const int       nt   = (int) (rest % p.n_tiles);
+        const int       b    = (int) (rest / p.n_tiles);
+        const int       col  = nt * TILE_N + j;
+        uint4           o    = make_uint4(0, 0, 0, 0);
+        if (col < p.n) {
+            const int     i13 = b / p.ne12, i12 = b - i13 * p.ne12;
+            const float * src = (const float *) ((const char *) p.act + (long long) col * p.a_nb1 + (long long) i12 * p.a_nb2 +
+                                                 (long long) i13 * p.a_nb3) + kc * CHUNK_K + c * 8;
+            float v[8];
+            if (p.vec4) {
+                const float4 x = __ldg((const float4 *) src), y = __ldg((const float4 *) src + 1);
+                v[0] = x.x; v[1] = x.y; v[2] = x.z; v[3] = x.w; v[4] = y.x; v[5] = y.y; v[6] = y.z; v[7] = y.w;
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[i] = __ldg(src + i);
+            }
+            __nv_bfloat162 h0 = __floats2bfloat162_rn(v[0], v[1]), h1 = __floats2bfloat162_rn(v[2], v[3]);
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[4], v[5]), h3 = __floats2bfloat162_rn(v[6], v[7]);
+            o.x = *(uint32_t *) &h0; o.y = *(uint32_t *) &h1; o.z = *(uint32_t *) &h2; o.w = *(uint32_t *) &h3;
+        }
+        *(uint4 *) (p.out + blk * (long long) B_STAGE_BYTES + (long long) j * 128 + ((c ^ (j & 7)) << 4)) = o;
+    }
+}
+
+// ---- dequantizers: 32 consecutive k-elements of one row piece -> fp32 ------------------------------------------
+// `piece` is a generic pointer into shared memory at the first byte of the row's W-stage piece (a block / super-block
+// boundary, ANY byte alignment); b32 = index of the 32-element block inside the piece (0..7).
+__device__ __forceinline__ uint32_t ldu32(const uint8_t * p) {
+    const uintptr_t  a = (uintptr_t) p;
+    const uint32_t * w = (const uint32_t *) (a & ~(uintptr_t) 3);
+    return __funnelshift_r(w[0], w[1], (int) (a & 3) * 8);
+}
+__device__ __forceinline__ float ldh(const uint8_t * p) {  // fp16 at a 1-byte aligned address
+    return half_bits_to_float((uint16_t) (p[0] | (p[1] << 8)));
+}
+
+template <int T> struct Dq {
+    // generic (slow) path: the bit-exact scalar decoder of blocks.cuh
+    static __device__ __forceinline__ void run(const uint8_t * piece, int b32, float (&v)[32]) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = decode_elem<T>(piece, (int64_t) b32 * 32 + i);
+    }
+};
+template <> struct Dq<T_Q8_0> {
+    static __device__ __forceinline__ void run(const uint8_t * piece, int b32, float (&v)[32]) {
+        const uint8_t * b = piece + b32 * 34;
+        const float     d = ldh(b);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t w = ldu32(b + 2 + 4 * i);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[4 * i + j] = d * (float) (int8_t) (w >> (8 * j));
+        }
+    }
+};
+template <> struct Dq<T_Q4_0> {
+    static __device__ __forceinline__ void run(const uint8_t * piece, int b32, float (&v)[32]) {
+        const uint8_t * b  = piece + b32 * 18;
+        const float     d  = ldh(b);
+        const float     m8 = -8.0f * d;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t w = ldu32(b + 2 + 4 * i);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                v[4 * i + j]      = fmaf((float) ((w >> (8 * j)) & 0xF), d, m8);
+                v[16 + 4 * i + j] = fmaf((float) ((w >> (8 * j + 4)) & 0xF), d, m8);
+            }
+        }
+    }
+};
+template <> struct Dq<T_MXFP4> {
+    static __device__ __forceinline__ float kv(uint32_t nib) {  // doubled E2M1 code point (ggml-common.h:1094-1096)
+        const uint32_t mag = __byte_perm(0x03020100u, 0x0C080604u, nib & 7u) & 0xFFu;
+        const float    f   = (float) mag;
+        return (nib & 8u) ? -f : f;
+    }
+    static __device__ __forceinline__ void run(const uint8_t * piece, int b32, float (&v)[32]) {
+        const uint8_t * b = piece + b32 * 17;
+        const float     d = e8m0_half_to_float(b[0]);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t w = ldu32(b + 1 + 4 * i);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                v[4 * i + j]      = d * kv((w >> (8 * j)) & 0xF);
+                v[16 + 4 * i + j] = d * kv((w >> (8 * j + 4)) & 0xF);
+            }
+        }
+    }
+};
+template <> struct Dq<T_Q4_K> {
+    static __device__ __forceinline__ void run(const uint8_t * piece, int b32, float (&v)[32]) {
+        const float d = ldh(piece), dmin = ldh(piece + 2);
+        int         sc, mn;
+        k4_scale_min(b32, piece + 4, sc, mn);
+        const float     dsc = d * (float) sc, dm = -dmin * (float) mn;
+        const uint8_t * qs  = piece + 16 + 32 * (b32 >> 1);
+        const int       sh  = 4 * (b32 & 1);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t w = ldu32(qs + 4 * i) >> sh;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[4 * i + j] = fmaf((float) ((w >> (8 * j)) & 0xF), dsc, dm);
+        }
+    }
+};
+template <> struct Dq<T_Q6_K> {
+    static __device__ __forceinline__ void run(const uint8_t * piece, int b32, float (&v)[32]) {
+        const int       n128 = b32 >> 2, quad = b32 & 3;
+        const uint8_t * ql   = piece + 64 * n128 + 32 * (quad & 1);
+        const uint8_t * qh   = piece + 128 + 32 * n128;
+        const int       shl  = 4 * (quad >> 1), shh = 2 * quad;
+        const float     d    = ldh(piece + 208);
+        const float     s0   = d * (float) (int8_t) piece[192 + 8 * n128 + 2 * quad];
+        const float     s1   = d * (float) (int8_t) piece[192 + 8 * n128 + 2 * quad + 1];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t lo = (ldu32(ql + 4 * i) >> shl) & 0x0F0F0F0Fu;
+            const uint32_t hi = ((ldu32(qh + 4 * i) >> shh) & 0x03030303u) << 4;
+            const uint32_t q  = lo | hi;
+            const float    s  = i < 4 ? s0 : s1;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[4 * i + j] = s * (float) ((int) ((q >> (8 * j)) & 0xFF) - 32);
+        }
+    }
+};
+
+extern __shared__ __align__(1024) uint8_t mmq_smem_raw[];
+
+struct TileCoord {
+    int b, mt, nt;
+};
+__device__ __forceinline__ TileCoord tile_coord(const MmqParams & p, int t) {
+    TileCoord c;
+    c.nt           = t % p.n_tiles;
+    const int rest = t / p.n_tiles;
+    c.mt           = rest % p.m_tiles;
+    c.b            = rest / p.m_tiles;
+    return c;
+}
+// bytes of the raw row piece of W stage `ws` (the last stage of a row may be ragged for 32-element block types)
+__device__ __forceinline__ int piece_bytes_of(const MmqParams & p, int ws) {
+    const int elems = min(WSTAGE_K, p.k - ws * WSTAGE_K);
+    return elems == WSTAGE_K ? p.piece_bytes : (elems >> 5) * p.blk_bytes;
+}
+
+template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const MmqParams p) {
+    // 1024-byte aligned base (128B-swizzle atoms)
+    const uint32_t raw_addr = smem_u32(mmq_smem_raw);
+    const uint32_t base     = (raw_addr + 1023u) & ~1023u;
+    uint8_t *      sm       = mmq_smem_raw + (base - raw_addr);
+    const uint32_t bars     = base + p.off_bar;
+    volatile uint32_t * tmem_slot = (volatile uint32_t *) (sm + p.off_bar + BAR_COUNT * 8);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int num_tiles = p.nbatch * p.m_tiles * p.n_tiles;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < W_STAGES; ++s) {
+            mbar_init(bars + 8 * (BAR_W_FULL + s), 32);
+            mbar_init(bars + 8 * (BAR_W_EMPTY + s), N_DQ_WARPS);
+        }
+        for (int s = 0; s < AB_STAGES; ++s) {
+            mbar_init(bars + 8 * (BAR_A_FULL + s), N_DQ_WARPS);
+            mbar_init(bars + 8 * (BAR_B_FULL + s), 1);
+            mbar_init(bars + 8 * (BAR_AB_EMPTY + s), 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(bars + 8 * (BAR_ACC_FULL + s), 1);
+            mbar_init(bars + 8 * (BAR_ACC_EMPTY + s), N_EPI_WARPS);
+        }
+        mbar_fence_init();
+    }
+    if (warp == WARP_MMA) {
+        tmem_alloc(smem_u32((const void *) tmem_slot), TMEM_COLS);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == WARP_WPROD) {
+        // ------------------------------------------------------------------ raw weight rows -> W ring
+        int wsi = 0;
+        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            const TileCoord tc  = tile_coord(p, t);
+            const int       i13 = tc.b / p.ne12, i12 = tc.b - i13 * p.ne12;
+            const uint8_t * wb  = p.w + (long long) (i12 / p.r2) * p.w_nb2 + (long long) (i13 / p.r3) * p.w_nb3;
+            for (int ws = 0; ws < p.w_stages_per_tile; ++ws, ++wsi) {
+                const int slot = wsi % W_STAGES;
+                mbar_wait(bars + 8 * (BAR_W_EMPTY + slot), ((wsi / W_STAGES) & 1) ^ 1);
+                const int      pb   = piece_bytes_of(p, ws);
+                const uint32_t full = bars + 8 * (BAR_W_FULL + slot);
+                const uint8_t * src[4];
+                uint32_t        bytes[4], total = 0;
+#pragma unroll
+                for (int rr = 0; rr < 4; ++rr) {
+                    const int row = min(tc.mt * TILE_M + lane + 32 * rr, p.m - 1);
+                    const uint8_t * a = wb + (long long) row * p.w_nb1 + (long long) ws * p.piece_bytes;
+                    const uint32_t  lead = (uint32_t) ((uintptr_t) a & 15);
+                    src[rr]   = a - lead;
+                    bytes[rr] = (lead + (uint32_t) pb + 15u) & ~15u;
+                    total += bytes[rr];
+                }
+                mbar_expect_tx(full, total);
+#pragma unroll
+                for (int rr = 0; rr < 4; ++rr) {
+                    bulk_g2s(base + p.off_w + (uint32_t) slot * p.w_stage_bytes + (uint32_t) (lane + 32 * rr) * p.w_pitch,
+                             src[rr], bytes[rr], full);
+                }
+            }
+        }
+    } else if (warp == WARP_BPROD) {
+        // ------------------------------------------------------------------ packed activation tiles -> B ring
+        if (lane == 0) {
+            int g = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                const TileCoord tc    = tile_coord(p, t);
+                const int       ncols = min(TILE_N, p.n - tc.nt * TILE_N);
+                const uint32_t  bytes = (uint32_t) ((ncols + 15) & ~15) * 128u;
+                const uint8_t * src   = p.actp + ((long long) (tc.b * p.n_tiles + tc.nt) * p.k_chunks) * B_STAGE_BYTES;
+                for (int c = 0; c < p.k_chunks; ++c, ++g) {
+                    const int slot = g % AB_STAGES;
+                    mbar_wait(bars + 8 * (BAR_AB_EMPTY + slot), ((g / AB_STAGES) & 1) ^ 1);
+                    const uint32_t full = bars + 8 * (BAR_B_FULL + slot);
+                    mbar_expect_tx(full, bytes);
+                    bulk_g2s(base + p.off_b + (uint32_t) slot * B_STAGE_BYTES, src + (long long) c * B_STAGE_BYTES, bytes, full);
+                }
+            }
+        }
+    } else if (warp == WARP_MMA) {
+        // ------------------------------------------------------------------ tensor-core issue (one thread)
+        if (lane == 0) {
+            int g = 0, ti = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++ti) {
+                const TileCoord tc    = tile_coord(p, t);
+                const int       ncols = min(TILE_N, p.n - tc.nt * TILE_N);
+                const uint32_t  idesc = umma_idesc_bf16_f32(TILE_M, (ncols + 15) & ~15);
+                const int       ab    = ti & 1;
+                mbar_wait(bars + 8 * (BAR_ACC_EMPTY + ab), ((ti >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t) ab * TILE_N;
+                for (int c = 0; c < p.k_chunks; ++c, ++g) {
+                    const int      slot = g % AB_STAGES;
+                    const uint32_t ph   = (g / AB_STAGES) & 1;
+                    mbar_wait(bars + 8 * (BAR_A_FULL + slot), ph);
+                    mbar_wait(bars + 8 * (BAR_B_FULL + slot), ph);
+                    tc_fence_after();
+                    const uint64_t adesc = umma_desc_k_sw128(base + (uint32_t) slot * A_STAGE_BYTES);
+                    const uint64_t bdesc = umma_desc_k_sw128(base + p.off_b + (uint32_t) slot * B_STAGE_BYTES);
+#pragma unroll
+                    for (int kk = 0; kk < CHUNK_K / 16; ++kk) {
+                        // +32 bytes (16 bf16) along K inside the 128-byte swizzle atom = +2 in the address field
+                        umma_f16(d_tmem, adesc + 2 * kk, bdesc + 2 * kk, idesc, (c | kk) != 0);
+                    }
+                    umma_commit(bars + 8 * (BAR_AB_EMPTY + slot));
+                }
+                umma_commit(bars + 8 * (BAR_ACC_FULL + ab));
+            }
+        }
+    } else if (warp >= WARP_DQ0) {
+        // ------------------------------------------------------------------ dequantizers: W ring -> A ring (bf16)
+        const int dt   = threadIdx.x - WARP_DQ0 * 32;  // 0..255
+        const int row  = dt >> 1, half = dt & 1;
+        const uint32_t a_row_off = (uint32_t) row * 128u;
+        const uint32_t sw        = (uint32_t) (row & 7);
+        int wsi = 0, g = 0;
+        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            const TileCoord tc  = tile_coord(p, t);
+            const int       i13 = tc.b / p.ne12, i12 = tc.b - i13 * p.ne12;
+            const uint8_t * wb  = p.w + (long long) (i12 / p.r2) * p.w_nb2 + (long long) (i13 / p.r3) * p.w_nb3;
+            const int       grow = min(tc.mt * TILE_M + row, p.m - 1);
+            const uint8_t * rowp = wb + (long long) grow * p.w_nb1;
+            for (int ws = 0; ws < p.w_stages_per_tile; ++ws, ++wsi) {
+                const int wslot = wsi % W_STAGES;
+                mbar_wait(bars + 8 * (BAR_W_FULL + wslot), (wsi / W_STAGES) & 1);
+                const uint32_t  lead  = (uint32_t) ((uintptr_t) (rowp + (long long) ws * p.piece_bytes) & 15);
+                const uint8_t * piece = sm + p.off_w + (uint32_t) wslot * p.w_stage_bytes + (uint32_t) row * p.w_pitch + lead;
+                const int nchunks = min(WSTAGE_K / CHUNK_K, p.k_chunks - ws * (WSTAGE_K / CHUNK_K));
+                for (int c = 0; c < nchunks; ++c, ++g) {
+                    const int slot = g % AB_STAGES;
+                    float v[32];
+                    Dq<T>::run(piece, 2 * c + half, v);
+                    mbar_wait(bars + 8 * (BAR_AB_EMPTY + slot), ((g / AB_STAGES) & 1) ^ 1);
+                    uint8_t * arow = sm + (uint32_t) slot * A_STAGE_BYTES + a_row_off;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        __nv_bfloat162 h0 = __floats2bfloat162_rn(v[8 * i + 0], v[8 * i + 1]);
+                        __nv_bfloat162 h1 = __floats2bfloat162_rn(v[8 * i + 2], v[8 * i + 3]);
+                        __nv_bfloat162 h2 = __floats2bfloat162_rn(v[8 * i + 4], v[8 * i + 5]);
+                        __nv_bfloat162 h3 = __floats2bfloat162_rn(v[8 * i + 6], v[8 * i + 7]);
+                        uint4 o;
+                        o.x = *(uint32_t *) &h0; o.y = *(uint32_t *) &h1; o.z = *(uint32_t *) &h2; o.w = *(uint32_t *) &h3;
+                        *(uint4 *) (arow + ((((uint32_t) (4 * half + i)) ^ sw) << 4)) = o;
+                    }
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bars + 8 * (BAR_A_FULL + slot));
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bars + 8 * (BAR_W_EMPTY + wslot));
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------ epilogue: TMEM -> dst
+        int ti = 0;
+        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++ti) {
+            const TileCoord tc  = tile_coord(p, t);
+            const int       i13 = tc.b / p.ne12, i12 = tc.b - i13 * p.ne12;
+            const int       ab  = ti & 1;
+            const int       row = tc.mt * TILE_M + warp * 32 + lane;
+            const int       n0  = tc.nt * TILE_N;
+            const int       ncols = min(TILE_N, p.n - n0);
+            char * dbase = (char *) p.dst + (long long) i12 * p.d_nb2 + (long long) i13 * p.d_nb3 + (long long) row * 4;
+            mbar_wait(bars + 8 * (BAR_ACC_FULL + ab), (ti >> 1) & 1);
+            tc_fence_after();
+            for (int c0 = 0; c0 < ncols; c0 += 32) {
+                float v[32];
+                tmem_ld32(tmem_base + ((uint32_t) (warp * 32) << 16) + (uint32_t) (ab * TILE_N + c0), v);
+                if (row < p.m) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        if (c0 + j < ncols) {
+                            *(float *) (dbase + (long long) (n0 + c0 + j) * p.d_nb1) = v[j];
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bars + 8 * (BAR_ACC_EMPTY + ab));
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == WARP_MMA) {
+        tmem_dealloc(tmem_base, TMEM_COLS);
+    }
+}
+
+typedef void (*mmq_kernel_t)(const MmqParams);
+
+mmq_kernel_t mmq_kernel_for(int type) {
+    switch (type) {
+        case T_Q4_0:  return mmq_kernel<T_Q4_0>;
+        case T_Q4_1:  return mmq_kernel<T_Q4_1>;
+        case T_Q5_0:  return mmq_kernel<T_Q5_0>;
+        case T_Q5_1:  return mmq_kernel<T_Q5_1>;
+        case T_Q8_0:  return mmq_kernel<T_Q8_0>;
+        case T_MXFP4: return mmq_kernel<T_MXFP4>;
+        case T_Q4_K:  return mmq_kernel<T_Q4_K>;
+        case T_Q5_K:  return mmq_kernel<T_Q5_K>;
+        case T_Q6_K:  return mmq_kernel<T_Q6_K>;
+        default: return nullptr;
+    }
+}
+
+inline int round_up_i(int x, int a) { return (x + a - 1) / a * a; }
+
+}  // namespace
+
+bool mmq_supported(int type, int64_t k) {
+    return mmq_kernel_for(type) != nullptr && k > 0 && k % CHUNK_K == 0 && k % blck_elems(type) == 0;
+}
+
+size_t mmq_workspace_bytes(int64_t k, int64_t n, int64_t nbatch) {
+    const int64_t n_tiles = (n + TILE_N - 1) / TILE_N;
+    return (size_t) (nbatch * n_tiles * (k / CHUNK_K)) * B_STAGE_BYTES;
+}
+
+int mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, std::string & err) {
+    mmq_kernel_t fn = mmq_kernel_for(a.type);
+    if (!fn || !mmq_supported(a.type, a.k)) {
+        err = "mmq: unsupported type / k";
+        return B200Q_ENOTSUP;
+    }
+    if (((uintptr_t) workspace & 15) != 0) {
+        err = "mmq: workspace must be 16-byte aligned";
+        return B200Q_EINVAL;
+    }
+    const int nbatch = (int) (a.ne12 * a.ne13);
+
+    PackParams pp{};
+    pp.act = a.act; pp.out = (uint8_t *) workspace;
+    pp.k = (int) a.k; pp.n = (int) a.n; pp.ne12 = (int) a.ne12; pp.nbatch = nbatch;
+    pp.n_tiles  = (int) ((a.n + TILE_N - 1) / TILE_N);
+    pp.k_chunks = (int) (a.k / CHUNK_K);
+    pp.a_nb1 = a.a_nb1; pp.a_nb2 = a.a_nb2; pp.a_nb3 = a.a_nb3;
+    pp.vec4  = ((uintptr_t) a.act & 15) == 0 && (a.a_nb1 & 15) == 0 && (a.a_nb2 & 15) == 0 && (a.a_nb3 & 15) == 0;
+    {
+        const long long total = (long long) nbatch * pp.n_tiles * pp.k_chunks * TILE_N * 8;
+        const int       grid  = (int) std::min<long long>((total + 255) / 256, (long long) sms * 8);
+        mmq_pack_act<<<grid, 256, 0, st>>>(pp);
+    }
+
+    MmqParams p{};
+    p.w = a.w; p.actp = (const uint8_t *) workspace; p.dst = a.dst;
+    p.k = (int) a.k; p.m = (int) a.m; p.n = (int) a.n;
+    p.ne12 = (int) a.ne12; p.r2 = (int) (a.ne12 / a.ne02); p.r3 = (int) (a.ne13 / a.ne03); p.nbatch = nbatch;
+    p.w_nb1 = a.w_nb1; p.w_nb2 = a.w_nb2; p.w_nb3 = a.w_nb3;
+    p.d_nb1 = a.d_nb1; p.d_nb2 = a.d_nb2; p.d_nb3 = a.d_nb3;
+    p.m_tiles  = (int) ((a.m + TILE_M - 1) / TILE_M);
+    p.n_tiles  = pp.n_tiles;
+    p.k_chunks = pp.k_chunks;
+    p.w_stages_per_tile = (int) ((a.k + WSTAGE_K - 1) / WSTAGE_K);
+    const int be = blck_elems(a.type), bb = blck_bytes(a.type);
+    p.piece_bytes   = WSTAGE_K / be * bb;
+    p.blk_bytes     = be == 32 ? bb : 0;
+    p.w_pitch       = round_up_i(p.piece_bytes + 32, 16);
+    p.w_stage_bytes = TILE_M * p.w_pitch;
+    p.off_b   = AB_STAGES * A_STAGE_BYTES;
+    p.off_w   = p.off_b + AB_STAGES * B_STAGE_BYTES;
+    p.off_bar = p.off_w + W_STAGES * p.w_stage_bytes;
+    const int smem = 1024 + (int) p.off_bar + BAR_COUNT * 8 + 16;
+
+    static std::mutex                            mu;
+    static std::set<std::pair<int, const void *>> done;
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        std::lock_guard<std::mutex> lk(mu);
+        if (!done.count({ dev, (const void *) fn })) {
+            cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem > 227 * 1024 ? smem : 227 * 1024);
+            if (e != cudaSuccess) {
+                err = std::string("mmq: cudaFuncSetAttribute: ") + cudaGetErrorString(e);
+                return B200Q_ECUDA;
+            }
+            done.insert({ dev, (const void *) fn });
+        }
+    }
+    const int num_tiles = nbatch * p.m_tiles * p.n_tiles;
+    const int grid      = std::min(num_tiles, sms);
+    fn<<<grid, NTHREADS, smem, st>>>(p);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        err = std::string("mmq: launch failed: ") + cudaGetErrorString(e);
+        return B200Q_ECUDA;
+    }
+    return 0;
+}
+
 }  // namespace b200q

@@ -82,6 +82,32 @@ if __name__ == "__main__":
             names = ["start", "pdl_wait", "quant", "first_full", "end", "act_loaded", "q_done_t0"]
             order = [0, 1, 5, 6, 2, 3, 4]
             print(f"kernel {i}: " + "  ".join(f"{names[j]}: med {int(np.median(a[:, j]) - t0):6d} max {int(a[:, j].max() - t0):6d}" for j in order))
+    elif which == "mmq":
+        # prompt processing (n = 512): TFLOP/s = 2*m*n*k / time (test-backend-ops' definition, :3114-3117)
+        import json
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+        bf16 = peaks.get("bf16_tflops", 1590.0)
+        n = int(sys.argv[2]) if len(sys.argv) > 2 else 512
+        for (t, m, k) in [(refs.Q8_0, 4096, 4096), (refs.Q8_0, 1024, 4096), (refs.Q8_0, 14336, 4096), (refs.Q8_0, 4096, 14336),
+                          (refs.Q4_K, 14336, 4096), (refs.Q6_K, 4096, 14336), (refs.Q4_0, 4096, 4096), (refs.MXFP4, 2880, 2880),
+                          (refs.Q8_0, 128256, 4096)]:
+            base = refs.random_blocks(t, min(m, 512), k, seed=1)
+            host = np.tile(base, ((m + base.shape[0] - 1) // base.shape[0], 1))[:m]
+            w = b200q.upload(t, (m, k), host)
+            act = torch.rand(n, k, device="cuda") * 2 - 1
+            out = torch.empty(n, m, device="cuda")
+            for _ in range(3):
+                b200q.mul_mat(w, act, out=out)
+            torch.cuda.synchronize()
+            e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+            iters = 20
+            e0.record()
+            for _ in range(iters):
+                b200q.mul_mat(w, act, out=out)
+            e1.record(); torch.cuda.synchronize()
+            us = e0.elapsed_time(e1) * 1e3 / iters
+            tf = 2.0 * m * n * k / us / 1e6
+            print(f"{refs.NAMES[t]:6s} m={m:6d} k={k:6d} n={n}: {us:9.2f} us  {tf:8.1f} TFLOP/s  ({tf / bf16 * 100:5.1f}% of measured bf16 {bf16:.0f})", flush=True)
     elif which == "small":
         for (m, k) in [(4096, 4096), (14336, 4096), (4096, 14336), (1024, 4096)]:
             bench(refs.Q4_K, m, k, 1)
