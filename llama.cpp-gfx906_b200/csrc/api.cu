@@ -206,6 +206,7 @@ extern "C" {
 int          b200q_version(void) { return 100; }
 // development aid: device buffer of [grid][8] u64 that GEMV CTAs fill with %globaltimer stamps (NULL = off)
 B200Q_API void b200q_debug_timestamps(void * dev_buf) { g_ts = (unsigned long long *) dev_buf; }
+B200Q_API void b200q_debug_mmq_stamps(void * dev_buf) { mmq_set_debug((unsigned long long *) dev_buf); }
 const char * b200q_last_error(void) { return g_err.c_str(); }
 
 int b200q_device_count(void) {

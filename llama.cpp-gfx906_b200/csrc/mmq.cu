@@ -13,16 +13,16 @@
 // is MORE accurate than the reference's int8 activations), and kind::f16 MMAs accumulate the whole K extent in fp32 in
 // TMEM with no per-block epilogue.
 //
-// CTA = 15 warps, one CTA per SM, persistent over output tiles of 128 weight rows x 256 activation columns:
+// CTA = 18 warps, one CTA per SM, persistent over output tiles of 128 weight rows x 256 activation columns:
 //   warps 0-3   epilogue: tcgen05.ld of the finished accumulator (TMEM lane = weight row, column = token) and
 //               coalesced stores to dst (ggml layout: rows contiguous); overlaps the next tile's main loop because
 //               the 512 TMEM columns hold two 256-column accumulators
-//   warp  4     W producer: per stage one bulk copy per weight row of the raw quantized bytes of 256 k-elements,
+//   warps 4-7   W producers: thread = weight row; 16-byte cp.async of the raw quantized bytes of 128/256 k-elements,
 //               16-byte-aligned windows around arbitrarily aligned 17/18/34/210-byte blocks
-//   warp  5     B producer: one bulk copy per 64-wide k-chunk of the bf16 activation tile, which mmq_pack_act has
+//   warp  8     B producer: one bulk copy per 64-wide k-chunk of the bf16 activation tile, which mmq_pack_act has
 //               already written in the exact swizzled shared-memory image (so no tensor map is needed)
-//   warp  6     MMA issuer: one thread, 4 x tcgen05.mma (M=128, N<=256, K=16) per k-chunk, tcgen05.commit to free stages
-//   warps 7-14  dequantizers: thread = (row, 32-element block); raw bytes -> fp32 -> bf16 -> 4 x STS.128 (conflict-free
+//   warp  9     MMA issuer: one thread, 4 x tcgen05.mma (M=128, N<=256, K=16) per k-chunk, tcgen05.commit to free stages
+//   warps 10-17 dequantizers: thread = (row, 32-element block); raw bytes -> fp32 -> bf16 -> 4 x STS.128 (conflict-free
 //               under the 128B swizzle), fence.proxy.async, arrive
 #include "mmq.cuh"
 
@@ -33,6 +33,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
+#include <cstdlib>
 #include <mutex>
 #include <set>
 
@@ -45,21 +46,20 @@ using namespace sm100;
 constexpr int TILE_M  = 128;  // weight rows per tile (UMMA M)
 constexpr int TILE_N  = 256;  // activation columns per tile (UMMA N, <= 256)
 constexpr int CHUNK_K = 64;   // bf16 elements per 128-byte swizzled row
-constexpr int WSTAGE_K = 256; // k-elements of raw weights per W stage
 constexpr int AB_STAGES = 3;
-constexpr int W_STAGES  = 2;
+constexpr int MAX_W_STAGES = 4;
 constexpr int A_STAGE_BYTES = TILE_M * 128;  // 16 KB
 constexpr int B_STAGE_BYTES = TILE_N * 128;  // 32 KB
-constexpr int N_EPI_WARPS = 4, N_DQ_WARPS = 8;
-constexpr int WARP_WPROD = 4, WARP_BPROD = 5, WARP_MMA = 6, WARP_DQ0 = 7;
-constexpr int NTHREADS = (WARP_DQ0 + N_DQ_WARPS) * 32;  // 480
+constexpr int N_EPI_WARPS = 4, N_WP_WARPS = 4, N_DQ_WARPS = 16, N_DQ_GROUPS = 2;  // dequant groups take alternate k-chunks
+constexpr int WARP_WPROD = 4, WARP_BPROD = 8, WARP_MMA = 9, WARP_DQ0 = 10;
+constexpr int NTHREADS = (WARP_DQ0 + N_DQ_WARPS) * 32;  // 832
 constexpr int TMEM_COLS = 512;
 
 // barrier slots (8 bytes each) inside the barrier block
 enum {
-    BAR_W_FULL  = 0,                       // [W_STAGES]  count 32 (producer lanes) + tx bytes
-    BAR_W_EMPTY = BAR_W_FULL + W_STAGES,   // [W_STAGES]  count N_DQ_WARPS
-    BAR_A_FULL  = BAR_W_EMPTY + W_STAGES,  // [AB_STAGES] count N_DQ_WARPS
+    BAR_W_FULL  = 0,                           // [MAX_W_STAGES] count 128 (cp.async.mbarrier.arrive.noinc per producer thread)
+    BAR_W_EMPTY = BAR_W_FULL + MAX_W_STAGES,   // [MAX_W_STAGES] count N_DQ_WARPS
+    BAR_A_FULL  = BAR_W_EMPTY + MAX_W_STAGES,  // [AB_STAGES] count N_DQ_WARPS / N_DQ_GROUPS
     BAR_B_FULL  = BAR_A_FULL + AB_STAGES,  // [AB_STAGES] count 1 + tx bytes
     BAR_AB_EMPTY = BAR_B_FULL + AB_STAGES, // [AB_STAGES] count 1 (tcgen05.commit)
     BAR_ACC_FULL = BAR_AB_EMPTY + AB_STAGES,  // [2] count 1 (tcgen05.commit)
@@ -76,12 +76,26 @@ struct MmqParams {
     long long w_nb1, w_nb2, w_nb3;
     long long d_nb1, d_nb2, d_nb3;
     int   m_tiles, n_tiles, k_chunks, w_stages_per_tile;
-    int   piece_bytes;   // raw bytes of WSTAGE_K elements of one row
+    int   w_stage_k;     // k-elements of raw weights per W stage (128 for 32-element block types, 256 for K-quants)
+    int   w_stages;      // W ring depth (2..MAX_W_STAGES, what fits in shared memory)
+    int   piece_bytes;   // raw bytes of w_stage_k elements of one row
     int   blk_bytes;     // bytes per 32 elements (32-block types) — used for the ragged last stage
     int   w_pitch;       // shared-memory pitch of one row piece
     int   w_stage_bytes; // TILE_M * w_pitch
     uint32_t off_b, off_w, off_bar;  // shared-memory offsets from the 1024-aligned base
+    int dbg_flags;                   // development aid (timing experiments only): 1 = skip W loads, 2 = skip dequant math, 4 = skip B loads
+    unsigned long long * dbg;        // development aid: CTA 0 stores clock64 stamps [chunk][8] for its first 256 chunks
 };
+__device__ __forceinline__ void dbg_phase(const MmqParams & p, int slot) {  // globaltimer (ns) stamps of CTA 0's phases
+    if (p.dbg && blockIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        p.dbg[255 * 8 + slot] = t;
+    }
+}
+__device__ __forceinline__ void dbg_stamp(const MmqParams & p, int g, int slot) {
+    if (p.dbg && blockIdx.x == 0 && g < 256) p.dbg[g * 8 + slot] = (unsigned long long) clock64();
+}
 
 struct PackParams {
     const float * act;
@@ -129,48 +143,76 @@ __global__ void __launch_bounds__(256) mmq_pack_act(const PackParams p) {
 }
 
 // ---- dequantizers: 32 consecutive k-elements of one row piece -> fp32 ------------------------------------------
-// `piece` is a generic pointer into shared memory at the first byte of the row's W-stage piece (a block / super-block
-// boundary, ANY byte alignment); b32 = index of the 32-element block inside the piece (0..7).
-__device__ __forceinline__ uint32_t ldu32(const uint8_t * p) {
-    const uintptr_t  a = (uintptr_t) p;
-    const uint32_t * w = (const uint32_t *) (a & ~(uintptr_t) 3);
-    return __funnelshift_r(w[0], w[1], (int) (a & 3) * 8);
+// `piece` is the SHARED-WINDOW address (32-bit) of the first byte of the row's W-stage piece (a block / super-block
+// boundary, ANY byte alignment); b32 = index of the 32-element block inside the piece (0..7).  All loads are explicit
+// ld.shared (a generic pointer here costs an LD.E through the L1TEX path per access: measured 3x slower).
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
 }
-__device__ __forceinline__ float ldh(const uint8_t * p) {  // fp16 at a 1-byte aligned address
-    return half_bits_to_float((uint16_t) (p[0] | (p[1] << 8)));
+__device__ __forceinline__ uint32_t lds_u8(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+// 32-bit little-endian word at any byte address: the two aligned words that cover it + funnel shift
+__device__ __forceinline__ uint32_t ldu32(uint32_t a) {
+    const uint32_t w = a & ~3u;
+    return __funnelshift_r(lds_u32(w), lds_u32(w + 4), (int) (a & 3u) * 8);
+}
+// N consecutive words from any byte address: N+1 aligned loads
+template <int N> __device__ __forceinline__ void ldu32_n(uint32_t a, uint32_t (&out)[N]) {
+    const uint32_t w  = a & ~3u;
+    const int      sh = (int) (a & 3u) * 8;
+    uint32_t       prev = lds_u32(w);
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        const uint32_t next = lds_u32(w + 4 * (i + 1));
+        out[i]              = __funnelshift_r(prev, next, sh);
+        prev                = next;
+    }
+}
+__device__ __forceinline__ float ldh(uint32_t a) {  // fp16 at a 1-byte aligned address
+    return half_bits_to_float((uint16_t) (ldu32(a) & 0xffffu));
 }
 
 template <int T> struct Dq {
-    // generic (slow) path: the bit-exact scalar decoder of blocks.cuh
-    static __device__ __forceinline__ void run(const uint8_t * piece, int b32, float (&v)[32]) {
+    // generic (slow) path: the bit-exact scalar decoder of blocks.cuh on a generic pointer
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        const uint8_t * gp = (const uint8_t *) __cvta_shared_to_generic((size_t) piece);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = decode_elem<T>(piece, (int64_t) b32 * 32 + i);
+        for (int i = 0; i < 32; ++i) v[i] = decode_elem<T>(gp, (int64_t) b32 * 32 + i);
     }
 };
 template <> struct Dq<T_Q8_0> {
-    static __device__ __forceinline__ void run(const uint8_t * piece, int b32, float (&v)[32]) {
-        const uint8_t * b = piece + b32 * 34;
-        const float     d = ldh(b);
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        const uint32_t b = piece + b32 * 34;
+        uint32_t       w[9];  // [d | q0 q1] ... [q30 q31 | next]
+        ldu32_n<9>(b, w);
+        const float d = half_bits_to_float((uint16_t) (w[0] & 0xffffu));
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const uint32_t w = ldu32(b + 2 + 4 * i);
+            const uint32_t q = __funnelshift_r(w[i], w[i + 1], 16);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) v[4 * i + j] = d * (float) (int8_t) (w >> (8 * j));
+            for (int j = 0; j < 4; ++j) v[4 * i + j] = d * (float) (int8_t) (q >> (8 * j));
         }
     }
 };
 template <> struct Dq<T_Q4_0> {
-    static __device__ __forceinline__ void run(const uint8_t * piece, int b32, float (&v)[32]) {
-        const uint8_t * b  = piece + b32 * 18;
-        const float     d  = ldh(b);
-        const float     m8 = -8.0f * d;
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        const uint32_t b = piece + b32 * 18;
+        uint32_t       w[5];  // [d | qs0 qs1] [qs2..5] [qs6..9] [qs10..13] [qs14 qs15 | next]
+        ldu32_n<5>(b, w);
+        const float d  = half_bits_to_float((uint16_t) (w[0] & 0xffffu));
+        const float m8 = -8.0f * d;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const uint32_t w = ldu32(b + 2 + 4 * i);
+            const uint32_t q = __funnelshift_r(w[i], w[i + 1], 16);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                v[4 * i + j]      = fmaf((float) ((w >> (8 * j)) & 0xF), d, m8);
-                v[16 + 4 * i + j] = fmaf((float) ((w >> (8 * j + 4)) & 0xF), d, m8);
+                v[4 * i + j]      = fmaf((float) ((q >> (8 * j)) & 0xF), d, m8);
+                v[16 + 4 * i + j] = fmaf((float) ((q >> (8 * j + 4)) & 0xF), d, m8);
             }
         }
     }
@@ -181,51 +223,65 @@ template <> struct Dq<T_MXFP4> {
         const float    f   = (float) mag;
         return (nib & 8u) ? -f : f;
     }
-    static __device__ __forceinline__ void run(const uint8_t * piece, int b32, float (&v)[32]) {
-        const uint8_t * b = piece + b32 * 17;
-        const float     d = e8m0_half_to_float(b[0]);
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        const uint32_t b = piece + b32 * 17;
+        uint32_t       w[5];  // [e | qs0 qs1 qs2] ... [qs15 | next]
+        ldu32_n<5>(b, w);
+        const float d = e8m0_half_to_float((uint8_t) (w[0] & 0xff));
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const uint32_t w = ldu32(b + 1 + 4 * i);
+            const uint32_t q = __funnelshift_r(w[i], w[i + 1], 8);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                v[4 * i + j]      = d * kv((w >> (8 * j)) & 0xF);
-                v[16 + 4 * i + j] = d * kv((w >> (8 * j + 4)) & 0xF);
+                v[4 * i + j]      = d * kv((q >> (8 * j)) & 0xF);
+                v[16 + 4 * i + j] = d * kv((q >> (8 * j + 4)) & 0xF);
             }
         }
     }
 };
 template <> struct Dq<T_Q4_K> {
-    static __device__ __forceinline__ void run(const uint8_t * piece, int b32, float (&v)[32]) {
-        const float d = ldh(piece), dmin = ldh(piece + 2);
-        int         sc, mn;
-        k4_scale_min(b32, piece + 4, sc, mn);
-        const float     dsc = d * (float) sc, dm = -dmin * (float) mn;
-        const uint8_t * qs  = piece + 16 + 32 * (b32 >> 1);
-        const int       sh  = 4 * (b32 & 1);
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        uint32_t h[4];  // [d dmin] [scales x3]
+        ldu32_n<4>(piece, h);
+        const float d = half_bits_to_float((uint16_t) (h[0] & 0xffffu)), dmin = half_bits_to_float((uint16_t) (h[0] >> 16));
+        // get_scale_min_k4 (ggml-quants.c:703-710) on the three scale words
+        int sc, mn;
+        if (b32 < 4) {
+            sc = (int) ((h[1] >> (8 * b32)) & 63);
+            mn = (int) ((h[2] >> (8 * b32)) & 63);
+        } else {
+            const int      jj = b32 - 4;
+            const uint32_t hi = (h[3] >> (8 * jj)) & 0xff;
+            sc                = (int) ((hi & 0xF) | (((h[1] >> (8 * jj + 6)) & 3) << 4));
+            mn                = (int) ((hi >> 4) | (((h[2] >> (8 * jj + 6)) & 3) << 4));
+        }
+        const float dsc = d * (float) sc, dm = -dmin * (float) mn;
+        const int   sh  = 4 * (b32 & 1);
+        uint32_t    q[8];
+        ldu32_n<8>(piece + 16 + 32 * (b32 >> 1), q);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const uint32_t w = ldu32(qs + 4 * i) >> sh;
+            const uint32_t w = q[i] >> sh;
 #pragma unroll
             for (int j = 0; j < 4; ++j) v[4 * i + j] = fmaf((float) ((w >> (8 * j)) & 0xF), dsc, dm);
         }
     }
 };
 template <> struct Dq<T_Q6_K> {
-    static __device__ __forceinline__ void run(const uint8_t * piece, int b32, float (&v)[32]) {
-        const int       n128 = b32 >> 2, quad = b32 & 3;
-        const uint8_t * ql   = piece + 64 * n128 + 32 * (quad & 1);
-        const uint8_t * qh   = piece + 128 + 32 * n128;
-        const int       shl  = 4 * (quad >> 1), shh = 2 * quad;
-        const float     d    = ldh(piece + 208);
-        const float     s0   = d * (float) (int8_t) piece[192 + 8 * n128 + 2 * quad];
-        const float     s1   = d * (float) (int8_t) piece[192 + 8 * n128 + 2 * quad + 1];
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        const int n128 = b32 >> 2, quad = b32 & 3;
+        const int shl  = 4 * (quad >> 1), shh = 2 * quad;
+        uint32_t  ql[8], qh[8];
+        ldu32_n<8>(piece + 64 * n128 + 32 * (quad & 1), ql);
+        ldu32_n<8>(piece + 128 + 32 * n128, qh);
+        const float    d  = ldh(piece + 208);
+        const uint32_t sw = ldu32(piece + 192 + 8 * n128 + 2 * quad);
+        const float    s0 = d * (float) (int8_t) (sw & 0xff);
+        const float    s1 = d * (float) (int8_t) ((sw >> 8) & 0xff);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const uint32_t lo = (ldu32(ql + 4 * i) >> shl) & 0x0F0F0F0Fu;
-            const uint32_t hi = ((ldu32(qh + 4 * i) >> shh) & 0x03030303u) << 4;
-            const uint32_t q  = lo | hi;
-            const float    s  = i < 4 ? s0 : s1;
+            const uint32_t q = ((ql[i] >> shl) & 0x0F0F0F0Fu) | (((qh[i] >> shh) & 0x03030303u) << 4);
+            const float    s = i < 4 ? s0 : s1;
 #pragma unroll
             for (int j = 0; j < 4; ++j) v[4 * i + j] = s * (float) ((int) ((q >> (8 * j)) & 0xFF) - 32);
         }
@@ -247,8 +303,8 @@ __device__ __forceinline__ TileCoord tile_coord(const MmqParams & p, int t) {
 }
 // bytes of the raw row piece of W stage `ws` (the last stage of a row may be ragged for 32-element block types)
 __device__ __forceinline__ int piece_bytes_of(const MmqParams & p, int ws) {
-    const int elems = min(WSTAGE_K, p.k - ws * WSTAGE_K);
-    return elems == WSTAGE_K ? p.piece_bytes : (elems >> 5) * p.blk_bytes;
+    const int elems = min(p.w_stage_k, p.k - ws * p.w_stage_k);
+    return elems == p.w_stage_k ? p.piece_bytes : (elems >> 5) * p.blk_bytes;
 }
 
 template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const MmqParams p) {
@@ -261,14 +317,15 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int num_tiles = p.nbatch * p.m_tiles * p.n_tiles;
+    if (threadIdx.x == 0) dbg_phase(p, 0);
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < W_STAGES; ++s) {
-            mbar_init(bars + 8 * (BAR_W_FULL + s), 32);
+        for (int s = 0; s < p.w_stages; ++s) {
+            mbar_init(bars + 8 * (BAR_W_FULL + s), N_WP_WARPS * 32);
             mbar_init(bars + 8 * (BAR_W_EMPTY + s), N_DQ_WARPS);
         }
         for (int s = 0; s < AB_STAGES; ++s) {
-            mbar_init(bars + 8 * (BAR_A_FULL + s), N_DQ_WARPS);
+            mbar_init(bars + 8 * (BAR_A_FULL + s), N_DQ_WARPS / N_DQ_GROUPS);
             mbar_init(bars + 8 * (BAR_B_FULL + s), 1);
             mbar_init(bars + 8 * (BAR_AB_EMPTY + s), 1);
         }
@@ -285,39 +342,41 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (threadIdx.x == 0) dbg_phase(p, 1);
 
-    if (warp == WARP_WPROD) {
+    if (warp >= WARP_WPROD && warp < WARP_WPROD + N_WP_WARPS) {
+        if (!(p.dbg_flags & 64)) {
         // ------------------------------------------------------------------ raw weight rows -> W ring
+        // coalesced 16-byte cp.async (LDGSTS): a half-warp covers the aligned window around one row piece (<= 16 chunks
+        // of 16 bytes), so one warp instruction touches 2 rows x <= 3 cache lines instead of 32 rows
+        const int wp  = warp - WARP_WPROD;
+        const int l16 = lane & 15, hf = lane >> 4;
+        const int cpr = p.w_pitch >> 4;  // 16-byte chunks copied per row (the whole pitch; over-read stays inside the tensor + pad)
         int wsi = 0;
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
             const TileCoord tc  = tile_coord(p, t);
             const int       i13 = tc.b / p.ne12, i12 = tc.b - i13 * p.ne12;
             const uint8_t * wb  = p.w + (long long) (i12 / p.r2) * p.w_nb2 + (long long) (i13 / p.r3) * p.w_nb3;
             for (int ws = 0; ws < p.w_stages_per_tile; ++ws, ++wsi) {
-                const int slot = wsi % W_STAGES;
-                mbar_wait(bars + 8 * (BAR_W_EMPTY + slot), ((wsi / W_STAGES) & 1) ^ 1);
-                const int      pb   = piece_bytes_of(p, ws);
-                const uint32_t full = bars + 8 * (BAR_W_FULL + slot);
-                const uint8_t * src[4];
-                uint32_t        bytes[4], total = 0;
-#pragma unroll
-                for (int rr = 0; rr < 4; ++rr) {
-                    const int row = min(tc.mt * TILE_M + lane + 32 * rr, p.m - 1);
-                    const uint8_t * a = wb + (long long) row * p.w_nb1 + (long long) ws * p.piece_bytes;
-                    const uint32_t  lead = (uint32_t) ((uintptr_t) a & 15);
-                    src[rr]   = a - lead;
-                    bytes[rr] = (lead + (uint32_t) pb + 15u) & ~15u;
-                    total += bytes[rr];
+                const int slot = wsi % p.w_stages;
+                mbar_wait(bars + 8 * (BAR_W_EMPTY + slot), ((wsi / p.w_stages) & 1) ^ 1);
+                const uint32_t sbase = base + p.off_w + (uint32_t) slot * p.w_stage_bytes + 16u * l16;
+                if (l16 < cpr && !((p.dbg_flags & 1) && wsi >= p.w_stages)) {
+#pragma unroll 4
+                    for (int it = 0; it < TILE_M / 8; ++it) {
+                        const int       row = it * 8 + wp * 2 + hf;
+                        const uint8_t * a   = wb + (long long) min(tc.mt * TILE_M + row, p.m - 1) * p.w_nb1 + (long long) ws * p.piece_bytes;
+                        const uint8_t * src = (const uint8_t *) ((uintptr_t) a & ~(uintptr_t) 15) + 16 * l16;
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sbase + (uint32_t) row * p.w_pitch), "l"(src) : "memory");
+                    }
                 }
-                mbar_expect_tx(full, total);
-#pragma unroll
-                for (int rr = 0; rr < 4; ++rr) {
-                    bulk_g2s(base + p.off_w + (uint32_t) slot * p.w_stage_bytes + (uint32_t) (lane + 32 * rr) * p.w_pitch,
-                             src[rr], bytes[rr], full);
-                }
+                asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bars + 8 * (BAR_W_FULL + slot)) : "memory");
             }
         }
+        }
+        asm volatile("cp.async.wait_all;" ::: "memory");
     } else if (warp == WARP_BPROD) {
+        if (!(p.dbg_flags & 128))
         // ------------------------------------------------------------------ packed activation tiles -> B ring
         if (lane == 0) {
             int g = 0;
@@ -330,8 +389,13 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
                     const int slot = g % AB_STAGES;
                     mbar_wait(bars + 8 * (BAR_AB_EMPTY + slot), ((g / AB_STAGES) & 1) ^ 1);
                     const uint32_t full = bars + 8 * (BAR_B_FULL + slot);
-                    mbar_expect_tx(full, bytes);
-                    bulk_g2s(base + p.off_b + (uint32_t) slot * B_STAGE_BYTES, src + (long long) c * B_STAGE_BYTES, bytes, full);
+                    dbg_stamp(p, g, 7);
+                    if ((p.dbg_flags & 4) && g >= AB_STAGES) {
+                        mbar_arrive(full);
+                    } else {
+                        mbar_expect_tx(full, bytes);
+                        bulk_g2s(base + p.off_b + (uint32_t) slot * B_STAGE_BYTES, src + (long long) c * B_STAGE_BYTES, bytes, full);
+                    }
                 }
             }
         }
@@ -350,24 +414,31 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
                 for (int c = 0; c < p.k_chunks; ++c, ++g) {
                     const int      slot = g % AB_STAGES;
                     const uint32_t ph   = (g / AB_STAGES) & 1;
+                    dbg_stamp(p, g, 0);
                     mbar_wait(bars + 8 * (BAR_A_FULL + slot), ph);
-                    mbar_wait(bars + 8 * (BAR_B_FULL + slot), ph);
+                    dbg_stamp(p, g, 1);
+                    if (!(p.dbg_flags & 128)) mbar_wait(bars + 8 * (BAR_B_FULL + slot), ph);
+                    dbg_stamp(p, g, 2);
                     tc_fence_after();
                     const uint64_t adesc = umma_desc_k_sw128(base + (uint32_t) slot * A_STAGE_BYTES);
                     const uint64_t bdesc = umma_desc_k_sw128(base + p.off_b + (uint32_t) slot * B_STAGE_BYTES);
+                    if (!(p.dbg_flags & 32))
 #pragma unroll
                     for (int kk = 0; kk < CHUNK_K / 16; ++kk) {
                         // +32 bytes (16 bf16) along K inside the 128-byte swizzle atom = +2 in the address field
                         umma_f16(d_tmem, adesc + 2 * kk, bdesc + 2 * kk, idesc, (c | kk) != 0);
                     }
                     umma_commit(bars + 8 * (BAR_AB_EMPTY + slot));
+                    dbg_stamp(p, g, 3);
                 }
                 umma_commit(bars + 8 * (BAR_ACC_FULL + ab));
+                dbg_phase(p, 2);
             }
         }
     } else if (warp >= WARP_DQ0) {
         // ------------------------------------------------------------------ dequantizers: W ring -> A ring (bf16)
-        const int dt   = threadIdx.x - WARP_DQ0 * 32;  // 0..255
+        const int dt   = (threadIdx.x - WARP_DQ0 * 32) & 255;  // 0..255 inside the group
+        const int grp  = (threadIdx.x - WARP_DQ0 * 32) >> 8;   // group g handles k-chunks with (chunk & 1) == g
         const int row  = dt >> 1, half = dt & 1;
         const uint32_t a_row_off = (uint32_t) row * 128u;
         const uint32_t sw        = (uint32_t) (row & 7);
@@ -379,17 +450,28 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
             const int       grow = min(tc.mt * TILE_M + row, p.m - 1);
             const uint8_t * rowp = wb + (long long) grow * p.w_nb1;
             for (int ws = 0; ws < p.w_stages_per_tile; ++ws, ++wsi) {
-                const int wslot = wsi % W_STAGES;
-                mbar_wait(bars + 8 * (BAR_W_FULL + wslot), (wsi / W_STAGES) & 1);
+                const int wslot = wsi % p.w_stages;
+                if (!(p.dbg_flags & 64)) mbar_wait(bars + 8 * (BAR_W_FULL + wslot), (wsi / p.w_stages) & 1);
                 const uint32_t  lead  = (uint32_t) ((uintptr_t) (rowp + (long long) ws * p.piece_bytes) & 15);
-                const uint8_t * piece = sm + p.off_w + (uint32_t) wslot * p.w_stage_bytes + (uint32_t) row * p.w_pitch + lead;
-                const int nchunks = min(WSTAGE_K / CHUNK_K, p.k_chunks - ws * (WSTAGE_K / CHUNK_K));
+                const uint32_t  piece = base + p.off_w + (uint32_t) wslot * p.w_stage_bytes + (uint32_t) row * p.w_pitch + lead;
+                const int cps     = p.w_stage_k / CHUNK_K;
+                const int nchunks = min(cps, p.k_chunks - ws * cps);
                 for (int c = 0; c < nchunks; ++c, ++g) {
+                    if ((g & (N_DQ_GROUPS - 1)) != grp) continue;
                     const int slot = g % AB_STAGES;
                     float v[32];
-                    Dq<T>::run(piece, 2 * c + half, v);
+                    if (dt == 0) dbg_stamp(p, g, 4);
+                    if (p.dbg_flags & 2) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) v[i] = (float) (i + row);
+                    } else {
+                        Dq<T>::run(piece, 2 * c + half, v);
+                    }
+                    if (dt == 0) dbg_stamp(p, g, 5);
                     mbar_wait(bars + 8 * (BAR_AB_EMPTY + slot), ((g / AB_STAGES) & 1) ^ 1);
+                    if (dt == 0) dbg_stamp(p, g, 6);
                     uint8_t * arow = sm + (uint32_t) slot * A_STAGE_BYTES + a_row_off;
+                    if (!(p.dbg_flags & 8))
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
                         __nv_bfloat162 h0 = __floats2bfloat162_rn(v[8 * i + 0], v[8 * i + 1]);
@@ -400,12 +482,12 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
                         o.x = *(uint32_t *) &h0; o.y = *(uint32_t *) &h1; o.z = *(uint32_t *) &h2; o.w = *(uint32_t *) &h3;
                         *(uint4 *) (arow + ((((uint32_t) (4 * half + i)) ^ sw) << 4)) = o;
                     }
-                    fence_proxy_async_smem();
+                    if (!(p.dbg_flags & 16)) fence_proxy_async_smem();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bars + 8 * (BAR_A_FULL + slot));
                 }
                 __syncwarp();
-                if (lane == 0) mbar_arrive(bars + 8 * (BAR_W_EMPTY + wslot));
+                if (lane == 0 && !(p.dbg_flags & 64)) mbar_arrive(bars + 8 * (BAR_W_EMPTY + wslot));
             }
         }
     } else {
@@ -421,14 +503,23 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
             char * dbase = (char *) p.dst + (long long) i12 * p.d_nb2 + (long long) i13 * p.d_nb3 + (long long) row * 4;
             mbar_wait(bars + 8 * (BAR_ACC_FULL + ab), (ti >> 1) & 1);
             tc_fence_after();
+            if (threadIdx.x == 0) dbg_phase(p, 3);
             for (int c0 = 0; c0 < ncols; c0 += 32) {
                 float v[32];
                 tmem_ld32(tmem_base + ((uint32_t) (warp * 32) << 16) + (uint32_t) (ab * TILE_N + c0), v);
                 if (row < p.m) {
+                    char * dp = dbase + (long long) (n0 + c0) * p.d_nb1;  // one coalesced 128-byte warp store per column
+                    if (c0 + 32 <= ncols) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        if (c0 + j < ncols) {
-                            *(float *) (dbase + (long long) (n0 + c0 + j) * p.d_nb1) = v[j];
+                        for (int j = 0; j < 32; ++j) {
+                            *(float *) dp = v[j];
+                            dp += p.d_nb1;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            if (c0 + j < ncols) *(float *) dp = v[j];
+                            dp += p.d_nb1;
                         }
                     }
                 }
@@ -436,17 +527,20 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(bars + 8 * (BAR_ACC_EMPTY + ab));
+            if (threadIdx.x == 0) dbg_phase(p, 4);
         }
     }
 
     tc_fence_before();
     __syncthreads();
+    if (threadIdx.x == 0) dbg_phase(p, 5);
     if (warp == WARP_MMA) {
         tmem_dealloc(tmem_base, TMEM_COLS);
     }
 }
 
 typedef void (*mmq_kernel_t)(const MmqParams);
+unsigned long long * g_mmq_dbg = nullptr;
 
 mmq_kernel_t mmq_kernel_for(int type) {
     switch (type) {
@@ -466,6 +560,8 @@ mmq_kernel_t mmq_kernel_for(int type) {
 inline int round_up_i(int x, int a) { return (x + a - 1) / a * a; }
 
 }  // namespace
+
+void mmq_set_debug(unsigned long long * buf) { g_mmq_dbg = buf; }
 
 bool mmq_supported(int type, int64_t k) {
     return mmq_kernel_for(type) != nullptr && k > 0 && k % CHUNK_K == 0 && k % blck_elems(type) == 0;
@@ -510,15 +606,25 @@ int mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, st
     p.m_tiles  = (int) ((a.m + TILE_M - 1) / TILE_M);
     p.n_tiles  = pp.n_tiles;
     p.k_chunks = pp.k_chunks;
-    p.w_stages_per_tile = (int) ((a.k + WSTAGE_K - 1) / WSTAGE_K);
     const int be = blck_elems(a.type), bb = blck_bytes(a.type);
-    p.piece_bytes   = WSTAGE_K / be * bb;
+    p.w_stage_k     = be == 32 ? 128 : 256;
+    p.w_stages_per_tile = (int) ((a.k + p.w_stage_k - 1) / p.w_stage_k);
+    p.piece_bytes   = p.w_stage_k / be * bb;
     p.blk_bytes     = be == 32 ? bb : 0;
-    p.w_pitch       = round_up_i(p.piece_bytes + 32, 16);
+    p.w_pitch       = round_up_i(p.piece_bytes + 15 + 4, 16);  // lead <= 15 bytes + one word of funnel-shift over-read
     p.w_stage_bytes = TILE_M * p.w_pitch;
     p.off_b   = AB_STAGES * A_STAGE_BYTES;
     p.off_w   = p.off_b + AB_STAGES * B_STAGE_BYTES;
-    p.off_bar = p.off_w + W_STAGES * p.w_stage_bytes;
+    {
+        const int avail = 227 * 1024 - 1024 - (int) p.off_w - BAR_COUNT * 8 - 16;
+        p.w_stages      = std::max(2, std::min(MAX_W_STAGES, avail / p.w_stage_bytes));
+    }
+    p.off_bar = p.off_w + p.w_stages * p.w_stage_bytes;
+    p.dbg = g_mmq_dbg;
+    {
+        static const int flags = getenv("B200Q_MMQ_DBG") ? atoi(getenv("B200Q_MMQ_DBG")) : 0;
+        p.dbg_flags = flags;
+    }
     const int smem = 1024 + (int) p.off_bar + BAR_COUNT * 8 + 16;
 
     static std::mutex                            mu;

@@ -21,6 +21,7 @@ struct MmqArgs {
 
 bool   mmq_supported(int type, int64_t k);
 size_t mmq_workspace_bytes(int64_t k, int64_t n, int64_t nbatch);
+void   mmq_set_debug(unsigned long long * dev_buf);  // development aid (clock64 stamps of CTA 0)
 int    mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, std::string & err);
 
 }  // namespace b200q

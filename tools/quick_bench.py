@@ -101,9 +101,13 @@ if __name__ == "__main__":
             torch.cuda.synchronize()
             e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
             iters = 20
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                for _ in range(iters):
+                    b200q.mul_mat(w, act, out=out)
+            g.replay(); torch.cuda.synchronize()
             e0.record()
-            for _ in range(iters):
-                b200q.mul_mat(w, act, out=out)
+            g.replay()
             e1.record(); torch.cuda.synchronize()
             us = e0.elapsed_time(e1) * 1e3 / iters
             tf = 2.0 * m * n * k / us / 1e6
