@@ -233,10 +233,13 @@ def main_b200(args):
     ops = workload_ops(args.workload)
 
     # ---- resident state: weights (row shard of every matrix when world > 1), activations, results ------------
+    from b200q import rowsplit
     shards = []
     for i, o in enumerate(ops):
-        row0, nrows = workloads.row_partition(o.m, world, align=32)[rank]
-        shards.append((row0, nrows, workloads.synth_weights_device(o, seed=1234 + i, rows=nrows, row0=row0)))
+        parts = rowsplit.row_split(o.m, world)
+        row0, nrows = parts[rank]
+        shard = workloads.synth_weights_device(o, seed=1234 + i, rows=nrows, row0=row0)
+        shards.append(rowsplit.RowSplitWeight(o.qtype, o.m, o.k, rank, world, parts, shard))
     k_off, m_off = [0], [0]
     for o in ops:
         k_off.append(k_off[-1] + o.k)
@@ -245,22 +248,16 @@ def main_b200(args):
     g.manual_seed(4321)
     act_dev = torch.rand(k_off[-1], device="cuda", generator=g) * 2 - 1          # all activation vectors, f32
     out_dev = torch.zeros(m_off[-1], device="cuda")                              # all (gathered) results, f32
-    slice_dev = torch.zeros(max(s[1] for s in shards), device="cuda") if world > 1 else None
     act_host = act_dev.cpu().pin_memory()
     out_host = torch.empty(m_off[-1], dtype=torch.float32).pin_memory()
 
     def run_pass():
         """one pass over the matmul list; every launch goes to torch's current stream through the C-ABI"""
         for i, o in enumerate(ops):
-            row0, nrows, w = shards[i]
             a = act_dev[k_off[i]:k_off[i + 1]].view(1, o.k)
-            full = out_dev[m_off[i]:m_off[i + 1]]
-            if world == 1:
-                b200q.mul_mat(w, a, out=full.view(1, o.m))
-            else:
-                part = full[row0:row0 + nrows]   # equal slices (m % (32*world) == 0 for these shapes)
-                b200q.mul_mat(w, a, out=part.view(1, nrows))
-                dist.all_gather_into_tensor(full, part)
+            full = out_dev[m_off[i]:m_off[i + 1]].view(1, o.m)
+            # world == 1: the plain kernel; world > 1: this rank's rows + NCCL all-gather of the slices (rowsplit.py)
+            rowsplit.mul_mat_row_split(shards[i], a, out=full)
 
     for _ in range(2):
         run_pass()
@@ -323,10 +320,19 @@ def main_b200(args):
     ms_e2e = reduce_max(max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3 * 0.0)) / args.steps
     finite = bool(torch.isfinite(out_host).all())
 
-    if rank != 0:
+    def leave():
+        """all ranks: flush, meet once more, then leave without tearing NCCL down (destroy_process_group can hang behind
+        captured graphs that still reference the communicator)"""
+        sys.stdout.flush()
+        sys.stderr.flush()
         if dist is not None:
-            dist.destroy_process_group()
+            torch.cuda.synchronize()
+            dist.barrier()
+            os._exit(0)
         return 0
+
+    if rank != 0:
+        return leave()
 
     algo = sum(o.algo_bytes(1) for o in ops)
     value = algo / (ms_dev * 1e-3) / 1e9
@@ -362,9 +368,7 @@ def main_b200(args):
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = run_cpu_reference(cpu_sample_ops(ops), args.cpu_seconds)
     print(json.dumps(out))
-    if dist is not None:
-        dist.destroy_process_group()
-    return 0
+    return leave()
 
 
 if __name__ == "__main__":
