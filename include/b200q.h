@@ -134,6 +134,21 @@ B200Q_API size_t b200q_mul_mat_workspace(const b200q_mul_mat_args * a);
 B200Q_API int    b200q_mul_mat(const b200q_mul_mat_args * a, const void * w, const float * act, float * dst,
                                void * workspace, size_t workspace_bytes, void * stream);
 
+/* ---- grouped decode MUL_MAT: up to 4 weight matrices [m_g][k] of one type that multiply the SAME activation vector
+ *      (n = 1: wq/wk/wv, ffn_gate/ffn_up) in one launch.  Equivalent to n_mats calls of b200q_mul_mat (bit-identical
+ *      results); replaces the reference's fused gate/up GEMV (ggml-cuda mmvq.cu, fusion args of mul_mat_vec_q).
+ *      Rows dense (row pitch = b200q_row_size), all pointers 16-byte aligned. ------------------------------------ */
+#define B200Q_MAX_GROUP 4
+typedef struct b200q_mul_mat_group_args {
+    int      type;
+    int64_t  k;
+    int      n_mats;
+    int64_t  m[B200Q_MAX_GROUP];
+    uint32_t flags;
+} b200q_mul_mat_group_args;
+B200Q_API int b200q_mul_mat_group(const b200q_mul_mat_group_args * a, const void * const * w, const float * act,
+                                  float * const * dst, void * stream);
+
 /* ---- MUL_MAT_ID (MoE) ------------------------------------------------------------------------ */
 /* dst[t][s][:] = W[ids[t][s]] . b[t][s or 0][:]     (ggml_mul_mat_id, ggml.c:3056-3080) */
 typedef struct b200q_mul_mat_id_args {

@@ -31,7 +31,7 @@ FLAG_WEIGHTS_IMMUTABLE, FLAG_FORCE_GEMV, FLAG_FORCE_MMQ, FLAG_NO_PDL = 1, 2, 4, 
 EXPORTS = [
     "b200q_version", "b200q_last_error", "b200q_device_count", "b200q_device_info", "b200q_blck_size",
     "b200q_type_size", "b200q_row_size", "b200q_type_supported", "b200q_dequantize", "b200q_get_rows",
-    "b200q_mul_mat_workspace", "b200q_mul_mat", "b200q_mul_mat_id_workspace", "b200q_mul_mat_id",
+    "b200q_mul_mat_workspace", "b200q_mul_mat", "b200q_mul_mat_group", "b200q_mul_mat_id_workspace", "b200q_mul_mat_id",
     "b200q_mul_mat_host", "b200q_set_device", "b200q_malloc", "b200q_free", "b200q_memset", "b200q_memcpy",
     "b200q_stream_create", "b200q_stream_destroy", "b200q_stream_synchronize", "b200q_host_alloc", "b200q_host_free",
 ]
@@ -43,6 +43,10 @@ class MulMatArgs(C.Structure):
                 ("nb01", C.c_size_t), ("nb02", C.c_size_t), ("nb03", C.c_size_t),
                 ("nb11", C.c_size_t), ("nb12", C.c_size_t), ("nb13", C.c_size_t),
                 ("nb1", C.c_size_t), ("nb2", C.c_size_t), ("nb3", C.c_size_t), ("flags", C.c_uint32)]
+
+
+class MulMatGroupArgs(C.Structure):
+    _fields_ = [("type", C.c_int), ("k", C.c_int64), ("n_mats", C.c_int), ("m", C.c_int64 * 4), ("flags", C.c_uint32)]
 
 
 class MulMatIdArgs(C.Structure):
@@ -229,6 +233,21 @@ def mul_mat(w: QTensor, act, out=None, flags: int = FLAG_WEIGHTS_IMMUTABLE):
     _check(lib().b200q_mul_mat(C.byref(a), w.data.data_ptr(), act.data_ptr(), out.data_ptr(),
                                ws.data_ptr() if ws is not None else None, ws_n, _stream()), "b200q_mul_mat")
     return out
+
+
+def mul_mat_group(ws, act, outs=None, flags: int = FLAG_WEIGHTS_IMMUTABLE):
+    """n = 1 ggml_mul_mat of up to 4 weight matrices of one type against the SAME activation vector (wq/wk/wv,
+    ffn_gate/ffn_up) in one launch; returns the list of f32 results [1, m_g] (bit-identical to separate mul_mat calls)."""
+    torch = _torch()
+    assert 1 <= len(ws) <= 4 and all(len(w.shape) == 2 and w.qtype == ws[0].qtype and w.k == ws[0].k for w in ws)
+    assert act.dtype == torch.float32 and act.is_cuda and act.numel() == ws[0].k and act.is_contiguous()
+    if outs is None:
+        outs = [torch.empty((1, w.m), dtype=torch.float32, device=act.device) for w in ws]
+    a = MulMatGroupArgs(ws[0].qtype, ws[0].k, len(ws), (C.c_int64 * 4)(*([w.m for w in ws] + [0] * (4 - len(ws)))), flags)
+    wp = (C.c_void_p * len(ws))(*[w.data.data_ptr() for w in ws])
+    dp = (C.c_void_p * len(ws))(*[o.data_ptr() for o in outs])
+    _check(lib().b200q_mul_mat_group(C.byref(a), wp, C.c_void_p(act.data_ptr()), dp, _stream()), "b200q_mul_mat_group")
+    return outs
 
 
 def mul_mat_id(w: QTensor, b, ids, n_used: Optional[int] = None, out=None, flags: int = FLAG_WEIGHTS_IMMUTABLE):

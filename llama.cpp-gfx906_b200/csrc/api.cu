@@ -5,6 +5,7 @@
 #include "blocks.cuh"
 #include "dequant.cuh"
 #include "gemv.cuh"
+#include "gemv_kq.cuh"
 #include "mmq.cuh"
 
 #include <cuda_runtime.h>
@@ -151,6 +152,9 @@ bool plan_gemv(GemvPlan & plan, int type, int ncols, const DevInfo & di) {
         if (S < std::max(3, p.groups + 1)) S = (int) ((di.max_smem - p.stage_off) / p.stage_bytes);
         if (S >= std::max(2, p.groups + 1)) {
             p.nstages = std::min(S, 8);
+            // a slot must always be consumed by the SAME warp group, else a fast group can test a slot's full-barrier one
+            // phase early (parity ABA) when bulk copies complete out of order
+            p.nstages -= p.nstages % p.groups;
             break;
         }
         if (p.groups > 1) { p.groups /= 2; continue; }   // fewer, larger stages cannot help; fewer groups can
@@ -196,6 +200,80 @@ int launch_gemv(GemvPlan & plan, int type, int ncols, uint32_t flags, cudaStream
     return 0;
 }
 
+// ---- K-quant decode GEMV (gemv_kq.cu): n = 1, q4_K / q6_K, up to KQ_MAX_SEG matrices sharing the activations ------
+bool plan_kq(KqParams & p, int & grid, int & smem, int type, int64_t k, int nseg, const void * const * w, float * const * dst,
+             const int64_t * m, const float * act, const DevInfo & di) {
+    if (type != T_Q4_K && type != T_Q6_K) return false;
+    if (nseg < 1 || nseg > KQ_MAX_SEG || k <= 0 || k % 256) return false;
+    static const bool off = getenv("B200Q_NO_KQ") != nullptr;
+    if (off) return false;
+    p.nsb       = (int) (k / 256);
+    p.k         = (int) k;
+    p.row_bytes = p.nsb * blck_bytes(type);
+    if (p.row_bytes % 16 || ((uintptr_t) act & 15)) return false;
+    int lpr = 1;
+    while (lpr < 8 && lpr < p.nsb) lpr *= 2;
+    if (p.nsb > 16) lpr = 16;
+    if (p.nsb > 32) lpr = 32;
+    p.lpr            = lpr;
+    p.rows_per_stage = 32 / lpr;
+    p.stage_bytes    = round_up(p.rows_per_stage * p.row_bytes + 16, 128);
+    p.off_q     = 384;
+    p.off_dx    = p.off_q + p.nsb * 256;
+    p.off_bs16  = round_up(p.off_dx + p.nsb * 4, 16);
+    p.off_bs32  = p.off_bs16 + p.nsb * 32;
+    p.off_stage = round_up(p.off_bs32 + p.nsb * 16, 128);
+    static const int budget_kb = getenv("B200Q_KQ_SMEM_KB") ? atoi(getenv("B200Q_KQ_SMEM_KB")) : 110;
+    const int NWc = kq_consumer_warps();
+    int S = (budget_kb * 1024 - p.off_stage) / p.stage_bytes;  // two launches co-resident per SM
+    if (S < NWc) S = (di.max_smem - p.off_stage) / p.stage_bytes;
+    if (S < NWc) return false;
+    p.nstages = std::min(S / NWc, 2) * NWc;  // each consumer warp owns nstages / NW slots (gemv_kq.cu)
+    long long total = 0;
+    for (int g = 0; g < nseg; ++g) {
+        if (m[g] <= 0 || m[g] > (1 << 30) || ((uintptr_t) w[g] & 15)) return false;
+        p.seg[g].w      = (const uint8_t *) w[g];
+        p.seg[g].dst    = dst[g];
+        p.seg[g].m      = (int) m[g];
+        p.seg[g].stage0 = (int) total;
+        total += (m[g] + p.rows_per_stage - 1) / p.rows_per_stage;
+    }
+    if (total > (1ll << 30)) return false;
+    p.nseg         = nseg;
+    p.act          = act;
+    p.total_stages = (int) total;
+    grid           = (int) std::min<long long>(total, di.sms);
+    smem           = p.off_stage + p.nstages * p.stage_bytes;
+    return true;
+}
+
+int launch_kq(KqParams & p, int grid, int smem, int type, uint32_t flags, cudaStream_t st) {
+    kq_kernel_t fn = kq_kernel_for(type);
+    if (!fn) return fail(B200Q_ENOTSUP, "gemv_kq: unsupported type %d", type);
+    const DevInfo & di = dev_info();
+    if (int rc = ensure_smem_attr((const void *) fn, di.max_smem)) return rc;
+    const bool pdl   = !(flags & B200Q_FLAG_NO_PDL);
+    p.early_prefetch = pdl && (flags & B200Q_FLAG_WEIGHTS_IMMUTABLE) ? 1 : 0;
+    static const bool debug = getenv("B200Q_DEBUG") != nullptr;
+    if (debug) {
+        fprintf(stderr, "[b200q] gemv_kq type=%d k=%d nseg=%d m0=%d grid=%d smem=%d lpr=%d rps=%d stage_bytes=%d S=%d stages=%d pdl=%d early=%d\n",
+                type, p.k, p.nseg, p.seg[0].m, grid, smem, p.lpr, p.rows_per_stage, p.stage_bytes, p.nstages, p.total_stages,
+                (int) pdl, p.early_prefetch);
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim          = dim3(grid);
+    cfg.blockDim         = dim3(kq_threads());
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream           = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs                                          = attr;
+    cfg.numAttrs                                       = pdl ? 1 : 0;
+    CUDA_TRY(cudaLaunchKernelEx(&cfg, fn, p));
+    return 0;
+}
+
 bool aligned16(const void * p, long long stride) { return ((uintptr_t) p & 15) == 0 && (stride & 15) == 0; }
 
 }  // namespace
@@ -206,6 +284,7 @@ extern "C" {
 int          b200q_version(void) { return 100; }
 // development aid: device buffer of [grid][8] u64 that GEMV CTAs fill with %globaltimer stamps (NULL = off)
 B200Q_API void b200q_debug_timestamps(void * dev_buf) { g_ts = (unsigned long long *) dev_buf; }
+B200Q_API void b200q_debug_hang_buffer(void * host_mapped) { kq_set_hang_buffer((unsigned long long *) host_mapped); }
 B200Q_API void b200q_debug_mmq_stamps(void * dev_buf) { mmq_set_debug((unsigned long long *) dev_buf); }
 const char * b200q_last_error(void) { return g_err.c_str(); }
 
@@ -395,6 +474,18 @@ int b200q_mul_mat(const b200q_mul_mat_args * a, const void * w, const float * ac
         return 0;
     }
 
+    // decode fast path: one activation column, K-quant weights, dense rows
+    if (a->n == 1 && a->ne12 * a->ne13 == 1 && a->nb01 == b200q_row_size(a->type, a->k)) {
+        KqParams kq{};
+        int      grid = 0, smem = 0;
+        const void * wl[1] = { w };
+        float *      dl[1] = { dst };
+        const int64_t ml[1] = { a->m };
+        if (plan_kq(kq, grid, smem, a->type, a->k, 1, wl, dl, ml, act, di)) {
+            return launch_kq(kq, grid, smem, a->type, a->flags, st);
+        }
+    }
+
     // GEMV path: up to 8 activation columns per launch (more columns = several passes over the weights)
     GemvPlan plan{};
     GemvParams & p = plan.p;
@@ -424,6 +515,38 @@ int b200q_mul_mat(const b200q_mul_mat_args * a, const void * w, const float * ac
         p.act = (const float *) ((const char *) act + j0 * (long long) a->nb11);
         p.dst = (float *) ((char *) dst + j0 * (long long) a->nb1);
         if (int rc = launch_gemv(plan, a->type, nc, a->flags, st)) return rc;
+    }
+    return 0;
+}
+
+// ---- grouped decode GEMV: matrices that share one activation vector (q/k/v, gate/up) in one launch ------------------
+int b200q_mul_mat_group(const b200q_mul_mat_group_args * a, const void * const * w, const float * act, float * const * dst,
+                        void * stream) {
+    if (!a || !w || !act || !dst) return fail(B200Q_EINVAL, "mul_mat_group: null argument");
+    if (a->n_mats < 1 || a->n_mats > B200Q_MAX_GROUP) return fail(B200Q_EINVAL, "mul_mat_group: n_mats must be 1..%d", B200Q_MAX_GROUP);
+    const int be = blck_elems(a->type);
+    if (!be || a->type == T_F32) return fail(B200Q_ENOTSUP, "mul_mat_group: unsupported weight type %d", a->type);
+    if (a->k <= 0 || a->k % be) return fail(B200Q_EINVAL, "mul_mat_group: bad k");
+    const DevInfo & di = dev_info();
+    if (!di.ok) return fail(B200Q_ENODEVICE, "mul_mat_group: no CUDA device");
+    for (int g = 0; g < a->n_mats; ++g) {
+        if (!w[g] || !dst[g] || a->m[g] < 0) return fail(B200Q_EINVAL, "mul_mat_group: bad matrix %d", g);
+    }
+    KqParams kq{};
+    int      grid = 0, smem = 0;
+    if (plan_kq(kq, grid, smem, a->type, a->k, a->n_mats, w, dst, a->m, act, di)) {
+        return launch_kq(kq, grid, smem, a->type, a->flags, (cudaStream_t) stream);
+    }
+    // anything the grouped kernel does not take: one launch per matrix (same results)
+    for (int g = 0; g < a->n_mats; ++g) {
+        b200q_mul_mat_args q{};
+        q.type = a->type; q.k = a->k; q.m = a->m[g]; q.n = 1;
+        q.ne02 = q.ne03 = q.ne12 = q.ne13 = 1;
+        q.nb01 = b200q_row_size(a->type, a->k); q.nb02 = q.nb03 = q.nb01 * (size_t) a->m[g];
+        q.nb11 = q.nb12 = q.nb13 = (size_t) a->k * 4;
+        q.nb1 = q.nb2 = q.nb3 = (size_t) a->m[g] * 4;
+        q.flags = a->flags;
+        if (int rc = b200q_mul_mat(&q, w[g], act, dst[g], nullptr, 0, stream)) return rc;
     }
     return 0;
 }

@@ -1,0 +1,384 @@
+// gemv_kq.cu — decode GEMV (n = 1) for the K-quants (q4_K, q6_K), the formats that carry a Q4_K_M model.
+//
+// Same role as gemv.cu (it replaces the reference's quantize_q8_1 + mul_mat_vec_q pair, ggml-cuda/quantize.cu:4-48,
+// mmvq.cu:139-226), redesigned around what the B200 timeline of gemv.cu showed (profiles/r01_gemv_timeline_v1.txt):
+//
+//   * 9 warps and <= 112 registers, <= ~110 KB of shared memory per CTA, one CTA per SM per launch, so that TWO launches
+//     are co-resident on every SM under programmatic dependent launch: while kernel i computes, kernel i+1 has already
+//     filled its ring with ~100 KB of weights per SM, i.e. the HBM pipe keeps streaming across the launch boundary.
+//   * activations are quantized per 256-element super-block (one fp32 scale + int16 partial sums per 16 / 32 values),
+//     the arithmetic ggml-cpu itself uses for these formats (quantize_row_q8_K + ggml_vec_dot_q4_K_q8_K /
+//     _q6_K_q8_K, ggml-cpu/quants.c:550-623, :705-758): the 6-bit sub-block scales then multiply INTEGER sums
+//     (IMAD / dp2a) instead of costing an I2F + FFMA per 32 values, and the kernel needs ~0.7 (q4_K) / ~1.6 (q6_K)
+//     instructions per weight instead of ~2.3.
+//   * a lane owns whole super-blocks (LDS.128 for q4_K; q6_K's 210-byte blocks through aligned words + funnel shift),
+//     lanes of a row read consecutive 16-byte activation chunks (chunk-major layout: conflict-free), one row per lane
+//     group, one warp pass = one ring stage, warps consume alternate stages on their own (no CTA-wide barrier in the
+//     main loop).
+//   * up to 4 matrices that share the activation vector (q/k/v, gate/up) run in ONE launch ("segments"): one
+//     activation load + quantization, one launch hop.
+// Fixed summation order: results are bit-reproducible and independent of the grid (row-split relies on it).
+#include "gemv_kq.cuh"
+
+#include "blocks.cuh"
+#include "sm100.cuh"
+
+#include <cuda_runtime.h>
+
+namespace b200q {
+
+namespace {
+
+using namespace sm100;
+
+constexpr int NW       = 8;              // consumer warps
+constexpr int NTHREADS = NW * 32;
+constexpr int MAX_S    = 24;             // ring depth limit
+constexpr uint32_t OFF_FULL = 0;  // full-barriers (8 B each, MAX_S of them); data regions start at 384
+
+extern __shared__ __align__(128) uint8_t kq_smem[];
+
+// development aid: a host-mapped buffer that stuck waiters report into (b200q_debug_hang_buffer)
+__device__ unsigned long long * g_kq_hang = nullptr;
+__device__ __forceinline__ void mbar_wait_dbg(uint32_t bar, uint32_t parity, int tag, int j) {
+    unsigned long long * hb = g_kq_hang;
+    if (!hb) {
+        mbar_wait(bar, parity);
+        return;
+    }
+    unsigned spins = 0;
+    for (;;) {
+        uint32_t ok;
+        asm volatile(
+            "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+            : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (ok) return;
+        if (++spins == (1u << 20)) {
+            const unsigned long long idx = atomicAdd(hb, 1ull);
+            if (idx < 500) {
+                unsigned long long st;
+                asm volatile("ld.shared.b64 %0, [%1];" : "=l"(st) : "r"(bar));
+                hb[1 + idx * 4 + 0] = ((unsigned long long) blockIdx.x << 32) | threadIdx.x;
+                hb[1 + idx * 4 + 1] = ((unsigned long long) tag << 32) | (unsigned) j;
+                hb[1 + idx * 4 + 2] = parity;
+                hb[1 + idx * 4 + 3] = st;
+                __threadfence_system();
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ int4 lds128(uint32_t a) {
+    int4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ float lds32f(uint32_t a) { return __uint_as_float(lds32(a)); }
+__device__ __forceinline__ int dp4a_us(uint32_t a, int b, int c) {  // a: 4 unsigned bytes, b: 4 signed bytes
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp2a_lo_su(int a, uint32_t b, int c) {  // a: 2 x s16, b: bytes 0,1 unsigned
+    int d;
+    asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp2a_hi_su(int a, uint32_t b, int c) {  // bytes 2,3 of b
+    int d;
+    asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp2a_lo_ss(int a, int b, int c) {
+    int d;
+    asm("dp2a.lo.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp2a_hi_ss(int a, int b, int c) {
+    int d;
+    asm("dp2a.hi.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+// ---- activation quantization: f32 [k] -> per super-block int8 (chunk-major), scale, int16 sums -----------------
+//   q   : 16-byte chunk c (0..15) of super-block s at off_q + (c * nsb + s) * 16
+//   dx  : float at off_dx + 4 s                      (x ~= dx * q)
+//   bs16: 16 x int16 at off_bs16 + 32 s              (sums of q over 16 values)
+//   bs32:  8 x int16 at off_bs32 + 16 s              (sums over 32 values)
+// One warp per super-block per step; lane l holds values 8l .. 8l+7 (coalesced 1 KB per warp).
+__device__ __forceinline__ void quantize_act(const KqParams & p, uint32_t sb, int warp, int lane) {
+    constexpr int QB = 4;
+    for (int s0 = warp; s0 < p.nsb; s0 += NW * QB) {
+        float4 x[QB][2];
+#pragma unroll
+        for (int b = 0; b < QB; ++b) {
+            const int s = s0 + b * NW;
+            if (s < p.nsb) {
+                const float4 * src = (const float4 *) (p.act + (size_t) s * 256 + lane * 8);
+                x[b][0] = __ldg(src);
+                x[b][1] = __ldg(src + 1);
+            }
+        }
+#pragma unroll
+        for (int b = 0; b < QB; ++b) {
+            const int s = s0 + b * NW;
+            if (s >= p.nsb) break;  // warp-uniform
+            const float v[8] = { x[b][0].x, x[b][0].y, x[b][0].z, x[b][0].w, x[b][1].x, x[b][1].y, x[b][1].z, x[b][1].w };
+            float amax = 0.0f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(v[i]));
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+            const float d  = amax * (1.0f / 127.0f);
+            const float id = amax > 0.0f ? 127.0f / amax : 0.0f;
+            int q[8], sum = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                q[i] = __float2int_rn(v[i] * id);
+                sum += q[i];
+            }
+            const uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t) q[3] << 24);
+            const uint32_t w1 = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t) q[7] << 24);
+            const uint32_t qa = sb + p.off_q + (uint32_t) (((lane >> 1) * p.nsb + s) * 16 + (lane & 1) * 8);
+            asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(qa), "r"(w0), "r"(w1) : "memory");
+            const int s16 = sum + __shfl_xor_sync(0xffffffffu, sum, 1);
+            const int s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 2);
+            if ((lane & 1) == 0) {
+                asm volatile("st.shared.u16 [%0], %1;" ::"r"(sb + p.off_bs16 + (uint32_t) (s * 32 + (lane >> 1) * 2)), "h"((short) s16) : "memory");
+            }
+            if ((lane & 3) == 0) {
+                asm volatile("st.shared.u16 [%0], %1;" ::"r"(sb + p.off_bs32 + (uint32_t) (s * 16 + (lane >> 2) * 2)), "h"((short) s32) : "memory");
+            }
+            if (lane == 0) {
+                asm volatile("st.shared.f32 [%0], %1;" ::"r"(sb + p.off_dx + (uint32_t) s * 4), "f"(d) : "memory");
+            }
+        }
+    }
+}
+
+// ---- super-block dots ---------------------------------------------------------------------------------------------
+// returns  sum_{i in super-block s} w_i * x_i   for the row that starts at shared address `row`
+template <int T> struct SbDot;
+
+template <> struct SbDot<T_Q4_K> {
+    static constexpr int SB_BYTES = 144;
+    static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int s) {
+        const uint32_t b = row + (uint32_t) s * 144u;
+        const int4     h = lds128(b);  // [d dmin] [scales x3]
+        // get_scale_min_k4 (ggml-quants.c:703-710) on whole words: bytes of sc_lo/mn_lo = sub-blocks 0..3, *_hi = 4..7
+        const uint32_t sc_lo = (uint32_t) h.y & 0x3F3F3F3Fu, mn_lo = (uint32_t) h.z & 0x3F3F3F3Fu;
+        const uint32_t sc_hi = ((uint32_t) h.w & 0x0F0F0F0Fu) | (((uint32_t) h.y >> 2) & 0x30303030u);
+        const uint32_t mn_hi = (((uint32_t) h.w >> 4) & 0x0F0F0F0Fu) | (((uint32_t) h.z >> 2) & 0x30303030u);
+        const uint32_t qbase = sb + p.off_q + (uint32_t) s * 16u;
+        const uint32_t cstr  = (uint32_t) p.nsb * 16u;  // distance between consecutive activation chunks of one super-block
+        int acc = 0;
+#pragma unroll
+        for (int pq = 0; pq < 4; ++pq) {
+            const int4 q0 = lds128(b + 16 + 32 * pq), q1 = lds128(b + 32 + 32 * pq);
+            const int4 a0 = lds128(qbase + (4 * pq + 0) * cstr), a1 = lds128(qbase + (4 * pq + 1) * cstr);
+            const int4 a2 = lds128(qbase + (4 * pq + 2) * cstr), a3 = lds128(qbase + (4 * pq + 3) * cstr);
+            int lo = 0, lo2 = 0, hi = 0, hi2 = 0;  // hi sums carry a factor 16 (high nibbles are not shifted down)
+            lo  = dp4a_us((uint32_t) q0.x & 0x0F0F0F0Fu, a0.x, lo);
+            lo2 = dp4a_us((uint32_t) q0.y & 0x0F0F0F0Fu, a0.y, lo2);
+            lo  = dp4a_us((uint32_t) q0.z & 0x0F0F0F0Fu, a0.z, lo);
+            lo2 = dp4a_us((uint32_t) q0.w & 0x0F0F0F0Fu, a0.w, lo2);
+            lo  = dp4a_us((uint32_t) q1.x & 0x0F0F0F0Fu, a1.x, lo);
+            lo2 = dp4a_us((uint32_t) q1.y & 0x0F0F0F0Fu, a1.y, lo2);
+            lo  = dp4a_us((uint32_t) q1.z & 0x0F0F0F0Fu, a1.z, lo);
+            lo2 = dp4a_us((uint32_t) q1.w & 0x0F0F0F0Fu, a1.w, lo2);
+            hi  = dp4a_us((uint32_t) q0.x & 0xF0F0F0F0u, a2.x, hi);
+            hi2 = dp4a_us((uint32_t) q0.y & 0xF0F0F0F0u, a2.y, hi2);
+            hi  = dp4a_us((uint32_t) q0.z & 0xF0F0F0F0u, a2.z, hi);
+            hi2 = dp4a_us((uint32_t) q0.w & 0xF0F0F0F0u, a2.w, hi2);
+            hi  = dp4a_us((uint32_t) q1.x & 0xF0F0F0F0u, a3.x, hi);
+            hi2 = dp4a_us((uint32_t) q1.y & 0xF0F0F0F0u, a3.y, hi2);
+            hi  = dp4a_us((uint32_t) q1.z & 0xF0F0F0F0u, a3.z, hi);
+            hi2 = dp4a_us((uint32_t) q1.w & 0xF0F0F0F0u, a3.w, hi2);
+            const uint32_t scw = pq < 2 ? sc_lo : sc_hi;
+            const int      sh  = 16 * (pq & 1);
+            acc += (int) ((scw >> sh) & 0xFFu) * (lo + lo2) + (int) ((scw >> (sh + 8)) & 0xFFu) * ((hi + hi2) >> 4);
+        }
+        const int4 bs = lds128(sb + p.off_bs32 + (uint32_t) s * 16u);  // 8 x int16 sums over 32 activations
+        int mins = dp2a_lo_su(bs.x, mn_lo, 0);
+        mins     = dp2a_hi_su(bs.y, mn_lo, mins);
+        mins     = dp2a_lo_su(bs.z, mn_hi, mins);
+        mins     = dp2a_hi_su(bs.w, mn_hi, mins);
+        const float d    = half_bits_to_float((uint16_t) ((uint32_t) h.x & 0xffffu));
+        const float dmin = half_bits_to_float((uint16_t) ((uint32_t) h.x >> 16));
+        const float dx   = lds32f(sb + p.off_dx + (uint32_t) s * 4u);
+        return dx * (d * (float) acc - dmin * (float) mins);
+    }
+};
+
+template <> struct SbDot<T_Q6_K> {
+    static constexpr int SB_BYTES = 210;
+    // 210-byte super-blocks are only 2-byte aligned: aligned words + funnel shift (shift is 0 or 16, constant per lane)
+    template <int N> static __device__ __forceinline__ void ldw(uint32_t b4, int sh, int first, uint32_t (&out)[N]) {
+        uint32_t prev = lds32(b4 + 4u * first);
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            const uint32_t next = lds32(b4 + 4u * (first + i + 1));
+            out[i]              = __funnelshift_r(prev, next, sh);
+            prev                = next;
+        }
+    }
+    static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int s) {
+        const uint32_t b     = row + (uint32_t) s * 210u;
+        const uint32_t b4    = b & ~3u;
+        const int      sh    = (int) (b & 2u) * 8;
+        const uint32_t qbase = sb + p.off_q + (uint32_t) s * 16u;
+        const uint32_t cstr  = (uint32_t) p.nsb * 16u;
+        uint32_t scw[5];  // [sc0..3] [sc4..7] [sc8..11] [sc12..15] [d | next]
+        ldw<5>(b4, sh, 48, scw);
+        int acc = 0;
+#pragma unroll
+        for (int n = 0; n < 2; ++n) {  // 128-element halves
+            uint32_t ql[16], qh[8];
+            ldw<16>(b4, sh, 16 * n, ql);      // ql[l], l = 0..63 of this half
+            ldw<8>(b4, sh, 32 + 8 * n, qh);   // qh[l], l = 0..31
+#pragma unroll
+            for (int quad = 0; quad < 4; ++quad) {  // elements 128 n + 32 quad + l
+                const int4 a0 = lds128(qbase + (uint32_t) (8 * n + 2 * quad) * cstr);
+                const int4 a1 = lds128(qbase + (uint32_t) (8 * n + 2 * quad + 1) * cstr);
+                const int  av[8] = { a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w };
+                int        s0 = 0, s1 = 0;
+#pragma unroll
+                for (int wi = 0; wi < 8; ++wi) {
+                    const uint32_t lw = ql[wi + 8 * (quad & 1)];
+                    const uint32_t lo = (quad < 2 ? lw : lw >> 4) & 0x0F0F0F0Fu;
+                    const uint32_t h2 = quad == 0 ? qh[wi] << 4 : quad == 1 ? qh[wi] << 2 : quad == 2 ? qh[wi] : qh[wi] >> 2;
+                    const uint32_t v  = lo | (h2 & 0x30303030u);  // 6-bit value 0..63 (offset -32 applied through bs16)
+                    if (wi < 4) s0 = dp4a_us(v, av[wi], s0); else s1 = dp4a_us(v, av[wi], s1);
+                }
+                const uint32_t w  = scw[2 * n + (quad >> 1)];
+                const int      sa = (int) (int8_t) (w >> (16 * (quad & 1)));
+                const int      sb_ = (int) (int8_t) (w >> (16 * (quad & 1) + 8));
+                acc += sa * s0 + sb_ * s1;
+            }
+        }
+        // - 32 * sum_g sc_g * bs16_g
+        const int4 bs0 = lds128(sb + p.off_bs16 + (uint32_t) s * 32u), bs1 = lds128(sb + p.off_bs16 + (uint32_t) s * 32u + 16u);
+        int off = dp2a_lo_ss(bs0.x, (int) scw[0], 0);
+        off     = dp2a_hi_ss(bs0.y, (int) scw[0], off);
+        off     = dp2a_lo_ss(bs0.z, (int) scw[1], off);
+        off     = dp2a_hi_ss(bs0.w, (int) scw[1], off);
+        off     = dp2a_lo_ss(bs1.x, (int) scw[2], off);
+        off     = dp2a_hi_ss(bs1.y, (int) scw[2], off);
+        off     = dp2a_lo_ss(bs1.z, (int) scw[3], off);
+        off     = dp2a_hi_ss(bs1.w, (int) scw[3], off);
+        const float d  = half_bits_to_float((uint16_t) (scw[4] & 0xffffu));
+        const float dx = lds32f(sb + p.off_dx + (uint32_t) s * 4u);
+        return dx * d * (float) (acc - 32 * off);
+    }
+};
+
+struct StageInfo {
+    int g, r0, nrows;
+};
+__device__ __forceinline__ StageInfo stage_info(const KqParams & p, int t) {
+    StageInfo si;
+    si.g = 0;
+#pragma unroll
+    for (int i = 1; i < KQ_MAX_SEG; ++i) {
+        if (i < p.nseg && t >= p.seg[i].stage0) si.g = i;
+    }
+    si.r0    = (t - p.seg[si.g].stage0) * p.rows_per_stage;
+    si.nrows = min(p.rows_per_stage, p.seg[si.g].m - si.r0);
+    return si;
+}
+
+template <int T> __global__ void __launch_bounds__(NTHREADS, 2) gemv_kq_kernel(const KqParams p) {
+    const uint32_t sb   = smem_u32(kq_smem);
+    const int      warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int      S    = p.nstages;  // a multiple of NW
+    const int      D    = S / NW;     // ring depth per consumer warp
+    // this CTA's contiguous range of stages
+    const int T0 = (int) ((long long) p.total_stages * blockIdx.x / gridDim.x);
+    const int T1 = (int) ((long long) p.total_stages * (blockIdx.x + 1) / gridDim.x);
+    if (g_kq_hang && threadIdx.x == 0) atomicAdd(g_kq_hang + 2041, 1ull);  // CTAs started
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < S; ++s) {
+            mbar_init(sb + OFF_FULL + 8 * s, 1);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    pdl_launch_dependents();  // the next launch may become co-resident and start prefetching its weights
+
+    // Every warp feeds itself: lane 0 bulk-copies the warp's own next stages into the warp's own D slots (slot ownership:
+    // warp w owns slots w, w + NW, ...), so successive uses of a slot's full-barrier are waited on by ONE warp in order.
+    // (A ring shared by all warps let a fast warp test a slot's barrier one phase early — parity ABA — when bulk copies
+    // completed out of order: stale data, a desynchronised ring, rare hangs / launch failures.)  No empty-barriers and no
+    // producer hop: the warp that finishes a slot refills it at once.
+    const uint64_t pol    = policy_evict_first();
+    const int      nmine  = T0 + warp < T1 ? (T1 - T0 - warp + NW - 1) / NW : 0;  // stages of this warp
+    auto           issue  = [&](int i) {
+        const int       t     = T0 + warp + i * NW, slot = warp + NW * (i % D);
+        const StageInfo si    = stage_info(p, t);
+        const uint32_t  bytes = (uint32_t) si.nrows * (uint32_t) p.row_bytes;
+        const uint32_t  full  = sb + OFF_FULL + 8 * slot;
+        mbar_expect_tx(full, bytes);
+        bulk_g2s_hint(sb + p.off_stage + (uint32_t) slot * p.stage_bytes, p.seg[si.g].w + (size_t) si.r0 * p.row_bytes, bytes,
+                      full, pol);
+    };
+    if (p.early_prefetch && lane == 0) {
+        for (int i = 0; i < min(D, nmine); ++i) issue(i);  // immutable weights: stream them under the previous kernel's tail
+    }
+    pdl_wait();  // the activations (and dst) belong to the previous kernels of the stream
+    if (!p.early_prefetch && lane == 0) {
+        for (int i = 0; i < min(D, nmine); ++i) issue(i);
+    }
+    quantize_act(p, sb, warp, lane);
+    __syncthreads();
+
+    const int lpr  = p.lpr;
+    const int sub  = lane & (lpr - 1);
+    const int lrow = lane / lpr;
+    for (int i = 0; i < nmine; ++i) {
+        const int       t = T0 + warp + i * NW, slot = warp + NW * (i % D), use = i / D;
+        const StageInfo si = stage_info(p, t);
+        mbar_wait_dbg(sb + OFF_FULL + 8 * slot, use & 1, 2, i);
+        const uint32_t row = sb + p.off_stage + (uint32_t) slot * p.stage_bytes + (uint32_t) lrow * (uint32_t) p.row_bytes;
+        float acc = 0.0f;
+        if (lrow < si.nrows) {
+            for (int s = sub; s < p.nsb; s += lpr) {
+                acc += SbDot<T>::run(p, sb, row, s);
+            }
+        }
+        __syncwarp();  // every lane is done reading the slot
+        if (lane == 0 && i + D < nmine) {
+            fence_proxy_async_smem();  // order the generic-proxy reads before the async-proxy refill
+            issue(i + D);
+        }
+        for (int o = lpr >> 1; o > 0; o >>= 1) {
+            acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        }
+        if (sub == 0 && lrow < si.nrows) {
+            p.seg[si.g].dst[si.r0 + lrow] = acc;
+        }
+    }
+    if (g_kq_hang && threadIdx.x == 0) atomicAdd(g_kq_hang + 2042, 1ull);  // warp 0 of a CTA done
+}
+
+}  // namespace
+
+kq_kernel_t kq_kernel_for(int type) {
+    switch (type) {
+        case T_Q4_K: return gemv_kq_kernel<T_Q4_K>;
+        case T_Q6_K: return gemv_kq_kernel<T_Q6_K>;
+        default: return nullptr;
+    }
+}
+void kq_set_hang_buffer(unsigned long long * host_mapped) {
+    cudaMemcpyToSymbol(g_kq_hang, &host_mapped, sizeof(host_mapped));
+}
+int kq_threads() { return NTHREADS; }
+int kq_consumer_warps() { return NW; }
+
+}  // namespace b200q

@@ -1,0 +1,39 @@
+// gemv_kq.cuh — launch parameters of the K-quant decode GEMV (gemv_kq.cu): n = 1, q4_K / q6_K, up to 4 weight
+// matrices that share one activation vector (q/k/v, gate/up) in ONE launch.
+#pragma once
+#include <stdint.h>
+
+namespace b200q {
+
+constexpr int KQ_MAX_SEG = 4;
+
+struct KqSegment {
+    const uint8_t * w;    // [m][row_bytes] quantized rows, contiguous, 16-byte aligned
+    float *         dst;  // [m] f32
+    int             m;
+    int             stage0;  // first stage index of this segment (stages never straddle segments)
+};
+
+struct KqParams {
+    KqSegment     seg[KQ_MAX_SEG];
+    int           nseg;
+    const float * act;  // [k] f32 (16-byte aligned)
+    int           k, nsb;        // row length, super-blocks per row
+    int           row_bytes;     // nsb * 144 (q4_K) | nsb * 210 (q6_K); multiple of 16
+    int           lpr;           // lanes per row: 8, 16 or 32
+    int           rows_per_stage;  // 32 / lpr: one stage = one warp pass
+    int           total_stages;
+    int           nstages;       // ring depth
+    int           stage_bytes;   // rows_per_stage * row_bytes rounded up to 128
+    // shared-memory offsets
+    int           off_q, off_dx, off_bs16, off_bs32, off_stage;
+    int           early_prefetch;  // weights immutable: stream them before griddepcontrol.wait
+};
+
+typedef void (*kq_kernel_t)(const KqParams);
+kq_kernel_t kq_kernel_for(int type);
+void        kq_set_hang_buffer(unsigned long long * host_mapped);  // development aid
+int         kq_threads();
+int         kq_consumer_warps();
+
+}  // namespace b200q

@@ -177,3 +177,36 @@ def test_full_size_properties_llama8b_ffn():
     deq = b200q.dequantize(wt).double()
     ref = (deq @ torch.from_numpy(act).cuda().double().T).T.cpu().numpy()
     assert refs.nmse(out, ref) <= MAX_NMSE
+
+
+@pytest.mark.parametrize("t", [refs.Q4_K, refs.Q6_K], ids=lambda t: refs.NAMES[t])
+@pytest.mark.parametrize("m,k", [(1, 256), (5, 512), (1024, 4096), (4096, 4096), (300, 14336), (64, 8192), (33, 28672),
+                                 (200, 1280)])
+def test_kquant_decode_kernel(t, m, k):
+    """the K-quant decode kernel (gemv_kq.cu, per-256 activation scales like ggml-cpu's q8_K) against the oracle"""
+    import b200q
+    torch = _t()
+    w = refs.make_weights(t, m, k, seed=1300 + t + m)
+    act = refs.uniform_weights(1, k, seed=1301 + k)
+    want = refs.orc_mul_mat(t, w, act)
+    got = b200q.mul_mat(_up(t, w, (m, k)), torch.from_numpy(act).cuda()).cpu().numpy()
+    assert np.isfinite(got).all()
+    assert refs.nmse(got, want) <= MAX_NMSE
+
+
+@pytest.mark.parametrize("t", [refs.Q4_K, refs.Q6_K, refs.Q8_0], ids=lambda t: refs.NAMES[t])
+def test_mul_mat_group_equals_separate_calls(t):
+    """q/k/v- and gate/up-style groups: one launch, bit-identical to one launch per matrix; also vs the oracle"""
+    import b200q
+    torch = _t()
+    k = 4096
+    ms = [4096, 1024, 1024, 37]
+    ws = [refs.make_weights(t, m, k, seed=1400 + i) for i, m in enumerate(ms)]
+    act_h = refs.uniform_weights(1, k, seed=1410)
+    act = torch.from_numpy(act_h).cuda()
+    qts = [_up(t, w, (m, k)) for w, m in zip(ws, ms)]
+    outs = b200q.mul_mat_group(qts, act)
+    for w, qt, o in zip(ws, qts, outs):
+        single = b200q.mul_mat(qt, act)
+        assert torch.equal(o, single)
+        assert refs.nmse(o.cpu().numpy(), refs.orc_mul_mat(t, w, act_h)) <= MAX_NMSE

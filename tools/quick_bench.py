@@ -82,6 +82,43 @@ if __name__ == "__main__":
             names = ["start", "pdl_wait", "quant", "first_full", "end", "act_loaded", "q_done_t0"]
             order = [0, 1, 5, 6, 2, 3, 4]
             print(f"kernel {i}: " + "  ".join(f"{names[j]}: med {int(np.median(a[:, j]) - t0):6d} max {int(a[:, j].max() - t0):6d}" for j in order))
+    elif which == "layer":
+        # one Llama-3-8B layer + chain, grouped (qkv, o, gate+up, down) vs ungrouped launches, cold HBM (distinct copies)
+        t = refs.Q4_K
+        def mk(m, k):
+            host = np.tile(refs.random_blocks(t, 256, k, seed=1), ((m + 255) // 256, 1))[:m]
+            return b200q.upload(t, (m, k), host)
+        L = 24
+        layers = [dict(q=mk(4096, 4096), k=mk(1024, 4096), v=mk(1024, 4096), o=mk(4096, 4096), g=mk(14336, 4096),
+                       u=mk(14336, 4096), d=mk(4096, 14336)) for _ in range(L)]
+        a4 = torch.rand(1, 4096, device="cuda") * 2 - 1
+        a14 = torch.rand(1, 14336, device="cuda") * 2 - 1
+        outs = {n: torch.empty(1, layers[0][n].m, device="cuda") for n in "qkvogud"}
+        byt = sum(w.nbytes for w in layers[0].values())
+        def run(grouped):
+            for l in layers:
+                if grouped:
+                    b200q.mul_mat_group([l["q"], l["k"], l["v"]], a4, [outs["q"], outs["k"], outs["v"]])
+                    b200q.mul_mat(l["o"], a4, out=outs["o"])
+                    b200q.mul_mat_group([l["g"], l["u"]], a4, [outs["g"], outs["u"]])
+                    b200q.mul_mat(l["d"], a14, out=outs["d"])
+                else:
+                    for n in "qkvogu":
+                        b200q.mul_mat(l[n], a4, out=outs[n])
+                    b200q.mul_mat(l["d"], a14, out=outs["d"])
+        for grouped in (False, True):
+            run(grouped); torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                run(grouped)
+            g.replay(); torch.cuda.synchronize()
+            e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(5):
+                g.replay()
+            e1.record(); torch.cuda.synchronize()
+            us = e0.elapsed_time(e1) * 1e3 / 5 / L
+            print(f"layer (q4_K, 7 matmuls, {byt/1e6:.0f} MB) grouped={grouped}: {us:7.2f} us/layer  {byt/us/1e3:7.1f} GB/s ({byt/us/1e3/6545*100:.1f}% of measured HBM)", flush=True)
     elif which == "mmq":
         # prompt processing (n = 512): TFLOP/s = 2*m*n*k / time (test-backend-ops' definition, :3114-3117)
         import json
