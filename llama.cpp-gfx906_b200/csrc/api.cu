@@ -211,24 +211,28 @@ bool plan_kq(KqParams & p, int & grid, int & smem, int type, int64_t k, int nseg
     p.k         = (int) k;
     p.row_bytes = p.nsb * blck_bytes(type);
     if (p.row_bytes % 16 || ((uintptr_t) act & 15)) return false;
-    int lpr = 1;
-    while (lpr < 8 && lpr < p.nsb) lpr *= 2;
-    if (p.nsb > 16) lpr = 16;
-    if (p.nsb > 32) lpr = 32;
-    p.lpr            = lpr;
-    p.rows_per_stage = 32 / lpr;
-    p.stage_bytes    = round_up(p.rows_per_stage * p.row_bytes + 16, 128);
+    static const int lpr_cap   = getenv("B200Q_KQ_LPR") ? atoi(getenv("B200Q_KQ_LPR")) : 8;
+    static const int budget_kb = getenv("B200Q_KQ_SMEM_KB") ? atoi(getenv("B200Q_KQ_SMEM_KB")) : 110;
+    const int NWc = kq_consumer_warps();
     p.off_q     = 384;
     p.off_dx    = p.off_q + p.nsb * 256;
     p.off_bs16  = round_up(p.off_dx + p.nsb * 4, 16);
     p.off_bs32  = p.off_bs16 + p.nsb * 32;
     p.off_stage = round_up(p.off_bs32 + p.nsb * 16, 128);
-    static const int budget_kb = getenv("B200Q_KQ_SMEM_KB") ? atoi(getenv("B200Q_KQ_SMEM_KB")) : 110;
-    const int NWc = kq_consumer_warps();
-    int S = (budget_kb * 1024 - p.off_stage) / p.stage_bytes;  // two launches co-resident per SM
-    if (S < NWc) S = (di.max_smem - p.off_stage) / p.stage_bytes;
-    if (S < NWc) return false;
-    p.nstages = std::min(S / NWc, 2) * NWc;  // each consumer warp owns nstages / NW slots (gemv_kq.cu)
+    // lanes per row: few lanes = many rows per stage = less per-stage overhead, but two launches must stay co-resident
+    // per SM (the next one prefetches under this one's tail) with at least ~1.25 slots per warp in flight
+    int lpr = 1, S = 0;
+    while (lpr < lpr_cap && lpr < p.nsb) lpr *= 2;
+    for (;; lpr *= 2) {
+        p.lpr            = lpr;
+        p.rows_per_stage = 32 / lpr;
+        p.stage_bytes    = round_up(p.rows_per_stage * p.row_bytes + 16, 128);
+        S                = (budget_kb * 1024 - p.off_stage) / p.stage_bytes;
+        if (S >= NWc + 2 || lpr == 32) break;
+    }
+    if (S < NWc / 2) S = (di.max_smem - p.off_stage) / p.stage_bytes;  // very long rows: one CTA per SM
+    if (S < 2) return false;
+    p.nstages = std::min(S, 32);  // each warp owns nstages / NW (+1) slots (gemv_kq.cu)
     long long total = 0;
     for (int g = 0; g < nseg; ++g) {
         if (m[g] <= 0 || m[g] > (1 << 30) || ((uintptr_t) w[g] & 15)) return false;

@@ -33,7 +33,7 @@ using namespace sm100;
 
 constexpr int NW       = 8;              // consumer warps
 constexpr int NTHREADS = NW * 32;
-constexpr int MAX_S    = 24;             // ring depth limit
+constexpr int MAX_S    = 32;             // ring depth limit
 constexpr uint32_t OFF_FULL = 0;  // full-barriers (8 B each, MAX_S of them); data regions start at 384
 
 extern __shared__ __align__(128) uint8_t kq_smem[];
@@ -295,8 +295,11 @@ __device__ __forceinline__ StageInfo stage_info(const KqParams & p, int t) {
 template <int T> __global__ void __launch_bounds__(NTHREADS, 2) gemv_kq_kernel(const KqParams p) {
     const uint32_t sb   = smem_u32(kq_smem);
     const int      warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int      S    = p.nstages;  // a multiple of NW
-    const int      D    = S / NW;     // ring depth per consumer warp
+    const int      S    = p.nstages;
+    const int      NA   = min(NW, S);  // warps that own slots (very long rows: fewer slots than warps fit)
+    // ring depth and first slot of this warp (the S % NA spare slots go to the first warps)
+    const int      D     = warp < NA ? S / NA + (warp < S % NA ? 1 : 0) : 1;
+    const int      slot0 = warp * (S / NA) + min(warp, S % NA);
     // this CTA's contiguous range of stages
     const int T0 = (int) ((long long) p.total_stages * blockIdx.x / gridDim.x);
     const int T1 = (int) ((long long) p.total_stages * (blockIdx.x + 1) / gridDim.x);
@@ -312,14 +315,14 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 2) gemv_kq_kernel(c
     pdl_launch_dependents();  // the next launch may become co-resident and start prefetching its weights
 
     // Every warp feeds itself: lane 0 bulk-copies the warp's own next stages into the warp's own D slots (slot ownership:
-    // warp w owns slots w, w + NW, ...), so successive uses of a slot's full-barrier are waited on by ONE warp in order.
+    // warp w owns D consecutive slots), so successive uses of a slot's full-barrier are waited on by ONE warp in order.
     // (A ring shared by all warps let a fast warp test a slot's barrier one phase early — parity ABA — when bulk copies
     // completed out of order: stale data, a desynchronised ring, rare hangs / launch failures.)  No empty-barriers and no
     // producer hop: the warp that finishes a slot refills it at once.
     const uint64_t pol    = policy_evict_first();
-    const int      nmine  = T0 + warp < T1 ? (T1 - T0 - warp + NW - 1) / NW : 0;  // stages of this warp
+    const int      nmine  = warp < NA && T0 + warp < T1 ? (T1 - T0 - warp + NA - 1) / NA : 0;  // stages of this warp
     auto           issue  = [&](int i) {
-        const int       t     = T0 + warp + i * NW, slot = warp + NW * (i % D);
+        const int       t     = T0 + warp + i * NA, slot = slot0 + i % D;
         const StageInfo si    = stage_info(p, t);
         const uint32_t  bytes = (uint32_t) si.nrows * (uint32_t) p.row_bytes;
         const uint32_t  full  = sb + OFF_FULL + 8 * slot;
@@ -341,7 +344,7 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 2) gemv_kq_kernel(c
     const int sub  = lane & (lpr - 1);
     const int lrow = lane / lpr;
     for (int i = 0; i < nmine; ++i) {
-        const int       t = T0 + warp + i * NW, slot = warp + NW * (i % D), use = i / D;
+        const int       t = T0 + warp + i * NA, slot = slot0 + i % D, use = i / D;
         const StageInfo si = stage_info(p, t);
         mbar_wait_dbg(sb + OFF_FULL + 8 * slot, use & 1, 2, i);
         const uint32_t row = sb + p.off_stage + (uint32_t) slot * p.stage_bytes + (uint32_t) lrow * (uint32_t) p.row_bytes;
