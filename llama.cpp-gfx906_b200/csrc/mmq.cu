@@ -35,7 +35,9 @@
 
 #include <cstdlib>
 #include <mutex>
+#include <map>
 #include <set>
+#include <tuple>
 
 namespace b200q {
 
@@ -46,7 +48,8 @@ using namespace sm100;
 constexpr int TILE_M  = 128;  // weight rows per tile (UMMA M)
 constexpr int TILE_N  = 256;  // activation columns per tile (UMMA N, <= 256)
 constexpr int CHUNK_K = 64;   // bf16 elements per 128-byte swizzled row
-constexpr int AB_STAGES = 3;
+constexpr int A_STAGES = 3;      // dequantized weight chunks (bf16)
+constexpr int MAX_B_STAGES = 4;  // packed activation chunks (bf16); 3 when the W ring needs the room
 constexpr int MAX_W_STAGES = 4;
 constexpr int A_STAGE_BYTES = TILE_M * 128;  // 16 KB
 constexpr int B_STAGE_BYTES = TILE_N * 128;  // 32 KB
@@ -59,10 +62,11 @@ constexpr int TMEM_COLS = 512;
 enum {
     BAR_W_FULL  = 0,                           // [MAX_W_STAGES] count 128 (cp.async.mbarrier.arrive.noinc per producer thread)
     BAR_W_EMPTY = BAR_W_FULL + MAX_W_STAGES,   // [MAX_W_STAGES] count N_DQ_WARPS
-    BAR_A_FULL  = BAR_W_EMPTY + MAX_W_STAGES,  // [AB_STAGES] count N_DQ_WARPS / N_DQ_GROUPS
-    BAR_B_FULL  = BAR_A_FULL + AB_STAGES,  // [AB_STAGES] count 1 + tx bytes
-    BAR_AB_EMPTY = BAR_B_FULL + AB_STAGES, // [AB_STAGES] count 1 (tcgen05.commit)
-    BAR_ACC_FULL = BAR_AB_EMPTY + AB_STAGES,  // [2] count 1 (tcgen05.commit)
+    BAR_A_FULL  = BAR_W_EMPTY + MAX_W_STAGES,  // [A_STAGES] count N_DQ_WARPS / N_DQ_GROUPS
+    BAR_A_EMPTY = BAR_A_FULL + A_STAGES,       // [A_STAGES] count 1 (tcgen05.commit after the chunk's last MMA)
+    BAR_B_FULL  = BAR_A_EMPTY + A_STAGES,      // [MAX_B_STAGES] count 1 + tx bytes
+    BAR_B_EMPTY = BAR_B_FULL + MAX_B_STAGES,   // [MAX_B_STAGES] count 1 (tcgen05.commit)
+    BAR_ACC_FULL = BAR_B_EMPTY + MAX_B_STAGES,  // [2] count 1 (tcgen05.commit)
     BAR_ACC_EMPTY = BAR_ACC_FULL + 2,         // [2] count N_EPI_WARPS
     BAR_COUNT = BAR_ACC_EMPTY + 2,
 };
@@ -78,6 +82,14 @@ struct MmqParams {
     int   m_tiles, n_tiles, k_chunks, w_stages_per_tile;
     int   w_stage_k;     // k-elements of raw weights per W stage (128 for 32-element block types, 256 for K-quants)
     int   w_stages;      // W ring depth (2..MAX_W_STAGES, what fits in shared memory)
+    int   b_stages;      // B ring depth (3 or 4)
+    int   n_super;       // column super-tiles per row tile: two 256-column accumulators share ONE dequantized A chunk
+    int   n_sub;         // column tiles per super-tile (2, or 1 when there are too few tiles to fill the GPU otherwise)
+    int   cluster;       // CTAs per cluster (1, 2 or 4): they take adjacent row tiles and share every B chunk by multicast
+    int   m_groups;      // ceil(m_tiles / cluster)
+    int   ksplit;        // 1 or 2: k-halves of one tile go to different CTAs and are summed with fp32 atomics into a zeroed dst
+                         // (two addends on zero: the result does not depend on the arrival order)
+    int   ws_per_split;  // W stages per k-split
     int   piece_bytes;   // raw bytes of w_stage_k elements of one row
     int   blk_bytes;     // bytes per 32 elements (32-block types) — used for the ragged last stage
     int   w_pitch;       // shared-memory pitch of one row piece
@@ -100,6 +112,9 @@ __device__ __forceinline__ void dbg_stamp(const MmqParams & p, int g, int slot) 
 struct PackParams {
     const float * act;
     uint8_t *     out;
+    float *       zero_dst;  // != nullptr: also clear dst [nbatch][n][m] (k-split results are accumulated with atomics)
+    int           m;
+    long long     d_nb1, d_nb2, d_nb3;
     int   k, n, ne12, nbatch, n_tiles, k_chunks;
     long long a_nb1, a_nb2, a_nb3;
     int   vec4;
@@ -109,6 +124,16 @@ struct PackParams {
 //   block (batch, n_tile, k_chunk) = TILE_N rows x 128 bytes; 16-byte chunk c of row j sits at chunk (c ^ (j & 7)).
 // One thread = one 16-byte chunk (8 elements).  Rows >= n are written as zeros.
 __global__ void __launch_bounds__(256) mmq_pack_act(const PackParams p) {
+    if (p.zero_dst) {
+        const long long cells = (long long) p.nbatch * p.n * p.m;
+        for (long long idx = (long long) blockIdx.x * blockDim.x + threadIdx.x; idx < cells; idx += (long long) gridDim.x * blockDim.x) {
+            const int       i   = (int) (idx % p.m);
+            const long long r   = idx / p.m;
+            const int       col = (int) (r % p.n), b = (int) (r / p.n);
+            const int       i13 = b / p.ne12, i12 = b - i13 * p.ne12;
+            *(float *) ((char *) p.zero_dst + (long long) i * 4 + col * p.d_nb1 + i12 * p.d_nb2 + i13 * p.d_nb3) = 0.0f;
+        }
+    }
     const long long chunks_per_block = TILE_N * 8;
     const long long total = (long long) p.nbatch * p.n_tiles * p.k_chunks * chunks_per_block;
     for (long long idx = (long long) blockIdx.x * blockDim.x + threadIdx.x; idx < total;
@@ -177,6 +202,13 @@ __device__ __forceinline__ float ldh(uint32_t a) {  // fp16 at a 1-byte aligned 
     return half_bits_to_float((uint16_t) (ldu32(a) & 0xffffu));
 }
 
+// int -> float without the I2F instruction (quarter-rate XU pipe): byte j of `word` dropped into the mantissa of 2^23
+// gives the float 8388608 + byte exactly; one FADD / FFMA on the FP32 pipe removes the bias.
+constexpr float MAGIC = 8388608.0f;
+__device__ __forceinline__ float magic_u8(uint32_t word, int j) {
+    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7540u + j));
+}
+
 template <int T> struct Dq {
     // generic (slow) path: the bit-exact scalar decoder of blocks.cuh on a generic pointer
     static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
@@ -190,12 +222,12 @@ template <> struct Dq<T_Q8_0> {
         const uint32_t b = piece + b32 * 34;
         uint32_t       w[9];  // [d | q0 q1] ... [q30 q31 | next]
         ldu32_n<9>(b, w);
-        const float d = half_bits_to_float((uint16_t) (w[0] & 0xffffu));
+        const float d  = half_bits_to_float((uint16_t) (w[0] & 0xffffu));
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const uint32_t q = __funnelshift_r(w[i], w[i + 1], 16);
+            const uint32_t q = __funnelshift_r(w[i], w[i + 1], 16) ^ 0x80808080u;  // q + 128 per byte
 #pragma unroll
-            for (int j = 0; j < 4; ++j) v[4 * i + j] = d * (float) (int8_t) (q >> (8 * j));
+            for (int j = 0; j < 4; ++j) v[4 * i + j] = d * (magic_u8(q, j) - (MAGIC + 128.0f));
         }
     }
 };
@@ -205,22 +237,22 @@ template <> struct Dq<T_Q4_0> {
         uint32_t       w[5];  // [d | qs0 qs1] [qs2..5] [qs6..9] [qs10..13] [qs14 qs15 | next]
         ldu32_n<5>(b, w);
         const float d  = half_bits_to_float((uint16_t) (w[0] & 0xffffu));
-        const float m8 = -8.0f * d;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const uint32_t q = __funnelshift_r(w[i], w[i + 1], 16);
+            const uint32_t q  = __funnelshift_r(w[i], w[i + 1], 16);
+            const uint32_t lo = q & 0x0F0F0F0Fu, hi = (q >> 4) & 0x0F0F0F0Fu;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                v[4 * i + j]      = fmaf((float) ((q >> (8 * j)) & 0xF), d, m8);
-                v[16 + 4 * i + j] = fmaf((float) ((q >> (8 * j + 4)) & 0xF), d, m8);
+                v[4 * i + j]      = d * (magic_u8(lo, j) - (MAGIC + 8.0f));
+                v[16 + 4 * i + j] = d * (magic_u8(hi, j) - (MAGIC + 8.0f));
             }
         }
     }
 };
 template <> struct Dq<T_MXFP4> {
     static __device__ __forceinline__ float kv(uint32_t nib) {  // doubled E2M1 code point (ggml-common.h:1094-1096)
-        const uint32_t mag = __byte_perm(0x03020100u, 0x0C080604u, nib & 7u) & 0xFFu;
-        const float    f   = (float) mag;
+        const uint32_t mag = __byte_perm(0x03020100u, 0x0C080604u, nib & 7u);
+        const float    f   = magic_u8(mag, 0) - MAGIC;
         return (nib & 8u) ? -f : f;
     }
     static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
@@ -261,9 +293,9 @@ template <> struct Dq<T_Q4_K> {
         ldu32_n<8>(piece + 16 + 32 * (b32 >> 1), q);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const uint32_t w = q[i] >> sh;
+            const uint32_t w = (q[i] >> sh) & 0x0F0F0F0Fu;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) v[4 * i + j] = fmaf((float) ((w >> (8 * j)) & 0xF), dsc, dm);
+            for (int j = 0; j < 4; ++j) v[4 * i + j] = fmaf(magic_u8(w, j) - MAGIC, dsc, dm);
         }
     }
 };
@@ -283,7 +315,7 @@ template <> struct Dq<T_Q6_K> {
             const uint32_t q = ((ql[i] >> shl) & 0x0F0F0F0Fu) | (((qh[i] >> shh) & 0x03030303u) << 4);
             const float    s = i < 4 ? s0 : s1;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) v[4 * i + j] = s * (float) ((int) ((q >> (8 * j)) & 0xFF) - 32);
+            for (int j = 0; j < 4; ++j) v[4 * i + j] = s * (magic_u8(q, j) - (MAGIC + 32.0f));
         }
     }
 };
@@ -291,14 +323,26 @@ template <> struct Dq<T_Q6_K> {
 extern __shared__ __align__(1024) uint8_t mmq_smem_raw[];
 
 struct TileCoord {
-    int b, mt, nt;
+    int b, mt, nt, ns;  // batch, row tile, first column tile, column tiles in this super-tile (1 or 2)
+    int ws0, ws1;       // W stages [ws0, ws1) of the row pieces
+    int c0, c1;         // k-chunks [c0, c1)
 };
-__device__ __forceinline__ TileCoord tile_coord(const MmqParams & p, int t) {
+// work unit `t` of a cluster; CTA `rank` of the cluster takes row tile group * cluster + rank, which may lie past the
+// last row tile (a phantom tile: the CTA still feeds its share of B to its peers, its results are not stored)
+__device__ __forceinline__ TileCoord tile_coord(const MmqParams & p, int t, int rank) {
     TileCoord c;
-    c.nt           = t % p.n_tiles;
-    const int rest = t / p.n_tiles;
-    c.mt           = rest % p.m_tiles;
-    c.b            = rest / p.m_tiles;
+    const int ks   = t % p.ksplit;
+    t /= p.ksplit;
+    c.ws0          = ks * p.ws_per_split;
+    c.ws1          = min(p.w_stages_per_tile, c.ws0 + p.ws_per_split);
+    const int cps  = p.w_stage_k / CHUNK_K;
+    c.c0           = c.ws0 * cps;
+    c.c1           = min(p.k_chunks, c.ws1 * cps);
+    c.nt           = (t % p.n_super) * p.n_sub;
+    const int rest = t / p.n_super;
+    c.mt           = (rest % p.m_groups) * p.cluster + rank;
+    c.b            = rest / p.m_groups;
+    c.ns           = min(p.n_sub, p.n_tiles - c.nt);
     return c;
 }
 // bytes of the raw row piece of W stage `ws` (the last stage of a row may be ragged for 32-element block types)
@@ -316,7 +360,11 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
     volatile uint32_t * tmem_slot = (volatile uint32_t *) (sm + p.off_bar + BAR_COUNT * 8);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int num_tiles = p.nbatch * p.m_tiles * p.n_tiles;
+    const int  num_tiles = p.nbatch * p.m_groups * p.n_super * p.ksplit;  // work units of a cluster
+    const bool dual      = p.n_sub > 1;  // both accumulators belong to one super-tile (else: double-buffered tiles)
+    const int  crank     = p.cluster > 1 ? (int) cluster_ctarank() : 0;
+    const int  cid       = blockIdx.x / p.cluster, ncl = gridDim.x / p.cluster;
+    const uint16_t cmask = (uint16_t) ((1u << p.cluster) - 1u);
     if (threadIdx.x == 0) dbg_phase(p, 0);
 
     if (threadIdx.x == 0) {
@@ -324,10 +372,13 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
             mbar_init(bars + 8 * (BAR_W_FULL + s), N_WP_WARPS * 32);
             mbar_init(bars + 8 * (BAR_W_EMPTY + s), N_DQ_WARPS);
         }
-        for (int s = 0; s < AB_STAGES; ++s) {
+        for (int s = 0; s < A_STAGES; ++s) {
             mbar_init(bars + 8 * (BAR_A_FULL + s), N_DQ_WARPS / N_DQ_GROUPS);
+            mbar_init(bars + 8 * (BAR_A_EMPTY + s), 1);
+        }
+        for (int s = 0; s < p.b_stages; ++s) {
             mbar_init(bars + 8 * (BAR_B_FULL + s), 1);
-            mbar_init(bars + 8 * (BAR_AB_EMPTY + s), 1);
+            mbar_init(bars + 8 * (BAR_B_EMPTY + s), p.cluster);  // every CTA of the cluster releases every copy
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(bars + 8 * (BAR_ACC_FULL + s), 1);
@@ -340,6 +391,7 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
     }
     tc_fence_before();
     __syncthreads();
+    if (p.cluster > 1) cluster_sync();  // peers' barriers are initialised before anything is multicast to them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     if (threadIdx.x == 0) dbg_phase(p, 1);
@@ -353,11 +405,11 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
         const int l16 = lane & 15, hf = lane >> 4;
         const int cpr = p.w_pitch >> 4;  // 16-byte chunks copied per row (the whole pitch; over-read stays inside the tensor + pad)
         int wsi = 0;
-        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-            const TileCoord tc  = tile_coord(p, t);
+        for (int t = cid; t < num_tiles; t += ncl) {
+            const TileCoord tc  = tile_coord(p, t, crank);
             const int       i13 = tc.b / p.ne12, i12 = tc.b - i13 * p.ne12;
             const uint8_t * wb  = p.w + (long long) (i12 / p.r2) * p.w_nb2 + (long long) (i13 / p.r3) * p.w_nb3;
-            for (int ws = 0; ws < p.w_stages_per_tile; ++ws, ++wsi) {
+            for (int ws = tc.ws0; ws < tc.ws1; ++ws, ++wsi) {
                 const int slot = wsi % p.w_stages;
                 mbar_wait(bars + 8 * (BAR_W_EMPTY + slot), ((wsi / p.w_stages) & 1) ^ 1);
                 const uint32_t sbase = base + p.off_w + (uint32_t) slot * p.w_stage_bytes + 16u * l16;
@@ -379,22 +431,45 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
         if (!(p.dbg_flags & 128))
         // ------------------------------------------------------------------ packed activation tiles -> B ring
         if (lane == 0) {
-            int g = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-                const TileCoord tc    = tile_coord(p, t);
-                const int       ncols = min(TILE_N, p.n - tc.nt * TILE_N);
-                const uint32_t  bytes = (uint32_t) ((ncols + 15) & ~15) * 128u;
-                const uint8_t * src   = p.actp + ((long long) (tc.b * p.n_tiles + tc.nt) * p.k_chunks) * B_STAGE_BYTES;
-                for (int c = 0; c < p.k_chunks; ++c, ++g) {
-                    const int slot = g % AB_STAGES;
-                    mbar_wait(bars + 8 * (BAR_AB_EMPTY + slot), ((g / AB_STAGES) & 1) ^ 1);
-                    const uint32_t full = bars + 8 * (BAR_B_FULL + slot);
-                    dbg_stamp(p, g, 7);
-                    if ((p.dbg_flags & 4) && g >= AB_STAGES) {
-                        mbar_arrive(full);
-                    } else {
-                        mbar_expect_tx(full, bytes);
-                        bulk_g2s(base + p.off_b + (uint32_t) slot * B_STAGE_BYTES, src + (long long) c * B_STAGE_BYTES, bytes, full);
+            // (one thread: keep the per-stage instruction count small — ring slot / phase are running counters, the source
+            // pointers advance by one stage per chunk; runtime div/mod here cost more than the copy they issue)
+            int      slot = 0, issued = 0;
+            uint32_t ph   = 0;
+            for (int t = cid; t < num_tiles; t += ncl) {
+                const TileCoord tc = tile_coord(p, t, crank);
+                const uint8_t * src[2];
+                uint32_t        bytes[2];
+                for (int sn = 0; sn < 2; ++sn) {
+                    const int nt    = min(tc.nt + sn, p.n_tiles - 1);
+                    const int ncols = min(TILE_N, p.n - nt * TILE_N);
+                    bytes[sn]       = (uint32_t) ((ncols + 15) & ~15) * 128u;
+                    src[sn]         = p.actp + ((long long) (tc.b * p.n_tiles + nt) * p.k_chunks + tc.c0) * B_STAGE_BYTES;
+                    if (p.cluster > 1) {  // this CTA fetches 1/cluster of every chunk and multicasts it to its peers
+                        bytes[sn] /= (uint32_t) p.cluster;  // a multiple of 2048 before: the slices stay 16-byte multiples
+                        src[sn] += bytes[sn] * (uint32_t) crank;
+                    }
+                }
+                for (int c = tc.c0; c < tc.c1; ++c) {
+                    for (int sn = 0; sn < tc.ns; ++sn) {
+                        mbar_wait(bars + 8 * (BAR_B_EMPTY + slot), ph ^ 1);
+                        if (sn == 0) dbg_stamp(p, c, 7);
+                        const uint32_t full = bars + 8 * (BAR_B_FULL + slot);
+                        const uint32_t dst  = base + p.off_b + (uint32_t) slot * B_STAGE_BYTES;
+                        if ((p.dbg_flags & 4) && issued >= p.b_stages) {
+                            mbar_arrive(full);
+                        } else if (p.cluster == 1) {
+                            mbar_expect_tx(full, bytes[sn]);
+                            bulk_g2s(dst, src[sn], bytes[sn], full);
+                        } else {
+                            mbar_expect_tx(full, bytes[sn] * (uint32_t) p.cluster);
+                            bulk_g2s_multicast(dst + bytes[sn] * (uint32_t) crank, src[sn], bytes[sn], full, cmask);
+                        }
+                        src[sn] += B_STAGE_BYTES;
+                        ++issued;
+                        if (++slot == p.b_stages) {
+                            slot = 0;
+                            ph ^= 1;
+                        }
                     }
                 }
             }
@@ -402,36 +477,54 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
     } else if (warp == WARP_MMA) {
         // ------------------------------------------------------------------ tensor-core issue (one thread)
         if (lane == 0) {
-            int g = 0, ti = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++ti) {
-                const TileCoord tc    = tile_coord(p, t);
-                const int       ncols = min(TILE_N, p.n - tc.nt * TILE_N);
-                const uint32_t  idesc = umma_idesc_bf16_f32(TILE_M, (ncols + 15) & ~15);
-                const int       ab    = ti & 1;
-                mbar_wait(bars + 8 * (BAR_ACC_EMPTY + ab), ((ti >> 1) & 1) ^ 1);
-                tc_fence_after();
-                const uint32_t d_tmem = tmem_base + (uint32_t) ab * TILE_N;
-                for (int c = 0; c < p.k_chunks; ++c, ++g) {
-                    const int      slot = g % AB_STAGES;
-                    const uint32_t ph   = (g / AB_STAGES) & 1;
-                    dbg_stamp(p, g, 0);
-                    mbar_wait(bars + 8 * (BAR_A_FULL + slot), ph);
-                    dbg_stamp(p, g, 1);
-                    if (!(p.dbg_flags & 128)) mbar_wait(bars + 8 * (BAR_B_FULL + slot), ph);
-                    dbg_stamp(p, g, 2);
-                    tc_fence_after();
-                    const uint64_t adesc = umma_desc_k_sw128(base + (uint32_t) slot * A_STAGE_BYTES);
-                    const uint64_t bdesc = umma_desc_k_sw128(base + p.off_b + (uint32_t) slot * B_STAGE_BYTES);
-                    if (!(p.dbg_flags & 32))
-#pragma unroll
-                    for (int kk = 0; kk < CHUNK_K / 16; ++kk) {
-                        // +32 bytes (16 bf16) along K inside the 128-byte swizzle atom = +2 in the address field
-                        umma_f16(d_tmem, adesc + 2 * kk, bdesc + 2 * kk, idesc, (c | kk) != 0);
-                    }
-                    umma_commit(bars + 8 * (BAR_AB_EMPTY + slot));
-                    dbg_stamp(p, g, 3);
+            int      g = 0, ti = 0, aslot = 0, bslot = 0;
+            uint32_t a_ph = 0, b_ph = 0;
+            for (int t = cid; t < num_tiles; t += ncl, ++ti) {
+                const TileCoord tc  = tile_coord(p, t, crank);
+                const int       abi = dual ? 0 : (ti & 1);              // accumulator barrier pair
+                const uint32_t  aph = dual ? (ti & 1) : ((ti >> 1) & 1);
+                uint32_t idesc[2], d_tmem[2];
+                for (int sn = 0; sn < 2; ++sn) {
+                    const int ncols = min(TILE_N, p.n - (tc.nt + sn) * TILE_N);
+                    idesc[sn]  = umma_idesc_bf16_f32(TILE_M, (max(ncols, 1) + 15) & ~15);
+                    d_tmem[sn] = tmem_base + (uint32_t) (dual ? sn : abi) * TILE_N;
                 }
-                umma_commit(bars + 8 * (BAR_ACC_FULL + ab));
+                mbar_wait(bars + 8 * (BAR_ACC_EMPTY + abi), aph ^ 1);
+                tc_fence_after();
+                for (int c = tc.c0; c < tc.c1; ++c, ++g) {
+                    dbg_stamp(p, g, 0);
+                    mbar_wait(bars + 8 * (BAR_A_FULL + aslot), a_ph);
+                    dbg_stamp(p, g, 1);
+                    const uint64_t adesc = umma_desc_k_sw128(base + (uint32_t) aslot * A_STAGE_BYTES);
+                    for (int sn = 0; sn < tc.ns; ++sn) {
+                        if (!(p.dbg_flags & 128)) mbar_wait(bars + 8 * (BAR_B_FULL + bslot), b_ph);
+                        if (p.dbg_flags & 512) dbg_stamp(p, g, sn == 0 ? 4 : 6);
+                        // no tcgen05.fence here: operands arrive through shared memory (mbarrier-ordered); the fence is
+                        // only needed around TMEM hand-offs (accumulator release above)
+                        const uint64_t bdesc = umma_desc_k_sw128(base + p.off_b + (uint32_t) bslot * B_STAGE_BYTES);
+                        if (!(p.dbg_flags & 32))
+#pragma unroll
+                        for (int kk = 0; kk < CHUNK_K / 16; ++kk) {
+                            // +32 bytes (16 bf16) along K inside the 128-byte swizzle atom = +2 in the address field
+                            umma_f16(d_tmem[sn], adesc + 2 * kk, bdesc + 2 * kk, idesc[sn], c != tc.c0 || kk != 0);
+                        }
+                        if (p.cluster == 1) umma_commit(bars + 8 * (BAR_B_EMPTY + bslot));
+                        else umma_commit_multicast(bars + 8 * (BAR_B_EMPTY + bslot), cmask);
+                        if ((p.dbg_flags & 512) && sn == 0) dbg_stamp(p, g, 5);
+                        if (++bslot == p.b_stages) {
+                            bslot = 0;
+                            b_ph ^= 1;
+                        }
+                    }
+                    dbg_stamp(p, g, 2);
+                    umma_commit(bars + 8 * (BAR_A_EMPTY + aslot));
+                    dbg_stamp(p, g, 3);
+                    if (++aslot == A_STAGES) {
+                        aslot = 0;
+                        a_ph ^= 1;
+                    }
+                }
+                umma_commit(bars + 8 * (BAR_ACC_FULL + abi));
                 dbg_phase(p, 2);
             }
         }
@@ -443,33 +536,33 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
         const uint32_t a_row_off = (uint32_t) row * 128u;
         const uint32_t sw        = (uint32_t) (row & 7);
         int wsi = 0, g = 0;
-        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-            const TileCoord tc  = tile_coord(p, t);
+        for (int t = cid; t < num_tiles; t += ncl) {
+            const TileCoord tc  = tile_coord(p, t, crank);
             const int       i13 = tc.b / p.ne12, i12 = tc.b - i13 * p.ne12;
             const uint8_t * wb  = p.w + (long long) (i12 / p.r2) * p.w_nb2 + (long long) (i13 / p.r3) * p.w_nb3;
             const int       grow = min(tc.mt * TILE_M + row, p.m - 1);
             const uint8_t * rowp = wb + (long long) grow * p.w_nb1;
-            for (int ws = 0; ws < p.w_stages_per_tile; ++ws, ++wsi) {
+            for (int ws = tc.ws0; ws < tc.ws1; ++ws, ++wsi) {
                 const int wslot = wsi % p.w_stages;
                 if (!(p.dbg_flags & 64)) mbar_wait(bars + 8 * (BAR_W_FULL + wslot), (wsi / p.w_stages) & 1);
                 const uint32_t  lead  = (uint32_t) ((uintptr_t) (rowp + (long long) ws * p.piece_bytes) & 15);
                 const uint32_t  piece = base + p.off_w + (uint32_t) wslot * p.w_stage_bytes + (uint32_t) row * p.w_pitch + lead;
                 const int cps     = p.w_stage_k / CHUNK_K;
-                const int nchunks = min(cps, p.k_chunks - ws * cps);
+                const int nchunks = min(cps, tc.c1 - ws * cps);
                 for (int c = 0; c < nchunks; ++c, ++g) {
                     if ((g & (N_DQ_GROUPS - 1)) != grp) continue;
-                    const int slot = g % AB_STAGES;
+                    const int slot = g % A_STAGES;
                     float v[32];
-                    if (dt == 0) dbg_stamp(p, g, 4);
+                    if (dt == 0 && !(p.dbg_flags & 512)) dbg_stamp(p, g, 4);
                     if (p.dbg_flags & 2) {
 #pragma unroll
                         for (int i = 0; i < 32; ++i) v[i] = (float) (i + row);
                     } else {
                         Dq<T>::run(piece, 2 * c + half, v);
                     }
-                    if (dt == 0) dbg_stamp(p, g, 5);
-                    mbar_wait(bars + 8 * (BAR_AB_EMPTY + slot), ((g / AB_STAGES) & 1) ^ 1);
-                    if (dt == 0) dbg_stamp(p, g, 6);
+                    if (dt == 0 && !(p.dbg_flags & 512)) dbg_stamp(p, g, 5);
+                    mbar_wait(bars + 8 * (BAR_A_EMPTY + slot), ((g / A_STAGES) & 1) ^ 1);
+                    if (dt == 0 && !(p.dbg_flags & 512)) dbg_stamp(p, g, 6);
                     uint8_t * arow = sm + (uint32_t) slot * A_STAGE_BYTES + a_row_off;
                     if (!(p.dbg_flags & 8))
 #pragma unroll
@@ -493,33 +586,43 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
     } else {
         // ------------------------------------------------------------------ epilogue: TMEM -> dst
         int ti = 0;
-        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++ti) {
-            const TileCoord tc  = tile_coord(p, t);
+        for (int t = cid; t < num_tiles; t += ncl, ++ti) {
+            const TileCoord tc  = tile_coord(p, t, crank);
             const int       i13 = tc.b / p.ne12, i12 = tc.b - i13 * p.ne12;
-            const int       ab  = ti & 1;
+            const int       ab  = dual ? 0 : (ti & 1);
+            const uint32_t  aph = dual ? (ti & 1) : ((ti >> 1) & 1);
             const int       row = tc.mt * TILE_M + warp * 32 + lane;
-            const int       n0  = tc.nt * TILE_N;
-            const int       ncols = min(TILE_N, p.n - n0);
             char * dbase = (char *) p.dst + (long long) i12 * p.d_nb2 + (long long) i13 * p.d_nb3 + (long long) row * 4;
-            mbar_wait(bars + 8 * (BAR_ACC_FULL + ab), (ti >> 1) & 1);
+            mbar_wait(bars + 8 * (BAR_ACC_FULL + ab), aph);
             tc_fence_after();
             if (threadIdx.x == 0) dbg_phase(p, 3);
-            for (int c0 = 0; c0 < ncols; c0 += 32) {
-                float v[32];
-                tmem_ld32(tmem_base + ((uint32_t) (warp * 32) << 16) + (uint32_t) (ab * TILE_N + c0), v);
-                if (row < p.m) {
-                    char * dp = dbase + (long long) (n0 + c0) * p.d_nb1;  // one coalesced 128-byte warp store per column
-                    if (c0 + 32 <= ncols) {
+            for (int sn = 0; sn < tc.ns; ++sn) {
+                const int n0    = (tc.nt + sn) * TILE_N;
+                const int ncols = min(TILE_N, p.n - n0);
+                const int acol  = (dual ? sn : ab) * TILE_N;
+                for (int c0 = 0; c0 < ncols; c0 += 32) {
+                    float v[32];
+                    tmem_ld32(tmem_base + ((uint32_t) (warp * 32) << 16) + (uint32_t) (acol + c0), v);
+                    if (row < p.m) {
+                        char * dp = dbase + (long long) (n0 + c0) * p.d_nb1;  // one coalesced 128-byte warp store per column
+                        if (p.ksplit > 1) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            *(float *) dp = v[j];
-                            dp += p.d_nb1;
-                        }
-                    } else {
+                            for (int j = 0; j < 32; ++j) {
+                                if (c0 + j < ncols) atomicAdd((float *) dp, v[j]);  // RED.ADD.F32 (result unused)
+                                dp += p.d_nb1;
+                            }
+                        } else if (c0 + 32 <= ncols) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            if (c0 + j < ncols) *(float *) dp = v[j];
-                            dp += p.d_nb1;
+                            for (int j = 0; j < 32; ++j) {
+                                *(float *) dp = v[j];
+                                dp += p.d_nb1;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                if (c0 + j < ncols) *(float *) dp = v[j];
+                                dp += p.d_nb1;
+                            }
                         }
                     }
                 }
@@ -533,6 +636,7 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
 
     tc_fence_before();
     __syncthreads();
+    if (p.cluster > 1) cluster_sync();  // no CTA leaves while a peer may still multicast into it / arrive on its barriers
     if (threadIdx.x == 0) dbg_phase(p, 5);
     if (warp == WARP_MMA) {
         tmem_dealloc(tmem_base, TMEM_COLS);
@@ -591,11 +695,6 @@ int mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, st
     pp.k_chunks = (int) (a.k / CHUNK_K);
     pp.a_nb1 = a.a_nb1; pp.a_nb2 = a.a_nb2; pp.a_nb3 = a.a_nb3;
     pp.vec4  = ((uintptr_t) a.act & 15) == 0 && (a.a_nb1 & 15) == 0 && (a.a_nb2 & 15) == 0 && (a.a_nb3 & 15) == 0;
-    {
-        const long long total = (long long) nbatch * pp.n_tiles * pp.k_chunks * TILE_N * 8;
-        const int       grid  = (int) std::min<long long>((total + 255) / 256, (long long) sms * 8);
-        mmq_pack_act<<<grid, 256, 0, st>>>(pp);
-    }
 
     MmqParams p{};
     p.w = a.w; p.actp = (const uint8_t *) workspace; p.dst = a.dst;
@@ -612,12 +711,37 @@ int mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, st
     p.piece_bytes   = p.w_stage_k / be * bb;
     p.blk_bytes     = be == 32 ? bb : 0;
     p.w_pitch       = round_up_i(p.piece_bytes + 15 + 4, 16);  // lead <= 15 bytes + one word of funnel-shift over-read
+    if (!((p.w_pitch >> 4) & 1)) p.w_pitch += 16;              // odd multiple of 16: rows spread over the banks
     p.w_stage_bytes = TILE_M * p.w_pitch;
-    p.off_b   = AB_STAGES * A_STAGE_BYTES;
-    p.off_w   = p.off_b + AB_STAGES * B_STAGE_BYTES;
+    // unit shape: two accumulators share each dequantized chunk (n_sub = 2) when that still leaves a unit for most SMs;
+    // otherwise one accumulator per unit, and the k range is halved (ksplit = 2) if even that underfills the GPU
+    static const int force_sub = getenv("B200Q_MMQ_NSUB") ? atoi(getenv("B200Q_MMQ_NSUB")) : 0;
+    static const int force_ks  = getenv("B200Q_MMQ_KSPLIT") ? atoi(getenv("B200Q_MMQ_KSPLIT")) : 0;
+    static const int force_cl  = getenv("B200Q_MMQ_CLUSTER") ? atoi(getenv("B200Q_MMQ_CLUSTER")) : 0;
     {
+        const long long fill       = (long long) sms * 6 / 10;
+        const long long units_dual = (long long) nbatch * p.m_tiles * ((p.n_tiles + 1) / 2);
+        const long long units_one  = (long long) nbatch * p.m_tiles * p.n_tiles;
+        p.n_sub  = p.n_tiles > 1 && units_dual >= fill ? 2 : 1;
+        p.ksplit = p.n_sub == 1 && units_one < fill && p.w_stages_per_tile >= 4 ? 2 : 1;
+        if (force_sub) p.n_sub = p.n_tiles > 1 ? std::min(force_sub, 2) : 1;
+        if (force_ks) p.ksplit = p.w_stages_per_tile >= 2 ? std::min(force_ks, 2) : 1;
+    }
+    p.ws_per_split = (p.w_stages_per_tile + p.ksplit - 1) / p.ksplit;
+    p.n_super = (p.n_tiles + p.n_sub - 1) / p.n_sub;
+    p.cluster = force_cl ? force_cl : 1;  // multicast of the B chunks measured no gain (L2 already dedups the reads)
+    while (p.cluster > 1 && sms / p.cluster < 1) p.cluster >>= 1;
+    p.m_groups = (p.m_tiles + p.cluster - 1) / p.cluster;
+    p.off_b   = A_STAGES * A_STAGE_BYTES;
+    for (p.b_stages = MAX_B_STAGES;; --p.b_stages) {
+        p.off_w         = p.off_b + p.b_stages * B_STAGE_BYTES;
         const int avail = 227 * 1024 - 1024 - (int) p.off_w - BAR_COUNT * 8 - 16;
-        p.w_stages      = std::max(2, std::min(MAX_W_STAGES, avail / p.w_stage_bytes));
+        p.w_stages      = std::min(MAX_W_STAGES, avail / p.w_stage_bytes);
+        if (p.w_stages >= 2 || p.b_stages == 2) break;
+    }
+    if (p.w_stages < 2) {
+        err = "mmq: W ring does not fit in shared memory";
+        return B200Q_ENOTSUP;
     }
     p.off_bar = p.off_w + p.w_stages * p.w_stage_bytes;
     p.dbg = g_mmq_dbg;
@@ -642,10 +766,57 @@ int mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, st
             done.insert({ dev, (const void *) fn });
         }
     }
-    const int num_tiles = nbatch * p.m_tiles * p.n_tiles;
-    const int grid      = std::min(num_tiles, sms);
-    fn<<<grid, NTHREADS, smem, st>>>(p);
-    cudaError_t e = cudaGetLastError();
+    const int num_units = nbatch * p.m_groups * p.n_super * p.ksplit;
+    cudaLaunchConfig_t cfg{};
+    cfg.blockDim         = dim3(NTHREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream           = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id               = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = p.cluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs                = attr;
+    cfg.numAttrs             = 1;
+    // persistent grid = the clusters that are co-resident (a GPC whose SM count is not a multiple of the cluster size
+    // leaves SMs out, so this can be less than sms / cluster)
+    int max_clusters = sms / p.cluster;
+    {
+        static std::map<std::tuple<int, const void *, int, int>, int> cache;
+        int dev = 0;
+        cudaGetDevice(&dev);
+        std::lock_guard<std::mutex> lk(mu);
+        auto key = std::make_tuple(dev, (const void *) fn, p.cluster, smem);
+        auto it  = cache.find(key);
+        if (it == cache.end()) {
+            int n = 0;
+            cfg.gridDim = dim3(sms / p.cluster * p.cluster);
+            if (cudaOccupancyMaxActiveClusters(&n, fn, &cfg) != cudaSuccess || n < 1) {
+                cudaGetLastError();
+                n = max_clusters;
+            }
+            it = cache.emplace(key, n).first;
+        }
+        max_clusters = std::min(max_clusters, it->second);
+    }
+    const int grid = std::min(num_units, max_clusters) * p.cluster;
+    cfg.gridDim    = dim3(grid);
+    static const bool debug = getenv("B200Q_DEBUG") != nullptr;
+    if (debug) {
+        fprintf(stderr, "[b200q] mmq type=%d m=%d n=%d k=%d cluster=%d n_sub=%d ksplit=%d units=%d grid=%d w_stages=%d b_stages=%d pitch=%d\n",
+                a.type, p.m, p.n, p.k, p.cluster, p.n_sub, p.ksplit, num_units, grid, p.w_stages, p.b_stages, p.w_pitch);
+    }
+    {
+        if (p.ksplit > 1) {
+            pp.zero_dst = a.dst; pp.m = (int) a.m;
+            pp.d_nb1 = a.d_nb1; pp.d_nb2 = a.d_nb2; pp.d_nb3 = a.d_nb3;
+        }
+        const long long total = (long long) nbatch * pp.n_tiles * pp.k_chunks * TILE_N * 8;
+        const int       pgrid = (int) std::min<long long>((total + 255) / 256, (long long) sms * 8);
+        mmq_pack_act<<<pgrid, 256, 0, st>>>(pp);
+    }
+    cudaError_t e = cudaLaunchKernelEx(&cfg, fn, p);
+    if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) {
         err = std::string("mmq: launch failed: ") + cudaGetErrorString(e);
         return B200Q_ECUDA;

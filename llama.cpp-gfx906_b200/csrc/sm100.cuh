@@ -52,6 +52,23 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void * src_gme
                  "l"(src_gmem), "r"(bytes), "r"(bar)
                  : "memory");
 }
+// the same copy delivered to the same shared-memory offset (and the same barrier offset) of every CTA in `cta_mask`
+__device__ __forceinline__ void bulk_g2s_multicast(uint32_t dst_smem, const void * src_gmem, uint32_t bytes, uint32_t bar,
+                                                   uint16_t cta_mask) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;" ::
+            "r"(dst_smem),
+        "l"(src_gmem), "r"(bytes), "r"(bar), "h"(cta_mask)
+        : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void bulk_g2s_hint(uint32_t dst_smem, const void * src_gmem, uint32_t bytes, uint32_t bar,
                                               uint64_t policy) {
     asm volatile(
@@ -103,6 +120,12 @@ __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64
 // arrive on `bar` when all tcgen05.mma issued so far by this thread have completed (implies fence::before_thread_sync)
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// the same arrive on the barrier at this offset in every CTA of `cta_mask`
+__device__ __forceinline__ void umma_commit_multicast(uint32_t bar, uint16_t cta_mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+                 "h"(cta_mask)
+                 : "memory");
 }
 // 32 consecutive fp32 columns of this thread's TMEM lane (warp w of a warpgroup owns lanes 32*(w%4) .. +31)
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {

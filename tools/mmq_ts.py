@@ -22,9 +22,9 @@ T = buf.cpu().numpy().reshape(256, 8)
 t0 = T[0, 0]
 ph = T[255]
 print("phases (ns from kernel begin): setup done %d, mma last commit %d, acc ready seen by epilogue %d, epilogue done %d, all warps done %d" % tuple(int(ph[i] - ph[0]) for i in range(1, 6)))
-names = ["mma:wait", "mma:A ok", "mma:B ok", "mma:issued", "dq:start", "dq:done", "dq:slot free", "B:request"]
+names = ["mma:wait", "mma:A ok", "mma:issued", "mma:commit", "dq:start", "dq:done", "dq:slot free", "B:slot free"]
 print("chunk " + " ".join(f"{x:>12s}" for x in names))
-for g in list(range(0, 24)) + list(range(60, 72)):
+for g in list(range(0, 20)) + list(range(56, 64)):
     print(f"{g:5d} " + " ".join(f"{int(T[g, j] - t0):12d}" for j in range(8)))
-d = np.diff(T[8:120, 3])
-print("cycles per chunk (MMA issue to issue), chunks 8..120: median", np.median(d), "mean", d.mean())
+d = np.diff(T[8:60, 3])
+print("cycles per chunk (MMA issue to issue), chunks 8..60: median", np.median(d), "mean", d.mean())
