@@ -430,8 +430,8 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
     } else if (warp == WARP_BPROD) {
         if (!(p.dbg_flags & 128))
         // ------------------------------------------------------------------ packed activation tiles -> B ring
-        if (lane == 0) {
-            // (one thread: keep the per-stage instruction count small — ring slot / phase are running counters, the source
+        {
+            // (the whole warp runs the loop, one elected lane issues: keep the per-stage instruction count small — ring slot / phase are running counters, the source
             // pointers advance by one stage per chunk; runtime div/mod here cost more than the copy they issue)
             int      slot = 0, issued = 0;
             uint32_t ph   = 0;
@@ -452,18 +452,21 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
                 for (int c = tc.c0; c < tc.c1; ++c) {
                     for (int sn = 0; sn < tc.ns; ++sn) {
                         mbar_wait(bars + 8 * (BAR_B_EMPTY + slot), ph ^ 1);
-                        if (sn == 0) dbg_stamp(p, c, 7);
                         const uint32_t full = bars + 8 * (BAR_B_FULL + slot);
                         const uint32_t dst  = base + p.off_b + (uint32_t) slot * B_STAGE_BYTES;
-                        if ((p.dbg_flags & 4) && issued >= p.b_stages) {
-                            mbar_arrive(full);
-                        } else if (p.cluster == 1) {
-                            mbar_expect_tx(full, bytes[sn]);
-                            bulk_g2s(dst, src[sn], bytes[sn], full);
-                        } else {
-                            mbar_expect_tx(full, bytes[sn] * (uint32_t) p.cluster);
-                            bulk_g2s_multicast(dst + bytes[sn] * (uint32_t) crank, src[sn], bytes[sn], full, cmask);
+                        if (elect_one()) {
+                            if (sn == 0) dbg_stamp(p, c, 7);
+                            if ((p.dbg_flags & 4) && issued >= p.b_stages) {
+                                mbar_arrive(full);
+                            } else if (p.cluster == 1) {
+                                mbar_expect_tx(full, bytes[sn]);
+                                bulk_g2s(dst, src[sn], bytes[sn], full);
+                            } else {
+                                mbar_expect_tx(full, bytes[sn] * (uint32_t) p.cluster);
+                                bulk_g2s_multicast(dst + bytes[sn] * (uint32_t) crank, src[sn], bytes[sn], full, cmask);
+                            }
                         }
+                        __syncwarp();
                         src[sn] += B_STAGE_BYTES;
                         ++issued;
                         if (++slot == p.b_stages) {
@@ -475,8 +478,8 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
             }
         }
     } else if (warp == WARP_MMA) {
-        // ------------------------------------------------------------------ tensor-core issue (one thread)
-        if (lane == 0) {
+        // ------------------------------------------------------------------ tensor-core issue (whole warp loops, one lane issues)
+        {
             int      g = 0, ti = 0, aslot = 0, bslot = 0;
             uint32_t a_ph = 0, b_ph = 0;
             for (int t = cid; t < num_tiles; t += ncl, ++ti) {
@@ -492,40 +495,42 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
                 mbar_wait(bars + 8 * (BAR_ACC_EMPTY + abi), aph ^ 1);
                 tc_fence_after();
                 for (int c = tc.c0; c < tc.c1; ++c, ++g) {
-                    dbg_stamp(p, g, 0);
+                    if (lane == 0) dbg_stamp(p, g, 0);
                     mbar_wait(bars + 8 * (BAR_A_FULL + aslot), a_ph);
-                    dbg_stamp(p, g, 1);
+                    if (lane == 0) dbg_stamp(p, g, 1);
                     const uint64_t adesc = umma_desc_k_sw128(base + (uint32_t) aslot * A_STAGE_BYTES);
                     for (int sn = 0; sn < tc.ns; ++sn) {
                         if (!(p.dbg_flags & 128)) mbar_wait(bars + 8 * (BAR_B_FULL + bslot), b_ph);
-                        if (p.dbg_flags & 512) dbg_stamp(p, g, sn == 0 ? 4 : 6);
+                        if ((p.dbg_flags & 512) && lane == 0) dbg_stamp(p, g, sn == 0 ? 4 : 6);
                         // no tcgen05.fence here: operands arrive through shared memory (mbarrier-ordered); the fence is
                         // only needed around TMEM hand-offs (accumulator release above)
                         const uint64_t bdesc = umma_desc_k_sw128(base + p.off_b + (uint32_t) bslot * B_STAGE_BYTES);
-                        if (!(p.dbg_flags & 32))
+                        if (elect_one()) {
+                            if (!(p.dbg_flags & 32))
 #pragma unroll
-                        for (int kk = 0; kk < CHUNK_K / 16; ++kk) {
-                            // +32 bytes (16 bf16) along K inside the 128-byte swizzle atom = +2 in the address field
-                            umma_f16(d_tmem[sn], adesc + 2 * kk, bdesc + 2 * kk, idesc[sn], c != tc.c0 || kk != 0);
+                            for (int kk = 0; kk < CHUNK_K / 16; ++kk) {
+                                // +32 bytes (16 bf16) along K inside the 128-byte swizzle atom = +2 in the address field
+                                umma_f16(d_tmem[sn], adesc + 2 * kk, bdesc + 2 * kk, idesc[sn], c != tc.c0 || kk != 0);
+                            }
+                            if (p.cluster == 1) umma_commit(bars + 8 * (BAR_B_EMPTY + bslot));
+                            else umma_commit_multicast(bars + 8 * (BAR_B_EMPTY + bslot), cmask);
+                            if (sn == tc.ns - 1) umma_commit(bars + 8 * (BAR_A_EMPTY + aslot));  // after the chunk's last MMA
+                            if (sn == tc.ns - 1 && c == tc.c1 - 1) umma_commit(bars + 8 * (BAR_ACC_FULL + abi));
                         }
-                        if (p.cluster == 1) umma_commit(bars + 8 * (BAR_B_EMPTY + bslot));
-                        else umma_commit_multicast(bars + 8 * (BAR_B_EMPTY + bslot), cmask);
-                        if ((p.dbg_flags & 512) && sn == 0) dbg_stamp(p, g, 5);
+                        __syncwarp();
+                        if ((p.dbg_flags & 512) && sn == 0 && lane == 0) dbg_stamp(p, g, 5);
                         if (++bslot == p.b_stages) {
                             bslot = 0;
                             b_ph ^= 1;
                         }
                     }
-                    dbg_stamp(p, g, 2);
-                    umma_commit(bars + 8 * (BAR_A_EMPTY + aslot));
-                    dbg_stamp(p, g, 3);
+                    if (lane == 0) dbg_stamp(p, g, 3);
                     if (++aslot == A_STAGES) {
                         aslot = 0;
                         a_ph ^= 1;
                     }
                 }
-                umma_commit(bars + 8 * (BAR_ACC_FULL + abi));
-                dbg_phase(p, 2);
+                if (lane == 0) dbg_phase(p, 2);
             }
         }
     } else if (warp >= WARP_DQ0) {

@@ -35,6 +35,31 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "memory");
 }
 
+// warp-wide wait with ONE polling lane (32 lanes spinning on try_wait multiply the traffic on the barrier unit that the
+// critical producer / issuer threads need); the other lanes take their own acquire with a single, immediate try_wait
+__device__ __forceinline__ void mbar_wait_warp(uint32_t bar, uint32_t parity) {
+    if ((threadIdx.x & 31) == 0) mbar_wait(bar, parity);
+    __syncwarp();
+    mbar_wait(bar, parity);
+}
+// long waits (e.g. the epilogue waiting for a whole tile): back off between polls
+__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity, unsigned ns) {
+    if ((threadIdx.x & 31) == 0) {
+        for (;;) {
+            uint32_t ok;
+            asm volatile(
+                "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                : "=r"(ok)
+                : "r"(bar), "r"(parity)
+                : "memory");
+            if (ok) break;
+            __nanosleep(ns);
+        }
+    }
+    __syncwarp();
+    mbar_wait(bar, parity);
+}
+
 // ---- bulk copy (TMA 1-D) ------------------------------------------------------------------------------------
 __device__ __forceinline__ uint64_t policy_evict_first() {
     uint64_t pol;
@@ -60,6 +85,13 @@ __device__ __forceinline__ void bulk_g2s_multicast(uint32_t dst_smem, const void
             "r"(dst_smem),
         "l"(src_gmem), "r"(bytes), "r"(bar), "h"(cta_mask)
         : "memory");
+}
+// one lane of a fully active warp (warp-uniform control flow around it keeps descriptors in uniform registers; code
+// under `if (lane == 0)` makes the compiler wrap every tcgen05 / bulk-copy instruction in an ELECT / R2UR.BROADCAST loop)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(pred));
+    return pred != 0;
 }
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
