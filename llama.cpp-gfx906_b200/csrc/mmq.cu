@@ -82,7 +82,8 @@ struct MmqParams {
     int   m_tiles, n_tiles, k_chunks, w_stages_per_tile;
     int   w_stage_k;     // k-elements of raw weights per W stage (128 for 32-element block types, 256 for K-quants)
     int   w_stages;      // W ring depth (2..MAX_W_STAGES, what fits in shared memory)
-    int   b_stages;      // B ring depth (3 or 4)
+    int   b_stages;      // B ring depth in stages of n_sub x 32 KB (the column tiles of one k-chunk travel as ONE stage)
+    int   b_stage_bytes; // n_sub * B_STAGE_BYTES
     int   n_super;       // column super-tiles per row tile: two 256-column accumulators share ONE dequantized A chunk
     int   n_sub;         // column tiles per super-tile (2, or 1 when there are too few tiles to fill the GPU otherwise)
     int   cluster;       // CTAs per cluster (1, 2 or 4): they take adjacent row tiles and share every B chunk by multicast
@@ -116,6 +117,7 @@ struct PackParams {
     int           m;
     long long     d_nb1, d_nb2, d_nb3;
     int   k, n, ne12, nbatch, n_tiles, k_chunks;
+    int   n_sub, n_super;  // blocks are ordered (batch, super-tile, k-chunk, column tile of the super-tile)
     long long a_nb1, a_nb2, a_nb3;
     int   vec4;
 };
@@ -135,17 +137,19 @@ __global__ void __launch_bounds__(256) mmq_pack_act(const PackParams p) {
         }
     }
     const long long chunks_per_block = TILE_N * 8;
-    const long long total = (long long) p.nbatch * p.n_tiles * p.k_chunks * chunks_per_block;
+    const long long total = (long long) p.nbatch * p.n_super * p.n_sub * p.k_chunks * chunks_per_block;
     for (long long idx = (long long) blockIdx.x * blockDim.x + threadIdx.x; idx < total;
          idx += (long long) gridDim.x * blockDim.x) {
         const int       c    = (int) (idx & 7);
         const int       j    = (int) ((idx >> 3) & (TILE_N - 1));
         const long long blk  = idx / chunks_per_block;
-        const int       kc   = (int) (blk % p.k_chunks);
-        const long long rest = blk / p.k_chunks;
-        const int       nt   = (int) (rest % p.n_tiles);
-        const int       b    = (int) (rest / p.n_tiles);
-        const int       col  = nt * TILE_N + j;
+        const int       sn   = (int) (blk % p.n_sub);
+        const long long r1   = blk / p.n_sub;
+        const int       kc   = (int) (r1 % p.k_chunks);
+        const long long rest = r1 / p.k_chunks;
+        const int       nt   = (int) (rest % p.n_super) * p.n_sub + sn;
+        const int       b    = (int) (rest / p.n_super);
+        const int       col  = nt * TILE_N + j;  // >= n for the padding tile of an odd tile count
         uint4           o    = make_uint4(0, 0, 0, 0);
         if (col < p.n) {
             const int     i13 = b / p.ne12, i12 = b - i13 * p.ne12;
@@ -431,48 +435,44 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
         if (!(p.dbg_flags & 128))
         // ------------------------------------------------------------------ packed activation tiles -> B ring
         {
-            // (the whole warp runs the loop, one elected lane issues: keep the per-stage instruction count small — ring slot / phase are running counters, the source
-            // pointers advance by one stage per chunk; runtime div/mod here cost more than the copy they issue)
+            // (the whole warp runs the loop, one elected lane issues; ring slot / phase are running counters and the source
+            // pointer advances by one stage per chunk: runtime div / mod here cost more than the copy they issue)
             int      slot = 0, issued = 0;
             uint32_t ph   = 0;
             for (int t = cid; t < num_tiles; t += ncl) {
                 const TileCoord tc = tile_coord(p, t, crank);
-                const uint8_t * src[2];
-                uint32_t        bytes[2];
-                for (int sn = 0; sn < 2; ++sn) {
-                    const int nt    = min(tc.nt + sn, p.n_tiles - 1);
-                    const int ncols = min(TILE_N, p.n - nt * TILE_N);
-                    bytes[sn]       = (uint32_t) ((ncols + 15) & ~15) * 128u;
-                    src[sn]         = p.actp + ((long long) (tc.b * p.n_tiles + nt) * p.k_chunks + tc.c0) * B_STAGE_BYTES;
-                    if (p.cluster > 1) {  // this CTA fetches 1/cluster of every chunk and multicasts it to its peers
-                        bytes[sn] /= (uint32_t) p.cluster;  // a multiple of 2048 before: the slices stay 16-byte multiples
-                        src[sn] += bytes[sn] * (uint32_t) crank;
-                    }
+                // the column tiles of one k-chunk are adjacent in the packed workspace: one copy per chunk
+                const int ncols_last = min(TILE_N, p.n - (tc.nt + tc.ns - 1) * TILE_N);
+                uint32_t  bytes      = (uint32_t) (tc.ns - 1) * B_STAGE_BYTES + (uint32_t) ((ncols_last + 15) & ~15) * 128u;
+                const uint8_t * src  = p.actp + (((long long) (tc.b * p.n_super + tc.nt / p.n_sub) * p.k_chunks + tc.c0) * p.n_sub) * B_STAGE_BYTES;
+                uint32_t doff = 0;
+                if (p.cluster > 1) {  // this CTA fetches 1/cluster of every chunk and multicasts it to its peers
+                    bytes /= (uint32_t) p.cluster;  // a multiple of 2048 before: the slices stay 16-byte multiples
+                    doff = bytes * (uint32_t) crank;
+                    src += doff;
                 }
                 for (int c = tc.c0; c < tc.c1; ++c) {
-                    for (int sn = 0; sn < tc.ns; ++sn) {
-                        mbar_wait(bars + 8 * (BAR_B_EMPTY + slot), ph ^ 1);
-                        const uint32_t full = bars + 8 * (BAR_B_FULL + slot);
-                        const uint32_t dst  = base + p.off_b + (uint32_t) slot * B_STAGE_BYTES;
-                        if (elect_one()) {
-                            if (sn == 0) dbg_stamp(p, c, 7);
-                            if ((p.dbg_flags & 4) && issued >= p.b_stages) {
-                                mbar_arrive(full);
-                            } else if (p.cluster == 1) {
-                                mbar_expect_tx(full, bytes[sn]);
-                                bulk_g2s(dst, src[sn], bytes[sn], full);
-                            } else {
-                                mbar_expect_tx(full, bytes[sn] * (uint32_t) p.cluster);
-                                bulk_g2s_multicast(dst + bytes[sn] * (uint32_t) crank, src[sn], bytes[sn], full, cmask);
-                            }
+                    mbar_wait(bars + 8 * (BAR_B_EMPTY + slot), ph ^ 1);
+                    const uint32_t full = bars + 8 * (BAR_B_FULL + slot);
+                    const uint32_t dst  = base + p.off_b + (uint32_t) slot * (uint32_t) p.b_stage_bytes + doff;
+                    if (elect_one()) {
+                        dbg_stamp(p, c, 7);
+                        if ((p.dbg_flags & 4) && issued >= p.b_stages) {
+                            mbar_arrive(full);
+                        } else if (p.cluster == 1) {
+                            mbar_expect_tx(full, bytes);
+                            bulk_g2s(dst, src, bytes, full);
+                        } else {
+                            mbar_expect_tx(full, bytes * (uint32_t) p.cluster);
+                            bulk_g2s_multicast(dst, src, bytes, full, cmask);
                         }
-                        __syncwarp();
-                        src[sn] += B_STAGE_BYTES;
-                        ++issued;
-                        if (++slot == p.b_stages) {
-                            slot = 0;
-                            ph ^= 1;
-                        }
+                    }
+                    __syncwarp();
+                    src += p.b_stage_bytes;
+                    ++issued;
+                    if (++slot == p.b_stages) {
+                        slot = 0;
+                        ph ^= 1;
                     }
                 }
             }
@@ -498,33 +498,37 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
                     if (lane == 0) dbg_stamp(p, g, 0);
                     mbar_wait(bars + 8 * (BAR_A_FULL + aslot), a_ph);
                     if (lane == 0) dbg_stamp(p, g, 1);
+                    if (!(p.dbg_flags & 128)) mbar_wait(bars + 8 * (BAR_B_FULL + bslot), b_ph);
+                    // no tcgen05.fence here: operands arrive through shared memory (mbarrier-ordered); the fence is only
+                    // needed around TMEM hand-offs (accumulator release above)
                     const uint64_t adesc = umma_desc_k_sw128(base + (uint32_t) aslot * A_STAGE_BYTES);
-                    for (int sn = 0; sn < tc.ns; ++sn) {
-                        if (!(p.dbg_flags & 128)) mbar_wait(bars + 8 * (BAR_B_FULL + bslot), b_ph);
-                        if ((p.dbg_flags & 512) && lane == 0) dbg_stamp(p, g, sn == 0 ? 4 : 6);
-                        // no tcgen05.fence here: operands arrive through shared memory (mbarrier-ordered); the fence is
-                        // only needed around TMEM hand-offs (accumulator release above)
-                        const uint64_t bdesc = umma_desc_k_sw128(base + p.off_b + (uint32_t) bslot * B_STAGE_BYTES);
-                        if (elect_one()) {
-                            if (!(p.dbg_flags & 32))
+                    const uint64_t bdesc = umma_desc_k_sw128(base + p.off_b + (uint32_t) bslot * (uint32_t) p.b_stage_bytes);
+                    if (elect_one()) {
+                        if (!(p.dbg_flags & 32)) {
 #pragma unroll
-                            for (int kk = 0; kk < CHUNK_K / 16; ++kk) {
-                                // +32 bytes (16 bf16) along K inside the 128-byte swizzle atom = +2 in the address field
-                                umma_f16(d_tmem[sn], adesc + 2 * kk, bdesc + 2 * kk, idesc[sn], c != tc.c0 || kk != 0);
+                            for (int sn = 0; sn < 2; ++sn) {
+                                if (sn < tc.ns) {
+#pragma unroll
+                                    for (int kk = 0; kk < CHUNK_K / 16; ++kk) {
+                                        // +32 bytes (16 bf16) along K inside the 128-byte swizzle atom = +2 in the address
+                                        // field; the second column tile sits B_STAGE_BYTES further
+                                        umma_f16(d_tmem[sn], adesc + 2 * kk, bdesc + 2 * kk + sn * (B_STAGE_BYTES >> 4), idesc[sn],
+                                                 c != tc.c0 || kk != 0);
+                                    }
+                                }
                             }
-                            if (p.cluster == 1) umma_commit(bars + 8 * (BAR_B_EMPTY + bslot));
-                            else umma_commit_multicast(bars + 8 * (BAR_B_EMPTY + bslot), cmask);
-                            if (sn == tc.ns - 1) umma_commit(bars + 8 * (BAR_A_EMPTY + aslot));  // after the chunk's last MMA
-                            if (sn == tc.ns - 1 && c == tc.c1 - 1) umma_commit(bars + 8 * (BAR_ACC_FULL + abi));
                         }
-                        __syncwarp();
-                        if ((p.dbg_flags & 512) && sn == 0 && lane == 0) dbg_stamp(p, g, 5);
-                        if (++bslot == p.b_stages) {
-                            bslot = 0;
-                            b_ph ^= 1;
-                        }
+                        if (p.cluster == 1) umma_commit(bars + 8 * (BAR_B_EMPTY + bslot));
+                        else umma_commit_multicast(bars + 8 * (BAR_B_EMPTY + bslot), cmask);
+                        umma_commit(bars + 8 * (BAR_A_EMPTY + aslot));
+                        if (c == tc.c1 - 1) umma_commit(bars + 8 * (BAR_ACC_FULL + abi));
                     }
+                    __syncwarp();
                     if (lane == 0) dbg_stamp(p, g, 3);
+                    if (++bslot == p.b_stages) {
+                        bslot = 0;
+                        b_ph ^= 1;
+                    }
                     if (++aslot == A_STAGES) {
                         aslot = 0;
                         a_ph ^= 1;
@@ -678,7 +682,7 @@ bool mmq_supported(int type, int64_t k) {
 
 size_t mmq_workspace_bytes(int64_t k, int64_t n, int64_t nbatch) {
     const int64_t n_tiles = (n + TILE_N - 1) / TILE_N;
-    return (size_t) (nbatch * n_tiles * (k / CHUNK_K)) * B_STAGE_BYTES;
+    return (size_t) (nbatch * ((n_tiles + 1) / 2 * 2) * (k / CHUNK_K)) * B_STAGE_BYTES;  // room for the padding tile of a pair
 }
 
 int mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, std::string & err) {
@@ -732,18 +736,28 @@ int mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, st
         if (force_sub) p.n_sub = p.n_tiles > 1 ? std::min(force_sub, 2) : 1;
         if (force_ks) p.ksplit = p.w_stages_per_tile >= 2 ? std::min(force_ks, 2) : 1;
     }
+    p.off_b = A_STAGES * A_STAGE_BYTES;
+    auto fit_rings = [&](int n_sub) {  // B ring (stages of n_sub x 32 KB, at most 128 KB) + W ring in what is left
+        p.b_stage_bytes = n_sub * B_STAGE_BYTES;
+        for (int b32 = MAX_B_STAGES; b32 >= 2 * n_sub; b32 -= n_sub) {
+            p.b_stages      = b32 / n_sub;
+            p.off_w         = p.off_b + p.b_stages * p.b_stage_bytes;
+            const int avail = 227 * 1024 - 1024 - (int) p.off_w - BAR_COUNT * 8 - 16;
+            p.w_stages      = std::min(MAX_W_STAGES, avail / p.w_stage_bytes);
+            if (p.w_stages >= 2) return true;
+        }
+        return false;
+    };
+    if (!fit_rings(p.n_sub) && p.n_sub == 2) {  // wide raw rows (q6_K, q5_K): one accumulator per unit
+        p.n_sub = 1;
+        p.w_stages = 0;
+        fit_rings(1);
+    }
     p.ws_per_split = (p.w_stages_per_tile + p.ksplit - 1) / p.ksplit;
     p.n_super = (p.n_tiles + p.n_sub - 1) / p.n_sub;
     p.cluster = force_cl ? force_cl : 1;  // multicast of the B chunks measured no gain (L2 already dedups the reads)
     while (p.cluster > 1 && sms / p.cluster < 1) p.cluster >>= 1;
     p.m_groups = (p.m_tiles + p.cluster - 1) / p.cluster;
-    p.off_b   = A_STAGES * A_STAGE_BYTES;
-    for (p.b_stages = MAX_B_STAGES;; --p.b_stages) {
-        p.off_w         = p.off_b + p.b_stages * B_STAGE_BYTES;
-        const int avail = 227 * 1024 - 1024 - (int) p.off_w - BAR_COUNT * 8 - 16;
-        p.w_stages      = std::min(MAX_W_STAGES, avail / p.w_stage_bytes);
-        if (p.w_stages >= 2 || p.b_stages == 2) break;
-    }
     if (p.w_stages < 2) {
         err = "mmq: W ring does not fit in shared memory";
         return B200Q_ENOTSUP;
@@ -816,7 +830,8 @@ int mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, st
             pp.zero_dst = a.dst; pp.m = (int) a.m;
             pp.d_nb1 = a.d_nb1; pp.d_nb2 = a.d_nb2; pp.d_nb3 = a.d_nb3;
         }
-        const long long total = (long long) nbatch * pp.n_tiles * pp.k_chunks * TILE_N * 8;
+        pp.n_sub = p.n_sub; pp.n_super = p.n_super;
+        const long long total = (long long) nbatch * pp.n_super * pp.n_sub * pp.k_chunks * TILE_N * 8;
         const int       pgrid = (int) std::min<long long>((total + 255) / 256, (long long) sms * 8);
         mmq_pack_act<<<pgrid, 256, 0, st>>>(pp);
     }

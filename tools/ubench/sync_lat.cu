@@ -105,6 +105,31 @@ __global__ void __launch_bounds__(128, 1) k(long long * out, const uint8_t * src
         }
     }
     __syncthreads();
+    // (9) three commits back to back, nobody waiting (one thread), then the whole-warp elect pattern of the MMQ issuer
+    if (threadIdx.x == 0) {
+        long long t0 = clock64();
+        for (int i = 0; i < 64; ++i) {
+            umma_commit(bar1);
+            umma_commit(bar2);
+            umma_commit(bar0 + 80);
+        }
+        out[20] = (clock64() - t0) / 64;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        long long t0 = clock64();
+        for (int i = 0; i < 64; ++i) {
+            for (int sn = 0; sn < 2; ++sn) {
+                if (elect_one()) {
+                    umma_commit(bar1);
+                    if (sn == 1) umma_commit(bar2);
+                }
+                __syncwarp();
+            }
+        }
+        if (lane == 0) out[21] = (clock64() - t0) / 64;
+    }
+    __syncthreads();
     // (8) cross-warp ping-pong: warp 1 lane 0 <-> warp 2 lane 0 through two barriers (round trip)
     if (threadIdx.x == 32) {
         uint32_t ph = 0;
@@ -156,6 +181,7 @@ int main() {
     printf("bulk copy 32 KB + wait      %lld %lld %lld cycles\n", out[4], out[5], out[6]);
     printf("4 x bulk copy 32 KB + wait  %lld cycles\n", out[7]);
     printf("cross-warp round trip       %lld cycles\n", out[8]);
+    printf("3 commits, no waiter        %lld cycles per iteration (one thread), %lld (warp + elect)\n", out[20], out[21]);
     for (int r = 0; r < 4; ++r) printf("%2d MMAs 128x256x16 + commit: issue %lld, complete %lld cycles\n", 4 << r, out[10 + 2 * r], out[11 + 2 * r]);
     return 0;
 }
