@@ -45,6 +45,14 @@ namespace {
 
 using namespace sm100;
 
+// development aids (B200Q_MMQ_DBG knock-out flags, clock stamps) are compiled in only with -DB200Q_MMQ_DEVTOOLS=1: in the
+// one-warp issue loops every predicated-off instruction still costs issue slots
+#ifndef B200Q_MMQ_DEVTOOLS
+#define B200Q_MMQ_DEVTOOLS 0
+#endif
+constexpr bool DEV = B200Q_MMQ_DEVTOOLS != 0;
+#define DEVF (DEV ? p.dbg_flags : 0)
+
 constexpr int TILE_M  = 128;  // weight rows per tile (UMMA M)
 constexpr int TILE_N  = 256;  // activation columns per tile (UMMA N, <= 256)
 constexpr int CHUNK_K = 64;   // bf16 elements per 128-byte swizzled row
@@ -100,14 +108,14 @@ struct MmqParams {
     unsigned long long * dbg;        // development aid: CTA 0 stores clock64 stamps [chunk][8] for its first 256 chunks
 };
 __device__ __forceinline__ void dbg_phase(const MmqParams & p, int slot) {  // globaltimer (ns) stamps of CTA 0's phases
-    if (p.dbg && blockIdx.x == 0) {
+    if (DEV && p.dbg && blockIdx.x == 0) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         p.dbg[255 * 8 + slot] = t;
     }
 }
 __device__ __forceinline__ void dbg_stamp(const MmqParams & p, int g, int slot) {
-    if (p.dbg && blockIdx.x == 0 && g < 256) p.dbg[g * 8 + slot] = (unsigned long long) clock64();
+    if (DEV && p.dbg && blockIdx.x == 0 && g < 256) p.dbg[g * 8 + slot] = (unsigned long long) clock64();
 }
 
 struct PackParams {
@@ -401,7 +409,7 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
     if (threadIdx.x == 0) dbg_phase(p, 1);
 
     if (warp >= WARP_WPROD && warp < WARP_WPROD + N_WP_WARPS) {
-        if (!(p.dbg_flags & 64)) {
+        if (!(DEVF & 64)) {
         // ------------------------------------------------------------------ raw weight rows -> W ring
         // coalesced 16-byte cp.async (LDGSTS): a half-warp covers the aligned window around one row piece (<= 16 chunks
         // of 16 bytes), so one warp instruction touches 2 rows x <= 3 cache lines instead of 32 rows
@@ -417,7 +425,7 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
                 const int slot = wsi % p.w_stages;
                 mbar_wait(bars + 8 * (BAR_W_EMPTY + slot), ((wsi / p.w_stages) & 1) ^ 1);
                 const uint32_t sbase = base + p.off_w + (uint32_t) slot * p.w_stage_bytes + 16u * l16;
-                if (l16 < cpr && !((p.dbg_flags & 1) && wsi >= p.w_stages)) {
+                if (l16 < cpr && !((DEVF & 1) && wsi >= p.w_stages)) {
 #pragma unroll 4
                     for (int it = 0; it < TILE_M / 8; ++it) {
                         const int       row = it * 8 + wp * 2 + hf;
@@ -432,7 +440,7 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
         }
         asm volatile("cp.async.wait_all;" ::: "memory");
     } else if (warp == WARP_BPROD) {
-        if (!(p.dbg_flags & 128))
+        if (!(DEVF & 128))
         // ------------------------------------------------------------------ packed activation tiles -> B ring
         {
             // (the whole warp runs the loop, one elected lane issues; ring slot / phase are running counters and the source
@@ -457,7 +465,7 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
                     const uint32_t dst  = base + p.off_b + (uint32_t) slot * (uint32_t) p.b_stage_bytes + doff;
                     if (elect_one()) {
                         dbg_stamp(p, c, 7);
-                        if ((p.dbg_flags & 4) && issued >= p.b_stages) {
+                        if ((DEVF & 4) && issued >= p.b_stages) {
                             mbar_arrive(full);
                         } else if (p.cluster == 1) {
                             mbar_expect_tx(full, bytes);
@@ -482,6 +490,9 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
         {
             int      g = 0, ti = 0, aslot = 0, bslot = 0;
             uint32_t a_ph = 0, b_ph = 0;
+            // shared-memory descriptors advance with the ring slots (address field = bytes >> 4)
+            const uint64_t adesc0 = umma_desc_k_sw128(base), bdesc0 = umma_desc_k_sw128(base + p.off_b);
+            uint64_t       adesc = adesc0, bdesc = bdesc0;
             for (int t = cid; t < num_tiles; t += ncl, ++ti) {
                 const TileCoord tc  = tile_coord(p, t, crank);
                 const int       abi = dual ? 0 : (ti & 1);              // accumulator barrier pair
@@ -498,13 +509,11 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
                     if (lane == 0) dbg_stamp(p, g, 0);
                     mbar_wait(bars + 8 * (BAR_A_FULL + aslot), a_ph);
                     if (lane == 0) dbg_stamp(p, g, 1);
-                    if (!(p.dbg_flags & 128)) mbar_wait(bars + 8 * (BAR_B_FULL + bslot), b_ph);
+                    if (!(DEVF & 128)) mbar_wait(bars + 8 * (BAR_B_FULL + bslot), b_ph);
                     // no tcgen05.fence here: operands arrive through shared memory (mbarrier-ordered); the fence is only
                     // needed around TMEM hand-offs (accumulator release above)
-                    const uint64_t adesc = umma_desc_k_sw128(base + (uint32_t) aslot * A_STAGE_BYTES);
-                    const uint64_t bdesc = umma_desc_k_sw128(base + p.off_b + (uint32_t) bslot * (uint32_t) p.b_stage_bytes);
                     if (elect_one()) {
-                        if (!(p.dbg_flags & 32)) {
+                        if (!(DEVF & 32)) {
 #pragma unroll
                             for (int sn = 0; sn < 2; ++sn) {
                                 if (sn < tc.ns) {
@@ -525,13 +534,17 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
                     }
                     __syncwarp();
                     if (lane == 0) dbg_stamp(p, g, 3);
+                    bdesc += (uint64_t) (p.b_stage_bytes >> 4);
                     if (++bslot == p.b_stages) {
                         bslot = 0;
                         b_ph ^= 1;
+                        bdesc = bdesc0;
                     }
+                    adesc += A_STAGE_BYTES >> 4;
                     if (++aslot == A_STAGES) {
                         aslot = 0;
                         a_ph ^= 1;
+                        adesc = adesc0;
                     }
                 }
                 if (lane == 0) dbg_phase(p, 2);
@@ -553,7 +566,7 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
             const uint8_t * rowp = wb + (long long) grow * p.w_nb1;
             for (int ws = tc.ws0; ws < tc.ws1; ++ws, ++wsi) {
                 const int wslot = wsi % p.w_stages;
-                if (!(p.dbg_flags & 64)) mbar_wait(bars + 8 * (BAR_W_FULL + wslot), (wsi / p.w_stages) & 1);
+                if (!(DEVF & 64)) mbar_wait(bars + 8 * (BAR_W_FULL + wslot), (wsi / p.w_stages) & 1);
                 const uint32_t  lead  = (uint32_t) ((uintptr_t) (rowp + (long long) ws * p.piece_bytes) & 15);
                 const uint32_t  piece = base + p.off_w + (uint32_t) wslot * p.w_stage_bytes + (uint32_t) row * p.w_pitch + lead;
                 const int cps     = p.w_stage_k / CHUNK_K;
@@ -562,18 +575,18 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
                     if ((g & (N_DQ_GROUPS - 1)) != grp) continue;
                     const int slot = g % A_STAGES;
                     float v[32];
-                    if (dt == 0 && !(p.dbg_flags & 512)) dbg_stamp(p, g, 4);
-                    if (p.dbg_flags & 2) {
+                    if (dt == 0 && !(DEVF & 512)) dbg_stamp(p, g, 4);
+                    if (DEVF & 2) {
 #pragma unroll
                         for (int i = 0; i < 32; ++i) v[i] = (float) (i + row);
                     } else {
                         Dq<T>::run(piece, 2 * c + half, v);
                     }
-                    if (dt == 0 && !(p.dbg_flags & 512)) dbg_stamp(p, g, 5);
+                    if (dt == 0 && !(DEVF & 512)) dbg_stamp(p, g, 5);
                     mbar_wait(bars + 8 * (BAR_A_EMPTY + slot), ((g / A_STAGES) & 1) ^ 1);
-                    if (dt == 0 && !(p.dbg_flags & 512)) dbg_stamp(p, g, 6);
+                    if (dt == 0 && !(DEVF & 512)) dbg_stamp(p, g, 6);
                     uint8_t * arow = sm + (uint32_t) slot * A_STAGE_BYTES + a_row_off;
-                    if (!(p.dbg_flags & 8))
+                    if (!(DEVF & 8))
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
                         __nv_bfloat162 h0 = __floats2bfloat162_rn(v[8 * i + 0], v[8 * i + 1]);
@@ -584,12 +597,12 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
                         o.x = *(uint32_t *) &h0; o.y = *(uint32_t *) &h1; o.z = *(uint32_t *) &h2; o.w = *(uint32_t *) &h3;
                         *(uint4 *) (arow + ((((uint32_t) (4 * half + i)) ^ sw) << 4)) = o;
                     }
-                    if (!(p.dbg_flags & 16)) fence_proxy_async_smem();
+                    if (!(DEVF & 16)) fence_proxy_async_smem();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bars + 8 * (BAR_A_FULL + slot));
                 }
                 __syncwarp();
-                if (lane == 0 && !(p.dbg_flags & 64)) mbar_arrive(bars + 8 * (BAR_W_EMPTY + wslot));
+                if (lane == 0 && !(DEVF & 64)) mbar_arrive(bars + 8 * (BAR_W_EMPTY + wslot));
             }
         }
     } else {
