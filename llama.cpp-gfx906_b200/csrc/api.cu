@@ -203,31 +203,47 @@ int launch_gemv(GemvPlan & plan, int type, int ncols, uint32_t flags, cudaStream
 // ---- K-quant decode GEMV (gemv_kq.cu): n = 1, q4_K / q6_K, up to KQ_MAX_SEG matrices sharing the activations ------
 bool plan_kq(KqParams & p, int & grid, int & smem, int type, int64_t k, int nseg, const void * const * w, float * const * dst,
              const int64_t * m, const float * act, const DevInfo & di) {
-    if (type != T_Q4_K && type != T_Q6_K) return false;
-    if (nseg < 1 || nseg > KQ_MAX_SEG || k <= 0 || k % 256) return false;
-    static const bool off = getenv("B200Q_NO_KQ") != nullptr;
-    if (off) return false;
-    p.nsb       = (int) (k / 256);
+    if (!kq_kernel_for(type)) return false;
+    const bool kquant = type == T_Q4_K || type == T_Q6_K;
+    const int  unit   = kquant ? 256 : 32;  // elements per unit of lane work (super-block | block)
+    if (nseg < 1 || nseg > KQ_MAX_SEG || k <= 0 || k % unit) return false;
+    static const bool off   = getenv("B200Q_NO_KQ") != nullptr;
+    static const bool off32 = getenv("B200Q_NO_KQ32") != nullptr;
+    if (off || (!kquant && off32)) return false;
+    p.nsb       = (int) (k / unit);
     p.k         = (int) k;
     p.row_bytes = p.nsb * blck_bytes(type);
-    if (p.row_bytes % 16 || ((uintptr_t) act & 15)) return false;
+    if ((kquant && p.row_bytes % 16) || ((uintptr_t) act & 15)) return false;
     static const int lpr_cap   = getenv("B200Q_KQ_LPR") ? atoi(getenv("B200Q_KQ_LPR")) : 8;
     static const int budget_kb = getenv("B200Q_KQ_SMEM_KB") ? atoi(getenv("B200Q_KQ_SMEM_KB")) : 110;
     const int NWc = kq_consumer_warps();
-    p.off_q     = 384;
-    p.off_dx    = p.off_q + p.nsb * 256;
-    p.off_bs16  = round_up(p.off_dx + p.nsb * 4, 16);
-    p.off_bs32  = p.off_bs16 + p.nsb * 32;
-    p.off_stage = round_up(p.off_bs32 + p.nsb * 16, 128);
+    p.off_q = 384;
+    if (kquant) {
+        p.off_dx    = p.off_q + p.nsb * 256;
+        p.off_bs16  = round_up(p.off_dx + p.nsb * 4, 16);
+        p.off_bs32  = p.off_bs16 + p.nsb * 32;
+        p.off_stage = round_up(p.off_bs32 + p.nsb * 16, 128);
+    } else {
+        p.off_dx    = p.off_q + p.nsb * 32;  // int8 values, then (d, d * sum) per block
+        p.off_bs16  = p.off_bs32 = 0;
+        p.off_stage = round_up(p.off_dx + p.nsb * 8, 128);
+    }
+    const int work = kquant ? p.nsb : std::max(1, p.nsb / 8);  // lane work per row in super-block equivalents
     // lanes per row: few lanes = many rows per stage = less per-stage overhead, but two launches must stay co-resident
     // per SM (the next one prefetches under this one's tail) with at least ~1.25 slots per warp in flight
     int lpr = 1, S = 0;
-    while (lpr < lpr_cap && lpr < p.nsb) lpr *= 2;
+    while (lpr < lpr_cap && lpr < work) lpr *= 2;
+    // a launch that streams for tens of microseconds (the output head) gains more from a deep ring of large stages than
+    // from sharing the SM with its successor: give it the whole shared memory
+    long long rows_total = 0;
+    for (int g = 0; g < nseg; ++g) rows_total += m[g];
+    const bool big    = rows_total * p.row_bytes >= (64ll << 20);
+    const int  budget = big ? di.max_smem : budget_kb * 1024;
     for (;; lpr *= 2) {
         p.lpr            = lpr;
         p.rows_per_stage = 32 / lpr;
-        p.stage_bytes    = round_up(p.rows_per_stage * p.row_bytes + 16, 128);
-        S                = (budget_kb * 1024 - p.off_stage) / p.stage_bytes;
+        p.stage_bytes    = round_up(p.rows_per_stage * p.row_bytes + 48, 128);  // + alignment lead, tail, funnel over-read
+        S                = (budget - p.off_stage) / p.stage_bytes;
         if (S >= NWc + 2 || lpr == 32) break;
     }
     if (S < NWc / 2) S = (di.max_smem - p.off_stage) / p.stage_bytes;  // very long rows: one CTA per SM

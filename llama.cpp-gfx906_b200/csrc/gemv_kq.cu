@@ -277,6 +277,202 @@ template <> struct SbDot<T_Q6_K> {
     }
 };
 
+// ---- 32-element block formats (q4_0 q4_1 q5_0 q5_1 q8_0 mxfp4) --------------------------------------------------
+// Activations are quantized per 32 values, the arithmetic of ggml-cpu's q8_0 / q8_1 partners (quantize_row_q8_1,
+// ggml-cpu/quants.c; vec_dot_q4_0_q8_0 ... vec_dot_mxfp4_q8_0):
+//   q  : 16-byte chunk c (0..1) of block b at off_q + (c * nb + b) * 16     (chunk-major: lanes on consecutive blocks
+//        read consecutive 16-byte chunks, conflict-free)
+//   ds : float2 (d, d * sum q) at off_dx + 8 b
+// One warp per 256 values per step; lane l holds values 8l .. 8l+7, 4 lanes per block.
+__device__ __forceinline__ void quantize_act32(const KqParams & p, uint32_t sb, int warp, int lane) {
+    const int nb = p.nsb;  // 32-element blocks per row
+    for (int g = warp; g * 8 < nb; g += NW) {
+        const int  b     = g * 8 + (lane >> 2);
+        const bool valid = b < nb;  // uniform over the 4 lanes of a block
+        float4     x0 = make_float4(0.f, 0.f, 0.f, 0.f), x1 = x0;
+        if (valid) {
+            const float4 * src = (const float4 *) (p.act + (size_t) g * 256 + lane * 8);
+            x0 = __ldg(src);
+            x1 = __ldg(src + 1);
+        }
+        const float v[8] = { x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w };
+        float amax = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(v[i]));
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+        const float d  = amax * (1.0f / 127.0f);
+        const float id = amax > 0.0f ? 127.0f / amax : 0.0f;
+        int q[8], sum = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            q[i] = __float2int_rn(v[i] * id);
+            sum += q[i];
+        }
+        sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+        sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+        if (valid) {
+            const uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t) q[3] << 24);
+            const uint32_t w1 = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t) q[7] << 24);
+            const int      c  = (lane & 3) >> 1;
+            const uint32_t qa = sb + p.off_q + (uint32_t) ((c * nb + b) * 16 + (lane & 1) * 8);
+            asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(qa), "r"(w0), "r"(w1) : "memory");
+            if ((lane & 3) == 0) {
+                asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(sb + p.off_dx + (uint32_t) b * 8), "f"(d), "f"(d * (float) sum) : "memory");
+            }
+        }
+    }
+}
+
+// N consecutive little-endian words from ANY byte address of shared memory: N+1 aligned loads + funnel shifts
+template <int N> __device__ __forceinline__ void ldsu_n(uint32_t a, uint32_t (&out)[N]) {
+    const uint32_t w    = a & ~3u;
+    const int      sh   = (int) (a & 3u) * 8;
+    uint32_t       prev = lds32(w);
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        const uint32_t next = lds32(w + 4 * (i + 1));
+        out[i]              = __funnelshift_r(prev, next, sh);
+        prev                = next;
+    }
+}
+__device__ __forceinline__ int dp4a_ss(int a, int b, int c) {
+    int d;
+    asm("dp4a.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+// bit i of b -> bit 8 i (the 5th bits of q5_0 / q5_1)
+__device__ __forceinline__ uint32_t spread4_(uint32_t b) { return ((b & 0xFu) * 0x00204081u) & 0x01010101u; }
+
+// 8 nibbles of one word -> int8x4 words of the (doubled) E2M1 code points (ggml-common.h kvalues_mxfp4), low / high nibbles
+__device__ __forceinline__ void mxfp4_words(uint32_t q, uint32_t & lo, uint32_t & hi) {
+    const uint32_t t0 = 0x03020100u, t1 = 0x0C080604u, t2 = 0xFDFEFF00u, t3 = 0xF4F8FAFCu;
+    uint32_t       r[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const uint32_t n   = (q >> (4 * h)) & 0x0F0F0F0Fu;
+        const uint32_t sel = n & 0x07070707u;
+        const uint32_t s   = (sel & 0xF) | ((sel >> 4) & 0xF0) | ((sel >> 8) & 0xF00) | ((sel >> 12) & 0xF000);
+        const uint32_t pos = __byte_perm(t0, t1, s), neg = __byte_perm(t2, t3, s);
+        const uint32_t m   = ((n >> 3) & 0x01010101u) * 0xFFu;
+        r[h]               = (pos & ~m) | (neg & m);
+    }
+    lo = r[0];
+    hi = r[1];
+}
+
+// dot of block b of the row at shared address `row` (any byte alignment) with the quantized activations:
+//   returns  sum_{i in block} w_i * x_i  =  d_w * (d_x * sum q_w q_x)  +  m_w * (d_x * sum q_x)
+template <int T> struct B32Dot;
+template <int T> __device__ __forceinline__ void act_block(const KqParams & p, uint32_t sb, int b, int (&a)[8], float2 & ds) {
+    const int4 a0 = lds128(sb + p.off_q + (uint32_t) b * 16u), a1 = lds128(sb + p.off_q + (uint32_t) (p.nsb + b) * 16u);
+    a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(ds.x), "=f"(ds.y) : "r"(sb + p.off_dx + (uint32_t) b * 8u));
+}
+template <> struct B32Dot<T_Q4_0> {
+    static constexpr int BLK = 18;
+    static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int b) {
+        uint32_t w[5];  // [d | qs0 qs1] [qs2..5] [qs6..9] [qs10..13] [qs14 qs15 | next]
+        ldsu_n<5>(row + (uint32_t) b * BLK, w);
+        int a[8]; float2 ds;
+        act_block<T_Q4_0>(p, sb, b, a, ds);
+        int sumi = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t q = __funnelshift_r(w[i], w[i + 1], 16);
+            sumi = dp4a_us(q & 0x0F0F0F0Fu, a[i], sumi);
+            sumi = dp4a_us((q >> 4) & 0x0F0F0F0Fu, a[4 + i], sumi);
+        }
+        const float d = half_bits_to_float((uint16_t) (w[0] & 0xffffu));
+        return d * (ds.x * (float) sumi) + (-8.0f * d) * ds.y;
+    }
+};
+template <> struct B32Dot<T_Q4_1> {
+    static constexpr int BLK = 20;
+    static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int b) {
+        uint32_t w[5];  // [d m] [qs x4]
+        ldsu_n<5>(row + (uint32_t) b * BLK, w);
+        int a[8]; float2 ds;
+        act_block<T_Q4_1>(p, sb, b, a, ds);
+        int sumi = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            sumi = dp4a_us(w[1 + i] & 0x0F0F0F0Fu, a[i], sumi);
+            sumi = dp4a_us((w[1 + i] >> 4) & 0x0F0F0F0Fu, a[4 + i], sumi);
+        }
+        return half_bits_to_float((uint16_t) (w[0] & 0xffffu)) * (ds.x * (float) sumi) + half_bits_to_float((uint16_t) (w[0] >> 16)) * ds.y;
+    }
+};
+template <> struct B32Dot<T_Q5_0> {
+    static constexpr int BLK = 22;
+    static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int b) {
+        uint32_t w[6];  // [d | qh0 qh1] [qh2 qh3 | qs0 qs1] [qs2..5] [qs6..9] [qs10..13] [qs14 qs15 | next]
+        ldsu_n<6>(row + (uint32_t) b * BLK, w);
+        int a[8]; float2 ds;
+        act_block<T_Q5_0>(p, sb, b, a, ds);
+        const uint32_t qh = __funnelshift_r(w[0], w[1], 16);
+        int sumi = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t q = __funnelshift_r(w[1 + i], w[2 + i], 16);
+            sumi = dp4a_us((q & 0x0F0F0F0Fu) | (spread4_(qh >> (4 * i)) << 4), a[i], sumi);
+            sumi = dp4a_us(((q >> 4) & 0x0F0F0F0Fu) | (spread4_(qh >> (16 + 4 * i)) << 4), a[4 + i], sumi);
+        }
+        const float d = half_bits_to_float((uint16_t) (w[0] & 0xffffu));
+        return d * (ds.x * (float) sumi) + (-16.0f * d) * ds.y;
+    }
+};
+template <> struct B32Dot<T_Q5_1> {
+    static constexpr int BLK = 24;
+    static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int b) {
+        uint32_t w[6];  // [d m] [qh] [qs x4]
+        ldsu_n<6>(row + (uint32_t) b * BLK, w);
+        int a[8]; float2 ds;
+        act_block<T_Q5_1>(p, sb, b, a, ds);
+        const uint32_t qh = w[1];
+        int sumi = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            sumi = dp4a_us((w[2 + i] & 0x0F0F0F0Fu) | (spread4_(qh >> (4 * i)) << 4), a[i], sumi);
+            sumi = dp4a_us(((w[2 + i] >> 4) & 0x0F0F0F0Fu) | (spread4_(qh >> (16 + 4 * i)) << 4), a[4 + i], sumi);
+        }
+        return half_bits_to_float((uint16_t) (w[0] & 0xffffu)) * (ds.x * (float) sumi) + half_bits_to_float((uint16_t) (w[0] >> 16)) * ds.y;
+    }
+};
+template <> struct B32Dot<T_Q8_0> {
+    static constexpr int BLK = 34;
+    static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int b) {
+        uint32_t w[9];  // [d | q0 q1] ... [q30 q31 | next]
+        ldsu_n<9>(row + (uint32_t) b * BLK, w);
+        int a[8]; float2 ds;
+        act_block<T_Q8_0>(p, sb, b, a, ds);
+        int sumi = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) sumi = dp4a_ss((int) __funnelshift_r(w[i], w[i + 1], 16), a[i], sumi);
+        return half_bits_to_float((uint16_t) (w[0] & 0xffffu)) * (ds.x * (float) sumi);
+    }
+};
+template <> struct B32Dot<T_MXFP4> {
+    static constexpr int BLK = 17;
+    static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int b) {
+        uint32_t w[5];  // [e | qs0 qs1 qs2] ... [qs15 | next]
+        ldsu_n<5>(row + (uint32_t) b * BLK, w);
+        int a[8]; float2 ds;
+        act_block<T_MXFP4>(p, sb, b, a, ds);
+        int sumi = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            uint32_t lo, hi;
+            mxfp4_words(__funnelshift_r(w[i], w[i + 1], 8), lo, hi);
+            sumi = dp4a_ss((int) lo, a[i], sumi);
+            sumi = dp4a_ss((int) hi, a[4 + i], sumi);
+        }
+        return e8m0_half_to_float((uint8_t) (w[0] & 0xff)) * (ds.x * (float) sumi);
+    }
+};
+
+template <int T> struct IsKQuant { static constexpr bool value = T == T_Q4_K || T == T_Q6_K; };
+
 struct StageInfo {
     int g, r0, nrows;
 };
@@ -324,11 +520,14 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 2) gemv_kq_kernel(c
     auto           issue  = [&](int i) {
         const int       t     = T0 + warp + i * NA, slot = slot0 + i % D;
         const StageInfo si    = stage_info(p, t);
-        const uint32_t  bytes = (uint32_t) si.nrows * (uint32_t) p.row_bytes;
+        // rows of the 32-element block formats need not be 16-byte multiples: copy the aligned window around the rows
+        // (the over-read stays inside the tensor or its allocation slack, include/b200q.h)
+        const uint8_t * src   = p.seg[si.g].w + (size_t) si.r0 * p.row_bytes;
+        const uint32_t  lead  = (uint32_t) ((uintptr_t) src & 15);
+        const uint32_t  bytes = (lead + (uint32_t) si.nrows * (uint32_t) p.row_bytes + 15u) & ~15u;
         const uint32_t  full  = sb + OFF_FULL + 8 * slot;
         mbar_expect_tx(full, bytes);
-        bulk_g2s_hint(sb + p.off_stage + (uint32_t) slot * p.stage_bytes, p.seg[si.g].w + (size_t) si.r0 * p.row_bytes, bytes,
-                      full, pol);
+        bulk_g2s_hint(sb + p.off_stage + (uint32_t) slot * p.stage_bytes, src - lead, bytes, full, pol);
     };
     if (p.early_prefetch && lane == 0) {
         for (int i = 0; i < min(D, nmine); ++i) issue(i);  // immutable weights: stream them under the previous kernel's tail
@@ -337,7 +536,8 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 2) gemv_kq_kernel(c
     if (!p.early_prefetch && lane == 0) {
         for (int i = 0; i < min(D, nmine); ++i) issue(i);
     }
-    quantize_act(p, sb, warp, lane);
+    if (IsKQuant<T>::value) quantize_act(p, sb, warp, lane);
+    else quantize_act32(p, sb, warp, lane);
     __syncthreads();
 
     const int lpr  = p.lpr;
@@ -347,11 +547,13 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 2) gemv_kq_kernel(c
         const int       t = T0 + warp + i * NA, slot = slot0 + i % D, use = i / D;
         const StageInfo si = stage_info(p, t);
         mbar_wait_dbg(sb + OFF_FULL + 8 * slot, use & 1, 2, i);
-        const uint32_t row = sb + p.off_stage + (uint32_t) slot * p.stage_bytes + (uint32_t) lrow * (uint32_t) p.row_bytes;
+        const uint32_t lead = (uint32_t) ((uintptr_t) (p.seg[si.g].w + (size_t) si.r0 * p.row_bytes) & 15);
+        const uint32_t row  = sb + p.off_stage + (uint32_t) slot * p.stage_bytes + lead + (uint32_t) lrow * (uint32_t) p.row_bytes;
         float acc = 0.0f;
         if (lrow < si.nrows) {
             for (int s = sub; s < p.nsb; s += lpr) {
-                acc += SbDot<T>::run(p, sb, row, s);
+                if constexpr (IsKQuant<T>::value) acc += SbDot<T>::run(p, sb, row, s);
+                else acc += B32Dot<T>::run(p, sb, row, s);
             }
         }
         __syncwarp();  // every lane is done reading the slot
@@ -375,6 +577,12 @@ kq_kernel_t kq_kernel_for(int type) {
     switch (type) {
         case T_Q4_K: return gemv_kq_kernel<T_Q4_K>;
         case T_Q6_K: return gemv_kq_kernel<T_Q6_K>;
+        case T_Q4_0: return gemv_kq_kernel<T_Q4_0>;
+        case T_Q4_1: return gemv_kq_kernel<T_Q4_1>;
+        case T_Q5_0: return gemv_kq_kernel<T_Q5_0>;
+        case T_Q5_1: return gemv_kq_kernel<T_Q5_1>;
+        case T_Q8_0: return gemv_kq_kernel<T_Q8_0>;
+        case T_MXFP4: return gemv_kq_kernel<T_MXFP4>;
         default: return nullptr;
     }
 }

@@ -18,13 +18,13 @@ struct KqParams {
     KqSegment     seg[KQ_MAX_SEG];
     int           nseg;
     const float * act;  // [k] f32 (16-byte aligned)
-    int           k, nsb;        // row length, super-blocks per row
-    int           row_bytes;     // nsb * 144 (q4_K) | nsb * 210 (q6_K); multiple of 16
+    int           k, nsb;        // row length; units per row: 256-element super-blocks (K-quants) | 32-element blocks
+    int           row_bytes;     // nsb * block bytes (K-quants: a multiple of 16; 32-element block formats: any)
     int           lpr;           // lanes per row: 8, 16 or 32
     int           rows_per_stage;  // 32 / lpr: one stage = one warp pass
     int           total_stages;
     int           nstages;       // ring depth
-    int           stage_bytes;   // rows_per_stage * row_bytes rounded up to 128
+    int           stage_bytes;   // rows_per_stage * row_bytes + alignment lead / over-read, rounded up to 128
     // shared-memory offsets
     int           off_q, off_dx, off_bs16, off_bs32, off_stage;
     int           early_prefetch;  // weights immutable: stream them before griddepcontrol.wait
