@@ -572,15 +572,20 @@ int b200q_mul_mat_group(const b200q_mul_mat_group_args * a, const void * const *
 }
 
 // ---- MUL_MAT_ID ----------------------------------------------------------------------------------------
+// (token, slot) rows from which MUL_MAT_ID groups the rows per expert and runs the tensor-core kernel; below it every
+// row is one GEMV channel
+static bool moe_use_mmq(const b200q_mul_mat_id_args * a) {
+    static const long long min_rows = getenv("B200Q_MOE_MMQ_MIN") ? atoll(getenv("B200Q_MOE_MMQ_MIN")) : 32;
+    return a->n_tokens * a->n_used >= min_rows && mmq_supported(a->type, a->k) && a->n_expert <= 1024;
+}
+
 size_t b200q_mul_mat_id_workspace(const b200q_mul_mat_id_args * a) {
-    (void) a;
-    return 0;
+    if (!a || !moe_use_mmq(a)) return 0;
+    return mmq_moe_workspace_bytes(a->k, a->n_tokens, a->n_used, a->n_expert);
 }
 
 int b200q_mul_mat_id(const b200q_mul_mat_id_args * a, const void * as, const float * b, const int32_t * ids, float * dst,
                      void * workspace, size_t workspace_bytes, void * stream) {
-    (void) workspace;
-    (void) workspace_bytes;
     if (!a || !as || !b || !ids || !dst) return fail(B200Q_EINVAL, "mul_mat_id: null argument");
     const int be = blck_elems(a->type);
     if (!be || a->type == T_F32) return fail(B200Q_ENOTSUP, "mul_mat_id: unsupported weight type %d", a->type);
@@ -589,6 +594,24 @@ int b200q_mul_mat_id(const b200q_mul_mat_id_args * a, const void * as, const flo
     if (a->m == 0 || a->n_tokens == 0 || a->n_used == 0) return 0;
     const DevInfo & di = dev_info();
     if (!di.ok) return fail(B200Q_ENODEVICE, "mul_mat_id: no CUDA device");
+
+    if (moe_use_mmq(a)) {
+        const size_t need = mmq_moe_workspace_bytes(a->k, a->n_tokens, a->n_used, a->n_expert);
+        if (!workspace || workspace_bytes < need) {
+            return fail(B200Q_EINVAL, "mul_mat_id: workspace of %zu bytes needed (b200q_mul_mat_id_workspace)", need);
+        }
+        MmqMoeArgs q{};
+        q.type = a->type; q.k = a->k; q.m = a->m; q.n_expert = a->n_expert; q.n_used = a->n_used; q.n_tokens = a->n_tokens;
+        q.b_bcast = a->b_ne1 == 1;
+        q.w_nb1 = (long long) a->nb01; q.w_nb2 = (long long) a->nb02;
+        q.a_nb1 = (long long) a->nb11; q.a_nb2 = (long long) a->nb12;
+        q.ids_nb1 = (long long) a->ids_nb1;
+        q.d_nb1 = (long long) a->nb1; q.d_nb2 = (long long) a->nb2;
+        q.w = (const uint8_t *) as; q.act = b; q.ids = ids; q.dst = dst;
+        std::string err;
+        if (int rc = mmq_moe_launch(q, workspace, (cudaStream_t) stream, di.sms, err)) return fail(rc, "%s", err.c_str());
+        return 0;
+    }
 
     // one GEMV channel per (token, slot); expert ids are read on the device (no host round trip, cf. mmq.cu:161)
     GemvPlan plan{};

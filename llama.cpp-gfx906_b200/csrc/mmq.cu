@@ -96,6 +96,11 @@ struct MmqParams {
     int   n_sub;         // column tiles per super-tile (2, or 1 when there are too few tiles to fill the GPU otherwise)
     int   cluster;       // CTAs per cluster (1, 2 or 4): they take adjacent row tiles and share every B chunk by multicast
     int   m_groups;      // ceil(m_tiles / cluster)
+    // MoE (MUL_MAT_ID) mode: the column tiles are per-expert lists of (token, slot) rows built on the device (moe_route)
+    const int * moe;         // header: [0] total column tiles, then the tables below (nullptr: plain MUL_MAT)
+    const int * moe_tile_expert, * moe_tile_col0, * moe_count, * moe_offset, * moe_rows;
+    int   n_used;
+    long long w_nb_expert;
     int   ksplit;        // 1 or 2: k-halves of one tile go to different CTAs and are summed with fp32 atomics into a zeroed dst
                          // (two addends on zero: the result does not depend on the arrival order)
     int   ws_per_split;  // W stages per k-split
@@ -338,11 +343,26 @@ struct TileCoord {
     int b, mt, nt, ns;  // batch, row tile, first column tile, column tiles in this super-tile (1 or 2)
     int ws0, ws1;       // W stages [ws0, ws1) of the row pieces
     int c0, c1;         // k-chunks [c0, c1)
+    int ncols[2];       // valid columns of the (up to two) column tiles
+    long long w_off;    // byte offset of the unit's weight matrix (batch broadcast | expert)
+    int row_base;       // MoE: index of the tile's first entry in moe_rows
 };
 // work unit `t` of a cluster; CTA `rank` of the cluster takes row tile group * cluster + rank, which may lie past the
 // last row tile (a phantom tile: the CTA still feeds its share of B to its peers, its results are not stored)
 __device__ __forceinline__ TileCoord tile_coord(const MmqParams & p, int t, int rank) {
     TileCoord c;
+    if (p.moe) {  // unit = (column tile of one expert, row tile); row tiles fastest so that neighbours share the B tile
+        c.mt           = t % p.m_tiles;
+        const int ts   = t / p.m_tiles;
+        const int e    = p.moe_tile_expert[ts], col0 = p.moe_tile_col0[ts];
+        c.b = 0; c.nt = ts; c.ns = 1;
+        c.ws0 = 0; c.ws1 = p.w_stages_per_tile; c.c0 = 0; c.c1 = p.k_chunks;
+        c.ncols[0]     = min(TILE_N, p.moe_count[e] - col0);
+        c.ncols[1]     = 0;
+        c.w_off        = (long long) e * p.w_nb_expert;
+        c.row_base     = p.moe_offset[e] + col0;
+        return c;
+    }
     const int ks   = t % p.ksplit;
     t /= p.ksplit;
     c.ws0          = ks * p.ws_per_split;
@@ -355,6 +375,11 @@ __device__ __forceinline__ TileCoord tile_coord(const MmqParams & p, int t, int 
     c.mt           = (rest % p.m_groups) * p.cluster + rank;
     c.b            = rest / p.m_groups;
     c.ns           = min(p.n_sub, p.n_tiles - c.nt);
+    c.ncols[0]     = min(TILE_N, p.n - c.nt * TILE_N);
+    c.ncols[1]     = max(0, min(TILE_N, p.n - (c.nt + 1) * TILE_N));
+    const int i13  = c.b / p.ne12, i12 = c.b - i13 * p.ne12;
+    c.w_off        = (long long) (i12 / p.r2) * p.w_nb2 + (long long) (i13 / p.r3) * p.w_nb3;
+    c.row_base     = 0;
     return c;
 }
 // bytes of the raw row piece of W stage `ws` (the last stage of a row may be ragged for 32-element block types)
@@ -372,7 +397,7 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
     volatile uint32_t * tmem_slot = (volatile uint32_t *) (sm + p.off_bar + BAR_COUNT * 8);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int  num_tiles = p.nbatch * p.m_groups * p.n_super * p.ksplit;  // work units of a cluster
+    const int  num_tiles = p.moe ? p.moe[0] * p.m_tiles : p.nbatch * p.m_groups * p.n_super * p.ksplit;  // work units of a cluster
     const bool dual      = p.n_sub > 1;  // both accumulators belong to one super-tile (else: double-buffered tiles)
     const int  crank     = p.cluster > 1 ? (int) cluster_ctarank() : 0;
     const int  cid       = blockIdx.x / p.cluster, ncl = gridDim.x / p.cluster;
@@ -419,8 +444,7 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
         int wsi = 0;
         for (int t = cid; t < num_tiles; t += ncl) {
             const TileCoord tc  = tile_coord(p, t, crank);
-            const int       i13 = tc.b / p.ne12, i12 = tc.b - i13 * p.ne12;
-            const uint8_t * wb  = p.w + (long long) (i12 / p.r2) * p.w_nb2 + (long long) (i13 / p.r3) * p.w_nb3;
+            const uint8_t * wb  = p.w + tc.w_off;
             for (int ws = tc.ws0; ws < tc.ws1; ++ws, ++wsi) {
                 const int slot = wsi % p.w_stages;
                 mbar_wait(bars + 8 * (BAR_W_EMPTY + slot), ((wsi / p.w_stages) & 1) ^ 1);
@@ -450,9 +474,10 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
             for (int t = cid; t < num_tiles; t += ncl) {
                 const TileCoord tc = tile_coord(p, t, crank);
                 // the column tiles of one k-chunk are adjacent in the packed workspace: one copy per chunk
-                const int ncols_last = min(TILE_N, p.n - (tc.nt + tc.ns - 1) * TILE_N);
+                const int ncols_last = tc.ncols[tc.ns - 1];
                 uint32_t  bytes      = (uint32_t) (tc.ns - 1) * B_STAGE_BYTES + (uint32_t) ((ncols_last + 15) & ~15) * 128u;
-                const uint8_t * src  = p.actp + (((long long) (tc.b * p.n_super + tc.nt / p.n_sub) * p.k_chunks + tc.c0) * p.n_sub) * B_STAGE_BYTES;
+                const uint8_t * src  = p.moe ? p.actp + ((long long) tc.nt * p.k_chunks) * B_STAGE_BYTES
+                                             : p.actp + (((long long) (tc.b * p.n_super + tc.nt / p.n_sub) * p.k_chunks + tc.c0) * p.n_sub) * B_STAGE_BYTES;
                 uint32_t doff = 0;
                 if (p.cluster > 1) {  // this CTA fetches 1/cluster of every chunk and multicasts it to its peers
                     bytes /= (uint32_t) p.cluster;  // a multiple of 2048 before: the slices stay 16-byte multiples
@@ -499,8 +524,7 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
                 const uint32_t  aph = dual ? (ti & 1) : ((ti >> 1) & 1);
                 uint32_t idesc[2], d_tmem[2];
                 for (int sn = 0; sn < 2; ++sn) {
-                    const int ncols = min(TILE_N, p.n - (tc.nt + sn) * TILE_N);
-                    idesc[sn]  = umma_idesc_bf16_f32(TILE_M, (max(ncols, 1) + 15) & ~15);
+                    idesc[sn]  = umma_idesc_bf16_f32(TILE_M, (max(tc.ncols[sn], 1) + 15) & ~15);
                     d_tmem[sn] = tmem_base + (uint32_t) (dual ? sn : abi) * TILE_N;
                 }
                 mbar_wait(bars + 8 * (BAR_ACC_EMPTY + abi), aph ^ 1);
@@ -560,8 +584,7 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
         int wsi = 0, g = 0;
         for (int t = cid; t < num_tiles; t += ncl) {
             const TileCoord tc  = tile_coord(p, t, crank);
-            const int       i13 = tc.b / p.ne12, i12 = tc.b - i13 * p.ne12;
-            const uint8_t * wb  = p.w + (long long) (i12 / p.r2) * p.w_nb2 + (long long) (i13 / p.r3) * p.w_nb3;
+            const uint8_t * wb  = p.w + tc.w_off;
             const int       grow = min(tc.mt * TILE_M + row, p.m - 1);
             const uint8_t * rowp = wb + (long long) grow * p.w_nb1;
             for (int ws = tc.ws0; ws < tc.ws1; ++ws, ++wsi) {
@@ -620,12 +643,22 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
             if (threadIdx.x == 0) dbg_phase(p, 3);
             for (int sn = 0; sn < tc.ns; ++sn) {
                 const int n0    = (tc.nt + sn) * TILE_N;
-                const int ncols = min(TILE_N, p.n - n0);
+                const int ncols = tc.ncols[sn];
                 const int acol  = (dual ? sn : ab) * TILE_N;
                 for (int c0 = 0; c0 < ncols; c0 += 32) {
                     float v[32];
                     tmem_ld32(tmem_base + ((uint32_t) (warp * 32) << 16) + (uint32_t) (acol + c0), v);
-                    if (row < p.m) {
+                    if (row < p.m && p.moe) {
+                        // scatter: column j of this tile is the (token, slot) row moe_rows[row_base + j] of dst
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            if (c0 + j < ncols) {
+                                const int r  = __ldg(p.moe_rows + tc.row_base + c0 + j);
+                                const int tk = r / p.n_used, sl = r - tk * p.n_used;
+                                *(float *) ((char *) p.dst + (long long) tk * p.d_nb2 + (long long) sl * p.d_nb1 + (long long) row * 4) = v[j];
+                            }
+                        }
+                    } else if (row < p.m) {
                         char * dp = dbase + (long long) (n0 + c0) * p.d_nb1;  // one coalesced 128-byte warp store per column
                         if (p.ksplit > 1) {
 #pragma unroll
@@ -665,6 +698,115 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
     }
 }
 
+// ---- MoE routing: ids [T][n_used] -> per-expert row lists and the column-tile table ---------------------------------
+// header layout (int32): [0] total tiles | [16, 16+E) count | [.., +E) offset | [.., +maxT) tile_expert |
+// [.., +maxT) tile_col0 | [.., +R) rows  (R = T * n_used, maxT = ceil(R / TILE_N) + E)
+struct MoeTables {
+    int * total, * count, * offset, * tile_expert, * tile_col0, * rows;
+    size_t bytes;  // header bytes, rounded up to 1024
+};
+inline MoeTables moe_tables(void * ws, int n_expert, int rows, int max_tiles) {
+    MoeTables t;
+    int *     b   = (int *) ws;
+    t.total       = b;
+    t.count       = b + 16;
+    t.offset      = t.count + n_expert;
+    t.tile_expert = t.offset + n_expert;
+    t.tile_col0   = t.tile_expert + max_tiles;
+    t.rows        = t.tile_col0 + max_tiles;
+    t.bytes       = ((size_t) (16 + 2 * n_expert + 2 * max_tiles + rows) * 4 + 1023) / 1024 * 1024;
+    return t;
+}
+struct MoeRouteParams {
+    const int32_t * ids;
+    long long       ids_nb1;
+    int             n_tokens, n_used, n_expert;
+    MoeTables       t;
+};
+// one CTA.  Rows of an expert are listed in increasing (token, slot) order (ranks by a prefix count, no atomics), so
+// the layout — and with it every byte the MMQ kernel reads or writes — is reproducible.
+__global__ void __launch_bounds__(1024) moe_route(const MoeRouteParams p) {
+    extern __shared__ int rs[];  // [n_expert] counts, then per-thread-chunk partial counts are avoided: two passes
+    const int R = p.n_tokens * p.n_used;
+    for (int e = threadIdx.x; e < p.n_expert; e += blockDim.x) rs[e] = 0;
+    __syncthreads();
+    for (int r = threadIdx.x; r < R; r += blockDim.x) {
+        const int t = r / p.n_used, sl = r - t * p.n_used;
+        const int e = *(const int32_t *) ((const char *) p.ids + (long long) t * p.ids_nb1 + sl * 4);
+        if (e >= 0 && e < p.n_expert) atomicAdd(&rs[e], 1);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int off = 0, ts = 0;
+        for (int e = 0; e < p.n_expert; ++e) {
+            const int c   = rs[e];
+            p.t.count[e]  = c;
+            p.t.offset[e] = off;
+            for (int c0 = 0; c0 < c; c0 += TILE_N, ++ts) {
+                p.t.tile_expert[ts] = e;
+                p.t.tile_col0[ts]   = c0;
+            }
+            off += c;
+        }
+        p.t.total[0] = ts;
+    }
+    __syncthreads();
+    // stable fill: one warp per expert scans the rows in order (ballot + popc ranks)
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    for (int e = warp; e < p.n_expert; e += nwarps) {
+        if (rs[e] == 0) continue;
+        int pos = p.t.offset[e];
+        for (int r0 = 0; r0 < R; r0 += 32) {
+            const int r = r0 + lane;
+            bool      mine = false;
+            if (r < R) {
+                const int t = r / p.n_used, sl = r - t * p.n_used;
+                mine = *(const int32_t *) ((const char *) p.ids + (long long) t * p.ids_nb1 + sl * 4) == e;
+            }
+            const unsigned bal = __ballot_sync(0xffffffffu, mine);
+            if (mine) p.t.rows[pos + __popc(bal & ((1u << lane) - 1u))] = r;
+            pos += __popc(bal);
+        }
+    }
+}
+
+struct MoePackParams {
+    const float * act;
+    uint8_t *     out;
+    MoeTables     t;
+    int           k_chunks, n_used, b_bcast, max_tiles;
+    long long     a_nb1, a_nb2;  // byte strides of b: slot, token
+};
+// gathered f32 rows -> the same swizzled bf16 tile image as mmq_pack_act; block (tile, k_chunk)
+__global__ void __launch_bounds__(256) moe_pack_act(const MoePackParams p) {
+    const int       total_tiles = p.t.total[0];
+    const long long per_tile    = (long long) p.k_chunks * TILE_N * 8;
+    const long long total       = (long long) total_tiles * per_tile;
+    for (long long idx = (long long) blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long) gridDim.x * blockDim.x) {
+        const int c  = (int) (idx & 7);
+        const int j  = (int) ((idx >> 3) & (TILE_N - 1));
+        const long long blk = idx / (TILE_N * 8);
+        const int kc = (int) (blk % p.k_chunks);
+        const int ts = (int) (blk / p.k_chunks);
+        const int e  = p.t.tile_expert[ts], col = p.t.tile_col0[ts] + j, cnt = p.t.count[e];
+        if (col >= ((cnt + 15) & ~15)) continue;  // the MMA reads whole groups of 16 columns only
+        uint4 o = make_uint4(0, 0, 0, 0);
+        if (col < cnt) {
+            const int     r  = p.t.rows[p.t.offset[e] + col];
+            const int     tk = r / p.n_used, sl = r - tk * p.n_used;
+            const float * src = (const float *) ((const char *) p.act + (long long) tk * p.a_nb2 + (p.b_bcast ? 0ll : (long long) sl * p.a_nb1)) +
+                                kc * CHUNK_K + c * 8;
+            float v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = __ldg(src + i);
+            __nv_bfloat162 h0 = __floats2bfloat162_rn(v[0], v[1]), h1 = __floats2bfloat162_rn(v[2], v[3]);
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[4], v[5]), h3 = __floats2bfloat162_rn(v[6], v[7]);
+            o.x = *(uint32_t *) &h0; o.y = *(uint32_t *) &h1; o.z = *(uint32_t *) &h2; o.w = *(uint32_t *) &h3;
+        }
+        *(uint4 *) (p.out + blk * (long long) B_STAGE_BYTES + (long long) j * 128 + ((c ^ (j & 7)) << 4)) = o;
+    }
+}
+
 typedef void (*mmq_kernel_t)(const MmqParams);
 unsigned long long * g_mmq_dbg = nullptr;
 
@@ -698,7 +840,35 @@ size_t mmq_workspace_bytes(int64_t k, int64_t n, int64_t nbatch) {
     return (size_t) (nbatch * ((n_tiles + 1) / 2 * 2) * (k / CHUNK_K)) * B_STAGE_BYTES;  // room for the padding tile of a pair
 }
 
+size_t mmq_moe_workspace_bytes(int64_t k, int64_t n_tokens, int64_t n_used, int64_t n_expert) {
+    const int64_t rows = n_tokens * n_used, max_tiles = (rows + TILE_N - 1) / TILE_N + n_expert;
+    return moe_tables(nullptr, (int) n_expert, (int) rows, (int) max_tiles).bytes + (size_t) (max_tiles * (k / CHUNK_K)) * B_STAGE_BYTES;
+}
+
+static int mmq_launch_impl(const MmqArgs & a, const MmqMoeArgs * moe, void * workspace, cudaStream_t st, int sms, std::string & err);
+
 int mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, std::string & err) {
+    return mmq_launch_impl(a, nullptr, workspace, st, sms, err);
+}
+
+// MUL_MAT_ID for many tokens: the (token, slot) rows are grouped per expert on the device and every expert's rows run
+// through the tensor-core kernel as column tiles of that expert's matrix (replaces the reference's mmq ids path,
+// ggml-cuda/mmq.cu:161-, mmid.cu)
+int mmq_moe_launch(const MmqMoeArgs & m, void * workspace, cudaStream_t st, int sms, std::string & err) {
+    if (m.n_expert > 1024) {
+        err = "mmq: more than 1024 experts";
+        return B200Q_ENOTSUP;
+    }
+    MmqArgs a{};
+    a.type = m.type; a.k = m.k; a.m = m.m; a.n = TILE_N;
+    a.ne02 = a.ne03 = a.ne12 = a.ne13 = 1;
+    a.w_nb1 = m.w_nb1; a.w_nb2 = a.w_nb3 = 0;
+    a.d_nb1 = m.d_nb1; a.d_nb2 = m.d_nb2; a.d_nb3 = 0;
+    a.w = m.w; a.act = m.act; a.dst = m.dst;
+    return mmq_launch_impl(a, &m, workspace, st, sms, err);
+}
+
+static int mmq_launch_impl(const MmqArgs & a, const MmqMoeArgs * moe, void * workspace, cudaStream_t st, int sms, std::string & err) {
     mmq_kernel_t fn = mmq_kernel_for(a.type);
     if (!fn || !mmq_supported(a.type, a.k)) {
         err = "mmq: unsupported type / k";
@@ -719,7 +889,17 @@ int mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, st
     pp.vec4  = ((uintptr_t) a.act & 15) == 0 && (a.a_nb1 & 15) == 0 && (a.a_nb2 & 15) == 0 && (a.a_nb3 & 15) == 0;
 
     MmqParams p{};
-    p.w = a.w; p.actp = (const uint8_t *) workspace; p.dst = a.dst;
+    MoeTables mt{};
+    int       moe_max_tiles = 0;
+    if (moe) {
+        const int rows = (int) (moe->n_tokens * moe->n_used);
+        moe_max_tiles  = (rows + TILE_N - 1) / TILE_N + (int) moe->n_expert;
+        mt             = moe_tables(workspace, (int) moe->n_expert, rows, moe_max_tiles);
+        p.moe = mt.total; p.moe_tile_expert = mt.tile_expert; p.moe_tile_col0 = mt.tile_col0;
+        p.moe_count = mt.count; p.moe_offset = mt.offset; p.moe_rows = mt.rows;
+        p.n_used = (int) moe->n_used; p.w_nb_expert = moe->w_nb2;
+    }
+    p.w = a.w; p.actp = (const uint8_t *) workspace + mt.bytes; p.dst = a.dst;
     p.k = (int) a.k; p.m = (int) a.m; p.n = (int) a.n;
     p.ne12 = (int) a.ne12; p.r2 = (int) (a.ne12 / a.ne02); p.r3 = (int) (a.ne13 / a.ne03); p.nbatch = nbatch;
     p.w_nb1 = a.w_nb1; p.w_nb2 = a.w_nb2; p.w_nb3 = a.w_nb3;
@@ -748,6 +928,7 @@ int mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, st
         p.ksplit = p.n_sub == 1 && units_one < fill && p.w_stages_per_tile >= 4 ? 2 : 1;
         if (force_sub) p.n_sub = p.n_tiles > 1 ? std::min(force_sub, 2) : 1;
         if (force_ks) p.ksplit = p.w_stages_per_tile >= 2 ? std::min(force_ks, 2) : 1;
+        if (moe) p.n_sub = p.ksplit = 1;
     }
     p.off_b = A_STAGES * A_STAGE_BYTES;
     auto fit_rings = [&](int n_sub) {  // B ring (stages of n_sub x 32 KB, at most 128 KB) + W ring in what is left
@@ -768,7 +949,7 @@ int mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, st
     }
     p.ws_per_split = (p.w_stages_per_tile + p.ksplit - 1) / p.ksplit;
     p.n_super = (p.n_tiles + p.n_sub - 1) / p.n_sub;
-    p.cluster = force_cl ? force_cl : 1;  // multicast of the B chunks measured no gain (L2 already dedups the reads)
+    p.cluster = force_cl && !moe ? force_cl : 1;  // multicast of the B chunks measured no gain (L2 already dedups the reads)
     while (p.cluster > 1 && sms / p.cluster < 1) p.cluster >>= 1;
     p.m_groups = (p.m_tiles + p.cluster - 1) / p.cluster;
     if (p.w_stages < 2) {
@@ -798,7 +979,7 @@ int mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, st
             done.insert({ dev, (const void *) fn });
         }
     }
-    const int num_units = nbatch * p.m_groups * p.n_super * p.ksplit;
+    const int num_units = moe ? moe_max_tiles * p.m_tiles : nbatch * p.m_groups * p.n_super * p.ksplit;  // MoE: upper bound
     cudaLaunchConfig_t cfg{};
     cfg.blockDim         = dim3(NTHREADS);
     cfg.dynamicSmemBytes = smem;
@@ -838,7 +1019,18 @@ int mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, st
         fprintf(stderr, "[b200q] mmq type=%d m=%d n=%d k=%d cluster=%d n_sub=%d ksplit=%d units=%d grid=%d w_stages=%d b_stages=%d pitch=%d\n",
                 a.type, p.m, p.n, p.k, p.cluster, p.n_sub, p.ksplit, num_units, grid, p.w_stages, p.b_stages, p.w_pitch);
     }
-    {
+    if (moe) {
+        MoeRouteParams rp{};
+        rp.ids = moe->ids; rp.ids_nb1 = moe->ids_nb1;
+        rp.n_tokens = (int) moe->n_tokens; rp.n_used = (int) moe->n_used; rp.n_expert = (int) moe->n_expert;
+        rp.t = mt;
+        moe_route<<<1, 1024, (size_t) moe->n_expert * sizeof(int), st>>>(rp);
+        MoePackParams mp{};
+        mp.act = moe->act; mp.out = (uint8_t *) workspace + mt.bytes; mp.t = mt;
+        mp.k_chunks = p.k_chunks; mp.n_used = (int) moe->n_used; mp.b_bcast = moe->b_bcast ? 1 : 0; mp.max_tiles = moe_max_tiles;
+        mp.a_nb1 = moe->a_nb1; mp.a_nb2 = moe->a_nb2;
+        moe_pack_act<<<sms * 8, 256, 0, st>>>(mp);
+    } else {
         if (p.ksplit > 1) {
             pp.zero_dst = a.dst; pp.m = (int) a.m;
             pp.d_nb1 = a.d_nb1; pp.d_nb2 = a.d_nb2; pp.d_nb3 = a.d_nb3;

@@ -95,3 +95,34 @@ def test_mmq_baseline_sizes(t, m, k):
     # the tiled rows repeat every 512: identical weight rows must give identical bits (fixed accumulation order)
     if m >= 1024:
         assert torch.equal(got[:, :512], got[:, 512:1024])
+
+
+@pytest.mark.parametrize("t", [refs.Q4_0, refs.Q8_0, refs.MXFP4, refs.Q4_K, refs.Q6_K, refs.Q5_1], ids=lambda t: refs.NAMES[t])
+@pytest.mark.parametrize("n_tokens,n_expert,n_used,bcast,m,k", [(40, 8, 4, True, 257, 512), (300, 6, 2, False, 128, 256),
+                                                                (9, 4, 4, True, 64, 1024), (130, 32, 4, True, 96, 2880)])
+def test_moe_through_mmq(t, n_tokens, n_expert, n_used, bcast, m, k):
+    """MUL_MAT_ID with many (token, slot) rows: rows grouped per expert on the device, each expert's rows through the
+    tensor-core kernel; against the oracle's mul_mat_id (ids a strided view, experts with zero / >256 rows)"""
+    import b200q
+    import torch
+    if k % refs.BLCK[t][0]:
+        pytest.skip("k not a multiple of the block size")
+    w = refs.make_weights(t, n_expert * m, k, seed=900 + t)
+    b_ne1 = 1 if bcast else n_used
+    b = refs.uniform_weights(n_tokens * b_ne1, k, seed=901).reshape(n_tokens, b_ne1, k)
+    rng = np.random.default_rng(902 + n_tokens)
+    # skewed routing: expert 0 is popular (more than one 256-column tile at 300 tokens), the last expert never chosen
+    ids_full = np.stack([rng.permutation(n_expert - 1) for _ in range(n_tokens)]).astype(np.int32)
+    for r in range(0, n_tokens, 2):
+        j = int(np.where(ids_full[r] == 0)[0][0])
+        ids_full[r, j], ids_full[r, 0] = ids_full[r, 0], 0
+    ids_full = np.concatenate([ids_full, np.zeros((n_tokens, 1), np.int32)], axis=1)  # a wider tensor: stride n_expert
+    want = refs.orc_mul_mat_id(t, w.reshape(n_expert, m, -1), b, ids_full, n_used)
+    ids_dev = torch.from_numpy(ids_full).cuda()[:, :n_used]
+    wt = b200q.upload(t, (n_expert, m, k), w)
+    got = b200q.mul_mat_id(wt, torch.from_numpy(b).cuda(), ids_dev, n_used=n_used)
+    got2 = b200q.mul_mat_id(wt, torch.from_numpy(b).cuda(), ids_dev, n_used=n_used)
+    assert torch.equal(got, got2)  # reproducible
+    got = got.cpu().numpy()
+    assert np.isfinite(got).all()
+    assert refs.nmse(got, want) <= MAX_NMSE
