@@ -202,11 +202,12 @@ int launch_gemv(GemvPlan & plan, int type, int ncols, uint32_t flags, cudaStream
 
 // ---- K-quant decode GEMV (gemv_kq.cu): n = 1, q4_K / q6_K, up to KQ_MAX_SEG matrices sharing the activations ------
 bool plan_kq(KqParams & p, int & grid, int & smem, int type, int64_t k, int nseg, const void * const * w, float * const * dst,
-             const int64_t * m, const float * act, const DevInfo & di) {
+             const int64_t * m, const float * act, const DevInfo & di, const int32_t * ids = nullptr, long long expert_stride = 0,
+             long long act_seg_stride = 0) {
     if (!kq_kernel_for(type)) return false;
     const bool kquant = type == T_Q4_K || type == T_Q6_K;
     const int  unit   = kquant ? 256 : 32;  // elements per unit of lane work (super-block | block)
-    if (nseg < 1 || nseg > KQ_MAX_SEG || k <= 0 || k % unit) return false;
+    if (nseg < 1 || nseg > kq_max_segments(ids != nullptr) || k <= 0 || k % unit) return false;
     static const bool off   = getenv("B200Q_NO_KQ") != nullptr;
     static const bool off32 = getenv("B200Q_NO_KQ32") != nullptr;
     if (off || (!kquant && off32)) return false;
@@ -228,6 +229,13 @@ bool plan_kq(KqParams & p, int & grid, int & smem, int type, int64_t k, int nseg
         p.off_bs16  = p.off_bs32 = 0;
         p.off_stage = round_up(p.off_dx + p.nsb * 8, 128);
     }
+    if (act_seg_stride) {  // MoE down projection: one quantized activation image per segment
+        if ((act_seg_stride * 4) % 16) return false;
+        p.act_smem_stride = round_up(p.off_stage - p.off_q, 128);
+        p.off_stage += (nseg - 1) * p.act_smem_stride;
+    }
+    if (ids && kquant && expert_stride % 16) return false;
+    p.ids = ids; p.expert_stride = expert_stride; p.act_seg_stride = act_seg_stride;
     const int work = kquant ? p.nsb : std::max(1, p.nsb / 8);  // lane work per row in super-block equivalents
     // lanes per row: few lanes = many rows per stage = less per-stage overhead, but two launches must stay co-resident
     // per SM (the next one prefetches under this one's tail) with at least ~1.25 slots per warp in flight
@@ -268,12 +276,12 @@ bool plan_kq(KqParams & p, int & grid, int & smem, int type, int64_t k, int nseg
 }
 
 int launch_kq(KqParams & p, int grid, int smem, int type, uint32_t flags, cudaStream_t st) {
-    kq_kernel_t fn = kq_kernel_for(type);
+    kq_kernel_t fn = kq_kernel_for(type, p.ids != nullptr);
     if (!fn) return fail(B200Q_ENOTSUP, "gemv_kq: unsupported type %d", type);
     const DevInfo & di = dev_info();
     if (int rc = ensure_smem_attr((const void *) fn, di.max_smem)) return rc;
     const bool pdl   = !(flags & B200Q_FLAG_NO_PDL);
-    p.early_prefetch = pdl && (flags & B200Q_FLAG_WEIGHTS_IMMUTABLE) ? 1 : 0;
+    p.early_prefetch = pdl && (flags & B200Q_FLAG_WEIGHTS_IMMUTABLE) && !p.ids ? 1 : 0;  // ids belong to an earlier kernel
     static const bool debug = getenv("B200Q_DEBUG") != nullptr;
     if (debug) {
         fprintf(stderr, "[b200q] gemv_kq type=%d k=%d nseg=%d m0=%d grid=%d smem=%d lpr=%d rps=%d stage_bytes=%d S=%d stages=%d pdl=%d early=%d\n",
@@ -611,6 +619,26 @@ int b200q_mul_mat_id(const b200q_mul_mat_id_args * a, const void * as, const flo
         std::string err;
         if (int rc = mmq_moe_launch(q, workspace, (cudaStream_t) stream, di.sms, err)) return fail(rc, "%s", err.c_str());
         return 0;
+    }
+
+    // decode (one token): the selected experts are the segments of ONE launch of the ring kernel
+    static const bool no_kq_moe = getenv("B200Q_NO_KQ_MOE") != nullptr;
+    if (a->n_tokens == 1 && a->n_used <= KQ_MAX_SEG && a->nb01 == b200q_row_size(a->type, a->k) && !no_kq_moe &&
+        (a->b_ne1 == 1 || a->nb11 % 4 == 0) && a->nb1 % 4 == 0) {
+        KqParams     kq{};
+        int          grid = 0, smem = 0;
+        const void * wl[KQ_MAX_SEG];
+        float *      dl[KQ_MAX_SEG];
+        int64_t      ml[KQ_MAX_SEG];
+        for (int g = 0; g < a->n_used; ++g) {
+            wl[g] = as;  // expert 0; the kernel adds ids[g] * nb02
+            dl[g] = (float *) ((char *) dst + (size_t) g * a->nb1);
+            ml[g] = a->m;
+        }
+        if (plan_kq(kq, grid, smem, a->type, a->k, (int) a->n_used, wl, dl, ml, b, di, ids, (long long) a->nb02,
+                    a->b_ne1 == 1 ? 0 : (long long) (a->nb11 / 4))) {
+            return launch_kq(kq, grid, smem, a->type, a->flags, (cudaStream_t) stream);
+        }
     }
 
     // one GEMV channel per (token, slot); expert ids are read on the device (no host round trip, cf. mmq.cu:161)

@@ -111,7 +111,7 @@ __device__ __forceinline__ int dp2a_hi_ss(int a, int b, int c) {
 //   bs16: 16 x int16 at off_bs16 + 32 s              (sums of q over 16 values)
 //   bs32:  8 x int16 at off_bs32 + 16 s              (sums over 32 values)
 // One warp per super-block per step; lane l holds values 8l .. 8l+7 (coalesced 1 KB per warp).
-__device__ __forceinline__ void quantize_act(const KqParams & p, uint32_t sb, int warp, int lane) {
+__device__ __forceinline__ void quantize_act(const KqParams & p, const float * act, uint32_t sb, int warp, int lane) {
     constexpr int QB = 4;
     for (int s0 = warp; s0 < p.nsb; s0 += NW * QB) {
         float4 x[QB][2];
@@ -119,7 +119,7 @@ __device__ __forceinline__ void quantize_act(const KqParams & p, uint32_t sb, in
         for (int b = 0; b < QB; ++b) {
             const int s = s0 + b * NW;
             if (s < p.nsb) {
-                const float4 * src = (const float4 *) (p.act + (size_t) s * 256 + lane * 8);
+                const float4 * src = (const float4 *) (act + (size_t) s * 256 + lane * 8);
                 x[b][0] = __ldg(src);
                 x[b][1] = __ldg(src + 1);
             }
@@ -284,14 +284,14 @@ template <> struct SbDot<T_Q6_K> {
 //        read consecutive 16-byte chunks, conflict-free)
 //   ds : float2 (d, d * sum q) at off_dx + 8 b
 // One warp per 256 values per step; lane l holds values 8l .. 8l+7, 4 lanes per block.
-__device__ __forceinline__ void quantize_act32(const KqParams & p, uint32_t sb, int warp, int lane) {
+__device__ __forceinline__ void quantize_act32(const KqParams & p, const float * act, uint32_t sb, int warp, int lane) {
     const int nb = p.nsb;  // 32-element blocks per row
     for (int g = warp; g * 8 < nb; g += NW) {
         const int  b     = g * 8 + (lane >> 2);
         const bool valid = b < nb;  // uniform over the 4 lanes of a block
         float4     x0 = make_float4(0.f, 0.f, 0.f, 0.f), x1 = x0;
         if (valid) {
-            const float4 * src = (const float4 *) (p.act + (size_t) g * 256 + lane * 8);
+            const float4 * src = (const float4 *) (act + (size_t) g * 256 + lane * 8);
             x0 = __ldg(src);
             x1 = __ldg(src + 1);
         }
@@ -476,11 +476,11 @@ template <int T> struct IsKQuant { static constexpr bool value = T == T_Q4_K || 
 struct StageInfo {
     int g, r0, nrows;
 };
-__device__ __forceinline__ StageInfo stage_info(const KqParams & p, int t) {
+template <int NSEG> __device__ __forceinline__ StageInfo stage_info(const KqParams & p, int t) {
     StageInfo si;
     si.g = 0;
 #pragma unroll
-    for (int i = 1; i < KQ_MAX_SEG; ++i) {
+    for (int i = 1; i < NSEG; ++i) {
         if (i < p.nseg && t >= p.seg[i].stage0) si.g = i;
     }
     si.r0    = (t - p.seg[si.g].stage0) * p.rows_per_stage;
@@ -488,7 +488,21 @@ __device__ __forceinline__ StageInfo stage_info(const KqParams & p, int t) {
     return si;
 }
 
-template <int T> __global__ void __launch_bounds__(NTHREADS, 2) gemv_kq_kernel(const KqParams p) {
+__device__ __forceinline__ const uint8_t * seg_ptr(const uint8_t * const (&w)[KQ_MAX_SEG], int g) {
+    const uint8_t * r = w[0];
+#pragma unroll
+    for (int i = 1; i < KQ_MAX_SEG; ++i) {
+        if (g == i) r = w[i];
+    }
+    return r;
+}
+
+// MOE = false: up to KQ_PLAIN_SEG matrices sharing one activation vector; MOE = true: up to KQ_MAX_SEG experts chosen by
+// ids[], optionally one activation vector per expert (kept out of the plain instantiation: its prologue is on the
+// latency chain of every decode launch)
+constexpr int KQ_PLAIN_SEG = 4;
+template <int T, bool MOE> __global__ void __launch_bounds__(NTHREADS, 2) gemv_kq_kernel(const KqParams p) {
+    constexpr int NSEG = MOE ? KQ_MAX_SEG : KQ_PLAIN_SEG;
     const uint32_t sb   = smem_u32(kq_smem);
     const int      warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int      S    = p.nstages;
@@ -515,14 +529,21 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 2) gemv_kq_kernel(c
     // (A ring shared by all warps let a fast warp test a slot's barrier one phase early — parity ABA — when bulk copies
     // completed out of order: stale data, a desynchronised ring, rare hangs / launch failures.)  No empty-barriers and no
     // producer hop: the warp that finishes a slot refills it at once.
+    // MoE: the experts are chosen by ids[] (written by an earlier kernel of the stream: read only after the wait)
+    const uint8_t * segw[KQ_MAX_SEG];
+    if (MOE) {
+#pragma unroll
+        for (int g = 0; g < KQ_MAX_SEG; ++g) segw[g] = p.seg[g].w;
+    }
+    auto seg_w = [&](int g) -> const uint8_t * { return MOE ? seg_ptr(segw, g) : p.seg[g].w; };
     const uint64_t pol    = policy_evict_first();
     const int      nmine  = warp < NA && T0 + warp < T1 ? (T1 - T0 - warp + NA - 1) / NA : 0;  // stages of this warp
     auto           issue  = [&](int i) {
         const int       t     = T0 + warp + i * NA, slot = slot0 + i % D;
-        const StageInfo si    = stage_info(p, t);
+        const StageInfo si    = stage_info<NSEG>(p, t);
         // rows of the 32-element block formats need not be 16-byte multiples: copy the aligned window around the rows
         // (the over-read stays inside the tensor or its allocation slack, include/b200q.h)
-        const uint8_t * src   = p.seg[si.g].w + (size_t) si.r0 * p.row_bytes;
+        const uint8_t * src   = seg_w(si.g) + (size_t) si.r0 * p.row_bytes;
         const uint32_t  lead  = (uint32_t) ((uintptr_t) src & 15);
         const uint32_t  bytes = (lead + (uint32_t) si.nrows * (uint32_t) p.row_bytes + 15u) & ~15u;
         const uint32_t  full  = sb + OFF_FULL + 8 * slot;
@@ -533,11 +554,20 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 2) gemv_kq_kernel(c
         for (int i = 0; i < min(D, nmine); ++i) issue(i);  // immutable weights: stream them under the previous kernel's tail
     }
     pdl_wait();  // the activations (and dst) belong to the previous kernels of the stream
+    if (MOE && p.ids) {
+#pragma unroll
+        for (int g = 0; g < KQ_MAX_SEG; ++g) {
+            if (g < p.nseg) segw[g] = p.seg[g].w + (long long) __ldg(p.ids + g) * p.expert_stride;
+        }
+    }
     if (!p.early_prefetch && lane == 0) {
         for (int i = 0; i < min(D, nmine); ++i) issue(i);
     }
-    if (IsKQuant<T>::value) quantize_act(p, sb, warp, lane);
-    else quantize_act32(p, sb, warp, lane);
+    for (int g = 0; g < (MOE && p.act_smem_stride ? p.nseg : 1); ++g) {
+        const float * av = p.act + (size_t) g * p.act_seg_stride;
+        if (IsKQuant<T>::value) quantize_act(p, av, sb + (uint32_t) (g * p.act_smem_stride), warp, lane);
+        else quantize_act32(p, av, sb + (uint32_t) (g * p.act_smem_stride), warp, lane);
+    }
     __syncthreads();
 
     const int lpr  = p.lpr;
@@ -545,15 +575,16 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 2) gemv_kq_kernel(c
     const int lrow = lane / lpr;
     for (int i = 0; i < nmine; ++i) {
         const int       t = T0 + warp + i * NA, slot = slot0 + i % D, use = i / D;
-        const StageInfo si = stage_info(p, t);
+        const StageInfo si = stage_info<NSEG>(p, t);
         mbar_wait_dbg(sb + OFF_FULL + 8 * slot, use & 1, 2, i);
-        const uint32_t lead = (uint32_t) ((uintptr_t) (p.seg[si.g].w + (size_t) si.r0 * p.row_bytes) & 15);
+        const uint32_t lead = (uint32_t) ((uintptr_t) (seg_w(si.g) + (size_t) si.r0 * p.row_bytes) & 15);
+        const uint32_t sba  = MOE ? sb + (uint32_t) (si.g * p.act_smem_stride) : sb;  // this segment's quantized activations
         const uint32_t row  = sb + p.off_stage + (uint32_t) slot * p.stage_bytes + lead + (uint32_t) lrow * (uint32_t) p.row_bytes;
         float acc = 0.0f;
         if (lrow < si.nrows) {
             for (int s = sub; s < p.nsb; s += lpr) {
-                if constexpr (IsKQuant<T>::value) acc += SbDot<T>::run(p, sb, row, s);
-                else acc += B32Dot<T>::run(p, sb, row, s);
+                if constexpr (IsKQuant<T>::value) acc += SbDot<T>::run(p, sba, row, s);
+                else acc += B32Dot<T>::run(p, sba, row, s);
             }
         }
         __syncwarp();  // every lane is done reading the slot
@@ -573,19 +604,21 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 2) gemv_kq_kernel(c
 
 }  // namespace
 
-kq_kernel_t kq_kernel_for(int type) {
+template <bool MOE> static kq_kernel_t kq_kernel_sel(int type) {
     switch (type) {
-        case T_Q4_K: return gemv_kq_kernel<T_Q4_K>;
-        case T_Q6_K: return gemv_kq_kernel<T_Q6_K>;
-        case T_Q4_0: return gemv_kq_kernel<T_Q4_0>;
-        case T_Q4_1: return gemv_kq_kernel<T_Q4_1>;
-        case T_Q5_0: return gemv_kq_kernel<T_Q5_0>;
-        case T_Q5_1: return gemv_kq_kernel<T_Q5_1>;
-        case T_Q8_0: return gemv_kq_kernel<T_Q8_0>;
-        case T_MXFP4: return gemv_kq_kernel<T_MXFP4>;
+        case T_Q4_K: return gemv_kq_kernel<T_Q4_K, MOE>;
+        case T_Q6_K: return gemv_kq_kernel<T_Q6_K, MOE>;
+        case T_Q4_0: return gemv_kq_kernel<T_Q4_0, MOE>;
+        case T_Q4_1: return gemv_kq_kernel<T_Q4_1, MOE>;
+        case T_Q5_0: return gemv_kq_kernel<T_Q5_0, MOE>;
+        case T_Q5_1: return gemv_kq_kernel<T_Q5_1, MOE>;
+        case T_Q8_0: return gemv_kq_kernel<T_Q8_0, MOE>;
+        case T_MXFP4: return gemv_kq_kernel<T_MXFP4, MOE>;
         default: return nullptr;
     }
 }
+kq_kernel_t kq_kernel_for(int type, bool moe) { return moe ? kq_kernel_sel<true>(type) : kq_kernel_sel<false>(type); }
+int         kq_max_segments(bool moe) { return moe ? KQ_MAX_SEG : KQ_PLAIN_SEG; }
 void kq_set_hang_buffer(unsigned long long * host_mapped) {
     cudaMemcpyToSymbol(g_kq_hang, &host_mapped, sizeof(host_mapped));
 }

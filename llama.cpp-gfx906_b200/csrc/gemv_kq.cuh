@@ -5,7 +5,7 @@
 
 namespace b200q {
 
-constexpr int KQ_MAX_SEG = 4;
+constexpr int KQ_MAX_SEG = 8;
 
 struct KqSegment {
     const uint8_t * w;    // [m][row_bytes] quantized rows, contiguous, 16-byte aligned
@@ -28,10 +28,17 @@ struct KqParams {
     // shared-memory offsets
     int           off_q, off_dx, off_bs16, off_bs32, off_stage;
     int           early_prefetch;  // weights immutable: stream them before griddepcontrol.wait
+    // MUL_MAT_ID decode (one token): segment g multiplies expert ids[g]'s matrix; every segment may have its own
+    // activation vector (b->ne[1] == n_used) with its own quantized image in shared memory
+    const int32_t * ids;           // nullptr: plain segments
+    long long       expert_stride; // bytes between expert matrices (seg[g].w holds the base of expert 0)
+    long long       act_seg_stride;  // floats between the segments' activation vectors (0: shared)
+    int             act_smem_stride; // bytes between the segments' quantized activation images (0: shared)
 };
 
 typedef void (*kq_kernel_t)(const KqParams);
-kq_kernel_t kq_kernel_for(int type);
+kq_kernel_t kq_kernel_for(int type, bool moe = false);
+int         kq_max_segments(bool moe);
 void        kq_set_hang_buffer(unsigned long long * host_mapped);  // development aid
 int         kq_threads();
 int         kq_consumer_warps();
