@@ -284,7 +284,9 @@ template <> struct SbDot<T_Q6_K> {
 //        read consecutive 16-byte chunks, conflict-free)
 //   ds : float2 (d, d * sum q) at off_dx + 8 b
 // One warp per 256 values per step; lane l holds values 8l .. 8l+7, 4 lanes per block.
-__device__ __forceinline__ void quantize_act32(const KqParams & p, const float * act, uint32_t sb, int warp, int lane) {
+// ILV (mxfp4): the 8 words of a block are stored as (e, e+16, e+1, e+17) for e = 0, 2, .. 14 — the order in which a 16-bit
+// slice of the packed nibbles (lo(qs[e]), hi(qs[e]), lo(qs[e+1]), hi(qs[e+1])) indexes a PRMT table look-up
+template <bool ILV> __device__ __forceinline__ void quantize_act32(const KqParams & p, const float * act, uint32_t sb, int warp, int lane) {
     const int nb = p.nsb;  // 32-element blocks per row
     for (int g = warp; g * 8 < nb; g += NW) {
         const int  b     = g * 8 + (lane >> 2);
@@ -311,12 +313,26 @@ __device__ __forceinline__ void quantize_act32(const KqParams & p, const float *
         }
         sum += __shfl_xor_sync(0xffffffffu, sum, 1);
         sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+        if (ILV) {
+            const uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t) q[3] << 24);
+            const uint32_t w1 = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t) q[7] << 24);
+            // lanes 0,1 of a block hold elements 0..15, lanes 2,3 elements 16..31: fetch the partner half
+            const uint32_t h0 = __shfl_xor_sync(0xffffffffu, w0, 2), h1 = __shfl_xor_sync(0xffffffffu, w1, 2);
+            if (valid && (lane & 2) == 0) {
+                const uint32_t o0 = __byte_perm(w0, h0, 0x5140), o1 = __byte_perm(w0, h0, 0x7362);
+                const uint32_t o2 = __byte_perm(w1, h1, 0x5140), o3 = __byte_perm(w1, h1, 0x7362);
+                const uint32_t qa = sb + p.off_q + (uint32_t) (((lane & 1) * nb + b) * 16);
+                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(qa), "r"(o0), "r"(o1), "r"(o2), "r"(o3) : "memory");
+            }
+        }
         if (valid) {
             const uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t) q[3] << 24);
             const uint32_t w1 = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t) q[7] << 24);
-            const int      c  = (lane & 3) >> 1;
-            const uint32_t qa = sb + p.off_q + (uint32_t) ((c * nb + b) * 16 + (lane & 1) * 8);
-            asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(qa), "r"(w0), "r"(w1) : "memory");
+            if (!ILV) {
+                const int      c  = (lane & 3) >> 1;
+                const uint32_t qa = sb + p.off_q + (uint32_t) ((c * nb + b) * 16 + (lane & 1) * 8);
+                asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(qa), "r"(w0), "r"(w1) : "memory");
+            }
             if ((lane & 3) == 0) {
                 asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(sb + p.off_dx + (uint32_t) b * 8), "f"(d), "f"(d * (float) sum) : "memory");
             }
@@ -452,22 +468,37 @@ template <> struct B32Dot<T_Q8_0> {
         return half_bits_to_float((uint16_t) (w[0] & 0xffffu)) * (ds.x * (float) sumi);
     }
 };
+__device__ __forceinline__ uint32_t prmt_(uint32_t a, uint32_t b, uint32_t sel) {  // bit 3 of a selector nibble: sign-replicate
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+    return d;
+}
 template <> struct B32Dot<T_MXFP4> {
     static constexpr int BLK = 17;
+    // Each 16-bit slice of the nibble words IS a PRMT selector: the low 3 bits of a nibble index the magnitude table
+    // (doubled E2M1 code points, ggml-common.h kvalues_mxfp4), bit 3 (the fp4 sign) turns the look-up into a sign
+    // replication that yields the negative-lane mask.  Magnitudes split into a positive and a negative word, two
+    // unsigned dp4a each against activations stored in the matching interleaved order (quantize_act32<true>).
     static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int b) {
         uint32_t w[5];  // [e | qs0 qs1 qs2] ... [qs15 | next]
         ldsu_n<5>(row + (uint32_t) b * BLK, w);
         int a[8]; float2 ds;
         act_block<T_MXFP4>(p, sb, b, a, ds);
-        int sumi = 0;
+        const uint32_t t0 = 0x03020100u, t1 = 0x0C080604u, sg = 0x80808080u;
+        int sp = 0, sn = 0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            uint32_t lo, hi;
-            mxfp4_words(__funnelshift_r(w[i], w[i + 1], 8), lo, hi);
-            sumi = dp4a_ss((int) lo, a[i], sumi);
-            sumi = dp4a_ss((int) hi, a[4 + i], sumi);
+            const uint32_t q  = __funnelshift_r(w[i], w[i + 1], 8);
+            const uint32_t q7 = q & 0x77777777u;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const uint32_t mag = prmt_(t0, t1, q7 >> (16 * h));
+                const uint32_t neg = mag & prmt_(sg, sg, q >> (16 * h)) & 0x7F7F7F7Fu;  // 0xFF where the sign is set, 0x80 elsewhere
+                sp = dp4a_us(mag ^ neg, a[2 * i + h], sp);
+                sn = dp4a_us(neg, a[2 * i + h], sn);
+            }
         }
-        return e8m0_half_to_float((uint8_t) (w[0] & 0xff)) * (ds.x * (float) sumi);
+        return e8m0_half_to_float((uint8_t) (w[0] & 0xff)) * (ds.x * (float) (sp - sn));
     }
 };
 
@@ -566,7 +597,7 @@ template <int T, bool MOE> __global__ void __launch_bounds__(NTHREADS, 2) gemv_k
     for (int g = 0; g < (MOE && p.act_smem_stride ? p.nseg : 1); ++g) {
         const float * av = p.act + (size_t) g * p.act_seg_stride;
         if (IsKQuant<T>::value) quantize_act(p, av, sb + (uint32_t) (g * p.act_smem_stride), warp, lane);
-        else quantize_act32(p, av, sb + (uint32_t) (g * p.act_smem_stride), warp, lane);
+        else quantize_act32<T == T_MXFP4>(p, av, sb + (uint32_t) (g * p.act_smem_stride), warp, lane);
     }
     __syncthreads();
 
