@@ -247,7 +247,16 @@ def main_b200(args):
     g = torch.Generator(device="cuda")
     g.manual_seed(4321)
     act_dev = torch.rand(k_off[-1], device="cuda", generator=g) * 2 - 1          # all activation vectors, f32
-    out_dev = torch.zeros(m_off[-1], device="cuda")                              # all (gathered) results, f32
+    # row split (N > 1): "peer" = the decode kernel stores its rows into every rank's result buffer itself (NVLink peer
+    # stores in the epilogue, one small all-reduce per step as the completion fence); "nccl" = all-gather per matmul
+    split_mode = os.environ.get("B200Q_ROWSPLIT", "peer") if world > 1 else "single"
+    peer_dst = None
+    if split_mode == "peer":
+        peer_dst = rowsplit.PeerDst(m_off[-1], rank, world)
+        out_dev = peer_dst.tensor
+        out_dev.zero_()
+    else:
+        out_dev = torch.zeros(m_off[-1], device="cuda")                          # all (gathered) results, f32
     act_host = act_dev.cpu().pin_memory()
     out_host = torch.empty(m_off[-1], dtype=torch.float32).pin_memory()
 
@@ -258,7 +267,7 @@ def main_b200(args):
     for i, o in enumerate(ops):
         leaf = o.name.split(".")[-1]
         prev = launches[-1] if launches else None
-        if (world == 1 and prev is not None and len(prev) < 4 and ops[prev[0]].qtype == o.qtype and ops[prev[0]].k == o.k
+        if (split_mode != "nccl" and prev is not None and len(prev) < 4 and ops[prev[0]].qtype == o.qtype and ops[prev[0]].k == o.k
                 and ops[prev[0]].name.rsplit(".", 1)[0] == o.name.rsplit(".", 1)[0]
                 and any(leaf in grp and ops[prev[0]].name.split(".")[-1] in grp for grp in SHARED)):
             prev.append(i)
@@ -273,9 +282,13 @@ def main_b200(args):
             if world == 1:
                 b200q.mul_mat_group([shards[j].shard for j in idx], a,
                                     outs=[out_dev[m_off[j]:m_off[j + 1]].view(1, ops[j].m) for j in idx])
+            elif split_mode == "peer":
+                rowsplit.mul_mat_row_split_peer([shards[j] for j in idx], a, peer_dst, [m_off[j] for j in idx])
             else:
                 # this rank's rows + NCCL all-gather of the slices (rowsplit.py)
                 rowsplit.mul_mat_row_split(shards[i], a, out=out_dev[m_off[i]:m_off[i + 1]].view(1, ops[i].m))
+        if peer_dst is not None:
+            peer_dst.fence()  # every rank's rows have landed in every rank's buffer
 
     for _ in range(2):
         run_pass()
@@ -373,7 +386,9 @@ def main_b200(args):
         "config": {"workload": args.workload + " decode GEMV set, n=1, tg (one step = the 225 matmuls of one token)",
                    "n_matmuls": desc["n_matmuls"], "weight_bytes": desc["weight_bytes"], "shapes": desc["shapes"],
                    "l2": "inputs larger than L2 (4.6 GB of distinct weights per step), no flush needed",
-                   "parallelism": "single GPU" if world == 1 else f"row-split x{world} + NCCL all-gather per matmul",
+                   "parallelism": "single GPU" if world == 1 else (
+                       f"row-split x{world}, result rows stored to all peers by the kernel (NVLink), one all-reduce fence per step"
+                       if split_mode == "peer" else f"row-split x{world} + NCCL all-gather per matmul"),
                    "tg_tok_s_matmul_only": 1e3 / ms_dev},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e, "results_finite": finite,

@@ -149,6 +149,18 @@ typedef struct b200q_mul_mat_group_args {
 B200Q_API int b200q_mul_mat_group(const b200q_mul_mat_group_args * a, const void * const * w, const float * act,
                                   float * const * dst, void * stream);
 
+/* ---- row split over the GPUs of one box, one process per GPU (replaces the split buffer's cudaMemcpyPeerAsync of
+ *      the dst slices, ggml-cuda.cu:1700-1740): the decode kernel stores every result row into the dst buffer of each
+ *      peer GPU as well (NVLink peer stores in the epilogue), so no collective follows the matmul.  peer_delta[r] =
+ *      (this process's mapping of peer r's dst buffer) - (this GPU's own dst buffer), in bytes; the buffers have the
+ *      same layout.  The stores are complete when the kernel is: consumers on the peer need a stream-ordered
+ *      cross-GPU fence (e.g. one small collective per step).  b200q_ipc_* exchange the mappings (cudaIpc). ---------- */
+B200Q_API int b200q_mul_mat_group_peers(const b200q_mul_mat_group_args * a, const void * const * w, const float * act,
+                                        float * const * dst, int n_peers, const int64_t * peer_delta, void * stream);
+B200Q_API int b200q_ipc_export(void * dev_ptr, void * handle64);          /* dev_ptr from b200q_malloc; 64-byte handle */
+B200Q_API int b200q_ipc_import(const void * handle64, void ** dev_ptr);   /* maps the peer's buffer, enables peer access */
+B200Q_API int b200q_ipc_close(void * dev_ptr);
+
 /* ---- MUL_MAT_ID (MoE) ------------------------------------------------------------------------ */
 /* dst[t][s][:] = W[ids[t][s]] . b[t][s or 0][:]     (ggml_mul_mat_id, ggml.c:3056-3080) */
 typedef struct b200q_mul_mat_id_args {

@@ -31,7 +31,8 @@ FLAG_WEIGHTS_IMMUTABLE, FLAG_FORCE_GEMV, FLAG_FORCE_MMQ, FLAG_NO_PDL = 1, 2, 4, 
 EXPORTS = [
     "b200q_version", "b200q_last_error", "b200q_device_count", "b200q_device_info", "b200q_blck_size",
     "b200q_type_size", "b200q_row_size", "b200q_type_supported", "b200q_dequantize", "b200q_get_rows",
-    "b200q_mul_mat_workspace", "b200q_mul_mat", "b200q_mul_mat_group", "b200q_mul_mat_id_workspace", "b200q_mul_mat_id",
+    "b200q_mul_mat_workspace", "b200q_mul_mat", "b200q_mul_mat_group", "b200q_mul_mat_group_peers", "b200q_ipc_export",
+    "b200q_ipc_import", "b200q_ipc_close", "b200q_mul_mat_id_workspace", "b200q_mul_mat_id",
     "b200q_mul_mat_host", "b200q_set_device", "b200q_malloc", "b200q_free", "b200q_memset", "b200q_memcpy",
     "b200q_stream_create", "b200q_stream_destroy", "b200q_stream_synchronize", "b200q_host_alloc", "b200q_host_free",
 ]
@@ -233,6 +234,38 @@ def mul_mat(w: QTensor, act, out=None, flags: int = FLAG_WEIGHTS_IMMUTABLE):
     _check(lib().b200q_mul_mat(C.byref(a), w.data.data_ptr(), act.data_ptr(), out.data_ptr(),
                                ws.data_ptr() if ws is not None else None, ws_n, _stream()), "b200q_mul_mat")
     return out
+
+
+def mul_mat_group_ptr(ws, act, dst_ptrs, peer_deltas=(), flags: int = FLAG_WEIGHTS_IMMUTABLE):
+    """mul_mat_group on raw dst device pointers (row split: slices of a b200q_malloc'ed, IPC-shared buffer); with
+    peer_deltas every result row is also stored into the peers' buffers (b200q_mul_mat_group_peers)."""
+    torch = _torch()
+    assert 1 <= len(ws) <= 4 and len(dst_ptrs) == len(ws)
+    assert act.dtype == torch.float32 and act.is_cuda and act.numel() == ws[0].k and act.is_contiguous()
+    a = MulMatGroupArgs(ws[0].qtype, ws[0].k, len(ws), (C.c_int64 * 4)(*([w.m for w in ws] + [0] * (4 - len(ws)))), flags)
+    wp = (C.c_void_p * len(ws))(*[w.data.data_ptr() for w in ws])
+    dp = (C.c_void_p * len(ws))(*[int(d) for d in dst_ptrs])
+    pd = (C.c_int64 * max(1, len(peer_deltas)))(*([int(d) for d in peer_deltas] or [0]))
+    _check(lib().b200q_mul_mat_group_peers(C.byref(a), wp, C.c_void_p(act.data_ptr()), dp, len(peer_deltas), pd, _stream()),
+           "b200q_mul_mat_group_peers")
+
+
+def device_malloc(nbytes: int) -> int:
+    p = C.c_void_p()
+    _check(lib().b200q_malloc(C.byref(p), C.c_size_t(nbytes)), "b200q_malloc")
+    return int(p.value)
+
+
+def ipc_export(dev_ptr: int) -> bytes:
+    h = C.create_string_buffer(64)
+    _check(lib().b200q_ipc_export(C.c_void_p(dev_ptr), h), "b200q_ipc_export")
+    return h.raw
+
+
+def ipc_import(handle: bytes) -> int:
+    p = C.c_void_p()
+    _check(lib().b200q_ipc_import(C.c_char_p(handle), C.byref(p)), "b200q_ipc_import")
+    return int(p.value)
 
 
 def mul_mat_group(ws, act, outs=None, flags: int = FLAG_WEIGHTS_IMMUTABLE):

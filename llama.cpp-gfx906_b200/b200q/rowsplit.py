@@ -131,3 +131,54 @@ def mul_mat_row_split(w: RowSplitWeight, act, out=None, group=None, compute: Cal
         if nr > 0:
             out[:, r0:r0 + nr] = stage[r, :, :nr]
     return out
+
+
+class PeerDst:
+    """Row split without a collective per matmul: every rank owns one b200q_malloc'ed result buffer of the same layout,
+    maps the buffers of its peers (cudaIpc), and the decode kernel stores each result row into all of them in its
+    epilogue (b200q_mul_mat_group_peers; NVLink peer stores).  ``fence()`` is the stream-ordered cross-GPU completion
+    point (one tiny NCCL all-reduce): after it every rank's buffer holds every rank's rows.  Replaces the reference's
+    per-op copy of the dst slices to the main device (ggml-cuda.cu:1700-1740)."""
+
+    def __init__(self, n_floats: int, rank: int, world: int, dist=None, group=None):
+        import torch
+        from . import device_malloc, ipc_export, ipc_import
+        if dist is None:
+            import torch.distributed as dist
+        self.rank, self.world, self.n, self.dist, self.group = rank, world, int(n_floats), dist, group
+        self.ptr = device_malloc(self.n * 4 + 256)
+        handles = [None] * world
+        dist.all_gather_object(handles, ipc_export(self.ptr), group=group)
+        self.peer_ptrs = [self.ptr if r == rank else ipc_import(handles[r]) for r in range(world)]
+        self.deltas = [self.peer_ptrs[r] - self.ptr for r in range(world) if r != rank]
+        self._flag = torch.zeros(1, device="cuda")
+        # a torch view of the local buffer (no ownership: the memory lives until the process exits)
+        self.tensor = _as_tensor(self.ptr, self.n)
+
+    def addr(self, float_offset: int) -> int:
+        return self.ptr + 4 * int(float_offset)
+
+    def fence(self):
+        self.dist.all_reduce(self._flag, group=self.group)
+
+
+def _as_tensor(ptr: int, n_floats: int):
+    import torch
+
+    class _Holder:
+        pass
+
+    h = _Holder()
+    h.__cuda_array_interface__ = {"shape": (int(n_floats),), "typestr": "<f4", "data": (int(ptr), False), "version": 3,
+                                  "strides": None}
+    return torch.as_tensor(h, device="cuda")
+
+
+def mul_mat_row_split_peer(ws: Sequence[RowSplitWeight], act, dst: PeerDst, float_offsets: Sequence[int]):
+    """dst[off_g + row] for the rows of this rank's shards of up to 4 matrices that share ``act`` (n = 1), stored into
+    every rank's buffer by the kernel itself.  Call ``dst.fence()`` before another GPU's results are read."""
+    from . import mul_mat_group_ptr
+    live = [(w, off) for w, off in zip(ws, float_offsets) if w.nrows > 0]
+    if not live:
+        return
+    mul_mat_group_ptr([w.shard for w, _ in live], act.reshape(-1), [dst.addr(off + w.row0) for w, off in live], dst.deltas)

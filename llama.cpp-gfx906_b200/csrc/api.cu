@@ -548,8 +548,42 @@ int b200q_mul_mat(const b200q_mul_mat_args * a, const void * w, const float * ac
 }
 
 // ---- grouped decode GEMV: matrices that share one activation vector (q/k/v, gate/up) in one launch ------------------
+static int mul_mat_group_impl(const b200q_mul_mat_group_args * a, const void * const * w, const float * act, float * const * dst,
+                              int n_peers, const int64_t * peer_delta, void * stream);
+
 int b200q_mul_mat_group(const b200q_mul_mat_group_args * a, const void * const * w, const float * act, float * const * dst,
                         void * stream) {
+    return mul_mat_group_impl(a, w, act, dst, 0, nullptr, stream);
+}
+
+int b200q_mul_mat_group_peers(const b200q_mul_mat_group_args * a, const void * const * w, const float * act, float * const * dst,
+                              int n_peers, const int64_t * peer_delta, void * stream) {
+    if (n_peers < 0 || n_peers > 7 || (n_peers && !peer_delta)) return fail(B200Q_EINVAL, "mul_mat_group_peers: 0..7 peers");
+    return mul_mat_group_impl(a, w, act, dst, n_peers, peer_delta, stream);
+}
+
+// ---- inter-process device memory (row split: one process per GPU) -------------------------------------------------
+int b200q_ipc_export(void * dev_ptr, void * handle64) {
+    if (!dev_ptr || !handle64) return fail(B200Q_EINVAL, "ipc_export: null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    CUDA_TRY(cudaIpcGetMemHandle((cudaIpcMemHandle_t *) handle64, dev_ptr));
+    return 0;
+}
+int b200q_ipc_import(const void * handle64, void ** dev_ptr) {
+    if (!dev_ptr || !handle64) return fail(B200Q_EINVAL, "ipc_import: null argument");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, sizeof(h));
+    CUDA_TRY(cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+int b200q_ipc_close(void * dev_ptr) {
+    if (!dev_ptr) return 0;
+    CUDA_TRY(cudaIpcCloseMemHandle(dev_ptr));
+    return 0;
+}
+
+static int mul_mat_group_impl(const b200q_mul_mat_group_args * a, const void * const * w, const float * act, float * const * dst,
+                              int n_peers, const int64_t * peer_delta, void * stream) {
     if (!a || !w || !act || !dst) return fail(B200Q_EINVAL, "mul_mat_group: null argument");
     if (a->n_mats < 1 || a->n_mats > B200Q_MAX_GROUP) return fail(B200Q_EINVAL, "mul_mat_group: n_mats must be 1..%d", B200Q_MAX_GROUP);
     const int be = blck_elems(a->type);
@@ -563,8 +597,11 @@ int b200q_mul_mat_group(const b200q_mul_mat_group_args * a, const void * const *
     KqParams kq{};
     int      grid = 0, smem = 0;
     if (plan_kq(kq, grid, smem, a->type, a->k, a->n_mats, w, dst, a->m, act, di)) {
+        kq.n_peers = n_peers;
+        for (int r = 0; r < n_peers; ++r) kq.peer_delta[r] = (long long) peer_delta[r];
         return launch_kq(kq, grid, smem, a->type, a->flags, (cudaStream_t) stream);
     }
+    if (n_peers) return fail(B200Q_ENOTSUP, "mul_mat_group_peers: shape / type not handled by the ring kernel");
     // anything the grouped kernel does not take: one launch per matrix (same results)
     for (int g = 0; g < a->n_mats; ++g) {
         b200q_mul_mat_args q{};

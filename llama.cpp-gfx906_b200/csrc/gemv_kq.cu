@@ -627,7 +627,11 @@ template <int T, bool MOE> __global__ void __launch_bounds__(NTHREADS, 2) gemv_k
             acc += __shfl_xor_sync(0xffffffffu, acc, o);
         }
         if (sub == 0 && lrow < si.nrows) {
-            p.seg[si.g].dst[si.r0 + lrow] = acc;
+            float * d = p.seg[si.g].dst + si.r0 + lrow;
+            *d = acc;
+            for (int r = 0; r < p.n_peers; ++r) {  // fire-and-forget stores over NVLink (visible at kernel completion)
+                *(float *) ((char *) d + p.peer_delta[r]) = acc;
+            }
         }
     }
     if (g_kq_hang && threadIdx.x == 0) atomicAdd(g_kq_hang + 2042, 1ull);  // warp 0 of a CTA done

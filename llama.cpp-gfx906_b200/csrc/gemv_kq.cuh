@@ -28,6 +28,10 @@ struct KqParams {
     // shared-memory offsets
     int           off_q, off_dx, off_bs16, off_bs32, off_stage;
     int           early_prefetch;  // weights immutable: stream them before griddepcontrol.wait
+    // row split: every result is also stored into the same place of the dst buffer of each peer GPU (peer_delta = the
+    // byte distance from this GPU's buffer to the peer's mapping of its own) — the all-gather is the kernel's epilogue
+    int             n_peers;
+    long long       peer_delta[7];
     // MUL_MAT_ID decode (one token): segment g multiplies expert ids[g]'s matrix; every segment may have its own
     // activation vector (b->ne[1] == n_used) with its own quantized image in shared memory
     const int32_t * ids;           // nullptr: plain segments

@@ -1,4 +1,5 @@
-"""Row split on real GPUs (needs >= 2 devices; skipped on a 1-GPU box): one process per GPU, NCCL all-gather.
+"""Row split on real GPUs (needs >= 2 devices; skipped on a 1-GPU box): one process per GPU, NCCL all-gather and the
+fused variant (peer stores in the kernel epilogue).
 The split result must equal the single-GPU kernel's result BIT FOR BIT, for the decode GEMV (n = 1),
 a ragged split (m not a multiple of world*128) and the tensor-core path (n = 64)."""
 import os
@@ -50,6 +51,17 @@ def _worker(rank, world, port, q):
             single = b200q.mul_mat(b200q.upload(t, (m, k), w), act)
             torch.cuda.synchronize()
             ok.append(bool(torch.equal(got, single)))
+            if n == 1:
+                # the same split with the all-gather folded into the kernel's epilogue (peer stores over NVLink)
+                from b200q.rowsplit import PeerDst, mul_mat_row_split_peer
+                dst = PeerDst(m + 64, rank, world)
+                dst.tensor.zero_()
+                torch.cuda.synchronize()
+                dist.barrier()
+                mul_mat_row_split_peer([ws], act, dst, [32])
+                dst.fence()
+                torch.cuda.synchronize()
+                ok.append(bool(torch.equal(dst.tensor[32:32 + m].view(1, m), single)))
         q.put((rank, ok))
     finally:
         dist.destroy_process_group()
