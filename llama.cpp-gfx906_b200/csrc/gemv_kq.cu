@@ -1,9 +1,10 @@
-// gemv_kq.cu — decode GEMV (n = 1) for the K-quants (q4_K, q6_K), the formats that carry a Q4_K_M model.
+// gemv_kq.cu — decode GEMV (n = 1): K-quants (q4_K, q6_K — the formats that carry a Q4_K_M model) and the 32-element
+// block formats (q4_0 q4_1 q5_0 q5_1 q8_0 mxfp4); MUL_MAT_ID for one token; row-split peer stores.
 //
 // Same role as gemv.cu (it replaces the reference's quantize_q8_1 + mul_mat_vec_q pair, ggml-cuda/quantize.cu:4-48,
 // mmvq.cu:139-226), redesigned around what the B200 timeline of gemv.cu showed (profiles/r01_gemv_timeline_v1.txt):
 //
-//   * 9 warps and <= 112 registers, <= ~110 KB of shared memory per CTA, one CTA per SM per launch, so that TWO launches
+//   * 8 warps, <= 110 registers, <= ~110 KB of shared memory per CTA, one CTA per SM per launch, so that TWO launches
 //     are co-resident on every SM under programmatic dependent launch: while kernel i computes, kernel i+1 has already
 //     filled its ring with ~100 KB of weights per SM, i.e. the HBM pipe keeps streaming across the launch boundary.
 //   * activations are quantized per 256-element super-block (one fp32 scale + int16 partial sums per 16 / 32 values),
@@ -13,8 +14,8 @@
 //     instructions per weight instead of ~2.3.
 //   * a lane owns whole super-blocks (LDS.128 for q4_K; q6_K's 210-byte blocks through aligned words + funnel shift),
 //     lanes of a row read consecutive 16-byte activation chunks (chunk-major layout: conflict-free), one row per lane
-//     group, one warp pass = one ring stage, warps consume alternate stages on their own (no CTA-wide barrier in the
-//     main loop).
+//     group, one warp pass = one ring stage; every warp owns its ring slots and refills them itself (no producer warp,
+//     no CTA-wide barrier in the main loop).
 //   * up to 4 matrices that share the activation vector (q/k/v, gate/up) run in ONE launch ("segments"): one
 //     activation load + quantization, one launch hop.
 // Fixed summation order: results are bit-reproducible and independent of the grid (row-split relies on it).

@@ -13,17 +13,21 @@
 // is MORE accurate than the reference's int8 activations), and kind::f16 MMAs accumulate the whole K extent in fp32 in
 // TMEM with no per-block epilogue.
 //
-// CTA = 18 warps, one CTA per SM, persistent over output tiles of 128 weight rows x 256 activation columns:
-//   warps 0-3   epilogue: tcgen05.ld of the finished accumulator (TMEM lane = weight row, column = token) and
-//               coalesced stores to dst (ggml layout: rows contiguous); overlaps the next tile's main loop because
-//               the 512 TMEM columns hold two 256-column accumulators
-//   warps 4-7   W producers: thread = weight row; 16-byte cp.async of the raw quantized bytes of 128/256 k-elements,
+// CTA = 26 warps, one CTA per SM, persistent over work units of 128 weight rows x 512 activation columns (two 128x256
+// fp32 accumulators fill the 512 TMEM columns and share ONE dequantized A chunk; 128x256 units, double-buffered across
+// tiles, when that fills the SMs better; the k range halved across two CTAs + order-independent atomics for m <= 4096):
+//   warps 0-3   epilogue: tcgen05.ld of the finished accumulators (TMEM lane = weight row, column = token) and
+//               coalesced stores to dst (ggml layout: rows contiguous); MoE: scatter through the expert's row list
+//   warps 4-7   W producers: coalesced 16-byte cp.async of the raw quantized bytes of 128/256 k-elements per row,
 //               16-byte-aligned windows around arbitrarily aligned 17/18/34/210-byte blocks
-//   warp  8     B producer: one bulk copy per 64-wide k-chunk of the bf16 activation tile, which mmq_pack_act has
-//               already written in the exact swizzled shared-memory image (so no tensor map is needed)
-//   warp  9     MMA issuer: one thread, 4 x tcgen05.mma (M=128, N<=256, K=16) per k-chunk, tcgen05.commit to free stages
-//   warps 10-17 dequantizers: thread = (row, 32-element block); raw bytes -> fp32 -> bf16 -> 4 x STS.128 (conflict-free
-//               under the 128B swizzle), fence.proxy.async, arrive
+//   warp  8     B producer: one bulk copy per 64-wide k-chunk of the bf16 activation tiles (both column tiles, adjacent
+//               in the workspace), which mmq_pack_act has already written in the exact swizzled shared-memory image
+//   warp  9     MMA issuer: the WHOLE warp runs the loop (warp-uniform control flow keeps descriptors in uniform
+//               registers), one elected lane issues 8 x tcgen05.mma (M=128, N<=256, K=16) per k-chunk and the commits
+//   warps 10-25 dequantizers, two groups on alternate k-chunks: thread = (row, 32-element block); raw bytes -> fp32
+//               (PRMT into the mantissa of 2^23, no I2F) -> bf16 -> 4 x STS.128 under the 128B swizzle,
+//               fence.proxy.async, arrive
+// MUL_MAT_ID for many tokens runs through the same kernel (moe_route / moe_pack_act below).
 #include "mmq.cuh"
 
 #include "../../include/b200q.h"
