@@ -6,6 +6,7 @@
 #include "dequant.cuh"
 #include "gemv.cuh"
 #include "gemv_kq.cuh"
+#include "gemv_mma.cuh"
 #include "mmq.cuh"
 
 #include <cuda_runtime.h>
@@ -302,6 +303,84 @@ int launch_kq(KqParams & p, int grid, int smem, int type, uint32_t flags, cudaSt
     return 0;
 }
 
+// ---- decode GEMV for 2..8 columns on the MMA tile kernel (gemv_mma.cu): K-quants, dense rows ---------------------
+bool plan_mma(MmaParams & p, int & grid, int & smem, int type, int64_t m, int64_t k, int n, const void * w, const float * act,
+              long long a_nb1, float * dst, long long d_nb1, const DevInfo & di) {
+    if (!mma_kernel_for(type)) return false;
+    static const bool off = getenv("B200Q_NO_MMA_GEMV") != nullptr;
+    if (off || n < 2 || n > 8 || k <= 0 || k % 256 || m <= 0 || m > (1 << 30)) return false;
+    const int bb = blck_bytes(type), NWc = mma_warps();
+    p.nsb        = (int) (k / 256);
+    p.row_bytes  = p.nsb * bb;
+    if (p.row_bytes % 16 || ((uintptr_t) w & 15) || ((uintptr_t) act & 15) || (a_nb1 & 15) || ((uintptr_t) dst & 3) || (d_nb1 & 3)) return false;
+    static const int kc_env = getenv("B200Q_MMA_KC") ? atoi(getenv("B200Q_MMA_KC")) : 4;
+    p.kc = 1;
+    for (int c = 8; c > 1; c >>= 1) {
+        if (c <= kc_env && p.nsb % c == 0) { p.kc = c; break; }
+    }
+    p.chunk_bytes = p.kc * bb;
+    p.chunks      = p.nsb / p.kc;
+    // every row of a stage is copied as the 16-byte aligned window around its chunk (lead <= 14 bytes); the pitch between
+    // rows is == 32 or 96 mod 128 so that the LDS.64 of 4 rows x 4 lanes (one half-warp) touch 32 distinct banks
+    int pitch = round_up(p.chunk_bytes + 14, 16);
+    while (pitch % 128 != 32 && pitch % 128 != 96) pitch += 16;
+    p.pitch       = pitch;
+    p.stage_bytes = 16 * pitch;
+    p.col_pitch   = (int) k + 64;
+    p.off_q       = 384;
+    p.off_dx      = p.off_q + n * p.col_pitch;
+    p.off_bs      = round_up(p.off_dx + n * p.nsb * 4, 16);
+    p.off_part    = round_up(p.off_bs + n * p.nsb * mma_bs_bytes(type), 16);
+    p.off_stage   = round_up(p.off_part + NWc * 2 * 512, 128);
+    const int S   = (di.max_smem - p.off_stage - 64) / p.stage_bytes;  // + slack for the funnel over-read of the last row
+    if (S < NWc) return false;
+    p.nstages = std::min(S, 40);
+    p.groups  = (int) ((m + 15) / 16);
+    grid      = std::min(p.groups, di.sms);
+    // warps per 16-row group along k: the fewest sequential stages per warp
+    static const int kp_env = getenv("B200Q_MMA_KP") ? atoi(getenv("B200Q_MMA_KP")) : 0;
+    const int gpc = (p.groups + grid - 1) / grid;
+    long long best = -1;
+    for (int kp = 1; kp <= NWc; kp *= 2) {
+        if (p.chunks % kp) continue;
+        if (kp_env && kp != kp_env) continue;
+        const int       teams = NWc / kp;
+        const long long cost  = (long long) ((gpc + teams - 1) / teams) * (p.chunks / kp);
+        if (best < 0 || cost < best) { best = cost; p.kp = kp; }
+    }
+    if (best < 0) return false;
+    p.cpm = p.chunks / p.kp;
+    p.w = (const uint8_t *) w; p.act = act; p.dst = dst; p.a_nb1 = a_nb1; p.d_nb1 = d_nb1;
+    p.m = (int) m; p.k = (int) k; p.n = n;
+    smem = p.off_stage + p.nstages * p.stage_bytes + 64;
+    return true;
+}
+
+int launch_mma(const MmaParams & p, int grid, int smem, int type, uint32_t flags, cudaStream_t st) {
+    mma_kernel_t fn = mma_kernel_for(type);
+    if (!fn) return fail(B200Q_ENOTSUP, "gemv_mma: unsupported type %d", type);
+    const DevInfo & di = dev_info();
+    if (int rc = ensure_smem_attr((const void *) fn, di.max_smem)) return rc;
+    const bool pdl = !(flags & B200Q_FLAG_NO_PDL);
+    static const bool debug = getenv("B200Q_DEBUG") != nullptr;
+    if (debug) {
+        fprintf(stderr, "[b200q] gemv_mma type=%d m=%d k=%d n=%d grid=%d smem=%d kc=%d chunks=%d kp=%d pitch=%d stage_bytes=%d S=%d groups=%d\n",
+                type, p.m, p.k, p.n, grid, smem, p.kc, p.chunks, p.kp, p.pitch, p.stage_bytes, p.nstages, p.groups);
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim          = dim3(grid);
+    cfg.blockDim         = dim3(mma_threads());
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream           = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs                                          = attr;
+    cfg.numAttrs                                       = pdl ? 1 : 0;
+    CUDA_TRY(cudaLaunchKernelEx(&cfg, fn, p));
+    return 0;
+}
+
 bool aligned16(const void * p, long long stride) { return ((uintptr_t) p & 15) == 0 && (stride & 15) == 0; }
 
 }  // namespace
@@ -511,6 +590,29 @@ int b200q_mul_mat(const b200q_mul_mat_args * a, const void * w, const float * ac
         const int64_t ml[1] = { a->m };
         if (plan_kq(kq, grid, smem, a->type, a->k, 1, wl, dl, ml, act, di)) {
             return launch_kq(kq, grid, smem, a->type, a->flags, st);
+        }
+    }
+
+    // 2..8 columns on K-quants: the MMA tile kernel (one pass over the weights; the columns are halved only when their
+    // quantized images do not fit beside the ring in shared memory)
+    if (a->n >= 2 && a->n <= 8 && a->ne12 * a->ne13 == 1 && a->nb01 == b200q_row_size(a->type, a->k) && mma_kernel_for(a->type)) {
+        MmaParams mp{};
+        int       grid = 0, smem = 0;
+        int       nc   = (int) a->n;
+        auto      col_act = [&](int64_t j) { return (const float *) ((const char *) act + j * (long long) a->nb11); };
+        auto      col_dst = [&](int64_t j) { return (float *) ((char *) dst + j * (long long) a->nb1); };
+        while (nc >= 2 && !plan_mma(mp, grid, smem, a->type, a->m, a->k, nc, w, act, (long long) a->nb11, dst, (long long) a->nb1, di)) {
+            nc = (nc + 1) / 2;
+        }
+        if (nc >= 2 && (a->n % nc == 0 || a->n % nc >= 2)) {
+            for (int64_t j0 = 0; j0 < a->n; j0 += nc) {
+                const int cur = (int) std::min<int64_t>(nc, a->n - j0);
+                if (!plan_mma(mp, grid, smem, a->type, a->m, a->k, cur, w, col_act(j0), (long long) a->nb11, col_dst(j0), (long long) a->nb1, di)) {
+                    return fail(B200Q_ENOTSUP, "mul_mat: gemv_mma plan failed");
+                }
+                if (int rc = launch_mma(mp, grid, smem, a->type, a->flags, st)) return rc;
+            }
+            return 0;
         }
     }
 

