@@ -308,32 +308,52 @@ bool plan_mma(MmaParams & p, int & grid, int & smem, int type, int64_t m, int64_
               long long a_nb1, float * dst, long long d_nb1, const DevInfo & di) {
     if (!mma_kernel_for(type)) return false;
     static const bool off = getenv("B200Q_NO_MMA_GEMV") != nullptr;
-    if (off || n < 2 || n > 8 || k <= 0 || k % 256 || m <= 0 || m > (1 << 30)) return false;
-    const int bb = blck_bytes(type), NWc = mma_warps();
-    p.nsb        = (int) (k / 256);
+    const bool kquant = type == T_Q4_K || type == T_Q5_K || type == T_Q6_K;
+    const int  unit   = kquant ? 256 : 32;  // elements per unit: super-block | block
+    if (off || n < 2 || n > 8 || k <= 0 || k % unit || m <= 0 || m > (1 << 30)) return false;
+    const int bb = blck_bytes(type);
+    p.nsb        = (int) (k / unit);
     p.row_bytes  = p.nsb * bb;
     if (p.row_bytes % 16 || ((uintptr_t) w & 15) || ((uintptr_t) act & 15) || (a_nb1 & 15) || ((uintptr_t) dst & 3) || (d_nb1 & 3)) return false;
-    static const int kc_env = getenv("B200Q_MMA_KC") ? atoi(getenv("B200Q_MMA_KC")) : 4;
-    p.kc = 1;
-    for (int c = 8; c > 1; c >>= 1) {
-        if (c <= kc_env && p.nsb % c == 0) { p.kc = c; break; }
+    // quantized activations: int8 images (K-quants: permuted per super-block, pitch k + 64; blocks: natural, k + 16), scales
+    // (K-quants: one float, blocks: (d, d * sum)), K-quant partial sums — each column one unit longer than needed, so the 4
+    // columns a warp reads at once sit in different banks — then the teams' partial tiles and the ring
+    p.col_pitch = (int) k + (kquant ? 64 : 16);
+    p.dx_pitch  = (p.nsb + 1) * (kquant ? 4 : 8);
+    p.bs_pitch  = (p.nsb + 1) * mma_bs_bytes(type);
+    p.off_q     = 384;
+    p.off_dx    = p.off_q + n * p.col_pitch;
+    p.off_bs    = round_up(p.off_dx + n * p.dx_pitch, 16);
+    p.off_part  = round_up(p.off_bs + n * p.bs_pitch, 16);
+    p.off_stage = round_up(p.off_part + mma_max_warps() * 2 * 512, 128);
+    // units per stage: the largest chunk (<= the cap) that divides the row and leaves every warp a ring slot; 16 warps when
+    // the ring has 16 slots, else 8.  Every row of a stage is copied as the 16-byte aligned window around its chunk
+    // (lead <= 14 bytes); the pitch between rows makes the A-fragment loads conflict-free: LDS.64 of 4 rows x 4 lanes per
+    // half-warp (q4_K, q5_K) -> pitch == 32 or 96 mod 128; LDS.32 of 8 rows x 4 lanes per warp (q6_K, blocks) -> pitch an
+    // odd multiple of 16
+    static const int kc_env = getenv("B200Q_MMA_KC") ? atoi(getenv("B200Q_MMA_KC")) : 0;
+    static const int nw_env = getenv("B200Q_MMA_NW") ? atoi(getenv("B200Q_MMA_NW")) : 16;
+    const int        kc_cap = kc_env ? kc_env : kquant ? 4 : 32;
+    const bool       lds64  = type == T_Q4_K || type == T_Q5_K;
+    int              S      = 0;
+    p.nwarps                = 0;
+    for (int nw = nw_env >= 16 ? 16 : 8; nw >= 8 && !p.nwarps; nw -= 8) {
+        for (int c = 64; c >= 1; c >>= 1) {
+            if (c > kc_cap || p.nsb % c) continue;
+            p.kc          = c;
+            p.chunk_bytes = c * bb;
+            int pitch     = round_up(p.chunk_bytes + 14, 16);
+            while (lds64 ? (pitch % 128 != 32 && pitch % 128 != 96) : (pitch / 16) % 2 == 0) pitch += 16;
+            p.pitch       = pitch;
+            p.stage_bytes = 16 * pitch;
+            S             = (di.max_smem - p.off_stage - 64) / p.stage_bytes;  // + slack for the over-read behind the last row
+            if (S >= nw && p.chunk_bytes >= 256) { p.nwarps = nw; break; }
+            if (S >= nw && nw == 8) { p.nwarps = nw; break; }
+        }
     }
-    p.chunk_bytes = p.kc * bb;
-    p.chunks      = p.nsb / p.kc;
-    // every row of a stage is copied as the 16-byte aligned window around its chunk (lead <= 14 bytes); the pitch between
-    // rows is == 32 or 96 mod 128 so that the LDS.64 of 4 rows x 4 lanes (one half-warp) touch 32 distinct banks
-    int pitch = round_up(p.chunk_bytes + 14, 16);
-    while (pitch % 128 != 32 && pitch % 128 != 96) pitch += 16;
-    p.pitch       = pitch;
-    p.stage_bytes = 16 * pitch;
-    p.col_pitch   = (int) k + 64;
-    p.off_q       = 384;
-    p.off_dx      = p.off_q + n * p.col_pitch;
-    p.off_bs      = round_up(p.off_dx + n * p.nsb * 4, 16);
-    p.off_part    = round_up(p.off_bs + n * p.nsb * mma_bs_bytes(type), 16);
-    p.off_stage   = round_up(p.off_part + NWc * 2 * 512, 128);
-    const int S   = (di.max_smem - p.off_stage - 64) / p.stage_bytes;  // + slack for the funnel over-read of the last row
-    if (S < NWc) return false;
+    if (!p.nwarps) return false;
+    const int NWc = p.nwarps;
+    p.chunks  = p.nsb / p.kc;
     p.nstages = std::min(S, 40);
     p.groups  = (int) ((m + 15) / 16);
     grid      = std::min(p.groups, di.sms);
@@ -341,10 +361,11 @@ bool plan_mma(MmaParams & p, int & grid, int & smem, int type, int64_t m, int64_
     static const int kp_env = getenv("B200Q_MMA_KP") ? atoi(getenv("B200Q_MMA_KP")) : 0;
     const int gpc = (p.groups + grid - 1) / grid;
     long long best = -1;
-    for (int kp = 1; kp <= NWc; kp *= 2) {
+    for (int kp = 1; kp <= 8; kp *= 2) {
         if (p.chunks % kp) continue;
         if (kp_env && kp != kp_env) continue;
         const int       teams = NWc / kp;
+        if (kp > 1 && teams > 8) continue;  // named barriers 1..8
         const long long cost  = (long long) ((gpc + teams - 1) / teams) * (p.chunks / kp);
         if (best < 0 || cost < best) { best = cost; p.kp = kp; }
     }
@@ -364,12 +385,12 @@ int launch_mma(const MmaParams & p, int grid, int smem, int type, uint32_t flags
     const bool pdl = !(flags & B200Q_FLAG_NO_PDL);
     static const bool debug = getenv("B200Q_DEBUG") != nullptr;
     if (debug) {
-        fprintf(stderr, "[b200q] gemv_mma type=%d m=%d k=%d n=%d grid=%d smem=%d kc=%d chunks=%d kp=%d pitch=%d stage_bytes=%d S=%d groups=%d\n",
-                type, p.m, p.k, p.n, grid, smem, p.kc, p.chunks, p.kp, p.pitch, p.stage_bytes, p.nstages, p.groups);
+        fprintf(stderr, "[b200q] gemv_mma type=%d m=%d k=%d n=%d grid=%d smem=%d nw=%d kc=%d chunks=%d kp=%d pitch=%d stage_bytes=%d S=%d groups=%d\n",
+                type, p.m, p.k, p.n, grid, smem, p.nwarps, p.kc, p.chunks, p.kp, p.pitch, p.stage_bytes, p.nstages, p.groups);
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim          = dim3(grid);
-    cfg.blockDim         = dim3(mma_threads());
+    cfg.blockDim         = dim3(32 * p.nwarps);
     cfg.dynamicSmemBytes = smem;
     cfg.stream           = st;
     cudaLaunchAttribute attr[1];

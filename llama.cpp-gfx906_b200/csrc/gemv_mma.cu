@@ -4,7 +4,7 @@
 // Replaces the reference's quantize_q8_1 + mul_mat_vec_q<ncols_dst = 2..8> pair (ggml-cuda/quantize.cu:4-48,
 // mmvq.cu:139-226).
 //
-//   * 8 warps, one CTA per SM with the whole shared memory: quantized activation images of all columns (int8, permuted
+//   * 16 warps (8 when the ring cannot give each of 16 a slot), one CTA per SM with the whole shared memory: quantized activation images of all columns (int8, permuted
 //     into B-fragment order) + a ring of stages.  A stage = 16 rows x kc super-blocks; every row of a stage is its own
 //     bulk copy (TMA 1-D) into a padded pitch (== 32 or 96 mod 128), which makes the per-lane A-fragment loads
 //     (LDS.64, rows 8 apart) bank-conflict-free without touching the GGUF layout in HBM.
@@ -26,9 +26,8 @@ namespace {
 using namespace sm100;
 using namespace mma;
 
-constexpr int NW       = 8;
-constexpr int NTHREADS = NW * 32;
-constexpr int MAX_S    = 40;  // ring depth limit (full-barriers live in the first 384 bytes)
+constexpr int MAX_WARPS   = 16;
+constexpr int MAX_THREADS = MAX_WARPS * 32;
 
 extern __shared__ __align__(128) uint8_t mma_smem[];
 
@@ -37,6 +36,14 @@ struct DevExec {
 #ifdef __CUDA_ARCH__
         asm volatile(
             "mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%10, %10, %10, %10};"
+            : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3])
+            : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "r"(0));
+#endif
+    }
+    __host__ __device__ __forceinline__ void mma32s(int, int (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+#ifdef __CUDA_ARCH__
+        asm volatile(
+            "mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%10, %10, %10, %10};"
             : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3])
             : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "r"(0));
 #endif
@@ -54,48 +61,121 @@ struct DevExec {
 // ---- activation quantization: f32 column -> int8 image in B-fragment order, scale, int16 partial sums -------------
 // the arithmetic of gemv_kq.cu's quantize_act (per 256 values: d = amax / 127, q = round(x * 127 / amax)); one warp
 // per super-block, lane l holds values 8l .. 8l+7
-template <int T> __device__ __forceinline__ void quantize_cols(const MmaParams & p, uint32_t sb, int warp, int lane) {
+template <int T> __device__ __forceinline__ void quantize_cols(const MmaParams & p, uint32_t sb, int warp, int lane, int nw) {
     constexpr int BSB = T == T_Q6_K ? 32 : 16;
+    constexpr int QB  = 8;  // units in flight per warp: the global loads of a batch are issued together
     const int     total = p.n * p.nsb;
-    for (int u = warp; u < total; u += NW) {
-        const int      col = u / p.nsb, s = u - col * p.nsb;
-        const float4 * src = (const float4 *) ((const char *) p.act + (long long) col * p.a_nb1) + (size_t) s * 64 + lane * 2;
-        const float4   x0 = __ldg(src), x1 = __ldg(src + 1);
-        const float    v[8] = { x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w };
-        float amax = 0.0f;
+    for (int u0 = warp; u0 < total; u0 += nw * QB) {
+        float4 x[QB][2];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(v[i]));
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-        const float d  = amax * (1.0f / 127.0f);
-        const float id = amax > 0.0f ? 127.0f / amax : 0.0f;
-        int q[8], sum = 0;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            q[i] = __float2int_rn(v[i] * id);
-            sum += q[i];
+        for (int b = 0; b < QB; ++b) {
+            const int u = u0 + b * nw;
+            if (u < total) {
+                const int      col = u / p.nsb, s = u - col * p.nsb;
+                const float4 * src = (const float4 *) ((const char *) p.act + (long long) col * p.a_nb1) + (size_t) s * 64 + lane * 2;
+                x[b][0] = __ldg(src);
+                x[b][1] = __ldg(src + 1);
+            }
         }
-        const uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t) q[3] << 24);
-        const uint32_t w1 = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t) q[7] << 24);
-        const uint32_t qa = sb + p.off_q + (uint32_t) col * (uint32_t) p.col_pitch + (uint32_t) s * 256u;
-        asm volatile("st.shared.u32 [%0], %1;" ::"r"(qa + (uint32_t) act_word_off<T>(lane * 8)), "r"(w0) : "memory");
-        asm volatile("st.shared.u32 [%0], %1;" ::"r"(qa + (uint32_t) act_word_off<T>(lane * 8 + 4)), "r"(w1) : "memory");
-        const int      s16 = sum + __shfl_xor_sync(0xffffffffu, sum, 1);
-        const int      s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 2);
-        const uint32_t bsa = sb + p.off_bs + (uint32_t) u * BSB;
-        if (T == T_Q6_K) {
-            if ((lane & 1) == 0) asm volatile("st.shared.u16 [%0], %1;" ::"r"(bsa + (uint32_t) (lane >> 1) * 2), "h"((short) s16) : "memory");
-        } else {
-            if ((lane & 3) == 0) asm volatile("st.shared.u16 [%0], %1;" ::"r"(bsa + (uint32_t) (lane >> 2) * 2), "h"((short) s32) : "memory");
+#pragma unroll
+        for (int b = 0; b < QB; ++b) {
+            const int u = u0 + b * nw;
+            if (u >= total) break;  // warp-uniform
+            const int   col = u / p.nsb, s = u - col * p.nsb;
+            const float v[8] = { x[b][0].x, x[b][0].y, x[b][0].z, x[b][0].w, x[b][1].x, x[b][1].y, x[b][1].z, x[b][1].w };
+            float amax = 0.0f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(v[i]));
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+            const float d  = amax * (1.0f / 127.0f);
+            const float id = amax > 0.0f ? 127.0f / amax : 0.0f;
+            int q[8], sum = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                q[i] = __float2int_rn(v[i] * id);
+                sum += q[i];
+            }
+            const uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t) q[3] << 24);
+            const uint32_t w1 = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t) q[7] << 24);
+            const uint32_t qa = sb + p.off_q + (uint32_t) col * (uint32_t) p.col_pitch + (uint32_t) s * 256u;
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(qa + (uint32_t) act_word_off<T>(lane * 8)), "r"(w0) : "memory");
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(qa + (uint32_t) act_word_off<T>(lane * 8 + 4)), "r"(w1) : "memory");
+            const int      s16 = sum + __shfl_xor_sync(0xffffffffu, sum, 1);
+            const int      s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 2);
+            const uint32_t bsa = sb + p.off_bs + (uint32_t) (col * p.bs_pitch + s * BSB);
+            if (T == T_Q6_K) {
+                if ((lane & 1) == 0) asm volatile("st.shared.u16 [%0], %1;" ::"r"(bsa + (uint32_t) (lane >> 1) * 2), "h"((short) s16) : "memory");
+            } else {
+                if ((lane & 3) == 0) asm volatile("st.shared.u16 [%0], %1;" ::"r"(bsa + (uint32_t) (lane >> 2) * 2), "h"((short) s32) : "memory");
+            }
+            if (lane == 0) asm volatile("st.shared.f32 [%0], %1;" ::"r"(sb + p.off_dx + (uint32_t) (col * p.dx_pitch + s * 4)), "f"(d) : "memory");
         }
-        if (lane == 0) asm volatile("st.shared.f32 [%0], %1;" ::"r"(sb + p.off_dx + (uint32_t) u * 4), "f"(d) : "memory");
     }
 }
 
-template <int T> __global__ void __launch_bounds__(NTHREADS, 1) gemv_mma_kernel(const MmaParams p) {
+// 32-element block formats: per-32 scales, natural element order, (d, d * sum q) per block — quantize_row_q8_1's numbers
+// (gemv_kq.cu quantize_act32).  One warp per 256 values per step; lane l holds values 8l .. 8l+7, 4 lanes per block.
+__device__ __forceinline__ void quantize_cols32(const MmaParams & p, uint32_t sb, int warp, int lane, int nw) {
+    constexpr int QB = 8;
+    const int nb = p.nsb, ng = (nb + 7) / 8, total = p.n * ng;
+    for (int u0 = warp; u0 < total; u0 += nw * QB) {
+        float4 x[QB][2];
+#pragma unroll
+        for (int bi = 0; bi < QB; ++bi) {
+            const int u = u0 + bi * nw;
+            x[bi][0] = x[bi][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (u < total) {
+                const int col = u / ng, g = u - col * ng;
+                if (g * 8 + (lane >> 2) < nb) {
+                    const float4 * src = (const float4 *) ((const char *) p.act + (long long) col * p.a_nb1) + (size_t) g * 64 + lane * 2;
+                    x[bi][0] = __ldg(src);
+                    x[bi][1] = __ldg(src + 1);
+                }
+            }
+        }
+#pragma unroll
+        for (int bi = 0; bi < QB; ++bi) {
+            const int u = u0 + bi * nw;
+            if (u >= total) break;  // warp-uniform
+            const int   col = u / ng, g = u - col * ng;
+            const int   b     = g * 8 + (lane >> 2);
+            const bool  valid = b < nb;  // uniform over the 4 lanes of a block
+            const float v[8] = { x[bi][0].x, x[bi][0].y, x[bi][0].z, x[bi][0].w, x[bi][1].x, x[bi][1].y, x[bi][1].z, x[bi][1].w };
+            float amax = 0.0f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(v[i]));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+            const float d  = amax * (1.0f / 127.0f);
+            const float id = amax > 0.0f ? 127.0f / amax : 0.0f;
+            int q[8], sum = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                q[i] = __float2int_rn(v[i] * id);
+                sum += q[i];
+            }
+            sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+            sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+            if (valid) {
+                const uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t) q[3] << 24);
+                const uint32_t w1 = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t) q[7] << 24);
+                const uint32_t qa = sb + p.off_q + (uint32_t) col * (uint32_t) p.col_pitch + (uint32_t) (g * 256 + lane * 8);
+                asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(qa), "r"(w0), "r"(w1) : "memory");
+                if ((lane & 3) == 0) {
+                    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(sb + p.off_dx + (uint32_t) (col * p.dx_pitch + b * 8)), "f"(d), "f"(d * (float) sum) : "memory");
+                }
+            }
+        }
+    }
+}
+
+template <int T> __global__ void __launch_bounds__(MAX_THREADS, 1) gemv_mma_kernel(const MmaParams p) {
     constexpr int BB   = BlockInfo<T>::BYTES;
     const uint32_t sb   = smem_u32(mma_smem);
-    const int      warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int      NW   = (int) (blockDim.x >> 5);                                // 8 or 16 warps (planner)
+    const int      warp = __shfl_sync(0xffffffffu, (int) (threadIdx.x >> 5), 0);  // warp-uniform for the compiler
+    const int      lane = threadIdx.x & 31;
     const int      S    = p.nstages;
     // ring slots of this warp (the S % NW spare slots go to the first warps)
     const int D     = S / NW + (warp < S % NW ? 1 : 0);
@@ -116,7 +196,9 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) gemv_mma_kernel(
     pdl_launch_dependents();
 
     const uint64_t pol   = policy_evict_first();
-    auto           issue = [&](int i) {  // whole warp
+    // whole warp, warp-uniform operands; one elected lane issues (code under `if (lane == 0)` would make the compiler
+    // wrap every bulk copy in an ELECT / R2UR.BROADCAST loop)
+    auto issue = [&](int i) {
         const int       it = i / cpm, ci = i - it * cpm;
         const int       g = G0 + team + it * teams, chunk = member * cpm + ci;
         const int       nrows = min(16, p.m - 16 * g);
@@ -124,22 +206,25 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) gemv_mma_kernel(
         const uint32_t  lead  = (uint32_t) (coff & 15);
         const uint32_t  win   = (lead + (uint32_t) p.chunk_bytes + 15u) & ~15u;
         const uint32_t  full  = sb + 8 * (slot0 + i % D);
-        if (lane == 0) mbar_expect_tx(full, win * (uint32_t) nrows);
+        const uint8_t * src   = p.w + (long long) (16 * g) * p.row_bytes + coff - lead;
+        uint32_t        dst   = sb + p.off_stage + (uint32_t) (slot0 + i % D) * p.stage_bytes;
+        if (elect_one()) mbar_expect_tx(full, win * (uint32_t) nrows);
         __syncwarp();
-        if (lane < nrows) {
-            const uint8_t * src = p.w + (long long) (16 * g + lane) * p.row_bytes + coff - lead;
-            bulk_g2s_hint(sb + p.off_stage + (uint32_t) (slot0 + i % D) * p.stage_bytes + (uint32_t) lane * p.pitch, src, win, full, pol);
+        for (int r = 0; r < nrows; ++r) {
+            if (elect_one()) bulk_g2s_hint(dst, src, win, full, pol);
+            src += p.row_bytes;
+            dst += p.pitch;
         }
     };
-    // weights may be prefetched before the predecessor has finished only when the caller marks them immutable; this
-    // kernel owns the whole shared memory, so it never runs beside its predecessor anyway: keep the simple order
+    // this kernel owns the whole shared memory, so it never runs beside its predecessor: nothing to prefetch early
     pdl_wait();
     for (int i = 0; i < min(D, nmine); ++i) issue(i);
-    if (T == T_Q6_K) quantize_cols<T_Q6_K>(p, sb, warp, lane);
-    else quantize_cols<T_Q4_K>(p, sb, warp, lane);  // q4_K and q5_K share the layout
+    if (!MmaIsKQuant<T>::value) quantize_cols32(p, sb, warp, lane, NW);
+    else if (T == T_Q6_K) quantize_cols<T_Q6_K>(p, sb, warp, lane, NW);
+    else quantize_cols<T_Q4_K>(p, sb, warp, lane, NW);  // q4_K and q5_K share the layout
     __syncthreads();
 
-    const TileCtx t{ sb + (uint32_t) p.off_q, sb + (uint32_t) p.off_dx, sb + (uint32_t) p.off_bs, p.col_pitch, p.nsb, p.n };
+    const TileCtx t{ sb + (uint32_t) p.off_q, sb + (uint32_t) p.off_dx, sb + (uint32_t) p.off_bs, p.col_pitch, p.dx_pitch, p.bs_pitch, p.n };
     DevExec       ex;
     const int     r = lane >> 2, c = lane & 3;
     float         facc[4] = { 0.f, 0.f, 0.f, 0.f };
@@ -150,8 +235,15 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) gemv_mma_kernel(
         mbar_wait(sb + 8 * slot, use & 1);
         const uint32_t lead = (uint32_t) (((long long) chunk * p.chunk_bytes) & 15);
         const uint32_t blk  = sb + p.off_stage + (uint32_t) slot * p.stage_bytes + lead + (uint32_t) r * p.pitch;
-        for (int sbi = 0; sbi < p.kc; ++sbi) {
-            TileSb<T, DevExec>::run(ex, t, lane, chunk * p.kc + sbi, blk + (uint32_t) sbi * BB, blk + (uint32_t) sbi * BB + 8u * p.pitch, facc);
+        if constexpr (MmaIsKQuant<T>::value) {
+            for (int sbi = 0; sbi < p.kc; ++sbi) {
+                TileSb<T, DevExec>::run(ex, t, lane, chunk * p.kc + sbi, blk + (uint32_t) sbi * BB, blk + (uint32_t) sbi * BB + 8u * p.pitch, facc);
+            }
+        } else {
+#pragma unroll 4
+            for (int sbi = 0; sbi < p.kc; ++sbi) {
+                TileSb<T, DevExec>::run(ex, t, lane, chunk * p.kc + sbi, blk + (uint32_t) sbi * BB, blk + (uint32_t) sbi * BB + 8u * p.pitch, facc);
+            }
         }
         __syncwarp();              // every lane is done reading the slot
         fence_proxy_async_smem();  // order the generic-proxy reads before the async-proxy refill
@@ -191,11 +283,12 @@ mma_kernel_t mma_kernel_for(int type) {
         case T_Q4_K: return gemv_mma_kernel<T_Q4_K>;
         case T_Q5_K: return gemv_mma_kernel<T_Q5_K>;
         case T_Q6_K: return gemv_mma_kernel<T_Q6_K>;
+        case T_Q4_0: return gemv_mma_kernel<T_Q4_0>;
+        case T_Q8_0: return gemv_mma_kernel<T_Q8_0>;
         default: return nullptr;
     }
 }
-int mma_threads() { return NTHREADS; }
-int mma_warps() { return NW; }
-int mma_bs_bytes(int type) { return type == T_Q6_K ? 32 : 16; }
+int mma_max_warps() { return MAX_WARPS; }
+int mma_bs_bytes(int type) { return type == T_Q6_K ? 32 : type == T_Q4_K || type == T_Q5_K ? 16 : 0; }
 
 }  // namespace b200q

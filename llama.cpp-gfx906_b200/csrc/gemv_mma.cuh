@@ -28,9 +28,9 @@ struct MmaParams {
     float *         dst;  // column j at dst + j * d_nb1 bytes, rows contiguous
     long long       a_nb1, d_nb1;
     int             m, k, n;  // n = 2..8 columns
-    int             nsb;        // 256-element super-blocks per row
+    int             nsb;        // units per row: 256-element super-blocks (K-quants) | 32-element blocks
     int             row_bytes;  // nsb * block bytes (a multiple of 16)
-    int             kc;         // super-blocks per ring stage (one k-chunk of 16 rows)
+    int             kc;         // units per ring stage (one k-chunk of 16 rows)
     int             chunk_bytes;  // kc * block bytes
     int             chunks;     // nsb / kc
     int             kp;         // warps that share one 16-row group along k (1, 2, 4 or 8)
@@ -39,14 +39,15 @@ struct MmaParams {
     int             pitch;      // shared-memory distance between the rows of a stage (== 32 or 96 mod 128: conflict-free)
     int             stage_bytes;  // 16 * pitch
     int             nstages;    // ring depth (>= number of warps)
-    int             col_pitch;  // bytes between the int8 images of two columns (k + 64: conflict-free LDS.128)
+    int             nwarps;     // 8 or 16 (block size = 32 * nwarps)
+    int             col_pitch;  // bytes between the int8 images of two columns (k + 64 | k + 16: conflict-free fragment loads)
+    int             dx_pitch, bs_pitch;  // bytes between the columns' scales / partial sums (one unit of padding each)
     int             off_q, off_dx, off_bs, off_part, off_stage;  // shared-memory offsets
 };
 
 typedef void (*mma_kernel_t)(const MmaParams);
 mma_kernel_t mma_kernel_for(int type);
-int          mma_threads();
-int          mma_warps();
+int          mma_max_warps();
 int          mma_bs_bytes(int type);  // bytes of activation partial sums per (column, super-block)
 
 namespace mma {
@@ -160,6 +161,25 @@ B200Q_HD int dp2a_hi_ss(int a, uint32_t b, int c) {
 #endif
 }
 
+// byte idx of w, zero- / sign-extended: one PRMT
+B200Q_HD int ubyte_of(uint32_t w, int idx) {
+#ifdef __CUDA_ARCH__
+    return (int) __byte_perm(w, 0, 0x4440 | idx);
+#else
+    return (int) ((w >> (8 * idx)) & 0xffu);
+#endif
+}
+B200Q_HD int sbyte_of(uint32_t w, int idx) {
+#ifdef __CUDA_ARCH__
+    // bit 3 of a selector nibble replicates the sign of the selected byte (__byte_perm only honours 3 bits: raw prmt)
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(w), "r"(0u), "r"((uint32_t) (((idx | 8) * 0x1110) | idx)));
+    return (int) d;
+#else
+    return (int) (int8_t) ((w >> (8 * idx)) & 0xffu);
+#endif
+}
+
 // ---- layout of the quantized activations in shared memory --------------------------------------------------------
 // A column's int8 image keeps 256 bytes per super-block, but permuted so that every lane of the MMA finds the B
 // fragments of a whole super-block in four 16-byte chunks (LDS.128, conflict-free with col_pitch == 64 mod 128).
@@ -179,14 +199,16 @@ template <int T> B200Q_HD int act_word_off(int e) {
 
 // where a warp finds things in shared memory (byte addresses)
 struct TileCtx {
-    uint32_t q, dx, bs;  // column 0 of: int8 images, float scales [col][nsb], int16 partial sums [col][nsb][8 | 16]
-    int      col_pitch, nsb, n;
+    uint32_t q, dx, bs;  // column 0 of: int8 images, scales [col][nsb], int16 partial sums [col][nsb][8 | 16]
+    int      col_pitch, dx_pitch, bs_pitch;  // bytes between columns (each one unit longer than a column: the 4 columns a warp reads
+                                             // at once then sit in different banks)
+    int      n;
 };
 
 // ---- one super-block of a 16-row x 8-column tile -------------------------------------------------------------------
 // lane = 4 * r + c : A fragments of rows r and r + 8 (shared addresses blk0 / blk1 of their blocks), B fragment of
 // column r, C fragment = rows {r, r, r+8, r+8} x columns {2c, 2c+1, 2c, 2c+1}.  facc[i] += this super-block's share.
-// E::mma32(id, C, A, b0, b1): C = A(16x32, u8) * B(32x8, s8);  E::mma16: the 16x16 * 16x8 form.
+// E::mma32(id, C, A, b0, b1): C = A(16x32, u8) * B(32x8, s8);  E::mma32s: A is s8;  E::mma16: the 16x16 * 16x8 form.
 template <int T, class E> struct TileSb;
 
 // get_scale_min_k4 (ggml-quants.c:703-710) on whole words: bytes of *_lo = sub-blocks 0..3, *_hi = 4..7
@@ -208,24 +230,30 @@ B200Q_HD K4Hdr k4_hdr(uint32_t blk) {
 
 template <int T, class E> struct TileSbK4 {  // q4_K, q5_K
     static B200Q_HD void run(E & ex, const TileCtx & t, int lane, int s, uint32_t blk0, uint32_t blk1, float (&facc)[4]) {
-        constexpr int QS = T == T_Q5_K ? 48 : 16;
+        constexpr int  QS = T == T_Q5_K ? 48 : 16;
+        constexpr bool X16 = T == T_Q4_K;  // high nibbles stay in place (values x 16 still fit u8): one AND instead of SHR + AND
         const int     r = lane >> 2, c = lane & 3;
         const K4Hdr   h0 = k4_hdr(blk0), h1 = k4_hdr(blk1);
-        const int     colb = r < t.n ? r : t.n - 1;  // B fragment column (columns >= n contribute zeros)
-        const uint32_t bmask = r < t.n ? 0xFFFFFFFFu : 0u;
-        const uint32_t qb = t.q + (uint32_t) colb * (uint32_t) t.col_pitch + (uint32_t) s * 256u + (uint32_t) c * 16u;
+        // B fragment column: columns >= n read column n - 1 (their results are never stored)
+        const uint32_t qb = t.q + (uint32_t) (r < t.n ? r : t.n - 1) * (uint32_t) t.col_pitch + (uint32_t) s * 256u + (uint32_t) c * 16u;
         U2 qh0 = { 0, 0 }, qh1 = { 0, 0 };
         if (T == T_Q5_K) {  // bit j of qh byte l: the 5th bit of element l of sub-block j
             qh0 = lds64(blk0 + 16 + 8 * c);
             qh1 = lds64(blk1 + 16 + 8 * c);
         }
-        int acc[4] = { 0, 0, 0, 0 };
+        int acc[4] = { 0, 0, 0, 0 }, acch[4] = { 0, 0, 0, 0 };
 #pragma unroll
         for (int pq = 0; pq < 4; ++pq) {
             const U2 w0 = lds64(blk0 + QS + 32 * pq + 8 * c), w1 = lds64(blk1 + QS + 32 * pq + 8 * c);
             const U4 b  = lds128(qb + 64 * pq);
             uint32_t alo[4] = { w0.x & 0x0F0F0F0Fu, w1.x & 0x0F0F0F0Fu, w0.y & 0x0F0F0F0Fu, w1.y & 0x0F0F0F0Fu };
-            uint32_t ahi[4] = { (w0.x >> 4) & 0x0F0F0F0Fu, (w1.x >> 4) & 0x0F0F0F0Fu, (w0.y >> 4) & 0x0F0F0F0Fu, (w1.y >> 4) & 0x0F0F0F0Fu };
+            uint32_t ahi[4];
+            if (X16) {
+                ahi[0] = w0.x & 0xF0F0F0F0u; ahi[1] = w1.x & 0xF0F0F0F0u; ahi[2] = w0.y & 0xF0F0F0F0u; ahi[3] = w1.y & 0xF0F0F0F0u;
+            } else {
+                ahi[0] = (w0.x >> 4) & 0x0F0F0F0Fu; ahi[1] = (w1.x >> 4) & 0x0F0F0F0Fu;
+                ahi[2] = (w0.y >> 4) & 0x0F0F0F0Fu; ahi[3] = (w1.y >> 4) & 0x0F0F0F0Fu;
+            }
             if (T == T_Q5_K) {
                 alo[0] |= ((qh0.x >> (2 * pq)) & 0x01010101u) << 4;
                 alo[1] |= ((qh1.x >> (2 * pq)) & 0x01010101u) << 4;
@@ -237,24 +265,28 @@ template <int T, class E> struct TileSbK4 {  // q4_K, q5_K
                 ahi[3] |= ((qh1.y >> (2 * pq + 1)) & 0x01010101u) << 4;
             }
             int clo[4], chi[4];
-            ex.mma32(2 * pq, clo, alo, b.x & bmask, b.y & bmask);
-            ex.mma32(2 * pq + 1, chi, ahi, b.z & bmask, b.w & bmask);
+            ex.mma32(2 * pq, clo, alo, b.x, b.y);
+            ex.mma32(2 * pq + 1, chi, ahi, b.z, b.w);
             const uint32_t s0 = pq < 2 ? h0.sc_lo : h0.sc_hi, s1 = pq < 2 ? h1.sc_lo : h1.sc_hi;
-            const int      sh = 16 * (pq & 1);
-            const int      s0a = (int) ((s0 >> sh) & 0xFFu), s0b = (int) ((s0 >> (sh + 8)) & 0xFFu);
-            const int      s1a = (int) ((s1 >> sh) & 0xFFu), s1b = (int) ((s1 >> (sh + 8)) & 0xFFu);
-            acc[0] += s0a * clo[0] + s0b * chi[0];
-            acc[1] += s0a * clo[1] + s0b * chi[1];
-            acc[2] += s1a * clo[2] + s1b * chi[2];
-            acc[3] += s1a * clo[3] + s1b * chi[3];
+            const int      s0a = ubyte_of(s0, 2 * (pq & 1)), s0b = ubyte_of(s0, 2 * (pq & 1) + 1);
+            const int      s1a = ubyte_of(s1, 2 * (pq & 1)), s1b = ubyte_of(s1, 2 * (pq & 1) + 1);
+            acc[0] += s0a * clo[0];
+            acc[1] += s0a * clo[1];
+            acc[2] += s1a * clo[2];
+            acc[3] += s1a * clo[3];
+            acch[0] += s0b * chi[0];
+            acch[1] += s0b * chi[1];
+            acch[2] += s1b * chi[2];
+            acch[3] += s1b * chi[3];
         }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc[i] += X16 ? acch[i] >> 4 : acch[i];  // exact: every term is a multiple of 16
         // - dmin * sum_j m_j * (sum of the activations of sub-block j), dx * d scaling: as ggml_vec_dot_q4_K_q8_K
 #pragma unroll
         for (int cc = 0; cc < 2; ++cc) {
             const int      col = 2 * c + cc < t.n ? 2 * c + cc : t.n - 1;
-            const uint32_t cs  = (uint32_t) (col * t.nsb + s);
-            const U4       bs  = lds128(t.bs + cs * 16u);  // 8 x int16 sums over 32 activations
-            const float    dx  = __uint_as_float_hd(lds32(t.dx + cs * 4u));
+            const U4       bs  = lds128(t.bs + (uint32_t) (col * t.bs_pitch + s * 16));  // 8 x int16 sums over 32 activations
+            const float    dx  = __uint_as_float_hd(lds32(t.dx + (uint32_t) (col * t.dx_pitch + s * 4)));
             int m0 = dp2a_lo_su((int) bs.x, h0.mn_lo, 0);
             m0     = dp2a_hi_su((int) bs.y, h0.mn_lo, m0);
             m0     = dp2a_lo_su((int) bs.z, h0.mn_hi, m0);
@@ -272,9 +304,7 @@ template <int T, class E> struct TileSbK4 {  // q4_K, q5_K
 template <class E> struct TileSbQ6 {  // q6_K: blocks are only 2-byte aligned
     static B200Q_HD void run(E & ex, const TileCtx & t, int lane, int s, uint32_t blk0, uint32_t blk1, float (&facc)[4]) {
         const int      r = lane >> 2, c = lane & 3;
-        const int      colb = r < t.n ? r : t.n - 1;
-        const uint32_t bmask = r < t.n ? 0xFFFFFFFFu : 0u;
-        const uint32_t qb = t.q + (uint32_t) colb * (uint32_t) t.col_pitch + (uint32_t) s * 256u + (uint32_t) c * 16u;
+        const uint32_t qb = t.q + (uint32_t) (r < t.n ? r : t.n - 1) * (uint32_t) t.col_pitch + (uint32_t) s * 256u + (uint32_t) c * 16u;
         uint32_t sc0[4], sc1[4];  // 16 int8 scales of rows r, r + 8
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -311,9 +341,9 @@ template <class E> struct TileSbQ6 {  // q6_K: blocks are only 2-byte aligned
                         const uint32_t bw = qq == 0 ? (hl == 0 ? b.x : b.y) : (hl == 0 ? b.z : b.w);
                         const int      g  = 8 * n + 2 * q + hl;
                         int            cf[4];
-                        ex.mma16(g, cf, a, bw & bmask);
-                        const int sa = (int) (int8_t) (sc0[g >> 2] >> (8 * (g & 3)));
-                        const int sb = (int) (int8_t) (sc1[g >> 2] >> (8 * (g & 3)));
+                        ex.mma16(g, cf, a, bw);
+                        const int sa = sbyte_of(sc0[g >> 2], g & 3);
+                        const int sb = sbyte_of(sc1[g >> 2], g & 3);
                         acc[0] += sa * cf[0];
                         acc[1] += sa * cf[1];
                         acc[2] += sb * cf[2];
@@ -327,9 +357,9 @@ template <class E> struct TileSbQ6 {  // q6_K: blocks are only 2-byte aligned
 #pragma unroll
         for (int cc = 0; cc < 2; ++cc) {
             const int      col = 2 * c + cc < t.n ? 2 * c + cc : t.n - 1;
-            const uint32_t cs  = (uint32_t) (col * t.nsb + s);
-            const U4       b0  = lds128(t.bs + cs * 32u), b1 = lds128(t.bs + cs * 32u + 16u);  // 16 x int16 sums over 16
-            const float    dx  = __uint_as_float_hd(lds32(t.dx + cs * 4u));
+            const uint32_t ba  = t.bs + (uint32_t) (col * t.bs_pitch + s * 32);
+            const U4       b0  = lds128(ba), b1 = lds128(ba + 16u);  // 16 x int16 sums over 16
+            const float    dx  = __uint_as_float_hd(lds32(t.dx + (uint32_t) (col * t.dx_pitch + s * 4)));
             int o0 = dp2a_lo_ss((int) b0.x, sc0[0], 0), o1 = dp2a_lo_ss((int) b0.x, sc1[0], 0);
             o0 = dp2a_hi_ss((int) b0.y, sc0[0], o0); o1 = dp2a_hi_ss((int) b0.y, sc1[0], o1);
             o0 = dp2a_lo_ss((int) b0.z, sc0[1], o0); o1 = dp2a_lo_ss((int) b0.z, sc1[1], o1);
@@ -344,9 +374,57 @@ template <class E> struct TileSbQ6 {  // q6_K: blocks are only 2-byte aligned
     }
 };
 
+// ---- 32-element block formats: one k32 MMA per block, float scales applied to the s32 tile ---------------------------
+// activations: natural-order int8 image per column (col_pitch = k + 16: the LDS.32 of 8 columns x 4 lanes are
+// conflict-free), (d, d * sum q) per (column, block) at t.dx — the arithmetic of quantize_row_q8_1 + vec_dot_q4_0_q8_0 /
+// vec_dot_q8_0_q8_0 (ggml-cpu/quants.c:115-149, :305-333), as in gemv_kq.cu's B32Dot.
+// lane = 4 r + c owns elements 4c .. 4c+3 and 16+4c .. 16+4c+3 of the block (the MMA's own k order).
+B200Q_HD U2 lds64f(uint32_t a) { return lds64(a); }
+template <int T, class E> struct TileB32;
+template <class E> struct TileB32<T_Q4_0, E> {
+    static B200Q_HD void run(E & ex, const TileCtx & t, int lane, int b, uint32_t blk0, uint32_t blk1, float (&facc)[4]) {
+        const int      r = lane >> 2, c = lane & 3;
+        const uint32_t qb = t.q + (uint32_t) (r < t.n ? r : t.n - 1) * (uint32_t) t.col_pitch + (uint32_t) b * 32u + (uint32_t) c * 4u;
+        const uint32_t w0 = ldu32(blk0 + 2 + 4 * c), w1 = ldu32(blk1 + 2 + 4 * c);  // qs[4c .. 4c+3]: low nibbles = elements 4c.., high = 16+4c..
+        const uint32_t a[4] = { w0 & 0x0F0F0F0Fu, w1 & 0x0F0F0F0Fu, (w0 >> 4) & 0x0F0F0F0Fu, (w1 >> 4) & 0x0F0F0F0Fu };
+        int            cf[4];
+        ex.mma32(0, cf, a, lds32(qb), lds32(qb + 16));
+        const float d0 = half_bits_to_float((uint16_t) lds16(blk0)), d1 = half_bits_to_float((uint16_t) lds16(blk1));
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+            const int col = 2 * c + cc < t.n ? 2 * c + cc : t.n - 1;
+            const U2  ds  = lds64f(t.dx + (uint32_t) (col * t.dx_pitch + b * 8));
+            const float dx = __uint_as_float_hd(ds.x), dxs = __uint_as_float_hd(ds.y);
+            facc[cc]     += d0 * (dx * (float) cf[cc]) + (-8.0f * d0) * dxs;
+            facc[2 + cc] += d1 * (dx * (float) cf[2 + cc]) + (-8.0f * d1) * dxs;
+        }
+    }
+};
+template <class E> struct TileB32<T_Q8_0, E> {
+    static B200Q_HD void run(E & ex, const TileCtx & t, int lane, int b, uint32_t blk0, uint32_t blk1, float (&facc)[4]) {
+        const int      r = lane >> 2, c = lane & 3;
+        const uint32_t qb = t.q + (uint32_t) (r < t.n ? r : t.n - 1) * (uint32_t) t.col_pitch + (uint32_t) b * 32u + (uint32_t) c * 4u;
+        const uint32_t a[4] = { ldu32(blk0 + 2 + 4 * c), ldu32(blk1 + 2 + 4 * c), ldu32(blk0 + 18 + 4 * c), ldu32(blk1 + 18 + 4 * c) };
+        int            cf[4];
+        ex.mma32s(0, cf, a, lds32(qb), lds32(qb + 16));
+        const float d0 = half_bits_to_float((uint16_t) lds16(blk0)), d1 = half_bits_to_float((uint16_t) lds16(blk1));
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+            const int   col = 2 * c + cc < t.n ? 2 * c + cc : t.n - 1;
+            const float dx  = __uint_as_float_hd(lds32(t.dx + (uint32_t) (col * t.dx_pitch + b * 8)));
+            facc[cc]     += d0 * (dx * (float) cf[cc]);
+            facc[2 + cc] += d1 * (dx * (float) cf[2 + cc]);
+        }
+    }
+};
+
+template <int T> struct MmaIsKQuant { static constexpr bool value = T == T_Q4_K || T == T_Q5_K || T == T_Q6_K; };
+
 template <class E> struct TileSb<T_Q4_K, E> : TileSbK4<T_Q4_K, E> {};
 template <class E> struct TileSb<T_Q5_K, E> : TileSbK4<T_Q5_K, E> {};
 template <class E> struct TileSb<T_Q6_K, E> : TileSbQ6<E> {};
+template <class E> struct TileSb<T_Q4_0, E> : TileB32<T_Q4_0, E> {};
+template <class E> struct TileSb<T_Q8_0, E> : TileB32<T_Q8_0, E> {};
 
 }  // namespace mma
 }  // namespace b200q

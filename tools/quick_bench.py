@@ -51,7 +51,7 @@ if __name__ == "__main__":
         bench(refs.Q4_K, 14336, 4096, 1, flags=b200q.FLAG_NO_PDL)
     elif which == "cols":
         # 2..8 activation columns (gemv_mma.cu; B200Q_NO_MMA_GEMV=1 times the per-column kernel it replaces)
-        types = [refs.Q4_K, refs.Q6_K] if len(sys.argv) < 3 else [{"q4_K": refs.Q4_K, "q5_K": refs.Q5_K, "q6_K": refs.Q6_K}[sys.argv[2]]]
+        types = [refs.Q4_K, refs.Q6_K] if len(sys.argv) < 3 else [{"q4_K": refs.Q4_K, "q5_K": refs.Q5_K, "q6_K": refs.Q6_K, "q4_0": refs.Q4_0, "q8_0": refs.Q8_0}[sys.argv[2]]]
         for t in types:
             for (m, k) in [(14336, 4096), (4096, 4096), (4096, 14336), (128256, 4096)]:
                 for n in (2, 4, 8):
