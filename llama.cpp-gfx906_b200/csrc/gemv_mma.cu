@@ -197,17 +197,18 @@ template <int T> __global__ void __launch_bounds__(MAX_THREADS, 1) gemv_mma_kern
 
     const uint64_t pol   = policy_evict_first();
     // whole warp, warp-uniform operands; one elected lane issues (code under `if (lane == 0)` would make the compiler
-    // wrap every bulk copy in an ELECT / R2UR.BROADCAST loop)
-    auto issue = [&](int i) {
-        const int       it = i / cpm, ci = i - it * cpm;
-        const int       g = G0 + team + it * teams, chunk = member * cpm + ci;
-        const int       nrows = min(16, p.m - 16 * g);
+    // wrap every bulk copy in an ELECT / R2UR.BROADCAST loop).  Stage i of this warp = (group G0 + team + it * teams,
+    // chunk member * cpm + ci) with i = it * cpm + ci, in ring slot slot0 + i % D: running cursors, no divisions.
+    int  p_g = G0 + team, p_ci = 0, p_slot = 0, issued = 0;  // next stage to request
+    auto issue_next = [&]() {
+        const int       chunk = member * cpm + p_ci;
+        const int       nrows = min(16, p.m - 16 * p_g);
         const long long coff  = (long long) chunk * p.chunk_bytes;
         const uint32_t  lead  = (uint32_t) (coff & 15);
         const uint32_t  win   = (lead + (uint32_t) p.chunk_bytes + 15u) & ~15u;
-        const uint32_t  full  = sb + 8 * (slot0 + i % D);
-        const uint8_t * src   = p.w + (long long) (16 * g) * p.row_bytes + coff - lead;
-        uint32_t        dst   = sb + p.off_stage + (uint32_t) (slot0 + i % D) * p.stage_bytes;
+        const uint32_t  full  = sb + 8 * (slot0 + p_slot);
+        const uint8_t * src   = p.w + (long long) (16 * p_g) * p.row_bytes + coff - lead;
+        uint32_t        dst   = sb + p.off_stage + (uint32_t) (slot0 + p_slot) * p.stage_bytes;
         if (elect_one()) mbar_expect_tx(full, win * (uint32_t) nrows);
         __syncwarp();
         for (int r = 0; r < nrows; ++r) {
@@ -215,10 +216,13 @@ template <int T> __global__ void __launch_bounds__(MAX_THREADS, 1) gemv_mma_kern
             src += p.row_bytes;
             dst += p.pitch;
         }
+        if (++p_ci == cpm) { p_ci = 0; p_g += teams; }
+        if (++p_slot == D) p_slot = 0;
+        ++issued;
     };
     // this kernel owns the whole shared memory, so it never runs beside its predecessor: nothing to prefetch early
     pdl_wait();
-    for (int i = 0; i < min(D, nmine); ++i) issue(i);
+    while (issued < min(D, nmine)) issue_next();
     if (!MmaIsKQuant<T>::value) quantize_cols32(p, sb, warp, lane, NW);
     else if (T == T_Q6_K) quantize_cols<T_Q6_K>(p, sb, warp, lane, NW);
     else quantize_cols<T_Q4_K>(p, sb, warp, lane, NW);  // q4_K and q5_K share the layout
@@ -228,13 +232,13 @@ template <int T> __global__ void __launch_bounds__(MAX_THREADS, 1) gemv_mma_kern
     DevExec       ex;
     const int     r = lane >> 2, c = lane & 3;
     float         facc[4] = { 0.f, 0.f, 0.f, 0.f };
+    int           g = G0 + team, ci = 0, slot = 0, it = 0;  // the stage being consumed
+    uint32_t      parity = 0;
     for (int i = 0; i < nmine; ++i) {
-        const int it = i / cpm, ci = i - it * cpm;
-        const int g = G0 + team + it * teams, chunk = member * cpm + ci;
-        const int slot = slot0 + i % D, use = i / D;
-        mbar_wait(sb + 8 * slot, use & 1);
+        const int chunk = member * cpm + ci;
+        mbar_wait(sb + 8 * (slot0 + slot), parity);
         const uint32_t lead = (uint32_t) (((long long) chunk * p.chunk_bytes) & 15);
-        const uint32_t blk  = sb + p.off_stage + (uint32_t) slot * p.stage_bytes + lead + (uint32_t) r * p.pitch;
+        const uint32_t blk  = sb + p.off_stage + (uint32_t) (slot0 + slot) * p.stage_bytes + lead + (uint32_t) r * p.pitch;
         if constexpr (MmaIsKQuant<T>::value) {
             for (int sbi = 0; sbi < p.kc; ++sbi) {
                 TileSb<T, DevExec>::run(ex, t, lane, chunk * p.kc + sbi, blk + (uint32_t) sbi * BB, blk + (uint32_t) sbi * BB + 8u * p.pitch, facc);
@@ -247,8 +251,10 @@ template <int T> __global__ void __launch_bounds__(MAX_THREADS, 1) gemv_mma_kern
         }
         __syncwarp();              // every lane is done reading the slot
         fence_proxy_async_smem();  // order the generic-proxy reads before the async-proxy refill
-        if (i + D < nmine) issue(i + D);
-        if (ci == cpm - 1) {  // this warp's share of group g is complete
+        if (issued < nmine) issue_next();  // stage i + D goes into the slot just finished
+        if (++slot == D) { slot = 0; parity ^= 1; }
+        if (++ci == cpm) {  // this warp's share of group g is complete
+            ci = 0;
             if (kp > 1) {
                 const uint32_t part = sb + p.off_part + (uint32_t) (((team * 2 + (it & 1)) * kp) * 32 + lane) * 16u;
                 if (member != 0) {
@@ -272,6 +278,8 @@ template <int T> __global__ void __launch_bounds__(MAX_THREADS, 1) gemv_mma_kern
                 }
             }
             facc[0] = facc[1] = facc[2] = facc[3] = 0.f;
+            g += teams;
+            ++it;
         }
     }
 }
