@@ -69,7 +69,7 @@ enum b200q_status {
 /* b200q_mul_mat flags */
 #define B200Q_FLAG_WEIGHTS_IMMUTABLE 1u /* src0 is never written by stream work => weight prefetch may start before the
                                             previous kernel finishes (programmatic dependent launch) */
-#define B200Q_FLAG_FORCE_GEMV        2u /* debugging / measurement: always take the GEMV kernel (n <= 8 required) */
+#define B200Q_FLAG_FORCE_GEMV        2u /* debugging / measurement: always take the GEMV kernels (8 columns per pass) */
 #define B200Q_FLAG_FORCE_MMQ         4u /* debugging / measurement: always take the tensor-core kernel */
 #define B200Q_FLAG_NO_PDL            8u /* launch without programmatic stream serialization */
 

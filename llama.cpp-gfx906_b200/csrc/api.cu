@@ -566,7 +566,15 @@ static int check_mm(const b200q_mul_mat_args * a) {
 static bool use_mmq(const b200q_mul_mat_args * a) {
     if (a->flags & B200Q_FLAG_FORCE_GEMV) return false;
     if (a->flags & B200Q_FLAG_FORCE_MMQ) return mmq_supported(a->type, a->k);
-    return a->n > 8 && mmq_supported(a->type, a->k);
+    // from this many columns on the tensor-core kernel (dequantize to bf16 + tcgen05: ~flat in n below 64 columns) beats
+    // repeated passes of the 8-column integer-MMA GEMV (gemv_mma.cu): two passes win, three are a draw, four lose
+    // (measured cross-over, profiles/r01_cols_crossover.txt)
+    static const int64_t min_n = getenv("B200Q_MMQ_MIN_N") ? atoll(getenv("B200Q_MMQ_MIN_N")) : 17;
+    if (a->n >= min_n) return mmq_supported(a->type, a->k);
+    if (a->n > 8 && !(mma_kernel_for(a->type) && a->ne12 * a->ne13 == 1 && a->nb01 == b200q_row_size(a->type, a->k))) {
+        return mmq_supported(a->type, a->k);  // no multi-pass GEMV for this case
+    }
+    return false;
 }
 
 size_t b200q_mul_mat_workspace(const b200q_mul_mat_args * a) {
@@ -616,18 +624,29 @@ int b200q_mul_mat(const b200q_mul_mat_args * a, const void * w, const float * ac
 
     // 2..8 columns on K-quants: the MMA tile kernel (one pass over the weights; the columns are halved only when their
     // quantized images do not fit beside the ring in shared memory)
-    if (a->n >= 2 && a->n <= 8 && a->ne12 * a->ne13 == 1 && a->nb01 == b200q_row_size(a->type, a->k) && mma_kernel_for(a->type)) {
+    if (a->n >= 2 && a->ne12 * a->ne13 == 1 && a->nb01 == b200q_row_size(a->type, a->k) && mma_kernel_for(a->type)) {
         MmaParams mp{};
         int       grid = 0, smem = 0;
-        int       nc   = (int) a->n;
+        int       nc   = (int) std::min<int64_t>(a->n, 8);
         auto      col_act = [&](int64_t j) { return (const float *) ((const char *) act + j * (long long) a->nb11); };
         auto      col_dst = [&](int64_t j) { return (float *) ((char *) dst + j * (long long) a->nb1); };
         while (nc >= 2 && !plan_mma(mp, grid, smem, a->type, a->m, a->k, nc, w, act, (long long) a->nb11, dst, (long long) a->nb1, di)) {
             nc = (nc + 1) / 2;
         }
-        if (nc >= 2 && (a->n % nc == 0 || a->n % nc >= 2)) {
+        // a last group of one column goes to the n = 1 kernel
+        KqParams     kq{};
+        int          kgrid = 0, ksmem = 0;
+        const bool   tail1 = a->n % nc == 1;
+        const void * wl[1] = { w };
+        float *      dl[1] = { col_dst(a->n - 1) };
+        const int64_t ml[1] = { a->m };
+        if (nc >= 2 && (!tail1 || plan_kq(kq, kgrid, ksmem, a->type, a->k, 1, wl, dl, ml, col_act(a->n - 1), di))) {
             for (int64_t j0 = 0; j0 < a->n; j0 += nc) {
                 const int cur = (int) std::min<int64_t>(nc, a->n - j0);
+                if (cur == 1) {
+                    if (int rc = launch_kq(kq, kgrid, ksmem, a->type, a->flags, st)) return rc;
+                    break;
+                }
                 if (!plan_mma(mp, grid, smem, a->type, a->m, a->k, cur, w, col_act(j0), (long long) a->nb11, col_dst(j0), (long long) a->nb1, di)) {
                     return fail(B200Q_ENOTSUP, "mul_mat: gemv_mma plan failed");
                 }

@@ -29,7 +29,9 @@ def _run(t, m, k, n, seed, flags=0):
                                    (257, 256, 40)])
 def test_mmq_vs_oracle(t, shape):
     m, k, n = shape
-    w, act, _, got = _run(t, m, k, n, seed=700 + t + m)
+    import b200q
+    # n <= 16 would take two passes of the 8-column GEMV (api.cu use_mmq): force the tensor-core kernel
+    w, act, _, got = _run(t, m, k, n, seed=700 + t + m, flags=b200q.FLAG_FORCE_MMQ)
     want = refs.orc_mul_mat(t, w, act)
     assert got.shape == want.shape
     assert np.isfinite(got).all()

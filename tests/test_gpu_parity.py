@@ -217,9 +217,11 @@ KQ_TYPES = [refs.Q4_K, refs.Q5_K, refs.Q6_K, refs.Q4_0, refs.Q8_0]  # the format
 
 @pytest.mark.parametrize("t", KQ_TYPES, ids=lambda t: refs.NAMES[t])
 @pytest.mark.parametrize("shape", [(1, 256, 2), (15, 512, 3), (17, 768, 5), (33, 1024, 7), (100, 2048, 8), (4096, 4096, 8),
-                                   (1024, 4096, 2), (2048, 14336, 4), (14336, 4096, 6), (40, 28672, 8), (3000, 8192, 8)])
+                                   (1024, 4096, 2), (2048, 14336, 4), (14336, 4096, 6), (40, 28672, 8), (3000, 8192, 8),
+                                   (300, 1024, 9), (200, 2048, 16), (64, 4096, 13)])
 def test_mul_mat_mma_columns(t, shape):
-    """n = 2..8 columns on the MMA tile kernel (gemv_mma.cu): ragged row groups (m % 16), every k-chunk size (k / 256
+    """n = 2..16 columns on the MMA tile kernel (gemv_mma.cu; 9..16 = two passes, a last single column on the n = 1
+    kernel): ragged row groups (m % 16), every k-chunk size (k / 256
     odd, even, multiple of 4), every team size (short and long matrices), columns that do not fit shared memory at
     once (k = 28672, n = 8).  Gate: NMSE <= 5e-4 against the oracle, and — because both kernels quantize the
     activations identically — agreement with the n = 1 kernel column by column to fp32 summation noise."""

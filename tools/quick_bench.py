@@ -56,6 +56,12 @@ if __name__ == "__main__":
             for (m, k) in [(14336, 4096), (4096, 4096), (4096, 14336), (128256, 4096)]:
                 for n in (2, 4, 8):
                     bench(t, m, k, n, copies=3 if m > 100000 else None)
+    elif which == "mid":
+        # 9..64 columns: B200Q_MMQ_MIN_N=9 -> tensor-core MMQ, B200Q_MMQ_MIN_N=100000 -> passes of the 8-column MMA GEMV
+        t = {"q4_K": refs.Q4_K, "q6_K": refs.Q6_K, "q8_0": refs.Q8_0, "q4_0": refs.Q4_0}[sys.argv[2]]
+        for (m, k) in [(14336, 4096), (4096, 4096), (4096, 14336)]:
+            for n in (9, 12, 16, 24, 32, 48, 64):
+                bench(t, m, k, n, iters=60)
     elif which == "one":
         t = {"q4_K": refs.Q4_K, "q6_K": refs.Q6_K, "q8_0": refs.Q8_0, "q4_0": refs.Q4_0, "mxfp4": refs.MXFP4}[sys.argv[2]]
         m, k, n = int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5])
