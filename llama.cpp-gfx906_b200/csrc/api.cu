@@ -371,6 +371,11 @@ bool plan_mma(MmaParams & p, int & grid, int & smem, int type, int64_t m, int64_
     }
     if (best < 0) return false;
     p.cpm = p.chunks / p.kp;
+    // CTA pairs (148 = 2 * 74 packs perfectly) share the quantization when it is long enough to matter
+    static const int cl_env = getenv("B200Q_MMA_CLUSTER") ? atoi(getenv("B200Q_MMA_CLUSTER")) : 2;
+    const int        q_units = n * (kquant ? p.nsb : (p.nsb + 7) / 8);  // warp-steps of the quantizer per CTA
+    p.cluster = cl_env >= 2 && grid >= 2 && q_units > 2 * p.nwarps ? 2 : 1;
+    if (p.cluster == 2) grid &= ~1;
     p.w = (const uint8_t *) w; p.act = act; p.dst = dst; p.a_nb1 = a_nb1; p.d_nb1 = d_nb1;
     p.m = (int) m; p.k = (int) k; p.n = n;
     smem = p.off_stage + p.nstages * p.stage_bytes + 64;
@@ -385,19 +390,30 @@ int launch_mma(const MmaParams & p, int grid, int smem, int type, uint32_t flags
     const bool pdl = !(flags & B200Q_FLAG_NO_PDL);
     static const bool debug = getenv("B200Q_DEBUG") != nullptr;
     if (debug) {
-        fprintf(stderr, "[b200q] gemv_mma type=%d m=%d k=%d n=%d grid=%d smem=%d nw=%d kc=%d chunks=%d kp=%d pitch=%d stage_bytes=%d S=%d groups=%d\n",
-                type, p.m, p.k, p.n, grid, smem, p.nwarps, p.kc, p.chunks, p.kp, p.pitch, p.stage_bytes, p.nstages, p.groups);
+        fprintf(stderr, "[b200q] gemv_mma type=%d m=%d k=%d n=%d grid=%d smem=%d nw=%d cluster=%d kc=%d chunks=%d kp=%d pitch=%d stage_bytes=%d S=%d groups=%d\n",
+                type, p.m, p.k, p.n, grid, smem, p.nwarps, p.cluster, p.kc, p.chunks, p.kp, p.pitch, p.stage_bytes, p.nstages, p.groups);
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim          = dim3(grid);
     cfg.blockDim         = dim3(32 * p.nwarps);
     cfg.dynamicSmemBytes = smem;
     cfg.stream           = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs                                          = attr;
-    cfg.numAttrs                                       = pdl ? 1 : 0;
+    cudaLaunchAttribute attr[2];
+    int                 na = 0;
+    if (pdl) {
+        attr[na].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    if (p.cluster > 1) {
+        attr[na].id               = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = (unsigned) p.cluster;
+        attr[na].val.clusterDim.y = 1;
+        attr[na].val.clusterDim.z = 1;
+        ++na;
+    }
+    cfg.attrs    = attr;
+    cfg.numAttrs = na;
     CUDA_TRY(cudaLaunchKernelEx(&cfg, fn, p));
     return 0;
 }

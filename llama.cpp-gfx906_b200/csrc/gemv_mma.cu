@@ -58,10 +58,46 @@ struct DevExec {
     }
 };
 
+// ---- 2-CTA clusters share the activation quantization: each CTA quantizes half of the (column, unit) pairs and stores
+// the result into its own shared memory AND its peer's (distributed shared memory), halving the prologue every CTA pays
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+struct Peer {  // peer's image of this CTA's shared window: remote address = rb + (local address - sb)
+    uint32_t sb, rb;
+    bool     on;
+};
+__device__ __forceinline__ void st_u32(const Peer & pr, uint32_t a, uint32_t v) {
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+    if (pr.on) asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(pr.rb + (a - pr.sb)), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_u16(const Peer & pr, uint32_t a, short v) {
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"(v) : "memory");
+    if (pr.on) asm volatile("st.shared::cluster.u16 [%0], %1;" ::"r"(pr.rb + (a - pr.sb)), "h"(v) : "memory");
+}
+__device__ __forceinline__ void st_f32(const Peer & pr, uint32_t a, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory");
+    if (pr.on) asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(pr.rb + (a - pr.sb)), "f"(v) : "memory");
+}
+__device__ __forceinline__ void st_v2u32(const Peer & pr, uint32_t a, uint32_t v0, uint32_t v1) {
+    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(a), "r"(v0), "r"(v1) : "memory");
+    if (pr.on) asm volatile("st.shared::cluster.v2.u32 [%0], {%1, %2};" ::"r"(pr.rb + (a - pr.sb)), "r"(v0), "r"(v1) : "memory");
+}
+__device__ __forceinline__ void st_v2f32(const Peer & pr, uint32_t a, float v0, float v1) {
+    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a), "f"(v0), "f"(v1) : "memory");
+    if (pr.on) asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(pr.rb + (a - pr.sb)), "f"(v0), "f"(v1) : "memory");
+}
+
 // ---- activation quantization: f32 column -> int8 image in B-fragment order, scale, int16 partial sums -------------
 // the arithmetic of gemv_kq.cu's quantize_act (per 256 values: d = amax / 127, q = round(x * 127 / amax)); one warp
 // per super-block, lane l holds values 8l .. 8l+7
-template <int T> __device__ __forceinline__ void quantize_cols(const MmaParams & p, uint32_t sb, int warp, int lane, int nw) {
+template <int T> __device__ __forceinline__ void quantize_cols(const MmaParams & p, uint32_t sb, int warp, int lane, int nw, const Peer & pr) {
+    // warp = this warp's index among the nw warps of the cluster (or CTA)
     constexpr int BSB = T == T_Q6_K ? 32 : 16;
     constexpr int QB  = 8;  // units in flight per warp: the global loads of a batch are issued together
     const int     total = p.n * p.nsb;
@@ -99,24 +135,24 @@ template <int T> __device__ __forceinline__ void quantize_cols(const MmaParams &
             const uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t) q[3] << 24);
             const uint32_t w1 = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t) q[7] << 24);
             const uint32_t qa = sb + p.off_q + (uint32_t) col * (uint32_t) p.col_pitch + (uint32_t) s * 256u;
-            asm volatile("st.shared.u32 [%0], %1;" ::"r"(qa + (uint32_t) act_word_off<T>(lane * 8)), "r"(w0) : "memory");
-            asm volatile("st.shared.u32 [%0], %1;" ::"r"(qa + (uint32_t) act_word_off<T>(lane * 8 + 4)), "r"(w1) : "memory");
+            st_u32(pr, qa + (uint32_t) act_word_off<T>(lane * 8), w0);
+            st_u32(pr, qa + (uint32_t) act_word_off<T>(lane * 8 + 4), w1);
             const int      s16 = sum + __shfl_xor_sync(0xffffffffu, sum, 1);
             const int      s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 2);
             const uint32_t bsa = sb + p.off_bs + (uint32_t) (col * p.bs_pitch + s * BSB);
             if (T == T_Q6_K) {
-                if ((lane & 1) == 0) asm volatile("st.shared.u16 [%0], %1;" ::"r"(bsa + (uint32_t) (lane >> 1) * 2), "h"((short) s16) : "memory");
+                if ((lane & 1) == 0) st_u16(pr, bsa + (uint32_t) (lane >> 1) * 2, (short) s16);
             } else {
-                if ((lane & 3) == 0) asm volatile("st.shared.u16 [%0], %1;" ::"r"(bsa + (uint32_t) (lane >> 2) * 2), "h"((short) s32) : "memory");
+                if ((lane & 3) == 0) st_u16(pr, bsa + (uint32_t) (lane >> 2) * 2, (short) s32);
             }
-            if (lane == 0) asm volatile("st.shared.f32 [%0], %1;" ::"r"(sb + p.off_dx + (uint32_t) (col * p.dx_pitch + s * 4)), "f"(d) : "memory");
+            if (lane == 0) st_f32(pr, sb + p.off_dx + (uint32_t) (col * p.dx_pitch + s * 4), d);
         }
     }
 }
 
 // 32-element block formats: per-32 scales, natural element order, (d, d * sum q) per block — quantize_row_q8_1's numbers
 // (gemv_kq.cu quantize_act32).  One warp per 256 values per step; lane l holds values 8l .. 8l+7, 4 lanes per block.
-__device__ __forceinline__ void quantize_cols32(const MmaParams & p, uint32_t sb, int warp, int lane, int nw) {
+__device__ __forceinline__ void quantize_cols32(const MmaParams & p, uint32_t sb, int warp, int lane, int nw, const Peer & pr) {
     constexpr int QB = 8;
     const int nb = p.nsb, ng = (nb + 7) / 8, total = p.n * ng;
     for (int u0 = warp; u0 < total; u0 += nw * QB) {
@@ -161,10 +197,8 @@ __device__ __forceinline__ void quantize_cols32(const MmaParams & p, uint32_t sb
                 const uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t) q[3] << 24);
                 const uint32_t w1 = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t) q[7] << 24);
                 const uint32_t qa = sb + p.off_q + (uint32_t) col * (uint32_t) p.col_pitch + (uint32_t) (g * 256 + lane * 8);
-                asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(qa), "r"(w0), "r"(w1) : "memory");
-                if ((lane & 3) == 0) {
-                    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(sb + p.off_dx + (uint32_t) (col * p.dx_pitch + b * 8)), "f"(d), "f"(d * (float) sum) : "memory");
-                }
+                st_v2u32(pr, qa, w0, w1);
+                if ((lane & 3) == 0) st_v2f32(pr, sb + p.off_dx + (uint32_t) (col * p.dx_pitch + b * 8), d, d * (float) sum);
             }
         }
     }
@@ -192,7 +226,14 @@ template <int T> __global__ void __launch_bounds__(MAX_THREADS, 1) gemv_mma_kern
         for (int s = 0; s < S; ++s) mbar_init(sb + 8 * s, 1);
         mbar_fence_init();
     }
-    __syncthreads();
+    const bool clustered = p.cluster > 1;
+    Peer       pr{ sb, 0u, clustered };
+    if (clustered) {
+        cluster_sync_all();  // the peer CTA is running: its shared memory may be written from here on
+        pr.rb = mapa_u32(sb, cluster_ctarank() ^ 1u);
+    } else {
+        __syncthreads();
+    }
     pdl_launch_dependents();
 
     const uint64_t pol   = policy_evict_first();
@@ -223,10 +264,14 @@ template <int T> __global__ void __launch_bounds__(MAX_THREADS, 1) gemv_mma_kern
     // this kernel owns the whole shared memory, so it never runs beside its predecessor: nothing to prefetch early
     pdl_wait();
     while (issued < min(D, nmine)) issue_next();
-    if (!MmaIsKQuant<T>::value) quantize_cols32(p, sb, warp, lane, NW);
-    else if (T == T_Q6_K) quantize_cols<T_Q6_K>(p, sb, warp, lane, NW);
-    else quantize_cols<T_Q4_K>(p, sb, warp, lane, NW);  // q4_K and q5_K share the layout
-    __syncthreads();
+    {
+        const int qw = clustered ? (int) cluster_ctarank() * NW + warp : warp, qn = clustered ? 2 * NW : NW;
+        if (!MmaIsKQuant<T>::value) quantize_cols32(p, sb, qw, lane, qn, pr);
+        else if (T == T_Q6_K) quantize_cols<T_Q6_K>(p, sb, qw, lane, qn, pr);
+        else quantize_cols<T_Q4_K>(p, sb, qw, lane, qn, pr);  // q4_K and q5_K share the layout
+    }
+    if (clustered) cluster_sync_all();  // both halves of the images have landed in both CTAs
+    else __syncthreads();
 
     const TileCtx t{ sb + (uint32_t) p.off_q, sb + (uint32_t) p.off_dx, sb + (uint32_t) p.off_bs, p.col_pitch, p.dx_pitch, p.bs_pitch, p.n };
     DevExec       ex;
