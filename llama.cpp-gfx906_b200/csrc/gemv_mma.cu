@@ -1,4 +1,4 @@
-// gemv_mma.cu — decode GEMV for 2..8 activation columns on K-quant weights (q4_K, q5_K, q6_K): the weights stream
+// gemv_mma.cu — decode GEMV for 2..8 activation columns (q4_K q5_K q6_K, q4_0 q4_1 q5_0 q5_1 q8_0): the weights stream
 // through shared memory once, a warp contracts a 16-row x 8-column tile per super-block with mma.sync (u8 x s8 -> s32),
 // so 8 columns cost the instructions of one (gemv_mma.cuh has the arithmetic and its CPU selftest).
 // Replaces the reference's quantize_q8_1 + mul_mat_vec_q<ncols_dst = 2..8> pair (ggml-cuda/quantize.cu:4-48,
@@ -338,6 +338,9 @@ mma_kernel_t mma_kernel_for(int type) {
         case T_Q6_K: return gemv_mma_kernel<T_Q6_K>;
         case T_Q4_0: return gemv_mma_kernel<T_Q4_0>;
         case T_Q8_0: return gemv_mma_kernel<T_Q8_0>;
+        case T_Q4_1: return gemv_mma_kernel<T_Q4_1>;
+        case T_Q5_0: return gemv_mma_kernel<T_Q5_0>;
+        case T_Q5_1: return gemv_mma_kernel<T_Q5_1>;
         default: return nullptr;
     }
 }

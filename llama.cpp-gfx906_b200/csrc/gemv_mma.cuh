@@ -419,6 +419,41 @@ template <class E> struct TileB32<T_Q8_0, E> {
     }
 };
 
+// bit i of b (i = 0..3) -> bit 8 i: the 5th bits of q5_0 / q5_1 for 4 consecutive elements
+B200Q_HD uint32_t spread4(uint32_t b) { return ((b & 0xFu) * 0x00204081u) & 0x01010101u; }
+
+// q4_1 / q5_0 / q5_1: the q4_0 tile with (d, m) headers and / or a 5th-bit plane (vec_dot_q4_1_q8_1, _q5_0_q8_0,
+// _q5_1_q8_1, ggml-cpu/quants.c:152-303).  HDR = bytes before qs, QH = offset of the 32 5th bits (or -1), M = has a min
+template <int T, class E, int QS, int QH, bool M> struct TileB32N {
+    static B200Q_HD void run(E & ex, const TileCtx & t, int lane, int b, uint32_t blk0, uint32_t blk1, float (&facc)[4]) {
+        const int      r = lane >> 2, c = lane & 3;
+        const uint32_t qb = t.q + (uint32_t) (r < t.n ? r : t.n - 1) * (uint32_t) t.col_pitch + (uint32_t) b * 32u + (uint32_t) c * 4u;
+        const uint32_t w0 = ldu32(blk0 + QS + 4 * c), w1 = ldu32(blk1 + QS + 4 * c);
+        uint32_t       a[4] = { w0 & 0x0F0F0F0Fu, w1 & 0x0F0F0F0Fu, (w0 >> 4) & 0x0F0F0F0Fu, (w1 >> 4) & 0x0F0F0F0Fu };
+        if constexpr (QH >= 0) {
+            const uint32_t h0 = ldu32(blk0 + (uint32_t) QH), h1 = ldu32(blk1 + (uint32_t) QH);
+            a[0] |= spread4(h0 >> (4 * c)) << 4;
+            a[1] |= spread4(h1 >> (4 * c)) << 4;
+            a[2] |= spread4(h0 >> (16 + 4 * c)) << 4;
+            a[3] |= spread4(h1 >> (16 + 4 * c)) << 4;
+        }
+        int cf[4];
+        ex.mma32(0, cf, a, lds32(qb), lds32(qb + 16));
+        const float d0 = half_bits_to_float((uint16_t) lds16(blk0)), d1 = half_bits_to_float((uint16_t) lds16(blk1));
+        // the offset term: m * (d_x * sum q_x) for the formats with a min, else -(8 | 16) * d * (d_x * sum q_x)
+        const float m0 = M ? half_bits_to_float((uint16_t) lds16(blk0 + 2)) : (QH >= 0 ? -16.0f : -8.0f) * d0;
+        const float m1 = M ? half_bits_to_float((uint16_t) lds16(blk1 + 2)) : (QH >= 0 ? -16.0f : -8.0f) * d1;
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+            const int   col = 2 * c + cc < t.n ? 2 * c + cc : t.n - 1;
+            const U2    ds  = lds64f(t.dx + (uint32_t) (col * t.dx_pitch + b * 8));
+            const float dx = __uint_as_float_hd(ds.x), dxs = __uint_as_float_hd(ds.y);
+            facc[cc]     += d0 * (dx * (float) cf[cc]) + m0 * dxs;
+            facc[2 + cc] += d1 * (dx * (float) cf[2 + cc]) + m1 * dxs;
+        }
+    }
+};
+
 template <int T> struct MmaIsKQuant { static constexpr bool value = T == T_Q4_K || T == T_Q5_K || T == T_Q6_K; };
 
 template <class E> struct TileSb<T_Q4_K, E> : TileSbK4<T_Q4_K, E> {};
@@ -426,6 +461,9 @@ template <class E> struct TileSb<T_Q5_K, E> : TileSbK4<T_Q5_K, E> {};
 template <class E> struct TileSb<T_Q6_K, E> : TileSbQ6<E> {};
 template <class E> struct TileSb<T_Q4_0, E> : TileB32<T_Q4_0, E> {};
 template <class E> struct TileSb<T_Q8_0, E> : TileB32<T_Q8_0, E> {};
+template <class E> struct TileSb<T_Q4_1, E> : TileB32N<T_Q4_1, E, 4, -1, true> {};
+template <class E> struct TileSb<T_Q5_0, E> : TileB32N<T_Q5_0, E, 6, 2, false> {};
+template <class E> struct TileSb<T_Q5_1, E> : TileB32N<T_Q5_1, E, 8, 4, true> {};
 
 }  // namespace mma
 }  // namespace b200q

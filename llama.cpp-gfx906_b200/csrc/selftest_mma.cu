@@ -110,7 +110,8 @@ static void fill_row(int type, uint8_t * row, int nblocks) {
     for (int b = 0; b < nblocks; ++b) {
         const int o = b * bb;
         if (type == T_Q6_K) put_half(o + 208, -0.05f, 0.05f);
-        else if (type == T_Q4_0 || type == T_Q8_0) put_half(o, -2.f, 2.f);
+        else if (type == T_Q4_0 || type == T_Q8_0 || type == T_Q5_0) put_half(o, -2.f, 2.f);
+        else if (type == T_Q4_1 || type == T_Q5_1) { put_half(o, 0.f, 2.f); put_half(o + 2, -3.f, 3.f); }
         else { put_half(o, 0.f, 0.1f); put_half(o + 2, 0.f, 0.1f); }
     }
 }
@@ -214,6 +215,9 @@ int main() {
     e += check_type<T_Q6_K>("q6_K");
     e += check_type<T_Q4_0>("q4_0");
     e += check_type<T_Q8_0>("q8_0");
+    e += check_type<T_Q4_1>("q4_1");
+    e += check_type<T_Q5_0>("q5_0");
+    e += check_type<T_Q5_1>("q5_1");
     printf(e ? "selftest_mma FAILED (%d)\n" : "selftest_mma passed\n", e);
     return e ? 1 : 0;
 }

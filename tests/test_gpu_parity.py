@@ -212,7 +212,7 @@ def test_mul_mat_group_equals_separate_calls(t):
         assert refs.nmse(o.cpu().numpy(), refs.orc_mul_mat(t, w, act_h)) <= MAX_NMSE
 
 
-KQ_TYPES = [refs.Q4_K, refs.Q5_K, refs.Q6_K, refs.Q4_0, refs.Q8_0]  # the formats gemv_mma.cu serves
+KQ_TYPES = [refs.Q4_K, refs.Q5_K, refs.Q6_K, refs.Q4_0, refs.Q4_1, refs.Q5_0, refs.Q5_1, refs.Q8_0]  # the formats gemv_mma.cu serves
 
 
 @pytest.mark.parametrize("t", KQ_TYPES, ids=lambda t: refs.NAMES[t])

@@ -6,6 +6,8 @@ timeout 300 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; ech
 timeout 300 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
 timeout 200 python tools/quick_bench.py basic > gpurun_out/quick_bench.log 2>&1; echo "quick rc=$?"
 timeout 100 python tools/quick_bench.py layer >> gpurun_out/quick_bench.log 2>&1
+timeout 200 python tools/quick_bench.py cols > gpurun_out/cols.log 2>&1; echo "cols rc=$?"
+for t in q8_0 q4_0 q5_K; do timeout 100 python tools/quick_bench.py cols $t >> gpurun_out/cols.log 2>&1; done
 bash tools/mmq_set.sh > gpurun_out/mmq_set.log 2>&1; echo "mmq set rc=$?"
 timeout 200 python tools/pp512_bench.py q8_0 512 > gpurun_out/pp512.log 2>&1
 timeout 200 python tools/pp512_bench.py q4_k_m 512 >> gpurun_out/pp512.log 2>&1
@@ -16,4 +18,6 @@ timeout 400 ncu --set full --clock-control none --import-source on -k regex:gemv
     python bench.py --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
 timeout 300 ncu --set full --clock-control none --import-source on -k regex:mmq_kernel -s 2 -c 1 -f -o gpurun_out/mmq_full \
     python tools/mmq_one.py q8_0 14336 4096 512 3 > gpurun_out/ncu_mmq.log 2>&1; echo "ncu mmq rc=$?"
+timeout 300 ncu --set full --clock-control none --import-source on -k regex:gemv_mma -s 4 -c 1 -f -o gpurun_out/mma_full \
+    python tools/quick_bench.py one q4_K 128256 4096 8 > gpurun_out/ncu_mma.log 2>&1; echo "ncu mma rc=$?"
 nvidia-smi > gpurun_out/nvidia_smi.txt; nproc >> gpurun_out/nvidia_smi.txt; lscpu | head -20 >> gpurun_out/nvidia_smi.txt
