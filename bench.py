@@ -403,6 +403,31 @@ def main_b200(args):
                      "avg_launch_us": ms_dev * 1e3 / n_launch, "frac_of_nominal_8TBs": value / world / 8000.0},
         "clocks": clocks,
     }
+    if world == 1:
+        # aux (not the headline): the longest launch of the step alone — the output head, 430 MB > L2, so every launch
+        # streams from HBM — on the n = 1 kernel and, with 8 activation columns, on the MMA tile kernel (gemv_mma.cu)
+        try:
+            head = max(range(len(ops)), key=lambda i: ops[i].m * ops[i].k)
+            o, wq = ops[head], shards[head].shard
+            aux = []
+            for n, kern in ((1, "gemv_kq_kernel"), (8, "gemv_mma_kernel")):
+                a = (torch.rand(n, o.k, device="cuda") * 2 - 1)
+                dst = torch.empty(n, o.m, device="cuda")
+                for _ in range(3):
+                    b200q.mul_mat(wq, a, out=dst)
+                torch.cuda.synchronize()
+                e0.record()
+                for _ in range(20):
+                    b200q.mul_mat(wq, a, out=dst)
+                e1.record()
+                torch.cuda.synchronize()
+                us = e0.elapsed_time(e1) * 1e3 / 20
+                gbs = o.algo_bytes(n) / us / 1e3
+                aux.append({"kernel": f"{kern}<{b200q.TYPE_NAMES.get(o.qtype, o.qtype)}>", "shape": f"{o.k}->{o.m}", "n": n, "us": us,
+                            "achieved": gbs, "unit": "GB/s", "frac": gbs / peak})
+            out["aux"] = {"single_launch": aux}
+        except Exception as e:  # never lose the headline line to the aux leg
+            out["aux"] = {"error": repr(e)}
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = run_cpu_reference(cpu_sample_ops(ops), args.cpu_seconds)
     print(json.dumps(out))
