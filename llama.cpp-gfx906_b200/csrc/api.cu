@@ -382,12 +382,14 @@ bool plan_mma(MmaParams & p, int & grid, int & smem, int type, int64_t m, int64_
     return true;
 }
 
-int launch_mma(const MmaParams & p, int grid, int smem, int type, uint32_t flags, cudaStream_t st) {
+int launch_mma(MmaParams & p, int grid, int smem, int type, uint32_t flags, cudaStream_t st) {
     mma_kernel_t fn = mma_kernel_for(type);
     if (!fn) return fail(B200Q_ENOTSUP, "gemv_mma: unsupported type %d", type);
     const DevInfo & di = dev_info();
     if (int rc = ensure_smem_attr((const void *) fn, di.max_smem)) return rc;
     const bool pdl = !(flags & B200Q_FLAG_NO_PDL);
+    static const bool early_on = !getenv("B200Q_MMA_EARLY") || atoi(getenv("B200Q_MMA_EARLY")) != 0;
+    p.early_prefetch = pdl && early_on && (flags & B200Q_FLAG_WEIGHTS_IMMUTABLE) ? 1 : 0;
     static const bool debug = getenv("B200Q_DEBUG") != nullptr;
     if (debug) {
         fprintf(stderr, "[b200q] gemv_mma type=%d m=%d k=%d n=%d grid=%d smem=%d nw=%d cluster=%d kc=%d chunks=%d kp=%d pitch=%d stage_bytes=%d S=%d groups=%d\n",

@@ -261,8 +261,12 @@ template <int T> __global__ void __launch_bounds__(MAX_THREADS, 1) gemv_mma_kern
         if (++p_slot == D) p_slot = 0;
         ++issued;
     };
-    // this kernel owns the whole shared memory, so it never runs beside its predecessor: nothing to prefetch early
-    pdl_wait();
+    // immutable weights may stream before the predecessor has finished: this kernel owns the whole shared memory, so a CTA
+    // only starts once its SM is free, but SMs whose predecessor CTA had less work are free early
+    if (p.early_prefetch) {
+        while (issued < min(D, nmine)) issue_next();
+    }
+    pdl_wait();  // the activations (and dst) belong to the previous kernels of the stream
     while (issued < min(D, nmine)) issue_next();
     {
         const int qw = clustered ? (int) cluster_ctarank() * NW + warp : warp, qn = clustered ? 2 * NW : NW;

@@ -40,6 +40,7 @@ struct MmaParams {
     int             stage_bytes;  // 16 * pitch
     int             nstages;    // ring depth (>= number of warps)
     int             nwarps;     // 8 or 16 (block size = 32 * nwarps)
+    int             early_prefetch;  // weights immutable: request the first stages before griddepcontrol.wait
     int             cluster;    // 1, or 2: CTA pairs share the activation quantization through distributed shared memory
     int             col_pitch;  // bytes between the int8 images of two columns (k + 64 | k + 16: conflict-free fragment loads)
     int             dx_pitch, bs_pitch;  // bytes between the columns' scales / partial sums (one unit of padding each)
