@@ -8,7 +8,8 @@ i.e. far larger than L2, so every step streams cold from HBM; no flush needed).
   value   algorithmic GB/s of the pass with everything resident in HBM (CUDA-graph replay of the 225 launches,
           CUDA events on the launching stream, max over ranks)
   e2e     the same pass through the C-ABI with HOST buffers: per step the activations are copied host->device from
-          pinned memory, the pass runs, all results are copied device->host (copies inside the timed region)
+          pinned memory, the pass runs, all results are copied device->host (copies inside the timed region; on one
+          GPU the copies of a chunk of launches overlap the compute of its neighbours, B200Q_BENCH_E2E=serial = old)
   --impl reference   the reference's own ggml-cpu implementation (oracle/_ref, unmodified) of the same matmuls on
           the box's host cores, on a bounded sample of the workload
 
@@ -331,12 +332,72 @@ def main_b200(args):
     h2d = act_host.numel() * 4
     d2h = out_host.numel() * 4
 
-    def e2e_step():
+    def e2e_step_serial():
         rc = L.b200q_memcpy(C.c_void_p(act_dev.data_ptr()), C.c_void_p(act_host.data_ptr()), C.c_size_t(h2d), 1, stream)
         assert rc == 0
         graph.replay()
         rc = L.b200q_memcpy(C.c_void_p(out_host.data_ptr()), C.c_void_p(out_dev.data_ptr()), C.c_size_t(d2h), 2, stream)
         assert rc == 0
+        assert L.b200q_stream_synchronize(stream) == 0
+
+    # single GPU: the same copies and launches as ONE CUDA graph in which the copies ride two copy streams — the
+    # activations of launch chunk c+1 arrive while chunk c computes, the results of chunk c leave while chunk c+1
+    # computes (every step still moves all h2d + d2h bytes inside the timed region)
+    e2e_mode, e2e_graph = "serial", None
+    if world == 1 and os.environ.get("B200Q_BENCH_E2E", "pipelined") == "pipelined":
+        try:
+            n_chunks = 16
+            per = (len(launches) + n_chunks - 1) // n_chunks
+            chunks = [launches[i:i + per] for i in range(0, len(launches), per)]
+            s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+
+            def copy(dst_t, src_t, lo, hi, kind, st):
+                rc = L.b200q_memcpy(C.c_void_p(dst_t.data_ptr() + 4 * lo), C.c_void_p(src_t.data_ptr() + 4 * lo),
+                                    C.c_size_t(4 * (hi - lo)), kind, C.c_void_p(st.cuda_stream))
+                assert rc == 0
+
+            e2e_graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(e2e_graph):
+                main = torch.cuda.current_stream()
+                s_in.wait_stream(main)
+                s_out.wait_stream(main)
+                arrived = []
+                for ch in chunks:
+                    ops_c = [j for idx in ch for j in idx]
+                    copy(act_dev, act_host, k_off[ops_c[0]], k_off[ops_c[-1] + 1], 1, s_in)
+                    ev = torch.cuda.Event()
+                    ev.record(s_in)
+                    arrived.append(ev)
+                for ch, ev in zip(chunks, arrived):
+                    ops_c = [j for idx in ch for j in idx]
+                    main.wait_event(ev)
+                    for idx in ch:
+                        i = idx[0]
+                        b200q.mul_mat_group([shards[j].shard for j in idx], act_dev[k_off[i]:k_off[i + 1]].view(1, ops[i].k),
+                                            outs=[out_dev[m_off[j]:m_off[j + 1]].view(1, ops[j].m) for j in idx])
+                    done = torch.cuda.Event()
+                    done.record(main)
+                    s_out.wait_event(done)
+                    copy(out_host, out_dev, m_off[ops_c[0]], m_off[ops_c[-1] + 1], 2, s_out)
+                main.wait_stream(s_in)
+                main.wait_stream(s_out)
+            # the pipelined graph must move exactly what the serial step moves
+            out_host.zero_()
+            e2e_graph.replay()
+            torch.cuda.synchronize()
+            chk = out_host.clone()
+            e2e_step_serial()
+            assert torch.equal(chk, out_host), "pipelined e2e graph and serial e2e step disagree"
+            e2e_mode = f"pipelined ({len(chunks)} chunks of launches, copies on two copy streams inside one CUDA graph)"
+        except Exception as e:  # keep the serial step rather than lose the bench line
+            print(f"[bench] pipelined e2e unavailable ({e!r}); using the serial step", file=sys.stderr)
+            e2e_graph = None
+            torch.cuda.synchronize()
+
+    def e2e_step():
+        if e2e_graph is None:
+            return e2e_step_serial()
+        e2e_graph.replay()
         assert L.b200q_stream_synchronize(stream) == 0
 
     for _ in range(max(3, args.warmup)):
@@ -393,7 +454,7 @@ def main_b200(args):
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e, "results_finite": finite,
                 "api": f"b200q_memcpy(H2D) + {n_launch} x b200q_mul_mat_group ({len(ops)} matmuls) + b200q_memcpy(D2H) + "
-                       "b200q_stream_synchronize"},
+                       "b200q_stream_synchronize", "mode": e2e_mode},
         "gpu_launches": n_launch * args.steps,
         "roofline": {"bound": "hbm", "achieved": value / world, "peak": peak, "unit": "GB/s",
                      "frac": value / world / peak, "traffic": traffic, "peak_source": peak_src,
