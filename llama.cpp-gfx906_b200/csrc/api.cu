@@ -360,16 +360,34 @@ bool plan_mma(MmaParams & p, int & grid, int & smem, int type, int64_t m, int64_
     // warps per 16-row group along k: the fewest sequential stages per warp
     static const int kp_env = getenv("B200Q_MMA_KP") ? atoi(getenv("B200Q_MMA_KP")) : 0;
     const int gpc = (p.groups + grid - 1) / grid;
-    long long best = -1;
-    for (int kp = 1; kp <= 8; kp *= 2) {
-        if (p.chunks % kp) continue;
-        if (kp_env && kp != kp_env) continue;
-        const int       teams = NWc / kp;
-        if (kp > 1 && teams > 8) continue;  // named barriers 1..8
-        const long long cost  = (long long) ((gpc + teams - 1) / teams) * (p.chunks / kp);
-        if (best < 0 || cost < best) { best = cost; p.kp = kp; }
-    }
+    auto best_kp = [&](int chunks, int & kp_out) -> long long {
+        long long best = -1;
+        for (int kp = 1; kp <= 8; kp *= 2) {
+            if (chunks % kp) continue;
+            if (kp_env && kp != kp_env) continue;
+            const int teams = NWc / kp;
+            if (kp > 1 && teams > 8) continue;  // named barriers 1..8
+            const long long cost = (long long) ((gpc + teams - 1) / teams) * (chunks / kp);
+            if (best < 0 || cost < best) { best = cost; kp_out = kp; }
+        }
+        return best;
+    };
+    long long best = best_kp(p.chunks, p.kp);
     if (best < 0) return false;
+    // long rows of a short matrix (ffn_down at n = 2): when a warp would walk >= 4 stages in sequence and half-size
+    // stages let twice as many warps share a group, the smaller copies pay off (4096x14336, n = 2: 16.1 -> 13.0 us)
+    if (!kc_env && best >= 4 && p.kc >= 2 && p.kc % 2 == 0) {
+        const int kc2 = p.kc / 2, cb2 = kc2 * bb;
+        int pitch2 = round_up(cb2 + 14, 16);
+        while (lds64 ? (pitch2 % 128 != 32 && pitch2 % 128 != 96) : (pitch2 / 16) % 2 == 0) pitch2 += 16;
+        const int S2 = (di.max_smem - p.off_stage - 64) / (16 * pitch2);
+        int       kp2 = 0;
+        const long long cost2 = S2 >= NWc && cb2 >= 256 ? best_kp(p.nsb / kc2, kp2) : -1;
+        if (cost2 > 0 && cost2 * kc2 * 10 <= best * p.kc * 6) {
+            p.kc = kc2; p.chunk_bytes = cb2; p.pitch = pitch2; p.stage_bytes = 16 * pitch2;
+            p.chunks = p.nsb / kc2; p.nstages = std::min(S2, 40); p.kp = kp2;
+        }
+    }
     p.cpm = p.chunks / p.kp;
     // CTA pairs (148 = 2 * 74 packs perfectly) share the quantization when it is long enough to matter
     static const int cl_env = getenv("B200Q_MMA_CLUSTER") ? atoi(getenv("B200Q_MMA_CLUSTER")) : 2;
@@ -433,6 +451,21 @@ B200Q_API void b200q_debug_timestamps(void * dev_buf) { g_ts = (unsigned long lo
 B200Q_API void b200q_debug_hang_buffer(void * host_mapped) { kq_set_hang_buffer((unsigned long long *) host_mapped); }
 B200Q_API void b200q_debug_mmq_stamps(void * dev_buf) { mmq_set_debug((unsigned long long *) dev_buf); }
 const char * b200q_last_error(void) { return g_err.c_str(); }
+// host-side test hook (tests/test_plan_cpu.py): the launch plan gemv_mma would get on a device with `sms` SMs and
+// `max_smem` bytes of shared memory per CTA; needs no GPU.  out[16] = nwarps, cluster, kc, chunks, kp, cpm, pitch,
+// stage_bytes, nstages, groups, grid, smem, col_pitch, off_stage, chunk_bytes, row_bytes.  Returns 1 if a plan exists.
+B200Q_API int b200q_debug_plan_gemv_mma(int type, int64_t m, int64_t k, int n, int sms, int max_smem, int * out) {
+    DevInfo di;
+    di.ok = true; di.sms = sms; di.max_smem = max_smem; di.cc = 100;
+    MmaParams p{};
+    int       grid = 0, smem = 0;
+    alignas(16) static float dummy[4];
+    if (!plan_mma(p, grid, smem, type, m, k, n, dummy, dummy, (long long) k * 4, dummy, (long long) m * 4, di)) return 0;
+    const int v[16] = { p.nwarps, p.cluster, p.kc, p.chunks, p.kp, p.cpm, p.pitch, p.stage_bytes, p.nstages, p.groups, grid, smem,
+                        p.col_pitch, p.off_stage, p.chunk_bytes, p.row_bytes };
+    for (int i = 0; i < 16; ++i) out[i] = v[i];
+    return 1;
+}
 
 int b200q_device_count(void) {
     int n = 0;

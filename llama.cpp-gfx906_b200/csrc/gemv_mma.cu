@@ -4,12 +4,14 @@
 // Replaces the reference's quantize_q8_1 + mul_mat_vec_q<ncols_dst = 2..8> pair (ggml-cuda/quantize.cu:4-48,
 // mmvq.cu:139-226).
 //
-//   * 16 warps (8 when the ring cannot give each of 16 a slot), one CTA per SM with the whole shared memory: quantized activation images of all columns (int8, permuted
-//     into B-fragment order) + a ring of stages.  A stage = 16 rows x kc super-blocks; every row of a stage is its own
-//     bulk copy (TMA 1-D) into a padded pitch (== 32 or 96 mod 128), which makes the per-lane A-fragment loads
-//     (LDS.64, rows 8 apart) bank-conflict-free without touching the GGUF layout in HBM.
-//   * every warp feeds itself (slot ownership, as in gemv_kq.cu): lanes 0..15 issue the 16 row copies of the warp's
-//     next stage into the slot the warp has just finished.
+//   * 16 warps (8 when the ring cannot give each of 16 a slot), one CTA per SM with the whole shared memory: quantized
+//     activation images of all columns (int8, permuted into B-fragment order) + a ring of stages.  A stage = 16 rows x kc
+//     super-blocks (or blocks); every row of a stage is its own bulk copy (TMA 1-D) into a padded pitch (== 32 or 96 mod
+//     128 for LDS.64 fragments, an odd multiple of 16 for LDS.32 ones), which makes the per-lane A-fragment loads (rows 8
+//     apart) bank-conflict-free without touching the GGUF layout in HBM.
+//   * every warp feeds itself (slot ownership, as in gemv_kq.cu): one elected lane issues the 16 row copies of the warp's
+//     next stage, from warp-uniform code, into the slot the warp has just finished.
+//   * CTA pairs (2-CTA clusters) split the activation quantization and store their halves into both shared memories.
 //   * a 16-row group is shared by kp warps along k ("team", kp = 1, 2, 4, 8 chosen by the planner so that short
 //     matrices still occupy every warp); partial tiles meet in shared memory behind a named barrier and are summed in
 //     fixed order: results are bit-reproducible and independent of the grid.

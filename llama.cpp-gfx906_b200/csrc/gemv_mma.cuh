@@ -1,5 +1,5 @@
-// gemv_mma.cuh — decode GEMV for 2..8 activation columns (speculative / batched decode) on K-quant weights:
-// launch parameters and the per-super-block tile arithmetic of gemv_mma.cu.
+// gemv_mma.cuh — decode GEMV for 2..8 activation columns (speculative / batched decode) on K-quant and 32-element block
+// weights: launch parameters and the per-super-block / per-block tile arithmetic of gemv_mma.cu.
 //
 // Role in the reference: mul_mat_vec_q with ncols_dst = 2..8 (ggml-cuda/mmvq.cu:139-226, the ncols switch :237-498),
 // which re-runs the per-column dp4a dot for every column.  Here one warp owns a 16-row x 8-column tile and contracts
