@@ -622,7 +622,8 @@ static bool use_mmq(const b200q_mul_mat_args * a) {
     // (measured cross-over, profiles/r01_cols_crossover.txt)
     static const int64_t min_n = getenv("B200Q_MMQ_MIN_N") ? atoll(getenv("B200Q_MMQ_MIN_N")) : 17;
     if (a->n >= min_n) return mmq_supported(a->type, a->k);
-    if (a->n > 8 && !(mma_kernel_for(a->type) && a->ne12 * a->ne13 == 1 && a->nb01 == b200q_row_size(a->type, a->k))) {
+    if (a->n > 8 && !(mma_kernel_for(a->type) && a->ne12 * a->ne13 == 1 && a->nb01 == b200q_row_size(a->type, a->k) &&
+                      a->nb01 % 16 == 0 && a->k % (blck_elems(a->type) == 256 ? 256 : 32) == 0)) {
         return mmq_supported(a->type, a->k);  // no multi-pass GEMV for this case
     }
     return false;
