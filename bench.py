@@ -346,7 +346,7 @@ def main_b200(args):
     e2e_mode, e2e_graph = "serial", None
     if world == 1 and os.environ.get("B200Q_BENCH_E2E", "pipelined") == "pipelined":
         try:
-            n_chunks = 16
+            n_chunks = int(os.environ.get("B200Q_BENCH_E2E_CHUNKS", "8"))
             per = (len(launches) + n_chunks - 1) // n_chunks
             chunks = [launches[i:i + per] for i in range(0, len(launches), per)]
             s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()

@@ -240,7 +240,8 @@ def test_mul_mat_mma_columns(t, shape):
     for j in range(n):
         one = b200q.mul_mat(wt, a[j:j + 1].contiguous()).cpu().numpy()
         # q5_K at n = 1 runs on the per-32 (q8_1) activation quantization of gemv.cu: only statistically equal
-        assert refs.nmse(got[j:j + 1], one) <= (1e-9 if t != refs.Q5_K else 2e-4), j
+        same_quant = t != refs.Q5_K and refs.row_size(t, k) % 16 == 0  # else: per-column kernel / tensor-core kernel took it
+        assert refs.nmse(got[j:j + 1], one) <= (1e-9 if same_quant else 2e-4), j
     # bit-reproducible
     again = b200q.mul_mat(wt, a).cpu().numpy()
     assert again.tobytes() == got.tobytes()
