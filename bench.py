@@ -346,7 +346,7 @@ def main_b200(args):
     e2e_mode, e2e_graph = "serial", None
     if world == 1 and os.environ.get("B200Q_BENCH_E2E", "pipelined") == "pipelined":
         try:
-            n_chunks = int(os.environ.get("B200Q_BENCH_E2E_CHUNKS", "8"))
+            n_chunks = int(os.environ.get("B200Q_BENCH_E2E_CHUNKS", "16"))
             per = (len(launches) + n_chunks - 1) // n_chunks
             chunks = [launches[i:i + per] for i in range(0, len(launches), per)]
             s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
@@ -361,16 +361,29 @@ def main_b200(args):
                 main = torch.cuda.current_stream()
                 s_in.wait_stream(main)
                 s_out.wait_stream(main)
-                arrived = []
-                for ch in chunks:
+                # activations: the first chunk's slice, then all the rest — only TWO joins into the compute stream (every
+                # join costs the programmatic-launch overlap of the kernel behind it); results leave chunk by chunk
+                n_join = int(os.environ.get("B200Q_BENCH_E2E_JOINS", "2"))
+                first = [j for idx in chunks[0] for j in idx]
+                arrived = {}
+                if n_join <= 2:
+                    copy(act_dev, act_host, k_off[first[0]], k_off[first[-1] + 1], 1, s_in)
+                    arrived[0] = torch.cuda.Event()
+                    arrived[0].record(s_in)
+                    if len(chunks) > 1:
+                        copy(act_dev, act_host, k_off[first[-1] + 1], k_off[-1], 1, s_in)
+                        arrived[1] = torch.cuda.Event()
+                        arrived[1].record(s_in)
+                else:
+                    for c, ch in enumerate(chunks):
+                        ops_c = [j for idx in ch for j in idx]
+                        copy(act_dev, act_host, k_off[ops_c[0]], k_off[ops_c[-1] + 1], 1, s_in)
+                        arrived[c] = torch.cuda.Event()
+                        arrived[c].record(s_in)
+                for c, ch in enumerate(chunks):
                     ops_c = [j for idx in ch for j in idx]
-                    copy(act_dev, act_host, k_off[ops_c[0]], k_off[ops_c[-1] + 1], 1, s_in)
-                    ev = torch.cuda.Event()
-                    ev.record(s_in)
-                    arrived.append(ev)
-                for ch, ev in zip(chunks, arrived):
-                    ops_c = [j for idx in ch for j in idx]
-                    main.wait_event(ev)
+                    if c in arrived:
+                        main.wait_event(arrived[c])
                     for idx in ch:
                         i = idx[0]
                         b200q.mul_mat_group([shards[j].shard for j in idx], act_dev[k_off[i]:k_off[i + 1]].view(1, ops[i].k),
@@ -388,7 +401,8 @@ def main_b200(args):
             chk = out_host.clone()
             e2e_step_serial()
             assert torch.equal(chk, out_host), "pipelined e2e graph and serial e2e step disagree"
-            e2e_mode = f"pipelined ({len(chunks)} chunks of launches, copies on two copy streams inside one CUDA graph)"
+            e2e_mode = (f"pipelined (one CUDA graph: activations H2D on a copy stream with {len(arrived)} joins, results D2H on a "
+                        f"second copy stream after each of {len(chunks)} chunks of launches)")
         except Exception as e:  # keep the serial step rather than lose the bench line
             print(f"[bench] pipelined e2e unavailable ({e!r}); using the serial step", file=sys.stderr)
             e2e_graph = None
