@@ -223,6 +223,10 @@ def main_b200(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly ONE JSON line: whatever libraries print meanwhile ("NCCL version ...") goes to stderr
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
     torch.cuda.set_device(local)
     dist = None
@@ -505,6 +509,8 @@ def main_b200(args):
             out["aux"] = {"error": repr(e)}
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = run_cpu_reference(cpu_sample_ops(ops), args.cpu_seconds)
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
     print(json.dumps(out))
     return leave()
 
