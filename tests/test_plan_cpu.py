@@ -77,3 +77,29 @@ def test_plan_uses_the_machine():
     assert wo["kp"] >= 4                                  # 256 row groups over 148 CTAs: k is split across warps
     down = plan(refs.Q4_K, 4096, 14336, 2)
     assert down["kc"] == 2 and down["kp"] == 4            # half-size stages so that four warps share a group
+
+
+def _workspace(t, m, k, n, flags=0, batch=1):
+    import b200q
+    rs = refs.row_size(t, k)
+    a = b200q.MulMatArgs(t, k, m, n, 1, 1, batch, 1, rs, rs * m, rs * m, k * 4, k * 4 * n, k * 4 * n * batch,
+                         m * 4, m * 4 * n, m * 4 * n * batch, flags)
+    fn = b200q.lib().b200q_mul_mat_workspace
+    fn.restype = C.c_size_t
+    return fn(C.byref(a))
+
+
+def test_kernel_choice_by_columns():
+    """b200q_mul_mat_workspace mirrors the dispatch (api.cu use_mmq): 0 bytes = a GEMV kernel serves the shape, > 0 = the
+    tensor-core kernel (which needs its packed bf16 activation tiles).  Pure host logic."""
+    import b200q
+    m, k = 4096, 4096
+    for n in (1, 2, 8, 9, 16):
+        assert _workspace(refs.Q4_K, m, k, n) == 0, n            # gemv_kq / gemv_mma (two passes for 9..16)
+    assert _workspace(refs.Q4_K, m, k, 17) > 0                   # measured cross-over: three passes no longer win
+    assert _workspace(refs.Q4_K, m, k, 512) > 0
+    assert _workspace(refs.MXFP4, m, k, 8) == 0 and _workspace(refs.MXFP4, m, k, 9) > 0      # no MMA GEMV tile
+    assert _workspace(refs.Q6_K, m, 1024, 8) == 0 and _workspace(refs.Q6_K, m, 1024, 9) > 0  # 840-byte rows: no plan
+    assert _workspace(refs.Q4_K, m, k, 12, batch=3) > 0          # batch dims: no multi-pass GEMV
+    assert _workspace(refs.Q4_K, m, k, 4, flags=b200q.FLAG_FORCE_MMQ) > 0
+    assert _workspace(refs.Q4_K, m, k, 512, flags=b200q.FLAG_FORCE_GEMV) == 0
