@@ -49,3 +49,20 @@ def test_compute_fails_loudly_without_a_gpu():
         pytest.skip("GPU present")
     with pytest.raises(RuntimeError):
         b200q.dequantize(b200q.QTensor(b200q.Q4_0, (1, 32), None))
+
+
+def test_plugin_exports_the_ggml_entry_points():
+    """libggml-b200.so exports what ggml-backend-reg.cpp:232-276 looks up by name; without a cc 10.0 device
+    ggml_backend_score() is 0 (the registry then refuses to load it: there is no CPU fallback to register)"""
+    import refs
+    import torch
+    plugin = os.path.join(ROOT, "llama.cpp-gfx906_b200", "lib", "libggml-b200.so")
+    d = refs.ref_dir()
+    if d is None or not os.path.exists(plugin):
+        pytest.skip("plugin or oracle/_ref not built (needs the reference headers)")
+    ctypes.CDLL(os.path.join(d, "libggml-base.so"), mode=ctypes.RTLD_GLOBAL)  # the host process provides ggml-base
+    P = ctypes.CDLL(plugin)
+    for name in ("ggml_backend_init", "ggml_backend_score", "ggml_backend_b200_reg"):
+        assert hasattr(P, name), name
+    if not torch.cuda.is_available():
+        assert P.ggml_backend_score() == 0

@@ -234,9 +234,10 @@ def test_mul_mat_mma_columns(t, shape):
     a = torch.from_numpy(act).cuda()
     got = b200q.mul_mat(wt, a).cpu().numpy()
     assert np.isfinite(got).all()
-    if m * k <= 4096 * 4096:
-        want = refs.orc_mul_mat(t, w, act)
-        assert refs.nmse(got, want) <= MAX_NMSE
+    # every shape is checked against the CPU path: the unmodified reference on all host threads when oracle/_ref is
+    # there (the BASELINE shapes take the scalar restatement tens of seconds), else the restatement
+    want = refs.ref_mul_mat(t, w, act)[0] if refs.ref() is not None else refs.orc_mul_mat(t, w, act)
+    assert refs.nmse(got, want) <= MAX_NMSE
     for j in range(n):
         one = b200q.mul_mat(wt, a[j:j + 1].contiguous()).cpu().numpy()
         # q5_K at n = 1 runs on the per-32 (q8_1) activation quantization of gemv.cu: only statistically equal

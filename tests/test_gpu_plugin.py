@@ -1,0 +1,133 @@
+"""The drop-in boundary under test: libggml-b200.so (the ggml backend plugin) driven by the reference's OWN code.
+
+  * test_backend_ops_*: the unmodified reference harness (oracle/_ref/**/test-backend-ops, built from
+    /root/reference/tests/test-backend-ops.cpp) runs its MUL_MAT / MUL_MAT_ID / GET_ROWS cases against the plugin
+    (GGML_BACKEND_PATH, ggml-backend-reg.cpp:588-592) with ggml-cpu as its oracle: NMSE <= 5e-4 for the matmuls
+    (test-backend-ops.cpp:3106-3108, 3209-3211), 1e-7 for GET_ROWS (:948-950).  Asserted: rc 0, zero FAIL lines, and at
+    least the number of supported + passing cases the previous round logged.
+  * test_inprocess_*: the plugin dlopen'ed INSIDE this process through ggml_backend_load (tests/plugin_driver.cpp),
+    used directly (alloc / set / graph_compute / get, workspace growth inside one graph) and through
+    ggml_backend_sched next to the CPU backend (supports_op, buffer types, cross-backend copies).
+"""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+import refs
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PLUGIN = os.path.join(ROOT, "llama.cpp-gfx906_b200", "lib", "libggml-b200.so")
+
+pytestmark = pytest.mark.gpu
+
+
+def _need_ref():
+    d = refs.ref_dir()
+    if d is None or not os.path.exists(PLUGIN):
+        pytest.skip("oracle/_ref (reference build) or the plugin is not present")
+    return d
+
+
+def _run_tbo(op, timeout=900):
+    d = _need_ref()
+    exe = os.path.join(d, "test-backend-ops")
+    env = dict(os.environ, GGML_BACKEND_PATH=PLUGIN)
+    p = subprocess.run([exe, "test", "-o", op], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                       timeout=timeout)
+    out = re.sub(r"\x1b\[[0-9;]*m", "", p.stdout)
+    lines = [l for l in out.splitlines() if l.lstrip().startswith(op + "(")]
+    ok = sum(1 for l in lines if l.rstrip().endswith("OK"))
+    fail = [l for l in lines if "FAIL" in l]
+    unsup = sum(1 for l in lines if "not supported" in l)
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(ROOT, "gpurun_out", f"tbo_{op}.txt"), "w") as f:
+        f.write(out)
+    assert "Backend B2000" in out, out[-2000:]
+    return p.returncode, ok, fail, unsup, out
+
+
+# supported-and-passing counts of round 1 (profiles/r01_test_backend_ops_*_v2.txt); a regression in supports_op or in a
+# kernel shows up as a lower count or a FAIL line
+@pytest.mark.parametrize("op,min_ok", [("GET_ROWS", 43), ("MUL_MAT", 243), ("MUL_MAT_ID", 194)])
+def test_backend_ops_against_plugin(op, min_ok):
+    rc, ok, fail, unsup, out = _run_tbo(op)
+    assert not fail, fail[:5]
+    assert rc == 0, out[-2000:]
+    assert ok >= min_ok, (ok, unsup)
+    assert re.search(r"Backend B2000: OK", out)
+
+
+_pd = None
+
+
+def _driver():
+    global _pd
+    if _pd is None:
+        d = _need_ref()
+        L = C.CDLL(os.path.join(d, "plugin_driver.so"))
+        L.pd_load.argtypes = [C.c_char_p]
+        L.pd_device_name.restype = C.c_char_p
+        L.pd_proc_address.restype = C.c_void_p
+        L.pd_proc_address.argtypes = [C.c_char_p]
+        L.pd_mul_mat_seq.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                     C.c_void_p]
+        L.pd_sched_mlp.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                   C.c_void_p, C.c_void_p, C.c_void_p]
+        n = L.pd_load(PLUGIN.encode())
+        assert n >= 1, f"ggml_backend_load({PLUGIN}) registered {n} devices"
+        _pd = L
+    return _pd
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def test_inprocess_load_and_registry():
+    L = _driver()
+    assert L.pd_device_name(0) == b"B2000"
+    assert L.pd_proc_address(b"ggml_backend_get_features")
+    with open("/proc/self/maps") as f:
+        assert "libggml-b200.so" in f.read()
+
+
+@pytest.mark.parametrize("t", [refs.Q4_K, refs.Q8_0], ids=lambda t: refs.NAMES[t])
+def test_inprocess_mul_mat_workspace_growth(t):
+    """one graph_compute, four MUL_MAT nodes with 1, 40, 300 and 700 columns: GEMV, then the tensor-core kernel whose
+    workspace has to grow twice while earlier nodes are still in flight on the stream"""
+    L = _driver()
+    m, k = 384, 1024
+    ns = np.array([1, 40, 300, 700], dtype=np.int64)
+    w = refs.make_weights(t, m, k, seed=31 + t)
+    act = refs.uniform_weights(int(ns.max()), k, seed=32)
+    out = np.zeros(int(ns.sum()) * m, dtype=np.float32)
+    rc = L.pd_mul_mat_seq(0, t, m, k, _p(w), _p(ns), len(ns), _p(act), _p(out))
+    assert rc == 0, rc
+    off = 0
+    for n in ns:
+        n = int(n)
+        want = refs.ref_mul_mat(t, w, act[:n])[0]
+        got = out[off:off + n * m].reshape(n, m)
+        assert refs.nmse(got, want) <= 5e-4, n
+        off += n * m
+
+
+def test_inprocess_scheduler_with_cpu_backend():
+    """W2 . silu(W1 . x) through ggml_backend_sched over [B200, CPU] equals the CPU backend alone (NMSE <= 5e-4)"""
+    L = _driver()
+    t, k, m, n = refs.Q4_K, 1024, 2048, 3
+    w1 = refs.make_weights(t, m, k, seed=41)
+    w2 = refs.make_weights(t, k, m, seed=42)
+    x = refs.uniform_weights(n, k, seed=43)
+    y = np.zeros((n, k), dtype=np.float32)
+    y_cpu = np.zeros((n, k), dtype=np.float32)
+    splits = C.c_int(0)
+    rc = L.pd_sched_mlp(0, t, k, m, _p(w1), _p(w2), _p(x), n, _p(y), _p(y_cpu), C.byref(splits))
+    assert rc == 0, rc
+    assert np.isfinite(y).all() and np.abs(y_cpu).max() > 0
+    assert refs.nmse(y, y_cpu) <= 5e-4
+    assert splits.value >= 1
