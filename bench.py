@@ -42,6 +42,14 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_bf16():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f).get("bf16_tflops", 1675.0))
+    return 1675.0
+
+
 class ClockSampler:
     """samples nvidia-smi clocks / throttle reasons while the timed region runs"""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
@@ -212,6 +220,119 @@ def main_reference(args):
 # --------------------------------------------------------------------------------------------------------------
 # the B200 arm
 # --------------------------------------------------------------------------------------------------------------
+SHARED_LEAVES = ("attn_k", "attn_v", "ffn_up")  # read the same vector as the op before them (wq/wk/wv, ffn_gate/ffn_up)
+
+
+def _timeit(torch, fn, reps, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def aux_single_gpu(torch, b200q, workloads, peak_hbm, bf16_peak):
+    """BASELINE configs 1, 3, 4 — not the headline; each entry: us, achieved, unit, frac, peak"""
+    import refs
+    aux = {}
+    # config 1: Q4_0 4096 x 4096, n = 1; 64 distinct weight copies (604 MB > 4 x L2) so every launch streams from HBM
+    try:
+        op = workloads.MatMul("c1", refs.Q4_0, 4096, 4096)
+        ws = [workloads.synth_weights_device(op, seed=900 + i) for i in range(64)]
+        a = torch.rand(4096, device="cuda") * 2 - 1
+        outs = [torch.zeros(4096, device="cuda") for _ in ws]
+        lst = b200q.MatmulList([(w, a, o, False) for w, o in zip(ws, outs)])
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            lst.launch()
+        us_list = _timeit(torch, g.replay, 20) * 1e3 / len(ws)
+        g2 = torch.cuda.CUDAGraph()
+        b200q.mul_mat(ws[0], a.view(1, -1), out=outs[0].view(1, -1))
+        torch.cuda.synchronize()
+        with torch.cuda.graph(g2):
+            for w, o in zip(ws, outs):
+                b200q.mul_mat(w, a.view(1, -1), out=o.view(1, -1))
+        us_chain = _timeit(torch, g2.replay, 20) * 1e3 / len(ws)
+        bytes_ = op.algo_bytes(1)
+        aux["config1_q4_0_4096x4096_n1"] = {
+            "us": us_list, "achieved": bytes_ / us_list / 1e3, "unit": "GB/s", "frac": bytes_ / us_list / 1e3 / peak_hbm, "peak": peak_hbm,
+            "how": "64 distinct weight copies (604 MB, > 4 x L2) as one persistent list launch, us per matmul",
+            "per_launch_chain_us": us_chain, "per_launch_chain_frac": bytes_ / us_chain / 1e3 / peak_hbm}
+        del ws, outs, lst, g, g2
+    except Exception as e:
+        aux["config1_q4_0_4096x4096_n1"] = {"error": repr(e)}
+    # config 3: Q8_0 pp512 over the matmul set of 4 layers of Llama-3-8B shapes (928 MB of weights > L2)
+    try:
+        n = 512
+        ops = workloads.llama3_8b("q8_0", layers=4, with_output=False)
+        ws = [workloads.synth_weights_device(o, seed=950 + i) for i, o in enumerate(ops)]
+        acts = {k: torch.rand(n, k, device="cuda") * 2 - 1 for k in {o.k for o in ops}}
+        outs = {m: torch.empty(n, m, device="cuda") for m in {o.m for o in ops}}
+
+        def run():
+            for o, w in zip(ops, ws):
+                b200q.mul_mat(w, acts[o.k], out=outs[o.m])
+        run()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            run()
+        ms = _timeit(torch, g.replay, 10)
+        flops = sum(o.flops(n) for o in ops)
+        tf = flops / ms / 1e9
+        per = {}
+        for o, w in zip(ops[:7], ws[:7]):
+            us = _timeit(torch, lambda: b200q.mul_mat(w, acts[o.k], out=outs[o.m]), 10) * 1e3
+            per[f"{o.k}->{o.m}"] = {"us": us, "tflops": o.flops(n) / us / 1e6, "frac_bf16": o.flops(n) / us / 1e6 / bf16_peak}
+        aux["config3_q8_0_pp512"] = {
+            "us": ms * 1e3, "achieved": tf, "unit": "TFLOP/s", "frac": tf / bf16_peak, "peak": bf16_peak,
+            "frac_of_nominal_int8_4500": tf / 4500.0, "tok_s_matmul_only_32_layers": n / (ms * 8) * 1e3,
+            "how": "28 matmuls (4 layers, 928 MB of Q8_0 weights) x 512 tokens, CUDA-graph replay; tcgen05 kind::f16 on bf16-dequantized tiles",
+            "per_shape_L2_warm": per}
+        del ws, acts, outs, g
+    except Exception as e:
+        aux["config3_q8_0_pp512"] = {"error": repr(e)}
+    # config 4: gpt-oss-20B-shaped MoE, 32 experts [2880 -> 2880] MXFP4, top-4, T = 1 and T = 512
+    try:
+        import numpy as np
+        E, M, K, USED = 32, 2880, 2880, 4
+        base = refs.random_blocks(refs.MXFP4, 256, K, seed=5)
+        host = np.tile(base, ((E * M + 255) // 256, 1))[:E * M]
+        nrep = 5  # 5 expert tensors of 141 MB rotate (705 MB > 4 x L2)
+        wsx = [b200q.upload(refs.MXFP4, (E, M, K), host) for _ in range(nrep)]
+        rs = b200q.row_size(refs.MXFP4, K)
+        for T in (1, 512):
+            gen = torch.Generator(device="cpu")
+            gen.manual_seed(T)
+            ids = torch.stack([torch.randperm(E, generator=gen)[:USED] for _ in range(T)]).to(torch.int32).cuda()
+            b = torch.rand(T, 1, K, device="cuda") * 2 - 1
+            out = torch.empty(T, USED, M, device="cuda")
+            b200q.mul_mat_id(wsx[0], b, ids, out=out)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                for w in wsx:
+                    b200q.mul_mat_id(w, b, ids, out=out)
+            us = _timeit(torch, g.replay, 10 if T == 1 else 4) * 1e3 / nrep
+            if T == 1:
+                by = USED * M * rs + K * 4 + USED * M * 4
+                aux["config4_mxfp4_moe_T1"] = {"us": us, "achieved": by / us / 1e3, "unit": "GB/s", "frac": by / us / 1e3 / peak_hbm,
+                                               "peak": peak_hbm, "how": "4 of 32 experts [2880->2880], 5 rotating expert tensors"}
+            else:
+                fl = 2.0 * M * K * T * USED
+                aux["config4_mxfp4_moe_T512"] = {"us": us, "achieved": fl / us / 1e6, "unit": "TFLOP/s", "frac": fl / us / 1e6 / bf16_peak,
+                                                 "peak": bf16_peak, "how": "2048 (token, slot) rows over 32 experts, tcgen05 kind::f16"}
+        del wsx
+    except Exception as e:
+        aux["config4_mxfp4_moe"] = {"error": repr(e)}
+    return aux
+
+
 def main_b200(args):
     import ctypes as C
 
@@ -235,73 +356,7 @@ def main_b200(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     L = b200q.lib()
-    ops = workload_ops(args.workload)
-
-    # ---- resident state: weights (row shard of every matrix when world > 1), activations, results ------------
     from b200q import rowsplit
-    shards = []
-    for i, o in enumerate(ops):
-        parts = rowsplit.row_split(o.m, world)
-        row0, nrows = parts[rank]
-        shard = workloads.synth_weights_device(o, seed=1234 + i, rows=nrows, row0=row0)
-        shards.append(rowsplit.RowSplitWeight(o.qtype, o.m, o.k, rank, world, parts, shard))
-    k_off, m_off = [0], [0]
-    for o in ops:
-        k_off.append(k_off[-1] + o.k)
-        m_off.append(m_off[-1] + o.m)
-    g = torch.Generator(device="cuda")
-    g.manual_seed(4321)
-    act_dev = torch.rand(k_off[-1], device="cuda", generator=g) * 2 - 1          # all activation vectors, f32
-    # row split (N > 1): "peer" = the decode kernel stores its rows into every rank's result buffer itself (NVLink peer
-    # stores in the epilogue, one small all-reduce per step as the completion fence); "nccl" = all-gather per matmul
-    split_mode = os.environ.get("B200Q_ROWSPLIT", "peer") if world > 1 else "single"
-    peer_dst = None
-    if split_mode == "peer":
-        peer_dst = rowsplit.PeerDst(m_off[-1], rank, world)
-        out_dev = peer_dst.tensor
-        out_dev.zero_()
-    else:
-        out_dev = torch.zeros(m_off[-1], device="cuda")                          # all (gathered) results, f32
-    act_host = act_dev.cpu().pin_memory()
-    out_host = torch.empty(m_off[-1], dtype=torch.float32).pin_memory()
-
-    # launches of one pass: matrices of one type that multiply the same activation vector in the model (wq/wk/wv of a
-    # layer, ffn_gate/ffn_up) go out as ONE grouped launch (b200q_mul_mat_group) and read the same vector here too
-    SHARED = ({"attn_q", "attn_k", "attn_v"}, {"ffn_gate", "ffn_up"})
-    launches = []
-    for i, o in enumerate(ops):
-        leaf = o.name.split(".")[-1]
-        prev = launches[-1] if launches else None
-        if (split_mode != "nccl" and prev is not None and len(prev) < 4 and ops[prev[0]].qtype == o.qtype and ops[prev[0]].k == o.k
-                and ops[prev[0]].name.rsplit(".", 1)[0] == o.name.rsplit(".", 1)[0]
-                and any(leaf in grp and ops[prev[0]].name.split(".")[-1] in grp for grp in SHARED)):
-            prev.append(i)
-        else:
-            launches.append([i])
-
-    def run_pass():
-        """one pass over the matmul list; every launch goes to torch's current stream through the C-ABI"""
-        for idx in launches:
-            i = idx[0]
-            a = act_dev[k_off[i]:k_off[i + 1]].view(1, ops[i].k)
-            if world == 1:
-                b200q.mul_mat_group([shards[j].shard for j in idx], a,
-                                    outs=[out_dev[m_off[j]:m_off[j + 1]].view(1, ops[j].m) for j in idx])
-            elif split_mode == "peer":
-                rowsplit.mul_mat_row_split_peer([shards[j] for j in idx], a, peer_dst, [m_off[j] for j in idx])
-            else:
-                # this rank's rows + NCCL all-gather of the slices (rowsplit.py)
-                rowsplit.mul_mat_row_split(shards[i], a, out=out_dev[m_off[i]:m_off[i + 1]].view(1, ops[i].m))
-        if peer_dst is not None:
-            peer_dst.fence()  # every rank's rows have landed in every rank's buffer
-
-    for _ in range(2):
-        run_pass()
-    torch.cuda.synchronize()
-    graph = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(graph):
-        run_pass()
-    torch.cuda.synchronize()
 
     def barrier():
         if dist is not None:
@@ -315,9 +370,90 @@ def main_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    class Pass:
+        """the resident state of one workload: this rank's row shard of every matrix, all activation vectors, results"""
+
+        def __init__(self, name, seed0=1234):
+            self.ops = workload_ops(name)
+            ops = self.ops
+            self.shards = []
+            for i, o in enumerate(ops):
+                parts = rowsplit.row_split(o.m, world)
+                row0, nrows = parts[rank]
+                shard = workloads.synth_weights_device(o, seed=seed0 + i, rows=nrows, row0=row0)
+                self.shards.append(rowsplit.RowSplitWeight(o.qtype, o.m, o.k, rank, world, parts, shard))
+            self.k_off, self.m_off = [0], [0]
+            for o in ops:
+                self.k_off.append(self.k_off[-1] + o.k)
+                self.m_off.append(self.m_off[-1] + o.m)
+            g = torch.Generator(device="cuda")
+            g.manual_seed(4321)
+            self.act_dev = torch.rand(self.k_off[-1], device="cuda", generator=g) * 2 - 1
+            self.algo = sum(o.algo_bytes(1) for o in ops)
+            # results: two buffers that alternate by step parity (row split: a peer may still read step n while step n + 1
+            # is stored into the other one; include/b200q.h, b200q_list_peers)
+            self.peer = None
+            if world > 1:
+                self.peer = [rowsplit.PeerDst(self.m_off[-1], rank, world) for _ in range(2)]
+                self.out = [p.tensor for p in self.peer]
+                self.sync = rowsplit.PeerSync(rank, world)
+            else:
+                self.out = [torch.zeros(self.m_off[-1], device="cuda") for _ in range(2)]
+            for o in self.out:
+                o.zero_()
+
+        def same_vec(self, i):
+            o, ops = self.ops[i], self.ops
+            return i > 0 and o.name.split(".")[-1] in SHARED_LEAVES and ops[i - 1].k == o.k
+
+        def list_ops(self, buf, lo, hi, dep):
+            """b200q_list ops of matmuls [lo, hi): consecutive ops of one group read the same vector; with dep every NEW vector
+            waits for all earlier ops (the model's chain: qkv -> wo -> gate/up -> down -> next layer)"""
+            res, src = [], None
+            for i in range(lo, hi):
+                o = self.ops[i]
+                if not (self.same_vec(i) and src is not None):
+                    src = self.act_dev[self.k_off[i]:self.k_off[i + 1]]
+                sh = self.shards[i]
+                dptr = (self.peer[buf].addr(self.m_off[i] + sh.row0) if self.peer else
+                        self.out[buf][self.m_off[i]:self.m_off[i + 1]])
+                w = sh.shard if sh.nrows > 0 else b200q.QTensor(o.qtype, (0, o.k), self.act_dev)
+                res.append((w, src, dptr, bool(dep and i > lo and not self.same_vec(i))))
+            return res
+
+        def make_list(self, buf, lo=0, hi=None, dep=True):
+            hi = len(self.ops) if hi is None else hi
+            peers = None
+            if self.peer:
+                peers = (rank, world, self.peer[buf].deltas, self.sync.ptrs)
+            return b200q.MatmulList(self.list_ops(buf, lo, hi, dep), peers=peers)
+
+    P = Pass(args.workload)
+    ops = P.ops
+    dep_chain = os.environ.get("B200Q_BENCH_DEP", "1") != "0"
+    lists = [P.make_list(b, dep=dep_chain) for b in range(2)]
+    for l in lists:
+        l.launch()
+    torch.cuda.synchronize()
+    barrier()
+    graphs = []
+    for l in lists:
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            l.launch()
+        graphs.append(g)
+    torch.cuda.synchronize()
+    barrier()
+
     # ---- value: device-resident ---------------------------------------------------------------------------
-    for _ in range(max(3, args.warmup)):
-        graph.replay()
+    step_no = [0]
+
+    def dev_step():
+        graphs[step_no[0] & 1].replay()
+        step_no[0] += 1
+
+    for _ in range(max(4, args.warmup + (args.warmup & 1))):
+        dev_step()
     barrier()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -325,100 +461,121 @@ def main_b200(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
-        graph.replay()
+        dev_step()
     e1.record()
     barrier()
     ms_dev = reduce_max(e0.elapsed_time(e1)) / args.steps
     clocks = sampler.stop() if rank == 0 else None
+    if step_no[0] & 1:
+        dev_step()  # keep the step parity of all ranks even
+    barrier()
+
+    # ---- row-split parity: gathered peer-store results == the un-sharded single-GPU result, bit for bit --------
+    rowsplit_parity = None
+    if world > 1:
+        mism = 0
+        seen = set()
+        if rank == 0:
+            for i, o in enumerate(ops):
+                key = (o.qtype, o.k, o.m)
+                if key in seen:
+                    continue
+                seen.add(key)
+                # the same bytes every rank generated for its shard, assembled into the whole matrix on this GPU
+                parts = P.shards[i].parts
+                pieces = [workloads.synth_weights_device(o, seed=1234 + i, rows=nr, row0=r0) for (r0, nr) in parts if nr > 0]
+                rs = b200q.row_size(o.qtype, o.k)
+                full = torch.zeros(o.m * rs + 64, dtype=torch.uint8, device="cuda")
+                pos = 0
+                for pc in pieces:
+                    nb = pc.m * rs
+                    full[pos:pos + nb] = pc.data[:nb]
+                    pos += nb
+                dst = torch.zeros(o.m, device="cuda")
+                src = P.act_dev[P.k_off[i]:P.k_off[i + 1]]
+                if P.same_vec(i):
+                    src = P.act_dev[P.k_off[i - 1]:P.k_off[i]] if not P.same_vec(i - 1) else P.act_dev[P.k_off[i - 2]:P.k_off[i - 1]]
+                one = b200q.MatmulList([(b200q.QTensor(o.qtype, (o.m, o.k), full), src, dst, False)])
+                one.launch()
+                torch.cuda.synchronize()
+                for b in range(2):
+                    got = P.out[b][P.m_off[i]:P.m_off[i + 1]]
+                    mism += int((got.view(torch.int32) != dst.view(torch.int32)).sum().item())
+                del full, pieces, one
+        rowsplit_parity = "bit-exact" if mism == 0 else f"{mism} mismatches"
+        barrier()
 
     # ---- e2e: host buffers through the C-ABI, copies inside the timed region --------------------------------
     stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    act_host = P.act_dev.cpu().pin_memory()
+    n_out = P.m_off[-1]
+    # every rank brings in all activations (they are replicated); the results leave from rank 0's buffer only when the
+    # job is a row split (every rank holds all rows after the kernel; one copy of them is the job's result)
+    out_host = torch.empty(n_out, dtype=torch.float32).pin_memory()
     h2d = act_host.numel() * 4
-    d2h = out_host.numel() * 4
+    d2h = n_out * 4
+    n_chunks = int(os.environ.get("B200Q_BENCH_E2E_CHUNKS", "8"))
+    layer_starts = [i for i, o in enumerate(ops) if o.name.endswith("attn_q")] + [len(ops)]
+    per = max(1, (len(layer_starts) - 1 + n_chunks - 1) // n_chunks)
+    cuts = layer_starts[:-1:per] + [len(ops)]
+    if cuts[-2] != len(ops) - 1 and ops[-1].name == "output":
+        cuts = cuts[:-1] + [len(ops) - 1, len(ops)]  # the head is its own chunk
+    chunk_lists = [[P.make_list(b, lo, hi, dep=dep_chain) for lo, hi in zip(cuts[:-1], cuts[1:])] for b in range(2)]
+    s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
 
-    def e2e_step_serial():
-        rc = L.b200q_memcpy(C.c_void_p(act_dev.data_ptr()), C.c_void_p(act_host.data_ptr()), C.c_size_t(h2d), 1, stream)
+    def copy(dst_t, src_t, lo, hi, kind, st):
+        rc = L.b200q_memcpy(C.c_void_p(dst_t.data_ptr() + 4 * lo), C.c_void_p(src_t.data_ptr() + 4 * lo),
+                            C.c_size_t(4 * (hi - lo)), kind, C.c_void_p(st.cuda_stream))
         assert rc == 0
-        graph.replay()
-        rc = L.b200q_memcpy(C.c_void_p(out_host.data_ptr()), C.c_void_p(out_dev.data_ptr()), C.c_size_t(d2h), 2, stream)
-        assert rc == 0
-        assert L.b200q_stream_synchronize(stream) == 0
 
-    # single GPU: the same copies and launches as ONE CUDA graph in which the copies ride two copy streams — the
-    # activations of launch chunk c+1 arrive while chunk c computes, the results of chunk c leave while chunk c+1
-    # computes (every step still moves all h2d + d2h bytes inside the timed region)
-    e2e_mode, e2e_graph = "serial", None
-    if world == 1 and os.environ.get("B200Q_BENCH_E2E", "pipelined") == "pipelined":
-        try:
-            n_chunks = int(os.environ.get("B200Q_BENCH_E2E_CHUNKS", "16"))
-            per = (len(launches) + n_chunks - 1) // n_chunks
-            chunks = [launches[i:i + per] for i in range(0, len(launches), per)]
-            s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
-
-            def copy(dst_t, src_t, lo, hi, kind, st):
-                rc = L.b200q_memcpy(C.c_void_p(dst_t.data_ptr() + 4 * lo), C.c_void_p(src_t.data_ptr() + 4 * lo),
-                                    C.c_size_t(4 * (hi - lo)), kind, C.c_void_p(st.cuda_stream))
-                assert rc == 0
-
-            e2e_graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(e2e_graph):
-                main = torch.cuda.current_stream()
-                s_in.wait_stream(main)
-                s_out.wait_stream(main)
-                # activations: the first chunk's slice, then all the rest — only TWO joins into the compute stream (every
-                # join costs the programmatic-launch overlap of the kernel behind it); results leave chunk by chunk
-                n_join = int(os.environ.get("B200Q_BENCH_E2E_JOINS", "2"))
-                first = [j for idx in chunks[0] for j in idx]
-                arrived = {}
-                if n_join <= 2:
-                    copy(act_dev, act_host, k_off[first[0]], k_off[first[-1] + 1], 1, s_in)
-                    arrived[0] = torch.cuda.Event()
-                    arrived[0].record(s_in)
-                    if len(chunks) > 1:
-                        copy(act_dev, act_host, k_off[first[-1] + 1], k_off[-1], 1, s_in)
-                        arrived[1] = torch.cuda.Event()
-                        arrived[1].record(s_in)
-                else:
-                    for c, ch in enumerate(chunks):
-                        ops_c = [j for idx in ch for j in idx]
-                        copy(act_dev, act_host, k_off[ops_c[0]], k_off[ops_c[-1] + 1], 1, s_in)
-                        arrived[c] = torch.cuda.Event()
-                        arrived[c].record(s_in)
-                for c, ch in enumerate(chunks):
-                    ops_c = [j for idx in ch for j in idx]
-                    if c in arrived:
-                        main.wait_event(arrived[c])
-                    for idx in ch:
-                        i = idx[0]
-                        b200q.mul_mat_group([shards[j].shard for j in idx], act_dev[k_off[i]:k_off[i + 1]].view(1, ops[i].k),
-                                            outs=[out_dev[m_off[j]:m_off[j + 1]].view(1, ops[j].m) for j in idx])
+    e2e_graphs = []
+    for b in range(2):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            main = torch.cuda.current_stream()
+            s_in.wait_stream(main)
+            s_out.wait_stream(main)
+            # activations: the first chunk's slice, then all the rest (two joins); results leave chunk by chunk
+            copy(P.act_dev, act_host, P.k_off[cuts[0]], P.k_off[cuts[1]], 1, s_in)
+            ev0 = torch.cuda.Event()
+            ev0.record(s_in)
+            ev1 = None
+            if len(cuts) > 2:
+                copy(P.act_dev, act_host, P.k_off[cuts[1]], P.k_off[-1], 1, s_in)
+                ev1 = torch.cuda.Event()
+                ev1.record(s_in)
+            for c, lst in enumerate(chunk_lists[b]):
+                if c == 0:
+                    main.wait_event(ev0)
+                elif c == 1 and ev1 is not None:
+                    main.wait_event(ev1)
+                lst.launch()
+                if rank == 0:
                     done = torch.cuda.Event()
                     done.record(main)
                     s_out.wait_event(done)
-                    copy(out_host, out_dev, m_off[ops_c[0]], m_off[ops_c[-1] + 1], 2, s_out)
-                main.wait_stream(s_in)
-                main.wait_stream(s_out)
-            # the pipelined graph must move exactly what the serial step moves
-            out_host.zero_()
-            e2e_graph.replay()
-            torch.cuda.synchronize()
-            chk = out_host.clone()
-            e2e_step_serial()
-            assert torch.equal(chk, out_host), "pipelined e2e graph and serial e2e step disagree"
-            e2e_mode = (f"pipelined (one CUDA graph: activations H2D on a copy stream with {len(arrived)} joins, results D2H on a "
-                        f"second copy stream after each of {len(chunks)} chunks of launches)")
-        except Exception as e:  # keep the serial step rather than lose the bench line
-            print(f"[bench] pipelined e2e unavailable ({e!r}); using the serial step", file=sys.stderr)
-            e2e_graph = None
-            torch.cuda.synchronize()
+                    copy(out_host, P.out[b], P.m_off[cuts[c]], P.m_off[cuts[c + 1]], 2, s_out)
+            main.wait_stream(s_in)
+            main.wait_stream(s_out)
+        e2e_graphs.append(g)
+    torch.cuda.synchronize()
+    barrier()
+    e2e_no = [0]
 
     def e2e_step():
-        if e2e_graph is None:
-            return e2e_step_serial()
-        e2e_graph.replay()
+        e2e_graphs[e2e_no[0] & 1].replay()
+        e2e_no[0] += 1
         assert L.b200q_stream_synchronize(stream) == 0
 
-    for _ in range(max(3, args.warmup)):
+    # the pipelined graph must deliver what the resident pass computed
+    out_host.zero_()
+    e2e_step()
+    e2e_step()
+    torch.cuda.synchronize()
+    e2e_ok = True
+    if rank == 0:
+        e2e_ok = bool(torch.equal(out_host, P.out[1].cpu())) and bool(torch.equal(P.out[0], P.out[1]))
+    for _ in range(max(4, args.warmup + (args.warmup & 1))):
         e2e_step()
     barrier()
     t0 = time.perf_counter()
@@ -426,9 +583,43 @@ def main_b200(args):
     for _ in range(args.steps):
         e2e_step()
     e1.record()
+    torch.cuda.synchronize()
+    wall_ms = (time.perf_counter() - t0) * 1e3
     barrier()
-    ms_e2e = reduce_max(max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3 * 0.0)) / args.steps
+    ms_e2e = reduce_max(max(e0.elapsed_time(e1), wall_ms)) / args.steps
     finite = bool(torch.isfinite(out_host).all())
+    if e2e_no[0] & 1:
+        e2e_step()
+    barrier()
+
+    # ---- second leg for row split: the 70B shapes of BASELINE configs[4] (the north star's scaling target) -----
+    leg70 = None
+    if os.environ.get("B200Q_BENCH_70B", "1" if world > 1 else "0") == "1" and args.workload != "llama3-70b-q4_k":
+        try:
+            del lists, graphs, chunk_lists, e2e_graphs
+            P70 = Pass("llama3-70b-q4_k", seed0=5678)
+            l70 = [P70.make_list(b, dep=dep_chain) for b in range(2)]
+            n70 = [0]
+
+            def step70():
+                l70[n70[0] & 1].launch()
+                n70[0] += 1
+            for _ in range(4):
+                step70()
+            barrier()
+            k70 = max(4, min(args.steps, 40)) & ~1
+            e0.record()
+            for _ in range(k70):
+                step70()
+            e1.record()
+            barrier()
+            ms70 = reduce_max(e0.elapsed_time(e1)) / k70
+            leg70 = {"workload": "llama3-70b-q4_k decode GEMV set, n=1 (561 matmuls, 39.4 GB)", "ms_per_step": ms70,
+                     "value": P70.algo / ms70 / 1e6, "unit": UNIT, "steps": k70, "launches_per_step": l70[0].n_launches,
+                     "barrier_points_per_step": l70[0].n_barrier_points, "per_gpu_frac_of_measured_hbm": P70.algo / ms70 / 1e6 / world / measured_peaks()[0]}
+        except Exception as e:
+            leg70 = {"error": repr(e)}
+        barrier()
 
     def leave():
         """all ranks: flush, meet once more, then leave without tearing NCCL down (destroy_process_group can hang behind
@@ -444,20 +635,16 @@ def main_b200(args):
     if rank != 0:
         return leave()
 
-    algo = sum(o.algo_bytes(1) for o in ops)
+    algo = P.algo
     value = algo / (ms_dev * 1e-3) / 1e9
     e2e_value = algo / (ms_e2e * 1e-3) / 1e9
     peak, peak_src = measured_peaks()
-    n_launch = len(launches)
+    bf16_peak = measured_bf16()
+    info = P.make_list(0, dep=dep_chain)
+    n_launch = info.n_launches
     desc = workloads.describe(ops)
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "gemv_traffic.json")
-    if os.path.exists(tpath):
-        with open(tpath) as f:
-            tj = json.load(f)
-            # ncu --set full capture of 8 consecutive launches (one layer): dram bytes / algorithmic bytes, applied to the
-            # step's average launch
-            traffic = tj.get("dram_over_algorithmic", 0) * algo / n_launch or None
+    chain_txt = ("every new activation vector waits for all earlier matmuls (model order: qkv -> wo -> gate/up -> down -> next layer), "
+                 f"{info.n_barrier_points} device-side barrier points per step" if dep_chain else "no dependencies between matmuls (upper bound)")
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -465,53 +652,72 @@ def main_b200(args):
         "config": {"workload": args.workload + " decode GEMV set, n=1, tg (one step = the 225 matmuls of one token)",
                    "n_matmuls": desc["n_matmuls"], "weight_bytes": desc["weight_bytes"], "shapes": desc["shapes"],
                    "l2": "inputs larger than L2 (4.6 GB of distinct weights per step), no flush needed",
-                   "parallelism": "single GPU" if world == 1 else (
-                       f"row-split x{world}, result rows stored to all peers by the kernel (NVLink), one all-reduce fence per step"
-                       if split_mode == "peer" else f"row-split x{world} + NCCL all-gather per matmul"),
+                   "dependencies": chain_txt,
+                   "parallelism": "single GPU, one persistent kernel launch per step (b200q_list)" if world == 1 else (
+                       f"row-split x{world}: one persistent launch per rank and step, result rows stored to all peers by the kernel "
+                       f"(NVLink), consecutive matmul groups are DEPENDENT across GPUs through {info.n_barrier_points} per-group arrival "
+                       "flags (no collective, no host sync)"),
                    "tg_tok_s_matmul_only": 1e3 / ms_dev},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": ms_e2e, "results_finite": finite,
-                "api": f"b200q_memcpy(H2D) + {n_launch} x b200q_mul_mat_group ({len(ops)} matmuls) + b200q_memcpy(D2H) + "
-                       "b200q_stream_synchronize", "mode": e2e_mode},
+                "ms_per_step": ms_e2e, "results_finite": finite, "matches_resident_pass": e2e_ok,
+                "api": f"b200q_memcpy(H2D) + {len(cuts) - 1} x b200q_list_launch ({len(ops)} matmuls) + b200q_memcpy(D2H) + "
+                       "b200q_stream_synchronize",
+                "mode": f"one CUDA graph per step: activations H2D on a copy stream (2 joins), {len(cuts) - 1} list launches, results "
+                        "D2H on a second copy stream after each launch" + ("" if world == 1 else "; every rank copies all activations in, rank 0 copies the results out")},
         "gpu_launches": n_launch * args.steps,
         "roofline": {"bound": "hbm", "achieved": value / world, "peak": peak, "unit": "GB/s",
-                     "frac": value / world / peak, "traffic": traffic, "peak_source": peak_src,
-                     "kernel": f"gemv_kq_kernel<q4_K | q6_K> (all {n_launch} launches of the step; wq/wk/wv and gate/up grouped)",
+                     "frac": value / world / peak, "traffic": None, "peak_source": peak_src,
+                     "traffic_note": "not measured in this run; ncu dram bytes per launch are in profiles/ (see DESIGN.md section 5)",
+                     "kernel": "gemv_list_kernel (one launch = the whole step)",
                      "launches_per_step": n_launch,
-                     "algorithmic_bytes_per_launch_avg": algo / n_launch,
-                     "avg_launch_us": ms_dev * 1e3 / n_launch, "frac_of_nominal_8TBs": value / world / 8000.0},
+                     "algorithmic_bytes_per_launch_avg": algo / world / max(1, n_launch),
+                     "avg_launch_us": ms_dev * 1e3 / max(1, n_launch), "frac_of_nominal_8TBs": value / world / 8000.0},
         "clocks": clocks,
     }
+    if rowsplit_parity is not None:
+        out["rowsplit_parity"] = rowsplit_parity
+    if leg70 is not None:
+        out.setdefault("aux", {})["config5_llama3_70b_rowsplit"] = leg70
     if world == 1:
-        # aux (not the headline): the longest launch of the step alone — the output head, 430 MB > L2, so every launch
-        # streams from HBM — on the n = 1 kernel and, with 8 activation columns, on the MMA tile kernel (gemv_mma.cu)
+        aux = out.setdefault("aux", {})
         try:
-            head = max(range(len(ops)), key=lambda i: ops[i].m * ops[i].k)
-            o, wq = ops[head], shards[head].shard
-            aux = []
-            for n, kern in ((1, "gemv_kq_kernel"), (8, "gemv_mma_kernel")):
-                a = (torch.rand(n, o.k, device="cuda") * 2 - 1)
-                dst = torch.empty(n, o.m, device="cuda")
-                for _ in range(3):
-                    b200q.mul_mat(wq, a, out=dst)
-                torch.cuda.synchronize()
-                e0.record()
-                for _ in range(20):
-                    b200q.mul_mat(wq, a, out=dst)
-                e1.record()
-                torch.cuda.synchronize()
-                us = e0.elapsed_time(e1) * 1e3 / 20
-                gbs = o.algo_bytes(n) / us / 1e3
-                aux.append({"kernel": f"{kern}<{b200q.TYPE_NAMES.get(o.qtype, o.qtype)}>", "shape": f"{o.k}->{o.m}", "n": n, "us": us,
-                            "achieved": gbs, "unit": "GB/s", "frac": gbs / peak})
-            out["aux"] = {"single_launch": aux}
+            # the same step without barrier points (upper bound) and as round 1's chain of grouped launches
+            nd = P.make_list(0, dep=not dep_chain)
+            ms_nd = _timeit(torch, nd.launch, 20)
+            aux["step_variants"] = {("no_dependencies" if dep_chain else "with_dependencies"): {"ms_per_step": ms_nd, "GB/s": algo / ms_nd / 1e6}}
+
+            def chain():
+                i = 0
+                while i < len(ops):
+                    j = i + 1
+                    while j < len(ops) and j - i < 4 and P.same_vec(j) and ops[j].qtype == ops[i].qtype:
+                        j += 1
+                    b200q.mul_mat_group([P.shards[q].shard for q in range(i, j)], P.act_dev[P.k_off[i]:P.k_off[i + 1]].view(1, -1),
+                                        outs=[P.out[0][P.m_off[q]:P.m_off[q + 1]].view(1, -1) for q in range(i, j)])
+                    i = j
+            chain()
+            torch.cuda.synchronize()
+            gc = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gc):
+                chain()
+            ms_c = _timeit(torch, gc.replay, 20)
+            aux["step_variants"]["round1_chain_of_grouped_launches"] = {"ms_per_step": ms_c, "GB/s": algo / ms_c / 1e6}
+        except Exception as e:
+            aux["step_variants"] = {"error": repr(e)}
+        try:
+            aux.update(aux_single_gpu(torch, b200q, workloads, peak, bf16_peak))
         except Exception as e:  # never lose the headline line to the aux leg
-            out["aux"] = {"error": repr(e)}
+            aux["error"] = repr(e)
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = run_cpu_reference(cpu_sample_ops(ops), args.cpu_seconds)
+    if rowsplit_parity not in (None, "bit-exact"):
+        out["error"] = "row-split result differs from the single-GPU result"
     sys.stdout.flush()
     os.dup2(saved_stdout, 1)
     print(json.dumps(out))
+    if rowsplit_parity not in (None, "bit-exact"):
+        sys.stdout.flush()
+        os._exit(3)
     return leave()
 
 

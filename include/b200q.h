@@ -161,6 +161,45 @@ B200Q_API int b200q_ipc_export(void * dev_ptr, void * handle64);          /* dev
 B200Q_API int b200q_ipc_import(const void * handle64, void ** dev_ptr);   /* maps the peer's buffer, enables peer access */
 B200Q_API int b200q_ipc_close(void * dev_ptr);
 
+/* ---- persistent decode list: a whole run of n = 1 matmuls (a decode token's layers) in ONE launch -------------------
+ *      Replaces the per-matmul launch pair of the reference's decode path (quantize_q8_1 + mul_mat_vec_q,
+ *      ggml-cuda/quantize.cu:148-160, mmvq.cu:500-570, called once per MUL_MAT node by ggml_cuda_compute_forward,
+ *      ggml-cuda.cu:2230-2520): the CTAs never exit between matrices, the weight stream continues across matrix
+ *      boundaries, and data dependencies are device-side barrier points instead of kernel boundaries.
+ *      Weights must be immutable while a list exists and rows dense (pitch = b200q_row_size); w and act 16-byte aligned.
+ *      Consecutive ops that read the same `act` share one quantization.  B200Q_LIST_DEP on an op says its `act` is written
+ *      by earlier ops of this list (on this GPU or, in a row split, on its peers): the kernel then waits until EVERY
+ *      earlier op is complete everywhere before it reads the vector.  A dst must not overlap the `act` of an earlier op
+ *      unless a B200Q_LIST_DEP op lies between them.  Results are bit-reproducible and do not depend on how a list is
+ *      composed, launched or sharded (fixed summation order per (type, k)). */
+#define B200Q_LIST_DEP 1u
+typedef struct b200q_list_op {
+    int           type;
+    int64_t       m, k;   /* dst[m] = W[m][k] . act[k];  m may be 0 (a rank without rows of a small matrix) */
+    const void *  w;
+    const float * act;
+    float *       dst;
+    uint32_t      flags;
+} b200q_list_op;
+/* row split: every result row is also stored into the same place of each peer's dst buffer (peer_delta[i] = this
+ * process's mapping of the i-th OTHER rank's dst buffer minus this GPU's own, ascending rank order), and every barrier
+ * point — plus one at the end of every launch — is a cross-GPU one: sync[r] = device pointer to rank r's 256-byte,
+ * zero-initialised sync block (own block at sync[rank], peers' mapped with b200q_ipc_import).  All ranks must create and
+ * launch the same lists in the same order.  A list must not be launched again before every rank has consumed the dst
+ * regions it overwrites (alternate two dst buffers, or fence). */
+typedef struct b200q_list_peers {
+    int             rank, world;
+    const int64_t * peer_delta;  /* [world - 1] */
+    void * const *  sync;        /* [world] */
+} b200q_list_peers;
+typedef struct b200q_list b200q_list;
+B200Q_API int b200q_list_create(const b200q_list_op * ops, int n_ops, const b200q_list_peers * peers /* NULL: one GPU */,
+                                b200q_list ** out);     /* B200Q_ENOTSUP: some op is not served by the list kernel */
+B200Q_API int b200q_list_launch(b200q_list * list, void * stream);   /* asynchronous; capturable in a CUDA graph */
+B200Q_API int b200q_list_destroy(b200q_list * list);
+/* out[4] = kernel launches per b200q_list_launch, barrier points, activation generations, ring slots of the first launch */
+B200Q_API int b200q_list_info(const b200q_list * list, int * out);
+
 /* ---- MUL_MAT_ID (MoE) ------------------------------------------------------------------------ */
 /* dst[t][s][:] = W[ids[t][s]] . b[t][s or 0][:]     (ggml_mul_mat_id, ggml.c:3056-3080) */
 typedef struct b200q_mul_mat_id_args {

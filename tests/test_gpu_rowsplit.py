@@ -62,6 +62,42 @@ def _worker(rank, world, port, q):
                 dst.fence()
                 torch.cuda.synchronize()
                 ok.append(bool(torch.equal(dst.tensor[32:32 + m].view(1, m), single)))
+        # the persistent list across GPUs: a dependency chain x -> W0 -> W1 -> W2 whose links are row-split; every rank's
+        # kernel stores its rows into all peers' buffers and the next link waits on the per-group arrival flags.  Must equal
+        # the same chain on one GPU bit for bit, on every launch (two result buffers alternate, include/b200q.h).
+        from b200q.rowsplit import PeerDst, PeerSync
+        depth, dim = 6, 2048
+        t = refs.Q4_K
+        wl = [refs.make_weights(t, dim, dim, seed=70 + i) for i in range(depth)]
+        x = torch.from_numpy(refs.uniform_weights(1, dim, seed=71)).cuda().view(-1)
+        full = [b200q.upload(t, (dim, dim), w) for w in wl]
+        want = []
+        cur = x
+        for i in range(depth):
+            d = torch.zeros(dim, device="cuda")
+            one = b200q.MatmulList([(full[i], cur, d, False)])
+            one.launch()
+            torch.cuda.synchronize()
+            want.append(d)
+            cur = d
+        sync = PeerSync(rank, world)
+        bufs = [PeerDst(depth * dim, rank, world) for _ in range(2)]
+        shards = [upload_row_split(t, (dim, dim), w, rank, world) for w in wl]
+        lists = []
+        for b in range(2):
+            lo = []
+            for i in range(depth):
+                src = x if i == 0 else bufs[b].tensor[(i - 1) * dim:i * dim]
+                lo.append((shards[i].shard, src, bufs[b].addr(i * dim + shards[i].row0), i > 0))
+            lists.append(b200q.MatmulList(lo, peers=(rank, world, bufs[b].deltas, sync.ptrs)))
+        for it in range(20):
+            b = it & 1
+            bufs[b].tensor.fill_(float(it))
+            torch.cuda.synchronize()
+            dist.barrier()
+            lists[b].launch()
+            torch.cuda.synchronize()
+            ok.append(all(bool(torch.equal(bufs[b].tensor[i * dim:(i + 1) * dim], want[i])) for i in range(depth)))
         q.put((rank, ok))
     finally:
         dist.destroy_process_group()

@@ -103,3 +103,117 @@ def test_kernel_choice_by_columns():
     assert _workspace(refs.Q4_K, m, k, 12, batch=3) > 0          # batch dims: no multi-pass GEMV
     assert _workspace(refs.Q4_K, m, k, 4, flags=b200q.FLAG_FORCE_MMQ) > 0
     assert _workspace(refs.Q4_K, m, k, 512, flags=b200q.FLAG_FORCE_GEMV) == 0
+
+
+# ---- the persistent decode list (csrc/api.cu list_plan / gemv_list.cu) ------------------------------------------------
+LIST_PAYLOAD, LIST_MIN_SLOTS = 9216, 16  # csrc/gemv_list.cuh (8 warps)
+
+
+def plan_list(ops, world=1, sms=SMS, max_smem=MAX_SMEM):
+    """ops: [(type, m, k, dep, same_act_as_previous)] -> (per-op dicts, per-launch dicts)"""
+    import b200q
+    fn = b200q.lib().b200q_debug_plan_list
+    fn.restype = C.c_int
+    n = len(ops)
+    ty = (C.c_int * n)(*[o[0] for o in ops])
+    mm = (C.c_int64 * n)(*[o[1] for o in ops])
+    kk = (C.c_int64 * n)(*[o[2] for o in ops])
+    dep = (C.c_int * n)(*[int(o[3]) for o in ops])
+    same = (C.c_int * n)(*[int(o[4]) for o in ops])
+    out = (C.c_int * (8 * n))()
+    seg = (C.c_int * (8 * 64))()
+    rc = fn(ty, mm, kk, dep, same, n, world, sms, max_smem, out, seg, 64)
+    assert rc >= 1, (rc, b200q.lib().b200q_last_error())
+    on = ["launch", "units", "rps", "nch", "csb", "gen", "nsb", "rot"]
+    sn = ["n_ops", "n_gens", "total_units", "n_bp", "nslots", "smem", "grid", "act_stride"]
+    return ([dict(zip(on, out[8 * i:8 * i + 8])) for i in range(n)], [dict(zip(sn, seg[8 * i:8 * i + 8])) for i in range(rc)])
+
+
+def _model_ops(workload):
+    from b200q import workloads
+    ops = []
+    for o in workload:
+        leaf = o.name.split(".")[-1]
+        same = leaf in ("attn_k", "attn_v", "ffn_up")
+        ops.append((o.qtype, o.m, o.k, not same, same))
+    return ops
+
+
+def test_list_plan_llama3_8b_is_one_launch():
+    from b200q import workloads
+    ops = _model_ops(workloads.llama3_8b("q4_k_m"))
+    per_op, segs = plan_list(ops)
+    assert len(segs) == 1, segs
+    s = segs[0]
+    assert s["n_ops"] == 225 and s["n_gens"] == 129 and s["n_bp"] == 128  # the first generation follows a kernel boundary
+    assert s["nslots"] >= LIST_MIN_SLOTS and s["smem"] <= MAX_SMEM and s["grid"] == SMS
+    units = 0
+    for (t, m, k, _, _), p in zip(ops, per_op):
+        rb = refs.row_size(t, k)
+        assert p["units"] == (m + p["rps"] - 1) // p["rps"] and 0 <= p["rot"] < s["grid"]
+        if p["nch"] == 1:
+            assert p["rps"] * rb <= LIST_PAYLOAD and p["csb"] == p["nsb"]
+        else:
+            assert p["rps"] == 1 and p["csb"] * refs.BLCK[t][1] <= LIST_PAYLOAD and p["csb"] * p["nch"] >= p["nsb"] > p["csb"] * (p["nch"] - 1)
+        units += (m + p["rps"] - 1) // p["rps"]
+    assert units == s["total_units"]
+
+
+def test_list_plan_llama3_70b_splits_and_chunks():
+    from b200q import workloads
+    ops = _model_ops(workloads.llama3_70b("q4_k"))
+    per_op, segs = plan_list(ops, world=8)
+    assert 1 <= len(segs) <= 4
+    assert sum(s["n_ops"] for s in segs) == len(ops)
+    for s in segs:
+        assert s["nslots"] >= LIST_MIN_SLOTS and s["smem"] <= MAX_SMEM and s["n_bp"] >= 1  # row split: a final barrier point per launch
+    down = [p for (t, m, k, _, _), p in zip(ops, per_op) if k == 28672]
+    assert down and all(p["nch"] == 2 and p["rps"] == 1 for p in down)
+
+
+@pytest.mark.parametrize("t", [refs.Q4_K, refs.Q6_K, refs.Q8_0, refs.Q4_0, refs.Q4_1, refs.Q5_0, refs.Q5_1, refs.MXFP4],
+                         ids=lambda t: refs.NAMES[t])
+def test_list_geometry_depends_on_type_and_k_only(t):
+    """the same (type, k) gets the same stage geometry whatever the list looks like (results must not depend on it)"""
+    unit = 256 if t in (refs.Q4_K, refs.Q6_K) else 32
+    for k in (unit, 4 * unit, 2880 // 32 * 32 if unit == 32 else 1024, 4096, 14336 // unit * unit, 28672):
+        if k % unit:
+            continue
+        a, _ = plan_list([(t, 77, k, False, False)])
+        b, _ = plan_list([(refs.Q4_K, 4096, 4096, False, False), (t, 5000, k, True, False), (refs.Q6_K, 128, 14336, False, False)])
+        for f in ("rps", "nch", "csb", "nsb"):
+            assert a[0][f] == b[1][f], (k, f)
+
+
+def test_list_walk_covers_every_unit_exactly_once():
+    """emulation of gemv_list.cu's per-warp walk (next_op / advance) over the planned table: every unit of every op is
+    taken by exactly one (CTA, warp), the CTAs' loads differ by at most one unit over the whole launch"""
+    import numpy as np
+    from b200q import workloads
+    ops = _model_ops(workloads.llama3_8b("q4_k_m", layers=3)) + [(refs.Q4_0, 5, 1024, False, False), (refs.Q8_0, 0, 1024, False, False),
+                                                                 (refs.Q6_K, 1000, 2048, True, False)]
+    per_op, segs = plan_list(ops)
+    assert len(segs) == 1
+    G, NW = segs[0]["grid"], 8
+    seen = [np.zeros(p["units"], dtype=np.int32) for p in per_op]
+    load = np.zeros(G, dtype=np.int64)
+    for c in range(G):
+        for w in range(NW):
+            woff = 0
+            for j, p in enumerate(per_op):
+                base, rem = p["units"] // G, p["units"] % G
+                cp = c + p["rot"]
+                cp -= G if cp >= G else 0
+                ncta = base + (1 if cp < rem else 0)
+                first = (w - woff) & (NW - 1)
+                woff = (woff + ncta) & (NW - 1)
+                if ncta > first:
+                    start = cp * base + min(cp, rem) + first
+                    left = (ncta - first + NW - 1) // NW
+                    for i in range(left):
+                        seen[j][start + i * NW] += 1
+                    load[c] += left * p["nch"]
+    for j, sarr in enumerate(seen):
+        assert (sarr == 1).all(), j
+    nch_max = max(p["nch"] for p in per_op)
+    assert load.max() - load.min() <= 2 * nch_max + 1, (load.min(), load.max())  # units are balanced to 1; a chunked unit is nch stages
