@@ -220,37 +220,34 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
     };
 
     // ---- barrier point: everything before it is complete on every CTA (and every GPU) -------------------------------
+    // All warps of the CTA meet (bar.sync orders their result stores before warp 0's release at CTA scope; the release is
+    // cumulative), ONE thread counts the CTA in and polls — 148 pollers on the counter's L2 line instead of 1184, which sat
+    // in front of the arrivals (4.4 -> 2.4 us per barrier point) — and a second CTA barrier lets everybody continue behind
+    // its acquire.
     auto barrier_point = [&](int bp) {
-        if (p.n_peers) __threadfence_system(); else __threadfence();  // this lane's result stores, before the count
-        __syncwarp();
-        const unsigned want = (unsigned) bp * (unsigned) G;
-        if (lane == 0) {
-            unsigned old;
-            asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(sb + OFF_CNT + 4u * (bp & 1)) : "memory");
-            if (old == LIST_WARPS - 1) {  // last warp of this CTA
-                asm volatile("st.shared.u32 [%0], %1;" ::"r"(sb + OFF_CNT + 4u * (bp & 1)), "r"(0) : "memory");
-                __threadfence();
+        named_bar_sync(2, NTHREADS);
+        if (warp == 0) {
+            if (lane == 0) {
+                const unsigned want = (unsigned) bp * (unsigned) G;
+                if (p.n_peers) __threadfence_system();  // peer stores of this CTA's warps, before the count
                 const unsigned prev = atom_add_release_gpu(p.sync + LIST_SYNC_PROGRESS, 1u);
-                if (p.world > 1 && prev + 1u == want) {  // this GPU is complete up to bp: tell every rank
-                    __threadfence_system();
+                if (p.world > 1) {
                     const unsigned val = base + (unsigned) bp;
-                    st_release_sys(p.sync + LIST_SYNC_RANK0 + p.rank, val);
-                    for (int r = 0; r < p.n_peers; ++r) st_release_sys(p.peer_sync[r] + LIST_SYNC_RANK0 + p.rank, val);
+                    if (prev + 1u == want) {  // this GPU is complete up to bp: tell every rank
+                        __threadfence_system();
+                        st_release_sys(p.sync + LIST_SYNC_RANK0 + p.rank, val);
+                        for (int r = 0; r < p.n_peers; ++r) st_release_sys(p.peer_sync[r] + LIST_SYNC_RANK0 + p.rank, val);
+                    }
+                    for (int r = 0; r < p.world; ++r) {
+                        while ((int) (ld_acquire_sys(p.sync + LIST_SYNC_RANK0 + r) - val) < 0) {}
+                    }
+                } else {
+                    while ((int) (ld_acquire_gpu(p.sync + LIST_SYNC_PROGRESS) - want) < 0) {}
                 }
             }
-            if (p.world > 1) {
-                const unsigned val = base + (unsigned) bp;
-                for (int r = 0; r < p.world; ++r) {
-                    while ((int) (ld_acquire_sys(p.sync + LIST_SYNC_RANK0 + r) - val) < 0) {}
-                }
-            } else {
-                while ((int) (ld_acquire_gpu(p.sync + LIST_SYNC_PROGRESS) - want) < 0) {}
-            }
+            __syncwarp();
         }
-        __syncwarp();
-        // every lane takes its own acquire (the activations are read with plain L2 loads right after)
-        if (p.world > 1) (void) ld_acquire_sys(p.sync + LIST_SYNC_RANK0 + p.rank);
-        else (void) ld_acquire_gpu(p.sync + LIST_SYNC_PROGRESS);
+        named_bar_sync(3, NTHREADS);
     };
 
     // ---- generation switch: wait if needed, quantize this warp's share of the vector into image g & 1 ---------------
@@ -372,11 +369,27 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
                         }
                     }
                 }
-                if (last_ch) {
-                    finish_row(a0, rr0);
-                    if (pair) finish_row(a1, rr1);
-                } else {
+                if (!last_ch) {
                     acc = a0;
+                } else if (!pair) {
+                    finish_row(a0, rr0);
+                } else if (lpr == 1) {
+                    finish_row(a0, rr0);
+                    finish_row(a1, rr1);
+                } else {
+                    // two rows at once: the upper half of a row's lanes takes over row 1, the lower half row 0 (one exchange),
+                    // then both reduce side by side — log2(lpr) shuffles for the pair instead of 2 log2(lpr)
+                    const int   h    = lpr >> 1;
+                    const bool  up   = (sub & h) != 0;
+                    const float keep = up ? a1 : a0, send = up ? a0 : a1;
+                    float       v    = keep + __shfl_xor_sync(0xffffffffu, send, h);
+                    for (int o = h >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                    const int rr = up ? rr1 : rr0;
+                    if ((sub & (h - 1)) == 0 && rr < nr) {
+                        float * d = r.dst + r0 + rr;
+                        *d = v;
+                        for (int q = 0; q < p.n_peers; ++q) *(float *) ((char *) d + p.peer_delta[q]) = v;  // NVLink peer stores
+                    }
                 }
             }
         } else {
