@@ -97,7 +97,7 @@ __device__ __forceinline__ OpRec op_load(uint32_t tab, int op) {
 }
 
 // a warp's position in its own stage sequence: chunk `ch` of unit `unit` of op `op`; `left` units of this op remain for
-// this warp, `woff` = units this CTA has taken so far, mod 8 (the warp that gets the CTA's next unit)
+// this warp, `woff` = units this CTA has taken so far, mod LIST_WARPS (the warp that gets the CTA's next unit)
 struct Walk {
     int op, left, unit, ch, woff;
 };
@@ -177,8 +177,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
             int        cp = (int) blockIdx.x + q.w;
             if (cp >= G) cp -= G;
             const int ncta  = q.y + (cp < q.z ? 1 : 0);
-            const int first = (warp - w.woff) & (LIST_WARPS - 1);
-            w.woff          = (w.woff + ncta) & (LIST_WARPS - 1);
+            const int first = (warp - w.woff + LIST_WARPS) % LIST_WARPS;
+            w.woff          = (w.woff + ncta) % LIST_WARPS;
             if (ncta > first) {
                 w.unit = cp * q.y + min(cp, q.z) + first;
                 w.left = (ncta - first + LIST_WARPS - 1) / LIST_WARPS;
