@@ -1000,7 +1000,8 @@ int list_plan(const b200q_list_op * ops, int n_ops, int world, int sms, int max_
         for (auto & g : cur.gens) if (g.wait) g.bp = (uint16_t) ++nbp;
         p.n_bp   = nbp + p.final_bp;
         cur.smem = p.off_ring + p.nslots * LIST_SLOT_BYTES;
-        cur.grid = (int) std::max<long long>(1, std::min<long long>(units, sms));
+        // row split: every GPU counts the same number of CTAs in at a barrier point, whatever its share of the rows is
+        cur.grid = world > 1 ? sms : (int) std::max<long long>(1, std::min<long long>(units, sms));
         cur.total_units = units;
         // every op's units in `grid` contiguous ranges; the surplus ranges rotate on from op to op (gemv_list.cuh)
         long long rot = 0;
@@ -1153,7 +1154,7 @@ int b200q_list_launch(b200q_list * L, void * stream) {
     if (int rc = ensure_smem_attr((const void *) fn, di.max_smem)) return rc;
     static const bool debug = getenv("B200Q_DEBUG") != nullptr;
     for (auto & sg : L->segs) {
-        if (sg.total_units == 0) continue;
+        if (sg.total_units == 0 && sg.p.world == 1) continue;
         if (debug) {
             fprintf(stderr, "[b200q] gemv_list ops=%d gens=%d units=%d bp=%d slots=%d smem=%d grid=%d world=%d\n", sg.p.n_ops, sg.p.n_gens,
                     (int) sg.total_units, sg.p.n_bp, sg.p.nslots, sg.smem, sg.grid, sg.p.world);
@@ -1185,7 +1186,7 @@ int b200q_list_destroy(b200q_list * L) {
 int b200q_list_info(const b200q_list * L, int * out) {
     if (!L || !out) return fail(B200Q_EINVAL, "list_info: null argument");
     int launches = 0;
-    for (auto & sg : L->segs) launches += sg.total_units > 0;
+    for (auto & sg : L->segs) launches += sg.total_units > 0 || sg.p.world > 1;
     out[0] = launches; out[1] = L->n_bp; out[2] = L->n_gens; out[3] = L->segs.empty() ? 0 : L->segs[0].p.nslots;
     return 0;
 }

@@ -228,20 +228,20 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
         named_bar_sync(2, NTHREADS);
         if (warp == 0) {
             if (lane == 0) {
-                const unsigned want = (unsigned) bp * (unsigned) G;
-                if (p.n_peers) __threadfence_system();  // peer stores of this CTA's warps, before the count
-                const unsigned prev = atom_add_release_gpu(p.sync + LIST_SYNC_PROGRESS, 1u);
                 if (p.world > 1) {
-                    const unsigned val = base + (unsigned) bp;
-                    if (prev + 1u == want) {  // this GPU is complete up to bp: tell every rank
-                        __threadfence_system();
-                        st_release_sys(p.sync + LIST_SYNC_RANK0 + p.rank, val);
-                        for (int r = 0; r < p.n_peers; ++r) st_release_sys(p.peer_sync[r] + LIST_SYNC_RANK0 + p.rank, val);
+                    // row split: this CTA's peer stores must have landed before it is counted in (one system-scope fence per
+                    // CTA), then it counts itself in ON EVERY GPU — local and remote reductions, no hop through a "last CTA" —
+                    // and polls its own GPU's counter: all CTAs of all GPUs are in when it reads base + bp * G * world
+                    asm volatile("fence.acq_rel.sys;" ::: "memory");
+                    asm volatile("red.relaxed.sys.global.add.u32 [%0], 1;" ::"l"(p.sync + LIST_SYNC_ARRIVE) : "memory");
+                    for (int r = 0; r < p.n_peers; ++r) {
+                        asm volatile("red.relaxed.sys.global.add.u32 [%0], 1;" ::"l"(p.peer_sync[r] + LIST_SYNC_ARRIVE) : "memory");
                     }
-                    for (int r = 0; r < p.world; ++r) {
-                        while ((int) (ld_acquire_sys(p.sync + LIST_SYNC_RANK0 + r) - val) < 0) {}
-                    }
+                    const unsigned want = base + (unsigned) bp * (unsigned) G * (unsigned) p.world;
+                    while ((int) (ld_acquire_sys(p.sync + LIST_SYNC_ARRIVE) - want) < 0) {}
                 } else {
+                    const unsigned want = (unsigned) bp * (unsigned) G;
+                    atom_add_release_gpu(p.sync + LIST_SYNC_PROGRESS, 1u);
                     while ((int) (ld_acquire_gpu(p.sync + LIST_SYNC_PROGRESS) - want) < 0) {}
                 }
             }
@@ -433,7 +433,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
         if (prev == (unsigned) G - 1u) {
             p.sync[LIST_SYNC_PROGRESS] = 0u;
             p.sync[LIST_SYNC_EXIT]     = 0u;
-            if (p.world > 1) p.sync[LIST_SYNC_BASE] = base + (unsigned) p.n_bp;
+            if (p.world > 1) p.sync[LIST_SYNC_BASE] = base + (unsigned) p.n_bp * (unsigned) G * (unsigned) p.world;
             __threadfence();
         }
     }

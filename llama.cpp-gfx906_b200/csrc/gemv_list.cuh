@@ -51,7 +51,9 @@ struct ListGen {         // 16 bytes: one activation vector, quantized once per 
 static_assert(sizeof(ListGen) == 16, "ListGen is 16 bytes");
 
 // words of the 256-byte sync block (device memory, zero-initialised once)
-enum : int { LIST_SYNC_PROGRESS = 0, LIST_SYNC_EXIT = 1, LIST_SYNC_BASE = 2, LIST_SYNC_RANK0 = 8 /* .. + world */ };
+// PROGRESS / EXIT: CTAs of this launch that passed the current barrier point / left (re-armed by the last one);
+// ARRIVE: row split — CTAs of ALL GPUs counted in here, monotonic over launches; BASE: its value when this launch started
+enum : int { LIST_SYNC_PROGRESS = 0, LIST_SYNC_EXIT = 1, LIST_SYNC_BASE = 2, LIST_SYNC_ARRIVE = 4 };
 
 struct ListParams {
     const ListOp *  ops;    // [n_ops]

@@ -68,7 +68,11 @@ def _driver():
     global _pd
     if _pd is None:
         d = _need_ref()
-        L = C.CDLL(os.path.join(d, "plugin_driver.so"))
+        # a host that uses ggml links ggml-base into its global scope; the plugin resolves ggml_backend_buffer_init & co. from
+        # there (it is not linked against any ggml library itself), so do the same in this Python process
+        for lib in ("libggml-base.so", "libggml-cpu.so", "libggml.so"):
+            C.CDLL(os.path.join(d, lib), mode=C.RTLD_GLOBAL)
+        L = C.CDLL(os.path.join(d, "plugin_driver.so"), mode=C.RTLD_GLOBAL)
         L.pd_load.argtypes = [C.c_char_p]
         L.pd_device_name.restype = C.c_char_p
         L.pd_proc_address.restype = C.c_void_p
