@@ -134,6 +134,20 @@ B200Q_API size_t b200q_mul_mat_workspace(const b200q_mul_mat_args * a);
 B200Q_API int    b200q_mul_mat(const b200q_mul_mat_args * a, const void * w, const float * act, float * dst,
                                void * workspace, size_t workspace_bytes, void * stream);
 
+/* ---- MUL_MAT that allocates nothing.  No counterpart in the reference: added for
+ *      callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ *      Same arguments, kernels and results as b200q_mul_mat, but the tensor-core kernel's scratch (the packed bf16
+ *      activation image, b200q_mul_mat_workspace bytes) is a file-scope device array inside the library of
+ *      B200Q_STATIC_WORKSPACE_BYTES (16 MiB; every GPU that loads libb200q.so holds it until exit).  Shapes that need more
+ *      fail with B200Q_EWORKSPACE and a message that says so (512 columns fit up to k = 16384; decode shapes need none).
+ *      The call makes no cudaMalloc / cudaFree / allocating library call.  All calls share the one array, which keeps the
+ *      last call's contents (nothing in it has to start at zero: the pack kernel rewrites every byte the matmul reads):
+ *      calls that overlap on the GPU — different streams, or several host threads — race on it; serialise them on one
+ *      stream or use b200q_mul_mat with separate workspaces. */
+#define B200Q_STATIC_WORKSPACE_BYTES (16u << 20)
+B200Q_API int b200q_mul_mat_static(const b200q_mul_mat_args * a, const void * w, const float * act, float * dst,
+                                   void * stream);
+
 /* ---- grouped decode MUL_MAT: up to 4 weight matrices [m_g][k] of one type that multiply the SAME activation vector
  *      (n = 1: wq/wk/wv, ffn_gate/ffn_up) in one launch.  Equivalent to n_mats calls of b200q_mul_mat (bit-identical
  *      results); replaces the reference's fused gate/up GEMV (ggml-cuda mmvq.cu, fusion args of mul_mat_vec_q).

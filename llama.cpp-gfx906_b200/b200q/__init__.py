@@ -35,7 +35,7 @@ EXPORTS = [
     "b200q_ipc_import", "b200q_ipc_close", "b200q_mul_mat_id_workspace", "b200q_mul_mat_id",
     "b200q_mul_mat_host", "b200q_set_device", "b200q_malloc", "b200q_free", "b200q_memset", "b200q_memcpy",
     "b200q_stream_create", "b200q_stream_destroy", "b200q_stream_synchronize", "b200q_host_alloc", "b200q_host_free",
-    "b200q_list_create", "b200q_list_launch", "b200q_list_destroy", "b200q_list_info",
+    "b200q_list_create", "b200q_list_launch", "b200q_list_destroy", "b200q_list_info", "b200q_mul_mat_static",
 ]
 
 
@@ -100,6 +100,7 @@ def lib() -> C.CDLL:
         L.b200q_mul_mat.argtypes = [C.POINTER(MulMatArgs), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
                                     C.c_void_p]
         L.b200q_mul_mat_workspace.argtypes = [C.POINTER(MulMatArgs)]
+        L.b200q_mul_mat_static.argtypes = [C.POINTER(MulMatArgs), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.b200q_mul_mat_id.argtypes = [C.POINTER(MulMatIdArgs), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.c_void_p, C.c_size_t, C.c_void_p]
         L.b200q_mul_mat_id_workspace.argtypes = [C.POINTER(MulMatIdArgs)]
@@ -250,6 +251,25 @@ def mul_mat(w: QTensor, act, out=None, flags: int = FLAG_WEIGHTS_IMMUTABLE):
     ws, ws_n = _ws.get(need)
     _check(lib().b200q_mul_mat(C.byref(a), w.data.data_ptr(), act.data_ptr(), out.data_ptr(),
                                ws.data_ptr() if ws is not None else None, ws_n, _stream()), "b200q_mul_mat")
+    return out
+
+
+STATIC_WORKSPACE_BYTES = 16 << 20  # B200Q_STATIC_WORKSPACE_BYTES (include/b200q.h)
+
+
+def mul_mat_static(w: QTensor, act, out, flags: int = FLAG_WEIGHTS_IMMUTABLE):
+    """b200q_mul_mat_static: mul_mat on 2-D operands into a caller-provided ``out`` with the library's static scratch —
+    neither this wrapper nor the call allocates device memory.  Shapes whose scratch exceeds STATIC_WORKSPACE_BYTES raise."""
+    torch = _torch()
+    assert len(w.shape) == 2 and act.dim() == 2 and act.dtype == torch.float32 and act.is_cuda and act.stride(-1) == 1
+    k, m, n = w.k, w.m, act.shape[0]
+    assert act.shape[1] == k and out.dtype == torch.float32 and out.is_cuda and out.shape == (n, m) and out.is_contiguous()
+    rs = row_size(w.qtype, k)
+    nb11 = act.stride(0) * 4
+    a = MulMatArgs(w.qtype, k, m, n, 1, 1, 1, 1, rs, rs * m, rs * m, nb11, nb11 * n, nb11 * n, m * 4, m * 4 * n, m * 4 * n,
+                   flags)
+    _check(lib().b200q_mul_mat_static(C.byref(a), w.data.data_ptr(), act.data_ptr(), out.data_ptr(), _stream()),
+           "b200q_mul_mat_static")
     return out
 
 

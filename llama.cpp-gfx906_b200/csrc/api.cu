@@ -818,6 +818,44 @@ int b200q_mul_mat(const b200q_mul_mat_args * a, const void * w, const float * ac
     return 0;
 }
 
+// ---- MUL_MAT without any allocation (b200q_mul_mat_static, include/b200q.h) --------------------------------------------
+// For callers that cannot allocate (CUDA-graph capture, serving loops, harnesses that forbid cudaMalloc): the tensor-core
+// kernel's scratch (the packed bf16 activation image) lives in this file-scope device array instead of a caller buffer.
+// Every GPU that loads the library holds B200Q_STATIC_WORKSPACE_BYTES until exit.  The array's name is only a host-side
+// stand-in: host code gets the device address from cudaGetSymbolAddress, once per device, with that device current.
+static __device__ __align__(256) unsigned char g_static_workspace[B200Q_STATIC_WORKSPACE_BYTES];
+
+static int static_workspace_ptr(void ** out) {
+    static std::mutex mu;
+    static void *     ptr[64] = {};
+    int               dev     = -1;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(B200Q_EINVAL, "mul_mat_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptr[dev]) {
+        void * p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(&p, g_static_workspace));
+        if (!p) return fail(B200Q_ECUDA, "mul_mat_static: cudaGetSymbolAddress returned a null address");
+        ptr[dev] = p;
+    }
+    *out = ptr[dev];
+    return 0;
+}
+
+int b200q_mul_mat_static(const b200q_mul_mat_args * a, const void * w, const float * act, float * dst, void * stream) {
+    if (int rc = check_mm(a)) return rc;
+    const size_t need = b200q_mul_mat_workspace(a);
+    if (need > (size_t) B200Q_STATIC_WORKSPACE_BYTES) {
+        return fail(B200Q_EWORKSPACE, "mul_mat_static: this shape needs %zu bytes of scratch, the static workspace holds %zu "
+                    "(B200Q_STATIC_WORKSPACE_BYTES); use b200q_mul_mat with a caller workspace", need,
+                    (size_t) B200Q_STATIC_WORKSPACE_BYTES);
+    }
+    void * ws = nullptr;
+    if (int rc = static_workspace_ptr(&ws)) return rc;
+    // nothing in the scratch has to start at zero: mmq_pack_act rewrites every byte the kernel reads (padding tiles included)
+    return b200q_mul_mat(a, w, act, dst, ws, (size_t) B200Q_STATIC_WORKSPACE_BYTES, stream);
+}
+
 // ---- grouped decode GEMV: matrices that share one activation vector (q/k/v, gate/up) in one launch ------------------
 static int mul_mat_group_impl(const b200q_mul_mat_group_args * a, const void * const * w, const float * act, float * const * dst,
                               int n_peers, const int64_t * peer_delta, void * stream);
