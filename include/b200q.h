@@ -50,9 +50,13 @@ enum b200q_type {
     B200Q_TYPE_Q5_0  = 6,
     B200Q_TYPE_Q5_1  = 7,
     B200Q_TYPE_Q8_0  = 8,
+    B200Q_TYPE_Q2_K  = 10,
+    B200Q_TYPE_Q3_K  = 11,
     B200Q_TYPE_Q4_K  = 12,
     B200Q_TYPE_Q5_K  = 13,
     B200Q_TYPE_Q6_K  = 14,
+    B200Q_TYPE_IQ4_NL = 20,
+    B200Q_TYPE_IQ4_XS = 23,
     B200Q_TYPE_MXFP4 = 39,
 };
 
@@ -96,12 +100,25 @@ B200Q_API int b200q_stream_destroy(void * stream);
 B200Q_API int b200q_stream_synchronize(void * stream);
 B200Q_API int b200q_host_alloc(void ** ptr, size_t bytes);         /* pinned host memory */
 B200Q_API int b200q_host_free(void * ptr);
+/* events, cross-stream ordering, peer mappings (cudaEvent* / cudaStreamWaitEvent / cudaDeviceEnablePeerAccess /
+ * cudaMemcpyPeerAsync of ggml-cuda.cu:1358-1414, 2556-2605, 3038-3060): what the plugin's events, cpy_tensor_async and
+ * single-process row split are built from */
+B200Q_API int b200q_event_create(void ** event);                     /* on the current device, timing disabled */
+B200Q_API int b200q_event_destroy(void * event);
+B200Q_API int b200q_event_record(void * event, void * stream);
+B200Q_API int b200q_event_synchronize(void * event);
+B200Q_API int b200q_stream_wait_event(void * stream, void * event);  /* event may belong to another device */
+B200Q_API int b200q_enable_peer_access(int device, int peer);        /* kernels on `device` may load / store peer's memory;
+                                                                         B200Q_ENOTSUP when the link does not allow it */
+B200Q_API int b200q_memcpy_peer(void * dst, int dst_device, const void * src, int src_device, size_t bytes, void * stream);
 
 /* ---- type table (mirrors ggml_blck_size / ggml_type_size, ggml.c:586-876) -------------------- */
 B200Q_API int64_t b200q_blck_size(int type);
 B200Q_API size_t  b200q_type_size(int type);
 B200Q_API size_t  b200q_row_size(int type, int64_t ne0);
 B200Q_API int     b200q_type_supported(int type); /* 1 if usable as MUL_MAT/GET_ROWS weight type */
+B200Q_API int64_t b200q_max_k(int type);          /* longest row every MUL_MAT(_ID) shape of `type` is served at (host-only
+                                                      planner probe; what supports_op caps ne[0] with) */
 
 /* ---- dequantize / GET_ROWS (bit-exact vs dequantize_row_*) ----------------------------------- */
 /* contiguous: n_elems % blck_size == 0 */

@@ -21,10 +21,12 @@ LIB_PATH = os.environ.get("B200Q_LIB", os.path.join(os.path.dirname(_HERE), "lib
 
 # ggml_type numbers
 F32, Q4_0, Q4_1, Q5_0, Q5_1, Q8_0, Q4_K, Q5_K, Q6_K, MXFP4 = 0, 2, 3, 6, 7, 8, 12, 13, 14, 39
+Q2_K, Q3_K, IQ4_NL, IQ4_XS = 10, 11, 20, 23
 TYPE_NAMES = {Q4_0: "q4_0", Q4_1: "q4_1", Q5_0: "q5_0", Q5_1: "q5_1", Q8_0: "q8_0", Q4_K: "q4_K", Q5_K: "q5_K",
-              Q6_K: "q6_K", MXFP4: "mxfp4"}
+              Q6_K: "q6_K", MXFP4: "mxfp4", Q2_K: "q2_K", Q3_K: "q3_K", IQ4_NL: "iq4_nl", IQ4_XS: "iq4_xs"}
 BLCK = {Q4_0: (32, 18), Q4_1: (32, 20), Q5_0: (32, 22), Q5_1: (32, 24), Q8_0: (32, 34), MXFP4: (32, 17),
-        Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210), F32: (1, 4)}
+        Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210), F32: (1, 4), Q2_K: (256, 84), Q3_K: (256, 110),
+        IQ4_NL: (32, 18), IQ4_XS: (256, 136)}
 
 FLAG_WEIGHTS_IMMUTABLE, FLAG_FORCE_GEMV, FLAG_FORCE_MMQ, FLAG_NO_PDL = 1, 2, 4, 8
 
@@ -36,6 +38,8 @@ EXPORTS = [
     "b200q_mul_mat_host", "b200q_set_device", "b200q_malloc", "b200q_free", "b200q_memset", "b200q_memcpy",
     "b200q_stream_create", "b200q_stream_destroy", "b200q_stream_synchronize", "b200q_host_alloc", "b200q_host_free",
     "b200q_list_create", "b200q_list_launch", "b200q_list_destroy", "b200q_list_info", "b200q_mul_mat_static",
+    "b200q_event_create", "b200q_event_destroy", "b200q_event_record", "b200q_event_synchronize", "b200q_stream_wait_event",
+    "b200q_enable_peer_access", "b200q_memcpy_peer", "b200q_max_k",
 ]
 
 
@@ -90,6 +94,8 @@ def lib() -> C.CDLL:
         L = C.CDLL(LIB_PATH)
         L.b200q_last_error.restype = C.c_char_p
         L.b200q_blck_size.restype = C.c_int64
+        L.b200q_max_k.restype = C.c_int64
+        L.b200q_max_k.argtypes = [C.c_int]
         L.b200q_type_size.restype = C.c_size_t
         L.b200q_row_size.restype = C.c_size_t
         L.b200q_row_size.argtypes = [C.c_int, C.c_int64]

@@ -611,6 +611,37 @@ int b200q_stream_destroy(void * stream) { CUDA_TRY(cudaStreamDestroy((cudaStream
 int b200q_stream_synchronize(void * stream) { CUDA_TRY(cudaStreamSynchronize((cudaStream_t) stream)); return 0; }
 int b200q_host_alloc(void ** ptr, size_t bytes) { CUDA_TRY(cudaMallocHost(ptr, bytes)); return 0; }
 int b200q_host_free(void * ptr) { CUDA_TRY(cudaFreeHost(ptr)); return 0; }
+int b200q_event_create(void ** event) {
+    cudaEvent_t e = nullptr;
+    CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    *event = (void *) e;
+    return 0;
+}
+int b200q_event_destroy(void * event) { CUDA_TRY(cudaEventDestroy((cudaEvent_t) event)); return 0; }
+int b200q_event_record(void * event, void * stream) { CUDA_TRY(cudaEventRecord((cudaEvent_t) event, (cudaStream_t) stream)); return 0; }
+int b200q_event_synchronize(void * event) { CUDA_TRY(cudaEventSynchronize((cudaEvent_t) event)); return 0; }
+int b200q_stream_wait_event(void * stream, void * event) {
+    CUDA_TRY(cudaStreamWaitEvent((cudaStream_t) stream, (cudaEvent_t) event, 0));
+    return 0;
+}
+int b200q_enable_peer_access(int device, int peer) {
+    if (device == peer) return 0;
+    int can = 0;
+    CUDA_TRY(cudaDeviceCanAccessPeer(&can, device, peer));
+    if (!can) return fail(B200Q_ENOTSUP, "device %d cannot map the memory of device %d", device, peer);
+    int cur = 0;
+    CUDA_TRY(cudaGetDevice(&cur));
+    CUDA_TRY(cudaSetDevice(device));
+    cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); e = cudaSuccess; }
+    cudaSetDevice(cur);
+    if (e != cudaSuccess) return fail(B200Q_ECUDA, "cudaDeviceEnablePeerAccess(%d -> %d): %s", device, peer, cudaGetErrorString(e));
+    return 0;
+}
+int b200q_memcpy_peer(void * dst, int dst_device, const void * src, int src_device, size_t bytes, void * stream) {
+    CUDA_TRY(cudaMemcpyPeerAsync(dst, dst_device, src, src_device, bytes, (cudaStream_t) stream));
+    return 0;
+}
 
 int64_t b200q_blck_size(int type) { return blck_elems(type); }
 size_t  b200q_type_size(int type) { return (size_t) blck_bytes(type); }
@@ -619,6 +650,30 @@ size_t  b200q_row_size(int type, int64_t ne0) {
     return be ? (size_t) (ne0 / be) * (size_t) blck_bytes(type) : 0;
 }
 int b200q_type_supported(int type) { return type != T_F32 && blck_elems(type) > 0; }
+// largest row length every MUL_MAT / MUL_MAT_ID shape of `type` can be served at: the last-resort kernel (gemv_stream_kernel,
+// one column, rows at an arbitrary pitch) needs the int8 activation column, its scales and two ring stages in shared
+// memory.  Host-only (device attributes when a device is present, B200's otherwise): the plugin's supports_op asks this so
+// that an op it accepts never comes back as B200Q_ENOTSUP.
+int64_t b200q_max_k(int type) {
+    const int be = blck_elems(type);
+    if (!be || type == T_F32) return 0;
+    DevInfo di = dev_info();
+    if (!di.ok) { di.sms = 148; di.max_smem = 232448; }
+    auto fits = [&](int64_t k) {
+        GemvPlan plan{};
+        GemvParams & p = plan.p;
+        p.k = (int) k; p.m = 4096; p.nch = 1; p.mode = GEMV_MODE_BATCH; p.ne12 = 1; p.r2 = p.r3 = 1; p.n_used = p.n_expert = 1;
+        p.w_nb1 = (long long) (k / be) * blck_bytes(type) + 16;  // not dense: the padded shared-memory pitch
+        return plan_gemv(plan, type, 1, di);
+    };
+    const int64_t step = be == 32 ? 256 : be;
+    int64_t lo = 0, hi = (1 << 17) / step;  // k = step * i
+    while (lo < hi) {
+        const int64_t mid = (lo + hi + 1) / 2;
+        if (fits(mid * step)) lo = mid; else hi = mid - 1;
+    }
+    return lo * step;
+}
 
 // ---- dequantize / GET_ROWS -----------------------------------------------------------------------------
 static int launch_get_rows(const GetRowsParams & p, int type, cudaStream_t st) {

@@ -2,7 +2,8 @@
 //
 // The storage layouts are those of the reference's ggml/src/ggml-common.h (block_q4_0 :170-175,
 // block_q4_1 :178-189, block_mxfp4 :190-195, block_q5_0 :198-203, block_q5_1 :206-218, block_q8_0 :219-224,
-// block_q4_K :295-306, block_q5_K :312-324, block_q6_K :330-336) and are reused UNCHANGED so existing
+// block_q2_K :265-276, block_q3_K :282-288, block_q4_K :295-306, block_q5_K :312-324, block_q6_K :330-336, block_iq4_nl
+// :416-420, block_iq4_xs :422-428) and are reused UNCHANGED so existing
 // GGUF files work untouched.  We never dereference them as structs on the device (rows are only 1- or
 // 2-byte aligned at block granularity) — every access goes through byte offsets below.
 //
@@ -24,9 +25,13 @@ enum : int {
     T_Q5_0  = 6,
     T_Q5_1  = 7,
     T_Q8_0  = 8,
+    T_Q2_K  = 10,
+    T_Q3_K  = 11,
     T_Q4_K  = 12,
     T_Q5_K  = 13,
     T_Q6_K  = 14,
+    T_IQ4_NL = 20,
+    T_IQ4_XS = 23,
     T_MXFP4 = 39,
 };
 
@@ -37,14 +42,18 @@ template <> struct BlockInfo<T_Q5_0>  { static constexpr int ELEMS = 32,  BYTES 
 template <> struct BlockInfo<T_Q5_1>  { static constexpr int ELEMS = 32,  BYTES = 24;  };  // d:0 m:2 qh:4 qs:8
 template <> struct BlockInfo<T_Q8_0>  { static constexpr int ELEMS = 32,  BYTES = 34;  };  // d:0 qs:2
 template <> struct BlockInfo<T_MXFP4> { static constexpr int ELEMS = 32,  BYTES = 17;  };  // e:0 qs:1
+template <> struct BlockInfo<T_IQ4_NL> { static constexpr int ELEMS = 32, BYTES = 18;  };  // d:0 qs:2 (code points kvalues_iq4nl)
+template <> struct BlockInfo<T_Q2_K>  { static constexpr int ELEMS = 256, BYTES = 84;  };  // scales:0 qs:16 d:80 dmin:82
+template <> struct BlockInfo<T_Q3_K>  { static constexpr int ELEMS = 256, BYTES = 110; };  // hmask:0 qs:32 scales:96 d:108
+template <> struct BlockInfo<T_IQ4_XS> { static constexpr int ELEMS = 256, BYTES = 136; }; // d:0 scales_h:2 scales_l:4 qs:8
 template <> struct BlockInfo<T_Q4_K>  { static constexpr int ELEMS = 256, BYTES = 144; };  // d:0 dmin:2 scales:4 qs:16
 template <> struct BlockInfo<T_Q5_K>  { static constexpr int ELEMS = 256, BYTES = 176; };  // d:0 dmin:2 scales:4 qh:16 qs:48
 template <> struct BlockInfo<T_Q6_K>  { static constexpr int ELEMS = 256, BYTES = 210; };  // ql:0 qh:128 scales:192 d:208
 
 inline __host__ __device__ int blck_elems(int type) {
     switch (type) {
-        case T_Q4_0: case T_Q4_1: case T_Q5_0: case T_Q5_1: case T_Q8_0: case T_MXFP4: return 32;
-        case T_Q4_K: case T_Q5_K: case T_Q6_K: return 256;
+        case T_Q4_0: case T_Q4_1: case T_Q5_0: case T_Q5_1: case T_Q8_0: case T_MXFP4: case T_IQ4_NL: return 32;
+        case T_Q4_K: case T_Q5_K: case T_Q6_K: case T_Q2_K: case T_Q3_K: case T_IQ4_XS: return 256;
         case T_F32: return 1;
         default: return 0;
     }
@@ -54,6 +63,7 @@ inline __host__ __device__ int blck_bytes(int type) {
         case T_Q4_0: return 18;  case T_Q4_1: return 20;  case T_Q5_0: return 22;  case T_Q5_1: return 24;
         case T_Q8_0: return 34;  case T_MXFP4: return 17; case T_Q4_K: return 144; case T_Q5_K: return 176;
         case T_Q6_K: return 210; case T_F32: return 4;
+        case T_Q2_K: return 84;  case T_Q3_K: return 110; case T_IQ4_NL: return 18; case T_IQ4_XS: return 136;
         default: return 0;
     }
 }
@@ -259,6 +269,63 @@ template <> B200Q_HD float decode_elem<T_Q6_K>(const uint8_t * row, int64_t i) {
     const int       q    = (int) (int8_t) (nib | (hb << 4)) - 32;
     const int       sc   = (int8_t) b[192 + 8 * n128 + (l >> 4) + 2 * quad];
     return mul_rn(mul_rn(d, (float) sc), (float) q);
+}
+
+
+// non-linear 4-bit code points (kvalues_iq4nl, ggml-common.h:1088-1090)
+B200Q_HD int iq4nl_value(int nib) {
+    // -127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113 packed as bytes of four words
+    const uint32_t t[4] = { 0xBFAD9881u, 0xF6EADDCFu, 0x26190D01u, 0x71594535u };
+    return (int) (int8_t) (t[(nib >> 2) & 3] >> (8 * (nib & 3)));
+}
+// 6-bit scale j (0..15) of a q3_K super-block from its 12 packed bytes (the aux[] shuffle of dequantize_row_q3_K,
+// ggml-quants.c:1147-1152): low 4 bits in bytes 0..7 (low / high nibble), high 2 bits in bytes 8..11
+B200Q_HD int q3k_scale(const uint8_t * sc, int j) {
+    const int lo = j < 8 ? (sc[j] & 0xF) : (sc[j - 8] >> 4);
+    const int hi = (sc[8 + (j & 3)] >> (2 * (j >> 2))) & 3;
+    return (lo | (hi << 4)) - 32;
+}
+
+// dequantize_row_q2_K ggml-quants.c:784-814, _q3_K :1128-1176, _iq4_nl :2512-2528, _iq4_xs :2530-2550
+template <> B200Q_HD float decode_elem<T_Q2_K>(const uint8_t * row, int64_t i) {
+    const uint8_t * b = row + (i >> 8) * 84;
+    const int       r = (int) (i & 255);
+    const int       n = r >> 7, j = (r >> 5) & 3, h = (r >> 4) & 1, l = r & 15;
+    const float     d    = half_bits_to_float(ld_u16(b + 80));
+    const float     dmin = half_bits_to_float(ld_u16(b + 82));
+    const uint8_t   sc   = b[8 * n + 2 * j + h];
+    const float     dl   = mul_rn(d, (float) (sc & 0xF));
+    const float     ml   = mul_rn(dmin, (float) (sc >> 4));
+    const int       q    = (b[16 + 32 * n + 16 * h + l] >> (2 * j)) & 3;
+    return sub_rn(mul_rn(dl, (float) q), ml);
+}
+template <> B200Q_HD float decode_elem<T_Q3_K>(const uint8_t * row, int64_t i) {
+    const uint8_t * b = row + (i >> 8) * 110;
+    const int       r = (int) (i & 255);
+    const int       n = r >> 7, j = (r >> 5) & 3, h = (r >> 4) & 1, l = r & 15;
+    const float     d  = half_bits_to_float(ld_u16(b + 108));
+    const float     dl = mul_rn(d, (float) q3k_scale(b + 96, 8 * n + 2 * j + h));
+    const int       q  = (b[32 + 32 * n + 16 * h + l] >> (2 * j)) & 3;
+    const int       hm = (b[16 * h + l] >> (4 * n + j)) & 1;
+    return mul_rn(dl, (float) (q - (hm ? 0 : 4)));
+}
+template <> B200Q_HD float decode_elem<T_IQ4_NL>(const uint8_t * row, int64_t i) {
+    const uint8_t * b = row + (i >> 5) * 18;
+    const int       j = (int) (i & 31);
+    const float     d = half_bits_to_float(ld_u16(b));
+    const int       q = j < 16 ? (b[2 + j] & 0xF) : (b[2 + j - 16] >> 4);
+    return mul_rn(d, (float) iq4nl_value(q));
+}
+template <> B200Q_HD float decode_elem<T_IQ4_XS>(const uint8_t * row, int64_t i) {
+    const uint8_t * b  = row + (i >> 8) * 136;
+    const int       r  = (int) (i & 255);
+    const int       ib = r >> 5, j = r & 31;
+    const float     d  = half_bits_to_float(ld_u16(b));
+    const int       sh = ld_u16(b + 2);
+    const int       ls = ((b[4 + ib / 2] >> (4 * (ib % 2))) & 0xF) | (((sh >> (2 * ib)) & 3) << 4);
+    const float     dl = mul_rn(d, (float) (ls - 32));
+    const uint8_t   qb = b[8 + 16 * ib + (j & 15)];
+    return mul_rn(dl, (float) iq4nl_value(j < 16 ? (qb & 0xF) : (qb >> 4)));
 }
 
 }  // namespace b200q

@@ -418,7 +418,13 @@ __global__ void __launch_bounds__(NTHREADS, NW <= 8 ? 2 : 1) gemv_stream_kernel(
                                     aw[4 * i4 + 2] = t.z;
                                     aw[4 * i4 + 3] = t.w;
                                 }
-                                const float2 x = lds64f(p.ds_off + (uint32_t) (j * nblk + U::act_blk(u, g)) * 8);
+                                float2 x = lds64f(p.ds_off + (uint32_t) (j * nblk + U::act_blk(u, g)) * 8);
+                                if (U::MIN16) {  // the group's min applies to 16 activations: d_x * sum of this group's q_x
+                                    int asum = 0;
+#pragma unroll
+                                    for (int i = 0; i < U::GW; ++i) asum = dp4a_(0x01010101, aw[i], asum);
+                                    x.y = x.x * (float) asum;
+                                }
 #pragma unroll
                                 for (int rr = 0; rr < RB; ++rr) {
                                     int s0 = 0, s1 = 0;
@@ -545,6 +551,10 @@ gemv_kernel_t gemv_kernel_for(int type, int ncols) {
         case T_Q4_K:  return pick_ncols<T_Q4_K>(ncols);
         case T_Q5_K:  return pick_ncols<T_Q5_K>(ncols);
         case T_Q6_K:  return pick_ncols<T_Q6_K>(ncols);
+        case T_Q2_K:  return pick_ncols<T_Q2_K>(ncols);
+        case T_Q3_K:  return pick_ncols<T_Q3_K>(ncols);
+        case T_IQ4_NL: return pick_ncols<T_IQ4_NL>(ncols);
+        case T_IQ4_XS: return pick_ncols<T_IQ4_XS>(ncols);
         default: return nullptr;
     }
 }
@@ -554,7 +564,7 @@ int gemv_consumer_warps() { return NW; }
 int gemv_act_off() { return (int) OFF_ACT; }
 int gemv_unit_elems(int type) {
     switch (type) {
-        case T_Q4_K: case T_Q5_K: case T_Q6_K: return 64;
+        case T_Q4_K: case T_Q5_K: case T_Q6_K: case T_Q2_K: case T_Q3_K: return 64;
         default: return 32;
     }
 }

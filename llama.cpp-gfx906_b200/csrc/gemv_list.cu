@@ -11,7 +11,12 @@
 //     with the NEXT stage of its sequence — which may belong to a later matrix: the weights are immutable, so the HBM
 //     stream never stops at a matrix boundary, a dependency or an activation reload;
 //   * activations are quantized per CTA into one of two shared-memory images ("generations": consecutive ops that read
-//     the same vector share one), each warp doing its share as soon as it has finished the previous generation;
+//     the same vector share one) by a third warpgroup of 4 QUANTIZER warps that runs one generation ahead of the 8 compute
+//     warps (image FULL / FREE named barriers; setmaxnreg gives the compute warps 216 registers, the quantizers 72 —
+//     2 x 216 + 72 = the 3 x 168 a scheduler partition was allocated): the L2 round trips of the f32 vector and the compute
+//     warps' skew at a switch left the critical path (they were ~1.2 us per generation, 18 % of the 8B pass: every shape
+//     alone ran at 81-87 % of HBM, the pass at 69 %; now 87 %).  Quantizing a dependent vector with all 12 warps was tried:
+//     inlined it spills in the stage loop, out of line the call forces the 168-register ABI (both slower);
 //   * a generation whose vector is produced by earlier ops of the list (or by the other GPUs of a row split) sits behind
 //     a BARRIER POINT: every CTA counts itself in when its 8 warps have stored (and fenced) everything before it
 //     (one red.release per CTA), readers poll with ld.acquire; with row split the rank that completes a barrier point
@@ -35,7 +40,10 @@ namespace {
 using namespace sm100;
 using namespace kqdot;
 
-constexpr int NTHREADS = LIST_WARPS * 32;
+constexpr int CTHREADS = LIST_WARPS * 32;                    // compute warps (warpgroups 0 and 1)
+constexpr int NTHREADS = (LIST_WARPS + LIST_QWARPS) * 32;    // + the quantizer warpgroup
+// named barriers: 0 __syncthreads; 2, 3 barrier point (compute warps); 4, 5 image FULL; 6, 7 image FREE; 8 barrier point done
+constexpr int BAR_FULL = 4, BAR_FREE = 6, BAR_BPDONE = 8;
 constexpr uint32_t OFF_FULL = 0;    // full-barriers, 8 B each (LIST_MAX_SLOTS)
 constexpr uint32_t OFF_CNT  = 8 * LIST_MAX_SLOTS;  // 2 x u32: warps of this CTA that reached barrier point (bp & 1)
 
@@ -70,6 +78,9 @@ __device__ __forceinline__ unsigned long long gtime() {
 }
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ void named_bar_arrive(int id, int nthreads) {
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
 // one op record from the shared-memory table (48 bytes = 3 x int4, gemv_list.cuh)
@@ -225,7 +236,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
     // in front of the arrivals (4.4 -> 2.4 us per barrier point) — and a second CTA barrier lets everybody continue behind
     // its acquire.
     auto barrier_point = [&](int bp) {
-        named_bar_sync(2, NTHREADS);
+        named_bar_sync(2, CTHREADS);
         if (warp == 0) {
             if (lane == 0) {
                 if (p.world > 1) {
@@ -247,23 +258,20 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
             }
             __syncwarp();
         }
-        named_bar_sync(3, NTHREADS);
+        named_bar_sync(3, CTHREADS);
     };
 
-    // ---- generation switch: wait if needed, quantize this warp's share of the vector into image g & 1 ---------------
+    // ---- generations ------------------------------------------------------------------------------------------------
+    // decode of one generation record + the layout of its image
     ActLayout al{};
     uint32_t  abase = 0;
-    RegAct    RA;
-    auto gen_switch = [&](int g) {
-        const int4    gi    = lds128(gtab + 16u * (uint32_t) g);
-        const float * act   = (const float *) (((unsigned long long) (uint32_t) gi.y << 32) | (uint32_t) gi.x);
-        const int     nsb   = (int) ((uint32_t) gi.z & 0xffffu);
-        const int     qmode = (int) (((uint32_t) gi.z >> 16) & 0xffu);
-        const int     wait  = (int) ((uint32_t) gi.z >> 24);
-        const int     bp    = (int) ((uint32_t) gi.w & 0xffffu);
-        EV(1, g);
-        if (wait) barrier_point(bp);
-        EV(2, g);
+    auto gen_layout = [&](int g, const float *& act, int & qmode, int & wait, int & bp) {
+        const int4 gi  = lds128(gtab + 16u * (uint32_t) g);
+        act            = (const float *) (((unsigned long long) (uint32_t) gi.y << 32) | (uint32_t) gi.x);
+        const int nsb  = (int) ((uint32_t) gi.z & 0xffffu);
+        qmode          = (int) (((uint32_t) gi.z >> 16) & 0xffu);
+        wait           = (int) ((uint32_t) gi.z >> 24);
+        bp             = (int) ((uint32_t) gi.w & 0xffffu);
         al.nsb   = nsb;
         al.off_q = 0;
         if (qmode == 0) {
@@ -275,17 +283,47 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
             al.off_bs16 = al.off_bs32 = 0;
         }
         abase = sb + (uint32_t) p.off_act + (uint32_t) (g & 1) * (uint32_t) p.act_stride;
-        if (qmode == 0) quantize_act<LIST_WARPS>(al, act, abase, warp, lane);
-        else if (qmode == 1) quantize_act32<false, LIST_WARPS>(al, act, abase, warp, lane);
-        else quantize_act32<true, LIST_WARPS>(al, act, abase, warp, lane);
+    };
+
+    // ---- quantizer warpgroup: image g & 1 <- generation g, one generation ahead of the compute warps -------------------
+    if (warp >= LIST_WARPS) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+        const int qw = warp - LIST_WARPS;
+        for (int g = 0; g < p.n_gens; ++g) {
+            const float * act;
+            int           qmode, wait, bp;
+            gen_layout(g, act, qmode, wait, bp);
+            if (g >= 2) named_bar_sync(BAR_FREE + (g & 1), NTHREADS);  // the compute warps are done with generation g - 2
+            if (wait) named_bar_sync(BAR_BPDONE, NTHREADS);            // ... and have passed the barrier point in front of g
+            if (qmode == 0) quantize_act<LIST_QWARPS>(al, act, abase, qw, lane);
+            else if (qmode == 1) quantize_act32<false, LIST_QWARPS>(al, act, abase, qw, lane);
+            else quantize_act32<true, LIST_QWARPS>(al, act, abase, qw, lane);
+            named_bar_arrive(BAR_FULL + (g & 1), NTHREADS);
+        }
+    } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
+
+    // compute warps: switch to generation g (every warp takes part in every switch, with or without work in it)
+    RegAct RA;
+    auto gen_switch = [&](int g) {
+        const float * act;
+        int           qmode, wait, bp;
+        EV(1, g);
+        // this warp no longer reads the previous image; generation g + 1 will overwrite it
+        if (g >= 1 && g + 1 < p.n_gens) named_bar_arrive(BAR_FREE + ((g - 1) & 1), NTHREADS);
+        gen_layout(g, act, qmode, wait, bp);
+        if (wait) {
+            barrier_point(bp);
+            named_bar_arrive(BAR_BPDONE, NTHREADS);
+        }
+        EV(2, g);
+        named_bar_sync(BAR_FULL + (g & 1), NTHREADS);
         EV(3, g);
-        // all shares written; and nobody still reads image g & 1's next victim (generation g - 1's image is reused by g + 1)
-        named_bar_sync(1, NTHREADS);
         // column-owning lanes: this generation's quantized activations of "my" super-block columns -> registers
-        if (qmode == 0 && nsb <= LIST_REG_ACT_NSB) {
-            const int lpr = nsb == 1 ? 1 : 1 << (32 - __clz(nsb - 1));
+        if (qmode == 0 && al.nsb <= LIST_REG_ACT_NSB) {
+            const int lpr = al.nsb == 1 ? 1 : 1 << (32 - __clz(al.nsb - 1));
             const int col = lane & (lpr - 1);
-            if (col < nsb) RA.load(al, abase, col);
+            if (col < al.nsb) RA.load(al, abase, col);
         }
         EV(4, g);
     };
@@ -424,9 +462,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
     }
     while (g < p.n_gens - 1) gen_switch(++g);  // warps without work still take part in every switch
     if (p.final_bp) barrier_point(p.n_bp);
+    }  // compute warps
 
     // ---- exit: the last CTA re-arms the sync block for the next launch ------------------------------------------------
-    named_bar_sync(1, NTHREADS);
+    __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence();
         const unsigned prev = atomicAdd(p.sync + LIST_SYNC_EXIT, 1u);

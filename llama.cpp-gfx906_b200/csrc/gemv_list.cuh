@@ -13,7 +13,8 @@ namespace b200q {
 // activations in registers for the whole generation and walks the rows of the stage two at a time;
 // lpr = the power of two >= columns, 32 / lpr rows run side by side.  Everything else: a lane owns a row of the stage and
 // walks its blocks (gemv_kq.cu's scheme), activations read from shared memory.
-constexpr int LIST_WARPS         = 8;
+constexpr int LIST_WARPS         = 8;                         // compute warps (own the ring slots, walk the units)
+constexpr int LIST_QWARPS        = 4;                         // + one warpgroup that quantizes the activations one generation ahead
 constexpr int LIST_STAGE_PAYLOAD = 9216;                      // 4 rows of q4_K at k = 4096
 constexpr int LIST_SLOT_BYTES    = LIST_STAGE_PAYLOAD + 128;  // payload + <= 15 bytes of alignment lead + 16 bytes of over-read
 constexpr int LIST_MIN_SLOTS     = 2 * LIST_WARPS;            // every warp owns at least two ring slots

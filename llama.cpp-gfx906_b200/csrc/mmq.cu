@@ -825,6 +825,10 @@ mmq_kernel_t mmq_kernel_for(int type) {
         case T_Q4_K:  return mmq_kernel<T_Q4_K>;
         case T_Q5_K:  return mmq_kernel<T_Q5_K>;
         case T_Q6_K:  return mmq_kernel<T_Q6_K>;
+        case T_Q2_K:  return mmq_kernel<T_Q2_K>;    // these four dequantize through the scalar decoders of blocks.cuh
+        case T_Q3_K:  return mmq_kernel<T_Q3_K>;
+        case T_IQ4_NL: return mmq_kernel<T_IQ4_NL>;
+        case T_IQ4_XS: return mmq_kernel<T_IQ4_XS>;
         default: return nullptr;
     }
 }

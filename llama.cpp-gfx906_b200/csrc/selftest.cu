@@ -37,6 +37,10 @@ static void fill_row(int type, std::vector<uint8_t> & row, int nblocks) {
             case T_MXFP4: row[o] = (uint8_t) (110 + rng() % 30); break;
             case T_Q4_K: case T_Q5_K: put_half(o, 0.f, 0.1f); put_half(o + 2, 0.f, 0.1f); break;
             case T_Q6_K: put_half(o + 208, -0.05f, 0.05f); break;
+            case T_Q2_K: put_half(o + 80, 0.f, 0.1f); put_half(o + 82, 0.f, 0.1f); break;
+            case T_Q3_K: put_half(o + 108, -0.05f, 0.05f); break;
+            case T_IQ4_NL: put_half(o, -0.05f, 0.05f); break;
+            case T_IQ4_XS: put_half(o, -0.005f, 0.005f); break;
         }
     }
 }
@@ -118,6 +122,10 @@ int main() {
     e += check_type<T_Q4_K>("q4_K");
     e += check_type<T_Q5_K>("q5_K");
     e += check_type<T_Q6_K>("q6_K");
+    e += check_type<T_Q2_K>("q2_K");
+    e += check_type<T_Q3_K>("q3_K");
+    e += check_type<T_IQ4_NL>("iq4_nl");
+    e += check_type<T_IQ4_XS>("iq4_xs");
     printf(e ? "selftest FAILED (%d)\n" : "selftest passed\n", e);
     return e ? 1 : 0;
 }

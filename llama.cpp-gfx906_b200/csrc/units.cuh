@@ -179,7 +179,7 @@ template <int T> struct Unit;
 
 template <int T, int BYTES> struct UnitBlock32 {
     static constexpr int  ELEMS = 32, NG = 1, GW = 8;
-    static constexpr bool UNSIGNED_W = false;
+    static constexpr bool UNSIGNED_W = false, MIN16 = false;
     static B200Q_HD int  act_word(int u, int) { return u * 8; }
     static B200Q_HD int  act_blk(int u, int) { return u; }
 };
@@ -306,7 +306,7 @@ B200Q_HD void k4_scale_min_pair(uint32_t s0, uint32_t s1, uint32_t s2, int p, ui
 
 template <> struct Unit<T_Q4_K> {
     static constexpr int  ELEMS = 64, NG = 2, GW = 8;
-    static constexpr bool UNSIGNED_W = true;  // wq bytes are unsigned; group 1 holds 16 * nibble (scale pre-divided)
+    static constexpr bool UNSIGNED_W = true, MIN16 = false;  // wq bytes are unsigned; group 1 holds 16 * nibble (scale pre-divided)
     static B200Q_HD int  act_word(int u, int g) { return u * 16 + g * 8; }
     static B200Q_HD int  act_blk(int u, int g) { return u * 2 + g; }
     template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[16], float (&ws)[2], float (&wm)[2]) {
@@ -333,7 +333,7 @@ template <> struct Unit<T_Q4_K> {
 };
 template <> struct Unit<T_Q5_K> {
     static constexpr int  ELEMS = 64, NG = 2, GW = 8;
-    static constexpr bool UNSIGNED_W = true;
+    static constexpr bool UNSIGNED_W = true, MIN16 = false;
     static B200Q_HD int  act_word(int u, int g) { return u * 16 + g * 8; }
     static B200Q_HD int  act_blk(int u, int g) { return u * 2 + g; }
     template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[16], float (&ws)[2], float (&wm)[2]) {
@@ -364,7 +364,7 @@ template <> struct Unit<T_Q5_K> {
 template <> struct Unit<T_Q6_K> {
     // unit u = (super-block sb, half n, 16-lane half h): elements 256 sb + 128 n + 32 quad + 16 h + [0,16), quad = 0..3
     static constexpr int  ELEMS = 64, NG = 4, GW = 4;
-    static constexpr bool UNSIGNED_W = false;
+    static constexpr bool UNSIGNED_W = false, MIN16 = false;
     static B200Q_HD int  elem0(int u, int g) { return (u >> 2) * 256 + ((u >> 1) & 1) * 128 + g * 32 + (u & 1) * 16; }
     static B200Q_HD int  act_word(int u, int g) { return elem0(u, g) >> 2; }
     static B200Q_HD int  act_blk(int u, int g) { return elem0(u, g) >> 5; }
@@ -398,6 +398,118 @@ template <> struct Unit<T_Q6_K> {
     }
 };
 
+// 16-entry int8 table look-up on the 8 nibbles of one word (PRMT pairs, as mxfp4_lut): kvalues_iq4nl
+B200Q_HD void iq4nl_lut(uint32_t q, uint32_t & lo, uint32_t & hi) {
+    const uint32_t t0 = 0xBFAD9881u, t1 = 0xF6EADDCFu, t2 = 0x26190D01u, t3 = 0x71594535u;
+    uint32_t       r[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const uint32_t n   = (q >> (4 * h)) & 0x0F0F0F0Fu;
+        const uint32_t sel = n & 0x07070707u;
+        const uint32_t s   = (sel & 0xF) | ((sel >> 4) & 0xF0) | ((sel >> 8) & 0xF00) | ((sel >> 12) & 0xF000);
+        const uint32_t a   = byte_perm_(t0, t1, s);  // entries 0..7
+        const uint32_t b   = byte_perm_(t2, t3, s);  // entries 8..15
+        const uint32_t m   = ((n >> 3) & 0x01010101u) * 0xFFu;
+        r[h]               = (a & ~m) | (b & m);
+    }
+    lo = r[0];
+    hi = r[1];
+}
+template <> struct Unit<T_IQ4_NL> : UnitBlock32<T_IQ4_NL, 18> {  // vec_dot_iq4_nl_q8_1, vecdotq.cuh:1124-1146
+    template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
+        const A  b = row + u * 18;
+        uint32_t w[5];
+        ldw_n<5>(b, w);  // [d | qs0 qs1] [qs2..5] [qs6..9] [qs10..13] [qs14 qs15 | next]
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            uint32_t lo, hi;
+            iq4nl_lut(funnel_r(w[i], w[i + 1], 16), lo, hi);
+            wq[i]     = (int) lo;
+            wq[4 + i] = (int) hi;
+        }
+        ws[0] = half_bits_to_float((uint16_t) (w[0] & 0xffff));
+        wm[0] = 0.0f;
+    }
+};
+template <> struct Unit<T_IQ4_XS> : UnitBlock32<T_IQ4_XS, 0> {  // vec_dot_iq4_xs_q8_1, vecdotq.cuh:1148-1171
+    // unit u = sub-block ib = u & 7 of super-block u >> 3 (136 bytes: d, scales_h, scales_l[4], qs[128])
+    template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[8], float (&ws)[1], float (&wm)[1]) {
+        const int ib = u & 7;
+        const A   b  = row + (u >> 3) * 136;
+        uint32_t  h[2];
+        ldw_n<2>(b, h);  // [d | scales_h] [scales_l x4]
+        uint32_t q[4];
+        ldw_n<4>(b + 8 + 16 * ib, q);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            uint32_t lo, hi;
+            iq4nl_lut(q[i], lo, hi);
+            wq[i]     = (int) lo;
+            wq[4 + i] = (int) hi;
+        }
+        const int ls = (int) (((h[1] >> (4 * ib)) & 0xF) | ((((h[0] >> 16) >> (2 * ib)) & 3) << 4));
+        ws[0] = half_bits_to_float((uint16_t) (h[0] & 0xffff)) * (float) (ls - 32);
+        wm[0] = 0.0f;
+    }
+};
+// q2_K / q3_K: unit u = (super-block, 128-element half n, 16-byte half h) like q6_K: 16 bytes of 2-bit fields are four groups
+// (shift 2 g) of 16 elements 256 sb + 128 n + 32 g + 16 h + [0, 16), each with its own scale (vec_dot_q2_K_q8_1
+// vecdotq.cuh:268-311, vec_dot_q3_K_q8_1 :313-404)
+template <> struct Unit<T_Q2_K> {
+    static constexpr int  ELEMS = 64, NG = 4, GW = 4;
+    static constexpr bool UNSIGNED_W = true, MIN16 = true;  // the min of a group multiplies the sum of ITS 16 activations
+    static B200Q_HD int  elem0(int u, int g) { return (u >> 2) * 256 + ((u >> 1) & 1) * 128 + g * 32 + (u & 1) * 16; }
+    static B200Q_HD int  act_word(int u, int g) { return elem0(u, g) >> 2; }
+    static B200Q_HD int  act_blk(int u, int g) { return elem0(u, g) >> 5; }
+    template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[16], float (&ws)[4], float (&wm)[4]) {
+        const int n = (u >> 1) & 1, h = u & 1;
+        const A   b = row + (u >> 2) * 84;
+        uint32_t  q[4];
+        ldw_n<4>(b + 16 + 32 * n + 16 * h, q);
+        const uint32_t s0 = ldw(b + 8 * n), s1 = ldw(b + 8 * n + 4);  // scales[8n + 0..3], [8n + 4..7]
+        const uint32_t dm = ldw(b + 80);
+        const float    d = half_bits_to_float((uint16_t) (dm & 0xffff)), dmin = half_bits_to_float((uint16_t) (dm >> 16));
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) wq[4 * g + i] = (int) ((q[i] >> (2 * g)) & 0x03030303u);
+            const uint32_t sc = ((g < 2 ? s0 : s1) >> (16 * (g & 1) + 8 * h)) & 0xff;  // scales[8n + 2g + h]
+            ws[g] = d * (float) (sc & 0xF);
+            wm[g] = -dmin * (float) (sc >> 4);
+        }
+    }
+};
+template <> struct Unit<T_Q3_K> {
+    static constexpr int  ELEMS = 64, NG = 4, GW = 4;
+    static constexpr bool UNSIGNED_W = false, MIN16 = false;
+    static B200Q_HD int  elem0(int u, int g) { return (u >> 2) * 256 + ((u >> 1) & 1) * 128 + g * 32 + (u & 1) * 16; }
+    static B200Q_HD int  act_word(int u, int g) { return elem0(u, g) >> 2; }
+    static B200Q_HD int  act_blk(int u, int g) { return elem0(u, g) >> 5; }
+    template <class A> static B200Q_HD void decode(A row, int u, int (&wq)[16], float (&ws)[4], float (&wm)[4]) {
+        const int n = (u >> 1) & 1, h = u & 1;
+        const A   b = row + (u >> 2) * 110;
+        uint32_t  q[4], hm[4], sc[3];
+        ldw_n<4>(b + 32 + 32 * n + 16 * h, q);
+        ldw_n<4>(b + 16 * h, hm);
+        ldw_n<3>(b + 96, sc);  // 12 packed scale bytes
+        const float d = half_bits_to_float((uint16_t) (ldw(b + 108) & 0xffff));
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const uint32_t v = ((q[i] >> (2 * g)) & 0x03030303u) | (((hm[i] >> (4 * n + g)) & 0x01010101u) << 2);
+                wq[4 * g + i]    = (int) vsub4_(v, 0x04040404u);  // (q & 3) - (high bit set ? 0 : 4)
+            }
+            const int      j  = 8 * n + 2 * g + h;                // scale index
+            const uint32_t lw = sc[(j & 7) >> 2] >> (8 * (j & 3));
+            const int      lo = (int) (j < 8 ? (lw & 0xF) : ((lw >> 4) & 0xF));
+            const int      hi = (int) ((sc[2] >> (8 * (j & 3) + 2 * (j >> 2))) & 3);
+            ws[g] = d * (float) ((lo | (hi << 4)) - 32);
+            wm[g] = 0.0f;
+        }
+    }
+};
+
 // acc += sum over groups of  ws*d_x*dot + wm*s_x   against one activation column held as
 // int8x4 words `qa` and (d, s) pairs `ds`
 template <int T> B200Q_HD float unit_dot(const int (&wq)[Unit<T>::NG * Unit<T>::GW], const float (&ws)[Unit<T>::NG],
@@ -412,7 +524,13 @@ template <int T> B200Q_HD float unit_dot(const int (&wq)[Unit<T>::NG * Unit<T>::
         for (int i = 0; i < U::GW; ++i) {
             sumi = U::UNSIGNED_W ? dp4a_us((uint32_t) wq[g * U::GW + i], a[i], sumi) : dp4a_(wq[g * U::GW + i], a[i], sumi);
         }
-        const float2 x = ds[U::act_blk(u, g)];
+        float2 x = ds[U::act_blk(u, g)];
+        if (U::MIN16) {
+            int asum = 0;
+#pragma unroll
+            for (int i = 0; i < U::GW; ++i) asum = dp4a_(0x01010101, a[i], asum);
+            x.y = x.x * (float) asum;
+        }
         acc += ws[g] * (x.x * (float) sumi) + wm[g] * x.y;
     }
     return acc;

@@ -19,10 +19,12 @@
 #include "../../include/b200q.h"
 #include "../../include/ggml-b200.h"
 
+#include <array>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -42,11 +44,20 @@ namespace {
 constexpr size_t TENSOR_ALIGNMENT = 128;
 constexpr size_t BUFFER_SLACK     = 256;  // the kernels' 16-byte aligned bulk windows may over-read up to 15 bytes
 
+constexpr int    MAX_DEVICES  = 16;           // length of the tensor_split array llama passes (GGML_CUDA_MAX_DEVICES)
+constexpr size_t STAGE_BYTES  = 16u << 20;    // pinned staging buffers of the load path (two per device)
+constexpr size_t STAGE_MIN    = 1u << 20;     // uploads below this go straight through cudaMemcpyAsync
+constexpr int64_t SPLIT_ROUNDING = 128;       // row-split boundaries are multiples of the tensor-core kernel's row tile
+                                              // (the reference rounds to its mmq_y, ggml-cuda.cu:760-771)
+
 struct b200_device_ctx {
     int         device;       // CUDA ordinal
+    int         index;        // position in the registry (what tensor_split is indexed by)
     std::string name;         // "B2000", "B2001", ... (what `test-backend-ops -b` matches)
     std::string description;  // "NVIDIA B200"
     void *      xfer_stream = nullptr;  // stream for the synchronous buffer operations
+    void *      stage[2]    = { nullptr, nullptr };  // pinned staging buffers (load path)
+    void *      stage_ev[2] = { nullptr, nullptr };
     std::mutex  mu;
 };
 
@@ -55,12 +66,25 @@ struct b200_buffer_ctx {
     void * base;
 };
 
+// what a backend (a stream on the main device) keeps on ANOTHER device for row-split matmuls
+struct b200_split_peer {
+    void * stream    = nullptr;
+    void * done      = nullptr;  // event: this device's slice of dst has been stored into the main device's memory
+    void * act       = nullptr;  // local copy of the activations
+    size_t act_bytes = 0;
+    void * workspace = nullptr;
+    size_t ws_bytes  = 0;
+};
+
 struct b200_backend_ctx {
     int         device;
     std::string name;
     void *      stream    = nullptr;
     void *      workspace = nullptr;
     size_t      ws_bytes  = 0;
+    void *      copy_event = nullptr;            // cpy_tensor_async between two backends
+    void *      split_start = nullptr;           // event: the activations of a row-split matmul are ready on this stream
+    b200_split_peer peers[MAX_DEVICES];          // indexed by registry device index
 };
 
 void * device_xfer_stream(b200_device_ctx * d) {
@@ -94,12 +118,43 @@ void buffer_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, ui
     B200_CHECK(b200q_memset((char *) tensor->data + offset, value, size, s));
     B200_CHECK(b200q_stream_synchronize(s));
 }
-void buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
-    b200_device_ctx * d = buffer_device(buffer);
-    void *            s = device_xfer_stream(d);
+// host -> device upload of the load path (the reference's set_tensor is one synchronous cudaMemcpyAsync per
+// tensor from pageable memory, ggml-cuda.cu:601-607): large pageable sources (the mmap'ed GGUF) are cut into 16 MiB pieces
+// that alternate between two pinned staging buffers, so the host-side memcpy of piece i + 1 overlaps the DMA of piece i
+void upload(b200_device_ctx * d, void * dst, const void * src, size_t size) {
+    void * s = device_xfer_stream(d);
     B200_CHECK(b200q_set_device(d->device));
-    B200_CHECK(b200q_memcpy((char *) tensor->data + offset, data, size, B200Q_H2D, s));
+    static const bool no_stage = getenv("GGML_B200_NO_STAGING") != nullptr;
+    if (size < STAGE_MIN || no_stage) {
+        B200_CHECK(b200q_memcpy(dst, src, size, B200Q_H2D, s));
+        B200_CHECK(b200q_stream_synchronize(s));
+        return;
+    }
+    std::lock_guard<std::mutex> lk(d->mu);
+    for (int i = 0; i < 2; ++i) {
+        if (!d->stage[i]) {
+            if (b200q_host_alloc(&d->stage[i], STAGE_BYTES) != 0 || b200q_event_create(&d->stage_ev[i]) != 0) {
+                d->stage[i] = nullptr;  // no pinned memory: plain copy
+                B200_CHECK(b200q_memcpy(dst, src, size, B200Q_H2D, s));
+                B200_CHECK(b200q_stream_synchronize(s));
+                return;
+            }
+        }
+    }
+    size_t off = 0;
+    for (int i = 0; off < size; i ^= 1) {
+        const size_t n = size - off < STAGE_BYTES ? size - off : STAGE_BYTES;
+        B200_CHECK(b200q_event_synchronize(d->stage_ev[i]));  // the DMA that last read this staging buffer is done
+        memcpy(d->stage[i], (const char *) src + off, n);
+        B200_CHECK(b200q_memcpy((char *) dst + off, d->stage[i], n, B200Q_H2D, s));
+        B200_CHECK(b200q_event_record(d->stage_ev[i], s));
+        off += n;
+    }
     B200_CHECK(b200q_stream_synchronize(s));
+}
+
+void buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
+    upload(buffer_device(buffer), (char *) tensor->data + offset, data, size);
 }
 void buffer_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * tensor, void * data, size_t offset, size_t size) {
     b200_device_ctx * d = buffer_device(buffer);
@@ -175,6 +230,207 @@ const ggml_backend_buffer_type_i buft_iface = {
     /* .is_host        = */ buft_is_host,
 };
 
+// ------------------------------------------------------------------------------- registry (forward decls)
+struct b200_device;
+int               registry_device_count();
+b200_device_ctx * registry_device_ctx(int index);
+ggml_backend_dev_t registry_device(int index);
+
+// ------------------------------------------------------------------------------------- split buffer type
+// Row split behind the plugin (the reference's `-sm row`: ggml_backend_cuda_split_buffer_type, ggml-cuda.cu:794-1089,
+// looked up by llama through get_proc_address, src/llama-model.cpp:366-393).  A weight matrix allocated in this buffer
+// type is cut by rows over the devices — device i owns rows [round128(m * split[i]), round128(m * split[i + 1])), split
+// = cumulative normalised tensor_split, the last device takes the remainder (get_row_split, :773-786) — and every slice
+// is uploaded to its own device by set_tensor.  MUL_MAT on such a weight runs from ONE process (compute_mul_mat_split).
+struct b200_split_buft_ctx {
+    int                            main_device;  // registry index
+    std::array<float, MAX_DEVICES> split;        // cumulative fractions
+    std::string                    name;
+};
+struct b200_split_tensor {  // tensor->extra
+    void *  data[MAX_DEVICES]     = {};
+    int64_t row_low[MAX_DEVICES]  = {};
+    int64_t row_high[MAX_DEVICES] = {};
+};
+struct b200_split_buffer_ctx {
+    std::vector<b200_split_tensor *> tensors;
+};
+
+void split_rows(const b200_split_buft_ctx * bc, int64_t nrows, int id, int64_t * lo, int64_t * hi) {
+    const int n = registry_device_count();
+    *lo = id == 0 ? 0 : (int64_t) (nrows * bc->split[id]);
+    *lo -= *lo % SPLIT_ROUNDING;
+    if (id == n - 1) {
+        *hi = nrows;
+    } else {
+        *hi = (int64_t) (nrows * bc->split[id + 1]);
+        *hi -= *hi % SPLIT_ROUNDING;
+    }
+    if (id >= n) *lo = *hi = nrows;
+}
+
+const char * split_buft_get_name(ggml_backend_buffer_type_t buft) { return ((b200_split_buft_ctx *) buft->context)->name.c_str(); }
+bool buft_is_split(ggml_backend_buffer_type_t buft) { return buft->iface.get_name == split_buft_get_name; }
+
+void split_buffer_free(ggml_backend_buffer_t buffer) {
+    auto * ctx = (b200_split_buffer_ctx *) buffer->context;
+    for (b200_split_tensor * t : ctx->tensors) {
+        for (int id = 0; id < registry_device_count(); ++id) {
+            if (t->data[id]) {
+                b200q_set_device(registry_device_ctx(id)->device);
+                b200q_free(t->data[id]);
+            }
+        }
+        delete t;
+    }
+    delete ctx;
+}
+void * split_buffer_get_base(ggml_backend_buffer_t) { return (void *) 0x1000; }  // never dereferenced (as in the reference, :857-862)
+
+ggml_status split_buffer_init_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor) {
+    GGML_ASSERT(tensor->view_src == nullptr);  // views of split tensors are not supported
+    GGML_ASSERT(ggml_is_contiguous(tensor) && "split buffers only supported for contiguous tensors");
+    auto * ctx = (b200_split_buffer_ctx *) buffer->context;
+    auto * bc  = (b200_split_buft_ctx *) buffer->buft->context;
+    auto * ext = new b200_split_tensor;
+    ctx->tensors.push_back(ext);
+    const size_t row_bytes = ggml_row_size(tensor->type, tensor->ne[0]);
+    for (int id = 0; id < registry_device_count(); ++id) {
+        split_rows(bc, ggml_nrows(tensor), id, &ext->row_low[id], &ext->row_high[id]);
+        const int64_t nr = ext->row_high[id] - ext->row_low[id];
+        if (nr <= 0) continue;
+        B200_CHECK(b200q_set_device(registry_device_ctx(id)->device));
+        if (b200q_malloc(&ext->data[id], (size_t) nr * row_bytes + BUFFER_SLACK) != 0) {
+            fprintf(stderr, "ggml-b200: split slice of %s on device %d: %s\n", tensor->name, id, b200q_last_error());
+            return GGML_STATUS_ALLOC_FAILED;
+        }
+    }
+    tensor->extra = ext;
+    return GGML_STATUS_SUCCESS;
+}
+void upload(b200_device_ctx * d, void * dst, const void * src, size_t size);
+void split_buffer_set_tensor(ggml_backend_buffer_t, ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
+    GGML_ASSERT(offset == 0 && size == ggml_nbytes(tensor));  // split tensors are set in one piece (:883-887)
+    auto *       ext       = (b200_split_tensor *) tensor->extra;
+    const size_t row_bytes = ggml_row_size(tensor->type, tensor->ne[0]);
+    for (int id = 0; id < registry_device_count(); ++id) {
+        if (!ext->data[id]) continue;
+        upload(registry_device_ctx(id), ext->data[id], (const char *) data + (size_t) ext->row_low[id] * row_bytes,
+               (size_t) (ext->row_high[id] - ext->row_low[id]) * row_bytes);
+    }
+}
+void split_buffer_get_tensor(ggml_backend_buffer_t, const ggml_tensor * tensor, void * data, size_t offset, size_t size) {
+    GGML_ASSERT(offset == 0 && size == ggml_nbytes(tensor));
+    auto *       ext       = (b200_split_tensor *) tensor->extra;
+    const size_t row_bytes = ggml_row_size(tensor->type, tensor->ne[0]);
+    for (int id = 0; id < registry_device_count(); ++id) {
+        if (!ext->data[id]) continue;
+        b200_device_ctx * d = registry_device_ctx(id);
+        void *            s = device_xfer_stream(d);
+        B200_CHECK(b200q_set_device(d->device));
+        B200_CHECK(b200q_memcpy((char *) data + (size_t) ext->row_low[id] * row_bytes, ext->data[id],
+                                (size_t) (ext->row_high[id] - ext->row_low[id]) * row_bytes, B200Q_D2H, s));
+        B200_CHECK(b200q_stream_synchronize(s));
+    }
+}
+void split_buffer_clear(ggml_backend_buffer_t, uint8_t) {}
+
+const ggml_backend_buffer_i split_buffer_iface = {
+    /* .free_buffer   = */ split_buffer_free,
+    /* .get_base      = */ split_buffer_get_base,
+    /* .init_tensor   = */ split_buffer_init_tensor,
+    /* .memset_tensor = */ nullptr,
+    /* .set_tensor    = */ split_buffer_set_tensor,
+    /* .get_tensor    = */ split_buffer_get_tensor,
+    /* .cpy_tensor    = */ nullptr,
+    /* .clear         = */ split_buffer_clear,
+    /* .reset         = */ nullptr,
+};
+
+ggml_backend_buffer_t split_buft_alloc_buffer(ggml_backend_buffer_type_t buft, size_t size) {
+    // the slices are allocated per tensor in init_tensor (their sizes depend on the rounding); `size` is the cumulative
+    // bound ggml-alloc enforces, as returned by get_alloc_size
+    return ggml_backend_buffer_init(buft, split_buffer_iface, new b200_split_buffer_ctx, size);
+}
+size_t split_buft_get_alignment(ggml_backend_buffer_type_t) { return TENSOR_ALIGNMENT; }
+size_t split_buft_get_alloc_size(ggml_backend_buffer_type_t buft, const ggml_tensor * tensor) {
+    auto * bc = (b200_split_buft_ctx *) buft->context;
+    GGML_ASSERT(ggml_is_contiguous(tensor) && "split buffers only supported for contiguous tensors");
+    size_t total = 0;
+    for (int id = 0; id < registry_device_count(); ++id) {
+        int64_t lo, hi;
+        split_rows(bc, ggml_nrows(tensor), id, &lo, &hi);
+        if (hi > lo) total += (size_t) (hi - lo) * ggml_row_size(tensor->type, tensor->ne[0]) + BUFFER_SLACK;
+    }
+    return total;
+}
+bool split_buft_is_host(ggml_backend_buffer_type_t) { return false; }
+
+const ggml_backend_buffer_type_i split_buft_iface = {
+    /* .get_name       = */ split_buft_get_name,
+    /* .alloc_buffer   = */ split_buft_alloc_buffer,
+    /* .get_alignment  = */ split_buft_get_alignment,
+    /* .get_max_size   = */ nullptr,
+    /* .get_alloc_size = */ split_buft_get_alloc_size,
+    /* .is_host        = */ split_buft_is_host,
+};
+
+// ggml_backend_split_buffer_type_t (ggml-backend.h:185-186): tensor_split has MAX_DEVICES entries (proportions per
+// device; all zero or NULL = equal shares)
+ggml_backend_buffer_type_t split_buffer_type(int main_device, const float * tensor_split) {
+    static std::mutex mu;
+    static std::map<std::pair<int, std::array<float, MAX_DEVICES>>, ggml_backend_buffer_type> bufts;
+    std::lock_guard<std::mutex> lk(mu);
+    const int n = registry_device_count();
+    if (main_device < 0 || main_device >= n) return nullptr;
+    std::array<float, MAX_DEVICES> cum = {};
+    float sum = 0.0f;
+    for (int i = 0; i < n && tensor_split; ++i) sum += tensor_split[i];
+    float run = 0.0f;
+    for (int i = 0; i < n; ++i) {
+        cum[i] = sum > 0.0f ? run / sum : (float) i / n;
+        if (sum > 0.0f) run += tensor_split[i];
+    }
+    for (int i = n; i < MAX_DEVICES; ++i) cum[i] = 1.0f;
+    auto key = std::make_pair(main_device, cum);
+    auto it  = bufts.find(key);
+    if (it != bufts.end()) return &it->second;
+    auto * ctx = new b200_split_buft_ctx{ main_device, cum, "B200" + std::to_string(main_device) + "_Split" };
+    ggml_backend_buffer_type buft{ split_buft_iface, registry_device(main_device), ctx };
+    return &bufts.emplace(key, buft).first->second;
+}
+
+// -------------------------------------------------------------------------------------- host buffer type
+// pinned host memory for the tensors llama keeps on the CPU side of a partially offloaded model and for its input
+// staging (ggml_backend_cuda_host_buffer_type, ggml-cuda.cu:1093-1160): the buffer behaves like a CPU buffer, only the
+// allocation differs, so asynchronous copies from it really are asynchronous
+const char * host_buft_get_name(ggml_backend_buffer_type_t) { return "B200_Host"; }
+void host_buffer_free(ggml_backend_buffer_t buffer) { b200q_host_free(buffer->context); }
+ggml_backend_buffer_t host_buft_alloc_buffer(ggml_backend_buffer_type_t buft, size_t size) {
+    void * ptr = nullptr;
+    if (getenv("GGML_B200_NO_PINNED") || b200q_host_alloc(&ptr, size) != 0 || !ptr) {
+        return ggml_backend_buft_alloc_buffer(ggml_backend_cpu_buffer_type(), size);  // pageable host memory, as the reference
+    }
+    ggml_backend_buffer_t buffer = ggml_backend_cpu_buffer_from_ptr(ptr, size);
+    buffer->buft              = buft;
+    buffer->iface.free_buffer = host_buffer_free;
+    return buffer;
+}
+size_t host_buft_get_alignment(ggml_backend_buffer_type_t) { return ggml_backend_buft_get_alignment(ggml_backend_cpu_buffer_type()); }
+bool   host_buft_is_host(ggml_backend_buffer_type_t) { return true; }
+const ggml_backend_buffer_type_i host_buft_iface = {
+    /* .get_name       = */ host_buft_get_name,
+    /* .alloc_buffer   = */ host_buft_alloc_buffer,
+    /* .get_alignment  = */ host_buft_get_alignment,
+    /* .get_max_size   = */ nullptr,
+    /* .get_alloc_size = */ nullptr,  // ggml_nbytes
+    /* .is_host        = */ host_buft_is_host,
+};
+ggml_backend_buffer_type_t host_buffer_type() {
+    static ggml_backend_buffer_type buft{ host_buft_iface, registry_device(0), nullptr };
+    return &buft;
+}
+
 // ------------------------------------------------------------------------------------------------ ops
 bool type_ok(ggml_type t) { return b200q_type_supported((int) t) != 0; }
 
@@ -182,24 +438,34 @@ bool rows_dense(const ggml_tensor * t) { return t->nb[0] == ggml_type_size(t->ty
 
 // exactly what the kernels take; anything else is declined so the scheduler keeps it on another backend
 // (north_star: no CPU fallback for supported ops; cf. the reference's rules at ggml-cuda.cu:3265-3348)
-bool supports_mul_mat(const ggml_tensor * op) {
+bool tensor_is_split(const ggml_tensor * t) { return t->buffer && buft_is_split(t->buffer->buft); }
+
+bool supports_mul_mat(const b200_device_ctx * dev, const ggml_tensor * op) {
     const ggml_tensor * a = op->src[0];
     const ggml_tensor * b = op->src[1];
     if (!type_ok(a->type) || b->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
+    if (tensor_is_split(a)) {
+        // row-split weights: plain 2-D matrices only, and the device that runs the op must own rows (ggml-cuda.cu:3270-3283)
+        if (a->ne[2] > 1 || a->ne[3] > 1 || !ggml_is_contiguous(b) || !ggml_is_contiguous(op)) return false;
+        int64_t lo, hi;
+        split_rows((const b200_split_buft_ctx *) a->buffer->buft->context, ggml_nrows(a), dev->index, &lo, &hi);
+        if (lo == hi) return false;
+    }
     if (!rows_dense(a) || !rows_dense(b) || !rows_dense(op)) return false;  // dims 1..3 may be permuted / broadcast
     if (a->ne[0] != b->ne[0] || a->ne[0] % ggml_blck_size(a->type)) return false;
     if (b->ne[2] % a->ne[2] || b->ne[3] % a->ne[3]) return false;
-    if (a->ne[0] > (1 << 17)) return false;  // one row must fit a shared-memory stage
+    if (a->ne[0] > b200q_max_k((int) a->type)) return false;  // the kernels' shared-memory plans (host-side planner probe)
     return true;
 }
 bool supports_mul_mat_id(const ggml_tensor * op) {
     const ggml_tensor * as  = op->src[0];
     const ggml_tensor * b   = op->src[1];
     const ggml_tensor * ids = op->src[2];
+    if (tensor_is_split(as)) return false;  // experts are not row-split (the reference asserts the same, ggml-cuda.cu:2094)
     if (!type_ok(as->type) || b->type != GGML_TYPE_F32 || ids->type != GGML_TYPE_I32 || op->type != GGML_TYPE_F32) return false;
     if (!rows_dense(as) || !rows_dense(b) || !rows_dense(op) || ids->nb[0] != sizeof(int32_t)) return false;
     if (as->ne[3] != 1 || b->ne[3] != 1 || ids->ne[2] != 1 || ids->ne[3] != 1) return false;
-    if (as->ne[0] % ggml_blck_size(as->type) || as->ne[0] > (1 << 17)) return false;
+    if (as->ne[0] % ggml_blck_size(as->type) || as->ne[0] > b200q_max_k((int) as->type)) return false;
     if (b->ne[1] != 1 && b->ne[1] != ids->ne[0]) return false;
     return true;
 }
@@ -211,7 +477,7 @@ bool supports_get_rows(const ggml_tensor * op) {
     return true;
 }
 
-bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
+bool device_supports_op(ggml_backend_dev_t dev, const ggml_tensor * op) {
     switch (op->op) {
         case GGML_OP_NONE:
         case GGML_OP_VIEW:
@@ -219,7 +485,7 @@ bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
         case GGML_OP_PERMUTE:
         case GGML_OP_TRANSPOSE:
             return true;  // no-ops; the harness probes every tensor of the graph (test-backend-ops.cpp:1108-1115)
-        case GGML_OP_MUL_MAT:    return supports_mul_mat(op);
+        case GGML_OP_MUL_MAT:    return supports_mul_mat((const b200_device_ctx *) dev->context, op);
         case GGML_OP_MUL_MAT_ID: return supports_mul_mat_id(op);
         case GGML_OP_GET_ROWS:   return supports_get_rows(op);
         default: return false;
@@ -245,9 +511,86 @@ uint32_t weight_flags(const ggml_tensor * w) {
     return immutable ? B200Q_FLAG_WEIGHTS_IMMUTABLE : 0;
 }
 
+void * grow(void ** buf, size_t * have, size_t need, void * stream) {
+    if (need > *have) {
+        if (*buf) {
+            B200_CHECK(b200q_stream_synchronize(stream));
+            B200_CHECK(b200q_free(*buf));
+        }
+        const size_t bytes = need + need / 4;
+        B200_CHECK(b200q_malloc(buf, bytes));
+        *have = bytes;
+    }
+    return *buf;
+}
+
+// MUL_MAT on a row-split weight, from one process (replaces ggml_cuda_op_mul_mat, ggml-cuda.cu:1436-1754, which copies
+// src1 to every device, runs the slices and gathers dst through cudaMemcpy2DAsync on the main device).  Here every other
+// device gets the activations by ONE peer copy on its own stream, runs the ordinary kernel on its rows, and the kernel's
+// epilogue stores the result rows straight into the main device's dst over NVLink (dst + row_low; the pitch is that of the
+// whole tensor) — no gather copies, no collective; an event per device joins its stream back into the backend's stream.
+int compute_mul_mat_split(b200_backend_ctx * ctx, const ggml_tensor * op) {
+    const ggml_tensor * a   = op->src[0];
+    const ggml_tensor * b   = op->src[1];
+    auto *              ext = (b200_split_tensor *) a->extra;
+    const int           n_dev = registry_device_count();
+    const size_t        act_bytes = ggml_nbytes(b);
+    int main_index = -1;
+    for (int id = 0; id < n_dev; ++id) if (registry_device_ctx(id)->device == ctx->device) main_index = id;
+    if (main_index < 0 || !ext) return B200Q_EINVAL;
+    b200q_mul_mat_args q{};
+    q.type = (int) a->type;
+    q.k = a->ne[0]; q.n = b->ne[1];
+    q.ne02 = q.ne03 = q.ne12 = q.ne13 = 1;
+    q.nb01 = ggml_row_size(a->type, a->ne[0]);
+    q.nb11 = b->nb[1];
+    q.nb1  = op->nb[1];
+    q.flags = weight_flags(a);
+    bool forked = false;
+    for (int id = 0; id < n_dev; ++id) {
+        const int64_t lo = ext->row_low[id], nr = ext->row_high[id] - lo;
+        if (nr <= 0 || id == main_index) continue;
+        b200_device_ctx * d = registry_device_ctx(id);
+        b200_split_peer & pe = ctx->peers[id];
+        if (!forked) {
+            if (!ctx->split_start) B200_CHECK(b200q_event_create(&ctx->split_start));
+            B200_CHECK(b200q_event_record(ctx->split_start, ctx->stream));
+            forked = true;
+        }
+        B200_CHECK(b200q_set_device(d->device));
+        if (!pe.stream) {
+            if (int rc = b200q_enable_peer_access(d->device, ctx->device)) return rc;  // its kernels store into the main device
+            B200_CHECK(b200q_stream_create(&pe.stream));
+            B200_CHECK(b200q_event_create(&pe.done));
+        }
+        B200_CHECK(b200q_stream_wait_event(pe.stream, ctx->split_start));
+        void * act = grow(&pe.act, &pe.act_bytes, act_bytes, pe.stream);
+        B200_CHECK(b200q_memcpy_peer(act, d->device, b->data, ctx->device, act_bytes, pe.stream));
+        q.m = nr; q.nb02 = q.nb03 = q.nb01 * nr; q.nb12 = q.nb13 = q.nb11 * q.n; q.nb2 = q.nb3 = q.nb1 * q.n;
+        const size_t need = b200q_mul_mat_workspace(&q);
+        void *       ws   = need ? grow(&pe.workspace, &pe.ws_bytes, need, pe.stream) : nullptr;
+        int rc = b200q_mul_mat(&q, ext->data[id], (const float *) act, (float *) op->data + lo, ws, pe.ws_bytes, pe.stream);
+        if (rc == 0) rc = b200q_event_record(pe.done, pe.stream);
+        B200_CHECK(b200q_set_device(ctx->device));
+        if (rc) return rc;
+    }
+    {   // this device's own rows, on the backend's stream
+        const int64_t lo = ext->row_low[main_index], nr = ext->row_high[main_index] - lo;
+        q.m = nr; q.nb02 = q.nb03 = q.nb01 * nr; q.nb12 = q.nb13 = q.nb11 * q.n; q.nb2 = q.nb3 = q.nb1 * q.n;
+        const size_t need = b200q_mul_mat_workspace(&q);
+        void *       ws   = need ? backend_workspace(ctx, need) : nullptr;
+        if (int rc = b200q_mul_mat(&q, ext->data[main_index], (const float *) b->data, (float *) op->data + lo, ws, ctx->ws_bytes, ctx->stream)) return rc;
+    }
+    for (int id = 0; id < n_dev; ++id) {
+        if (id != main_index && ext->row_high[id] > ext->row_low[id]) B200_CHECK(b200q_stream_wait_event(ctx->stream, ctx->peers[id].done));
+    }
+    return 0;
+}
+
 int compute_mul_mat(b200_backend_ctx * ctx, const ggml_tensor * op) {
     const ggml_tensor * a = op->src[0];
     const ggml_tensor * b = op->src[1];
+    if (tensor_is_split(a)) return compute_mul_mat_split(ctx, op);
     b200q_mul_mat_args  q{};
     q.type = (int) a->type;
     q.k = a->ne[0]; q.m = a->ne[1]; q.n = b->ne[1];
@@ -300,7 +643,19 @@ void backend_free(ggml_backend_t backend) {
     if (ctx->stream) {
         b200q_stream_synchronize(ctx->stream);
         if (ctx->workspace) b200q_free(ctx->workspace);
+        if (ctx->copy_event) b200q_event_destroy(ctx->copy_event);
+        if (ctx->split_start) b200q_event_destroy(ctx->split_start);
         b200q_stream_destroy(ctx->stream);
+    }
+    for (int id = 0; id < MAX_DEVICES; ++id) {
+        b200_split_peer & pe = ctx->peers[id];
+        if (!pe.stream) continue;
+        b200q_set_device(registry_device_ctx(id)->device);
+        b200q_stream_synchronize(pe.stream);
+        if (pe.act) b200q_free(pe.act);
+        if (pe.workspace) b200q_free(pe.workspace);
+        b200q_event_destroy(pe.done);
+        b200q_stream_destroy(pe.stream);
     }
     delete ctx;
     delete backend;
@@ -319,6 +674,44 @@ void backend_get_tensor_async(ggml_backend_t backend, const ggml_tensor * tensor
     auto * ctx = (b200_backend_ctx *) backend->context;
     B200_CHECK(b200q_set_device(ctx->device));
     B200_CHECK(b200q_memcpy(data, (const char *) tensor->data + offset, size, B200Q_D2H, ctx->stream));
+}
+
+bool backend_is_b200(ggml_backend_t backend);
+
+// device -> device copy between two streams of this plugin, ordered on both (the reference's semantics: copy on the source
+// stream, the destination stream waits for it; ggml-cuda.cu:2556-2605)
+bool backend_cpy_tensor_async(ggml_backend_t backend_src, ggml_backend_t backend_dst, const ggml_tensor * src, ggml_tensor * dst) {
+    if (!backend_is_b200(backend_src) || !backend_is_b200(backend_dst)) return false;
+    ggml_backend_buffer_t buf_src = src->view_src ? src->view_src->buffer : src->buffer;
+    ggml_backend_buffer_t buf_dst = dst->view_src ? dst->view_src->buffer : dst->buffer;
+    if (!buf_src || !buf_dst || !buffer_is_b200(buf_src) || !buffer_is_b200(buf_dst)) return false;
+    auto * cs = (b200_backend_ctx *) backend_src->context;
+    auto * cd = (b200_backend_ctx *) backend_dst->context;
+    if (cs->device != ((b200_buffer_ctx *) buf_src->context)->device || cd->device != ((b200_buffer_ctx *) buf_dst->context)->device) return false;
+    B200_CHECK(b200q_set_device(cs->device));
+    if (backend_src == backend_dst) {
+        B200_CHECK(b200q_memcpy(dst->data, src->data, ggml_nbytes(dst), B200Q_D2D, cs->stream));
+        return true;
+    }
+    if (cs->device == cd->device) {
+        B200_CHECK(b200q_memcpy(dst->data, src->data, ggml_nbytes(dst), B200Q_D2D, cs->stream));
+    } else {
+        B200_CHECK(b200q_memcpy_peer(dst->data, cd->device, src->data, cs->device, ggml_nbytes(dst), cs->stream));
+    }
+    if (!cs->copy_event) B200_CHECK(b200q_event_create(&cs->copy_event));
+    B200_CHECK(b200q_event_record(cs->copy_event, cs->stream));
+    B200_CHECK(b200q_set_device(cd->device));
+    B200_CHECK(b200q_stream_wait_event(cd->stream, cs->copy_event));
+    return true;
+}
+void backend_event_record(ggml_backend_t backend, ggml_backend_event_t event) {
+    auto * ctx = (b200_backend_ctx *) backend->context;
+    B200_CHECK(b200q_event_record(event->context, ctx->stream));
+}
+void backend_event_wait(ggml_backend_t backend, ggml_backend_event_t event) {
+    auto * ctx = (b200_backend_ctx *) backend->context;
+    B200_CHECK(b200q_set_device(ctx->device));
+    B200_CHECK(b200q_stream_wait_event(ctx->stream, event->context));
 }
 
 // asynchronous: kernels are enqueued on the backend's stream, the caller follows with synchronize()
@@ -358,16 +751,17 @@ const ggml_backend_i backend_iface = {
     /* .free               = */ backend_free,
     /* .set_tensor_async   = */ backend_set_tensor_async,
     /* .get_tensor_async   = */ backend_get_tensor_async,
-    /* .cpy_tensor_async   = */ nullptr,
+    /* .cpy_tensor_async   = */ backend_cpy_tensor_async,
     /* .synchronize        = */ backend_synchronize,
     /* .graph_plan_create  = */ nullptr,
     /* .graph_plan_free    = */ nullptr,
     /* .graph_plan_update  = */ nullptr,
     /* .graph_plan_compute = */ nullptr,
     /* .graph_compute      = */ backend_graph_compute,
-    /* .event_record       = */ nullptr,
-    /* .event_wait         = */ nullptr,
+    /* .event_record       = */ backend_event_record,
+    /* .event_wait         = */ backend_event_wait,
 };
+bool backend_is_b200(ggml_backend_t backend) { return backend && backend->iface.get_name == backend_get_name; }
 
 ggml_guid_t backend_guid() {
     static ggml_guid guid = { 0xb2, 0x00, 0x71, 0x5e, 0x10, 0x0a, 0x4c, 0x0d, 0x9e, 0x51, 0x67, 0x67, 0x6d, 0x6c, 0x62, 0x32 };
@@ -394,7 +788,7 @@ void device_get_props(ggml_backend_dev_t dev, ggml_backend_dev_props * props) {
     props->description = device_get_description(dev);
     props->type        = device_get_type(dev);
     device_get_memory(dev, &props->memory_free, &props->memory_total);
-    props->caps = { /* async */ true, /* host_buffer */ false, /* buffer_from_host_ptr */ false, /* events */ false };
+    props->caps = { /* async */ true, /* host_buffer */ true, /* buffer_from_host_ptr */ false, /* events */ true };
 }
 ggml_backend_t device_init_backend(ggml_backend_dev_t dev, const char *) {
     auto * d   = (b200_device_ctx *) dev->context;
@@ -410,8 +804,21 @@ ggml_backend_buffer_type_t device_get_buffer_type(ggml_backend_dev_t dev) {
     return &((b200_device *) ((char *) dev - offsetof(b200_device, dev)))->buft;
 }
 bool device_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) {
-    return buft->iface.get_name == buft_get_name && buft->device == dev;
+    // its own device memory, or a split buffer whose main device it is (ggml-cuda.cu:3550-3556)
+    return (buft->iface.get_name == buft_get_name || buft_is_split(buft)) && buft->device == dev;
 }
+ggml_backend_buffer_type_t device_get_host_buffer_type(ggml_backend_dev_t) { return host_buffer_type(); }
+ggml_backend_event_t device_event_new(ggml_backend_dev_t dev) {
+    auto * d = (b200_device_ctx *) dev->context;
+    void * e = nullptr;
+    if (b200q_set_device(d->device) != 0 || b200q_event_create(&e) != 0) return nullptr;
+    return new ggml_backend_event{ dev, e };
+}
+void device_event_free(ggml_backend_dev_t, ggml_backend_event_t event) {
+    b200q_event_destroy(event->context);
+    delete event;
+}
+void device_event_synchronize(ggml_backend_dev_t, ggml_backend_event_t event) { B200_CHECK(b200q_event_synchronize(event->context)); }
 bool device_offload_op(ggml_backend_dev_t, const ggml_tensor * op) {
     // weights living in host memory are worth shipping to the device for batches, as in the reference
     // (ggml-cuda.cu offload_op: batch >= 32)
@@ -427,14 +834,14 @@ const ggml_backend_device_i device_iface = {
     /* .get_props            = */ device_get_props,
     /* .init_backend         = */ device_init_backend,
     /* .get_buffer_type      = */ device_get_buffer_type,
-    /* .get_host_buffer_type = */ nullptr,
+    /* .get_host_buffer_type = */ device_get_host_buffer_type,
     /* .buffer_from_host_ptr = */ nullptr,
     /* .supports_op          = */ device_supports_op,
     /* .supports_buft        = */ device_supports_buft,
     /* .offload_op           = */ device_offload_op,
-    /* .event_new            = */ nullptr,
-    /* .event_free           = */ nullptr,
-    /* .event_synchronize    = */ nullptr,
+    /* .event_new            = */ device_event_new,
+    /* .event_free           = */ device_event_free,
+    /* .event_synchronize    = */ device_event_synchronize,
 };
 
 // ------------------------------------------------------------------------------------------------ registry
@@ -457,6 +864,7 @@ ggml_backend_feature * get_features(ggml_backend_reg_t) {
 }
 void * reg_get_proc_address(ggml_backend_reg_t, const char * name) {
     if (strcmp(name, "ggml_backend_get_features") == 0) return (void *) get_features;
+    if (strcmp(name, "ggml_backend_split_buffer_type") == 0) return (void *) split_buffer_type;  // llama's -sm row
     return nullptr;
 }
 
@@ -466,6 +874,11 @@ const ggml_backend_reg_i reg_iface = {
     /* .get_device       = */ reg_get_device,
     /* .get_proc_address = */ reg_get_proc_address,
 };
+
+b200_reg_ctx * g_reg_ctx = nullptr;
+int               registry_device_count() { return g_reg_ctx ? (int) g_reg_ctx->devices.size() : 0; }
+b200_device_ctx * registry_device_ctx(int index) { return &g_reg_ctx->devices[index]->ctx; }
+ggml_backend_dev_t registry_device(int index) { return &g_reg_ctx->devices[index]->dev; }
 
 int count_blackwell_devices(std::vector<int> * ordinals) {
     int n = b200q_device_count(), found = 0;
@@ -496,6 +909,7 @@ ggml_backend_reg_t ggml_backend_b200_reg(void) {
         for (size_t i = 0; i < ordinals.size(); ++i) {
             auto * d            = new b200_device;
             d->ctx.device       = ordinals[i];
+            d->ctx.index        = (int) i;
             d->ctx.name         = "B200" + std::to_string(i);
             char name[128]      = "B200";
             b200q_device_info(ordinals[i], name, sizeof(name), nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
@@ -504,6 +918,7 @@ ggml_backend_reg_t ggml_backend_b200_reg(void) {
             d->buft             = ggml_backend_buffer_type{ buft_iface, &d->dev, nullptr };
             ctx->devices.push_back(d);
         }
+        g_reg_ctx   = ctx;
         reg         = ggml_backend_reg{ GGML_BACKEND_API_VERSION, reg_iface, ctx };
         initialised = true;
     }

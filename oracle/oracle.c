@@ -73,8 +73,8 @@ static inline int nearest_int(float v) { return (int) (f2u(v + 12582912.f) & 0x0
 int orc_blck_size(int t) {
     switch (t) {
         case ORC_F32: return 1;
-        case ORC_Q4_0: case ORC_Q4_1: case ORC_Q5_0: case ORC_Q5_1: case ORC_Q8_0: case ORC_Q8_1: case ORC_MXFP4: return 32;
-        case ORC_Q4_K: case ORC_Q5_K: case ORC_Q6_K: case ORC_Q8_K: return 256;
+        case ORC_Q4_0: case ORC_Q4_1: case ORC_Q5_0: case ORC_Q5_1: case ORC_Q8_0: case ORC_Q8_1: case ORC_MXFP4: case ORC_IQ4_NL: return 32;
+        case ORC_Q4_K: case ORC_Q5_K: case ORC_Q6_K: case ORC_Q8_K: case ORC_Q2_K: case ORC_Q3_K: case ORC_IQ4_XS: return 256;
         default: return 0;
     }
 }
@@ -83,6 +83,7 @@ size_t orc_type_size(int t) {
         case ORC_F32: return 4;   case ORC_Q4_0: return 18;  case ORC_Q4_1: return 20;  case ORC_Q5_0: return 22;
         case ORC_Q5_1: return 24; case ORC_Q8_0: return 34;  case ORC_Q8_1: return 36;  case ORC_MXFP4: return 17;
         case ORC_Q4_K: return 144; case ORC_Q5_K: return 176; case ORC_Q6_K: return 210; case ORC_Q8_K: return 292;
+        case ORC_Q2_K: return 84; case ORC_Q3_K: return 110; case ORC_IQ4_NL: return 18; case ORC_IQ4_XS: return 136;
         default: return 0;
     }
 }
@@ -91,9 +92,9 @@ size_t orc_row_size(int t, int64_t k) { int b = orc_blck_size(t); return b ? (si
 /* vec_dot_type column of type_traits_cpu (ggml-cpu/ggml-cpu.c:196-376) */
 int orc_vec_dot_type(int t) {
     switch (t) {
-        case ORC_Q4_0: case ORC_Q5_0: case ORC_Q8_0: case ORC_MXFP4: return ORC_Q8_0;
+        case ORC_Q4_0: case ORC_Q5_0: case ORC_Q8_0: case ORC_MXFP4: case ORC_IQ4_NL: return ORC_Q8_0;
         case ORC_Q4_1: case ORC_Q5_1: return ORC_Q8_1;
-        case ORC_Q4_K: case ORC_Q5_K: case ORC_Q6_K: return ORC_Q8_K;
+        case ORC_Q4_K: case ORC_Q5_K: case ORC_Q6_K: case ORC_Q2_K: case ORC_Q3_K: case ORC_IQ4_XS: return ORC_Q8_K;
         default: return -1;
     }
 }
@@ -122,6 +123,40 @@ static inline int q6k_code(const uint8_t * b, int i) {
 static inline int q6k_scale(const uint8_t * b, int i) {
     const int n = i >> 7, quad = (i >> 5) & 3, l = i & 31;
     return (int8_t) b[192 + 8 * n + 2 * quad + (l >> 4)];
+}
+
+/* kvalues_iq4nl (ggml-common.h:1088-1090) */
+static const int8_t IQ4NL_CODE[16] = { -127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113 };
+
+/* the 16 six-bit scales of a q3_K super-block, re-centred: the aux[] shuffle of ggml-quants.c:1147-1152 */
+static void q3k_scales(const uint8_t * sc12, int8_t out[16]) {
+    uint32_t aux[4];
+    memcpy(aux, sc12, 12);
+    const uint32_t kmask1 = 0x03030303u, kmask2 = 0x0f0f0f0fu, tmp = aux[2];
+    aux[2] = ((aux[0] >> 4) & kmask2) | (((tmp >> 4) & kmask1) << 4);
+    aux[3] = ((aux[1] >> 4) & kmask2) | (((tmp >> 6) & kmask1) << 4);
+    aux[0] = (aux[0] & kmask2) | (((tmp >> 0) & kmask1) << 4);
+    aux[1] = (aux[1] & kmask2) | (((tmp >> 2) & kmask1) << 4);
+    memcpy(out, aux, 16);
+    for (int j = 0; j < 16; ++j) out[j] = (int8_t) (out[j] - 32);
+}
+/* integer code of element i (0..255) of a q2_K (qs at +16) / q3_K (qs at +32, hmask at +0) super-block and the index of
+ * its 16-element scale: elements come in the order (128-half n, shift j, 16-byte half h, l), ggml-quants.c:797-811 */
+static inline int k23_pos(int i, int * is, int * byte, int * shift) {
+    const int n = i >> 7, j = (i >> 5) & 3, h = (i >> 4) & 1, l = i & 15;
+    *is = 8 * n + 2 * j + h; *byte = 32 * n + 16 * h + l; *shift = 2 * j;
+    return 4 * n + j;  /* bit of hmask */
+}
+static inline int q2k_code(const uint8_t * b, int i, int * is) {
+    int byte, shift; k23_pos(i, is, &byte, &shift);
+    return (b[16 + byte] >> shift) & 3;
+}
+static inline int q3k_code(const uint8_t * b, int i, int * is) {
+    int byte, shift; const int hb = k23_pos(i, is, &byte, &shift);
+    return ((b[32 + byte] >> shift) & 3) - (((b[byte & 31] >> hb) & 1) ? 0 : 4);
+}
+static inline int iq4xs_scale(const uint8_t * b, int ib) {  /* :2541 */
+    return (((b[4 + ib / 2] >> (4 * (ib % 2))) & 0xf) | (((rd16(b + 2) >> (2 * ib)) & 3) << 4)) - 32;
 }
 
 /* ------------------------------------------------------------------------------------------------ */
@@ -190,6 +225,40 @@ int orc_dequantize_row(int t, const void * vsrc, float * y, int64_t k) {
                         int           q    = (sb & 1) ? (byte >> 4) : (byte & 15);
                         if (t == ORC_Q5_K && ((qh[l] >> sb) & 1)) q += 16;
                         y[32 * sb + l] = dl * (float) q - ml;
+                    }
+                }
+            } break;
+            case ORC_Q2_K: {  /* :784-814 */
+                const float d = rdh(b + 80), mn = rdh(b + 82);
+                for (int i = 0; i < 256; ++i) {
+                    int is; const int q = q2k_code(b, i, &is);
+                    const float dl = d * (float) (b[is] & 0xF), ml = mn * (float) (b[is] >> 4);
+                    y[i] = dl * (float) q - ml;
+                }
+            } break;
+            case ORC_Q3_K: {  /* :1128-1176 */
+                int8_t sc[16]; q3k_scales(b + 96, sc);
+                const float d = rdh(b + 108);
+                for (int i = 0; i < 256; ++i) {
+                    int is; const int q = q3k_code(b, i, &is);
+                    const float dl = d * (float) sc[is];
+                    y[i] = dl * (float) q;
+                }
+            } break;
+            case ORC_IQ4_NL: {  /* :2512-2528 */
+                const float d = rdh(b);
+                for (int j = 0; j < 16; ++j) {
+                    y[j]      = d * (float) IQ4NL_CODE[b[2 + j] & 0xf];
+                    y[j + 16] = d * (float) IQ4NL_CODE[b[2 + j] >> 4];
+                }
+            } break;
+            case ORC_IQ4_XS: {  /* :2530-2550 */
+                const float d = rdh(b);
+                for (int ib = 0; ib < 8; ++ib) {
+                    const float dl = d * (float) iq4xs_scale(b, ib);
+                    for (int j = 0; j < 16; ++j) {
+                        y[32 * ib + j]      = dl * (float) IQ4NL_CODE[b[8 + 16 * ib + j] & 0xf];
+                        y[32 * ib + j + 16] = dl * (float) IQ4NL_CODE[b[8 + 16 * ib + j] >> 4];
                     }
                 }
             } break;
@@ -295,6 +364,7 @@ static int code32(int t, const uint8_t * b, int j) {  /* integer weight code of 
                          return (j < 16 ? (b[8 + j] & 15) : (b[8 + j - 16] >> 4)) | q5_high(qh, j); }
         case ORC_Q8_0: return (int8_t) b[2 + j];
         case ORC_MXFP4: return MXFP4_CODE[j < 16 ? (b[1 + j] & 15) : (b[1 + j - 16] >> 4)];
+        case ORC_IQ4_NL: return IQ4NL_CODE[j < 16 ? (b[2 + j] & 15) : (b[2 + j - 16] >> 4)];
         default: return 0;
     }
 }
@@ -323,6 +393,7 @@ int orc_vec_dot(int t, int64_t k, const void * vw, const void * va, float * out)
                 case ORC_Q4_0:  sumf += (float) sumi * rdh(wb) * dy; break;                    /* :146 */
                 case ORC_Q8_0:  sumf += (float) sumi * (rdh(wb) * dy); break;                  /* :329 */
                 case ORC_Q5_0:  sumf += (rdh(wb) * dy) * (float) sumi; break;                  /* :257 */
+                case ORC_IQ4_NL: sumf += (dy * rdh(wb)) * (float) sumi; break;                 /* :1126-1133 */
                 case ORC_MXFP4: sumf += (dy * e8m0_half(wb[0])) * (float) sumi; break;        /* :204-214 */
                 case ORC_Q4_1: case ORC_Q5_1:
                     sumf += (rdh(wb) * dy) * (float) sumi + rdh(wb + 2) * rdh(ab + 2); break;  /* :182, :299 */
@@ -341,7 +412,29 @@ int orc_vec_dot(int t, int64_t k, const void * vw, const void * va, float * out)
         float           dy; memcpy(&dy, ab, 4);
         const int8_t *  q8 = (const int8_t *) (ab + 4);
         int32_t         acc[8] = { 0 };
-        if (t == ORC_Q6_K) {
+        if (t == ORC_Q2_K) {  /* ggml_vec_dot_q2_K_q8_K_generic, ggml-cpu/quants.c:419-469: plain integer sums, one fp32 update */
+            int16_t bsum[16]; memcpy(bsum, ab + 4 + 256, 32);
+            int     summs = 0, isum = 0;
+            for (int j = 0; j < 16; ++j) summs += bsum[j] * (wb[j] >> 4);
+            for (int i = 0; i < 256; ++i) { int is; const int q = q2k_code(wb, i, &is); isum += (wb[is] & 0xF) * (q8[i] * q); }
+            const float dall = dy * rdh(wb + 80), dmin = dy * rdh(wb + 82);
+            sumf += dall * (float) isum - dmin * (float) summs;
+        } else if (t == ORC_Q3_K) {  /* _q3_K_q8_K_generic :471-548: eight lanes like q6_K */
+            int8_t sc[16]; q3k_scales(wb + 96, sc);
+            for (int i = 0; i < 256; ++i) { int is; const int q = q3k_code(wb, i, &is); acc[i & 7] += sc[is] * (int16_t) (q8[i] * q); }
+            const float d = rdh(wb + 108) * dy;
+            for (int l = 0; l < 8; ++l) lanes[l] += d * (float) acc[l];
+        } else if (t == ORC_IQ4_XS) {  /* _iq4_xs_q8_K_generic :1137-1178: one fp32 update per 32-element sub-block */
+            const float d4d8 = rdh(wb) * dy;
+            for (int ib = 0; ib < 8; ++ib) {
+                int s1 = 0, s2 = 0;
+                for (int j = 0; j < 16; ++j) {
+                    s1 += q8[32 * ib + j] * IQ4NL_CODE[wb[8 + 16 * ib + j] & 0xf];
+                    s2 += q8[32 * ib + j + 16] * IQ4NL_CODE[wb[8 + 16 * ib + j] >> 4];
+                }
+                sumf += (d4d8 * (float) iq4xs_scale(wb, ib)) * (float) (s1 + s2);
+            }
+        } else if (t == ORC_Q6_K) {
             for (int i = 0; i < 256; ++i) acc[i & 7] += q6k_scale(wb, i) * (int16_t) (q8[i] * q6k_code(wb, i));
             const float d = rdh(wb + 208) * dy;
             for (int l = 0; l < 8; ++l) lanes[l] += d * (float) acc[l];

@@ -10,6 +10,10 @@
 //                       alloc_ctx_tensors + tensor_set + graph_compute + tensor_get
 //   pd_sched_mlp        ggml_backend_sched with [B200, CPU] (libllama's pattern, ggml-backend.cpp:852-1443): the ops the
 //                       plugin declines stay on the CPU backend, tensors cross backends through set/get/cpy
+//   pd_mul_mat_split    llama's `-sm row` (src/llama-model.cpp:366-393): the split buffer type from get_proc_address, a weight
+//                       allocated in it, MUL_MAT on the main device's backend next to the same MUL_MAT on a plain buffer
+//   pd_async_roundtrip  events, cpy_tensor_async between two backends (two streams, or two devices), the pinned host
+//                       buffer type (ggml-backend.cpp:327-376, 432-470; llama's input staging)
 #include <ggml.h>
 #include <ggml-alloc.h>
 #include <ggml-backend.h>
@@ -143,6 +147,138 @@ int pd_sched_mlp(int dev, int type, int64_t k, int64_t m, const void * w1, const
         ggml_backend_buffer_free(wbuf);
     }
     ggml_backend_free(cpu);
+    ggml_backend_free(be);
+    return rc;
+}
+
+// The same MUL_MAT twice in one graph: weights in the row-split buffer type (tensor_split: MAX 16 proportions, NULL = equal)
+// and in the device's ordinary buffer.  out_split / out_plain: [n][m] f32 each.  Returns 0 on success, 100 + i when the
+// bytes read back from the split tensor differ from w.
+int pd_mul_mat_split(int dev, const float * tensor_split, int type, int64_t m, int64_t k, const void * w, int64_t n,
+                     const float * act, float * out_split, float * out_plain) {
+    if (!g_reg) return -1;
+    typedef ggml_backend_buffer_type_t (*split_fn)(int, const float *);
+    split_fn get_split = (split_fn) ggml_backend_reg_get_proc_address(g_reg, "ggml_backend_split_buffer_type");
+    if (!get_split) return -2;
+    ggml_backend_dev_t         d     = ggml_backend_reg_dev_get(g_reg, dev);
+    ggml_backend_buffer_type_t sbuft = get_split(dev, tensor_split);
+    if (!sbuft) return -3;
+    if (!ggml_backend_dev_supports_buft(d, sbuft)) return -4;
+    ggml_backend_t be = ggml_backend_dev_init(d, nullptr);
+    if (!be) return -5;
+    int rc = 0;
+    {
+        ctx_scope sc(4), wc(4), cc(16);
+        ggml_tensor * as = ggml_new_tensor_2d(sc.ctx, (ggml_type) type, k, m);
+        ggml_tensor * ap = ggml_new_tensor_2d(wc.ctx, (ggml_type) type, k, m);
+        ggml_backend_buffer_t sbuf = ggml_backend_alloc_ctx_tensors_from_buft(sc.ctx, sbuft);
+        ggml_backend_buffer_t pbuf = ggml_backend_alloc_ctx_tensors(wc.ctx, be);
+        if (!sbuf || !pbuf) rc = -6;
+        ggml_backend_buffer_t cbuf = nullptr;
+        if (rc == 0) {
+            ggml_backend_buffer_set_usage(sbuf, GGML_BACKEND_BUFFER_USAGE_WEIGHTS);
+            ggml_backend_buffer_set_usage(pbuf, GGML_BACKEND_BUFFER_USAGE_WEIGHTS);
+            ggml_backend_tensor_set(as, w, 0, ggml_nbytes(as));
+            ggml_backend_tensor_set(ap, w, 0, ggml_nbytes(ap));
+            std::vector<uint8_t> back(ggml_nbytes(as));
+            ggml_backend_tensor_get(as, back.data(), 0, back.size());
+            if (memcmp(back.data(), w, back.size()) != 0) rc = 100;
+        }
+        if (rc == 0) {
+            ggml_tensor * b  = ggml_new_tensor_2d(cc.ctx, GGML_TYPE_F32, k, n);
+            ggml_tensor * os = ggml_mul_mat(cc.ctx, as, b);
+            ggml_tensor * op = ggml_mul_mat(cc.ctx, ap, b);
+            if (!ggml_backend_supports_op(be, os) || !ggml_backend_supports_op(be, op)) rc = -7;
+            ggml_cgraph * gf = ggml_new_graph(cc.ctx);
+            ggml_build_forward_expand(gf, os);
+            ggml_build_forward_expand(gf, op);
+            cbuf = rc == 0 ? ggml_backend_alloc_ctx_tensors(cc.ctx, be) : nullptr;
+            if (rc == 0 && !cbuf) rc = -8;
+            if (rc == 0) {
+                ggml_backend_tensor_set(b, act, 0, ggml_nbytes(b));
+                for (int rep = 0; rep < 2 && rc == 0; ++rep) {  // twice: the second pass reuses the peers' streams and buffers
+                    if (ggml_backend_graph_compute(be, gf) != GGML_STATUS_SUCCESS) rc = -9;
+                }
+                if (rc == 0) {
+                    ggml_backend_tensor_get(os, out_split, 0, ggml_nbytes(os));
+                    ggml_backend_tensor_get(op, out_plain, 0, ggml_nbytes(op));
+                }
+            }
+        }
+        if (cbuf) ggml_backend_buffer_free(cbuf);
+        if (pbuf) ggml_backend_buffer_free(pbuf);
+        if (sbuf) ggml_backend_buffer_free(sbuf);
+    }
+    ggml_backend_free(be);
+    return rc;
+}
+
+// x (host, n floats) -> pinned host buffer -> backend A (set_tensor_async) -> backend B on dev_b (cpy_tensor_async, ordered by
+// the plugin's events) -> y (get_tensor_async + an event the host waits on).  Returns 0 on success.
+int pd_async_roundtrip(int dev_a, int dev_b, const float * x, int64_t n, float * y) {
+    if (!g_reg) return -1;
+    ggml_backend_dev_t da = ggml_backend_reg_dev_get(g_reg, dev_a), db = ggml_backend_reg_dev_get(g_reg, dev_b);
+    ggml_backend_t     ba = ggml_backend_dev_init(da, nullptr), bb = ggml_backend_dev_init(db, nullptr);
+    if (!ba || !bb) return -2;
+    int rc = 0;
+    ggml_backend_buffer_type_t hbuft = ggml_backend_dev_host_buffer_type(da);
+    if (!hbuft || !ggml_backend_buft_is_host(hbuft)) rc = -3;
+    ggml_backend_dev_props props;
+    ggml_backend_dev_get_props(da, &props);
+    if (rc == 0 && (!props.caps.async || !props.caps.events || !props.caps.host_buffer)) rc = -4;
+    if (rc == 0) {
+        ctx_scope ca(2), cb(2), ch(2);
+        ggml_tensor * ta = ggml_new_tensor_1d(ca.ctx, GGML_TYPE_F32, n);
+        ggml_tensor * tb = ggml_new_tensor_1d(cb.ctx, GGML_TYPE_F32, n);
+        ggml_tensor * th = ggml_new_tensor_1d(ch.ctx, GGML_TYPE_F32, n);
+        ggml_backend_buffer_t bufa = ggml_backend_alloc_ctx_tensors(ca.ctx, ba);
+        ggml_backend_buffer_t bufb = ggml_backend_alloc_ctx_tensors(cb.ctx, bb);
+        ggml_backend_buffer_t bufh = ggml_backend_alloc_ctx_tensors_from_buft(ch.ctx, hbuft);
+        if (!bufa || !bufb || !bufh) rc = -5;
+        if (rc == 0) {
+            memcpy(th->data, x, (size_t) n * sizeof(float));  // a host buffer: tensor->data is host memory
+            ggml_backend_event_t ev = ggml_backend_event_new(db);
+            if (!ev) rc = -6;
+            if (rc == 0) {
+                ggml_backend_tensor_set_async(ba, ta, th->data, 0, ggml_nbytes(ta));
+                ggml_backend_tensor_copy_async(ba, bb, ta, tb);      // ordered after the upload on A, before the read on B
+                ggml_backend_tensor_get_async(bb, tb, y, 0, ggml_nbytes(tb));
+                ggml_backend_event_record(ev, bb);
+                ggml_backend_event_synchronize(ev);
+                // a second stream waits for the event, too (event_wait)
+                ggml_backend_event_wait(ba, ev);
+                ggml_backend_synchronize(ba);
+                ggml_backend_event_free(ev);
+            }
+        }
+        if (bufh) ggml_backend_buffer_free(bufh);
+        if (bufb) ggml_backend_buffer_free(bufb);
+        if (bufa) ggml_backend_buffer_free(bufa);
+    }
+    ggml_backend_free(bb);
+    ggml_backend_free(ba);
+    return rc;
+}
+
+// a large pageable upload (the load path's pinned double buffering) read back: returns 0 when the bytes match
+int pd_big_upload(int dev, const uint8_t * src, int64_t nbytes, uint8_t * back) {
+    if (!g_reg) return -1;
+    ggml_backend_dev_t d  = ggml_backend_reg_dev_get(g_reg, dev);
+    ggml_backend_t     be = ggml_backend_dev_init(d, nullptr);
+    if (!be) return -2;
+    int rc = 0;
+    {
+        ctx_scope c(2);
+        ggml_tensor * t = ggml_new_tensor_1d(c.ctx, GGML_TYPE_I8, nbytes);
+        ggml_backend_buffer_t buf = ggml_backend_alloc_ctx_tensors(c.ctx, be);
+        if (!buf) rc = -3;
+        if (rc == 0) {
+            ggml_backend_tensor_set(t, src, 0, (size_t) nbytes);
+            ggml_backend_tensor_get(t, back, 0, (size_t) nbytes);
+            if (memcmp(src, back, (size_t) nbytes) != 0) rc = 1;
+        }
+        if (buf) ggml_backend_buffer_free(buf);
+    }
     ggml_backend_free(be);
     return rc;
 }

@@ -10,12 +10,15 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 
 F32, Q4_0, Q4_1, Q5_0, Q5_1, Q8_0, Q8_1, Q4_K, Q5_K, Q6_K, Q8_K, MXFP4 = 0, 2, 3, 6, 7, 8, 9, 12, 13, 14, 15, 39
-WEIGHT_TYPES = [Q4_0, Q4_1, Q5_0, Q5_1, Q8_0, MXFP4, Q4_K, Q5_K, Q6_K]
+Q2_K, Q3_K, IQ4_NL, IQ4_XS = 10, 11, 20, 23
+WEIGHT_TYPES = [Q4_0, Q4_1, Q5_0, Q5_1, Q8_0, MXFP4, Q4_K, Q5_K, Q6_K, Q2_K, Q3_K, IQ4_NL, IQ4_XS]
 HEADLINE_TYPES = [Q4_0, Q8_0, MXFP4, Q4_K, Q6_K]
 NAMES = {Q4_0: "q4_0", Q4_1: "q4_1", Q5_0: "q5_0", Q5_1: "q5_1", Q8_0: "q8_0", Q8_1: "q8_1", Q4_K: "q4_K",
-         Q5_K: "q5_K", Q6_K: "q6_K", Q8_K: "q8_K", MXFP4: "mxfp4"}
+         Q5_K: "q5_K", Q6_K: "q6_K", Q8_K: "q8_K", MXFP4: "mxfp4", Q2_K: "q2_K", Q3_K: "q3_K", IQ4_NL: "iq4_nl",
+         IQ4_XS: "iq4_xs"}
 BLCK = {Q4_0: (32, 18), Q4_1: (32, 20), Q5_0: (32, 22), Q5_1: (32, 24), Q8_0: (32, 34), Q8_1: (32, 36),
-        MXFP4: (32, 17), Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210), Q8_K: (256, 292)}
+        MXFP4: (32, 17), Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210), Q8_K: (256, 292), Q2_K: (256, 84),
+        Q3_K: (256, 110), IQ4_NL: (32, 18), IQ4_XS: (256, 136)}
 
 _oracle = None
 _ref = None
@@ -119,6 +122,15 @@ def random_blocks(t, nrows, k, seed):
 
     if t in (Q4_0, Q5_0, Q8_0):
         raw[:, 0:2] = half(-0.5, 0.5)
+    elif t == IQ4_NL:
+        raw[:, 0:2] = half(-0.01, 0.01)
+    elif t == IQ4_XS:
+        raw[:, 0:2] = half(-0.001, 0.001)
+    elif t == Q2_K:
+        raw[:, 80:82] = half(0.0, 0.05)
+        raw[:, 82:84] = half(0.0, 0.05)
+    elif t == Q3_K:
+        raw[:, 108:110] = half(-0.01, 0.01)
     elif t in (Q4_1, Q5_1):
         raw[:, 0:2] = half(0.0, 0.5)
         raw[:, 2:4] = half(-1.0, 1.0)

@@ -81,6 +81,10 @@ def _driver():
                                      C.c_void_p]
         L.pd_sched_mlp.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                    C.c_void_p, C.c_void_p, C.c_void_p]
+        L.pd_mul_mat_split.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p,
+                                       C.c_void_p, C.c_void_p]
+        L.pd_async_roundtrip.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p]
+        L.pd_big_upload.argtypes = [C.c_int, C.c_void_p, C.c_int64, C.c_void_p]
         n = L.pd_load(PLUGIN.encode())
         assert n >= 1, f"ggml_backend_load({PLUGIN}) registered {n} devices"
         _pd = L
@@ -95,6 +99,7 @@ def test_inprocess_load_and_registry():
     L = _driver()
     assert L.pd_device_name(0) == b"B2000"
     assert L.pd_proc_address(b"ggml_backend_get_features")
+    assert L.pd_proc_address(b"ggml_backend_split_buffer_type")  # llama's -sm row hook (src/llama-model.cpp:372-373)
     with open("/proc/self/maps") as f:
         assert "libggml-b200.so" in f.read()
 
@@ -135,3 +140,67 @@ def test_inprocess_scheduler_with_cpu_backend():
     assert np.isfinite(y).all() and np.abs(y_cpu).max() > 0
     assert refs.nmse(y, y_cpu) <= 5e-4
     assert splits.value >= 1
+
+
+def _n_devices():
+    return _driver().pd_load(PLUGIN.encode())
+
+
+@pytest.mark.parametrize("t,m,k,n", [(refs.Q4_K, 4096, 4096, 1), (refs.Q6_K, 1024, 4096, 1), (refs.Q4_K, 1000, 1024, 5),
+                                     (refs.Q8_0, 2048, 2048, 64), (refs.Q4_K, 300, 512, 1)],
+                         ids=lambda v: refs.NAMES.get(v, str(v)) if isinstance(v, int) and v in refs.NAMES and v >= 0 else str(v))
+def test_inprocess_split_buffer_equals_plain(t, m, k, n):
+    """MUL_MAT on a weight in ggml_backend_split_buffer_type equals the same MUL_MAT on the device's plain buffer BIT FOR BIT
+    (the kernels' summation order does not depend on how the rows are distributed).  With one device the split degenerates
+    to a single slice; with >= 2 the slices live on different GPUs and the peers store their rows into the main device's
+    dst over NVLink.  300 rows: a device can end up without rows (rounding to 128)."""
+    L = _driver()
+    nd = _n_devices()
+    w = refs.make_weights(t, m, k, seed=51 + t + m)
+    act = refs.uniform_weights(n, k, seed=52)
+    for split in ([None] if nd == 1 else [None, [3.0, 1.0] + [0.0] * 14]):
+        a = np.zeros((n, m), dtype=np.float32)
+        b = np.zeros((n, m), dtype=np.float32)
+        ts = None if split is None else (C.c_float * 16)(*split)
+        rc = L.pd_mul_mat_split(0, ts, t, m, k, _p(w), n, _p(act), _p(a), _p(b))
+        assert rc == 0, rc
+        assert np.abs(b).max() > 0
+        assert a.tobytes() == b.tobytes(), (split, float(np.abs(a - b).max()))
+        want = refs.ref_mul_mat(t, w, act)[0]
+        assert refs.nmse(a, want) <= 5e-4
+
+
+def test_inprocess_split_buffer_other_main_device():
+    """main device 1: its backend runs the op, device 0 is the peer (needs 2 GPUs)"""
+    L = _driver()
+    if _n_devices() < 2:
+        pytest.skip("needs 2 GPUs")
+    t, m, k, n = refs.Q4_K, 2048, 4096, 1
+    w = refs.make_weights(t, m, k, seed=61)
+    act = refs.uniform_weights(n, k, seed=62)
+    a = np.zeros((n, m), dtype=np.float32)
+    b = np.zeros((n, m), dtype=np.float32)
+    assert L.pd_mul_mat_split(1, None, t, m, k, _p(w), n, _p(act), _p(a), _p(b)) == 0
+    assert a.tobytes() == b.tobytes()
+
+
+def test_inprocess_events_async_copies_host_buffer():
+    """pinned host buffer type -> set_tensor_async -> cpy_tensor_async to a second backend (a second GPU when there is one)
+    -> get_tensor_async + event_synchronize"""
+    L = _driver()
+    n = 1 << 20
+    x = refs.uniform_weights(1, n, seed=71).reshape(-1)
+    for dev_b in sorted({0, _n_devices() - 1}):
+        y = np.zeros(n, dtype=np.float32)
+        rc = L.pd_async_roundtrip(0, dev_b, _p(x), n, _p(y))
+        assert rc == 0, (rc, dev_b)
+        assert y.tobytes() == x.tobytes()
+
+
+def test_inprocess_staged_upload():
+    """set_tensor of 40 MB + 5 bytes from pageable memory: three pinned staging pieces, the last one ragged"""
+    L = _driver()
+    nbytes = 40 * (1 << 20) + 5
+    src = np.random.default_rng(81).integers(0, 256, nbytes, dtype=np.uint8)
+    back = np.zeros(nbytes, dtype=np.uint8)
+    assert L.pd_big_upload(0, _p(src), nbytes, _p(back)) == 0
