@@ -649,14 +649,15 @@ size_t  b200q_row_size(int type, int64_t ne0) {
     const int be = blck_elems(type);
     return be ? (size_t) (ne0 / be) * (size_t) blck_bytes(type) : 0;
 }
-int b200q_type_supported(int type) { return type != T_F32 && blck_elems(type) > 0; }
+int b200q_type_supported(int type) { return type != T_F32 && type != T_F32W && blck_elems(type) > 0; }
 // largest row length every MUL_MAT / MUL_MAT_ID shape of `type` can be served at: the last-resort kernel (gemv_stream_kernel,
 // one column, rows at an arbitrary pitch) needs the int8 activation column, its scales and two ring stages in shared
 // memory.  Host-only (device attributes when a device is present, B200's otherwise): the plugin's supports_op asks this so
 // that an op it accepts never comes back as B200Q_ENOTSUP.
 int64_t b200q_max_k(int type) {
     const int be = blck_elems(type);
-    if (!be || type == T_F32) return 0;
+    if (type == T_F32 || dense_type(type)) return 1 << 17;  // the tensor-core kernel streams k in chunks: no row-length limit
+    if (!be) return 0;
     DevInfo di = dev_info();
     if (!di.ok) { di.sms = 148; di.max_smem = 232448; }
     auto fits = [&](int64_t k) {
@@ -734,10 +735,16 @@ int b200q_get_rows(const b200q_get_rows_args * a, const void * src0, const int32
 }
 
 // ---- MUL_MAT -------------------------------------------------------------------------------------------
+// weight type as the kernels see it: f32 weights are the internal 32-value "block" type
+static int wtype(int type) { return type == T_F32 ? T_F32W : type; }
+
 static int check_mm(const b200q_mul_mat_args * a) {
     if (!a) return fail(B200Q_EINVAL, "mul_mat: null args");
-    const int be = blck_elems(a->type);
-    if (!be || a->type == T_F32) return fail(B200Q_ENOTSUP, "mul_mat: unsupported weight type %d", a->type);
+    const int be = blck_elems(wtype(a->type));
+    if (!be || a->type == T_F32W) return fail(B200Q_ENOTSUP, "mul_mat: unsupported weight type %d", a->type);
+    if (dense_type(wtype(a->type)) && a->k % 64) {
+        return fail(B200Q_ENOTSUP, "mul_mat: f16 / bf16 / f32 weights need k %% 64 == 0 (k=%lld)", (long long) a->k);
+    }
     if (a->k <= 0 || a->k % be) return fail(B200Q_EINVAL, "mul_mat: k=%lld not a positive multiple of %d", (long long) a->k, be);
     if (a->m < 0 || a->n < 0) return fail(B200Q_EINVAL, "mul_mat: negative dimension");
     if (a->ne02 <= 0 || a->ne03 <= 0 || a->ne12 <= 0 || a->ne13 <= 0 || a->ne12 % a->ne02 || a->ne13 % a->ne03) {
@@ -747,6 +754,7 @@ static int check_mm(const b200q_mul_mat_args * a) {
 }
 
 static bool use_mmq(const b200q_mul_mat_args * a) {
+    if (dense_type(wtype(a->type))) return true;  // unquantized weights: always the tensor-core kernel (no integer dot exists)
     if (a->flags & B200Q_FLAG_FORCE_GEMV) return false;
     if (a->flags & B200Q_FLAG_FORCE_MMQ) return mmq_supported(a->type, a->k);
     // from this many columns on the tensor-core kernel (dequantize to bf16 + tcgen05: ~flat in n below 64 columns) beats
@@ -778,7 +786,7 @@ int b200q_mul_mat(const b200q_mul_mat_args * a, const void * w, const float * ac
 
     if (use_mmq(a)) {
         MmqArgs q{};
-        q.type = a->type; q.k = a->k; q.m = a->m; q.n = a->n;
+        q.type = wtype(a->type); q.k = a->k; q.m = a->m; q.n = a->n;
         q.ne02 = a->ne02; q.ne03 = a->ne03; q.ne12 = a->ne12; q.ne13 = a->ne13;
         q.w_nb1 = (long long) a->nb01; q.w_nb2 = (long long) a->nb02; q.w_nb3 = (long long) a->nb03;
         q.a_nb1 = (long long) a->nb11; q.a_nb2 = (long long) a->nb12; q.a_nb3 = (long long) a->nb13;
@@ -985,6 +993,7 @@ static int mul_mat_group_impl(const b200q_mul_mat_group_args * a, const void * c
 // row is one GEMV channel
 static bool moe_use_mmq(const b200q_mul_mat_id_args * a) {
     static const long long min_rows = getenv("B200Q_MOE_MMQ_MIN") ? atoll(getenv("B200Q_MOE_MMQ_MIN")) : 32;
+    if (dense_type(wtype(a->type))) return mmq_supported(wtype(a->type), a->k) && a->n_expert <= 1024;
     return a->n_tokens * a->n_used >= min_rows && mmq_supported(a->type, a->k) && a->n_expert <= 1024;
 }
 
@@ -996,9 +1005,12 @@ size_t b200q_mul_mat_id_workspace(const b200q_mul_mat_id_args * a) {
 int b200q_mul_mat_id(const b200q_mul_mat_id_args * a, const void * as, const float * b, const int32_t * ids, float * dst,
                      void * workspace, size_t workspace_bytes, void * stream) {
     if (!a || !as || !b || !ids || !dst) return fail(B200Q_EINVAL, "mul_mat_id: null argument");
-    const int be = blck_elems(a->type);
-    if (!be || a->type == T_F32) return fail(B200Q_ENOTSUP, "mul_mat_id: unsupported weight type %d", a->type);
+    const int be = blck_elems(wtype(a->type));
+    if (!be || a->type == T_F32W) return fail(B200Q_ENOTSUP, "mul_mat_id: unsupported weight type %d", a->type);
     if (a->k <= 0 || a->k % be) return fail(B200Q_EINVAL, "mul_mat_id: bad k");
+    if (dense_type(wtype(a->type)) && !moe_use_mmq(a)) {
+        return fail(B200Q_ENOTSUP, "mul_mat_id: f16 / bf16 / f32 experts need k %% 64 == 0 and <= 1024 experts");
+    }
     if (a->b_ne1 != 1 && a->b_ne1 != a->n_used) return fail(B200Q_EINVAL, "mul_mat_id: b->ne[1] must be 1 or n_used");
     if (a->m == 0 || a->n_tokens == 0 || a->n_used == 0) return 0;
     const DevInfo & di = dev_info();
@@ -1010,7 +1022,7 @@ int b200q_mul_mat_id(const b200q_mul_mat_id_args * a, const void * as, const flo
             return fail(B200Q_EINVAL, "mul_mat_id: workspace of %zu bytes needed (b200q_mul_mat_id_workspace)", need);
         }
         MmqMoeArgs q{};
-        q.type = a->type; q.k = a->k; q.m = a->m; q.n_expert = a->n_expert; q.n_used = a->n_used; q.n_tokens = a->n_tokens;
+        q.type = wtype(a->type); q.k = a->k; q.m = a->m; q.n_expert = a->n_expert; q.n_used = a->n_used; q.n_tokens = a->n_tokens;
         q.b_bcast = a->b_ne1 == 1;
         q.w_nb1 = (long long) a->nb01; q.w_nb2 = (long long) a->nb02;
         q.a_nb1 = (long long) a->nb11; q.a_nb2 = (long long) a->nb12;

@@ -20,6 +20,9 @@ namespace b200q {
 
 enum : int {
     T_F32   = 0,
+    T_F16   = 1,     // unquantized weights take the tensor-core kernel as "blocks" of 32 plain values
+    T_BF16  = 30,
+    T_F32W  = 1000,  // internal: f32 as a MUL_MAT weight type (32 values = 128 bytes); T_F32 itself keeps block size 1
     T_Q4_0  = 2,
     T_Q4_1  = 3,
     T_Q5_0  = 6,
@@ -55,6 +58,7 @@ inline __host__ __device__ int blck_elems(int type) {
         case T_Q4_0: case T_Q4_1: case T_Q5_0: case T_Q5_1: case T_Q8_0: case T_MXFP4: case T_IQ4_NL: return 32;
         case T_Q4_K: case T_Q5_K: case T_Q6_K: case T_Q2_K: case T_Q3_K: case T_IQ4_XS: return 256;
         case T_F32: return 1;
+        case T_F16: case T_BF16: case T_F32W: return 32;
         default: return 0;
     }
 }
@@ -64,6 +68,7 @@ inline __host__ __device__ int blck_bytes(int type) {
         case T_Q8_0: return 34;  case T_MXFP4: return 17; case T_Q4_K: return 144; case T_Q5_K: return 176;
         case T_Q6_K: return 210; case T_F32: return 4;
         case T_Q2_K: return 84;  case T_Q3_K: return 110; case T_IQ4_NL: return 18; case T_IQ4_XS: return 136;
+        case T_F16: case T_BF16: return 64; case T_F32W: return 128;
         default: return 0;
     }
 }
@@ -271,6 +276,20 @@ template <> B200Q_HD float decode_elem<T_Q6_K>(const uint8_t * row, int64_t i) {
     return mul_rn(mul_rn(d, (float) sc), (float) q);
 }
 
+
+inline __host__ __device__ bool dense_type(int type) { return type == T_F16 || type == T_BF16 || type == T_F32W; }
+
+template <> B200Q_HD float decode_elem<T_F16>(const uint8_t * row, int64_t i) { return half_bits_to_float(ld_u16(row + 2 * i)); }
+template <> B200Q_HD float decode_elem<T_BF16>(const uint8_t * row, int64_t i) {
+    const uint32_t bits = (uint32_t) ld_u16(row + 2 * i) << 16;  // GGML_BF16_TO_FP32, ggml-impl.h
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(bits);
+#else
+    float f;
+    memcpy(&f, &bits, 4);
+    return f;
+#endif
+}
 
 // non-linear 4-bit code points (kvalues_iq4nl, ggml-common.h:1088-1090)
 B200Q_HD int iq4nl_value(int nib) {

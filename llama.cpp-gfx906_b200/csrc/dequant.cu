@@ -76,6 +76,8 @@ get_rows_kernel_t get_rows_kernel_for(int type) {
         case T_Q4_K:  return get_rows_kernel<T_Q4_K>;
         case T_Q5_K:  return get_rows_kernel<T_Q5_K>;
         case T_Q6_K:  return get_rows_kernel<T_Q6_K>;
+        case T_F16:   return get_rows_kernel<T_F16>;
+        case T_BF16:  return get_rows_kernel<T_BF16>;
         case T_Q2_K:  return get_rows_kernel<T_Q2_K>;
         case T_Q3_K:  return get_rows_kernel<T_Q3_K>;
         case T_IQ4_NL: return get_rows_kernel<T_IQ4_NL>;

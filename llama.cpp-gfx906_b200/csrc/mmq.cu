@@ -341,6 +341,38 @@ template <> struct Dq<T_Q6_K> {
     }
 };
 
+// unquantized weights (f16 / bf16 / f32 tensors of a model, the reference's mmvf.cu / mmf.cu / cuBLAS cases): 32 values per
+// "block", rounded to bf16 like every other operand of this kernel
+template <> struct Dq<T_F16> {
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        uint32_t w[16];
+        ldu32_n<16>(piece + b32 * 64, w);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const float2 f = __half22float2(*(const __half2 *) &w[i]);
+            v[2 * i] = f.x; v[2 * i + 1] = f.y;
+        }
+    }
+};
+template <> struct Dq<T_BF16> {
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        uint32_t w[16];
+        ldu32_n<16>(piece + b32 * 64, w);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            v[2 * i] = __uint_as_float(w[i] << 16); v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+        }
+    }
+};
+template <> struct Dq<T_F32W> {
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        uint32_t w[32];
+        ldu32_n<32>(piece + b32 * 128, w);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(w[i]);
+    }
+};
+
 extern __shared__ __align__(1024) uint8_t mmq_smem_raw[];
 
 struct TileCoord {
@@ -825,6 +857,9 @@ mmq_kernel_t mmq_kernel_for(int type) {
         case T_Q4_K:  return mmq_kernel<T_Q4_K>;
         case T_Q5_K:  return mmq_kernel<T_Q5_K>;
         case T_Q6_K:  return mmq_kernel<T_Q6_K>;
+        case T_F16:   return mmq_kernel<T_F16>;
+        case T_BF16:  return mmq_kernel<T_BF16>;
+        case T_F32W:  return mmq_kernel<T_F32W>;
         case T_Q2_K:  return mmq_kernel<T_Q2_K>;    // these four dequantize through the scalar decoders of blocks.cuh
         case T_Q3_K:  return mmq_kernel<T_Q3_K>;
         case T_IQ4_NL: return mmq_kernel<T_IQ4_NL>;
@@ -916,7 +951,7 @@ static int mmq_launch_impl(const MmqArgs & a, const MmqMoeArgs * moe, void * wor
     p.n_tiles  = pp.n_tiles;
     p.k_chunks = pp.k_chunks;
     const int be = blck_elems(a.type), bb = blck_bytes(a.type);
-    p.w_stage_k     = be == 32 ? 128 : 256;
+    p.w_stage_k     = a.type == T_F32W ? 64 : be == 32 ? 128 : 256;  // raw bytes per row and stage stay <= 256
     p.w_stages_per_tile = (int) ((a.k + p.w_stage_k - 1) / p.w_stage_k);
     p.piece_bytes   = p.w_stage_k / be * bb;
     p.blk_bytes     = be == 32 ? bb : 0;

@@ -433,6 +433,9 @@ ggml_backend_buffer_type_t host_buffer_type() {
 
 // ------------------------------------------------------------------------------------------------ ops
 bool type_ok(ggml_type t) { return b200q_type_supported((int) t) != 0; }
+// unquantized weights go through the tensor-core kernel in 64-element chunks
+bool dense_weight(ggml_type t) { return t == GGML_TYPE_F16 || t == GGML_TYPE_BF16 || t == GGML_TYPE_F32; }
+bool weight_ok(const ggml_tensor * a) { return (type_ok(a->type) || a->type == GGML_TYPE_F32) && (!dense_weight(a->type) || a->ne[0] % 64 == 0); }
 
 bool rows_dense(const ggml_tensor * t) { return t->nb[0] == ggml_type_size(t->type); }
 
@@ -443,7 +446,7 @@ bool tensor_is_split(const ggml_tensor * t) { return t->buffer && buft_is_split(
 bool supports_mul_mat(const b200_device_ctx * dev, const ggml_tensor * op) {
     const ggml_tensor * a = op->src[0];
     const ggml_tensor * b = op->src[1];
-    if (!type_ok(a->type) || b->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
+    if (!weight_ok(a) || b->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
     if (tensor_is_split(a)) {
         // row-split weights: plain 2-D matrices only, and the device that runs the op must own rows (ggml-cuda.cu:3270-3283)
         if (a->ne[2] > 1 || a->ne[3] > 1 || !ggml_is_contiguous(b) || !ggml_is_contiguous(op)) return false;
@@ -462,7 +465,7 @@ bool supports_mul_mat_id(const ggml_tensor * op) {
     const ggml_tensor * b   = op->src[1];
     const ggml_tensor * ids = op->src[2];
     if (tensor_is_split(as)) return false;  // experts are not row-split (the reference asserts the same, ggml-cuda.cu:2094)
-    if (!type_ok(as->type) || b->type != GGML_TYPE_F32 || ids->type != GGML_TYPE_I32 || op->type != GGML_TYPE_F32) return false;
+    if (!weight_ok(as) || as->ne[2] > 1024 || b->type != GGML_TYPE_F32 || ids->type != GGML_TYPE_I32 || op->type != GGML_TYPE_F32) return false;
     if (!rows_dense(as) || !rows_dense(b) || !rows_dense(op) || ids->nb[0] != sizeof(int32_t)) return false;
     if (as->ne[3] != 1 || b->ne[3] != 1 || ids->ne[2] != 1 || ids->ne[3] != 1) return false;
     if (as->ne[0] % ggml_blck_size(as->type) || as->ne[0] > b200q_max_k((int) as->type)) return false;
