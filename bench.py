@@ -595,6 +595,35 @@ def main_b200(args):
         e2e_step()
     barrier()
 
+    # ---- row split, the other dependency policy (aux): the same step without / with the per-group barrier points ----------
+    variant = None
+    if world > 1:
+        try:
+            vl = [P.make_list(b, dep=not dep_chain) for b in range(2)]
+            vn = [0]
+
+            def vstep():
+                vl[vn[0] & 1].launch()
+                vn[0] += 1
+            for _ in range(4):
+                vstep()
+            barrier()
+            kv = max(4, min(args.steps, 40)) & ~1
+            e0.record()
+            for _ in range(kv):
+                vstep()
+            e1.record()
+            barrier()
+            msv = reduce_max(e0.elapsed_time(e1)) / kv
+            variant = {("no_dependencies_upper_bound" if dep_chain else "with_dependencies"):
+                       {"ms_per_step": msv, "GB/s": P.algo / msv / 1e6, "barrier_points_per_step": vl[0].n_barrier_points,
+                        "note": "one cross-GPU barrier point per step only: nothing orders a matmul group behind the groups it would "
+                                "consume in a model" if dep_chain else "every new activation vector waits for all earlier groups on all GPUs"}}
+            del vl
+        except Exception as e:
+            variant = {"error": repr(e)}
+        barrier()
+
     # ---- second leg for row split: the 70B shapes of BASELINE configs[4] (the north star's scaling target) -----
     leg70 = None
     if os.environ.get("B200Q_BENCH_70B", "1" if world > 1 else "0") == "1" and args.workload != "llama3-70b-q4_k":
@@ -681,6 +710,8 @@ def main_b200(args):
         out["rowsplit_parity"] = rowsplit_parity
     if leg70 is not None:
         out.setdefault("aux", {})["config5_llama3_70b_rowsplit"] = leg70
+    if variant is not None:
+        out.setdefault("aux", {})["step_variants"] = variant
     if world == 1:
         aux = out.setdefault("aux", {})
         try:

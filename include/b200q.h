@@ -45,6 +45,10 @@ extern "C" {
 /* ggml_type numbers accepted as weight types */
 enum b200q_type {
     B200Q_TYPE_F32   = 0,
+    B200Q_TYPE_F16   = 1,   /* unquantized weights (k % 64 == 0) and operands of the elementwise operators */
+    B200Q_TYPE_BF16  = 30,
+    B200Q_TYPE_I32   = 26,  /* index / position tensors of the operators below */
+    B200Q_TYPE_I64   = 27,
     B200Q_TYPE_Q4_0  = 2,
     B200Q_TYPE_Q4_1  = 3,
     B200Q_TYPE_Q5_0  = 6,
@@ -250,6 +254,43 @@ B200Q_API size_t b200q_mul_mat_id_workspace(const b200q_mul_mat_id_args * a);
 B200Q_API int    b200q_mul_mat_id(const b200q_mul_mat_id_args * a, const void * as, const float * b,
                                   const int32_t * ids, float * dst, void * workspace, size_t workspace_bytes,
                                   void * stream);
+
+/* ---- the operators around the matmuls of a decoder layer: they keep a layer's graph on the device.  Each one
+ *      replaces the reference CUDA kernel named beside it (ggml/src/ggml-cuda/) and follows the arithmetic of the CPU operator
+ *      (ggml/src/ggml-cpu/ops.cpp); tensors are described ggml's way.  B200Q_ENOTSUP = layout / type the kernel does not take
+ *      (the plugin's supports_op declines exactly those). ------------------------------------------------------------------ */
+typedef struct b200q_tensor {
+    void *  data;   /* device pointer */
+    int     type;   /* b200q_type */
+    int64_t ne[4];  /* elements per dimension, ne[0] innermost */
+    size_t  nb[4];  /* byte strides */
+} b200q_tensor;
+enum { B200Q_BIN_ADD = 0, B200Q_BIN_SUB, B200Q_BIN_MUL, B200Q_BIN_DIV };
+enum { B200Q_UNARY_SILU = 0, B200Q_UNARY_GELU, B200Q_UNARY_GELU_QUICK, B200Q_UNARY_GELU_ERF, B200Q_UNARY_RELU, B200Q_UNARY_SIGMOID,
+       B200Q_UNARY_TANH, B200Q_UNARY_NEG, B200Q_UNARY_ABS, B200Q_UNARY_EXP };
+enum { B200Q_GLU_REGLU = 0, B200Q_GLU_GEGLU, B200Q_GLU_SWIGLU, B200Q_GLU_GEGLU_ERF, B200Q_GLU_GEGLU_QUICK, B200Q_GLU_SWIGLU_OAI };
+enum { B200Q_ROPE_NORMAL = 0, B200Q_ROPE_NEOX = 2 };
+typedef struct b200q_rope_params {
+    int   n_dims, mode;
+    float freq_base, freq_scale, ext_factor, attn_factor;
+    float corr_dims[2];  /* ggml_rope_yarn_corr_dims(n_dims, n_ctx_orig, freq_base, beta_fast, beta_slow) — host arithmetic */
+} b200q_rope_params;
+B200Q_API int b200q_op_rms_norm(const b200q_tensor * src, const b200q_tensor * dst, float eps, void * stream);            /* norm.cu */
+B200Q_API int b200q_op_bin(int op, const b200q_tensor * src0, const b200q_tensor * src1, const b200q_tensor * dst,
+                           void * stream);                                                                                 /* binbcast.cu */
+B200Q_API int b200q_op_scale(const b200q_tensor * src, const b200q_tensor * dst, float scale, float bias, void * stream); /* scale.cu */
+B200Q_API int b200q_op_unary(int op, const b200q_tensor * src, const b200q_tensor * dst, void * stream);                   /* unary.cu */
+/* src1 NULL: gate and value are the two halves of src0's rows (`swapped` picks the order); alpha, limit: SWIGLU_OAI only */
+B200Q_API int b200q_op_glu(int op, const b200q_tensor * src0, const b200q_tensor * src1, const b200q_tensor * dst, int swapped,
+                           float alpha, float limit, void * stream);                                                       /* unary.cu (glu) */
+/* mask (f32 | f16, broadcast over dims 2, 3) and sinks (f32 [n_head]) may be NULL */
+B200Q_API int b200q_op_soft_max(const b200q_tensor * src, const b200q_tensor * mask, const b200q_tensor * sinks,
+                                const b200q_tensor * dst, float scale, float max_bias, void * stream);                     /* softmax.cu */
+B200Q_API int b200q_op_rope(const b200q_tensor * src, const b200q_tensor * pos, const b200q_tensor * freq_factors /* or NULL */,
+                            const b200q_tensor * dst, const b200q_rope_params * p, void * stream);                         /* rope.cu */
+B200Q_API int b200q_op_cpy(const b200q_tensor * src, const b200q_tensor * dst, void * stream);       /* cpy.cu: CPY / CONT / DUP */
+B200Q_API int b200q_op_set_rows(const b200q_tensor * src, const b200q_tensor * idx, const b200q_tensor * dst,
+                                void * stream);                                                                            /* set-rows.cu */
 
 /* ---- host-buffer round trip (what a ggml caller does: tensor_set -> graph_compute -> tensor_get) --- */
 /* Weights stay resident on the device (w_dev); activations and results are HOST buffers (pinned or pageable).

@@ -517,6 +517,10 @@ bool aligned16(const void * p, long long stride) { return ((uintptr_t) p & 15) =
 }  // namespace
 
 // ======================================================================================================
+namespace b200q {
+int ops_fail(int code, const char * msg) { return fail(code, "%s", msg); }  // ops.cu reports through the same channel
+}
+
 extern "C" {
 
 int          b200q_version(void) { return 100; }

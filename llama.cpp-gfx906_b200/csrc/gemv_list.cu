@@ -12,8 +12,8 @@
 //     stream never stops at a matrix boundary, a dependency or an activation reload;
 //   * activations are quantized per CTA into one of two shared-memory images ("generations": consecutive ops that read
 //     the same vector share one) by a third warpgroup of 4 QUANTIZER warps that runs one generation ahead of the 8 compute
-//     warps (image FULL / FREE named barriers; setmaxnreg gives the compute warps 216 registers, the quantizers 72 —
-//     2 x 216 + 72 = the 3 x 168 a scheduler partition was allocated): the L2 round trips of the f32 vector and the compute
+//     warps (image FULL / FREE named barriers; setmaxnreg gives the compute warps 208 registers, the quantizers 88 —
+//     2 x 208 + 88 = the 3 x 168 a scheduler partition was allocated): the L2 round trips of the f32 vector and the compute
 //     warps' skew at a switch left the critical path (they were ~1.2 us per generation, 18 % of the 8B pass: every shape
 //     alone ran at 81-87 % of HBM, the pass at 69 %; now 87 %).  Quantizing a dependent vector with all 12 warps was tried:
 //     inlined it spills in the stage loop, out of line the call forces the 168-register ABI (both slower);
@@ -287,7 +287,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
 
     // ---- quantizer warpgroup: image g & 1 <- generation g, one generation ahead of the compute warps -------------------
     if (warp >= LIST_WARPS) {
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 88;");
         const int qw = warp - LIST_WARPS;
         for (int g = 0; g < p.n_gens; ++g) {
             const float * act;
@@ -301,7 +301,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
             named_bar_arrive(BAR_FULL + (g & 1), NTHREADS);
         }
     } else {
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
 
     // compute warps: switch to generation g (every warp takes part in every switch, with or without work in it)
     RegAct RA;

@@ -70,40 +70,58 @@ template <int NWQ = NW, class P> __device__ __forceinline__ void quantize_act(co
                 const float4 * src = (const float4 *) (act + (size_t) s * 256 + lane * 8);
                 x[b][0] = __ldcg(src);
                 x[b][1] = __ldcg(src + 1);
+            } else {
+                x[b][0] = x[b][1] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
         }
+        // the QB reductions advance in lockstep (the loop over shuffle distances is the outer one): a warp that quantizes
+        // alone on its scheduler has no other warp to hide the shuffle latency behind
+        float amax[QB];
+#pragma unroll
+        for (int b = 0; b < QB; ++b) {
+            amax[b] = fmaxf(fmaxf(fmaxf(fabsf(x[b][0].x), fabsf(x[b][0].y)), fmaxf(fabsf(x[b][0].z), fabsf(x[b][0].w))),
+                            fmaxf(fmaxf(fabsf(x[b][1].x), fabsf(x[b][1].y)), fmaxf(fabsf(x[b][1].z), fabsf(x[b][1].w))));
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+            for (int b = 0; b < QB; ++b) amax[b] = fmaxf(amax[b], __shfl_xor_sync(0xffffffffu, amax[b], o));
+        }
+        uint32_t w0[QB], w1[QB];
+        int      sum[QB];
+#pragma unroll
+        for (int b = 0; b < QB; ++b) {
+            const float v[8] = { x[b][0].x, x[b][0].y, x[b][0].z, x[b][0].w, x[b][1].x, x[b][1].y, x[b][1].z, x[b][1].w };
+            const float id   = amax[b] > 0.0f ? 127.0f / amax[b] : 0.0f;
+            int q[8];
+            sum[b] = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                q[i] = __float2int_rn(v[i] * id);
+                sum[b] += q[i];
+            }
+            w0[b] = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t) q[3] << 24);
+            w1[b] = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t) q[7] << 24);
+        }
+        int s16[QB], s32[QB];
+#pragma unroll
+        for (int b = 0; b < QB; ++b) s16[b] = sum[b] + __shfl_xor_sync(0xffffffffu, sum[b], 1);
+#pragma unroll
+        for (int b = 0; b < QB; ++b) s32[b] = s16[b] + __shfl_xor_sync(0xffffffffu, s16[b], 2);
 #pragma unroll
         for (int b = 0; b < QB; ++b) {
             const int s = s0 + b * NWQ;
             if (s >= p.nsb) break;  // warp-uniform
-            const float v[8] = { x[b][0].x, x[b][0].y, x[b][0].z, x[b][0].w, x[b][1].x, x[b][1].y, x[b][1].z, x[b][1].w };
-            float amax = 0.0f;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(v[i]));
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-            const float d  = amax * (1.0f / 127.0f);
-            const float id = amax > 0.0f ? 127.0f / amax : 0.0f;
-            int q[8], sum = 0;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                q[i] = __float2int_rn(v[i] * id);
-                sum += q[i];
-            }
-            const uint32_t w0 = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((uint32_t) q[3] << 24);
-            const uint32_t w1 = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((uint32_t) q[7] << 24);
             const uint32_t qa = sb + p.off_q + (uint32_t) (((lane >> 1) * p.nsb + s) * 16 + (lane & 1) * 8);
-            asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(qa), "r"(w0), "r"(w1) : "memory");
-            const int s16 = sum + __shfl_xor_sync(0xffffffffu, sum, 1);
-            const int s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 2);
+            asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(qa), "r"(w0[b]), "r"(w1[b]) : "memory");
             if ((lane & 1) == 0) {
-                asm volatile("st.shared.u16 [%0], %1;" ::"r"(sb + p.off_bs16 + (uint32_t) (s * 32 + (lane >> 1) * 2)), "h"((short) s16) : "memory");
+                asm volatile("st.shared.u16 [%0], %1;" ::"r"(sb + p.off_bs16 + (uint32_t) (s * 32 + (lane >> 1) * 2)), "h"((short) s16[b]) : "memory");
             }
             if ((lane & 3) == 0) {
-                asm volatile("st.shared.u16 [%0], %1;" ::"r"(sb + p.off_bs32 + (uint32_t) (s * 16 + (lane >> 2) * 2)), "h"((short) s32) : "memory");
+                asm volatile("st.shared.u16 [%0], %1;" ::"r"(sb + p.off_bs32 + (uint32_t) (s * 16 + (lane >> 2) * 2)), "h"((short) s32[b]) : "memory");
             }
             if (lane == 0) {
-                asm volatile("st.shared.f32 [%0], %1;" ::"r"(sb + p.off_dx + (uint32_t) s * 4), "f"(d) : "memory");
+                asm volatile("st.shared.f32 [%0], %1;" ::"r"(sb + p.off_dx + (uint32_t) s * 4), "f"(amax[b] * (1.0f / 127.0f)) : "memory");
             }
         }
     }

@@ -1,0 +1,462 @@
+// ops.cu — the operators that bracket the quantized matmuls in a decoder layer, so that a layer's graph does not bounce to
+// the CPU backend between them: RMS_NORM, ADD / SUB / MUL / DIV with ggml broadcasting, SCALE, the unary
+// activations, GLU (SWIGLU / GEGLU / REGLU / SWIGLU_OAI ...), SOFT_MAX (mask, ALiBi slopes, sinks), ROPE (normal / NeoX,
+// frequency factors, YaRN), CPY / CONT / DUP between f32 / f16 / bf16, SET_ROWS (the KV-cache write).
+//
+// Each kernel restates the arithmetic of the reference's CPU operator (ggml/src/ggml-cpu/ops.cpp: rms_norm :4138-4187,
+// soft_max :5218-5330, rope :6049-6330, glu :3285-3700, set_rows :5342-5400; binary-ops.cpp; unary-ops.cpp; vec.h
+// :601-700 for the activation formulas) and replaces the reference's norm.cu / binbcast.cu / scale.cu / unary.cu /
+// softmax.cu / rope.cu / cpy.cu / set-rows.cu.  All of it is HBM-bound elementwise or row work: coalesced accesses,
+// one CTA per row for the reductions, grid-stride loops sized in multiples of the SM count elsewhere; nothing here is
+// shaped into a GEMM.  Gate: NMSE <= 1e-7 against ggml-cpu (test-backend-ops' default, tests/test-backend-ops.cpp:948-950).
+#include "../../include/b200q.h"
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include <math.h>
+#include <stdint.h>
+
+namespace b200q {
+int ops_fail(int code, const char * msg);  // api.cu: records the message for b200q_last_error
+}
+using b200q::ops_fail;
+
+namespace {
+
+struct T4 {  // a tensor as a kernel sees it
+    char *    data;
+    long long ne[4];
+    long long nb[4];
+};
+T4 t4(const b200q_tensor * t) {
+    T4 r;
+    r.data = (char *) t->data;
+    for (int i = 0; i < 4; ++i) { r.ne[i] = t->ne[i]; r.nb[i] = (long long) t->nb[i]; }
+    return r;
+}
+long long nelem(const b200q_tensor * t) { return t->ne[0] * t->ne[1] * t->ne[2] * t->ne[3]; }
+long long nrows(const b200q_tensor * t) { return t->ne[1] * t->ne[2] * t->ne[3]; }
+size_t tsize(int type) { return type == B200Q_TYPE_F32 ? 4 : (type == B200Q_TYPE_F16 || type == B200Q_TYPE_BF16) ? 2 : type == B200Q_TYPE_I32 ? 4 : type == B200Q_TYPE_I64 ? 8 : 0; }
+bool contiguous(const b200q_tensor * t) {
+    size_t s = tsize(t->type);
+    if (!s) return false;
+    for (int i = 0; i < 4; ++i) {
+        if (t->ne[i] != 1 && t->nb[i] != s) return false;
+        s *= (size_t) t->ne[i];
+    }
+    return true;
+}
+bool contiguous_rows(const b200q_tensor * t) {  // ggml_is_contiguous_1: dims >= 1 dense, rows at any pitch
+    size_t s = t->nb[1];
+    if (t->nb[0] != tsize(t->type)) return false;
+    for (int i = 1; i < 4; ++i) {
+        if (t->ne[i] != 1 && t->nb[i] != s) return false;
+        s *= (size_t) t->ne[i];
+    }
+    return true;
+}
+bool same_shape(const b200q_tensor * a, const b200q_tensor * b) {
+    for (int i = 0; i < 4; ++i) if (a->ne[i] != b->ne[i]) return false;
+    return true;
+}
+int grid_for(long long n, int threads) {
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const long long want = (n + threads - 1) / threads;
+    const long long cap  = (long long) sms * 16;
+    return (int) (want < 1 ? 1 : want < cap ? want : cap);
+}
+int launched() {
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : ops_fail(B200Q_ECUDA, cudaGetErrorString(e));
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+template <bool MAX> __device__ __forceinline__ float block_reduce(float v, float * sh) {
+    v = MAX ? warp_max(v) : warp_sum(v);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = blockDim.x >> 5;
+    __syncthreads();  // sh may still be read from a previous reduction
+    if (l == 0) sh[w] = v;
+    __syncthreads();
+    v = l < nw ? sh[l] : (MAX ? -INFINITY : 0.0f);
+    return MAX ? warp_max(v) : warp_sum(v);
+}
+
+// ---- element load / store by type -----------------------------------------------------------------------------------------
+template <int TYPE> struct Elem;
+template <> struct Elem<B200Q_TYPE_F32> {
+    static __device__ __forceinline__ float ld(const char * p) { return *(const float *) p; }
+    static __device__ __forceinline__ void  st(char * p, float v) { *(float *) p = v; }
+};
+template <> struct Elem<B200Q_TYPE_F16> {
+    static __device__ __forceinline__ float ld(const char * p) { return __half2float(*(const __half *) p); }
+    static __device__ __forceinline__ void  st(char * p, float v) { *(__half *) p = __float2half_rn(v); }
+};
+template <> struct Elem<B200Q_TYPE_BF16> {
+    static __device__ __forceinline__ float ld(const char * p) { return __bfloat162float(*(const __nv_bfloat16 *) p); }
+    static __device__ __forceinline__ void  st(char * p, float v) { *(__nv_bfloat16 *) p = __float2bfloat16_rn(v); }
+};
+
+// ---- RMS_NORM: y = x / sqrt(mean(x^2) + eps), one CTA per row -------------------------------------------------------------
+__global__ void __launch_bounds__(256) rms_norm_kernel(T4 x, T4 y, float eps) {
+    __shared__ float sh[32];
+    const long long row = blockIdx.x;
+    const long long i3 = row / (x.ne[1] * x.ne[2]), i2 = (row / x.ne[1]) % x.ne[2], i1 = row % x.ne[1];
+    const float * xp = (const float *) (x.data + i1 * x.nb[1] + i2 * x.nb[2] + i3 * x.nb[3]);
+    float *       yp = (float *) (y.data + i1 * y.nb[1] + i2 * y.nb[2] + i3 * y.nb[3]);
+    const int     n  = (int) x.ne[0];
+    float s = 0.0f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const float v = xp[i];
+        s += v * v;
+    }
+    s = block_reduce<false>(s, sh);
+    const float scale = 1.0f / sqrtf(s / (float) n + eps);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) yp[i] = xp[i] * scale;
+}
+
+// ---- binary ops with ggml broadcasting: dst = src0 (op) src1, src1 repeated along every dim ---------------------------------
+template <int OP> __device__ __forceinline__ float bin_apply(float a, float b) {
+    return OP == B200Q_BIN_ADD ? a + b : OP == B200Q_BIN_SUB ? a - b : OP == B200Q_BIN_MUL ? a * b : a / b;
+}
+template <int OP> __global__ void __launch_bounds__(256) bin_kernel(T4 a, T4 b, T4 d, long long n) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
+        const long long i0 = i % d.ne[0], r = i / d.ne[0];
+        const long long i1 = r % d.ne[1], r2 = r / d.ne[1];
+        const long long i2 = r2 % d.ne[2], i3 = r2 / d.ne[2];
+        const float av = *(const float *) (a.data + i0 * a.nb[0] + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
+        const float bv = *(const float *) (b.data + (i0 % b.ne[0]) * b.nb[0] + (i1 % b.ne[1]) * b.nb[1] + (i2 % b.ne[2]) * b.nb[2] + (i3 % b.ne[3]) * b.nb[3]);
+        *(float *) (d.data + i0 * d.nb[0] + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = bin_apply<OP>(av, bv);
+    }
+}
+
+// ---- SCALE and the unary activations (contiguous f32) ---------------------------------------------------------------------
+__device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.0f + tanhf(0.79788456080286535587989211986876f * x * (1.0f + 0.044715f * x * x))); }
+__device__ __forceinline__ float gelu_quick_f(float x) { return x * (1.0f / (1.0f + expf(-1.702f * x))); }
+__device__ __forceinline__ float gelu_erf_f(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
+__device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
+__device__ __forceinline__ float unary_apply(int op, float x) {
+    switch (op) {
+        case B200Q_UNARY_SILU:       return silu_f(x);
+        case B200Q_UNARY_GELU:       return gelu_f(x);
+        case B200Q_UNARY_GELU_QUICK: return gelu_quick_f(x);
+        case B200Q_UNARY_GELU_ERF:   return gelu_erf_f(x);
+        case B200Q_UNARY_RELU:       return fmaxf(x, 0.0f);
+        case B200Q_UNARY_SIGMOID:    return 1.0f / (1.0f + expf(-x));
+        case B200Q_UNARY_TANH:       return tanhf(x);
+        case B200Q_UNARY_NEG:        return -x;
+        case B200Q_UNARY_ABS:        return fabsf(x);
+        case B200Q_UNARY_EXP:        return expf(x);
+        default:                     return x;
+    }
+}
+__global__ void __launch_bounds__(256) unary_kernel(const float * x, float * y, long long n, int op) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) y[i] = unary_apply(op, x[i]);
+}
+__global__ void __launch_bounds__(256) scale_kernel(const float * x, float * y, long long n, float s, float b) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) y[i] = x[i] * s + b;
+}
+
+// ---- GLU: dst[r][c] = act(x[r][c]) * g[r][c]; x and g are the two halves of one row or two tensors ------------------------------
+__global__ void __launch_bounds__(256) glu_kernel(const char * x, const char * g, char * d, long long nr, int nc, long long x_nb1,
+                                                  long long g_nb1, long long d_nb1, int op, float alpha, float limit) {
+    const long long n = nr * nc;
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
+        const long long r = i / nc;
+        const int       c = (int) (i - r * nc);
+        const float xv = ((const float *) (x + r * x_nb1))[c], gv = ((const float *) (g + r * g_nb1))[c];
+        float out;
+        switch (op) {
+            case B200Q_GLU_REGLU:       out = fmaxf(xv, 0.0f) * gv; break;
+            case B200Q_GLU_GEGLU:       out = gelu_f(xv) * gv; break;
+            case B200Q_GLU_GEGLU_ERF:   out = gelu_erf_f(xv) * gv; break;
+            case B200Q_GLU_GEGLU_QUICK: out = gelu_quick_f(xv) * gv; break;
+            case B200Q_GLU_SWIGLU_OAI: {
+                const float xc = fminf(xv, limit), yc = fminf(fmaxf(gv, -limit), limit);
+                out = (xc / (1.0f + expf(alpha * (-xc)))) * (yc + 1.0f);
+            } break;
+            default:                    out = silu_f(xv) * gv; break;  // SWIGLU
+        }
+        ((float *) (d + r * d_nb1))[c] = out;
+    }
+}
+
+// ---- SOFT_MAX over rows: softmax(x * scale + slope(head) * mask [, sink]), one CTA per row ----------------------------------
+template <bool MASK_F16> __global__ void __launch_bounds__(256) soft_max_kernel(T4 x, T4 m, const float * sinks, T4 d, float scale, float max_bias,
+                                                                                float m0, float m1, unsigned n_head_log2) {
+    __shared__ float sh[32];
+    const long long row = blockIdx.x;
+    const long long i3 = row / (x.ne[1] * x.ne[2]), i2 = (row / x.ne[1]) % x.ne[2], i1 = row % x.ne[1];
+    const float * xp = (const float *) (x.data + i1 * x.nb[1] + i2 * x.nb[2] + i3 * x.nb[3]);
+    float *       dp = (float *) (d.data + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
+    const char *  mp = m.data ? m.data + i1 * m.nb[1] + (i2 % m.ne[2]) * m.nb[2] + (i3 % m.ne[3]) * m.nb[3] : nullptr;
+    const int     n  = (int) x.ne[0];
+    const unsigned h = (unsigned) i2;
+    const float slope = max_bias > 0.0f ? (h < n_head_log2 ? powf(m0, (float) (h + 1)) : powf(m1, (float) (2 * (h - n_head_log2) + 1))) : 1.0f;
+    auto val = [&](int i) {
+        float v = xp[i] * scale;
+        if (mp) v += slope * (MASK_F16 ? __half2float(((const __half *) mp)[i]) : ((const float *) mp)[i]);
+        return v;
+    };
+    float mx = -INFINITY;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) mx = fmaxf(mx, val(i));
+    mx = block_reduce<true>(mx, sh);
+    if (sinks) mx = fmaxf(mx, sinks[i2]);
+    float s = 0.0f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const float e = expf(val(i) - mx);
+        dp[i] = e;
+        s += e;
+    }
+    s = block_reduce<false>(s, sh);
+    if (sinks) s += expf(sinks[i2] - mx);
+    const float inv = 1.0f / s;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) dp[i] *= inv;
+}
+
+// ---- ROPE: one thread per rotated pair ----------------------------------------------------------------------------------------
+struct RopeP {
+    int   n_dims, neox;
+    float theta_scale, freq_scale, ext_factor, attn_factor, corr0, corr1;
+};
+template <int TYPE> __global__ void __launch_bounds__(256) rope_kernel(T4 x, const int * pos, const float * ff, T4 d, RopeP p) {
+    const long long half = x.ne[0] / 2, n = half * x.ne[1] * x.ne[2] * x.ne[3];
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
+        const long long ip = i % half, r = i / half;
+        const long long i1 = r % x.ne[1], r2 = r / x.ne[1], i2 = r2 % x.ne[2], i3 = r2 / x.ne[2];
+        const char * xs = x.data + i1 * x.nb[1] + i2 * x.nb[2] + i3 * x.nb[3];
+        char *       ds = d.data + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3];
+        const long long i0 = 2 * ip;  // pair index in the rotation order
+        constexpr long long es = TYPE == B200Q_TYPE_F32 ? 4 : 2;
+        if (i0 >= p.n_dims) {  // channels past n_dims are copied
+            Elem<TYPE>::st(ds + i0 * es, Elem<TYPE>::ld(xs + i0 * es));
+            Elem<TYPE>::st(ds + (i0 + 1) * es, Elem<TYPE>::ld(xs + (i0 + 1) * es));
+            continue;
+        }
+        // rope_yarn (ops.cpp:6056-6071) on theta = pos * theta_scale^(i0/2) / freq_factor
+        const float theta_extrap = (float) pos[i2] * powf(p.theta_scale, (float) ip) / (ff ? ff[ip] : 1.0f);
+        const float theta_interp = p.freq_scale * theta_extrap;
+        float theta = theta_interp, mscale = p.attn_factor;
+        if (p.ext_factor != 0.0f) {
+            const float y    = ((float) ip - p.corr0) / fmaxf(0.001f, p.corr1 - p.corr0);
+            const float ramp = (1.0f - fminf(1.0f, fmaxf(0.0f, y))) * p.ext_factor;
+            theta            = theta_interp * (1.0f - ramp) + theta_extrap * ramp;
+            mscale *= 1.0f + 0.1f * logf(1.0f / p.freq_scale);
+        }
+        const float c = cosf(theta) * mscale, s = sinf(theta) * mscale;
+        const long long a0 = p.neox ? ip : i0, a1 = p.neox ? ip + p.n_dims / 2 : i0 + 1;
+        const float x0 = Elem<TYPE>::ld(xs + a0 * es), x1 = Elem<TYPE>::ld(xs + a1 * es);
+        Elem<TYPE>::st(ds + a0 * es, x0 * c - x1 * s);
+        Elem<TYPE>::st(ds + a1 * es, x0 * s + x1 * c);
+    }
+}
+
+// ---- CPY / CONT / DUP: element i of src (logical order) -> element i of dst (logical order), with type conversion ----------------
+template <int TS, int TD> __global__ void __launch_bounds__(256) cpy_kernel(T4 s, T4 d, long long n) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
+        long long r = i;
+        const long long s0 = r % s.ne[0]; r /= s.ne[0];
+        const long long s1 = r % s.ne[1]; r /= s.ne[1];
+        const long long s2 = r % s.ne[2], s3 = r / s.ne[2];
+        r = i;
+        const long long d0 = r % d.ne[0]; r /= d.ne[0];
+        const long long d1 = r % d.ne[1]; r /= d.ne[1];
+        const long long d2 = r % d.ne[2], d3 = r / d.ne[2];
+        Elem<TD>::st(d.data + d0 * d.nb[0] + d1 * d.nb[1] + d2 * d.nb[2] + d3 * d.nb[3],
+                     Elem<TS>::ld(s.data + s0 * s.nb[0] + s1 * s.nb[1] + s2 * s.nb[2] + s3 * s.nb[3]));
+    }
+}
+
+// ---- SET_ROWS: dst[idx[i1, i2 % ne11, i3 % ne12]][i2][i3] = src[i1][i2][i3] (rows), idx i64 ------------------------------------
+template <int TD> __global__ void __launch_bounds__(256) set_rows_kernel(T4 s, T4 idx, T4 d, long long n) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
+        long long r = i;
+        const long long i0 = r % s.ne[0]; r /= s.ne[0];
+        const long long i1 = r % s.ne[1]; r /= s.ne[1];
+        const long long i2 = r % s.ne[2], i3 = r / s.ne[2];
+        const long long row = *(const long long *) (idx.data + i1 * idx.nb[0] + (i2 % idx.ne[1]) * idx.nb[1] + (i3 % idx.ne[2]) * idx.nb[2]);
+        const float v = *(const float *) (s.data + i0 * s.nb[0] + i1 * s.nb[1] + i2 * s.nb[2] + i3 * s.nb[3]);
+        Elem<TD>::st(d.data + i0 * d.nb[0] + row * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3], v);
+    }
+}
+
+template <int TS> int cpy_to(const b200q_tensor * s, const b200q_tensor * d, long long n, cudaStream_t st) {
+    const int g = grid_for(n, 256);
+    switch (d->type) {
+        case B200Q_TYPE_F32:  cpy_kernel<TS, B200Q_TYPE_F32><<<g, 256, 0, st>>>(t4(s), t4(d), n); break;
+        case B200Q_TYPE_F16:  cpy_kernel<TS, B200Q_TYPE_F16><<<g, 256, 0, st>>>(t4(s), t4(d), n); break;
+        case B200Q_TYPE_BF16: cpy_kernel<TS, B200Q_TYPE_BF16><<<g, 256, 0, st>>>(t4(s), t4(d), n); break;
+        default: return ops_fail(B200Q_ENOTSUP, "cpy: destination type");
+    }
+    return launched();
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200q_op_rms_norm(const b200q_tensor * src, const b200q_tensor * dst, float eps, void * stream) {
+    if (!src || !dst || src->type != B200Q_TYPE_F32 || dst->type != B200Q_TYPE_F32 || !same_shape(src, dst) || src->nb[0] != 4 || dst->nb[0] != 4) {
+        return ops_fail(B200Q_ENOTSUP, "rms_norm: f32 rows with unit stride, same shape");
+    }
+    const long long nr = nrows(src);
+    if (nr == 0 || src->ne[0] == 0) return 0;
+    if (nr > 0x7fffffffLL) return ops_fail(B200Q_ENOTSUP, "rms_norm: too many rows");
+    rms_norm_kernel<<<(unsigned) nr, 256, 0, (cudaStream_t) stream>>>(t4(src), t4(dst), eps);
+    return launched();
+}
+
+int b200q_op_bin(int op, const b200q_tensor * a, const b200q_tensor * b, const b200q_tensor * dst, void * stream) {
+    if (!a || !b || !dst || a->type != B200Q_TYPE_F32 || b->type != B200Q_TYPE_F32 || dst->type != B200Q_TYPE_F32 || !same_shape(a, dst)) {
+        return ops_fail(B200Q_ENOTSUP, "bin: f32 operands, dst shaped like src0");
+    }
+    for (int i = 0; i < 4; ++i) if (b->ne[i] < 1 || dst->ne[i] % b->ne[i]) return ops_fail(B200Q_EINVAL, "bin: src1 does not broadcast");
+    const long long n = nelem(dst);
+    if (n == 0) return 0;
+    const int g = grid_for(n, 256);
+    cudaStream_t st = (cudaStream_t) stream;
+    switch (op) {
+        case B200Q_BIN_ADD: bin_kernel<B200Q_BIN_ADD><<<g, 256, 0, st>>>(t4(a), t4(b), t4(dst), n); break;
+        case B200Q_BIN_SUB: bin_kernel<B200Q_BIN_SUB><<<g, 256, 0, st>>>(t4(a), t4(b), t4(dst), n); break;
+        case B200Q_BIN_MUL: bin_kernel<B200Q_BIN_MUL><<<g, 256, 0, st>>>(t4(a), t4(b), t4(dst), n); break;
+        case B200Q_BIN_DIV: bin_kernel<B200Q_BIN_DIV><<<g, 256, 0, st>>>(t4(a), t4(b), t4(dst), n); break;
+        default: return ops_fail(B200Q_EINVAL, "bin: unknown op");
+    }
+    return launched();
+}
+
+int b200q_op_scale(const b200q_tensor * src, const b200q_tensor * dst, float scale, float bias, void * stream) {
+    if (!src || !dst || src->type != B200Q_TYPE_F32 || dst->type != B200Q_TYPE_F32 || !contiguous(src) || !contiguous(dst) || nelem(src) != nelem(dst)) {
+        return ops_fail(B200Q_ENOTSUP, "scale: contiguous f32");
+    }
+    const long long n = nelem(src);
+    if (n == 0) return 0;
+    scale_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t) stream>>>((const float *) src->data, (float *) dst->data, n, scale, bias);
+    return launched();
+}
+
+int b200q_op_unary(int op, const b200q_tensor * src, const b200q_tensor * dst, void * stream) {
+    if (!src || !dst || src->type != B200Q_TYPE_F32 || dst->type != B200Q_TYPE_F32 || !contiguous(src) || !contiguous(dst) || nelem(src) != nelem(dst) ||
+        op < B200Q_UNARY_SILU || op > B200Q_UNARY_EXP) {
+        return ops_fail(B200Q_ENOTSUP, "unary: contiguous f32, known op");
+    }
+    const long long n = nelem(src);
+    if (n == 0) return 0;
+    unary_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t) stream>>>((const float *) src->data, (float *) dst->data, n, op);
+    return launched();
+}
+
+int b200q_op_glu(int op, const b200q_tensor * src0, const b200q_tensor * src1, const b200q_tensor * dst, int swapped, float alpha, float limit,
+                 void * stream) {
+    if (!src0 || !dst || src0->type != B200Q_TYPE_F32 || dst->type != B200Q_TYPE_F32 || !contiguous_rows(src0) || !contiguous_rows(dst) ||
+        (src1 && (src1->type != B200Q_TYPE_F32 || !contiguous_rows(src1) || !same_shape(src0, src1))) || op < B200Q_GLU_REGLU || op > B200Q_GLU_SWIGLU_OAI) {
+        return ops_fail(B200Q_ENOTSUP, "glu: f32 tensors with dense rows");
+    }
+    const long long nc = src1 ? src0->ne[0] : src0->ne[0] / 2, nr = nrows(src0);
+    if (dst->ne[0] != nc || nrows(dst) != nr) return ops_fail(B200Q_EINVAL, "glu: dst shape");
+    if (nc == 0 || nr == 0) return 0;
+    const char * x = (const char *) src0->data;
+    const char * g = src1 ? (const char *) src1->data : (const char *) src0->data;
+    if (!src1) {  // the two halves of a row; `swapped` says which half is the gate
+        x += swapped ? nc * 4 : 0;
+        g += swapped ? 0 : nc * 4;
+    }
+    glu_kernel<<<grid_for(nr * nc, 256), 256, 0, (cudaStream_t) stream>>>(x, g, (char *) dst->data, nr, (int) nc, (long long) src0->nb[1],
+                                                                         (long long) (src1 ? src1->nb[1] : src0->nb[1]), (long long) dst->nb[1], op, alpha, limit);
+    return launched();
+}
+
+int b200q_op_soft_max(const b200q_tensor * src, const b200q_tensor * mask, const b200q_tensor * sinks, const b200q_tensor * dst, float scale,
+                      float max_bias, void * stream) {
+    if (!src || !dst || src->type != B200Q_TYPE_F32 || dst->type != B200Q_TYPE_F32 || !same_shape(src, dst) || src->nb[0] != 4 || !contiguous(dst)) {
+        return ops_fail(B200Q_ENOTSUP, "soft_max: f32 rows, contiguous dst");
+    }
+    if (mask && ((mask->type != B200Q_TYPE_F32 && mask->type != B200Q_TYPE_F16) || mask->nb[0] != tsize(mask->type) || mask->ne[0] != src->ne[0] ||
+                 mask->ne[1] < src->ne[1] || mask->ne[2] < 1 || mask->ne[3] < 1)) {
+        return ops_fail(B200Q_ENOTSUP, "soft_max: mask layout");
+    }
+    if (sinks && (sinks->type != B200Q_TYPE_F32 || sinks->ne[0] != src->ne[2] || !contiguous(sinks))) return ops_fail(B200Q_ENOTSUP, "soft_max: sinks");
+    const long long nr = nrows(src);
+    if (nr == 0 || src->ne[0] == 0) return 0;
+    if (nr > 0x7fffffffLL) return ops_fail(B200Q_ENOTSUP, "soft_max: too many rows");
+    const unsigned n_head = (unsigned) src->ne[2], n_head_log2 = 1u << (unsigned) floor(log2((double) n_head));
+    const float m0 = powf(2.0f, -(max_bias) / n_head_log2), m1 = powf(2.0f, -(max_bias / 2.0f) / n_head_log2);
+    T4 m{};
+    if (mask) m = t4(mask);
+    cudaStream_t st = (cudaStream_t) stream;
+    if (mask && mask->type == B200Q_TYPE_F16) {
+        soft_max_kernel<true><<<(unsigned) nr, 256, 0, st>>>(t4(src), m, sinks ? (const float *) sinks->data : nullptr, t4(dst), scale, max_bias, m0, m1, n_head_log2);
+    } else {
+        soft_max_kernel<false><<<(unsigned) nr, 256, 0, st>>>(t4(src), m, sinks ? (const float *) sinks->data : nullptr, t4(dst), scale, max_bias, m0, m1, n_head_log2);
+    }
+    return launched();
+}
+
+int b200q_op_rope(const b200q_tensor * src, const b200q_tensor * pos, const b200q_tensor * freq_factors, const b200q_tensor * dst,
+                  const b200q_rope_params * rp, void * stream) {
+    if (!src || !pos || !dst || !rp || (src->type != B200Q_TYPE_F32 && src->type != B200Q_TYPE_F16) || dst->type != src->type || !same_shape(src, dst) ||
+        src->nb[0] != tsize(src->type) || dst->nb[0] != tsize(dst->type) || pos->type != B200Q_TYPE_I32 || pos->ne[0] < src->ne[2] || pos->nb[0] != 4) {
+        return ops_fail(B200Q_ENOTSUP, "rope: f32 / f16 rows with unit stride, i32 positions");
+    }
+    if (rp->mode != B200Q_ROPE_NORMAL && rp->mode != B200Q_ROPE_NEOX) return ops_fail(B200Q_ENOTSUP, "rope: only the normal and NeoX modes");
+    if (rp->n_dims <= 0 || rp->n_dims % 2 || rp->n_dims > src->ne[0] || src->ne[0] % 2) return ops_fail(B200Q_EINVAL, "rope: n_dims");
+    if (freq_factors && (freq_factors->type != B200Q_TYPE_F32 || freq_factors->ne[0] < rp->n_dims / 2 || freq_factors->nb[0] != 4)) {
+        return ops_fail(B200Q_ENOTSUP, "rope: frequency factors");
+    }
+    const long long n = nelem(src) / 2;
+    if (n == 0) return 0;
+    RopeP p;
+    p.n_dims = rp->n_dims; p.neox = rp->mode == B200Q_ROPE_NEOX;
+    p.theta_scale = powf(rp->freq_base, -2.0f / rp->n_dims);
+    p.freq_scale = rp->freq_scale; p.ext_factor = rp->ext_factor; p.attn_factor = rp->attn_factor;
+    p.corr0 = rp->corr_dims[0]; p.corr1 = rp->corr_dims[1];
+    const float * ff = freq_factors ? (const float *) freq_factors->data : nullptr;
+    cudaStream_t  st = (cudaStream_t) stream;
+    if (src->type == B200Q_TYPE_F32) rope_kernel<B200Q_TYPE_F32><<<grid_for(n, 256), 256, 0, st>>>(t4(src), (const int *) pos->data, ff, t4(dst), p);
+    else rope_kernel<B200Q_TYPE_F16><<<grid_for(n, 256), 256, 0, st>>>(t4(src), (const int *) pos->data, ff, t4(dst), p);
+    return launched();
+}
+
+int b200q_op_cpy(const b200q_tensor * src, const b200q_tensor * dst, void * stream) {
+    if (!src || !dst || nelem(src) != nelem(dst)) return ops_fail(B200Q_EINVAL, "cpy: element counts differ");
+    const long long n = nelem(src);
+    if (n == 0) return 0;
+    switch (src->type) {
+        case B200Q_TYPE_F32:  return cpy_to<B200Q_TYPE_F32>(src, dst, n, (cudaStream_t) stream);
+        case B200Q_TYPE_F16:  return cpy_to<B200Q_TYPE_F16>(src, dst, n, (cudaStream_t) stream);
+        case B200Q_TYPE_BF16: return cpy_to<B200Q_TYPE_BF16>(src, dst, n, (cudaStream_t) stream);
+        default: return ops_fail(B200Q_ENOTSUP, "cpy: source type");
+    }
+}
+
+int b200q_op_set_rows(const b200q_tensor * src, const b200q_tensor * idx, const b200q_tensor * dst, void * stream) {
+    if (!src || !idx || !dst || src->type != B200Q_TYPE_F32 || idx->type != B200Q_TYPE_I64 || src->ne[0] != dst->ne[0] || src->ne[2] != dst->ne[2] ||
+        src->ne[3] != dst->ne[3] || idx->ne[0] != src->ne[1] || idx->ne[1] < 1 || idx->ne[2] < 1 || src->ne[2] % idx->ne[1] || src->ne[3] % idx->ne[2]) {
+        return ops_fail(B200Q_ENOTSUP, "set_rows: f32 rows, i64 indices [ne01, ne11 | ne02, ne12 | ne03]");
+    }
+    const long long n = nelem(src);
+    if (n == 0) return 0;
+    const int g = grid_for(n, 256);
+    cudaStream_t st = (cudaStream_t) stream;
+    switch (dst->type) {
+        case B200Q_TYPE_F32:  set_rows_kernel<B200Q_TYPE_F32><<<g, 256, 0, st>>>(t4(src), t4(idx), t4(dst), n); break;
+        case B200Q_TYPE_F16:  set_rows_kernel<B200Q_TYPE_F16><<<g, 256, 0, st>>>(t4(src), t4(idx), t4(dst), n); break;
+        case B200Q_TYPE_BF16: set_rows_kernel<B200Q_TYPE_BF16><<<g, 256, 0, st>>>(t4(src), t4(idx), t4(dst), n); break;
+        default: return ops_fail(B200Q_ENOTSUP, "set_rows: destination type");
+    }
+    return launched();
+}
+
+}  // extern "C"

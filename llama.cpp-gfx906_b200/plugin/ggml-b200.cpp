@@ -3,10 +3,11 @@
 // MUL_MAT / MUL_MAT_ID / GET_ROWS hot path to the hand-written sm_100a kernels behind include/b200q.h.
 //
 // It plays the role ggml-cuda.cu plays in the reference (reg :3751-3790, device :3148-3649, buffer type
-// :672-756, buffer :566-664, backend :2525-3077) but is NOT derived from it: no op besides the hot path is
-// claimed (supports_op is exact, so the scheduler leaves everything else on ggml-cpu), buffers are plain
-// device allocations with tail slack instead of per-row padding, MoE routing never touches the host, and
-// all CUDA calls go through the single runtime inside libb200q.so.
+// :672-756, buffer :566-664, backend :2525-3077) but is NOT derived from it: nothing besides the hot path and the
+// operators that bracket it in a decoder layer (csrc/ops.cu) is claimed (supports_op is exact, so the scheduler
+// leaves everything else on ggml-cpu), buffers are plain device allocations with tail slack instead of per-row
+// padding, MoE routing never touches the host, row split runs from one process with peer stores instead of gather
+// copies, and all CUDA calls go through the single runtime inside libb200q.so.
 //
 // Loading: dlopen'ed by the reference's registry (GGML_BACKEND_PATH=.../libggml-b200.so or
 // ggml_backend_load(), ggml-backend-reg.cpp:232-276,588-592).  The ggml-base symbols used here
@@ -480,6 +481,120 @@ bool supports_get_rows(const ggml_tensor * op) {
     return true;
 }
 
+// ---- the operators around the matmuls (csrc/ops.cu): what the kernels take, stated once for supports_op and compute ------
+b200q_tensor bt(const ggml_tensor * t) {
+    b200q_tensor r{};
+    r.data = t->data;
+    r.type = (int) t->type;  // F32 0, F16 1, I32 26, I64 27, BF16 30: ggml's numbers are the C-ABI's
+    for (int i = 0; i < 4; ++i) { r.ne[i] = t->ne[i]; r.nb[i] = t->nb[i]; }
+    return r;
+}
+bool is_f32(const ggml_tensor * t) { return t && t->type == GGML_TYPE_F32; }
+bool float_type(ggml_type t) { return t == GGML_TYPE_F32 || t == GGML_TYPE_F16 || t == GGML_TYPE_BF16; }
+int unary_code(const ggml_tensor * op) {
+    switch (ggml_get_unary_op(op)) {
+        case GGML_UNARY_OP_SILU:       return B200Q_UNARY_SILU;
+        case GGML_UNARY_OP_GELU:       return B200Q_UNARY_GELU;
+        case GGML_UNARY_OP_GELU_QUICK: return B200Q_UNARY_GELU_QUICK;
+        case GGML_UNARY_OP_GELU_ERF:   return B200Q_UNARY_GELU_ERF;
+        case GGML_UNARY_OP_RELU:       return B200Q_UNARY_RELU;
+        case GGML_UNARY_OP_SIGMOID:    return B200Q_UNARY_SIGMOID;
+        case GGML_UNARY_OP_TANH:       return B200Q_UNARY_TANH;
+        case GGML_UNARY_OP_NEG:        return B200Q_UNARY_NEG;
+        case GGML_UNARY_OP_ABS:        return B200Q_UNARY_ABS;
+        case GGML_UNARY_OP_EXP:        return B200Q_UNARY_EXP;
+        default:                       return -1;
+    }
+}
+int glu_code(const ggml_tensor * op) {
+    switch (ggml_get_glu_op(op)) {
+        case GGML_GLU_OP_REGLU:       return B200Q_GLU_REGLU;
+        case GGML_GLU_OP_GEGLU:       return B200Q_GLU_GEGLU;
+        case GGML_GLU_OP_SWIGLU:      return B200Q_GLU_SWIGLU;
+        case GGML_GLU_OP_GEGLU_ERF:   return B200Q_GLU_GEGLU_ERF;
+        case GGML_GLU_OP_GEGLU_QUICK: return B200Q_GLU_GEGLU_QUICK;
+        case GGML_GLU_OP_SWIGLU_OAI:  return B200Q_GLU_SWIGLU_OAI;
+        default:                      return -1;
+    }
+}
+int bin_code(ggml_op op) {
+    return op == GGML_OP_ADD ? B200Q_BIN_ADD : op == GGML_OP_SUB ? B200Q_BIN_SUB : op == GGML_OP_MUL ? B200Q_BIN_MUL : B200Q_BIN_DIV;
+}
+bool supports_elementwise(const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0];
+    const ggml_tensor * b = op->src[1];
+    switch (op->op) {
+        case GGML_OP_RMS_NORM:
+            return is_f32(a) && is_f32(op) && a->nb[0] == 4 && op->nb[0] == 4;
+        case GGML_OP_ADD: case GGML_OP_SUB: case GGML_OP_MUL: case GGML_OP_DIV:
+            return is_f32(a) && is_f32(b) && is_f32(op) && ggml_are_same_shape(a, op) && ggml_can_repeat(b, a);
+        case GGML_OP_SCALE:
+            return is_f32(a) && is_f32(op) && ggml_is_contiguous(a) && ggml_is_contiguous(op);
+        case GGML_OP_UNARY:
+            return is_f32(a) && is_f32(op) && ggml_is_contiguous(a) && ggml_is_contiguous(op) && unary_code(op) >= 0;
+        case GGML_OP_GLU:
+            return is_f32(a) && is_f32(op) && ggml_is_contiguous_1(a) && ggml_is_contiguous_1(op) && glu_code(op) >= 0 &&
+                   (!b || (is_f32(b) && ggml_is_contiguous_1(b) && ggml_are_same_shape(a, b)));
+        case GGML_OP_SOFT_MAX: {
+            const ggml_tensor * sinks = op->src[2];
+            if (!is_f32(a) || !is_f32(op) || a->nb[0] != 4 || !ggml_is_contiguous(op)) return false;
+            if (b && ((b->type != GGML_TYPE_F32 && b->type != GGML_TYPE_F16) || b->nb[0] != ggml_type_size(b->type) || b->ne[0] != a->ne[0] ||
+                      b->ne[1] < a->ne[1])) return false;
+            if (sinks && (!is_f32(sinks) || sinks->ne[0] != a->ne[2] || !ggml_is_contiguous(sinks))) return false;
+            return true;
+        }
+        case GGML_OP_ROPE: {
+            const int mode = ((const int32_t *) op->op_params)[2];
+            if (mode != 0 && mode != GGML_ROPE_TYPE_NEOX) return false;  // multimodal / vision rotary embeddings stay on the CPU backend
+            if ((a->type != GGML_TYPE_F32 && a->type != GGML_TYPE_F16) || op->type != a->type) return false;
+            if (a->nb[0] != ggml_type_size(a->type) || op->nb[0] != ggml_type_size(op->type) || a->ne[0] % 2) return false;
+            if (!b || b->type != GGML_TYPE_I32 || b->nb[0] != 4 || b->ne[0] < a->ne[2]) return false;
+            if (op->src[2] && (!is_f32(op->src[2]) || op->src[2]->nb[0] != 4)) return false;
+            return true;
+        }
+        case GGML_OP_CPY: case GGML_OP_CONT: case GGML_OP_DUP:
+            return float_type(a->type) && float_type(op->type) && ggml_nelements(a) == ggml_nelements(op);
+        case GGML_OP_SET_ROWS:
+            return is_f32(a) && b && b->type == GGML_TYPE_I64 && float_type(op->type) && a->ne[0] == op->ne[0] && a->ne[2] == op->ne[2] &&
+                   a->ne[3] == op->ne[3] && b->ne[0] == a->ne[1] && a->ne[2] % b->ne[1] == 0 && a->ne[3] % b->ne[2] == 0;
+        default:
+            return false;
+    }
+}
+int compute_elementwise(b200_backend_ctx * ctx, const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0];
+    const ggml_tensor * b = op->src[1];
+    const b200q_tensor  ta = bt(a), td = bt(op);
+    b200q_tensor        tb{}, tc{};
+    if (b) tb = bt(b);
+    if (op->src[2]) tc = bt(op->src[2]);
+    const float *   fp = (const float *) op->op_params;
+    const int32_t * ip = (const int32_t *) op->op_params;
+    switch (op->op) {
+        case GGML_OP_RMS_NORM: return b200q_op_rms_norm(&ta, &td, fp[0], ctx->stream);
+        case GGML_OP_ADD: case GGML_OP_SUB: case GGML_OP_MUL: case GGML_OP_DIV:
+            return b200q_op_bin(bin_code(op->op), &ta, &tb, &td, ctx->stream);
+        case GGML_OP_SCALE: return b200q_op_scale(&ta, &td, fp[0], fp[1], ctx->stream);
+        case GGML_OP_UNARY: return b200q_op_unary(unary_code(op), &ta, &td, ctx->stream);
+        case GGML_OP_GLU:   return b200q_op_glu(glu_code(op), &ta, b ? &tb : nullptr, &td, ip[1], fp[2], fp[3], ctx->stream);
+        case GGML_OP_SOFT_MAX:
+            return b200q_op_soft_max(&ta, b ? &tb : nullptr, op->src[2] ? &tc : nullptr, &td, fp[0], fp[1], ctx->stream);
+        case GGML_OP_ROPE: {
+            b200q_rope_params rp{};
+            rp.n_dims = ip[1]; rp.mode = ip[2];
+            const int n_ctx_orig = ip[4];
+            float beta_fast, beta_slow;
+            memcpy(&rp.freq_base, ip + 5, 4); memcpy(&rp.freq_scale, ip + 6, 4); memcpy(&rp.ext_factor, ip + 7, 4);
+            memcpy(&rp.attn_factor, ip + 8, 4); memcpy(&beta_fast, ip + 9, 4); memcpy(&beta_slow, ip + 10, 4);
+            ggml_rope_yarn_corr_dims(rp.n_dims, n_ctx_orig, rp.freq_base, beta_fast, beta_slow, rp.corr_dims);
+            return b200q_op_rope(&ta, &tb, op->src[2] ? &tc : nullptr, &td, &rp, ctx->stream);
+        }
+        case GGML_OP_CPY: case GGML_OP_CONT: case GGML_OP_DUP: return b200q_op_cpy(&ta, &td, ctx->stream);
+        case GGML_OP_SET_ROWS: return b200q_op_set_rows(&ta, &tb, &td, ctx->stream);
+        default: return B200Q_ENOTSUP;
+    }
+}
+
 bool device_supports_op(ggml_backend_dev_t dev, const ggml_tensor * op) {
     switch (op->op) {
         case GGML_OP_NONE:
@@ -491,7 +606,7 @@ bool device_supports_op(ggml_backend_dev_t dev, const ggml_tensor * op) {
         case GGML_OP_MUL_MAT:    return supports_mul_mat((const b200_device_ctx *) dev->context, op);
         case GGML_OP_MUL_MAT_ID: return supports_mul_mat_id(op);
         case GGML_OP_GET_ROWS:   return supports_get_rows(op);
-        default: return false;
+        default: return supports_elementwise(op);
     }
 }
 
@@ -737,6 +852,11 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) 
             case GGML_OP_MUL_MAT:    rc = compute_mul_mat(ctx, node); break;
             case GGML_OP_MUL_MAT_ID: rc = compute_mul_mat_id(ctx, node); break;
             case GGML_OP_GET_ROWS:   rc = compute_get_rows(ctx, node); break;
+            case GGML_OP_RMS_NORM: case GGML_OP_ADD: case GGML_OP_SUB: case GGML_OP_MUL: case GGML_OP_DIV: case GGML_OP_SCALE:
+            case GGML_OP_UNARY: case GGML_OP_GLU: case GGML_OP_SOFT_MAX: case GGML_OP_ROPE: case GGML_OP_CPY: case GGML_OP_CONT:
+            case GGML_OP_DUP: case GGML_OP_SET_ROWS:
+                rc = compute_elementwise(ctx, node);
+                break;
             default:
                 fprintf(stderr, "ggml-b200: op %s reached graph_compute but is not supported\n", ggml_op_name(node->op));
                 return GGML_STATUS_FAILED;

@@ -52,7 +52,14 @@ def _run_tbo(op, timeout=900):
 
 # supported-and-passing counts logged in profiles/r02_test_backend_ops_*_v2.txt (round 1: 43 / 243 / 194); a regression in supports_op or in a
 # kernel shows up as a lower count or a FAIL line
-@pytest.mark.parametrize("op,min_ok", [("GET_ROWS", 65), ("MUL_MAT", 470), ("MUL_MAT_ID", 270)])
+# the operators around the matmuls (csrc/ops.cu): NMSE <= 1e-7 against ggml-cpu, the harness' default (test-backend-ops.cpp:948-950)
+LAYER_OPS = [("RMS_NORM", 10), ("ADD", 35), ("SUB", 28), ("MUL", 28), ("DIV", 28), ("SCALE", 4), ("SILU", 4), ("GELU", 4),
+             ("GELU_QUICK", 4), ("GELU_ERF", 4), ("RELU", 4), ("SIGMOID", 4), ("TANH", 4), ("NEG", 4), ("ABS", 4), ("EXP", 4),
+             ("REGLU", 14), ("GEGLU", 14), ("SWIGLU", 14), ("SWIGLU_OAI", 10), ("GEGLU_ERF", 14), ("GEGLU_QUICK", 14),
+             ("SOFT_MAX", 201), ("ROPE", 178), ("CPY", 57), ("CONT", 12), ("DUP", 8), ("SET_ROWS", 63)]
+
+
+@pytest.mark.parametrize("op,min_ok", [("GET_ROWS", 65), ("MUL_MAT", 470), ("MUL_MAT_ID", 270)] + LAYER_OPS)
 def test_backend_ops_against_plugin(op, min_ok):
     rc, ok, fail, unsup, out = _run_tbo(op)
     assert not fail, fail[:5]
