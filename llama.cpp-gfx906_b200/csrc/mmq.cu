@@ -970,7 +970,7 @@ static int mmq_launch_impl(const MmqArgs & a, const MmqMoeArgs * moe, void * wor
         p.n_sub  = p.n_tiles > 1 && units_dual >= fill ? 2 : 1;
         p.ksplit = p.n_sub == 1 && units_one < fill && p.w_stages_per_tile >= 4 ? 2 : 1;
         if (force_sub) p.n_sub = p.n_tiles > 1 ? std::min(force_sub, 2) : 1;
-        if (force_ks) p.ksplit = p.w_stages_per_tile >= 2 ? std::min(force_ks, 2) : 1;
+        if (force_ks) p.ksplit = std::max(1, std::min(force_ks, std::min(8, p.w_stages_per_tile / 2)));
         if (moe) p.n_sub = p.ksplit = 1;
     }
     p.off_b = A_STAGES * A_STAGE_BYTES;
