@@ -699,7 +699,7 @@ def main_b200(args):
         "gpu_launches": n_launch * args.steps,
         "roofline": {"bound": "hbm", "achieved": value / world, "peak": peak, "unit": "GB/s",
                      "frac": value / world / peak, "traffic": None, "peak_source": peak_src,
-                     "traffic_note": "not measured in this run; ncu dram bytes per launch are in profiles/ (see DESIGN.md section 5)",
+                     "traffic_note": "not measured in this run; ncu --set full of the same kernel on an 8-layer slice: dram read + write = 1.002 x algorithmic bytes (profiles/list_traffic.json, profiles/r02_ncu_list_full_v1.csv)",
                      "kernel": "gemv_list_kernel (one launch = the whole step)",
                      "launches_per_step": n_launch,
                      "algorithmic_bytes_per_launch_avg": algo / world / max(1, n_launch),

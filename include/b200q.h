@@ -292,6 +292,13 @@ B200Q_API int b200q_op_cpy(const b200q_tensor * src, const b200q_tensor * dst, v
 B200Q_API int b200q_op_set_rows(const b200q_tensor * src, const b200q_tensor * idx, const b200q_tensor * dst,
                                 void * stream);                                                                            /* set-rows.cu */
 
+/* ---- experiment (no counterpart in the reference's shipped kernels): one CTA runs tcgen05.mma kind::mxf8f6f4.block_scale
+ *      (e2m1 A x e4m3 B, UE8M0 block-32 scales) on a 128 x n x 128 problem laid out by the host exactly as the instruction reads
+ *      it (csrc/mxf_probe.cu documents the images); `iters` repeats the four MMAs for an issue-rate measurement (cycles_dev:
+ *      device pointer to one int64, or NULL).  tools/mxf_probe.py validates the layouts against a CPU emulation. ------------ */
+B200Q_API int b200q_mxf_probe(const void * a_img, const void * b_img, const void * sfa_img, const void * sfb_img, float * d, int n,
+                              int iters, long long * cycles_dev, void * stream);
+
 /* ---- host-buffer round trip (what a ggml caller does: tensor_set -> graph_compute -> tensor_get) --- */
 /* Weights stay resident on the device (w_dev); activations and results are HOST buffers (pinned or pageable).
  * act_host: n*k floats contiguous, dst_host: n*m floats contiguous.  Synchronous. */

@@ -86,7 +86,12 @@ struct b200_backend_ctx {
     void *      copy_event = nullptr;            // cpy_tensor_async between two backends
     void *      split_start = nullptr;           // event: the activations of a row-split matmul are ready on this stream
     b200_split_peer peers[MAX_DEVICES];          // indexed by registry device index
+    // runs of decode matmuls go out as persistent lists (b200q_list_*), cached by their pointers and shapes: llama.cpp
+    // rebuilds its graph for every token but ggml-alloc hands out the same addresses
+    std::map<std::vector<int64_t>, b200q_list *> lists;
+    std::vector<std::vector<int64_t>>            list_order;  // insertion order, for eviction
 };
+constexpr size_t MAX_CACHED_LISTS = 512;
 
 void * device_xfer_stream(b200_device_ctx * d) {
     std::lock_guard<std::mutex> lk(d->mu);
@@ -765,6 +770,7 @@ void backend_free(ggml_backend_t backend) {
         if (ctx->split_start) b200q_event_destroy(ctx->split_start);
         b200q_stream_destroy(ctx->stream);
     }
+    for (auto & kv : ctx->lists) if (kv.second) b200q_list_destroy(kv.second);
     for (int id = 0; id < MAX_DEVICES; ++id) {
         b200_split_peer & pe = ctx->peers[id];
         if (!pe.stream) continue;
@@ -832,15 +838,94 @@ void backend_event_wait(ggml_backend_t backend, ggml_backend_event_t event) {
     B200_CHECK(b200q_stream_wait_event(ctx->stream, event->context));
 }
 
+// ---- runs of decode matmuls as ONE persistent launch (csrc/gemv_list.cu) -------------------------------------------------
+// A MUL_MAT node qualifies when it is a plain n = 1 product on immutable, dense, unsplit weights; a run = consecutive such
+// nodes (no-op view nodes between them are skipped).  wq / wk / wv and ffn_gate / ffn_up of a llama graph are such runs:
+// they share one quantized activation image and one launch.  A node whose activations overlap the result of an earlier
+// node of the run is flagged B200Q_LIST_DEP (device-side barrier point).  Results are bit-identical to the per-node path.
+bool noop_node(const ggml_tensor * t) {
+    return ggml_is_empty(t) || t->op == GGML_OP_NONE || t->op == GGML_OP_VIEW || t->op == GGML_OP_RESHAPE || t->op == GGML_OP_PERMUTE ||
+           t->op == GGML_OP_TRANSPOSE;
+}
+bool list_candidate(const ggml_tensor * op) {
+    if (op->op != GGML_OP_MUL_MAT) return false;
+    const ggml_tensor * a = op->src[0];
+    const ggml_tensor * b = op->src[1];
+    if (!a || !b || tensor_is_split(a) || !(weight_flags(a) & B200Q_FLAG_WEIGHTS_IMMUTABLE)) return false;
+    if (a->ne[2] != 1 || a->ne[3] != 1 || ggml_nrows(b) != 1 || b->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
+    if (dense_weight(a->type) || !type_ok(a->type) || a->nb[1] != ggml_row_size(a->type, a->ne[0])) return false;
+    if (b->nb[0] != 4 || op->nb[0] != 4 || ((uintptr_t) a->data & 15) || ((uintptr_t) b->data & 15)) return false;
+    return true;
+}
+// tries to run nodes [first, ...) as a list; returns the index behind the run (== first when no list was launched)
+int compute_list_run(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int first, int n_nodes) {
+    std::vector<b200q_list_op> ops;
+    int end = first;
+    for (int i = first; i < n_nodes && ops.size() < 64; ++i) {
+        ggml_tensor * t = ggml_graph_node(cgraph, i);
+        if (noop_node(t)) continue;
+        if (!list_candidate(t)) break;
+        b200q_list_op o{};
+        o.type = (int) t->src[0]->type; o.m = t->src[0]->ne[1]; o.k = t->src[0]->ne[0];
+        o.w = t->src[0]->data; o.act = (const float *) t->src[1]->data; o.dst = (float *) t->data;
+        const char * a0 = (const char *) o.act, * a1 = a0 + o.k * 4;
+        for (const b200q_list_op & e : ops) {  // reads what an earlier op of the run writes?
+            const char * d0 = (const char *) e.dst, * d1 = d0 + e.m * 4;
+            if (a0 < d1 && d0 < a1) o.flags |= B200Q_LIST_DEP;
+        }
+        ops.push_back(o);
+        end = i + 1;
+    }
+    if (ops.size() < 2) return first;
+    std::vector<int64_t> key;
+    key.reserve(ops.size() * 6);
+    for (const b200q_list_op & o : ops) {
+        key.push_back(o.type); key.push_back(o.m); key.push_back(o.k);
+        key.push_back((int64_t) (uintptr_t) o.w); key.push_back((int64_t) (uintptr_t) o.act);
+        key.push_back((int64_t) (uintptr_t) o.dst * 2 + (o.flags & B200Q_LIST_DEP ? 1 : 0));
+    }
+    auto it = ctx->lists.find(key);
+    if (it == ctx->lists.end()) {
+        b200q_list * l = nullptr;
+        if (b200q_list_create(ops.data(), (int) ops.size(), nullptr, &l) != 0) {
+            l = nullptr;  // some op is not served by the list kernel: remember that, the nodes go out one by one
+        }
+        if (ctx->lists.size() >= MAX_CACHED_LISTS) {  // evict the oldest entry
+            auto old = ctx->lists.find(ctx->list_order.front());
+            if (old != ctx->lists.end()) {
+                if (old->second) {
+                    B200_CHECK(b200q_stream_synchronize(ctx->stream));
+                    b200q_list_destroy(old->second);
+                }
+                ctx->lists.erase(old);
+            }
+            ctx->list_order.erase(ctx->list_order.begin());
+        }
+        it = ctx->lists.emplace(key, l).first;
+        ctx->list_order.push_back(key);
+    }
+    if (!it->second) return first;
+    if (b200q_list_launch(it->second, ctx->stream) != 0) return first;
+    return end;
+}
+
 // asynchronous: kernels are enqueued on the backend's stream, the caller follows with synchronize()
 // (ggml-backend.cpp:327-335).  Graph and tensor pointers are not retained (they may be stack temporaries).
 ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
     auto * ctx = (b200_backend_ctx *) backend->context;
     B200_CHECK(b200q_set_device(ctx->device));
-    const int n_nodes = ggml_graph_n_nodes(cgraph);
+    const int  n_nodes  = ggml_graph_n_nodes(cgraph);
+    const bool no_lists = getenv("GGML_B200_NO_LIST") != nullptr;
     for (int i = 0; i < n_nodes; ++i) {
         ggml_tensor * node = ggml_graph_node(cgraph, i);
         if (ggml_is_empty(node)) continue;
+        if (!no_lists && list_candidate(node)) {
+            const int next = compute_list_run(ctx, cgraph, i, n_nodes);
+            if (next > i) {
+                i = next - 1;
+                continue;
+            }
+        }
         int rc = 0;
         switch (node->op) {
             case GGML_OP_NONE:

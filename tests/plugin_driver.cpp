@@ -283,4 +283,54 @@ int pd_big_upload(int dev, const uint8_t * src, int64_t nbytes, uint8_t * back) 
     return rc;
 }
 
+// A decode-shaped graph on immutable weights: q = W1 x, k = W2 x, v = W3 x (one shared vector, W3 of type_v), o = W4 q (reads
+// what the first node wrote).  The plugin runs the four nodes as ONE persistent list (or one by one with GGML_B200_NO_LIST).
+// All matrices are [k][k]; x: k floats; out: 4 x k floats (q, k, v, o).  Returns 0 on success.
+int pd_decode_run(int dev, int type, int type_v, int64_t k, const void * w1, const void * w2, const void * w3, const void * w4,
+                  const float * x, float * out) {
+    if (!g_reg) return -1;
+    ggml_backend_dev_t d  = ggml_backend_reg_dev_get(g_reg, dev);
+    ggml_backend_t     be = ggml_backend_dev_init(d, nullptr);
+    if (!be) return -2;
+    int rc = 0;
+    {
+        ctx_scope wc(8), cc(16);
+        ggml_tensor * a1 = ggml_new_tensor_2d(wc.ctx, (ggml_type) type, k, k);
+        ggml_tensor * a2 = ggml_new_tensor_2d(wc.ctx, (ggml_type) type, k, k);
+        ggml_tensor * a3 = ggml_new_tensor_2d(wc.ctx, (ggml_type) type_v, k, k);
+        ggml_tensor * a4 = ggml_new_tensor_2d(wc.ctx, (ggml_type) type, k, k);
+        ggml_backend_buffer_t wbuf = ggml_backend_alloc_ctx_tensors(wc.ctx, be);
+        if (!wbuf) { ggml_backend_free(be); return -3; }
+        ggml_backend_buffer_set_usage(wbuf, GGML_BACKEND_BUFFER_USAGE_WEIGHTS);
+        ggml_backend_tensor_set(a1, w1, 0, ggml_nbytes(a1));
+        ggml_backend_tensor_set(a2, w2, 0, ggml_nbytes(a2));
+        ggml_backend_tensor_set(a3, w3, 0, ggml_nbytes(a3));
+        ggml_backend_tensor_set(a4, w4, 0, ggml_nbytes(a4));
+        ggml_tensor * xin = ggml_new_tensor_1d(cc.ctx, GGML_TYPE_F32, k);
+        ggml_tensor * q = ggml_mul_mat(cc.ctx, a1, xin);
+        ggml_tensor * kk = ggml_mul_mat(cc.ctx, a2, xin);
+        ggml_tensor * v = ggml_mul_mat(cc.ctx, a3, xin);
+        ggml_tensor * o = ggml_mul_mat(cc.ctx, a4, q);
+        ggml_cgraph * gf = ggml_new_graph(cc.ctx);
+        ggml_build_forward_expand(gf, q);
+        ggml_build_forward_expand(gf, kk);
+        ggml_build_forward_expand(gf, v);
+        ggml_build_forward_expand(gf, o);
+        ggml_backend_buffer_t cbuf = ggml_backend_alloc_ctx_tensors(cc.ctx, be);
+        if (!cbuf) rc = -4;
+        if (rc == 0) {
+            ggml_backend_tensor_set(xin, x, 0, ggml_nbytes(xin));
+            for (int rep = 0; rep < 3 && rc == 0; ++rep) {  // the second and third pass hit the plugin's list cache
+                if (ggml_backend_graph_compute(be, gf) != GGML_STATUS_SUCCESS) rc = -5;
+            }
+            ggml_tensor * outs[4] = { q, kk, v, o };
+            for (int i = 0; i < 4 && rc == 0; ++i) ggml_backend_tensor_get(outs[i], out + i * k, 0, (size_t) k * sizeof(float));
+        }
+        if (cbuf) ggml_backend_buffer_free(cbuf);
+        ggml_backend_buffer_free(wbuf);
+    }
+    ggml_backend_free(be);
+    return rc;
+}
+
 }  // extern "C"
