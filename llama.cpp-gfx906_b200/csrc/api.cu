@@ -9,6 +9,7 @@
 #include "gemv_list.cuh"
 #include "gemv_mma.cuh"
 #include "mmq.cuh"
+#include "mmq_mxf.cuh"
 
 #include <cuda_runtime.h>
 
@@ -773,8 +774,22 @@ static bool use_mmq(const b200q_mul_mat_args * a) {
     return false;
 }
 
+// MXFP4 on the native block-scaled tensor-core path (mmq_mxf.cu): plain 2-D products
+static long long k_mxf_dual_units(int64_t m, int64_t n) { return ((m + 127) / 128) * ((n + 511) / 512); }
+static bool use_mxf(const b200q_mul_mat_args * a) {
+    if (a->type != T_MXFP4 || a->ne02 * a->ne03 * a->ne12 * a->ne13 != 1 || !mxf_supported(a->type, a->k) || (a->flags & B200Q_FLAG_FORCE_GEMV)) return false;
+    if (!(a->flags & B200Q_FLAG_FORCE_MMQ) && a->n < 17) return false;
+    // measured (profiles/r02_mxf_vs_bf16_v1.txt): the native kernel wins wherever the bf16 kernel is dequantization-bound
+    // (1.3 - 1.8 x: few row tiles, few columns, MoE); where the bf16 kernel runs its two-accumulator units on a full GPU
+    // (n > 256 with >= 88 row tiles, e.g. 11520 x 2880 at n = 512: 55 vs 66 us) it stays ahead
+    static const bool always = getenv("B200Q_MXF_ALWAYS") != nullptr;
+    if (!always && a->n > 256 && k_mxf_dual_units(a->m, a->n) >= 88 && a->k % 64 == 0) return false;
+    return true;
+}
+
 size_t b200q_mul_mat_workspace(const b200q_mul_mat_args * a) {
     if (!a || check_mm(a)) return 0;
+    if (use_mxf(a)) return mxf_workspace_bytes(a->k, a->n);
     if (!use_mmq(a)) return 0;
     return mmq_workspace_bytes(a->k, a->n, a->ne12 * a->ne13);
 }
@@ -788,6 +803,16 @@ int b200q_mul_mat(const b200q_mul_mat_args * a, const void * w, const float * ac
     const DevInfo & di = dev_info();
     if (!di.ok) return fail(B200Q_ENODEVICE, "mul_mat: no CUDA device");
 
+    if (use_mxf(a)) {
+        const size_t need = mxf_workspace_bytes(a->k, a->n);
+        if (workspace_bytes < need || !workspace) return fail(B200Q_EWORKSPACE, "mul_mat: workspace %zu < required %zu", workspace_bytes, need);
+        MxfArgs q{};
+        q.k = a->k; q.m = a->m; q.n = a->n; q.w = (const uint8_t *) w; q.act = act; q.dst = dst;
+        q.w_nb1 = (long long) a->nb01; q.a_nb1 = (long long) a->nb11; q.d_nb1 = (long long) a->nb1;
+        std::string err;
+        if (int rc = mxf_launch(q, workspace, st, di.sms, err)) return fail(rc, "%s", err.c_str());
+        return 0;
+    }
     if (use_mmq(a)) {
         MmqArgs q{};
         q.type = wtype(a->type); q.k = a->k; q.m = a->m; q.n = a->n;
@@ -1001,7 +1026,13 @@ static bool moe_use_mmq(const b200q_mul_mat_id_args * a) {
     return a->n_tokens * a->n_used >= min_rows && mmq_supported(a->type, a->k) && a->n_expert <= 1024;
 }
 
+static bool moe_use_mxf(const b200q_mul_mat_id_args * a) {
+    static const long long min_rows = getenv("B200Q_MOE_MMQ_MIN") ? atoll(getenv("B200Q_MOE_MMQ_MIN")) : 32;
+    return a->type == T_MXFP4 && mxf_supported(a->type, a->k) && a->n_tokens * a->n_used >= min_rows && a->n_expert <= 1024;
+}
+
 size_t b200q_mul_mat_id_workspace(const b200q_mul_mat_id_args * a) {
+    if (a && moe_use_mxf(a)) return mxf_moe_workspace_bytes(a->k, a->n_tokens, a->n_used, a->n_expert);
     if (!a || !moe_use_mmq(a)) return 0;
     return mmq_moe_workspace_bytes(a->k, a->n_tokens, a->n_used, a->n_expert);
 }
@@ -1020,6 +1051,20 @@ int b200q_mul_mat_id(const b200q_mul_mat_id_args * a, const void * as, const flo
     const DevInfo & di = dev_info();
     if (!di.ok) return fail(B200Q_ENODEVICE, "mul_mat_id: no CUDA device");
 
+    if (moe_use_mxf(a)) {
+        const size_t need = mxf_moe_workspace_bytes(a->k, a->n_tokens, a->n_used, a->n_expert);
+        if (!workspace || workspace_bytes < need) return fail(B200Q_EINVAL, "mul_mat_id: workspace of %zu bytes needed (b200q_mul_mat_id_workspace)", need);
+        MxfArgs q{};
+        q.k = a->k; q.m = a->m; q.w = (const uint8_t *) as; q.act = b; q.dst = dst;
+        q.w_nb1 = (long long) a->nb01; q.w_nb2 = (long long) a->nb02;
+        q.a_nb1 = (long long) a->nb11; q.a_nb2 = (long long) a->nb12;
+        q.d_nb1 = (long long) a->nb1;  q.d_nb2 = (long long) a->nb2;
+        q.ids = ids; q.ids_nb1 = (long long) a->ids_nb1; q.n_expert = a->n_expert; q.n_used = a->n_used; q.n_tokens = a->n_tokens;
+        q.b_bcast = a->b_ne1 == 1;
+        std::string err;
+        if (int rc = mxf_launch(q, workspace, (cudaStream_t) stream, di.sms, err)) return fail(rc, "%s", err.c_str());
+        return 0;
+    }
     if (moe_use_mmq(a)) {
         const size_t need = mmq_moe_workspace_bytes(a->k, a->n_tokens, a->n_used, a->n_expert);
         if (!workspace || workspace_bytes < need) {
