@@ -22,11 +22,13 @@ LIB_PATH = os.environ.get("B200Q_LIB", os.path.join(os.path.dirname(_HERE), "lib
 # ggml_type numbers
 F32, Q4_0, Q4_1, Q5_0, Q5_1, Q8_0, Q4_K, Q5_K, Q6_K, MXFP4 = 0, 2, 3, 6, 7, 8, 12, 13, 14, 39
 Q2_K, Q3_K, IQ4_NL, IQ4_XS = 10, 11, 20, 23
+F16, BF16 = 1, 30  # unquantized weights (MUL_MAT / GET_ROWS): rows of plain values, any k
 TYPE_NAMES = {Q4_0: "q4_0", Q4_1: "q4_1", Q5_0: "q5_0", Q5_1: "q5_1", Q8_0: "q8_0", Q4_K: "q4_K", Q5_K: "q5_K",
-              Q6_K: "q6_K", MXFP4: "mxfp4", Q2_K: "q2_K", Q3_K: "q3_K", IQ4_NL: "iq4_nl", IQ4_XS: "iq4_xs"}
+              Q6_K: "q6_K", MXFP4: "mxfp4", Q2_K: "q2_K", Q3_K: "q3_K", IQ4_NL: "iq4_nl", IQ4_XS: "iq4_xs",
+              F16: "f16", BF16: "bf16", F32: "f32"}
 BLCK = {Q4_0: (32, 18), Q4_1: (32, 20), Q5_0: (32, 22), Q5_1: (32, 24), Q8_0: (32, 34), MXFP4: (32, 17),
         Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210), F32: (1, 4), Q2_K: (256, 84), Q3_K: (256, 110),
-        IQ4_NL: (32, 18), IQ4_XS: (256, 136)}
+        IQ4_NL: (32, 18), IQ4_XS: (256, 136), F16: (1, 2), BF16: (1, 2)}
 
 FLAG_WEIGHTS_IMMUTABLE, FLAG_FORCE_GEMV, FLAG_FORCE_MMQ, FLAG_NO_PDL = 1, 2, 4, 8
 

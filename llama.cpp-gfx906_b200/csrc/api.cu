@@ -8,6 +8,7 @@
 #include "gemv_kq.cuh"
 #include "gemv_list.cuh"
 #include "gemv_mma.cuh"
+#include "dense_mm.cuh"
 #include "mmq.cuh"
 #include "mmq_mxf.cuh"
 
@@ -648,9 +649,11 @@ int b200q_memcpy_peer(void * dst, int dst_device, const void * src, int src_devi
     return 0;
 }
 
-int64_t b200q_blck_size(int type) { return blck_elems(type); }
-size_t  b200q_type_size(int type) { return (size_t) blck_bytes(type); }
+// ggml's numbers: f16 / bf16 are plain values (the 32-value pseudo blocks the tensor-core kernel reads them in are internal)
+int64_t b200q_blck_size(int type) { return (type == T_F16 || type == T_BF16) ? 1 : blck_elems(type); }
+size_t  b200q_type_size(int type) { return (type == T_F16 || type == T_BF16) ? 2 : (size_t) blck_bytes(type); }
 size_t  b200q_row_size(int type, int64_t ne0) {
+    if (type == T_F16 || type == T_BF16) return (size_t) ne0 * 2;  // plain values (the 32-value pseudo blocks are a kernel detail)
     const int be = blck_elems(type);
     return be ? (size_t) (ne0 / be) * (size_t) blck_bytes(type) : 0;
 }
@@ -747,10 +750,10 @@ static int check_mm(const b200q_mul_mat_args * a) {
     if (!a) return fail(B200Q_EINVAL, "mul_mat: null args");
     const int be = blck_elems(wtype(a->type));
     if (!be || a->type == T_F32W) return fail(B200Q_ENOTSUP, "mul_mat: unsupported weight type %d", a->type);
-    if (dense_type(wtype(a->type)) && a->k % 64) {
-        return fail(B200Q_ENOTSUP, "mul_mat: f16 / bf16 / f32 weights need k %% 64 == 0 (k=%lld)", (long long) a->k);
+    // unquantized weights: any k (dense_mm.cu takes what the tensor-core kernel's 64-element chunks do not)
+    if (a->k <= 0 || (!dense_type(wtype(a->type)) && a->k % be)) {
+        return fail(B200Q_EINVAL, "mul_mat: k=%lld not a positive multiple of %d", (long long) a->k, be);
     }
-    if (a->k <= 0 || a->k % be) return fail(B200Q_EINVAL, "mul_mat: k=%lld not a positive multiple of %d", (long long) a->k, be);
     if (a->m < 0 || a->n < 0) return fail(B200Q_EINVAL, "mul_mat: negative dimension");
     if (a->ne02 <= 0 || a->ne03 <= 0 || a->ne12 <= 0 || a->ne13 <= 0 || a->ne12 % a->ne02 || a->ne13 % a->ne03) {
         return fail(B200Q_EINVAL, "mul_mat: bad batch dims");
@@ -758,8 +761,15 @@ static int check_mm(const b200q_mul_mat_args * a) {
     return 0;
 }
 
+// unquantized weights: few columns (one pass over the rows, HBM-bound) or a k the 64-element chunks do not divide go to the
+// CUDA-core kernel of dense_mm.cu; everything else to the tensor-core kernel
+static bool use_dense(const b200q_mul_mat_args * a) {
+    if (!dense_type(wtype(a->type))) return false;
+    if (a->flags & B200Q_FLAG_FORCE_MMQ) return a->k % 64 != 0;
+    return a->n <= 8 || a->k % 64 != 0;
+}
 static bool use_mmq(const b200q_mul_mat_args * a) {
-    if (dense_type(wtype(a->type))) return true;  // unquantized weights: always the tensor-core kernel (no integer dot exists)
+    if (dense_type(wtype(a->type))) return !use_dense(a);
     if (a->flags & B200Q_FLAG_FORCE_GEMV) return false;
     if (a->flags & B200Q_FLAG_FORCE_MMQ) return mmq_supported(a->type, a->k);
     // from this many columns on the tensor-core kernel (dequantize to bf16 + tcgen05: ~flat in n below 64 columns) beats
@@ -803,6 +813,18 @@ int b200q_mul_mat(const b200q_mul_mat_args * a, const void * w, const float * ac
     const DevInfo & di = dev_info();
     if (!di.ok) return fail(B200Q_ENODEVICE, "mul_mat: no CUDA device");
 
+    if (use_dense(a)) {
+        if (!dense_mm_supported(wtype(a->type), a->k, a->m, a->n, a->ne12 * a->ne13)) return fail(B200Q_ENOTSUP, "mul_mat: dense shape out of range");
+        MmqArgs q{};
+        q.type = wtype(a->type); q.k = a->k; q.m = a->m; q.n = a->n;
+        q.ne02 = a->ne02; q.ne03 = a->ne03; q.ne12 = a->ne12; q.ne13 = a->ne13;
+        q.w_nb1 = (long long) a->nb01; q.w_nb2 = (long long) a->nb02; q.w_nb3 = (long long) a->nb03;
+        q.a_nb1 = (long long) a->nb11; q.a_nb2 = (long long) a->nb12; q.a_nb3 = (long long) a->nb13;
+        q.d_nb1 = (long long) a->nb1;  q.d_nb2 = (long long) a->nb2;  q.d_nb3 = (long long) a->nb3;
+        q.w = (const uint8_t *) w; q.act = act; q.dst = dst;
+        if (int rc = dense_mm_launch(q, st)) return fail(rc, "mul_mat: dense launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+        return 0;
+    }
     if (use_mxf(a)) {
         const size_t need = mxf_workspace_bytes(a->k, a->n);
         if (workspace_bytes < need || !workspace) return fail(B200Q_EWORKSPACE, "mul_mat: workspace %zu < required %zu", workspace_bytes, need);

@@ -442,6 +442,8 @@ bool type_ok(ggml_type t) { return b200q_type_supported((int) t) != 0; }
 // unquantized weights go through the tensor-core kernel in 64-element chunks
 bool dense_weight(ggml_type t) { return t == GGML_TYPE_F16 || t == GGML_TYPE_BF16 || t == GGML_TYPE_F32; }
 bool weight_ok(const ggml_tensor * a) { return (type_ok(a->type) || a->type == GGML_TYPE_F32) && (!dense_weight(a->type) || a->ne[0] % 64 == 0); }
+// MUL_MAT takes unquantized weights with any k (dense_mm.cu: the attention products), MUL_MAT_ID and split weights do not
+bool mul_mat_weight_ok(const ggml_tensor * a) { return dense_weight(a->type) || weight_ok(a); }
 
 bool rows_dense(const ggml_tensor * t) { return t->nb[0] == ggml_type_size(t->type); }
 
@@ -452,9 +454,11 @@ bool tensor_is_split(const ggml_tensor * t) { return t->buffer && buft_is_split(
 bool supports_mul_mat(const b200_device_ctx * dev, const ggml_tensor * op) {
     const ggml_tensor * a = op->src[0];
     const ggml_tensor * b = op->src[1];
-    if (!weight_ok(a) || b->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
+    // f16 activations are converted to f32 first (the reference converts src1 as well: ggml-cuda.cu:1237-1262, 1489-1505)
+    if (!mul_mat_weight_ok(a) || (b->type != GGML_TYPE_F32 && b->type != GGML_TYPE_F16) || op->type != GGML_TYPE_F32) return false;
     if (tensor_is_split(a)) {
         // row-split weights: plain 2-D matrices only, and the device that runs the op must own rows (ggml-cuda.cu:3270-3283)
+        if (!weight_ok(a) || b->type != GGML_TYPE_F32) return false;
         if (a->ne[2] > 1 || a->ne[3] > 1 || !ggml_is_contiguous(b) || !ggml_is_contiguous(op)) return false;
         int64_t lo, hi;
         split_rows((const b200_split_buft_ctx *) a->buffer->buft->context, ggml_nrows(a), dev->index, &lo, &hi);
@@ -710,6 +714,7 @@ int compute_mul_mat_split(b200_backend_ctx * ctx, const ggml_tensor * op) {
     return 0;
 }
 
+b200q_tensor bt(const ggml_tensor * t);
 int compute_mul_mat(b200_backend_ctx * ctx, const ggml_tensor * op) {
     const ggml_tensor * a = op->src[0];
     const ggml_tensor * b = op->src[1];
@@ -722,9 +727,23 @@ int compute_mul_mat(b200_backend_ctx * ctx, const ggml_tensor * op) {
     q.nb11 = b->nb[1]; q.nb12 = b->nb[2]; q.nb13 = b->nb[3];
     q.nb1 = op->nb[1]; q.nb2 = op->nb[2]; q.nb3 = op->nb[3];
     q.flags = weight_flags(a);
+    size_t conv = 0;  // f16 activations: a contiguous f32 copy at the head of the workspace
+    if (b->type == GGML_TYPE_F16) {
+        conv   = ((size_t) ggml_nelements(b) * sizeof(float) + 255) & ~(size_t) 255;
+        q.nb11 = (size_t) b->ne[0] * sizeof(float); q.nb12 = q.nb11 * b->ne[1]; q.nb13 = q.nb12 * b->ne[2];
+    }
     const size_t need = b200q_mul_mat_workspace(&q);
-    void *       ws   = need ? backend_workspace(ctx, need) : nullptr;
-    return b200q_mul_mat(&q, a->data, (const float *) b->data, (float *) op->data, ws, ctx->ws_bytes, ctx->stream);
+    char *       ws   = need + conv ? (char *) backend_workspace(ctx, need + conv) : nullptr;
+    const float * act = (const float *) b->data;
+    if (conv) {
+        const b200q_tensor src = bt(b);
+        b200q_tensor       dst = src;
+        dst.data = ws; dst.type = B200Q_TYPE_F32;
+        dst.nb[0] = sizeof(float); dst.nb[1] = q.nb11; dst.nb[2] = q.nb12; dst.nb[3] = q.nb13;
+        if (int rc = b200q_op_cpy(&src, &dst, ctx->stream)) return rc;
+        act = (const float *) ws;
+    }
+    return b200q_mul_mat(&q, a->data, act, (float *) op->data, need ? ws + conv : nullptr, need ? ctx->ws_bytes - conv : 0, ctx->stream);
 }
 int compute_mul_mat_id(b200_backend_ctx * ctx, const ggml_tensor * op) {
     const ggml_tensor *   as  = op->src[0];
