@@ -189,7 +189,13 @@ B200Q_API int b200q_mul_mat_group(const b200q_mul_mat_group_args * a, const void
  *      peer GPU as well (NVLink peer stores in the epilogue), so no collective follows the matmul.  peer_delta[r] =
  *      (this process's mapping of peer r's dst buffer) - (this GPU's own dst buffer), in bytes; the buffers have the
  *      same layout.  The stores are complete when the kernel is: consumers on the peer need a stream-ordered
- *      cross-GPU fence (e.g. one small collective per step).  b200q_ipc_* exchange the mappings (cudaIpc). ---------- */
+ *      cross-GPU fence (e.g. one small collective per step).  REUSE RULE: that fence orders the stores before the peers'
+ *      reads only; a rank that has passed it may launch the next step, whose epilogues overwrite the same rows of the
+ *      peers' buffers — a peer still reading the previous step's rows needs a second (consumer-done) fence before the
+ *      buffer is reused, or one dst region per step.  Inside a persistent list (b200q_list_*, below) the rule holds by
+ *      construction — every in-list reader of a vector has passed a barrier point before any rank can store into it
+ *      again; kernels that read a list's results after the launch fall under the rule above (alternate two dst buffers).
+ *      b200q_ipc_* exchange the mappings (cudaIpc). ------------------------------------------------------------------- */
 B200Q_API int b200q_mul_mat_group_peers(const b200q_mul_mat_group_args * a, const void * const * w, const float * act,
                                         float * const * dst, int n_peers, const int64_t * peer_delta, void * stream);
 B200Q_API int b200q_ipc_export(void * dev_ptr, void * handle64);          /* dev_ptr from b200q_malloc; 64-byte handle */

@@ -8,6 +8,7 @@
 #include "gemv_kq.cuh"
 #include "gemv_list.cuh"
 #include "gemv_mma.cuh"
+#include "../../include/b200q_debug.h"
 #include "dense_mm.cuh"
 #include "mmq.cuh"
 #include "mmq_mxf.cuh"

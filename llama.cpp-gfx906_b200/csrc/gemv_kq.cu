@@ -40,7 +40,9 @@ constexpr uint32_t OFF_FULL = 0;  // full-barriers (8 B each, MAX_S of them); da
 
 extern __shared__ __align__(128) uint8_t kq_smem[];
 
-// development aid: a host-mapped buffer that stuck waiters report into (b200q_debug_hang_buffer)
+// development aid, compiled only with -DB200Q_DEBUG_HANG: a host-mapped buffer that stuck waiters report into
+// (b200q_debug_hang_buffer); the release kernel neither reads the pointer nor spins with a counter
+#ifdef B200Q_DEBUG_HANG
 __device__ unsigned long long * g_kq_hang = nullptr;
 __device__ __forceinline__ void mbar_wait_dbg(uint32_t bar, uint32_t parity, int tag, int j) {
     unsigned long long * hb = g_kq_hang;
@@ -69,6 +71,11 @@ __device__ __forceinline__ void mbar_wait_dbg(uint32_t bar, uint32_t parity, int
         }
     }
 }
+#define KQ_HANG_COUNT(i) do { if (g_kq_hang && threadIdx.x == 0) atomicAdd(g_kq_hang + (i), 1ull); } while (0)
+#else
+__device__ __forceinline__ void mbar_wait_dbg(uint32_t bar, uint32_t parity, int, int) { mbar_wait(bar, parity); }
+#define KQ_HANG_COUNT(i) do { } while (0)
+#endif
 
 template <int T> struct IsKQuant { static constexpr bool value = T == T_Q4_K || T == T_Q6_K; };
 
@@ -112,7 +119,7 @@ template <int T, bool MOE> __global__ void __launch_bounds__(NTHREADS, 2) gemv_k
     // this CTA's contiguous range of stages
     const int T0 = (int) ((long long) p.total_stages * blockIdx.x / gridDim.x);
     const int T1 = (int) ((long long) p.total_stages * (blockIdx.x + 1) / gridDim.x);
-    if (g_kq_hang && threadIdx.x == 0) atomicAdd(g_kq_hang + 2041, 1ull);  // CTAs started
+    KQ_HANG_COUNT(2041);  // CTAs started
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < S; ++s) {
@@ -202,7 +209,7 @@ template <int T, bool MOE> __global__ void __launch_bounds__(NTHREADS, 2) gemv_k
             }
         }
     }
-    if (g_kq_hang && threadIdx.x == 0) atomicAdd(g_kq_hang + 2042, 1ull);  // warp 0 of a CTA done
+    KQ_HANG_COUNT(2042);  // warp 0 of a CTA done
 }
 
 }  // namespace
@@ -223,7 +230,11 @@ template <bool MOE> static kq_kernel_t kq_kernel_sel(int type) {
 kq_kernel_t kq_kernel_for(int type, bool moe) { return moe ? kq_kernel_sel<true>(type) : kq_kernel_sel<false>(type); }
 int         kq_max_segments(bool moe) { return moe ? KQ_MAX_SEG : KQ_PLAIN_SEG; }
 void kq_set_hang_buffer(unsigned long long * host_mapped) {
+#ifdef B200Q_DEBUG_HANG
     cudaMemcpyToSymbol(g_kq_hang, &host_mapped, sizeof(host_mapped));
+#else
+    (void) host_mapped;  // release build: the kernels carry no hang reporting
+#endif
 }
 int kq_threads() { return NTHREADS; }
 int kq_consumer_warps() { return kqdot::NW; }

@@ -32,6 +32,18 @@ def test_library_exports_every_declared_symbol():
     assert set(declared("b200q.h")) - set(b200q.EXPORTS) <= set(n for n in declared("b200q.h") if "rowsplit" in n or "graph" in n or "route" in n)
 
 
+def test_debug_header_matches_the_library():
+    """development aids are declared too (include/b200q_debug.h): nothing is exported without a declaration"""
+    import subprocess
+    import b200q
+    L = ctypes.CDLL(b200q.LIB_PATH)
+    dbg = declared("b200q_debug.h")
+    assert dbg and not [n for n in dbg if not hasattr(L, n)]
+    out = subprocess.run(["nm", "-D", "--defined-only", b200q.LIB_PATH], capture_output=True, text=True).stdout
+    exported = set(re.findall(r"\b(b200q_\w+)\b", out))
+    assert exported <= set(declared("b200q.h")) | set(dbg), exported - set(declared("b200q.h")) - set(dbg)
+
+
 def test_type_table_matches_ggml_block_sizes():
     import b200q
     L = b200q.lib()
