@@ -525,7 +525,7 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
                     const uint32_t full = bars + 8 * (BAR_B_FULL + slot);
                     const uint32_t dst  = base + p.off_b + (uint32_t) slot * (uint32_t) p.b_stage_bytes + doff;
                     if (elect_one()) {
-                        dbg_stamp(p, c, 7);
+                        if (!(DEVF & 1024)) dbg_stamp(p, c, 7);
                         if ((DEVF & 4) && issued >= p.b_stages) {
                             mbar_arrive(full);
                         } else if (p.cluster == 1) {
@@ -565,14 +565,28 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
                 }
                 mbar_wait(bars + 8 * (BAR_ACC_EMPTY + abi), aph ^ 1);
                 tc_fence_after();
+                // The commits of chunk c are issued right in FRONT of the MMAs of chunk c + 1 (and after the last chunk of the
+                // unit), not behind their own MMAs: the tcgen05 queue is in order and only a few entries deep, so a commit
+                // behind eight 128-cycle MMAs blocks the issuing warp until most of them have run, and the warp's own work
+                // for the next chunk (ring counters, two barrier waits, descriptors: ~500 cycles) then starts with a nearly
+                // empty queue — the tensor pipe idled ~500 of every 1500 cycles (profiles/r02_mmq_dev_v2.txt).  Deferred,
+                // the commits still complete when their MMAs do (they are queued before those finish), and the warp does
+                // its bookkeeping while four MMAs are still queued.
+                uint32_t pend_a = 0, pend_b = 0;
                 for (int c = tc.c0; c < tc.c1; ++c, ++g) {
                     if (lane == 0) dbg_stamp(p, g, 0);
                     mbar_wait(bars + 8 * (BAR_A_FULL + aslot), a_ph);
                     if (lane == 0) dbg_stamp(p, g, 1);
                     if (!(DEVF & 128)) mbar_wait(bars + 8 * (BAR_B_FULL + bslot), b_ph);
+                    if (lane == 0) dbg_stamp(p, g, 2);
                     // no tcgen05.fence here: operands arrive through shared memory (mbarrier-ordered); the fence is only
                     // needed around TMEM hand-offs (accumulator release above)
                     if (elect_one()) {
+                        if (pend_a) {
+                            if (p.cluster == 1) umma_commit(pend_b);
+                            else umma_commit_multicast(pend_b, cmask);
+                            umma_commit(pend_a);
+                        }
                         if (!(DEVF & 32)) {
 #pragma unroll
                             for (int sn = 0; sn < 2; ++sn) {
@@ -587,12 +601,18 @@ template <int T> __global__ void __launch_bounds__(NTHREADS, 1) mmq_kernel(const
                                 }
                             }
                         }
-                        if (p.cluster == 1) umma_commit(bars + 8 * (BAR_B_EMPTY + bslot));
-                        else umma_commit_multicast(bars + 8 * (BAR_B_EMPTY + bslot), cmask);
-                        umma_commit(bars + 8 * (BAR_A_EMPTY + aslot));
-                        if (c == tc.c1 - 1) umma_commit(bars + 8 * (BAR_ACC_FULL + abi));
+                        if (DEVF & 1024) dbg_stamp(p, g, 7);  // timing aid: MMAs issued (replaces the B producer's stamp)
+                        if (c == tc.c1 - 1) {  // end of the unit: nothing follows to hide behind
+                            if (p.cluster == 1) umma_commit(bars + 8 * (BAR_B_EMPTY + bslot));
+                            else umma_commit_multicast(bars + 8 * (BAR_B_EMPTY + bslot), cmask);
+                            umma_commit(bars + 8 * (BAR_A_EMPTY + aslot));
+                            umma_commit(bars + 8 * (BAR_ACC_FULL + abi));
+                        }
                     }
                     __syncwarp();
+                    pend_a = bars + 8 * (BAR_A_EMPTY + aslot);
+                    pend_b = bars + 8 * (BAR_B_EMPTY + bslot);
+                    if (c == tc.c1 - 1) pend_a = 0;
                     if (lane == 0) dbg_stamp(p, g, 3);
                     bdesc += (uint64_t) (p.b_stage_bytes >> 4);
                     if (++bslot == p.b_stages) {

@@ -22,7 +22,7 @@ T = buf.cpu().numpy().reshape(256, 8)
 t0 = T[0, 0]
 ph = T[255]
 print("phases (ns from kernel begin): setup done %d, mma last commit %d, acc ready seen by epilogue %d, epilogue done %d, all warps done %d" % tuple(int(ph[i] - ph[0]) for i in range(1, 6)))
-names = ["mma:wait", "mma:A ok", "mma:issued", "mma:commit", "dq:start", "dq:done", "dq:slot free", "B:slot free"]
+names = ["mma:wait", "mma:A ok", "mma:B ok", "mma:commit", "dq:start", "dq:done", "dq:slot free", "B:free|mma:iss"]
 print("chunk " + " ".join(f"{x:>12s}" for x in names))
 for g in list(range(0, 20)) + list(range(56, 64)):
     print(f"{g:5d} " + " ".join(f"{int(T[g, j] - t0):12d}" for j in range(8)))
