@@ -107,6 +107,13 @@ B200Q_API int b200q_host_free(void * ptr);
 /* events, cross-stream ordering, peer mappings (cudaEvent* / cudaStreamWaitEvent / cudaDeviceEnablePeerAccess /
  * cudaMemcpyPeerAsync of ggml-cuda.cu:1358-1414, 2556-2605, 3038-3060): what the plugin's events, cpy_tensor_async and
  * single-process row split are built from */
+/* ---- stream capture: the plugin records a decode step's launches once and replays them as ONE CUDA graph (the reference's
+ *      cudaGraph path, ggml-cuda.cu:2876-3100).  begin/end bracket ordinary calls of this library on `stream`; calls that
+ *      synchronise or allocate (a workspace that has to grow) are not capturable — run the step once eagerly first. -------- */
+B200Q_API int b200q_graph_begin(void * stream);
+B200Q_API int b200q_graph_end(void * stream, void ** exec_out);   /* instantiated graph; NULL + error if the capture broke */
+B200Q_API int b200q_graph_launch(void * exec, void * stream);
+B200Q_API int b200q_graph_destroy(void * exec);
 B200Q_API int b200q_event_create(void ** event);                     /* on the current device, timing disabled */
 B200Q_API int b200q_event_destroy(void * event);
 B200Q_API int b200q_event_record(void * event, void * stream);
@@ -295,6 +302,8 @@ B200Q_API int b200q_op_soft_max(const b200q_tensor * src, const b200q_tensor * m
 B200Q_API int b200q_op_rope(const b200q_tensor * src, const b200q_tensor * pos, const b200q_tensor * freq_factors /* or NULL */,
                             const b200q_tensor * dst, const b200q_rope_params * p, void * stream);                         /* rope.cu */
 B200Q_API int b200q_op_cpy(const b200q_tensor * src, const b200q_tensor * dst, void * stream);       /* cpy.cu: CPY / CONT / DUP */
+B200Q_API int b200q_op_add_id(const b200q_tensor * a, const b200q_tensor * b, const b200q_tensor * ids, const b200q_tensor * dst,
+                              void * stream);  /* dst[i0,i1,i2] = a[i0,i1,i2] + b[i0, ids[i1,i2]] (MoE expert bias)      add-id.cu */
 B200Q_API int b200q_op_set_rows(const b200q_tensor * src, const b200q_tensor * idx, const b200q_tensor * dst,
                                 void * stream);                                                                            /* set-rows.cu */
 

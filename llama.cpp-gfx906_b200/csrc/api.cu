@@ -618,6 +618,40 @@ int b200q_stream_destroy(void * stream) { CUDA_TRY(cudaStreamDestroy((cudaStream
 int b200q_stream_synchronize(void * stream) { CUDA_TRY(cudaStreamSynchronize((cudaStream_t) stream)); return 0; }
 int b200q_host_alloc(void ** ptr, size_t bytes) { CUDA_TRY(cudaMallocHost(ptr, bytes)); return 0; }
 int b200q_host_free(void * ptr) { CUDA_TRY(cudaFreeHost(ptr)); return 0; }
+// ---- CUDA-graph capture of a stream's work (the plugin replays a decode step's launches as one graph; replaces the
+//      reference's cudaGraph path, ggml-cuda.cu:2876-3100) -----------------------------------------------------------------
+int b200q_graph_begin(void * stream) {
+    CUDA_TRY(cudaStreamBeginCapture((cudaStream_t) stream, cudaStreamCaptureModeRelaxed));
+    return 0;
+}
+int b200q_graph_end(void * stream, void ** exec_out) {
+    if (!exec_out) return fail(B200Q_EINVAL, "graph_end: null output");
+    *exec_out = nullptr;
+    cudaGraph_t g = nullptr;
+    cudaError_t e = cudaStreamEndCapture((cudaStream_t) stream, &g);
+    if (e != cudaSuccess || !g) {
+        cudaGetLastError();
+        return fail(B200Q_ECUDA, "graph_end: capture failed: %s", cudaGetErrorString(e));
+    }
+    cudaGraphExec_t x = nullptr;
+    e = cudaGraphInstantiate(&x, g, 0);
+    cudaGraphDestroy(g);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(B200Q_ECUDA, "graph_end: instantiate failed: %s", cudaGetErrorString(e));
+    }
+    *exec_out = (void *) x;
+    return 0;
+}
+int b200q_graph_launch(void * exec, void * stream) {
+    if (!exec) return fail(B200Q_EINVAL, "graph_launch: null graph");
+    CUDA_TRY(cudaGraphLaunch((cudaGraphExec_t) exec, (cudaStream_t) stream));
+    return 0;
+}
+int b200q_graph_destroy(void * exec) {
+    if (exec) CUDA_TRY(cudaGraphExecDestroy((cudaGraphExec_t) exec));
+    return 0;
+}
 int b200q_event_create(void ** event) {
     cudaEvent_t e = nullptr;
     CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));

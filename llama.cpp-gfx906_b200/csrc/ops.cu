@@ -292,6 +292,19 @@ template <int TD> __global__ void __launch_bounds__(256) set_rows_kernel(T4 s, T
     }
 }
 
+// ---- ADD_ID: dst[i0, i1, i2] = a[i0, i1, i2] + b[i0, ids[i1, i2]] (the per-expert bias of a MoE layer; add-id.cu) ----------------
+__global__ void __launch_bounds__(256) add_id_kernel(T4 a, T4 b, T4 ids, T4 d, long long n) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
+        long long r = i;
+        const long long i0 = r % a.ne[0]; r /= a.ne[0];
+        const long long i1 = r % a.ne[1], i2 = r / a.ne[1];
+        const int e = *(const int *) (ids.data + i1 * ids.nb[0] + i2 * ids.nb[1]);
+        const float x = *(const float *) (a.data + i0 * 4 + i1 * a.nb[1] + i2 * a.nb[2]);
+        const float y = *(const float *) (b.data + i0 * 4 + (long long) e * b.nb[1]);
+        *(float *) (d.data + i0 * 4 + i1 * d.nb[1] + i2 * d.nb[2]) = x + y;
+    }
+}
+
 template <int TS> int cpy_to(const b200q_tensor * s, const b200q_tensor * d, long long n, cudaStream_t st) {
     const int g = grid_for(n, 256);
     switch (d->type) {
@@ -439,6 +452,18 @@ int b200q_op_cpy(const b200q_tensor * src, const b200q_tensor * dst, void * stre
         case B200Q_TYPE_BF16: return cpy_to<B200Q_TYPE_BF16>(src, dst, n, (cudaStream_t) stream);
         default: return ops_fail(B200Q_ENOTSUP, "cpy: source type");
     }
+}
+
+int b200q_op_add_id(const b200q_tensor * a, const b200q_tensor * b, const b200q_tensor * ids, const b200q_tensor * dst, void * stream) {
+    if (!a || !b || !ids || !dst || a->type != B200Q_TYPE_F32 || b->type != B200Q_TYPE_F32 || ids->type != B200Q_TYPE_I32 ||
+        dst->type != B200Q_TYPE_F32 || a->nb[0] != 4 || b->nb[0] != 4 || dst->nb[0] != 4 || a->ne[3] != 1 || b->ne[0] != a->ne[0] ||
+        ids->ne[0] != a->ne[1] || ids->ne[1] != a->ne[2] || nelem(a) != nelem(dst)) {
+        return ops_fail(B200Q_ENOTSUP, "add_id: a f32 [n, used, tokens], b f32 [n, experts], ids i32 [used, tokens]");
+    }
+    const long long n = nelem(a);
+    if (n == 0) return 0;
+    add_id_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t) stream>>>(t4(a), t4(b), t4(ids), t4(dst), n);
+    return launched();
 }
 
 int b200q_op_set_rows(const b200q_tensor * src, const b200q_tensor * idx, const b200q_tensor * dst, void * stream) {

@@ -90,7 +90,16 @@ struct b200_backend_ctx {
     // rebuilds its graph for every token but ggml-alloc hands out the same addresses
     std::map<std::vector<int64_t>, b200q_list *> lists;
     std::vector<std::vector<int64_t>>            list_order;  // insertion order, for eviction
+    // CUDA-graph replay of a whole ggml graph (decode steps): the launches of a graph whose nodes, shapes, addresses and
+    // parameters equal the previous call's are captured on the second sighting and replayed from the third on
+    // (ggml-cuda.cu:2876-3100 does the same with cudaGraphExecUpdate; here a changed graph is simply re-captured)
+    // (several graphs alternate when the scheduler cuts a model into splits: a small cache keyed by the fingerprint)
+    struct graph_entry { void * exec = nullptr; int seen = 0; };
+    std::map<std::vector<uint64_t>, graph_entry> graphs;
+    std::vector<std::vector<uint64_t>>           graph_order;  // insertion order, for eviction
+    bool                                         graphs_off = false;  // a capture broke once: stay eager
 };
+constexpr size_t MAX_CACHED_GRAPHS = 256;
 constexpr size_t MAX_CACHED_LISTS = 512;
 
 void * device_xfer_stream(b200_device_ctx * d) {
@@ -563,6 +572,11 @@ bool supports_elementwise(const ggml_tensor * op) {
         }
         case GGML_OP_CPY: case GGML_OP_CONT: case GGML_OP_DUP:
             return float_type(a->type) && float_type(op->type) && ggml_nelements(a) == ggml_nelements(op);
+        case GGML_OP_ADD_ID: {  // a [n, used, tokens] + b [n, experts] picked by ids [used, tokens] (add-id.cu; ggml-cuda.cu:3455)
+            const ggml_tensor * ids = op->src[2];
+            return is_f32(a) && is_f32(b) && ids && ids->type == GGML_TYPE_I32 && is_f32(op) && a->nb[0] == 4 && b->nb[0] == 4 &&
+                   op->nb[0] == 4 && a->ne[3] == 1 && b->ne[0] == a->ne[0] && ids->ne[0] == a->ne[1] && ids->ne[1] == a->ne[2];
+        }
         case GGML_OP_SET_ROWS:
             return is_f32(a) && b && b->type == GGML_TYPE_I64 && float_type(op->type) && a->ne[0] == op->ne[0] && a->ne[2] == op->ne[2] &&
                    a->ne[3] == op->ne[3] && b->ne[0] == a->ne[1] && a->ne[2] % b->ne[1] == 0 && a->ne[3] % b->ne[2] == 0;
@@ -600,6 +614,7 @@ int compute_elementwise(b200_backend_ctx * ctx, const ggml_tensor * op) {
         }
         case GGML_OP_CPY: case GGML_OP_CONT: case GGML_OP_DUP: return b200q_op_cpy(&ta, &td, ctx->stream);
         case GGML_OP_SET_ROWS: return b200q_op_set_rows(&ta, &tb, &td, ctx->stream);
+        case GGML_OP_ADD_ID:   return b200q_op_add_id(&ta, &tb, &tc, &td, ctx->stream);
         default: return B200Q_ENOTSUP;
     }
 }
@@ -619,8 +634,19 @@ bool device_supports_op(ggml_backend_dev_t dev, const ggml_tensor * op) {
     }
 }
 
+// recorded graphs hold the workspace and the persistent lists by address: when either goes away, so do the graphs
+void drop_graphs(b200_backend_ctx * ctx) {
+    bool any = false;
+    for (auto & kv : ctx->graphs) any = any || kv.second.exec;
+    if (any) B200_CHECK(b200q_stream_synchronize(ctx->stream));
+    for (auto & kv : ctx->graphs) if (kv.second.exec) b200q_graph_destroy(kv.second.exec);
+    ctx->graphs.clear();
+    ctx->graph_order.clear();
+}
+
 void * backend_workspace(b200_backend_ctx * ctx, size_t need) {
     if (need > ctx->ws_bytes) {
+        drop_graphs(ctx);
         if (ctx->workspace) {
             B200_CHECK(b200q_stream_synchronize(ctx->stream));
             B200_CHECK(b200q_free(ctx->workspace));
@@ -789,6 +815,7 @@ void backend_free(ggml_backend_t backend) {
         if (ctx->split_start) b200q_event_destroy(ctx->split_start);
         b200q_stream_destroy(ctx->stream);
     }
+    for (auto & kv : ctx->graphs) if (kv.second.exec) b200q_graph_destroy(kv.second.exec);
     for (auto & kv : ctx->lists) if (kv.second) b200q_list_destroy(kv.second);
     for (int id = 0; id < MAX_DEVICES; ++id) {
         b200_split_peer & pe = ctx->peers[id];
@@ -913,6 +940,7 @@ int compute_list_run(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int first, in
             auto old = ctx->lists.find(ctx->list_order.front());
             if (old != ctx->lists.end()) {
                 if (old->second) {
+                    drop_graphs(ctx);
                     B200_CHECK(b200q_stream_synchronize(ctx->stream));
                     b200q_list_destroy(old->second);
                 }
@@ -928,11 +956,95 @@ int compute_list_run(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int first, in
     return end;
 }
 
+ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph);
+// statistics for tests and tuning (get_proc_address "ggml_backend_b200_graph_stats"): graphs recorded, graphs replayed
+int64_t g_graph_stats[2] = { 0, 0 };
+void    graph_stats(int64_t * recorded, int64_t * replayed) { *recorded = g_graph_stats[0]; *replayed = g_graph_stats[1]; }
+
+// everything a launch bakes into its arguments: op, types, shapes, strides, addresses, parameters of every node and source
+void graph_fingerprint(const ggml_cgraph * cgraph, std::vector<uint64_t> & key, bool * capturable) {
+    const int n_nodes = ggml_graph_n_nodes((ggml_cgraph *) cgraph);
+    key.clear();
+    key.reserve((size_t) n_nodes * 24);
+    *capturable = true;
+    auto put_tensor = [&](const ggml_tensor * t) {
+        key.push_back((uint64_t) (uintptr_t) t->data);
+        key.push_back((uint64_t) t->type);
+        for (int d = 0; d < 4; ++d) { key.push_back((uint64_t) t->ne[d]); key.push_back((uint64_t) t->nb[d]); }
+    };
+    for (int i = 0; i < n_nodes; ++i) {
+        const ggml_tensor * node = ggml_graph_node((ggml_cgraph *) cgraph, i);
+        key.push_back((uint64_t) node->op);
+        put_tensor(node);
+        uint64_t op[GGML_MAX_OP_PARAMS / sizeof(uint64_t)];
+        memcpy(op, node->op_params, sizeof(op));
+        for (uint64_t v : op) key.push_back(v);
+        for (int j = 0; j < GGML_MAX_SRC; ++j) {
+            if (!node->src[j]) { key.push_back(0); continue; }
+            put_tensor(node->src[j]);
+            if (tensor_is_split(node->src[j])) *capturable = false;  // other devices' streams and peer copies: eager
+        }
+    }
+}
+
 // asynchronous: kernels are enqueued on the backend's stream, the caller follows with synchronize()
 // (ggml-backend.cpp:327-335).  Graph and tensor pointers are not retained (they may be stack temporaries).
 ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
     auto * ctx = (b200_backend_ctx *) backend->context;
     B200_CHECK(b200q_set_device(ctx->device));
+    // graphs of a few nodes (test harnesses, prompt chunks that change every call) are not worth a capture
+    const bool try_graph = !ctx->graphs_off && ggml_graph_n_nodes(cgraph) >= 16 && getenv("GGML_B200_NO_GRAPHS") == nullptr;
+    if (!try_graph) return graph_dispatch(ctx, cgraph);
+    std::vector<uint64_t> key;
+    bool capturable = true;
+    graph_fingerprint(cgraph, key, &capturable);
+    if (!capturable) return graph_dispatch(ctx, cgraph);
+    auto it = ctx->graphs.find(key);
+    if (it == ctx->graphs.end()) {  // first sighting: eager (grows workspaces, creates the persistent lists)
+        if (ctx->graphs.size() >= MAX_CACHED_GRAPHS) {
+            auto old = ctx->graphs.find(ctx->graph_order.front());
+            if (old != ctx->graphs.end()) {
+                if (old->second.exec) {
+                    // the graph may still be running on the stream
+                    B200_CHECK(b200q_stream_synchronize(ctx->stream));
+                    b200q_graph_destroy(old->second.exec);
+                }
+                ctx->graphs.erase(old);
+            }
+            ctx->graph_order.erase(ctx->graph_order.begin());
+        }
+        b200_backend_ctx::graph_entry e;
+        e.seen = 1;
+        ctx->graphs.emplace(key, e);
+        ctx->graph_order.push_back(std::move(key));
+        return graph_dispatch(ctx, cgraph);
+    }
+    if (!it->second.exec) {  // second sighting: record
+        if (b200q_graph_begin(ctx->stream) != 0) { ctx->graphs_off = true; return graph_dispatch(ctx, cgraph); }
+        const ggml_status st = graph_dispatch(ctx, cgraph);
+        void * exec = nullptr;
+        const int rc = b200q_graph_end(ctx->stream, &exec);
+        if (st != GGML_STATUS_SUCCESS || rc != 0 || !exec) {
+            fprintf(stderr, "ggml-b200: CUDA-graph capture failed (%s); staying eager\n", b200q_last_error());
+            if (exec) b200q_graph_destroy(exec);
+            ctx->graphs_off = true;
+            return graph_dispatch(ctx, cgraph);
+        }
+        it = ctx->graphs.find(key);  // (the dispatch may have dropped the cache)
+        if (it == ctx->graphs.end()) {
+            b200q_graph_destroy(exec);
+            return graph_dispatch(ctx, cgraph);
+        }
+        it->second.exec = exec;
+        ++g_graph_stats[0];
+    } else {
+        ++g_graph_stats[1];
+    }
+    ++it->second.seen;
+    return b200q_graph_launch(it->second.exec, ctx->stream) == 0 ? GGML_STATUS_SUCCESS : GGML_STATUS_FAILED;
+}
+
+ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
     const int  n_nodes  = ggml_graph_n_nodes(cgraph);
     const bool no_lists = getenv("GGML_B200_NO_LIST") != nullptr;
     for (int i = 0; i < n_nodes; ++i) {
@@ -958,7 +1070,7 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) 
             case GGML_OP_GET_ROWS:   rc = compute_get_rows(ctx, node); break;
             case GGML_OP_RMS_NORM: case GGML_OP_ADD: case GGML_OP_SUB: case GGML_OP_MUL: case GGML_OP_DIV: case GGML_OP_SCALE:
             case GGML_OP_UNARY: case GGML_OP_GLU: case GGML_OP_SOFT_MAX: case GGML_OP_ROPE: case GGML_OP_CPY: case GGML_OP_CONT:
-            case GGML_OP_DUP: case GGML_OP_SET_ROWS:
+            case GGML_OP_DUP: case GGML_OP_SET_ROWS: case GGML_OP_ADD_ID:
                 rc = compute_elementwise(ctx, node);
                 break;
             default:
@@ -1092,6 +1204,7 @@ ggml_backend_feature * get_features(ggml_backend_reg_t) {
 void * reg_get_proc_address(ggml_backend_reg_t, const char * name) {
     if (strcmp(name, "ggml_backend_get_features") == 0) return (void *) get_features;
     if (strcmp(name, "ggml_backend_split_buffer_type") == 0) return (void *) split_buffer_type;  // llama's -sm row
+    if (strcmp(name, "ggml_backend_b200_graph_stats") == 0) return (void *) graph_stats;
     return nullptr;
 }
 

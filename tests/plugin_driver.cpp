@@ -22,6 +22,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <chrono>
 #include <vector>
 
 namespace {
@@ -326,6 +327,61 @@ int pd_decode_run(int dev, int type, int type_v, int64_t k, const void * w1, con
             ggml_tensor * outs[4] = { q, kk, v, o };
             for (int i = 0; i < 4 && rc == 0; ++i) ggml_backend_tensor_get(outs[i], out + i * k, 0, (size_t) k * sizeof(float));
         }
+        if (cbuf) ggml_backend_buffer_free(cbuf);
+        ggml_backend_buffer_free(wbuf);
+    }
+    ggml_backend_free(be);
+    return rc;
+}
+
+// A layer-like graph (rms_norm -> mul_mat -> silu -> mul_mat -> add, `layers` times: >= 16 nodes, so the plugin records it as a
+// CUDA graph on the second pass and replays it from the third) computed `reps` times on inputs x * (rep + 1); out [reps][k].
+// Results must not depend on whether a pass ran eagerly, was being recorded, or was a replay.
+static double g_last_us = 0.0;
+// microseconds per graph_compute + synchronize of the last pd_layer_replay call (mean over passes 4..reps)
+double pd_last_us(void) { return g_last_us; }
+int pd_layer_replay(int dev, int type, int64_t k, int layers, const void * wa, const void * wb, const float * x, int reps, float * out) {
+    if (!g_reg) return -1;
+    ggml_backend_dev_t d  = ggml_backend_reg_dev_get(g_reg, dev);
+    ggml_backend_t     be = ggml_backend_dev_init(d, nullptr);
+    if (!be) return -2;
+    int rc = 0;
+    {
+        ctx_scope wc(4), cc(16 + 8 * layers);
+        ggml_tensor * a = ggml_new_tensor_2d(wc.ctx, (ggml_type) type, k, k);
+        ggml_tensor * b = ggml_new_tensor_2d(wc.ctx, (ggml_type) type, k, k);
+        ggml_backend_buffer_t wbuf = ggml_backend_alloc_ctx_tensors(wc.ctx, be);
+        if (!wbuf) { ggml_backend_free(be); return -3; }
+        ggml_backend_buffer_set_usage(wbuf, GGML_BACKEND_BUFFER_USAGE_WEIGHTS);
+        ggml_backend_tensor_set(a, wa, 0, ggml_nbytes(a));
+        ggml_backend_tensor_set(b, wb, 0, ggml_nbytes(b));
+        ggml_tensor * xin = ggml_new_tensor_1d(cc.ctx, GGML_TYPE_F32, k);
+        ggml_tensor * cur = xin;
+        for (int l = 0; l < layers; ++l) {
+            ggml_tensor * h = ggml_rms_norm(cc.ctx, cur, 1e-5f);
+            h = ggml_mul_mat(cc.ctx, a, h);
+            h = ggml_silu(cc.ctx, h);
+            h = ggml_mul_mat(cc.ctx, b, h);
+            cur = ggml_add(cc.ctx, h, cur);
+        }
+        ggml_cgraph * gf = ggml_new_graph(cc.ctx);
+        ggml_build_forward_expand(gf, cur);
+        ggml_backend_buffer_t cbuf = ggml_backend_alloc_ctx_tensors(cc.ctx, be);
+        if (!cbuf) rc = -4;
+        std::vector<float> xr((size_t) k);
+        double     total_us      = 0.0;
+        const bool out_last_only = reps > 16;  // timing runs keep one result row
+        for (int rep = 0; rep < reps && rc == 0; ++rep) {
+            for (int64_t i = 0; i < k; ++i) xr[(size_t) i] = x[i] * (float) (rep % 7 + 1);
+            ggml_backend_tensor_set(xin, xr.data(), 0, ggml_nbytes(xin));
+            ggml_backend_synchronize(be);
+            const auto t0 = std::chrono::steady_clock::now();
+            if (ggml_backend_graph_compute(be, gf) != GGML_STATUS_SUCCESS) rc = -5;
+            ggml_backend_synchronize(be);
+            if (rep >= 3) total_us += std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count();
+            if (rc == 0 && out) ggml_backend_tensor_get(cur, out + (size_t) (out_last_only ? 0 : rep) * k, 0, (size_t) k * sizeof(float));
+        }
+        g_last_us = reps > 3 ? total_us / (reps - 3) : 0.0;
         if (cbuf) ggml_backend_buffer_free(cbuf);
         ggml_backend_buffer_free(wbuf);
     }

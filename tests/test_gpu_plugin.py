@@ -56,7 +56,7 @@ def _run_tbo(op, timeout=900):
 LAYER_OPS = [("RMS_NORM", 8), ("ADD", 33), ("SUB", 26), ("MUL", 26), ("DIV", 26), ("SCALE", 2), ("SILU", 2), ("GELU", 2),
              ("GELU_QUICK", 2), ("GELU_ERF", 2), ("RELU", 2), ("SIGMOID", 2), ("TANH", 2), ("NEG", 2), ("ABS", 2), ("EXP", 2),
              ("REGLU", 12), ("GEGLU", 12), ("SWIGLU", 12), ("SWIGLU_OAI", 8), ("GEGLU_ERF", 12), ("GEGLU_QUICK", 12),
-             ("SOFT_MAX", 199), ("ROPE", 176), ("CPY", 55), ("CONT", 10), ("DUP", 6), ("SET_ROWS", 61)]
+             ("SOFT_MAX", 199), ("ROPE", 176), ("CPY", 55), ("CONT", 10), ("DUP", 6), ("SET_ROWS", 61), ("ADD_ID", 34)]
 
 
 @pytest.mark.parametrize("op,min_ok", [("GET_ROWS", 65), ("MUL_MAT", 870), ("MUL_MAT_ID", 270)] + LAYER_OPS)
@@ -93,6 +93,8 @@ def _driver():
         L.pd_async_roundtrip.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p]
         L.pd_big_upload.argtypes = [C.c_int, C.c_void_p, C.c_int64, C.c_void_p]
         L.pd_decode_run.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int64] + [C.c_void_p] * 6
+        L.pd_layer_replay.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.pd_last_us.restype = C.c_double
         n = L.pd_load(PLUGIN.encode())
         assert n >= 1, f"ggml_backend_load({PLUGIN}) registered {n} devices"
         _pd = L
@@ -239,3 +241,54 @@ def test_inprocess_decode_run_as_list(t, tv):
     for i, tt in enumerate([t, t, tv]):
         assert refs.nmse(got[i], refs.ref_mul_mat(tt, ws[i], x)[0]) <= 5e-4
     assert refs.nmse(got[3], refs.ref_mul_mat(t, ws[3], got[0:1])[0]) <= 5e-4
+
+
+@pytest.mark.parametrize("t", [refs.Q4_K, refs.Q8_0], ids=lambda t: refs.NAMES[t])
+def test_inprocess_graph_replay(t):
+    """a 20-node layer-like graph computed six times on changing inputs: pass 1 runs eagerly, pass 2 is recorded as a CUDA
+    graph, passes 3-6 are replays (ggml-b200.cpp backend_graph_compute; the reference's cudaGraph path, ggml-cuda.cu:2876-3100).
+    Every pass must equal the all-eager run (GGML_B200_NO_GRAPHS) bit for bit, and the passes must differ from each other."""
+    L = _driver()
+    k, layers, reps = 1024, 4, 6
+    wa = refs.make_weights(t, k, k, seed=131)
+    wb = refs.make_weights(t, k, k, seed=132)
+    x = refs.uniform_weights(1, k, seed=133)
+    got = np.zeros((reps, k), dtype=np.float32)
+    eager = np.zeros((reps, k), dtype=np.float32)
+    os.environ.pop("GGML_B200_NO_GRAPHS", None)
+    stats = C.CFUNCTYPE(None, C.POINTER(C.c_int64), C.POINTER(C.c_int64))(L.pd_proc_address(b"ggml_backend_b200_graph_stats"))
+    rec0, rep0, rec1, rep1 = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
+    stats(C.byref(rec0), C.byref(rep0))
+    assert L.pd_layer_replay(0, t, k, layers, _p(wa), _p(wb), _p(x), reps, _p(got)) == 0
+    stats(C.byref(rec1), C.byref(rep1))
+    assert rec1.value - rec0.value == 1 and rep1.value - rep0.value == reps - 2, (rec1.value - rec0.value, rep1.value - rep0.value)
+    os.environ["GGML_B200_NO_GRAPHS"] = "1"
+    try:
+        assert L.pd_layer_replay(0, t, k, layers, _p(wa), _p(wb), _p(x), reps, _p(eager)) == 0
+    finally:
+        os.environ.pop("GGML_B200_NO_GRAPHS", None)
+    assert np.isfinite(got).all()
+    assert got.tobytes() == eager.tobytes(), [float(np.abs(got[r] - eager[r]).max()) for r in range(reps)]
+    for r in range(1, reps):
+        assert not np.array_equal(got[r], got[r - 1])
+
+
+def test_inprocess_graph_replay_is_not_slower():
+    """a 32-layer decode-like graph (160 nodes): time per graph_compute + synchronize, replayed vs eager; printed for the log"""
+    L = _driver()
+    t, k, layers, reps = refs.Q4_K, 4096, 32, 40
+    wa = refs.make_weights(t, k, k, seed=141)
+    wb = refs.make_weights(t, k, k, seed=142)
+    x = refs.uniform_weights(1, k, seed=143)
+    out = np.zeros((1, k), dtype=np.float32)
+    os.environ.pop("GGML_B200_NO_GRAPHS", None)
+    assert L.pd_layer_replay(0, t, k, layers, _p(wa), _p(wb), _p(x), reps, _p(out)) == 0
+    us_graph = L.pd_last_us()
+    os.environ["GGML_B200_NO_GRAPHS"] = "1"
+    try:
+        assert L.pd_layer_replay(0, t, k, layers, _p(wa), _p(wb), _p(x), reps, _p(out)) == 0
+    finally:
+        os.environ.pop("GGML_B200_NO_GRAPHS", None)
+    us_eager = L.pd_last_us()
+    print(f"\n[graph replay] 32-layer decode-like graph (160 nodes, q4_K 4096x4096): eager {us_eager:.1f} us, replay {us_graph:.1f} us")
+    assert us_graph <= us_eager * 1.10
