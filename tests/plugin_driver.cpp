@@ -23,6 +23,7 @@
 #include <cstdio>
 #include <cstring>
 #include <chrono>
+#include <cmath>
 #include <vector>
 
 namespace {
@@ -337,6 +338,140 @@ int pd_decode_run(int dev, int type, int type_v, int64_t k, const void * w1, con
 // A layer-like graph (rms_norm -> mul_mat -> silu -> mul_mat -> add, `layers` times: >= 16 nodes, so the plugin records it as a
 // CUDA graph on the second pass and replays it from the third) computed `reps` times on inputs x * (rep + 1); out [reps][k].
 // Results must not depend on whether a pass ran eagerly, was being recorded, or was a replay.
+// One Llama decoder layer exactly as llama.cpp builds it without flash attention (src/llama-graph.cpp build_attn_mha,
+// src/llama-kv-cache.cpp cpy_k / cpy_v with a non-transposed V cache, src/models llama: norm -> q/k/v -> rope -> KV store ->
+// K^T q -> soft_max(mask, scale) -> V kq -> wo -> residual -> norm -> swiglu ffn -> residual), run once on the plugin and once
+// on the reference's CPU backend with the same synthetic weights, inputs and pre-filled cache.  Returns 0 and fills
+// *nmse (plugin vs CPU on the layer output) and *unsupported (nodes the plugin's supports_op declines: must be 0 for the
+// layer to stay on the device).  type: weight type of the seven matrices (k-quants need n_embd % 256 == 0).
+namespace {
+struct lcg { uint32_t s; float next() { s = s * 1664525u + 1013904223u; return ((s >> 8) * (1.0f / 8388608.0f)) - 1.0f; } };
+struct layer_dims { int64_t n_embd = 512, n_head = 8, n_head_kv = 2, hd = 64, n_ff = 1024, n_ctx = 256; };
+
+int run_layer(ggml_backend_t be, int type, int n_tokens, int n_past, std::vector<float> & out, int * unsupported) {
+    const layer_dims D;
+    const int64_t n_kv   = ((n_past + n_tokens + 31) / 32) * 32;
+    const int64_t kv_dim = D.hd * D.n_head_kv;
+    ctx_scope wc(16), cc(96);
+    const ggml_type wt = (ggml_type) type;
+    ggml_tensor * wq = ggml_new_tensor_2d(wc.ctx, wt, D.n_embd, D.n_embd);
+    ggml_tensor * wk = ggml_new_tensor_2d(wc.ctx, wt, D.n_embd, kv_dim);
+    ggml_tensor * wv = ggml_new_tensor_2d(wc.ctx, wt, D.n_embd, kv_dim);
+    ggml_tensor * wo = ggml_new_tensor_2d(wc.ctx, wt, D.n_embd, D.n_embd);
+    ggml_tensor * wg = ggml_new_tensor_2d(wc.ctx, wt, D.n_embd, D.n_ff);
+    ggml_tensor * wu = ggml_new_tensor_2d(wc.ctx, wt, D.n_embd, D.n_ff);
+    ggml_tensor * wd = ggml_new_tensor_2d(wc.ctx, wt, D.n_ff, D.n_embd);
+    ggml_tensor * an = ggml_new_tensor_1d(wc.ctx, GGML_TYPE_F32, D.n_embd);
+    ggml_tensor * fn = ggml_new_tensor_1d(wc.ctx, GGML_TYPE_F32, D.n_embd);
+    ggml_tensor * kc = ggml_new_tensor_2d(wc.ctx, GGML_TYPE_F16, kv_dim, D.n_ctx);
+    ggml_tensor * vc = ggml_new_tensor_2d(wc.ctx, GGML_TYPE_F16, kv_dim, D.n_ctx);
+    ggml_backend_buffer_t wbuf = ggml_backend_alloc_ctx_tensors(wc.ctx, be);
+    if (!wbuf) return -3;
+    lcg rng{ 12345u };
+    auto fill_q = [&](ggml_tensor * t, float amp) {
+        const int64_t n = ggml_nelements(t);
+        std::vector<float> f((size_t) n);
+        for (auto & v : f) v = rng.next() * amp;
+        std::vector<uint8_t> q(ggml_nbytes(t));
+        if (t->type == GGML_TYPE_F32) memcpy(q.data(), f.data(), q.size());
+        else ggml_quantize_chunk(t->type, f.data(), q.data(), 0, n / t->ne[0], t->ne[0], nullptr);
+        ggml_backend_tensor_set(t, q.data(), 0, q.size());
+    };
+    for (ggml_tensor * t : { wq, wk, wv, wo, wg, wu, wd }) fill_q(t, 0.06f);
+    for (ggml_tensor * t : { an, fn }) fill_q(t, 1.0f);
+    for (ggml_tensor * t : { kc, vc }) fill_q(t, 0.5f);  // positions < n_past hold earlier tokens; the rest is masked out
+
+    ggml_tensor * x    = ggml_new_tensor_2d(cc.ctx, GGML_TYPE_F32, D.n_embd, n_tokens);
+    ggml_tensor * pos  = ggml_new_tensor_1d(cc.ctx, GGML_TYPE_I32, n_tokens);
+    ggml_tensor * idx  = ggml_new_tensor_1d(cc.ctx, GGML_TYPE_I64, n_tokens);
+    ggml_tensor * mask = ggml_new_tensor_2d(cc.ctx, GGML_TYPE_F32, n_kv, n_tokens);
+    ggml_context * c = cc.ctx;
+    ggml_tensor * cur = ggml_mul(c, ggml_rms_norm(c, x, 1e-5f), an);
+    ggml_tensor * Q = ggml_reshape_3d(c, ggml_mul_mat(c, wq, cur), D.hd, D.n_head, n_tokens);
+    ggml_tensor * K = ggml_reshape_3d(c, ggml_mul_mat(c, wk, cur), D.hd, D.n_head_kv, n_tokens);
+    ggml_tensor * V = ggml_mul_mat(c, wv, cur);
+    Q = ggml_rope_ext(c, Q, pos, nullptr, (int) D.hd, 0, 8192, 500000.0f, 1.0f, 0.0f, 1.0f, 32.0f, 1.0f);
+    K = ggml_rope_ext(c, K, pos, nullptr, (int) D.hd, 0, 8192, 500000.0f, 1.0f, 0.0f, 1.0f, 32.0f, 1.0f);
+    ggml_tensor * k_store = ggml_set_rows(c, kc, ggml_reshape_2d(c, K, kv_dim, n_tokens), idx);
+    ggml_tensor * v_store = ggml_set_rows(c, vc, V, idx);
+    ggml_tensor * q = ggml_permute(c, Q, 0, 2, 1, 3);
+    ggml_tensor * k = ggml_view_3d(c, kc, D.hd, n_kv, D.n_head_kv, kc->nb[1], ggml_row_size(kc->type, D.hd), 0);
+    ggml_tensor * v = ggml_view_3d(c, vc, D.hd, n_kv, D.n_head_kv, vc->nb[1], ggml_row_size(vc->type, D.hd), 0);
+    ggml_tensor * kq = ggml_mul_mat(c, k, q);
+    kq = ggml_soft_max_ext(c, kq, mask, 1.0f / 8.0f, 0.0f);
+    v = ggml_cont(c, ggml_transpose(c, v));
+    ggml_tensor * kqv = ggml_mul_mat(c, v, kq);
+    cur = ggml_cont_2d(c, ggml_permute(c, kqv, 0, 2, 1, 3), D.n_embd, n_tokens);
+    ggml_tensor * ffn_inp = ggml_add(c, ggml_mul_mat(c, wo, cur), x);
+    cur = ggml_mul(c, ggml_rms_norm(c, ffn_inp, 1e-5f), fn);
+    cur = ggml_swiglu_split(c, ggml_mul_mat(c, wg, cur), ggml_mul_mat(c, wu, cur));
+    ggml_tensor * res = ggml_add(c, ggml_mul_mat(c, wd, cur), ffn_inp);
+    ggml_cgraph * gf = ggml_new_graph(c);
+    ggml_build_forward_expand(gf, k_store);
+    ggml_build_forward_expand(gf, v_store);
+    ggml_build_forward_expand(gf, res);
+    ggml_backend_buffer_t cbuf = ggml_backend_alloc_ctx_tensors(cc.ctx, be);
+    int rc = cbuf ? 0 : -4;
+    if (rc == 0) {
+        if (unsupported) {
+            *unsupported = 0;
+            for (int i = 0; i < ggml_graph_n_nodes(gf); ++i) {
+                if (!ggml_backend_supports_op(be, ggml_graph_node(gf, i))) {
+                    ++*unsupported;
+                    fprintf(stderr, "pd_llama_layer: not supported: %s\n", ggml_op_desc(ggml_graph_node(gf, i)));
+                }
+            }
+        }
+        std::vector<float> xs((size_t) (D.n_embd * n_tokens));
+        for (auto & f : xs) f = rng.next();
+        std::vector<int32_t> ps((size_t) n_tokens);
+        std::vector<int64_t> is((size_t) n_tokens);
+        std::vector<float>   ms((size_t) (n_kv * n_tokens));
+        for (int t = 0; t < n_tokens; ++t) {
+            ps[(size_t) t] = n_past + t;
+            is[(size_t) t] = n_past + t;
+            for (int64_t j = 0; j < n_kv; ++j) ms[(size_t) (t * n_kv + j)] = j <= n_past + t ? 0.0f : -INFINITY;
+        }
+        ggml_backend_tensor_set(x, xs.data(), 0, ggml_nbytes(x));
+        ggml_backend_tensor_set(pos, ps.data(), 0, ggml_nbytes(pos));
+        ggml_backend_tensor_set(idx, is.data(), 0, ggml_nbytes(idx));
+        ggml_backend_tensor_set(mask, ms.data(), 0, ggml_nbytes(mask));
+        if (!unsupported || *unsupported == 0) {
+            if (ggml_backend_graph_compute(be, gf) != GGML_STATUS_SUCCESS) rc = -5;
+            out.resize((size_t) (D.n_embd * n_tokens));
+            if (rc == 0) ggml_backend_tensor_get(res, out.data(), 0, ggml_nbytes(res));
+        }
+    }
+    if (cbuf) ggml_backend_buffer_free(cbuf);
+    ggml_backend_buffer_free(wbuf);
+    return rc;
+}
+}  // namespace
+
+int pd_llama_layer(int dev, int type, int n_tokens, int n_past, double * nmse, int * unsupported) {
+    if (!g_reg) return -1;
+    ggml_backend_t be  = ggml_backend_dev_init(ggml_backend_reg_dev_get(g_reg, dev), nullptr);
+    ggml_backend_t cpu = ggml_backend_init_by_type(GGML_BACKEND_DEVICE_TYPE_CPU, nullptr);
+    if (!be || !cpu) return -2;
+    std::vector<float> got, want;
+    int rc = run_layer(be, type, n_tokens, n_past, got, unsupported);
+    if (rc == 0) rc = run_layer(cpu, type, n_tokens, n_past, want, nullptr);
+    if (rc == 0 && got.size() == want.size() && !got.empty()) {
+        double num = 0.0, den = 0.0;
+        for (size_t i = 0; i < got.size(); ++i) {
+            const double d = (double) got[i] - (double) want[i];
+            num += d * d;
+            den += (double) want[i] * (double) want[i];
+        }
+        *nmse = den > 0.0 ? num / den : 1.0;
+    } else if (rc == 0) {
+        *nmse = 1.0;
+    }
+    ggml_backend_free(cpu);
+    ggml_backend_free(be);
+    return rc;
+}
+
 static double g_last_us = 0.0;
 // microseconds per graph_compute + synchronize of the last pd_layer_replay call (mean over passes 4..reps)
 double pd_last_us(void) { return g_last_us; }

@@ -95,6 +95,7 @@ def _driver():
         L.pd_decode_run.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int64] + [C.c_void_p] * 6
         L.pd_layer_replay.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.pd_last_us.restype = C.c_double
+        L.pd_llama_layer.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         n = L.pd_load(PLUGIN.encode())
         assert n >= 1, f"ggml_backend_load({PLUGIN}) registered {n} devices"
         _pd = L
@@ -292,3 +293,18 @@ def test_inprocess_graph_replay_is_not_slower():
     us_eager = L.pd_last_us()
     print(f"\n[graph replay] 32-layer decode-like graph (160 nodes, q4_K 4096x4096): eager {us_eager:.1f} us, replay {us_graph:.1f} us")
     assert us_graph <= us_eager * 1.10
+
+
+@pytest.mark.parametrize("t", [refs.Q4_K, refs.Q8_0, refs.Q6_K], ids=lambda t: refs.NAMES[t])
+@pytest.mark.parametrize("n_tokens,n_past", [(1, 37), (1, 0), (5, 60), (17, 5), (40, 0)])
+def test_inprocess_llama_layer_stays_on_device(t, n_tokens, n_past):
+    """one whole Llama decoder layer as llama.cpp builds it without flash attention — norm, q/k/v, RoPE, KV
+    store (SET_ROWS into an f16 cache), K^T q on the cache view, masked soft_max, V kq, wo, residual, norm, SwiGLU FFN, residual —
+    every node is accepted by the plugin's supports_op (nothing bounces to the CPU) and the layer output equals the reference
+    CPU backend's on the same weights, inputs and pre-filled cache (decode, small batch and prompt shapes)."""
+    L = _driver()
+    nmse, unsup = C.c_double(-1.0), C.c_int(-1)
+    rc = L.pd_llama_layer(0, t, n_tokens, n_past, C.byref(nmse), C.byref(unsup))
+    assert rc == 0 and unsup.value == 0, (rc, unsup.value)
+    print(f"\n[llama layer] {refs.NAMES[t]} n_tokens={n_tokens} n_past={n_past}: nmse vs CPU backend {nmse.value:.2e}")
+    assert 0.0 <= nmse.value <= 1e-3
