@@ -304,6 +304,8 @@ B200Q_API int b200q_op_rope(const b200q_tensor * src, const b200q_tensor * pos, 
 B200Q_API int b200q_op_cpy(const b200q_tensor * src, const b200q_tensor * dst, void * stream);       /* cpy.cu: CPY / CONT / DUP */
 B200Q_API int b200q_op_add_id(const b200q_tensor * a, const b200q_tensor * b, const b200q_tensor * ids, const b200q_tensor * dst,
                               void * stream);  /* dst[i0,i1,i2] = a[i0,i1,i2] + b[i0, ids[i1,i2]] (MoE expert bias)      add-id.cu */
+B200Q_API int b200q_op_argsort(const b200q_tensor * src, const b200q_tensor * dst, int descending,
+                               void * stream);  /* f32 rows (ne0 <= 1024) -> i32 indices; ggml_top_k is a view of it   argsort.cu */
 B200Q_API int b200q_op_set_rows(const b200q_tensor * src, const b200q_tensor * idx, const b200q_tensor * dst,
                                 void * stream);                                                                            /* set-rows.cu */
 

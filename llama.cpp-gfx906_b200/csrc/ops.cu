@@ -305,6 +305,37 @@ __global__ void __launch_bounds__(256) add_id_kernel(T4 a, T4 b, T4 ids, T4 d, l
     }
 }
 
+// ---- ARGSORT: per row, the indices that sort it (MoE routers: top-k = a view of the descending argsort; argsort.cu) ----------
+// one CTA per row, bitonic network over the next power of two (padding sorts last), ne0 <= 1024
+__global__ void __launch_bounds__(1024) argsort_kernel(T4 s, T4 d, int npad, int desc) {
+    extern __shared__ int as_idx[];
+    const long long r  = blockIdx.x;
+    const long long i1 = r % s.ne[1], i2 = (r / s.ne[1]) % s.ne[2], i3 = r / (s.ne[1] * s.ne[2]);
+    const char * row = s.data + i1 * s.nb[1] + i2 * s.nb[2] + i3 * s.nb[3];
+    const int n = (int) s.ne[0], t = threadIdx.x;
+    auto val = [&](int i) { return *(const float *) (row + (long long) i * 4); };
+    if (t < npad) as_idx[t] = t;
+    __syncthreads();
+    for (int k = 2; k <= npad; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const int o = t ^ j;
+            if (t < npad && o > t) {
+                const int a = as_idx[t], b = as_idx[o];
+                // "a sorts after b": padding (index >= n) after everything, then by value
+                const bool after = a >= n ? b < n : (b < n && (desc ? val(a) < val(b) : val(a) > val(b)));
+                const bool before = b >= n ? a < n : (a < n && (desc ? val(b) < val(a) : val(b) > val(a)));
+                const bool up = (t & k) == 0;
+                if (up ? after : before) {
+                    as_idx[t] = b;
+                    as_idx[o] = a;
+                }
+            }
+            __syncthreads();
+        }
+    }
+    if (t < n) *(int *) (d.data + (long long) t * 4 + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = as_idx[t];
+}
+
 template <int TS> int cpy_to(const b200q_tensor * s, const b200q_tensor * d, long long n, cudaStream_t st) {
     const int g = grid_for(n, 256);
     switch (d->type) {
@@ -463,6 +494,20 @@ int b200q_op_add_id(const b200q_tensor * a, const b200q_tensor * b, const b200q_
     const long long n = nelem(a);
     if (n == 0) return 0;
     add_id_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t) stream>>>(t4(a), t4(b), t4(ids), t4(dst), n);
+    return launched();
+}
+
+int b200q_op_argsort(const b200q_tensor * src, const b200q_tensor * dst, int descending, void * stream) {
+    if (!src || !dst || src->type != B200Q_TYPE_F32 || dst->type != B200Q_TYPE_I32 || src->nb[0] != 4 || dst->nb[0] != 4 ||
+        src->ne[0] < 1 || src->ne[0] > 1024 || nelem(src) != nelem(dst)) {
+        return ops_fail(B200Q_ENOTSUP, "argsort: f32 rows of at most 1024 values -> i32");
+    }
+    const long long rows = nelem(src) / src->ne[0];
+    if (rows == 0) return 0;
+    if (rows > 0x7fffffffll) return ops_fail(B200Q_ENOTSUP, "argsort: too many rows");
+    int npad = 1;
+    while (npad < src->ne[0]) npad <<= 1;
+    argsort_kernel<<<(unsigned) rows, npad < 32 ? 32 : npad, npad * sizeof(int), (cudaStream_t) stream>>>(t4(src), t4(dst), npad, descending ? 1 : 0);
     return launched();
 }
 

@@ -572,6 +572,8 @@ bool supports_elementwise(const ggml_tensor * op) {
         }
         case GGML_OP_CPY: case GGML_OP_CONT: case GGML_OP_DUP:
             return float_type(a->type) && float_type(op->type) && ggml_nelements(a) == ggml_nelements(op);
+        case GGML_OP_ARGSORT:  // router top-k (ggml_top_k = a view of the descending argsort); argsort.cu takes the same row cap
+            return is_f32(a) && op->type == GGML_TYPE_I32 && a->nb[0] == 4 && op->nb[0] == 4 && a->ne[0] <= 1024;
         case GGML_OP_ADD_ID: {  // a [n, used, tokens] + b [n, experts] picked by ids [used, tokens] (add-id.cu; ggml-cuda.cu:3455)
             const ggml_tensor * ids = op->src[2];
             return is_f32(a) && is_f32(b) && ids && ids->type == GGML_TYPE_I32 && is_f32(op) && a->nb[0] == 4 && b->nb[0] == 4 &&
@@ -615,6 +617,7 @@ int compute_elementwise(b200_backend_ctx * ctx, const ggml_tensor * op) {
         case GGML_OP_CPY: case GGML_OP_CONT: case GGML_OP_DUP: return b200q_op_cpy(&ta, &td, ctx->stream);
         case GGML_OP_SET_ROWS: return b200q_op_set_rows(&ta, &tb, &td, ctx->stream);
         case GGML_OP_ADD_ID:   return b200q_op_add_id(&ta, &tb, &tc, &td, ctx->stream);
+        case GGML_OP_ARGSORT:  return b200q_op_argsort(&ta, &td, ip[0] == GGML_SORT_ORDER_DESC, ctx->stream);
         default: return B200Q_ENOTSUP;
     }
 }
@@ -1070,7 +1073,7 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
             case GGML_OP_GET_ROWS:   rc = compute_get_rows(ctx, node); break;
             case GGML_OP_RMS_NORM: case GGML_OP_ADD: case GGML_OP_SUB: case GGML_OP_MUL: case GGML_OP_DIV: case GGML_OP_SCALE:
             case GGML_OP_UNARY: case GGML_OP_GLU: case GGML_OP_SOFT_MAX: case GGML_OP_ROPE: case GGML_OP_CPY: case GGML_OP_CONT:
-            case GGML_OP_DUP: case GGML_OP_SET_ROWS: case GGML_OP_ADD_ID:
+            case GGML_OP_DUP: case GGML_OP_SET_ROWS: case GGML_OP_ADD_ID: case GGML_OP_ARGSORT:
                 rc = compute_elementwise(ctx, node);
                 break;
             default:

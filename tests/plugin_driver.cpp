@@ -448,6 +448,105 @@ int run_layer(ggml_backend_t be, int type, int n_tokens, int n_past, std::vector
 }
 }  // namespace
 
+// The MoE feed-forward block of gpt-oss as src/llama-graph.cpp build_moe_ffn builds it (SOFTMAX_WEIGHT gating): router matmul
+// (f32) + bias, top-k = view of the descending ARGSORT, GET_ROWS of the logits by the selection, soft_max over the selected,
+// MUL_MAT_ID (up, gate) + ADD_ID biases, SWIGLU_OAI, MUL_MAT_ID (down) + ADD_ID, weighting, and the sum over the used experts.
+namespace {
+int run_moe(ggml_backend_t be, int n_tokens, std::vector<float> & out, int * unsupported) {
+    const int64_t n_embd = 512, n_ff = 512, n_expert = 8, n_used = 4;
+    ctx_scope wc(16), cc(96);
+    ggml_tensor * gi  = ggml_new_tensor_2d(wc.ctx, GGML_TYPE_F32, n_embd, n_expert);
+    ggml_tensor * gib = ggml_new_tensor_1d(wc.ctx, GGML_TYPE_F32, n_expert);
+    ggml_tensor * up  = ggml_new_tensor_3d(wc.ctx, GGML_TYPE_MXFP4, n_embd, n_ff, n_expert);
+    ggml_tensor * gt  = ggml_new_tensor_3d(wc.ctx, GGML_TYPE_MXFP4, n_embd, n_ff, n_expert);
+    ggml_tensor * dn  = ggml_new_tensor_3d(wc.ctx, GGML_TYPE_MXFP4, n_ff, n_embd, n_expert);
+    ggml_tensor * upb = ggml_new_tensor_2d(wc.ctx, GGML_TYPE_F32, n_ff, n_expert);
+    ggml_tensor * gtb = ggml_new_tensor_2d(wc.ctx, GGML_TYPE_F32, n_ff, n_expert);
+    ggml_tensor * dnb = ggml_new_tensor_2d(wc.ctx, GGML_TYPE_F32, n_embd, n_expert);
+    ggml_backend_buffer_t wbuf = ggml_backend_alloc_ctx_tensors(wc.ctx, be);
+    if (!wbuf) return -3;
+    lcg rng{ 777u };
+    auto fill = [&](ggml_tensor * t, float amp) {
+        const int64_t n = ggml_nelements(t);
+        std::vector<float> f((size_t) n);
+        for (auto & v : f) v = rng.next() * amp;
+        std::vector<uint8_t> q(ggml_nbytes(t));
+        if (t->type == GGML_TYPE_F32) memcpy(q.data(), f.data(), q.size());
+        else ggml_quantize_chunk(t->type, f.data(), q.data(), 0, n / t->ne[0], t->ne[0], nullptr);
+        ggml_backend_tensor_set(t, q.data(), 0, q.size());
+    };
+    fill(gi, 0.5f); fill(gib, 0.1f); fill(up, 0.06f); fill(gt, 0.06f); fill(dn, 0.06f); fill(upb, 0.1f); fill(gtb, 0.1f); fill(dnb, 0.1f);
+    ggml_context * c = cc.ctx;
+    ggml_tensor * x = ggml_new_tensor_2d(c, GGML_TYPE_F32, n_embd, n_tokens);
+    ggml_tensor * logits = ggml_add(c, ggml_mul_mat(c, gi, x), gib);                          // [n_expert, n_tokens]
+    ggml_tensor * sel = ggml_top_k(c, logits, (int) n_used);                                  // [n_used, n_tokens] i32 (view)
+    ggml_tensor * w = ggml_get_rows(c, ggml_reshape_3d(c, logits, 1, n_expert, n_tokens), sel);  // [1, n_used, n_tokens]
+    w = ggml_reshape_3d(c, ggml_soft_max(c, ggml_reshape_2d(c, w, n_used, n_tokens)), 1, n_used, n_tokens);
+    ggml_tensor * cur = ggml_reshape_3d(c, x, n_embd, 1, n_tokens);
+    ggml_tensor * u = ggml_add_id(c, ggml_mul_mat_id(c, up, cur, sel), upb, sel);             // [n_ff, n_used, n_tokens]
+    ggml_tensor * g = ggml_add_id(c, ggml_mul_mat_id(c, gt, cur, sel), gtb, sel);
+    ggml_tensor * a = ggml_swiglu_oai(c, g, u, 1.702f, 7.0f);
+    ggml_tensor * e = ggml_add_id(c, ggml_mul_mat_id(c, dn, a, sel), dnb, sel);               // [n_embd, n_used, n_tokens]
+    e = ggml_mul(c, e, w);
+    ggml_cgraph * gf = ggml_new_graph(c);
+    ggml_tensor * parts[4];
+    for (int i = 0; i < (int) n_used; ++i) {
+        parts[i] = ggml_view_2d(c, e, n_embd, n_tokens, e->nb[2], (size_t) i * e->nb[1]);
+        ggml_build_forward_expand(gf, parts[i]);
+    }
+    ggml_tensor * res = parts[0];
+    for (int i = 1; i < (int) n_used; ++i) res = ggml_add(c, res, parts[i]);
+    ggml_build_forward_expand(gf, res);
+    ggml_backend_buffer_t cbuf = ggml_backend_alloc_ctx_tensors(cc.ctx, be);
+    int rc = cbuf ? 0 : -4;
+    if (rc == 0) {
+        if (unsupported) {
+            *unsupported = 0;
+            for (int i = 0; i < ggml_graph_n_nodes(gf); ++i) {
+                if (!ggml_backend_supports_op(be, ggml_graph_node(gf, i))) {
+                    ++*unsupported;
+                    fprintf(stderr, "pd_moe_block: not supported: %s\n", ggml_op_desc(ggml_graph_node(gf, i)));
+                }
+            }
+        }
+        std::vector<float> xs((size_t) (n_embd * n_tokens));
+        for (auto & f : xs) f = rng.next();
+        ggml_backend_tensor_set(x, xs.data(), 0, ggml_nbytes(x));
+        if (!unsupported || *unsupported == 0) {
+            if (ggml_backend_graph_compute(be, gf) != GGML_STATUS_SUCCESS) rc = -5;
+            out.resize((size_t) (n_embd * n_tokens));
+            if (rc == 0) ggml_backend_tensor_get(res, out.data(), 0, ggml_nbytes(res));
+        }
+    }
+    if (cbuf) ggml_backend_buffer_free(cbuf);
+    ggml_backend_buffer_free(wbuf);
+    return rc;
+}
+}  // namespace
+
+int pd_moe_block(int dev, int n_tokens, double * nmse, int * unsupported) {
+    if (!g_reg) return -1;
+    ggml_backend_t be  = ggml_backend_dev_init(ggml_backend_reg_dev_get(g_reg, dev), nullptr);
+    ggml_backend_t cpu = ggml_backend_init_by_type(GGML_BACKEND_DEVICE_TYPE_CPU, nullptr);
+    if (!be || !cpu) return -2;
+    std::vector<float> got, want;
+    int rc = run_moe(be, n_tokens, got, unsupported);
+    if (rc == 0) rc = run_moe(cpu, n_tokens, want, nullptr);
+    *nmse = 1.0;
+    if (rc == 0 && got.size() == want.size() && !got.empty()) {
+        double num = 0.0, den = 0.0;
+        for (size_t i = 0; i < got.size(); ++i) {
+            const double d = (double) got[i] - (double) want[i];
+            num += d * d;
+            den += (double) want[i] * (double) want[i];
+        }
+        *nmse = den > 0.0 ? num / den : 1.0;
+    }
+    ggml_backend_free(cpu);
+    ggml_backend_free(be);
+    return rc;
+}
+
 int pd_llama_layer(int dev, int type, int n_tokens, int n_past, double * nmse, int * unsupported) {
     if (!g_reg) return -1;
     ggml_backend_t be  = ggml_backend_dev_init(ggml_backend_reg_dev_get(g_reg, dev), nullptr);

@@ -56,7 +56,7 @@ def _run_tbo(op, timeout=900):
 LAYER_OPS = [("RMS_NORM", 8), ("ADD", 33), ("SUB", 26), ("MUL", 26), ("DIV", 26), ("SCALE", 2), ("SILU", 2), ("GELU", 2),
              ("GELU_QUICK", 2), ("GELU_ERF", 2), ("RELU", 2), ("SIGMOID", 2), ("TANH", 2), ("NEG", 2), ("ABS", 2), ("EXP", 2),
              ("REGLU", 12), ("GEGLU", 12), ("SWIGLU", 12), ("SWIGLU_OAI", 8), ("GEGLU_ERF", 12), ("GEGLU_QUICK", 12),
-             ("SOFT_MAX", 199), ("ROPE", 176), ("CPY", 55), ("CONT", 10), ("DUP", 6), ("SET_ROWS", 61), ("ADD_ID", 34)]
+             ("SOFT_MAX", 199), ("ROPE", 176), ("CPY", 55), ("CONT", 10), ("DUP", 6), ("SET_ROWS", 61), ("ADD_ID", 34), ("ARGSORT", 6)]
 
 
 @pytest.mark.parametrize("op,min_ok", [("GET_ROWS", 65), ("MUL_MAT", 870), ("MUL_MAT_ID", 270)] + LAYER_OPS)
@@ -96,6 +96,7 @@ def _driver():
         L.pd_layer_replay.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.pd_last_us.restype = C.c_double
         L.pd_llama_layer.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
+        L.pd_moe_block.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         n = L.pd_load(PLUGIN.encode())
         assert n >= 1, f"ggml_backend_load({PLUGIN}) registered {n} devices"
         _pd = L
@@ -307,4 +308,18 @@ def test_inprocess_llama_layer_stays_on_device(t, n_tokens, n_past):
     rc = L.pd_llama_layer(0, t, n_tokens, n_past, C.byref(nmse), C.byref(unsup))
     assert rc == 0 and unsup.value == 0, (rc, unsup.value)
     print(f"\n[llama layer] {refs.NAMES[t]} n_tokens={n_tokens} n_past={n_past}: nmse vs CPU backend {nmse.value:.2e}")
+    assert 0.0 <= nmse.value <= 1e-3
+
+
+@pytest.mark.parametrize("n_tokens", [1, 7, 40, 200])
+def test_inprocess_gpt_oss_moe_block_stays_on_device(n_tokens):
+    """the MoE feed-forward block of gpt-oss (src/llama-graph.cpp build_moe_ffn, SOFTMAX_WEIGHT gating) with MXFP4 experts: f32
+    router matmul + bias, top-k (a view of ARGSORT), GET_ROWS, soft_max over the selection, MUL_MAT_ID x3 with ADD_ID biases,
+    SWIGLU_OAI, weighting and the sum over the used experts — every node accepted by supports_op, output equal to the
+    reference CPU backend's (the routing is discrete: equal selections are part of what the NMSE checks)."""
+    L = _driver()
+    nmse, unsup = C.c_double(-1.0), C.c_int(-1)
+    rc = L.pd_moe_block(0, n_tokens, C.byref(nmse), C.byref(unsup))
+    assert rc == 0 and unsup.value == 0, (rc, unsup.value)
+    print(f"\n[gpt-oss moe block] n_tokens={n_tokens}: nmse vs CPU backend {nmse.value:.2e}")
     assert 0.0 <= nmse.value <= 1e-3
