@@ -326,7 +326,7 @@ def aux_single_gpu(torch, b200q, workloads, peak_hbm, bf16_peak):
             else:
                 fl = 2.0 * M * K * T * USED
                 aux["config4_mxfp4_moe_T512"] = {"us": us, "achieved": fl / us / 1e6, "unit": "TFLOP/s", "frac": fl / us / 1e6 / bf16_peak,
-                                                 "peak": bf16_peak, "how": "2048 (token, slot) rows over 32 experts, tcgen05 kind::f16"}
+                                                 "peak": bf16_peak, "how": "2048 (token, slot) rows over 32 experts, native block-scaled tcgen05 kind::mxf8f6f4 (hi + lo e4m3 activations); frac is against the measured bf16 peak"}
         del wsx
     except Exception as e:
         aux["config4_mxfp4_moe"] = {"error": repr(e)}
