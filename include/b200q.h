@@ -289,6 +289,10 @@ typedef struct b200q_rope_params {
     float corr_dims[2];  /* ggml_rope_yarn_corr_dims(n_dims, n_ctx_orig, freq_base, beta_fast, beta_slow) — host arithmetic */
 } b200q_rope_params;
 B200Q_API int b200q_op_rms_norm(const b200q_tensor * src, const b200q_tensor * dst, float eps, void * stream);            /* norm.cu */
+/* [ADD +] RMS_NORM + MUL in one launch (the reference fuses RMS_NORM + MUL (+ ADD) too, ggml-cuda.cu:2811-2845): x = a (+ b; the sum
+ * is also written to sum_out when given), dst = rms_norm(x, eps) * w with w broadcast over rows; rows of at most 8192 values */
+B200Q_API int b200q_op_norm_fused(const b200q_tensor * a, const b200q_tensor * b /* or NULL */, const b200q_tensor * sum_out /* or NULL */,
+                                  const b200q_tensor * w, const b200q_tensor * dst, float eps, void * stream);
 B200Q_API int b200q_op_bin(int op, const b200q_tensor * src0, const b200q_tensor * src1, const b200q_tensor * dst,
                            void * stream);                                                                                 /* binbcast.cu */
 B200Q_API int b200q_op_scale(const b200q_tensor * src, const b200q_tensor * dst, float scale, float bias, void * stream); /* scale.cu */

@@ -12,6 +12,7 @@
 #include "dense_mm.cuh"
 #include "mmq.cuh"
 #include "mmq_mxf.cuh"
+#include "pdl.cuh"
 
 #include <cuda_runtime.h>
 
@@ -728,7 +729,7 @@ static int launch_get_rows(const GetRowsParams & p, int type, cudaStream_t st) {
     const DevInfo & di   = dev_info();
     const long long want = (total + 255) / 256;
     const int       grid = (int) std::min<long long>(want, (long long) di.sms * 16);
-    fn<<<grid, 256, 0, st>>>(p);
+    launch_pdl(fn, dim3(grid), dim3(256), 0, st, p);  // get_rows_kernel starts with pdl_grid_sync()
     CUDA_TRY(cudaGetLastError());
     return 0;
 }

@@ -14,6 +14,7 @@
 
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
+#include "pdl.cuh"
 #include <cuda_runtime.h>
 
 namespace b200q {
@@ -56,6 +57,7 @@ __device__ __forceinline__ void batch_ptrs(const DenseParams & p, int b, const u
 constexpr int GV_WARPS = 4;
 
 template <int T, int NC> __global__ void __launch_bounds__(GV_WARPS * 32) dense_gemv_kernel(const DenseParams p) {
+    pdl_grid_sync();
     using E = typename Elem<T>::type;
     constexpr int VEC = 16 / (int) sizeof(E);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -115,6 +117,7 @@ template <int T, int NC> __global__ void __launch_bounds__(GV_WARPS * 32) dense_
 constexpr int TM = 64, TN = 64, TK = 16;
 
 template <int T> __global__ void __launch_bounds__(256) dense_tile_kernel(const DenseParams p) {
+    pdl_grid_sync();
     using E = typename Elem<T>::type;
     __shared__ float As[TK][TM + 4];
     __shared__ float Bs[TK][TN + 4];
@@ -172,15 +175,15 @@ template <int T> int launch_t(const DenseParams & p, cudaStream_t st) {
     const int nbatch = p.ne12 * p.ne13;
     if (p.n <= 8) {
         const dim3 grid((unsigned) ((p.m + GV_WARPS - 1) / GV_WARPS), (unsigned) (nbatch < 65535 ? nbatch : 65535));
-        if (p.n == 1) dense_gemv_kernel<T, 1><<<grid, GV_WARPS * 32, 0, st>>>(p);
-        else if (p.n == 2) dense_gemv_kernel<T, 2><<<grid, GV_WARPS * 32, 0, st>>>(p);
-        else if (p.n <= 4) dense_gemv_kernel<T, 4><<<grid, GV_WARPS * 32, 0, st>>>(p);
-        else dense_gemv_kernel<T, 8><<<grid, GV_WARPS * 32, 0, st>>>(p);
+        if (p.n == 1) launch_pdl(dense_gemv_kernel<T, 1>, dim3(grid), dim3(GV_WARPS * 32), 0, st, p);
+        else if (p.n == 2) launch_pdl(dense_gemv_kernel<T, 2>, dim3(grid), dim3(GV_WARPS * 32), 0, st, p);
+        else if (p.n <= 4) launch_pdl(dense_gemv_kernel<T, 4>, dim3(grid), dim3(GV_WARPS * 32), 0, st, p);
+        else launch_pdl(dense_gemv_kernel<T, 8>, dim3(grid), dim3(GV_WARPS * 32), 0, st, p);
     } else {
         const long long gy = (p.n + TN - 1) / TN;
         if (gy > 65535) return B200Q_ENOTSUP;
         const dim3 grid((unsigned) ((p.m + TM - 1) / TM), (unsigned) gy, (unsigned) (nbatch < 65535 ? nbatch : 65535));
-        dense_tile_kernel<T><<<grid, 256, 0, st>>>(p);
+        launch_pdl(dense_tile_kernel<T>, dim3(grid), dim3(256), 0, st, p);
     }
     return cudaGetLastError() == cudaSuccess ? 0 : B200Q_ECUDA;
 }

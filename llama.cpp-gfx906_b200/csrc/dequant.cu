@@ -11,6 +11,7 @@
 #include "blocks.cuh"
 #include "dequant.cuh"
 
+#include "pdl.cuh"
 #include <cuda_runtime.h>
 
 namespace b200q {
@@ -26,6 +27,7 @@ template <> __device__ __forceinline__ float decode_any<T_F32>(const uint8_t * r
 
 // dst[(i12, i11, i10)][i00] = decode(src0 row ids[i10, i11, i12] of plane (i11, i12))[i00]
 template <int T> __global__ void __launch_bounds__(256) get_rows_kernel(const GetRowsParams p) {
+    pdl_grid_sync();
     const int64_t quads_per_row = (p.ne00 + 3) >> 2;
     const int64_t total         = quads_per_row * p.n_rows;
     for (int64_t idx = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; idx < total;

@@ -13,6 +13,7 @@
 
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
+#include "pdl.cuh"
 #include <cuda_runtime.h>
 
 #include <math.h>
@@ -22,6 +23,8 @@ namespace b200q {
 int ops_fail(int code, const char * msg);  // api.cu: records the message for b200q_last_error
 }
 using b200q::ops_fail;
+using b200q::launch_pdl;
+using b200q::pdl_grid_sync;
 
 namespace {
 
@@ -111,6 +114,7 @@ template <> struct Elem<B200Q_TYPE_BF16> {
 
 // ---- RMS_NORM: y = x / sqrt(mean(x^2) + eps), one CTA per row -------------------------------------------------------------
 __global__ void __launch_bounds__(256) rms_norm_kernel(T4 x, T4 y, float eps) {
+    pdl_grid_sync();
     __shared__ float sh[32];
     const long long row = blockIdx.x;
     const long long i3 = row / (x.ne[1] * x.ne[2]), i2 = (row / x.ne[1]) % x.ne[2], i1 = row % x.ne[1];
@@ -127,11 +131,56 @@ __global__ void __launch_bounds__(256) rms_norm_kernel(T4 x, T4 y, float eps) {
     for (int i = threadIdx.x; i < n; i += blockDim.x) yp[i] = xp[i] * scale;
 }
 
+// ---- [ADD +] RMS_NORM [+ MUL] in one launch: x = a (+ b, optionally written out), y = (x / sqrt(mean(x^2) + eps)) (* w) ----------
+// The three operators are consecutive nodes twice per decoder layer (residual add -> norm -> norm weight); a decode token pays
+// ~3.5 us per launch, and the stand-alone norm re-read its row through possibly-aliasing pointers.  One CTA per row, the row
+// lives in registers (n <= 8 * blockDim.x), same arithmetic as the separate kernels (sum, then x * scale, then * w: no FMA
+// across the operator boundaries).  w is broadcast over rows as ggml's MUL does (index modulo its extents).
+template <bool ADD, bool MUL> __global__ void __launch_bounds__(1024) norm_fused_kernel(T4 a, T4 b, T4 so, T4 w, T4 y, float eps, int write_sum) {
+    pdl_grid_sync();
+    __shared__ float sh[32];
+    const long long row = blockIdx.x;
+    const long long i3 = row / (a.ne[1] * a.ne[2]), i2 = (row / a.ne[1]) % a.ne[2], i1 = row % a.ne[1];
+    const float * __restrict__ ap = (const float *) (a.data + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
+    const float * __restrict__ bp = ADD ? (const float *) (b.data + i1 * b.nb[1] + i2 * b.nb[2] + i3 * b.nb[3]) : nullptr;
+    float *       sp = ADD && write_sum ? (float *) (so.data + i1 * so.nb[1] + i2 * so.nb[2] + i3 * so.nb[3]) : nullptr;
+    const float * __restrict__ wp = MUL ? (const float *) (w.data + (i1 % w.ne[1]) * w.nb[1] + (i2 % w.ne[2]) * w.nb[2] + (i3 % w.ne[3]) * w.nb[3]) : nullptr;
+    float *       yp = (float *) (y.data + i1 * y.nb[1] + i2 * y.nb[2] + i3 * y.nb[3]);
+    const int     n  = (int) a.ne[0];
+    float v[8];
+    float s = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int i = threadIdx.x + j * blockDim.x;
+        float x = 0.0f;
+        if (i < n) {
+            x = ap[i];
+            if (ADD) {
+                x = x + bp[i];
+                if (sp) sp[i] = x;
+            }
+        }
+        v[j] = x;
+        s += x * x;
+    }
+    s = block_reduce<false>(s, sh);
+    const float scale = 1.0f / sqrtf(s / (float) n + eps);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int i = threadIdx.x + j * blockDim.x;
+        if (i < n) {
+            const float t = v[j] * scale;
+            yp[i] = MUL ? t * wp[i] : t;
+        }
+    }
+}
+
 // ---- binary ops with ggml broadcasting: dst = src0 (op) src1, src1 repeated along every dim ---------------------------------
 template <int OP> __device__ __forceinline__ float bin_apply(float a, float b) {
     return OP == B200Q_BIN_ADD ? a + b : OP == B200Q_BIN_SUB ? a - b : OP == B200Q_BIN_MUL ? a * b : a / b;
 }
 template <int OP> __global__ void __launch_bounds__(256) bin_kernel(T4 a, T4 b, T4 d, long long n) {
+    pdl_grid_sync();
     for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
         const long long i0 = i % d.ne[0], r = i / d.ne[0];
         const long long i1 = r % d.ne[1], r2 = r / d.ne[1];
@@ -163,15 +212,18 @@ __device__ __forceinline__ float unary_apply(int op, float x) {
     }
 }
 __global__ void __launch_bounds__(256) unary_kernel(const float * x, float * y, long long n, int op) {
+    pdl_grid_sync();
     for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) y[i] = unary_apply(op, x[i]);
 }
 __global__ void __launch_bounds__(256) scale_kernel(const float * x, float * y, long long n, float s, float b) {
+    pdl_grid_sync();
     for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) y[i] = x[i] * s + b;
 }
 
 // ---- GLU: dst[r][c] = act(x[r][c]) * g[r][c]; x and g are the two halves of one row or two tensors ------------------------------
 __global__ void __launch_bounds__(256) glu_kernel(const char * x, const char * g, char * d, long long nr, int nc, long long x_nb1,
                                                   long long g_nb1, long long d_nb1, int op, float alpha, float limit) {
+    pdl_grid_sync();
     const long long n = nr * nc;
     for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
         const long long r = i / nc;
@@ -196,6 +248,7 @@ __global__ void __launch_bounds__(256) glu_kernel(const char * x, const char * g
 // ---- SOFT_MAX over rows: softmax(x * scale + slope(head) * mask [, sink]), one CTA per row ----------------------------------
 template <bool MASK_F16> __global__ void __launch_bounds__(256) soft_max_kernel(T4 x, T4 m, const float * sinks, T4 d, float scale, float max_bias,
                                                                                 float m0, float m1, unsigned n_head_log2) {
+    pdl_grid_sync();
     __shared__ float sh[32];
     const long long row = blockIdx.x;
     const long long i3 = row / (x.ne[1] * x.ne[2]), i2 = (row / x.ne[1]) % x.ne[2], i1 = row % x.ne[1];
@@ -232,6 +285,7 @@ struct RopeP {
     float theta_scale, freq_scale, ext_factor, attn_factor, corr0, corr1;
 };
 template <int TYPE> __global__ void __launch_bounds__(256) rope_kernel(T4 x, const int * pos, const float * ff, T4 d, RopeP p) {
+    pdl_grid_sync();
     const long long half = x.ne[0] / 2, n = half * x.ne[1] * x.ne[2] * x.ne[3];
     for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
         const long long ip = i % half, r = i / half;
@@ -265,6 +319,7 @@ template <int TYPE> __global__ void __launch_bounds__(256) rope_kernel(T4 x, con
 
 // ---- CPY / CONT / DUP: element i of src (logical order) -> element i of dst (logical order), with type conversion ----------------
 template <int TS, int TD> __global__ void __launch_bounds__(256) cpy_kernel(T4 s, T4 d, long long n) {
+    pdl_grid_sync();
     for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
         long long r = i;
         const long long s0 = r % s.ne[0]; r /= s.ne[0];
@@ -281,6 +336,7 @@ template <int TS, int TD> __global__ void __launch_bounds__(256) cpy_kernel(T4 s
 
 // ---- SET_ROWS: dst[idx[i1, i2 % ne11, i3 % ne12]][i2][i3] = src[i1][i2][i3] (rows), idx i64 ------------------------------------
 template <int TD> __global__ void __launch_bounds__(256) set_rows_kernel(T4 s, T4 idx, T4 d, long long n) {
+    pdl_grid_sync();
     for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
         long long r = i;
         const long long i0 = r % s.ne[0]; r /= s.ne[0];
@@ -294,6 +350,7 @@ template <int TD> __global__ void __launch_bounds__(256) set_rows_kernel(T4 s, T
 
 // ---- ADD_ID: dst[i0, i1, i2] = a[i0, i1, i2] + b[i0, ids[i1, i2]] (the per-expert bias of a MoE layer; add-id.cu) ----------------
 __global__ void __launch_bounds__(256) add_id_kernel(T4 a, T4 b, T4 ids, T4 d, long long n) {
+    pdl_grid_sync();
     for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
         long long r = i;
         const long long i0 = r % a.ne[0]; r /= a.ne[0];
@@ -308,6 +365,7 @@ __global__ void __launch_bounds__(256) add_id_kernel(T4 a, T4 b, T4 ids, T4 d, l
 // ---- ARGSORT: per row, the indices that sort it (MoE routers: top-k = a view of the descending argsort; argsort.cu) ----------
 // one CTA per row, bitonic network over the next power of two (padding sorts last), ne0 <= 1024
 __global__ void __launch_bounds__(1024) argsort_kernel(T4 s, T4 d, int npad, int desc) {
+    pdl_grid_sync();
     extern __shared__ int as_idx[];
     const long long r  = blockIdx.x;
     const long long i1 = r % s.ne[1], i2 = (r / s.ne[1]) % s.ne[2], i3 = r / (s.ne[1] * s.ne[2]);
@@ -339,9 +397,9 @@ __global__ void __launch_bounds__(1024) argsort_kernel(T4 s, T4 d, int npad, int
 template <int TS> int cpy_to(const b200q_tensor * s, const b200q_tensor * d, long long n, cudaStream_t st) {
     const int g = grid_for(n, 256);
     switch (d->type) {
-        case B200Q_TYPE_F32:  cpy_kernel<TS, B200Q_TYPE_F32><<<g, 256, 0, st>>>(t4(s), t4(d), n); break;
-        case B200Q_TYPE_F16:  cpy_kernel<TS, B200Q_TYPE_F16><<<g, 256, 0, st>>>(t4(s), t4(d), n); break;
-        case B200Q_TYPE_BF16: cpy_kernel<TS, B200Q_TYPE_BF16><<<g, 256, 0, st>>>(t4(s), t4(d), n); break;
+        case B200Q_TYPE_F32:  launch_pdl(cpy_kernel<TS, B200Q_TYPE_F32>, dim3(g), dim3(256), 0, st, t4(s), t4(d), n); break;
+        case B200Q_TYPE_F16:  launch_pdl(cpy_kernel<TS, B200Q_TYPE_F16>, dim3(g), dim3(256), 0, st, t4(s), t4(d), n); break;
+        case B200Q_TYPE_BF16: launch_pdl(cpy_kernel<TS, B200Q_TYPE_BF16>, dim3(g), dim3(256), 0, st, t4(s), t4(d), n); break;
         default: return ops_fail(B200Q_ENOTSUP, "cpy: destination type");
     }
     return launched();
@@ -358,7 +416,31 @@ int b200q_op_rms_norm(const b200q_tensor * src, const b200q_tensor * dst, float 
     const long long nr = nrows(src);
     if (nr == 0 || src->ne[0] == 0) return 0;
     if (nr > 0x7fffffffLL) return ops_fail(B200Q_ENOTSUP, "rms_norm: too many rows");
-    rms_norm_kernel<<<(unsigned) nr, 256, 0, (cudaStream_t) stream>>>(t4(src), t4(dst), eps);
+    if (src->ne[0] <= 8192) {  // the row fits the registers of one CTA
+        const int threads = src->ne[0] <= 2048 ? 256 : 1024;
+        launch_pdl(norm_fused_kernel<false, false>, dim3((unsigned) nr), dim3(threads), 0, (cudaStream_t) stream, t4(src), t4(src), t4(src), t4(src), t4(dst), eps, 0);
+    } else {
+        launch_pdl(rms_norm_kernel, dim3((unsigned) nr), dim3(256), 0, (cudaStream_t) stream, t4(src), t4(dst), eps);
+    }
+    return launched();
+}
+
+// fused [ADD +] RMS_NORM + MUL (see norm_fused_kernel): a (+ b) -> sum_out (optional) ; dst = rms_norm(a (+ b)) * w
+int b200q_op_norm_fused(const b200q_tensor * a, const b200q_tensor * b, const b200q_tensor * sum_out, const b200q_tensor * w,
+                        const b200q_tensor * dst, float eps, void * stream) {
+    auto f32row = [](const b200q_tensor * t) { return t && t->type == B200Q_TYPE_F32 && t->nb[0] == 4; };
+    if (!f32row(a) || !f32row(w) || !f32row(dst) || !same_shape(a, dst) || w->ne[0] != a->ne[0] || a->ne[0] > 8192 || a->ne[0] < 1 ||
+        (b && (!f32row(b) || !same_shape(a, b))) || (sum_out && (!b || !f32row(sum_out) || !same_shape(a, sum_out))) ||
+        a->ne[1] % w->ne[1] || a->ne[2] % w->ne[2] || a->ne[3] % w->ne[3]) {
+        return ops_fail(B200Q_ENOTSUP, "norm_fused: f32 rows of at most 8192 values, b / sum_out shaped like a, w broadcast over rows");
+    }
+    const long long nr = nrows(a);
+    if (nr == 0) return 0;
+    if (nr > 0x7fffffffLL) return ops_fail(B200Q_ENOTSUP, "norm_fused: too many rows");
+    const int threads = a->ne[0] <= 2048 ? 256 : 1024;
+    cudaStream_t st = (cudaStream_t) stream;
+    if (b) launch_pdl(norm_fused_kernel<true, true>, dim3((unsigned) nr), dim3(threads), 0, st, t4(a), t4(b), t4(sum_out ? sum_out : a), t4(w), t4(dst), eps, sum_out ? 1 : 0);
+    else launch_pdl(norm_fused_kernel<false, true>, dim3((unsigned) nr), dim3(threads), 0, st, t4(a), t4(a), t4(a), t4(w), t4(dst), eps, 0);
     return launched();
 }
 
@@ -372,10 +454,10 @@ int b200q_op_bin(int op, const b200q_tensor * a, const b200q_tensor * b, const b
     const int g = grid_for(n, 256);
     cudaStream_t st = (cudaStream_t) stream;
     switch (op) {
-        case B200Q_BIN_ADD: bin_kernel<B200Q_BIN_ADD><<<g, 256, 0, st>>>(t4(a), t4(b), t4(dst), n); break;
-        case B200Q_BIN_SUB: bin_kernel<B200Q_BIN_SUB><<<g, 256, 0, st>>>(t4(a), t4(b), t4(dst), n); break;
-        case B200Q_BIN_MUL: bin_kernel<B200Q_BIN_MUL><<<g, 256, 0, st>>>(t4(a), t4(b), t4(dst), n); break;
-        case B200Q_BIN_DIV: bin_kernel<B200Q_BIN_DIV><<<g, 256, 0, st>>>(t4(a), t4(b), t4(dst), n); break;
+        case B200Q_BIN_ADD: launch_pdl(bin_kernel<B200Q_BIN_ADD>, dim3(g), dim3(256), 0, st, t4(a), t4(b), t4(dst), n); break;
+        case B200Q_BIN_SUB: launch_pdl(bin_kernel<B200Q_BIN_SUB>, dim3(g), dim3(256), 0, st, t4(a), t4(b), t4(dst), n); break;
+        case B200Q_BIN_MUL: launch_pdl(bin_kernel<B200Q_BIN_MUL>, dim3(g), dim3(256), 0, st, t4(a), t4(b), t4(dst), n); break;
+        case B200Q_BIN_DIV: launch_pdl(bin_kernel<B200Q_BIN_DIV>, dim3(g), dim3(256), 0, st, t4(a), t4(b), t4(dst), n); break;
         default: return ops_fail(B200Q_EINVAL, "bin: unknown op");
     }
     return launched();
@@ -387,7 +469,7 @@ int b200q_op_scale(const b200q_tensor * src, const b200q_tensor * dst, float sca
     }
     const long long n = nelem(src);
     if (n == 0) return 0;
-    scale_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t) stream>>>((const float *) src->data, (float *) dst->data, n, scale, bias);
+    launch_pdl(scale_kernel, dim3(grid_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, (const float *) src->data, (float *) dst->data, n, scale, bias);
     return launched();
 }
 
@@ -398,7 +480,7 @@ int b200q_op_unary(int op, const b200q_tensor * src, const b200q_tensor * dst, v
     }
     const long long n = nelem(src);
     if (n == 0) return 0;
-    unary_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t) stream>>>((const float *) src->data, (float *) dst->data, n, op);
+    launch_pdl(unary_kernel, dim3(grid_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, (const float *) src->data, (float *) dst->data, n, op);
     return launched();
 }
 
@@ -417,7 +499,7 @@ int b200q_op_glu(int op, const b200q_tensor * src0, const b200q_tensor * src1, c
         x += swapped ? nc * 4 : 0;
         g += swapped ? 0 : nc * 4;
     }
-    glu_kernel<<<grid_for(nr * nc, 256), 256, 0, (cudaStream_t) stream>>>(x, g, (char *) dst->data, nr, (int) nc, (long long) src0->nb[1],
+    launch_pdl(glu_kernel, dim3(grid_for(nr * nc, 256)), dim3(256), 0, (cudaStream_t) stream, x, g, (char *) dst->data, nr, (int) nc, (long long) src0->nb[1],
                                                                          (long long) (src1 ? src1->nb[1] : src0->nb[1]), (long long) dst->nb[1], op, alpha, limit);
     return launched();
 }
@@ -441,9 +523,9 @@ int b200q_op_soft_max(const b200q_tensor * src, const b200q_tensor * mask, const
     if (mask) m = t4(mask);
     cudaStream_t st = (cudaStream_t) stream;
     if (mask && mask->type == B200Q_TYPE_F16) {
-        soft_max_kernel<true><<<(unsigned) nr, 256, 0, st>>>(t4(src), m, sinks ? (const float *) sinks->data : nullptr, t4(dst), scale, max_bias, m0, m1, n_head_log2);
+        launch_pdl(soft_max_kernel<true>, dim3((unsigned) nr), dim3(256), 0, st, t4(src), m, sinks ? (const float *) sinks->data : nullptr, t4(dst), scale, max_bias, m0, m1, n_head_log2);
     } else {
-        soft_max_kernel<false><<<(unsigned) nr, 256, 0, st>>>(t4(src), m, sinks ? (const float *) sinks->data : nullptr, t4(dst), scale, max_bias, m0, m1, n_head_log2);
+        launch_pdl(soft_max_kernel<false>, dim3((unsigned) nr), dim3(256), 0, st, t4(src), m, sinks ? (const float *) sinks->data : nullptr, t4(dst), scale, max_bias, m0, m1, n_head_log2);
     }
     return launched();
 }
@@ -468,8 +550,8 @@ int b200q_op_rope(const b200q_tensor * src, const b200q_tensor * pos, const b200
     p.corr0 = rp->corr_dims[0]; p.corr1 = rp->corr_dims[1];
     const float * ff = freq_factors ? (const float *) freq_factors->data : nullptr;
     cudaStream_t  st = (cudaStream_t) stream;
-    if (src->type == B200Q_TYPE_F32) rope_kernel<B200Q_TYPE_F32><<<grid_for(n, 256), 256, 0, st>>>(t4(src), (const int *) pos->data, ff, t4(dst), p);
-    else rope_kernel<B200Q_TYPE_F16><<<grid_for(n, 256), 256, 0, st>>>(t4(src), (const int *) pos->data, ff, t4(dst), p);
+    if (src->type == B200Q_TYPE_F32) launch_pdl(rope_kernel<B200Q_TYPE_F32>, dim3(grid_for(n, 256)), dim3(256), 0, st, t4(src), (const int *) pos->data, ff, t4(dst), p);
+    else launch_pdl(rope_kernel<B200Q_TYPE_F16>, dim3(grid_for(n, 256)), dim3(256), 0, st, t4(src), (const int *) pos->data, ff, t4(dst), p);
     return launched();
 }
 
@@ -493,7 +575,7 @@ int b200q_op_add_id(const b200q_tensor * a, const b200q_tensor * b, const b200q_
     }
     const long long n = nelem(a);
     if (n == 0) return 0;
-    add_id_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t) stream>>>(t4(a), t4(b), t4(ids), t4(dst), n);
+    launch_pdl(add_id_kernel, dim3(grid_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, t4(a), t4(b), t4(ids), t4(dst), n);
     return launched();
 }
 
@@ -507,7 +589,7 @@ int b200q_op_argsort(const b200q_tensor * src, const b200q_tensor * dst, int des
     if (rows > 0x7fffffffll) return ops_fail(B200Q_ENOTSUP, "argsort: too many rows");
     int npad = 1;
     while (npad < src->ne[0]) npad <<= 1;
-    argsort_kernel<<<(unsigned) rows, npad < 32 ? 32 : npad, npad * sizeof(int), (cudaStream_t) stream>>>(t4(src), t4(dst), npad, descending ? 1 : 0);
+    launch_pdl(argsort_kernel, dim3((unsigned) rows), dim3(npad < 32 ? 32 : npad), npad * sizeof(int), (cudaStream_t) stream, t4(src), t4(dst), npad, descending ? 1 : 0);
     return launched();
 }
 
@@ -521,9 +603,9 @@ int b200q_op_set_rows(const b200q_tensor * src, const b200q_tensor * idx, const 
     const int g = grid_for(n, 256);
     cudaStream_t st = (cudaStream_t) stream;
     switch (dst->type) {
-        case B200Q_TYPE_F32:  set_rows_kernel<B200Q_TYPE_F32><<<g, 256, 0, st>>>(t4(src), t4(idx), t4(dst), n); break;
-        case B200Q_TYPE_F16:  set_rows_kernel<B200Q_TYPE_F16><<<g, 256, 0, st>>>(t4(src), t4(idx), t4(dst), n); break;
-        case B200Q_TYPE_BF16: set_rows_kernel<B200Q_TYPE_BF16><<<g, 256, 0, st>>>(t4(src), t4(idx), t4(dst), n); break;
+        case B200Q_TYPE_F32:  launch_pdl(set_rows_kernel<B200Q_TYPE_F32>, dim3(g), dim3(256), 0, st, t4(src), t4(idx), t4(dst), n); break;
+        case B200Q_TYPE_F16:  launch_pdl(set_rows_kernel<B200Q_TYPE_F16>, dim3(g), dim3(256), 0, st, t4(src), t4(idx), t4(dst), n); break;
+        case B200Q_TYPE_BF16: launch_pdl(set_rows_kernel<B200Q_TYPE_BF16>, dim3(g), dim3(256), 0, st, t4(src), t4(idx), t4(dst), n); break;
         default: return ops_fail(B200Q_ENOTSUP, "set_rows: destination type");
     }
     return launched();

@@ -14,6 +14,7 @@
 // (ggml_backend_buffer_init, ggml_nbytes, ...) are resolved from the host process at load time — the plugin
 // is deliberately not linked against any ggml library (and never against anything under oracle/).
 #include "ggml-backend-impl.h"
+#include "ggml-impl.h"
 #include "ggml-backend.h"
 #include "ggml.h"
 
@@ -42,7 +43,7 @@ namespace {
         if (rc_ != 0) b200_abort(#expr, rc_, __FILE__, __LINE__);  \
     } while (0)
 
-constexpr size_t TENSOR_ALIGNMENT = 128;
+constexpr size_t B200_TENSOR_ALIGNMENT = 128;
 constexpr size_t BUFFER_SLACK     = 256;  // the kernels' 16-byte aligned bulk windows may over-read up to 15 bytes
 
 constexpr int    MAX_DEVICES  = 16;           // length of the tensor_split array llama passes (GGML_CUDA_MAX_DEVICES)
@@ -228,7 +229,7 @@ ggml_backend_buffer_t buft_alloc_buffer(ggml_backend_buffer_type_t buft, size_t 
     }
     return ggml_backend_buffer_init(buft, buffer_iface, new b200_buffer_ctx{ d->device, base }, size);
 }
-size_t buft_get_alignment(ggml_backend_buffer_type_t) { return TENSOR_ALIGNMENT; }
+size_t buft_get_alignment(ggml_backend_buffer_type_t) { return B200_TENSOR_ALIGNMENT; }
 size_t buft_get_alloc_size(ggml_backend_buffer_type_t, const ggml_tensor * tensor) {
     // quantized rows are read through 16-byte aligned windows: keep 16 bytes of slack behind every such tensor so a
     // window never touches another tensor's bytes that a concurrent copy might be writing
@@ -367,7 +368,7 @@ ggml_backend_buffer_t split_buft_alloc_buffer(ggml_backend_buffer_type_t buft, s
     // bound ggml-alloc enforces, as returned by get_alloc_size
     return ggml_backend_buffer_init(buft, split_buffer_iface, new b200_split_buffer_ctx, size);
 }
-size_t split_buft_get_alignment(ggml_backend_buffer_type_t) { return TENSOR_ALIGNMENT; }
+size_t split_buft_get_alignment(ggml_backend_buffer_type_t) { return B200_TENSOR_ALIGNMENT; }
 size_t split_buft_get_alloc_size(ggml_backend_buffer_type_t buft, const ggml_tensor * tensor) {
     auto * bc = (b200_split_buft_ctx *) buft->context;
     GGML_ASSERT(ggml_is_contiguous(tensor) && "split buffers only supported for contiguous tensors");
@@ -906,14 +907,42 @@ bool list_candidate(const ggml_tensor * op) {
     if (b->nb[0] != 4 || op->nb[0] != 4 || ((uintptr_t) a->data & 15) || ((uintptr_t) b->data & 15)) return false;
     return true;
 }
-// tries to run nodes [first, ...) as a list; returns the index behind the run (== first when no list was launched)
-int compute_list_run(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int first, int n_nodes) {
+// Tries to run the decode matmuls that start at node `first` as ONE persistent list.  Members are the consecutive candidates
+// and — llama.cpp emits q, rope(q), k, rope(k), v: matmuls of one vector separated by other nodes — candidates up to a few
+// nodes further that multiply a vector an earlier member already multiplies.  Such a member runs EARLIER than its place in
+// the graph, which is only legal if nothing in between touches its result's memory (ggml-alloc reuses buffers): its dst range
+// must not overlap the dst or any source of a skipped node or of an earlier member.  Marks the members in `done` and returns
+// how many there are (0: no list was launched, nothing marked).
+bool ranges_overlap(const ggml_tensor * a, const ggml_tensor * b) {
+    if (!a || !b || !a->data || !b->data) return false;
+    const char * a0 = (const char *) a->data, * a1 = a0 + ggml_nbytes(a);
+    const char * b0 = (const char *) b->data, * b1 = b0 + ggml_nbytes(b);
+    return a0 < b1 && b0 < a1;
+}
+bool touches(const ggml_tensor * node, const ggml_tensor * t) {  // does `node` read or write memory of t's result?
+    if (ranges_overlap(node, t)) return true;
+    for (int j = 0; j < GGML_MAX_SRC; ++j) if (node->src[j] && ranges_overlap(node->src[j], t)) return true;
+    return false;
+}
+int compute_list_run(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int first, int n_nodes, std::vector<char> & done) {
     std::vector<b200q_list_op> ops;
-    int end = first;
+    std::vector<int>           members, skipped;
+    static const bool no_hoist = getenv("GGML_B200_NO_HOIST") != nullptr;
     for (int i = first; i < n_nodes && ops.size() < 64; ++i) {
         ggml_tensor * t = ggml_graph_node(cgraph, i);
-        if (noop_node(t)) continue;
-        if (!list_candidate(t)) break;
+        if (noop_node(t) || done[(size_t) i]) continue;
+        if (!list_candidate(t)) {
+            if (no_hoist || skipped.size() >= 6) break;
+            skipped.push_back(i);
+            continue;
+        }
+        if (!skipped.empty()) {
+            bool ok = false;
+            for (int mi : members) ok = ok || ggml_graph_node(cgraph, mi)->src[1]->data == t->src[1]->data;  // the vector is ready
+            for (int si : skipped) ok = ok && !touches(ggml_graph_node(cgraph, si), t) && !ranges_overlap(ggml_graph_node(cgraph, si), t->src[1]);
+            for (int mi : members) ok = ok && !touches(ggml_graph_node(cgraph, mi), t);
+            if (!ok) break;
+        }
         b200q_list_op o{};
         o.type = (int) t->src[0]->type; o.m = t->src[0]->ne[1]; o.k = t->src[0]->ne[0];
         o.w = t->src[0]->data; o.act = (const float *) t->src[1]->data; o.dst = (float *) t->data;
@@ -923,9 +952,9 @@ int compute_list_run(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int first, in
             if (a0 < d1 && d0 < a1) o.flags |= B200Q_LIST_DEP;
         }
         ops.push_back(o);
-        end = i + 1;
+        members.push_back(i);
     }
-    if (ops.size() < 2) return first;
+    if (ops.size() < 2) return 0;
     std::vector<int64_t> key;
     key.reserve(ops.size() * 6);
     for (const b200q_list_op & o : ops) {
@@ -954,9 +983,10 @@ int compute_list_run(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int first, in
         it = ctx->lists.emplace(key, l).first;
         ctx->list_order.push_back(key);
     }
-    if (!it->second) return first;
-    if (b200q_list_launch(it->second, ctx->stream) != 0) return first;
-    return end;
+    if (!it->second) return 0;
+    if (b200q_list_launch(it->second, ctx->stream) != 0) return 0;
+    for (int mi : members) done[(size_t) mi] = 1;
+    return (int) members.size();
 }
 
 ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph);
@@ -1047,20 +1077,69 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) 
     return b200q_graph_launch(it->second.exec, ctx->stream) == 0 ? GGML_STATUS_SUCCESS : GGML_STATUS_FAILED;
 }
 
+// [ADD ->] RMS_NORM -> MUL as one launch (b200q_op_norm_fused; the reference fuses the same run, ggml-cuda.cu:2811-2845,
+// 3000-3040).  Returns the number of nodes consumed (0: no fusion here).  The norm's own output is never written, so it
+// must have the MUL as its only consumer and be neither a view source nor a graph output (ggml_node_has_n_uses).
+int try_fuse_norm(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int i, int n_nodes, int * rc) {
+    auto f32row = [](const ggml_tensor * t) { return t && t->type == GGML_TYPE_F32 && t->nb[0] == sizeof(float); };
+    const ggml_tensor * add = nullptr;
+    int j = i;
+    if (ggml_graph_node(cgraph, j)->op == GGML_OP_ADD) {
+        add = ggml_graph_node(cgraph, j);
+        ++j;
+    }
+    if (j + 1 >= n_nodes) return 0;
+    const ggml_tensor * norm = ggml_graph_node(cgraph, j);
+    const ggml_tensor * mul  = ggml_graph_node(cgraph, j + 1);
+    if (norm->op != GGML_OP_RMS_NORM || mul->op != GGML_OP_MUL || !cgraph->use_counts) return 0;
+    if (add && norm->src[0] != add) return 0;
+    if (mul->src[0] != norm && mul->src[1] != norm) return 0;
+    if (!ggml_node_has_n_uses(cgraph, j, 1)) return 0;
+    const ggml_tensor * x = norm->src[0];
+    const ggml_tensor * w = mul->src[0] == norm ? mul->src[1] : mul->src[0];
+    if (!f32row(x) || !f32row(norm) || !f32row(mul) || !f32row(w) || x->ne[0] > 8192 || w->ne[0] != x->ne[0]) return 0;
+    if (!ggml_are_same_shape(x, norm) || !ggml_are_same_shape(norm, mul)) return 0;
+    for (int d = 1; d < 4; ++d) if (x->ne[d] % w->ne[d]) return 0;
+    if (tensor_is_split(w) || tensor_is_split(x)) return 0;
+    float eps;
+    memcpy(&eps, norm->op_params, sizeof(float));
+    const b200q_tensor tw = bt(w), td = bt(mul);
+    if (add) {
+        const ggml_tensor * a = add->src[0];
+        const ggml_tensor * b = add->src[1];
+        if (!f32row(a) || !f32row(b) || !f32row(add) || !ggml_are_same_shape(a, add) || !ggml_are_same_shape(b, add)) return 0;
+        const b200q_tensor ta = bt(a), tb = bt(b), ts = bt(add);
+        *rc = b200q_op_norm_fused(&ta, &tb, &ts, &tw, &td, eps, ctx->stream);
+        return 3;
+    }
+    const b200q_tensor tx = bt(x);
+    *rc = b200q_op_norm_fused(&tx, nullptr, nullptr, &tw, &td, eps, ctx->stream);
+    return 2;
+}
+
 ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
     const int  n_nodes  = ggml_graph_n_nodes(cgraph);
+    const bool no_fuse  = getenv("GGML_B200_NO_FUSE") != nullptr;
+    std::vector<char> done((size_t) n_nodes, 0);  // nodes that already went out with an earlier list
     const bool no_lists = getenv("GGML_B200_NO_LIST") != nullptr;
     for (int i = 0; i < n_nodes; ++i) {
         ggml_tensor * node = ggml_graph_node(cgraph, i);
-        if (ggml_is_empty(node)) continue;
+        if (ggml_is_empty(node) || done[(size_t) i]) continue;
         if (!no_lists && list_candidate(node)) {
-            const int next = compute_list_run(ctx, cgraph, i, n_nodes);
-            if (next > i) {
-                i = next - 1;
+            if (compute_list_run(ctx, cgraph, i, n_nodes, done) > 0) continue;
+        }
+        int rc = 0;
+        if (!no_fuse && (node->op == GGML_OP_ADD || node->op == GGML_OP_RMS_NORM)) {
+            const int used = try_fuse_norm(ctx, cgraph, i, n_nodes, &rc);
+            if (used > 0) {
+                if (rc != 0) {
+                    fprintf(stderr, "ggml-b200: fused norm (%s) failed (%d): %s\n", node->name, rc, b200q_last_error());
+                    return GGML_STATUS_FAILED;
+                }
+                i += used - 1;
                 continue;
             }
         }
-        int rc = 0;
         switch (node->op) {
             case GGML_OP_NONE:
             case GGML_OP_VIEW:
