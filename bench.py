@@ -104,6 +104,7 @@ def parse_args():
     ap.add_argument("--workload", default="llama3-8b-q4_k_m", choices=["llama3-8b-q4_k_m", "llama3-70b-q4_k"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-llama-bench", action="store_true", help="skip the aux leg that runs the reference's llama-bench on the plugin")
     return ap.parse_args()
 
 
@@ -331,6 +332,51 @@ def aux_single_gpu(torch, b200q, workloads, peak_hbm, bf16_peak):
     except Exception as e:
         aux["config4_mxfp4_moe"] = {"error": repr(e)}
     return aux
+
+
+def aux_llama_bench():
+    """tg128 / pp512 tok/s of the reference's OWN llama-bench (oracle/_ref/llama-bench, compiled unmodified by `make -C oracle
+    llama`; the second half of BASELINE.json's metric) on the plugin, synthetic-weight Llama-3-8B Q4_K_M GGUF written by
+    tools/make_synth_gguf.py.  Runs in a child process after this process has released nothing it needs (the model is 4.9 GB);
+    absent binary -> a note, never an error for the headline."""
+    import re
+    import subprocess
+    import tempfile
+    d = os.path.join(ROOT, "oracle", "_ref")
+    try:
+        with open("/proc/cpuinfo") as f:
+            if "avx512_vnni" in f.read() and os.path.exists(os.path.join(d, "avx512", "llama-bench")):
+                d = os.path.join(d, "avx512")
+    except OSError:
+        pass
+    exe = os.path.join(d, "llama-bench")
+    plugin = os.path.join(ROOT, "llama.cpp-gfx906_b200", "lib", "libggml-b200.so")
+    if not (os.path.exists(exe) and os.path.exists(plugin)):
+        return {"unavailable": "oracle/_ref/llama-bench not built (make -C oracle llama)"}
+    gguf = os.path.join(tempfile.gettempdir(), f"b200q-synth-{os.getpid()}.gguf")
+    try:
+        subprocess.run([sys.executable, os.path.join(ROOT, "tools", "make_synth_gguf.py"), "--out", gguf, "--layers", "32", "--ftype", "q4_k_m"],
+                       check=True, capture_output=True, timeout=300)
+        env = dict(os.environ, GGML_BACKEND_PATH=plugin)
+        r = subprocess.run([exe, "-m", gguf, "-ngl", "99", "-fa", "0", "-p", "512", "-n", "128", "-r", "3"], env=env, capture_output=True,
+                           text=True, timeout=600)
+        res = {}
+        for line in r.stdout.splitlines():
+            m = re.search(r"\|\s*(B200|CPU)\s*\|.*\|\s*(pp512|tg128)\s*\|\s*([0-9.]+)\s*±\s*([0-9.]+)", line)
+            if m:
+                res[m.group(2)] = {"tok_s": float(m.group(3)), "stdev": float(m.group(4)), "backend": m.group(1)}
+        if not res:
+            return {"error": (r.stdout + r.stderr)[-400:]}
+        res["how"] = ("reference llama-bench (unmodified) -ngl 99 -fa 0 -p 512 -n 128 -r 3 through GGML_BACKEND_PATH=libggml-b200.so; "
+                      "synthetic-weight Llama-3-8B Q4_K_M GGUF (4.9 GB, no tokenizer)")
+        return res
+    except Exception as e:  # noqa: BLE001
+        return {"error": repr(e)}
+    finally:
+        try:
+            os.remove(gguf)
+        except OSError:
+            pass
 
 
 def main_b200(args):
@@ -744,6 +790,9 @@ def main_b200(args):
             aux["error"] = repr(e)
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = run_cpu_reference(cpu_sample_ops(ops), args.cpu_seconds)
+    if world == 1 and not args.no_llama_bench:
+        torch.cuda.empty_cache()
+        out.setdefault("aux", {})["llama_bench_8b_q4_k_m"] = aux_llama_bench()
     if rowsplit_parity not in (None, "bit-exact"):
         out["error"] = "row-split result differs from the single-GPU result"
     sys.stdout.flush()
