@@ -80,6 +80,10 @@ enum b200q_status {
 #define B200Q_FLAG_FORCE_GEMV        2u /* debugging / measurement: always take the GEMV kernels (8 columns per pass) */
 #define B200Q_FLAG_FORCE_MMQ         4u /* debugging / measurement: always take the tensor-core kernel */
 #define B200Q_FLAG_NO_PDL            8u /* launch without programmatic stream serialization */
+#define B200Q_FLAG_ACT_UNCHANGED    16u /* b200q_mul_mat: `act` holds the same values as in the previous b200q_mul_mat call that used
+                                           this workspace on this stream (wq / wk / wv, ffn_gate / ffn_up of one vector): the
+                                           tensor-core kernel may reuse the packed image it left in the workspace instead of
+                                           packing again; ignored when the previous call's layout differs */
 
 /* ---- library / device ---------------------------------------------------------------------- */
 B200Q_API int          b200q_version(void);

@@ -868,6 +868,7 @@ int b200q_mul_mat(const b200q_mul_mat_args * a, const void * w, const float * ac
         q.k = a->k; q.m = a->m; q.n = a->n; q.w = (const uint8_t *) w; q.act = act; q.dst = dst;
         q.w_nb1 = (long long) a->nb01; q.a_nb1 = (long long) a->nb11; q.d_nb1 = (long long) a->nb1;
         std::string err;
+        mmq_forget_pack();
         if (int rc = mxf_launch(q, workspace, st, di.sms, err)) return fail(rc, "%s", err.c_str());
         return 0;
     }
@@ -879,6 +880,7 @@ int b200q_mul_mat(const b200q_mul_mat_args * a, const void * w, const float * ac
         q.a_nb1 = (long long) a->nb11; q.a_nb2 = (long long) a->nb12; q.a_nb3 = (long long) a->nb13;
         q.d_nb1 = (long long) a->nb1;  q.d_nb2 = (long long) a->nb2;  q.d_nb3 = (long long) a->nb3;
         q.w = (const uint8_t *) w; q.act = act; q.dst = dst;
+        q.reuse_pack = (a->flags & B200Q_FLAG_ACT_UNCHANGED) != 0;
         const size_t need = mmq_workspace_bytes(a->k, a->n, a->ne12 * a->ne13);
         if (workspace_bytes < need || !workspace) {
             return fail(B200Q_EWORKSPACE, "mul_mat: workspace %zu < required %zu", workspace_bytes, need);
@@ -1120,6 +1122,7 @@ int b200q_mul_mat_id(const b200q_mul_mat_id_args * a, const void * as, const flo
         q.ids = ids; q.ids_nb1 = (long long) a->ids_nb1; q.n_expert = a->n_expert; q.n_used = a->n_used; q.n_tokens = a->n_tokens;
         q.b_bcast = a->b_ne1 == 1;
         std::string err;
+        mmq_forget_pack();
         if (int rc = mxf_launch(q, workspace, (cudaStream_t) stream, di.sms, err)) return fail(rc, "%s", err.c_str());
         return 0;
     }

@@ -137,6 +137,7 @@ struct PackParams {
     int   n_sub, n_super;  // blocks are ordered (batch, super-tile, k-chunk, column tile of the super-tile)
     long long a_nb1, a_nb2, a_nb3;
     int   vec4;
+    int   zero_only;  // the packed image is already in the workspace (same activations as the previous call): only clear dst
 };
 
 // f32 activations [n][k] (byte strides) -> bf16 tiles in the shared-memory image the MMA reads:
@@ -153,6 +154,7 @@ __global__ void __launch_bounds__(256) mmq_pack_act(const PackParams p) {
             *(float *) ((char *) p.zero_dst + (long long) i * 4 + col * p.d_nb1 + i12 * p.d_nb2 + i13 * p.d_nb3) = 0.0f;
         }
     }
+    if (p.zero_only) return;
     const long long chunks_per_block = TILE_N * 8;
     const long long total = (long long) p.nbatch * p.n_super * p.n_sub * p.k_chunks * chunks_per_block;
     for (long long idx = (long long) blockIdx.x * blockDim.x + threadIdx.x; idx < total;
@@ -910,6 +912,14 @@ size_t mmq_moe_workspace_bytes(int64_t k, int64_t n_tokens, int64_t n_used, int6
 
 static int mmq_launch_impl(const MmqArgs & a, const MmqMoeArgs * moe, void * workspace, cudaStream_t st, int sms, std::string & err);
 
+// what the last plain (non-MoE) launch of this thread packed, and where (see the reuse in mmq_launch)
+struct LastPack {
+    const void * ws = nullptr; const float * act = nullptr; cudaStream_t st = nullptr;
+    long long k = 0, n = 0, ne12 = 0, ne13 = 0, nb1 = 0, nb2 = 0, nb3 = 0; int n_sub = 0, n_super = 0;
+};
+static thread_local LastPack g_last_pack;
+void mmq_forget_pack() { g_last_pack = LastPack{}; }
+
 int mmq_launch(const MmqArgs & a, void * workspace, cudaStream_t st, int sms, std::string & err) {
     return mmq_launch_impl(a, nullptr, workspace, st, sms, err);
 }
@@ -1083,6 +1093,7 @@ static int mmq_launch_impl(const MmqArgs & a, const MmqMoeArgs * moe, void * wor
                 a.type, p.m, p.n, p.k, p.cluster, p.n_sub, p.ksplit, num_units, grid, p.w_stages, p.b_stages, p.w_pitch);
     }
     if (moe) {
+        g_last_pack = LastPack{};  // the workspace now holds the MoE tables and per-expert tiles
         MoeRouteParams rp{};
         rp.ids = moe->ids; rp.ids_nb1 = moe->ids_nb1;
         rp.n_tokens = (int) moe->n_tokens; rp.n_used = (int) moe->n_used; rp.n_expert = (int) moe->n_expert;
@@ -1099,9 +1110,23 @@ static int mmq_launch_impl(const MmqArgs & a, const MmqMoeArgs * moe, void * wor
             pp.d_nb1 = a.d_nb1; pp.d_nb2 = a.d_nb2; pp.d_nb3 = a.d_nb3;
         }
         pp.n_sub = p.n_sub; pp.n_super = p.n_super;
-        const long long total = (long long) nbatch * pp.n_super * pp.n_sub * pp.k_chunks * TILE_N * 8;
-        const int       pgrid = (int) std::min<long long>((total + 255) / 256, (long long) sms * 8);
-        mmq_pack_act<<<pgrid, 256, 0, st>>>(pp);
+        // consecutive matmuls of one activation matrix (wq / wk / wv, ffn_gate / ffn_up): the caller may state that `act` is
+        // unchanged since the previous call (a.reuse_pack); the image is reused when that call packed the same matrix in
+        // the same layout into the same workspace on the same stream (per thread: a backend drives its stream from one)
+        LastPack & last = g_last_pack;
+        LastPack   cur;
+        cur.ws = workspace; cur.act = a.act; cur.st = st; cur.k = a.k; cur.n = a.n; cur.ne12 = a.ne12; cur.ne13 = a.ne13;
+        cur.nb1 = a.a_nb1; cur.nb2 = a.a_nb2; cur.nb3 = a.a_nb3; cur.n_sub = p.n_sub; cur.n_super = p.n_super;
+        const bool same = a.reuse_pack && last.ws == cur.ws && last.act == cur.act && last.st == cur.st && last.k == cur.k && last.n == cur.n &&
+                          last.ne12 == cur.ne12 && last.ne13 == cur.ne13 && last.nb1 == cur.nb1 && last.nb2 == cur.nb2 && last.nb3 == cur.nb3 &&
+                          last.n_sub == cur.n_sub && last.n_super == cur.n_super;
+        last = cur;
+        pp.zero_only = same ? 1 : 0;
+        if (!same || pp.zero_dst) {
+            const long long total = same ? (long long) nbatch * a.n * a.m : (long long) nbatch * pp.n_super * pp.n_sub * pp.k_chunks * TILE_N * 8;
+            const int       pgrid = (int) std::min<long long>((total + 255) / 256, (long long) sms * 8);
+            mmq_pack_act<<<pgrid, 256, 0, st>>>(pp);
+        }
     }
     cudaError_t e = cudaLaunchKernelEx(&cfg, fn, p);
     if (e == cudaSuccess) e = cudaGetLastError();

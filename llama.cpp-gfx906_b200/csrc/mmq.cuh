@@ -17,7 +17,10 @@ struct MmqArgs {
     const uint8_t * w;
     const float *   act;
     float *         dst;
+    bool            reuse_pack = false;  // caller: `act` holds the same values as in the previous call (B200Q_FLAG_ACT_UNCHANGED)
 };
+
+void mmq_forget_pack();  // another kernel family is about to overwrite the workspace: no packed image to reuse
 
 struct MmqMoeArgs {  // MUL_MAT_ID through the tensor-core kernel (many tokens)
     int             type;

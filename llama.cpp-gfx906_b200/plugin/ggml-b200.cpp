@@ -99,6 +99,8 @@ struct b200_backend_ctx {
     std::map<std::vector<uint64_t>, graph_entry> graphs;
     std::vector<std::vector<uint64_t>>           graph_order;  // insertion order, for eviction
     bool                                         graphs_off = false;  // a capture broke once: stay eager
+    // the activation matrix the last tensor-core MUL_MAT of this graph packed into the workspace (nullptr: none / overwritten)
+    const ggml_tensor * packed_act = nullptr;
 };
 constexpr size_t MAX_CACHED_GRAPHS = 256;
 constexpr size_t MAX_CACHED_LISTS = 512;
@@ -748,7 +750,10 @@ b200q_tensor bt(const ggml_tensor * t);
 int compute_mul_mat(b200_backend_ctx * ctx, const ggml_tensor * op) {
     const ggml_tensor * a = op->src[0];
     const ggml_tensor * b = op->src[1];
-    if (tensor_is_split(a)) return compute_mul_mat_split(ctx, op);
+    if (tensor_is_split(a)) {
+        ctx->packed_act = nullptr;
+        return compute_mul_mat_split(ctx, op);
+    }
     b200q_mul_mat_args  q{};
     q.type = (int) a->type;
     q.k = a->ne[0]; q.m = a->ne[1]; q.n = b->ne[1];
@@ -757,6 +762,8 @@ int compute_mul_mat(b200_backend_ctx * ctx, const ggml_tensor * op) {
     q.nb11 = b->nb[1]; q.nb12 = b->nb[2]; q.nb13 = b->nb[3];
     q.nb1 = op->nb[1]; q.nb2 = op->nb[2]; q.nb3 = op->nb[3];
     q.flags = weight_flags(a);
+    if (ctx->packed_act == b && b->type == GGML_TYPE_F32) q.flags |= B200Q_FLAG_ACT_UNCHANGED;  // wq / wk / wv, gate / up: pack once
+    ctx->packed_act = b->type == GGML_TYPE_F32 ? b : nullptr;
     size_t conv = 0;  // f16 activations: a contiguous f32 copy at the head of the workspace
     if (b->type == GGML_TYPE_F16) {
         conv   = ((size_t) ggml_nelements(b) * sizeof(float) + 255) & ~(size_t) 255;
@@ -1121,10 +1128,15 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
     const int  n_nodes  = ggml_graph_n_nodes(cgraph);
     const bool no_fuse  = getenv("GGML_B200_NO_FUSE") != nullptr;
     std::vector<char> done((size_t) n_nodes, 0);  // nodes that already went out with an earlier list
+    ctx->packed_act = nullptr;
     const bool no_lists = getenv("GGML_B200_NO_LIST") != nullptr;
     for (int i = 0; i < n_nodes; ++i) {
         ggml_tensor * node = ggml_graph_node(cgraph, i);
         if (ggml_is_empty(node) || done[(size_t) i]) continue;
+        // a node that writes over the packed activations (in-place operators) or takes the workspace for something else
+        if (ctx->packed_act && (node->op == GGML_OP_MUL_MAT_ID || (node->op != GGML_OP_MUL_MAT && ranges_overlap(node, ctx->packed_act)))) {
+            ctx->packed_act = nullptr;
+        }
         if (!no_lists && list_candidate(node)) {
             if (compute_list_run(ctx, cgraph, i, n_nodes, done) > 0) continue;
         }
