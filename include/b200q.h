@@ -307,6 +307,12 @@ B200Q_API int b200q_op_glu(int op, const b200q_tensor * src0, const b200q_tensor
 /* mask (f32 | f16, broadcast over dims 2, 3) and sinks (f32 [n_head]) may be NULL */
 B200Q_API int b200q_op_soft_max(const b200q_tensor * src, const b200q_tensor * mask, const b200q_tensor * sinks,
                                 const b200q_tensor * dst, float scale, float max_bias, void * stream);                     /* softmax.cu */
+/* decode attention core in one launch (what llama.cpp emits without flash attention as MUL_MAT(k, q) -> SOFT_MAX -> MUL_MAT(v, kq) ->
+ * PERMUTE -> CONT, llama-graph.cpp:1285-1330): q f32 [hd, n_tok, n_head], k f16 [hd, n_kv, n_head_kv], v f16 [n_kv, hd, n_head_kv]
+ * (the transposed V cache), mask f32 | f16 [n_kv, >= n_tok, 1 | n_head] or NULL, sinks f32 [n_head] or NULL, dst f32 [hd, n_head, n_tok];
+ * n_kv <= 8192, meant for a handful of tokens */
+B200Q_API int b200q_op_attn_decode(const b200q_tensor * q, const b200q_tensor * k, const b200q_tensor * v, const b200q_tensor * mask,
+                                   const b200q_tensor * sinks, const b200q_tensor * dst, float scale, void * stream);
 B200Q_API int b200q_op_rope(const b200q_tensor * src, const b200q_tensor * pos, const b200q_tensor * freq_factors /* or NULL */,
                             const b200q_tensor * dst, const b200q_rope_params * p, void * stream);                         /* rope.cu */
 B200Q_API int b200q_op_cpy(const b200q_tensor * src, const b200q_tensor * dst, void * stream);       /* cpy.cu: CPY / CONT / DUP */

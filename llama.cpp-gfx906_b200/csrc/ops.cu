@@ -342,6 +342,109 @@ template <bool MASK_F16> __global__ void __launch_bounds__(256) soft_max_warp_ke
     }
 }
 
+// ---- decode attention core in one launch: softmax(scale * K^T q + mask [, sink]) applied to V -------------------------------------
+// llama.cpp without flash attention emits MUL_MAT(k, q) -> SOFT_MAX -> MUL_MAT(v, kq) -> PERMUTE -> CONT; at decode these are
+// four ~3.5 us launches per layer around a few hundred KB of KV cache.  One CTA per (head, token): scores of all cached
+// positions into shared memory (a warp per position, K rows are read 64 bytes per warp-load), the softmax in place, then a
+// warp per output element over the transposed V rows.  f32 arithmetic throughout, same operations as the separate kernels
+// (different summation order).  q [hd, n_tok, n_head] f32; k [hd, n_kv, n_head_kv] f16; v [n_kv, hd, n_head_kv] f16 (the
+// transposed V cache); mask [n_kv, >= n_tok, ...] f32 | f16 or none; dst [hd, n_head, n_tok] f32.
+struct AttnP {
+    T4            q, k, v, m, d;
+    const float * sinks;
+    float         scale;
+    int           mask_f16;
+};
+__device__ __forceinline__ float dot8_h(const uint4 raw, const float * x) {
+    const __half2 * h = (const __half2 *) &raw;
+    float a = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float2 f = __half22float2(h[i]);
+        a = fmaf(x[2 * i], f.x, a);
+        a = fmaf(x[2 * i + 1], f.y, a);
+    }
+    return a;
+}
+__global__ void __launch_bounds__(256) attn_decode_kernel(const AttnP p) {
+    pdl_grid_sync();
+    extern __shared__ float at_smem[];  // [n_kv] scores | [hd] q | [256] partial outputs
+    __shared__ float sh[32];
+    const int h = blockIdx.x, t = blockIdx.y, tid = threadIdx.x;
+    const int hd = (int) p.q.ne[0], n_kv = (int) p.k.ne[1];
+    const int hk = h / (int) (p.q.ne[2] / p.k.ne[2]);  // ggml's batch broadcast: kv head = head / (n_head / n_head_kv)
+    float * sc = at_smem;
+    float * qs = at_smem + ((n_kv + 3) & ~3);
+    float * pt = qs + ((hd + 3) & ~3);
+    const float * qp = (const float *) (p.q.data + (long long) t * p.q.nb[1] + (long long) h * p.q.nb[2]);
+    for (int e = tid; e < hd; e += 256) qs[e] = qp[e];
+    __syncthreads();
+    // scores: one THREAD per cached position, its K row (hd f16, contiguous) in 16-byte loads — up to hd / 8 independent loads
+    // in flight per thread (a warp per position with a shuffle reduction was latency-bound: 22 us per layer)
+    const char * kb = p.k.data + (long long) hk * p.k.nb[2];
+    const char * mp = p.m.data ? p.m.data + (long long) t * p.m.nb[1] + (long long) (h % p.m.ne[2]) * p.m.nb[2] : nullptr;
+    const bool kvec = (hd & 7) == 0 && ((((uintptr_t) p.k.data) | (unsigned long long) p.k.nb[1] | (unsigned long long) p.k.nb[2]) & 15) == 0;
+    for (int j = tid; j < n_kv; j += 256) {
+        const char * kr = kb + (long long) j * p.k.nb[1];
+        float acc = 0.0f;
+        if (kvec) {
+#pragma unroll 4
+            for (int e = 0; e < hd; e += 8) acc += dot8_h(__ldg((const uint4 *) (kr + 2 * e)), qs + e);
+        } else {
+            for (int e = 0; e < hd; ++e) acc = fmaf(qs[e], __half2float(((const __half *) kr)[e]), acc);
+        }
+        float x = acc * p.scale;
+        if (mp) x += p.mask_f16 ? __half2float(((const __half *) mp)[j]) : ((const float *) mp)[j];
+        sc[j] = x;
+    }
+    __syncthreads();
+    float mx = -INFINITY;
+    for (int j = tid; j < n_kv; j += 256) mx = fmaxf(mx, sc[j]);
+    mx = block_reduce<true>(mx, sh);
+    if (p.sinks) mx = fmaxf(mx, p.sinks[h]);
+    float s = 0.0f;
+    for (int j = tid; j < n_kv; j += 256) {
+        const float e = expf(sc[j] - mx);
+        sc[j] = e;
+        s += e;
+    }
+    s = block_reduce<false>(s, sh);  // (its barriers also publish the exponentials)
+    if (p.sinks) s += expf(p.sinks[h] - mx);
+    const float inv = 1.0f / s;
+    // output: thread (element e, part) walks its share of the transposed V row e (contiguous over positions, 16-byte loads);
+    // the parts are added in a fixed order
+    const char * vb = p.v.data + (long long) hk * p.v.nb[2];
+    const int  parts = (hd <= 256 && 256 % hd == 0) ? 256 / hd : 1;
+    const bool vvec  = ((((uintptr_t) p.v.data) | (unsigned long long) p.v.nb[1] | (unsigned long long) p.v.nb[2]) & 15) == 0;
+    const int  chunk = (((n_kv + parts - 1) / parts) + 7) & ~7;
+    float *    dp    = (float *) (p.d.data + (long long) h * p.d.nb[1] + (long long) t * p.d.nb[2]);
+    for (int e0 = 0; e0 < hd; e0 += 256) {
+        const int e = e0 + (parts > 1 ? tid % hd : tid), part = parts > 1 ? tid / hd : 0;
+        float acc = 0.0f;
+        if (e < hd) {
+            const char * vr = vb + (long long) e * p.v.nb[1];
+            const int j0 = part * chunk, j1 = min(n_kv, j0 + chunk);
+            int j = j0;
+            if (vvec) {
+#pragma unroll 4
+                for (; j + 8 <= j1; j += 8) acc += dot8_h(__ldg((const uint4 *) (vr + 2 * j)), sc + j);
+            }
+            for (; j < j1; ++j) acc = fmaf(sc[j], __half2float(((const __half *) vr)[j]), acc);
+        }
+        if (parts > 1) {
+            pt[tid] = acc;
+            __syncthreads();
+            if (tid < hd) {
+                float o = pt[tid];
+                for (int q = 1; q < parts; ++q) o += pt[tid + q * hd];
+                dp[tid] = o * inv;
+            }
+        } else if (e < hd) {
+            dp[e] = acc * inv;
+        }
+    }
+}
+
 // ---- ROPE: one thread per rotated pair ----------------------------------------------------------------------------------------
 struct RopeP {
     int   n_dims, neox;
@@ -597,6 +700,28 @@ int b200q_op_soft_max(const b200q_tensor * src, const b200q_tensor * mask, const
     } else {
         launch_pdl(soft_max_kernel<false>, dim3((unsigned) nr), dim3(256), 0, st, t4(src), m, sinks ? (const float *) sinks->data : nullptr, t4(dst), scale, max_bias, m0, m1, n_head_log2);
     }
+    return launched();
+}
+
+int b200q_op_attn_decode(const b200q_tensor * q, const b200q_tensor * k, const b200q_tensor * v, const b200q_tensor * mask,
+                         const b200q_tensor * sinks, const b200q_tensor * dst, float scale, void * stream) {
+    if (!q || !k || !v || !dst || q->type != B200Q_TYPE_F32 || k->type != B200Q_TYPE_F16 || v->type != B200Q_TYPE_F16 || dst->type != B200Q_TYPE_F32 ||
+        q->nb[0] != 4 || k->nb[0] != 2 || v->nb[0] != 2 || dst->nb[0] != 4 || q->ne[3] != 1 || k->ne[3] != 1 || v->ne[3] != 1 ||
+        k->ne[0] != q->ne[0] || v->ne[0] != k->ne[1] || v->ne[1] != q->ne[0] || v->ne[2] != k->ne[2] || k->ne[2] < 1 || q->ne[2] % k->ne[2] ||
+        dst->ne[0] != q->ne[0] || dst->ne[1] != q->ne[2] || dst->ne[2] != q->ne[1] || q->ne[0] > 512 || k->ne[1] < 1 || k->ne[1] > 8192 ||
+        q->ne[1] > 65535 || (mask && ((mask->type != B200Q_TYPE_F32 && mask->type != B200Q_TYPE_F16) || mask->ne[0] < k->ne[1] || mask->ne[1] < q->ne[1] ||
+                                      mask->nb[0] != tsize(mask->type) || mask->ne[2] < 1 || mask->ne[3] != 1)) ||
+        (sinks && (sinks->type != B200Q_TYPE_F32 || sinks->ne[0] < q->ne[2] || sinks->nb[0] != 4))) {
+        return ops_fail(B200Q_ENOTSUP, "attn_decode: q f32 [hd, n_tok, n_head], k f16 [hd, n_kv, n_head_kv], v f16 [n_kv, hd, n_head_kv], n_kv <= 8192");
+    }
+    if (q->ne[1] == 0 || q->ne[2] == 0) return 0;
+    AttnP p{};
+    p.q = t4(q); p.k = t4(k); p.v = t4(v); p.d = t4(dst);
+    if (mask) p.m = t4(mask);
+    p.sinks = sinks ? (const float *) sinks->data : nullptr;
+    p.scale = scale; p.mask_f16 = mask && mask->type == B200Q_TYPE_F16;
+    const size_t smem = (size_t) (((k->ne[1] + 3) & ~3) + ((q->ne[0] + 3) & ~3) + 256) * sizeof(float);
+    launch_pdl(attn_decode_kernel, dim3((unsigned) q->ne[2], (unsigned) q->ne[1]), dim3(256), smem, (cudaStream_t) stream, p);
     return launched();
 }
 

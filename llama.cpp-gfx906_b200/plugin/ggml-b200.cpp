@@ -1124,6 +1124,69 @@ int try_fuse_norm(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int i, int n_nod
     return 2;
 }
 
+// The attention core of a decode step — MUL_MAT(k, q) -> SOFT_MAX -> MUL_MAT(v, kq) -> PERMUTE -> CONT as llama.cpp builds it
+// without flash attention (src/llama-graph.cpp:1285-1330) — as ONE launch (b200q_op_attn_decode) when there are few tokens and a
+// short cache: four ~3.5 us launches per layer otherwise.  Every intermediate result must have the next node of the run as
+// its only consumer.  Returns the index behind the run (i: no fusion).
+int32_t node_use_count(const ggml_cgraph * cgraph, const ggml_tensor * t) {
+    const size_t pos = ggml_hash_find(&cgraph->visited_hash_set, t);
+    if (pos == GGML_HASHSET_FULL || !ggml_bitset_get(cgraph->visited_hash_set.used, pos)) return -1;
+    return cgraph->use_counts[pos];
+}
+int try_fuse_attn(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int i, int n_nodes, int * rc) {
+    if (!cgraph->use_counts) return i;
+    auto next = [&](int j) {
+        for (++j; j < n_nodes; ++j) {
+            const ggml_tensor * t = ggml_graph_node(cgraph, j);
+            if (t->op != GGML_OP_VIEW && t->op != GGML_OP_RESHAPE && t->op != GGML_OP_NONE) return j;  // PERMUTE / TRANSPOSE are matched below
+        }
+        return n_nodes;
+    };
+    const ggml_tensor * kq = ggml_graph_node(cgraph, i);
+    const ggml_tensor * k = kq->src[0], * q = kq->src[1];
+    if (!k || !q || k->type != GGML_TYPE_F16 || q->type != GGML_TYPE_F32 || kq->type != GGML_TYPE_F32 || k->nb[0] != 2 || q->nb[0] != 4) return i;
+    if (q->ne[3] != 1 || k->ne[3] != 1 || q->ne[1] > 8 || k->ne[1] > 2048 || k->ne[0] != q->ne[0] || q->ne[0] > 512 || q->ne[2] % k->ne[2]) return i;
+    if (tensor_is_split(k)) return i;
+    const int j1 = next(i);
+    if (j1 >= n_nodes) return i;
+    const ggml_tensor * sm = ggml_graph_node(cgraph, j1);
+    float scale, max_bias;
+    memcpy(&scale, (const float *) sm->op_params + 0, sizeof(float));
+    memcpy(&max_bias, (const float *) sm->op_params + 1, sizeof(float));
+    if (sm->op != GGML_OP_SOFT_MAX || sm->src[0] != kq || max_bias != 0.0f || !ggml_is_contiguous(kq) || !ggml_is_contiguous(sm)) return i;
+    const ggml_tensor * mask = sm->src[1], * sinks = sm->src[2];
+    if (mask && ((mask->type != GGML_TYPE_F32 && mask->type != GGML_TYPE_F16) || mask->ne[0] < k->ne[1] || mask->ne[1] < q->ne[1] ||
+                 mask->nb[0] != ggml_type_size(mask->type) || mask->ne[3] != 1 || q->ne[2] % mask->ne[2])) return i;
+    if (sinks && (sinks->type != GGML_TYPE_F32 || sinks->ne[0] < q->ne[2] || sinks->nb[0] != 4)) return i;
+    const int j2 = next(j1);
+    if (j2 >= n_nodes) return i;
+    const ggml_tensor * kqv = ggml_graph_node(cgraph, j2);
+    const ggml_tensor * v = kqv->src[0];
+    if (kqv->op != GGML_OP_MUL_MAT || kqv->src[1] != sm || !v || v->type != GGML_TYPE_F16 || v->nb[0] != 2 || v->ne[0] != k->ne[1] ||
+        v->ne[1] != q->ne[0] || v->ne[2] != k->ne[2] || v->ne[3] != 1 || kqv->type != GGML_TYPE_F32 || !ggml_is_contiguous(kqv)) return i;
+    const int j3 = next(j2);
+    const int j4 = j3 < n_nodes ? next(j3) : n_nodes;
+    if (j4 >= n_nodes) return i;
+    const ggml_tensor * pm = ggml_graph_node(cgraph, j3);
+    const ggml_tensor * ct = ggml_graph_node(cgraph, j4);
+    if (pm->op != GGML_OP_PERMUTE || pm->src[0] != kqv || ct->op != GGML_OP_CONT || ct->src[0] != pm || ct->type != GGML_TYPE_F32 ||
+        !ggml_is_contiguous(ct)) return i;
+    // permute (0, 2, 1, 3): [hd, n_tok, n_head] -> [hd, n_head, n_tok]
+    if (pm->ne[0] != kqv->ne[0] || pm->ne[1] != kqv->ne[2] || pm->ne[2] != kqv->ne[1] || pm->nb[1] != kqv->nb[2] || pm->nb[2] != kqv->nb[1] ||
+        ggml_nelements(ct) != ggml_nelements(kqv)) return i;
+    if (node_use_count(cgraph, kq) != 1 || node_use_count(cgraph, sm) != 1 || node_use_count(cgraph, kqv) != 1 || node_use_count(cgraph, pm) != 1) return i;
+    for (const ggml_tensor * t : { kq, sm, kqv, pm }) if (t->flags & GGML_TENSOR_FLAG_OUTPUT) return i;
+    const b200q_tensor tq = bt(q), tk = bt(k), tv = bt(v);
+    b200q_tensor tm{}, ts{}, td{};
+    if (mask) tm = bt(mask);
+    if (sinks) ts = bt(sinks);
+    td.data = ct->data; td.type = B200Q_TYPE_F32;
+    td.ne[0] = q->ne[0]; td.ne[1] = q->ne[2]; td.ne[2] = q->ne[1]; td.ne[3] = 1;
+    td.nb[0] = 4; td.nb[1] = (size_t) q->ne[0] * 4; td.nb[2] = td.nb[1] * (size_t) q->ne[2]; td.nb[3] = td.nb[2] * (size_t) q->ne[1];
+    *rc = b200q_op_attn_decode(&tq, &tk, &tv, mask ? &tm : nullptr, sinks ? &ts : nullptr, &td, scale, ctx->stream);
+    return j4 + 1;
+}
+
 ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
     const int  n_nodes  = ggml_graph_n_nodes(cgraph);
     const bool no_fuse  = getenv("GGML_B200_NO_FUSE") != nullptr;
@@ -1149,6 +1212,18 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
                     return GGML_STATUS_FAILED;
                 }
                 i += used - 1;
+                continue;
+            }
+        }
+        if (!no_fuse && node->op == GGML_OP_MUL_MAT && node->src[0] && node->src[0]->type == GGML_TYPE_F16) {
+            const int behind = try_fuse_attn(ctx, cgraph, i, n_nodes, &rc);
+            if (behind > i) {
+                if (rc != 0) {
+                    fprintf(stderr, "ggml-b200: fused attention (%s) failed (%d): %s\n", node->name, rc, b200q_last_error());
+                    return GGML_STATUS_FAILED;
+                }
+                ctx->packed_act = nullptr;
+                i = behind - 1;
                 continue;
             }
         }
