@@ -323,6 +323,10 @@ B200Q_API int b200q_op_argsort(const b200q_tensor * src, const b200q_tensor * ds
 B200Q_API int b200q_op_set_rows(const b200q_tensor * src, const b200q_tensor * idx, const b200q_tensor * dst,
                                 void * stream);                                                                            /* set-rows.cu */
 
+/* two independent SET_ROWS with one destination type in one launch (a layer's K and V cache writes are consecutive nodes) */
+B200Q_API int b200q_op_set_rows_pair(const b200q_tensor * src0, const b200q_tensor * idx0, const b200q_tensor * dst0,
+                                     const b200q_tensor * src1, const b200q_tensor * idx1, const b200q_tensor * dst1, void * stream);
+
 /* ---- experiment (no counterpart in the reference's shipped kernels): one CTA runs tcgen05.mma kind::mxf8f6f4.block_scale
  *      (e2m1 A x e4m3 B, UE8M0 block-32 scales) on a 128 x n x 128 problem laid out by the host exactly as the instruction reads
  *      it (csrc/mxf_probe.cu documents the images); `iters` repeats the four MMAs for an issue-rate measurement (cycles_dev:

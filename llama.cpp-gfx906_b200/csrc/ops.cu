@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(256) rms_norm_kernel(T4 x, T4 y, float eps) {
 // ~3.5 us per launch, and the stand-alone norm re-read its row through possibly-aliasing pointers.  One CTA per row, the row
 // lives in registers (n <= 8 * blockDim.x), same arithmetic as the separate kernels (sum, then x * scale, then * w: no FMA
 // across the operator boundaries).  w is broadcast over rows as ggml's MUL does (index modulo its extents).
-template <bool ADD, bool MUL> __global__ void __launch_bounds__(1024) norm_fused_kernel(T4 a, T4 b, T4 so, T4 w, T4 y, float eps, int write_sum) {
+template <bool ADD, bool MUL> __global__ void __launch_bounds__(1024) norm_fused_kernel(T4 a, T4 b, T4 so, T4 w, T4 y, float eps, int write_sum, int vec4) {
     pdl_grid_sync();
     __shared__ float sh[32];
     const long long row = blockIdx.x;
@@ -147,18 +147,54 @@ template <bool ADD, bool MUL> __global__ void __launch_bounds__(1024) norm_fused
     const float * __restrict__ wp = MUL ? (const float *) (w.data + (i1 % w.ne[1]) * w.nb[1] + (i2 % w.ne[2]) * w.nb[2] + (i3 % w.ne[3]) * w.nb[3]) : nullptr;
     float *       yp = (float *) (y.data + i1 * y.nb[1] + i2 * y.nb[2] + i3 * y.nb[3]);
     const int     n  = (int) a.ne[0];
-    float v[8];
+    float v[8], wv[8];
     float s = 0.0f;
+    if (vec4) {
+        // 16-byte accesses, two per thread and operand (n <= 8 * blockDim.x, n % 4 == 0, rows 16-byte aligned); the norm weight
+        // is requested BEFORE the reduction so that its latency hides behind it (the decode step runs ONE row per launch)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int i = 4 * (threadIdx.x + j * blockDim.x);
+            float4 x = make_float4(0.0f, 0.0f, 0.0f, 0.0f), ww = x;
+            if (i < n) {
+                x = *(const float4 *) (ap + i);
+                if (ADD) {
+                    const float4 bb = *(const float4 *) (bp + i);
+                    x.x = x.x + bb.x; x.y = x.y + bb.y; x.z = x.z + bb.z; x.w = x.w + bb.w;
+                    if (sp) *(float4 *) (sp + i) = x;
+                }
+                if (MUL) ww = *(const float4 *) (wp + i);
+            }
+            v[4 * j] = x.x; v[4 * j + 1] = x.y; v[4 * j + 2] = x.z; v[4 * j + 3] = x.w;
+            wv[4 * j] = ww.x; wv[4 * j + 1] = ww.y; wv[4 * j + 2] = ww.z; wv[4 * j + 3] = ww.w;
+            s += x.x * x.x; s += x.y * x.y; s += x.z * x.z; s += x.w * x.w;
+        }
+        s = block_reduce<false>(s, sh);
+        const float scale = 1.0f / sqrtf(s / (float) n + eps);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int i = 4 * (threadIdx.x + j * blockDim.x);
+            if (i < n) {
+                float4 o;
+                o.x = v[4 * j] * scale; o.y = v[4 * j + 1] * scale; o.z = v[4 * j + 2] * scale; o.w = v[4 * j + 3] * scale;
+                if (MUL) { o.x = o.x * wv[4 * j]; o.y = o.y * wv[4 * j + 1]; o.z = o.z * wv[4 * j + 2]; o.w = o.w * wv[4 * j + 3]; }
+                *(float4 *) (yp + i) = o;
+            }
+        }
+        return;
+    }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const int i = threadIdx.x + j * blockDim.x;
         float x = 0.0f;
+        wv[j] = 0.0f;
         if (i < n) {
             x = ap[i];
             if (ADD) {
                 x = x + bp[i];
                 if (sp) sp[i] = x;
             }
+            if (MUL) wv[j] = wp[i];
         }
         v[j] = x;
         s += x * x;
@@ -170,7 +206,7 @@ template <bool ADD, bool MUL> __global__ void __launch_bounds__(1024) norm_fused
         const int i = threadIdx.x + j * blockDim.x;
         if (i < n) {
             const float t = v[j] * scale;
-            yp[i] = MUL ? t * wp[i] : t;
+            yp[i] = MUL ? t * wv[j] : t;
         }
     }
 }
@@ -514,6 +550,24 @@ template <int TD> __global__ void __launch_bounds__(256) set_rows_kernel(T4 s, T
     }
 }
 
+// two SET_ROWS in one launch (the K and the V write of a layer are consecutive nodes; blockIdx.y picks the tensor)
+template <int TD> __global__ void __launch_bounds__(256) set_rows_pair_kernel(T4 s0, T4 idx0, T4 d0, long long n0, T4 s1, T4 idx1, T4 d1, long long n1) {
+    pdl_grid_sync();
+    const T4 &      s   = blockIdx.y ? s1 : s0;
+    const T4 &      idx = blockIdx.y ? idx1 : idx0;
+    const T4 &      d   = blockIdx.y ? d1 : d0;
+    const long long n   = blockIdx.y ? n1 : n0;
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
+        long long r = i;
+        const long long i0 = r % s.ne[0]; r /= s.ne[0];
+        const long long i1 = r % s.ne[1]; r /= s.ne[1];
+        const long long i2 = r % s.ne[2], i3 = r / s.ne[2];
+        const long long row = *(const long long *) (idx.data + i1 * idx.nb[0] + (i2 % idx.ne[1]) * idx.nb[1] + (i3 % idx.ne[2]) * idx.nb[2]);
+        const float v = *(const float *) (s.data + i0 * s.nb[0] + i1 * s.nb[1] + i2 * s.nb[2] + i3 * s.nb[3]);
+        Elem<TD>::st(d.data + i0 * d.nb[0] + row * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3], v);
+    }
+}
+
 // ---- ADD_ID: dst[i0, i1, i2] = a[i0, i1, i2] + b[i0, ids[i1, i2]] (the per-expert bias of a MoE layer; add-id.cu) ----------------
 __global__ void __launch_bounds__(256) add_id_kernel(T4 a, T4 b, T4 ids, T4 d, long long n) {
     pdl_grid_sync();
@@ -575,6 +629,16 @@ template <int TS> int cpy_to(const b200q_tensor * s, const b200q_tensor * d, lon
 
 extern "C" {
 
+// every row of every operand starts on a 16-byte boundary and holds a multiple of four values
+static int norm_vec4(const b200q_tensor * a, const b200q_tensor * b, const b200q_tensor * s, const b200q_tensor * w, const b200q_tensor * d) {
+    if (a->ne[0] % 4) return 0;
+    for (const b200q_tensor * t : { a, b, s, w, d }) {
+        if (!t) continue;
+        if (((uintptr_t) t->data | (unsigned long long) t->nb[1] | (unsigned long long) t->nb[2] | (unsigned long long) t->nb[3]) & 15) return 0;
+    }
+    return 1;
+}
+
 int b200q_op_rms_norm(const b200q_tensor * src, const b200q_tensor * dst, float eps, void * stream) {
     if (!src || !dst || src->type != B200Q_TYPE_F32 || dst->type != B200Q_TYPE_F32 || !same_shape(src, dst) || src->nb[0] != 4 || dst->nb[0] != 4) {
         return ops_fail(B200Q_ENOTSUP, "rms_norm: f32 rows with unit stride, same shape");
@@ -584,7 +648,8 @@ int b200q_op_rms_norm(const b200q_tensor * src, const b200q_tensor * dst, float 
     if (nr > 0x7fffffffLL) return ops_fail(B200Q_ENOTSUP, "rms_norm: too many rows");
     if (src->ne[0] <= 8192) {  // the row fits the registers of one CTA
         const int threads = src->ne[0] <= 2048 ? 256 : 1024;
-        launch_pdl(norm_fused_kernel<false, false>, dim3((unsigned) nr), dim3(threads), 0, (cudaStream_t) stream, t4(src), t4(src), t4(src), t4(src), t4(dst), eps, 0);
+        launch_pdl(norm_fused_kernel<false, false>, dim3((unsigned) nr), dim3(threads), 0, (cudaStream_t) stream, t4(src), t4(src), t4(src), t4(src), t4(dst), eps, 0,
+                   norm_vec4(src, nullptr, nullptr, nullptr, dst));
     } else {
         launch_pdl(rms_norm_kernel, dim3((unsigned) nr), dim3(256), 0, (cudaStream_t) stream, t4(src), t4(dst), eps);
     }
@@ -605,8 +670,9 @@ int b200q_op_norm_fused(const b200q_tensor * a, const b200q_tensor * b, const b2
     if (nr > 0x7fffffffLL) return ops_fail(B200Q_ENOTSUP, "norm_fused: too many rows");
     const int threads = a->ne[0] <= 2048 ? 256 : 1024;
     cudaStream_t st = (cudaStream_t) stream;
-    if (b) launch_pdl(norm_fused_kernel<true, true>, dim3((unsigned) nr), dim3(threads), 0, st, t4(a), t4(b), t4(sum_out ? sum_out : a), t4(w), t4(dst), eps, sum_out ? 1 : 0);
-    else launch_pdl(norm_fused_kernel<false, true>, dim3((unsigned) nr), dim3(threads), 0, st, t4(a), t4(a), t4(a), t4(w), t4(dst), eps, 0);
+    const int vec4 = norm_vec4(a, b, sum_out, w, dst);
+    if (b) launch_pdl(norm_fused_kernel<true, true>, dim3((unsigned) nr), dim3(threads), 0, st, t4(a), t4(b), t4(sum_out ? sum_out : a), t4(w), t4(dst), eps, sum_out ? 1 : 0, vec4);
+    else launch_pdl(norm_fused_kernel<false, true>, dim3((unsigned) nr), dim3(threads), 0, st, t4(a), t4(a), t4(a), t4(w), t4(dst), eps, 0, vec4);
     return launched();
 }
 
@@ -785,6 +851,30 @@ int b200q_op_argsort(const b200q_tensor * src, const b200q_tensor * dst, int des
     int npad = 1;
     while (npad < src->ne[0]) npad <<= 1;
     launch_pdl(argsort_kernel, dim3((unsigned) rows), dim3(npad < 32 ? 32 : npad), npad * sizeof(int), (cudaStream_t) stream, t4(src), t4(dst), npad, descending ? 1 : 0);
+    return launched();
+}
+
+static bool set_rows_ok(const b200q_tensor * src, const b200q_tensor * idx, const b200q_tensor * dst) {
+    return src && idx && dst && src->type == B200Q_TYPE_F32 && idx->type == B200Q_TYPE_I64 && src->ne[0] == dst->ne[0] && src->ne[2] == dst->ne[2] &&
+           src->ne[3] == dst->ne[3] && idx->ne[0] == src->ne[1] && idx->ne[1] >= 1 && idx->ne[2] >= 1 && src->ne[2] % idx->ne[1] == 0 &&
+           src->ne[3] % idx->ne[2] == 0;
+}
+// two independent SET_ROWS with the same destination type in one launch (the K and V cache writes of a layer)
+int b200q_op_set_rows_pair(const b200q_tensor * src0, const b200q_tensor * idx0, const b200q_tensor * dst0, const b200q_tensor * src1,
+                           const b200q_tensor * idx1, const b200q_tensor * dst1, void * stream) {
+    if (!set_rows_ok(src0, idx0, dst0) || !set_rows_ok(src1, idx1, dst1) || dst0->type != dst1->type) {
+        return ops_fail(B200Q_ENOTSUP, "set_rows_pair: two set_rows (f32 rows, i64 indices) with one destination type");
+    }
+    const long long n0 = nelem(src0), n1 = nelem(src1);
+    if (n0 == 0 && n1 == 0) return 0;
+    const dim3 g((unsigned) grid_for(n0 > n1 ? n0 : n1, 256), 2);
+    cudaStream_t st = (cudaStream_t) stream;
+    switch (dst0->type) {
+        case B200Q_TYPE_F32:  launch_pdl(set_rows_pair_kernel<B200Q_TYPE_F32>, g, dim3(256), 0, st, t4(src0), t4(idx0), t4(dst0), n0, t4(src1), t4(idx1), t4(dst1), n1); break;
+        case B200Q_TYPE_F16:  launch_pdl(set_rows_pair_kernel<B200Q_TYPE_F16>, g, dim3(256), 0, st, t4(src0), t4(idx0), t4(dst0), n0, t4(src1), t4(idx1), t4(dst1), n1); break;
+        case B200Q_TYPE_BF16: launch_pdl(set_rows_pair_kernel<B200Q_TYPE_BF16>, g, dim3(256), 0, st, t4(src0), t4(idx0), t4(dst0), n0, t4(src1), t4(idx1), t4(dst1), n1); break;
+        default: return ops_fail(B200Q_ENOTSUP, "set_rows_pair: destination type");
+    }
     return launched();
 }
 

@@ -1215,6 +1215,22 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
                 continue;
             }
         }
+        if (!no_fuse && node->op == GGML_OP_SET_ROWS) {  // the K and V cache writes of a layer: one launch
+            int j = i + 1;
+            while (j < n_nodes && noop_node(ggml_graph_node(cgraph, j))) ++j;
+            const ggml_tensor * o = j < n_nodes ? ggml_graph_node(cgraph, j) : nullptr;
+            if (o && o->op == GGML_OP_SET_ROWS && !done[(size_t) j] && supports_elementwise(node) && supports_elementwise(o) && o->type == node->type &&
+                !touches(o, node) && !ranges_overlap(node, o)) {
+                const b200q_tensor s0 = bt(node->src[0]), x0 = bt(node->src[1]), d0 = bt(node), s1 = bt(o->src[0]), x1 = bt(o->src[1]), d1 = bt(o);
+                rc = b200q_op_set_rows_pair(&s0, &x0, &d0, &s1, &x1, &d1, ctx->stream);
+                if (rc != 0) {
+                    fprintf(stderr, "ggml-b200: set_rows pair (%s) failed (%d): %s\n", node->name, rc, b200q_last_error());
+                    return GGML_STATUS_FAILED;
+                }
+                i = j;
+                continue;
+            }
+        }
         if (!no_fuse && node->op == GGML_OP_MUL_MAT && node->src[0] && node->src[0]->type == GGML_TYPE_F16) {
             const int behind = try_fuse_attn(ctx, cgraph, i, n_nodes, &rc);
             if (behind > i) {
