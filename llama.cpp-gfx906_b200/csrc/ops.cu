@@ -536,6 +536,25 @@ template <int TS, int TD> __global__ void __launch_bounds__(256) cpy_kernel(T4 s
     }
 }
 
+// f32 -> f32 with unit-stride rows of a multiple of four values on both sides, everything 16-byte aligned (the CONT behind the
+// attention's permute at prompt sizes: 8 MB per layer): four values per thread, one index decomposition per four
+__global__ void __launch_bounds__(256) cpy_f32_vec4_kernel(T4 s, T4 d, long long n4) {
+    pdl_grid_sync();
+    for (long long q = (long long) blockIdx.x * blockDim.x + threadIdx.x; q < n4; q += (long long) gridDim.x * blockDim.x) {
+        const long long i = q * 4;
+        long long r = i;
+        const long long s0 = r % s.ne[0]; r /= s.ne[0];
+        const long long s1 = r % s.ne[1]; r /= s.ne[1];
+        const long long s2 = r % s.ne[2], s3 = r / s.ne[2];
+        r = i;
+        const long long d0 = r % d.ne[0]; r /= d.ne[0];
+        const long long d1 = r % d.ne[1]; r /= d.ne[1];
+        const long long d2 = r % d.ne[2], d3 = r / d.ne[2];
+        *(float4 *) (d.data + d0 * 4 + d1 * d.nb[1] + d2 * d.nb[2] + d3 * d.nb[3]) =
+            *(const float4 *) (s.data + s0 * 4 + s1 * s.nb[1] + s2 * s.nb[2] + s3 * s.nb[3]);
+    }
+}
+
 // ---- SET_ROWS: dst[idx[i1, i2 % ne11, i3 % ne12]][i2][i3] = src[i1][i2][i3] (rows), idx i64 ------------------------------------
 template <int TD> __global__ void __launch_bounds__(256) set_rows_kernel(T4 s, T4 idx, T4 d, long long n) {
     pdl_grid_sync();
@@ -615,6 +634,16 @@ __global__ void __launch_bounds__(1024) argsort_kernel(T4 s, T4 d, int npad, int
 }
 
 template <int TS> int cpy_to(const b200q_tensor * s, const b200q_tensor * d, long long n, cudaStream_t st) {
+    if (TS == B200Q_TYPE_F32 && d->type == B200Q_TYPE_F32 && s->nb[0] == 4 && d->nb[0] == 4 && s->ne[0] % 4 == 0 && d->ne[0] % 4 == 0) {
+        bool al = true;
+        for (const b200q_tensor * t : { s, d }) {
+            al = al && (((uintptr_t) t->data | (unsigned long long) t->nb[1] | (unsigned long long) t->nb[2] | (unsigned long long) t->nb[3]) & 15) == 0;
+        }
+        if (al) {
+            launch_pdl(cpy_f32_vec4_kernel, dim3(grid_for(n / 4, 256)), dim3(256), 0, st, t4(s), t4(d), n / 4);
+            return launched();
+        }
+    }
     const int g = grid_for(n, 256);
     switch (d->type) {
         case B200Q_TYPE_F32:  launch_pdl(cpy_kernel<TS, B200Q_TYPE_F32>, dim3(g), dim3(256), 0, st, t4(s), t4(d), n); break;
