@@ -626,6 +626,13 @@ int compute_elementwise(b200_backend_ctx * ctx, const ggml_tensor * op) {
 }
 
 bool device_supports_op(ggml_backend_dev_t dev, const ggml_tensor * op) {
+    // split buffers hold row slices on several devices and have no address: only MUL_MAT can read them (ggml-cuda.cu:3265-3283).
+    // llama.cpp asks this for every weight (a norm weight under MUL, an embedding under GET_ROWS) to choose its buffer type.
+    if (op->op != GGML_OP_MUL_MAT) {
+        for (int i = 0; i < GGML_MAX_SRC; ++i) {
+            if (op->src[i] && tensor_is_split(op->src[i])) return false;
+        }
+    }
     switch (op->op) {
         case GGML_OP_NONE:
         case GGML_OP_VIEW:

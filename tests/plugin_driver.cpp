@@ -335,6 +335,39 @@ int pd_decode_run(int dev, int type, int type_v, int64_t k, const void * w1, con
     return rc;
 }
 
+// llama.cpp picks a weight's buffer type by asking supports_op for the operator the weight is used in (src/llama-model.cpp:152-300):
+// with `-sm row` a norm weight (MUL) or an embedding (GET_ROWS) placed in the split buffer type must be declined — only MUL_MAT
+// can read row slices (ggml-cuda.cu:3265-3283).  Returns a bit mask of wrongly accepted operators (0 = all declined), < 0 on error.
+int pd_split_supports(int dev) {
+    if (!g_reg) return -1;
+    typedef ggml_backend_buffer_type_t (*split_fn)(int, const float *);
+    split_fn get_split = (split_fn) ggml_backend_reg_get_proc_address(g_reg, "ggml_backend_split_buffer_type");
+    if (!get_split) return -2;
+    ggml_backend_dev_t         d     = ggml_backend_reg_dev_get(g_reg, dev);
+    ggml_backend_buffer_type_t sbuft = get_split(dev, nullptr);
+    ggml_backend_t             be    = ggml_backend_dev_init(d, nullptr);
+    if (!sbuft || !be) return -3;
+    int bad = 0;
+    {
+        ctx_scope sc(4), cc(16);
+        ggml_tensor * w1 = ggml_new_tensor_1d(sc.ctx, GGML_TYPE_F32, 256);
+        ggml_tensor * w2 = ggml_new_tensor_2d(sc.ctx, GGML_TYPE_Q8_0, 256, 512);
+        ggml_backend_buffer_t sbuf = ggml_backend_alloc_ctx_tensors_from_buft(sc.ctx, sbuft);
+        if (!sbuf) { ggml_backend_free(be); return -4; }
+        ggml_tensor * x   = ggml_new_tensor_2d(cc.ctx, GGML_TYPE_F32, 256, 4);
+        ggml_tensor * idx = ggml_new_tensor_1d(cc.ctx, GGML_TYPE_I32, 4);
+        ggml_backend_buffer_t cbuf = ggml_backend_alloc_ctx_tensors(cc.ctx, be);
+        if (ggml_backend_supports_op(be, ggml_mul(cc.ctx, x, w1))) bad |= 1;
+        if (ggml_backend_supports_op(be, ggml_add(cc.ctx, x, w1))) bad |= 2;
+        if (ggml_backend_supports_op(be, ggml_get_rows(cc.ctx, w2, idx))) bad |= 4;
+        if (!ggml_backend_supports_op(be, ggml_mul_mat(cc.ctx, w2, x))) bad |= 8;  // the one operator that must be accepted
+        if (cbuf) ggml_backend_buffer_free(cbuf);
+        ggml_backend_buffer_free(sbuf);
+    }
+    ggml_backend_free(be);
+    return bad;
+}
+
 // A layer-like graph (rms_norm -> mul_mat -> silu -> mul_mat -> add, `layers` times: >= 16 nodes, so the plugin records it as a
 // CUDA graph on the second pass and replays it from the third) computed `reps` times on inputs x * (rep + 1); out [reps][k].
 // Results must not depend on whether a pass ran eagerly, was being recorded, or was a replay.

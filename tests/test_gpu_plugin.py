@@ -323,3 +323,12 @@ def test_inprocess_gpt_oss_moe_block_stays_on_device(n_tokens):
     assert rc == 0 and unsup.value == 0, (rc, unsup.value)
     print(f"\n[gpt-oss moe block] n_tokens={n_tokens}: nmse vs CPU backend {nmse.value:.2e}")
     assert 0.0 <= nmse.value <= 1e-3
+
+
+def test_inprocess_split_buffer_only_serves_mul_mat():
+    """llama.cpp chooses each weight's buffer type by asking supports_op for the operator it is used in; with -sm row a norm
+    weight (MUL / ADD) or an embedding (GET_ROWS) offered in the split buffer type must be declined, MUL_MAT accepted
+    (ggml-cuda.cu:3265-3283).  Found by llama-bench -sm row: the norm weights landed in the split buffer and the fused norm read
+    a slice table as an address."""
+    L = _driver()
+    assert L.pd_split_supports(0) == 0
