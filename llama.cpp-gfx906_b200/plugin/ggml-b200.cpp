@@ -101,7 +101,16 @@ struct b200_backend_ctx {
     bool                                         graphs_off = false;  // a capture broke once: stay eager
     // the activation matrix the last tensor-core MUL_MAT of this graph packed into the workspace (nullptr: none / overwritten)
     const ggml_tensor * packed_act = nullptr;
+    // Results of hoisted list members whose own buffer is still in use at the list's position (ggml-alloc reuses buffers: in
+    // llama's graphs k's result takes q's buffer once rope has read q): the list writes them into the head of the workspace —
+    // decode graphs leave it unused — and a device copy at the node's own position delivers them.  A bump allocator that
+    // restarts with every graph, so the same graph gets the same addresses (cached lists and recorded graphs hold them).
+    size_t hoist_used = 0;
+    bool   hoist_ok   = false;
+    struct hoist_copy { const void * src = nullptr; size_t bytes = 0; };
+    std::vector<hoist_copy> hoist_copies;  // per node of the graph being dispatched
 };
+constexpr size_t HOIST_BYTES = 1u << 20;
 constexpr size_t MAX_CACHED_GRAPHS = 256;
 constexpr size_t MAX_CACHED_LISTS = 512;
 
@@ -652,9 +661,19 @@ void drop_graphs(b200_backend_ctx * ctx) {
     bool any = false;
     for (auto & kv : ctx->graphs) any = any || kv.second.exec;
     if (any) B200_CHECK(b200q_stream_synchronize(ctx->stream));
-    for (auto & kv : ctx->graphs) if (kv.second.exec) b200q_graph_destroy(kv.second.exec);
-    ctx->graphs.clear();
-    ctx->graph_order.clear();
+    // (fingerprints that have only been sighted keep their count: nothing was recorded for them yet)
+    std::vector<std::vector<uint64_t>> keep;
+    for (auto & key : ctx->graph_order) {
+        auto it = ctx->graphs.find(key);
+        if (it == ctx->graphs.end()) continue;
+        if (it->second.exec) {
+            b200q_graph_destroy(it->second.exec);
+            ctx->graphs.erase(it);
+        } else {
+            keep.push_back(key);
+        }
+    }
+    ctx->graph_order.swap(keep);
 }
 
 void * backend_workspace(b200_backend_ctx * ctx, size_t need) {
@@ -941,7 +960,10 @@ bool touches(const ggml_tensor * node, const ggml_tensor * t) {  // does `node` 
 int compute_list_run(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int first, int n_nodes, std::vector<char> & done) {
     std::vector<b200q_list_op> ops;
     std::vector<int>           members, skipped;
-    static const bool no_hoist = getenv("GGML_B200_NO_HOIST") != nullptr;
+    std::vector<void *>        scratch_of;
+    const size_t               hoist_mark = ctx->hoist_used;
+    static const bool no_hoist   = getenv("GGML_B200_NO_HOIST") != nullptr;
+    static const bool no_scratch = getenv("GGML_B200_NO_SCRATCH") != nullptr;
     for (int i = first; i < n_nodes && ops.size() < 64; ++i) {
         ggml_tensor * t = ggml_graph_node(cgraph, i);
         if (noop_node(t) || done[(size_t) i]) continue;
@@ -950,16 +972,25 @@ int compute_list_run(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int first, in
             skipped.push_back(i);
             continue;
         }
+        void * scratch = nullptr;
         if (!skipped.empty()) {
-            bool ok = false;
+            bool ok = false, aliased = false;
             for (int mi : members) ok = ok || ggml_graph_node(cgraph, mi)->src[1]->data == t->src[1]->data;  // the vector is ready
-            for (int si : skipped) ok = ok && !touches(ggml_graph_node(cgraph, si), t) && !ranges_overlap(ggml_graph_node(cgraph, si), t->src[1]);
-            for (int mi : members) ok = ok && !touches(ggml_graph_node(cgraph, mi), t);
+            for (int si : skipped) ok = ok && !ranges_overlap(ggml_graph_node(cgraph, si), t->src[1]);      // ... and stays untouched
+            for (int si : skipped) aliased = aliased || touches(ggml_graph_node(cgraph, si), t);
+            for (int mi : members) aliased = aliased || touches(ggml_graph_node(cgraph, mi), t);
             if (!ok) break;
+            if (aliased) {  // its buffer is somebody else's until its own place in the graph: compute into scratch, copy there
+                const size_t bytes = ((size_t) t->src[0]->ne[1] * sizeof(float) + 255) & ~(size_t) 255;
+                if (no_scratch || !ctx->hoist_ok || !ggml_is_contiguous(t) || ctx->ws_bytes < HOIST_BYTES || ctx->hoist_used + bytes > HOIST_BYTES) break;
+                scratch = (char *) ctx->workspace + ctx->hoist_used;
+                ctx->hoist_used += bytes;
+            }
         }
         b200q_list_op o{};
         o.type = (int) t->src[0]->type; o.m = t->src[0]->ne[1]; o.k = t->src[0]->ne[0];
-        o.w = t->src[0]->data; o.act = (const float *) t->src[1]->data; o.dst = (float *) t->data;
+        o.w = t->src[0]->data; o.act = (const float *) t->src[1]->data; o.dst = scratch ? (float *) scratch : (float *) t->data;
+        scratch_of.push_back(scratch);
         const char * a0 = (const char *) o.act, * a1 = a0 + o.k * 4;
         for (const b200q_list_op & e : ops) {  // reads what an earlier op of the run writes?
             const char * d0 = (const char *) e.dst, * d1 = d0 + e.m * 4;
@@ -968,7 +999,10 @@ int compute_list_run(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int first, in
         ops.push_back(o);
         members.push_back(i);
     }
-    if (ops.size() < 2) return 0;
+    if (ops.size() < 2) {
+        ctx->hoist_used = hoist_mark;
+        return 0;
+    }
     std::vector<int64_t> key;
     key.reserve(ops.size() * 6);
     for (const b200q_list_op & o : ops) {
@@ -997,9 +1031,19 @@ int compute_list_run(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int first, in
         it = ctx->lists.emplace(key, l).first;
         ctx->list_order.push_back(key);
     }
-    if (!it->second) return 0;
-    if (b200q_list_launch(it->second, ctx->stream) != 0) return 0;
-    for (int mi : members) done[(size_t) mi] = 1;
+    if (!it->second || b200q_list_launch(it->second, ctx->stream) != 0) {
+        ctx->hoist_used = hoist_mark;
+        return 0;
+    }
+    for (size_t q = 0; q < members.size(); ++q) {
+        const int mi = members[q];
+        done[(size_t) mi] = 1;
+        if (scratch_of[q]) {
+            done[(size_t) mi] = 2;  // delivered by a copy at its own position
+            ctx->hoist_copies[(size_t) mi].src   = scratch_of[q];
+            ctx->hoist_copies[(size_t) mi].bytes = (size_t) ggml_graph_node(cgraph, mi)->src[0]->ne[1] * sizeof(float);
+        }
+    }
     return (int) members.size();
 }
 
@@ -1197,11 +1241,28 @@ int try_fuse_attn(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int i, int n_nod
 ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
     const int  n_nodes  = ggml_graph_n_nodes(cgraph);
     const bool no_fuse  = getenv("GGML_B200_NO_FUSE") != nullptr;
-    std::vector<char> done((size_t) n_nodes, 0);  // nodes that already went out with an earlier list
+    std::vector<char> done((size_t) n_nodes, 0);  // nodes that already went out with an earlier list (2: result waits in scratch)
     ctx->packed_act = nullptr;
+    ctx->hoist_used = 0;
+    ctx->hoist_copies.assign((size_t) n_nodes, b200_backend_ctx::hoist_copy{});
+    // scratch results live in the head of the workspace: only in graphs where no node needs the workspace for itself (the
+    // tensor-core kernel's packed activations, MoE tables, the f32 copy of f16 activations) — decode graphs
+    ctx->hoist_ok = getenv("GGML_B200_NO_LIST") == nullptr;
+    for (int i = 0; i < n_nodes && ctx->hoist_ok; ++i) {
+        const ggml_tensor * t = ggml_graph_node(cgraph, i);
+        if (t->op == GGML_OP_MUL_MAT_ID) ctx->hoist_ok = false;
+        if (t->op == GGML_OP_MUL_MAT && (t->src[1]->ne[1] > 8 || t->src[1]->type != GGML_TYPE_F32 || tensor_is_split(t->src[0]))) ctx->hoist_ok = false;
+    }
+    if (ctx->hoist_ok) backend_workspace(ctx, HOIST_BYTES);
     const bool no_lists = getenv("GGML_B200_NO_LIST") != nullptr;
     for (int i = 0; i < n_nodes; ++i) {
         ggml_tensor * node = ggml_graph_node(cgraph, i);
+        if (done[(size_t) i] == 2) {
+            const auto & hc = ctx->hoist_copies[(size_t) i];
+            if (ctx->packed_act && ranges_overlap(node, ctx->packed_act)) ctx->packed_act = nullptr;
+            B200_CHECK(b200q_memcpy(node->data, hc.src, hc.bytes, B200Q_D2D, ctx->stream));
+            continue;
+        }
         if (ggml_is_empty(node) || done[(size_t) i]) continue;
         // a node that writes over the packed activations (in-place operators) or takes the workspace for something else
         if (ctx->packed_act && (node->op == GGML_OP_MUL_MAT_ID || (node->op != GGML_OP_MUL_MAT && ranges_overlap(node, ctx->packed_act)))) {

@@ -7,6 +7,8 @@ export GGML_BACKEND_PATH=$PWD/llama.cpp-gfx906_b200/lib/libggml-b200.so
 {
 python tools/make_synth_gguf.py --out /tmp/synth-q4km.gguf --layers 32 --ftype q4_k_m
 timeout 600 $D/llama-bench -m /tmp/synth-q4km.gguf -ngl 99 -fa 0 -p 512 -n 128,512 -r 3 2>&1 | tail -5
+echo "=== GGML_B200_NO_SCRATCH=1"
+GGML_B200_NO_SCRATCH=1 timeout 600 $D/llama-bench -m /tmp/synth-q4km.gguf -ngl 99 -fa 0 -p 0 -n 128 -r 3 2>&1 | tail -3
 echo "=== GGML_B200_NO_FUSE=1"
 GGML_B200_NO_FUSE=1 timeout 600 $D/llama-bench -m /tmp/synth-q4km.gguf -ngl 99 -fa 0 -p 0 -n 128 -r 3 2>&1 | tail -3
 rm -f /tmp/synth-q4km.gguf
