@@ -327,6 +327,14 @@ B200Q_API int b200q_op_set_rows(const b200q_tensor * src, const b200q_tensor * i
 B200Q_API int b200q_op_set_rows_pair(const b200q_tensor * src0, const b200q_tensor * idx0, const b200q_tensor * dst0,
                                      const b200q_tensor * src1, const b200q_tensor * idx1, const b200q_tensor * dst1, void * stream);
 
+/* ---- expert-parallel MUL_MAT_ID across the GPUs of one box (NOT in the reference, which asserts that expert tensors are
+ *      never split, ggml-cuda.cu:2094).  Experts are sharded by id, activations and routing are replicated: every rank runs
+ *      b200q_mul_mat_id on the (token, slot) pairs whose expert it owns and stores the rows it computed into every rank's result
+ *      with this call (row r of src -> row row_index[r] of dst here and at dst + peer_delta[q] on every peer: NVLink stores, no
+ *      all-to-all); a stream-ordered cross-GPU fence completes the step.  Host logic: b200q/expert_parallel.py. ------------------ */
+B200Q_API int b200q_scatter_rows_peers(const float * src, const int32_t * row_index, float * dst, int64_t n_rows, int64_t m,
+                                       int64_t dst_row_stride /* floats */, int n_peers, const int64_t * peer_delta /* bytes */, void * stream);
+
 /* ---- experiment (no counterpart in the reference's shipped kernels): one CTA runs tcgen05.mma kind::mxf8f6f4.block_scale
  *      (e2m1 A x e4m3 B, UE8M0 block-32 scales) on a 128 x n x 128 problem laid out by the host exactly as the instruction reads
  *      it (csrc/mxf_probe.cu documents the images); `iters` repeats the four MMAs for an issue-rate measurement (cycles_dev:

@@ -587,6 +587,29 @@ template <int TD> __global__ void __launch_bounds__(256) set_rows_pair_kernel(T4
     }
 }
 
+// ---- expert-parallel combine: row r of src goes to row row_index[r] of dst on THIS GPU and on every peer (NVLink stores) --------
+// (no reference counterpart: experts are sharded by id, activations and routing are replicated, so "dispatch" is
+// free and "combine" is each rank storing the rows it computed into every rank's result — no all-to-all)
+struct ScatterP {
+    const float * src;
+    const int *   row_index;
+    float *       dst;
+    long long     m, n_rows, dst_row_stride;  // floats
+    int           n_peers;
+    long long     peer_delta[7];              // bytes, as b200q_mul_mat_group_peers
+};
+__global__ void __launch_bounds__(256) scatter_rows_peers_kernel(const ScatterP p) {
+    pdl_grid_sync();
+    const long long n = p.n_rows * p.m;
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
+        const long long r = i / p.m, c = i - r * p.m;
+        const float     v = p.src[i];
+        float *         d = p.dst + (long long) p.row_index[r] * p.dst_row_stride + c;
+        *d = v;
+        for (int q = 0; q < p.n_peers; ++q) *(float *) ((char *) d + p.peer_delta[q]) = v;
+    }
+}
+
 // ---- ADD_ID: dst[i0, i1, i2] = a[i0, i1, i2] + b[i0, ids[i1, i2]] (the per-expert bias of a MoE layer; add-id.cu) ----------------
 __global__ void __launch_bounds__(256) add_id_kernel(T4 a, T4 b, T4 ids, T4 d, long long n) {
     pdl_grid_sync();
@@ -904,6 +927,19 @@ int b200q_op_set_rows_pair(const b200q_tensor * src0, const b200q_tensor * idx0,
         case B200Q_TYPE_BF16: launch_pdl(set_rows_pair_kernel<B200Q_TYPE_BF16>, g, dim3(256), 0, st, t4(src0), t4(idx0), t4(dst0), n0, t4(src1), t4(idx1), t4(dst1), n1); break;
         default: return ops_fail(B200Q_ENOTSUP, "set_rows_pair: destination type");
     }
+    return launched();
+}
+
+int b200q_scatter_rows_peers(const float * src, const int32_t * row_index, float * dst, int64_t n_rows, int64_t m, int64_t dst_row_stride,
+                             int n_peers, const int64_t * peer_delta, void * stream) {
+    if (n_rows < 0 || m < 0 || n_peers < 0 || n_peers > 7 || (n_peers && !peer_delta) || (n_rows && m && (!src || !row_index || !dst))) {
+        return ops_fail(B200Q_EINVAL, "scatter_rows_peers: arguments (0..7 peers)");
+    }
+    if (n_rows == 0 || m == 0) return 0;
+    ScatterP p{};
+    p.src = src; p.row_index = row_index; p.dst = dst; p.m = m; p.n_rows = n_rows; p.dst_row_stride = dst_row_stride; p.n_peers = n_peers;
+    for (int q = 0; q < n_peers; ++q) p.peer_delta[q] = peer_delta[q];
+    launch_pdl(scatter_rows_peers_kernel, dim3(grid_for(n_rows * m, 256)), dim3(256), 0, (cudaStream_t) stream, p);
     return launched();
 }
 
