@@ -212,7 +212,7 @@ bool plan_kq(KqParams & p, int & grid, int & smem, int type, int64_t k, int nseg
              const int64_t * m, const float * act, const DevInfo & di, const int32_t * ids = nullptr, long long expert_stride = 0,
              long long act_seg_stride = 0) {
     if (!kq_kernel_for(type)) return false;
-    const bool kquant = type == T_Q4_K || type == T_Q6_K;
+    const bool kquant = type == T_Q4_K || type == T_Q5_K || type == T_Q6_K;
     const int  unit   = kquant ? 256 : 32;  // elements per unit of lane work (super-block | block)
     if (nseg < 1 || nseg > kq_max_segments(ids != nullptr) || k <= 0 || k % unit) return false;
     static const bool off   = getenv("B200Q_NO_KQ") != nullptr;

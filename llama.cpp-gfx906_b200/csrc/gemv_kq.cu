@@ -77,7 +77,7 @@ __device__ __forceinline__ void mbar_wait_dbg(uint32_t bar, uint32_t parity, int
 #define KQ_HANG_COUNT(i) do { } while (0)
 #endif
 
-template <int T> struct IsKQuant { static constexpr bool value = T == T_Q4_K || T == T_Q6_K; };
+template <int T> struct IsKQuant { static constexpr bool value = T == T_Q4_K || T == T_Q5_K || T == T_Q6_K; };
 
 struct StageInfo {
     int g, r0, nrows;
@@ -217,6 +217,7 @@ template <int T, bool MOE> __global__ void __launch_bounds__(NTHREADS, 2) gemv_k
 template <bool MOE> static kq_kernel_t kq_kernel_sel(int type) {
     switch (type) {
         case T_Q4_K: return gemv_kq_kernel<T_Q4_K, MOE>;
+        case T_Q5_K: return gemv_kq_kernel<T_Q5_K, MOE>;
         case T_Q6_K: return gemv_kq_kernel<T_Q6_K, MOE>;
         case T_Q4_0: return gemv_kq_kernel<T_Q4_0, MOE>;
         case T_Q4_1: return gemv_kq_kernel<T_Q4_1, MOE>;

@@ -215,6 +215,56 @@ template <> struct SbDot<T_Q4_K> {
     }
 };
 
+// q5_K (ggml-common.h block_q5_K, dequantize_row_q5_K ggml-quants.c:1477-1513): q4_K's layout with 32 bytes of fifth bits behind
+// the header — bit 2j of qh[l] lifts element l of sub-block 2j by 16, bit 2j + 1 that of sub-block 2j + 1.  Both nibbles are
+// brought down to bytes 0..31 so that the fifth bit fits (q4_K leaves the high nibbles in place and shifts the sum).
+template <> struct SbDot<T_Q5_K> {
+    static constexpr int SB_BYTES = 176;
+    template <class P> static __device__ __forceinline__ float run(const P & p, uint32_t sb, uint32_t row, int s) {
+        return core(row + (uint32_t) s * 176u, SmemAct<P>{ p, sb, s });
+    }
+    template <class A> static __device__ __forceinline__ float core(uint32_t b, const A & act) {
+        const int4     h = lds128(b);  // [d dmin] [scales x3]
+        const uint32_t sc_lo = (uint32_t) h.y & 0x3F3F3F3Fu, mn_lo = (uint32_t) h.z & 0x3F3F3F3Fu;
+        const uint32_t sc_hi = ((uint32_t) h.w & 0x0F0F0F0Fu) | (((uint32_t) h.y >> 2) & 0x30303030u);
+        const uint32_t mn_hi = (((uint32_t) h.w >> 4) & 0x0F0F0F0Fu) | (((uint32_t) h.z >> 2) & 0x30303030u);
+        const int4     f0 = lds128(b + 16), f1 = lds128(b + 32);  // qh[0..15], qh[16..31]
+        const uint32_t fh[8] = { (uint32_t) f0.x, (uint32_t) f0.y, (uint32_t) f0.z, (uint32_t) f0.w,
+                                 (uint32_t) f1.x, (uint32_t) f1.y, (uint32_t) f1.z, (uint32_t) f1.w };
+        int acc = 0;
+#pragma unroll
+        for (int pq = 0; pq < 4; ++pq) {
+            const int4 q0 = lds128(b + 48 + 32 * pq), q1 = lds128(b + 64 + 32 * pq);
+            const uint32_t qw[8] = { (uint32_t) q0.x, (uint32_t) q0.y, (uint32_t) q0.z, (uint32_t) q0.w,
+                                     (uint32_t) q1.x, (uint32_t) q1.y, (uint32_t) q1.z, (uint32_t) q1.w };
+            const int4 a0 = act.chunk(4 * pq + 0), a1 = act.chunk(4 * pq + 1);
+            const int4 a2 = act.chunk(4 * pq + 2), a3 = act.chunk(4 * pq + 3);
+            const int  al[8] = { a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w };
+            const int  ah[8] = { a2.x, a2.y, a2.z, a2.w, a3.x, a3.y, a3.z, a3.w };
+            int lo = 0, hi = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const uint32_t vl = (qw[i] & 0x0F0F0F0Fu) | (((fh[i] >> (2 * pq)) & 0x01010101u) << 4);
+                const uint32_t vh = ((qw[i] >> 4) & 0x0F0F0F0Fu) | (((fh[i] >> (2 * pq + 1)) & 0x01010101u) << 4);
+                lo = dp4a_us(vl, al[i], lo);
+                hi = dp4a_us(vh, ah[i], hi);
+            }
+            const uint32_t scw = pq < 2 ? sc_lo : sc_hi;
+            const int      sh  = 16 * (pq & 1);
+            acc += (int) ((scw >> sh) & 0xFFu) * lo + (int) ((scw >> (sh + 8)) & 0xFFu) * hi;
+        }
+        const int4 bs = act.bs32();  // 8 x int16 sums over 32 activations
+        int mins = dp2a_lo_su(bs.x, mn_lo, 0);
+        mins     = dp2a_hi_su(bs.y, mn_lo, mins);
+        mins     = dp2a_lo_su(bs.z, mn_hi, mins);
+        mins     = dp2a_hi_su(bs.w, mn_hi, mins);
+        const float d    = half_bits_to_float((uint16_t) ((uint32_t) h.x & 0xffffu));
+        const float dmin = half_bits_to_float((uint16_t) ((uint32_t) h.x >> 16));
+        const float dx   = act.dx();
+        return dx * (d * (float) acc - dmin * (float) mins);
+    }
+};
+
 template <> struct SbDot<T_Q6_K> {
     static constexpr int SB_BYTES = 210;
     // 210-byte super-blocks are only 2-byte aligned: aligned words + funnel shift (shift is 0 or 16, constant per lane)
