@@ -723,6 +723,19 @@ def main_b200(args):
     desc = workloads.describe(ops)
     chain_txt = ("every new activation vector waits for all earlier matmuls (model order: qkv -> wo -> gate/up -> down -> next layer), "
                  f"{info.n_barrier_points} device-side barrier points per step" if dep_chain else "no dependencies between matmuls (upper bound)")
+    # DRAM bytes of ONE launch of the dominant kernel from the committed ncu --set full capture of the same kernel on the same
+    # workload (profiles/list_traffic.json; ncu cannot run inside a timed bench): reported only for the configuration it was taken on
+    traffic, traffic_note = None, "no ncu capture for this configuration"
+    try:
+        with open(os.path.join(ROOT, "profiles", "list_traffic.json")) as f:
+            tj = json.load(f).get("full_step")
+        if tj and world == 1 and n_launch == 1 and args.workload == tj.get("workload") and int(algo) == int(tj["algorithmic_bytes"]):
+            traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
+            traffic_note = f"bytes per launch; {tj['source']}: dram read + write = {tj['ratio']} x algorithmic bytes (not measured in this run)"
+        elif tj:
+            traffic_note = "not measured for this configuration; single-GPU whole-step capture: " + tj["source"]
+    except Exception as e:  # noqa: BLE001
+        traffic_note = f"profiles/list_traffic.json unreadable: {e!r}"
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -744,8 +757,8 @@ def main_b200(args):
                         "D2H on a second copy stream after each launch" + ("" if world == 1 else "; every rank copies all activations in, rank 0 copies the results out")},
         "gpu_launches": n_launch * args.steps,
         "roofline": {"bound": "hbm", "achieved": value / world, "peak": peak, "unit": "GB/s",
-                     "frac": value / world / peak, "traffic": None, "peak_source": peak_src,
-                     "traffic_note": "not measured in this run; ncu --set full of the same kernel on an 8-layer slice: dram read + write = 1.002 x algorithmic bytes (profiles/list_traffic.json, profiles/r02_ncu_list_full_v1.csv)",
+                     "frac": value / world / peak, "traffic": traffic, "peak_source": peak_src,
+                     "traffic_note": traffic_note,
                      "kernel": "gemv_list_kernel (one launch = the whole step)",
                      "launches_per_step": n_launch,
                      "algorithmic_bytes_per_launch_avg": algo / world / max(1, n_launch),

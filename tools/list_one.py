@@ -1,5 +1,6 @@
 #!/usr/bin/env python3
-"""an 8-layer slice of the Llama-3-8B Q4_K_M decode list, launched a few times (ncu target): tools/list_one.py [dep=0] [layers=8]"""
+"""the Llama-3-8B Q4_K_M decode list (an n-layer slice, or the whole 225-matmul step with the output matrix), launched a few times
+(ncu target): tools/list_one.py [dep=0] [layers=8] [with_output=0]"""
 import os
 import sys
 
@@ -13,7 +14,8 @@ from b200q import workloads  # noqa: E402
 
 dep = int(sys.argv[1]) if len(sys.argv) > 1 else 0
 layers = int(sys.argv[2]) if len(sys.argv) > 2 else 8
-ops = workloads.llama3_8b("q4_k_m", layers=layers, with_output=False)
+with_output = bool(int(sys.argv[3])) if len(sys.argv) > 3 else False
+ops = workloads.llama3_8b("q4_k_m", layers=layers, with_output=with_output)
 shards = [workloads.synth_weights_device(o, seed=1234 + i) for i, o in enumerate(ops)]
 acts = [torch.rand(o.k, device="cuda") * 2 - 1 for o in ops]
 outs = [torch.zeros(o.m, device="cuda") for o in ops]
