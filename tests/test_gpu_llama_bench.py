@@ -20,15 +20,17 @@ def _exe():
     return os.path.join(d, "llama-bench")
 
 
-@pytest.mark.parametrize("ftype", ["q4_k_m", "q8_0"])
+@pytest.mark.parametrize("ftype", ["q4_k_m", "q8_0", "gpt-oss"])
 def test_llama_bench_runs_on_the_plugin(tmp_path, ftype):
     exe = _exe()
     plugin = os.path.join(ROOT, "llama.cpp-gfx906_b200", "lib", "libggml-b200.so")
     if not os.path.exists(exe):
         pytest.skip("oracle/_ref/llama-bench not built (make -C oracle llama)")
     gguf = str(tmp_path / "synth.gguf")
-    subprocess.run([sys.executable, os.path.join(ROOT, "tools", "make_synth_gguf.py"), "--out", gguf, "--layers", "4", "--ftype", ftype,
-                    "--vocab", "32000"], check=True, capture_output=True, timeout=300)
+    # "gpt-oss": the MoE architecture of BASELINE config 4 (MXFP4 experts, attention sinks, sliding window, biases through ADD_ID)
+    kind = ["--arch", "gpt-oss"] if ftype == "gpt-oss" else ["--ftype", ftype]
+    subprocess.run([sys.executable, os.path.join(ROOT, "tools", "make_synth_gguf.py"), "--out", gguf, "--layers", "4", "--vocab", "32000"] + kind,
+                   check=True, capture_output=True, timeout=300)
     env = dict(os.environ, GGML_BACKEND_PATH=plugin)
     r = subprocess.run([exe, "-m", gguf, "-ngl", "99", "-fa", "0", "-p", "64", "-n", "16", "-r", "2"], env=env, capture_output=True, text=True,
                        timeout=600)

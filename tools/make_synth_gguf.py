@@ -43,13 +43,82 @@ def use_more_bits(i, n):  # llama-quant.cpp: which layers get the wider type in 
     return i < n // 8 or i >= 7 * n // 8 or (i - n // 8) % 3 == 2
 
 
+def write_gguf(path, kvs, tensors):
+    """tensors: (name, ne in ggml order, type); data = valid random blocks tiled / f32 noise"""
+    def nbytes(ne, t):
+        rows = int(np.prod(ne[1:])) if len(ne) > 1 else 1
+        return rows * (ne[0] * 4 if t == F32 else refs.row_size(t, ne[0]))
+
+    head = struct.pack("<IIQQ", 0x46554747, 3, len(tensors), len(kvs)) + b"".join(kvs)
+    off, infos = 0, b""
+    for name, ne, t in tensors:
+        infos += _s(name.encode()) + struct.pack("<I", len(ne)) + b"".join(struct.pack("<Q", d) for d in ne)
+        infos += struct.pack("<IQ", t, off)
+        off += (nbytes(ne, t) + ALIGN - 1) // ALIGN * ALIGN
+    blocks = {}
+    with open(path, "wb") as f:
+        f.write(head + infos)
+        f.write(b"\0" * (-f.tell() % ALIGN))
+        for name, ne, t in tensors:
+            rows = int(np.prod(ne[1:])) if len(ne) > 1 else 1
+            if t == F32:
+                scale = 1.0 if name.endswith("norm.weight") else 0.0
+                data = (scale + 0.01 * np.random.default_rng(len(name)).standard_normal(ne[0] * rows)).astype(np.float32).tobytes()
+            else:
+                key = (t, ne[0])
+                if key not in blocks:
+                    blocks[key] = refs.random_blocks(t, 256, ne[0], seed=17 + t)
+                data = np.tile(blocks[key], ((rows + 255) // 256, 1))[:rows].tobytes()
+            assert len(data) == nbytes(ne, t), (name, len(data), nbytes(ne, t))
+            f.write(data)
+            f.write(b"\0" * (-len(data) % ALIGN))
+    print(f"{path}: {len(tensors)} tensors, {os.path.getsize(path) / 1e9:.2f} GB")
+
+
+def gpt_oss(a):
+    """gpt-oss-20B's architecture (src/llama-model.cpp LLM_ARCH_OPENAI_MOE): MXFP4 experts, q8_0 attention, f32 biases / sinks / router"""
+    n_embd, n_head, n_head_kv, hd, n_expert, n_used, n_ff = 2880, 64, 8, 64, 32, 4, 2880
+    layers = a.layers if a.layers != 32 else 24
+    vocab = a.vocab or 201088
+    Q8, MX = refs.Q8_0, refs.MXFP4
+    tensors = [("token_embd.weight", (n_embd, vocab), Q8)]
+    for i in range(layers):
+        p = f"blk.{i}."
+        tensors += [(p + "attn_norm.weight", (n_embd,), F32), (p + "post_attention_norm.weight", (n_embd,), F32),
+                    (p + "attn_q.weight", (n_embd, n_head * hd), Q8), (p + "attn_q.bias", (n_head * hd,), F32),
+                    (p + "attn_k.weight", (n_embd, n_head_kv * hd), Q8), (p + "attn_k.bias", (n_head_kv * hd,), F32),
+                    (p + "attn_v.weight", (n_embd, n_head_kv * hd), Q8), (p + "attn_v.bias", (n_head_kv * hd,), F32),
+                    (p + "attn_output.weight", (n_head * hd, n_embd), Q8), (p + "attn_output.bias", (n_embd,), F32),
+                    (p + "attn_sinks.weight", (n_head,), F32),
+                    (p + "ffn_gate_inp.weight", (n_embd, n_expert), F32), (p + "ffn_gate_inp.bias", (n_expert,), F32),
+                    (p + "ffn_gate_exps.weight", (n_embd, n_ff, n_expert), MX), (p + "ffn_gate_exps.bias", (n_ff, n_expert), F32),
+                    (p + "ffn_up_exps.weight", (n_embd, n_ff, n_expert), MX), (p + "ffn_up_exps.bias", (n_ff, n_expert), F32),
+                    (p + "ffn_down_exps.weight", (n_ff, n_embd, n_expert), MX), (p + "ffn_down_exps.bias", (n_embd, n_expert), F32)]
+    tensors += [("output_norm.weight", (n_embd,), F32), ("output.weight", (n_embd, vocab), Q8)]
+    A = "gpt-oss."
+    kvs = [kv("general.architecture", T_STR, "gpt-oss"), kv("general.name", T_STR, "synthetic gpt-oss-20b-shaped mxfp4"),
+           kv("general.alignment", T_U32, ALIGN), kv(A + "context_length", T_U32, 8192), kv(A + "embedding_length", T_U32, n_embd),
+           kv(A + "block_count", T_U32, layers), kv(A + "feed_forward_length", T_U32, n_ff), kv(A + "expert_feed_forward_length", T_U32, n_ff),
+           kv(A + "attention.head_count", T_U32, n_head), kv(A + "attention.head_count_kv", T_U32, n_head_kv),
+           kv(A + "attention.key_length", T_U32, hd), kv(A + "attention.value_length", T_U32, hd),
+           kv(A + "attention.layer_norm_rms_epsilon", T_F32, 1e-5), kv(A + "attention.sliding_window", T_U32, 128),
+           kv(A + "rope.dimension_count", T_U32, hd), kv(A + "rope.freq_base", T_F32, 150000.0),
+           kv(A + "expert_count", T_U32, n_expert), kv(A + "expert_used_count", T_U32, n_used), kv(A + "vocab_size", T_U32, vocab),
+           kv("tokenizer.ggml.model", T_STR, "no_vocab")]
+    write_gguf(a.out, kvs, tensors)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", required=True)
     ap.add_argument("--layers", type=int, default=32)
     ap.add_argument("--ftype", default="q4_k_m")
-    ap.add_argument("--vocab", type=int, default=128256)
+    ap.add_argument("--vocab", type=int, default=0)
+    ap.add_argument("--arch", default="llama", choices=["llama", "gpt-oss"])
     a = ap.parse_args()
+    if a.arch == "gpt-oss":
+        return gpt_oss(a)
+    a.vocab = a.vocab or 128256
     n_embd, n_ff, n_head, n_head_kv, hd = 4096, 14336, 32, 8, 128
     base = {"q4_k_m": refs.Q4_K, "q8_0": refs.Q8_0, "q4_0": refs.Q4_0}[a.ftype]
     wide = refs.Q6_K if a.ftype == "q4_k_m" else base
