@@ -323,6 +323,10 @@ B200Q_API int b200q_op_argsort(const b200q_tensor * src, const b200q_tensor * ds
 B200Q_API int b200q_op_set_rows(const b200q_tensor * src, const b200q_tensor * idx, const b200q_tensor * dst,
                                 void * stream);                                                                            /* set-rows.cu */
 
+/* MoE combine in one launch: dst[i0, t] = sum_s experts[i0, s, t] * weights[0, s, t] (llama.cpp emits MUL + one VIEW per used expert + a
+ * chain of ADDs, src/llama-graph.cpp build_moe_ffn); products rounded separately and added in slot order, as the separate operators do */
+B200Q_API int b200q_op_moe_weighted_sum(const b200q_tensor * experts, const b200q_tensor * weights, const b200q_tensor * dst, void * stream);
+
 /* two independent SET_ROWS with one destination type in one launch (a layer's K and V cache writes are consecutive nodes) */
 B200Q_API int b200q_op_set_rows_pair(const b200q_tensor * src0, const b200q_tensor * idx0, const b200q_tensor * dst0,
                                      const b200q_tensor * src1, const b200q_tensor * idx1, const b200q_tensor * dst1, void * stream);

@@ -56,12 +56,16 @@ __device__ __forceinline__ void batch_ptrs(const DenseParams & p, int b, const u
 
 constexpr int GV_WARPS = 4;
 
-template <int T, int NC> __global__ void __launch_bounds__(GV_WARPS * 32) dense_gemv_kernel(const DenseParams p) {
+// WIDE: few rows (a MoE router: 32 rows of 2880 values took 10 us with one warp per row) — one CTA per row, its four warps
+// split k and add their partial sums in warp order
+template <int T, int NC, bool WIDE> __global__ void __launch_bounds__(GV_WARPS * 32) dense_gemv_kernel(const DenseParams p) {
     pdl_grid_sync();
     using E = typename Elem<T>::type;
     constexpr int VEC = 16 / (int) sizeof(E);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int row  = blockIdx.x * GV_WARPS + warp;
+    constexpr int LANES = WIDE ? GV_WARPS * 32 : 32;  // threads that share one row
+    __shared__ float part[GV_WARPS][NC];
+    const int warp = threadIdx.x >> 5, lane = WIDE ? (int) threadIdx.x : (int) (threadIdx.x & 31);
+    const int row  = WIDE ? (int) blockIdx.x : (int) (blockIdx.x * GV_WARPS + warp);
     if (row >= p.m) return;
     for (int b = blockIdx.y; b < p.ne12 * p.ne13; b += gridDim.y) {
         const uint8_t *w, *act;
@@ -74,7 +78,7 @@ template <int T, int NC> __global__ void __launch_bounds__(GV_WARPS * 32) dense_
         int k0 = 0;
         if (p.vec) {
             const int nv = p.k / VEC;
-            for (int v = lane; v < nv; v += 32) {
+            for (int v = lane; v < nv; v += LANES) {
                 const uint4 raw = __ldg((const uint4 *) wr + v);
                 const E *   e   = (const E *) &raw;
                 float       wv[VEC];
@@ -97,7 +101,7 @@ template <int T, int NC> __global__ void __launch_bounds__(GV_WARPS * 32) dense_
             }
             k0 = nv * VEC;
         }
-        for (int i = k0 + lane; i < p.k; i += 32) {
+        for (int i = k0 + lane; i < p.k; i += LANES) {
             const float wv = Elem<T>::cvt(wr[i]);
 #pragma unroll
             for (int c = 0; c < NC; ++c) {
@@ -109,7 +113,21 @@ template <int T, int NC> __global__ void __launch_bounds__(GV_WARPS * 32) dense_
             float s = acc[c];
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            if (lane == 0 && c < p.n) *((float *) (dst + (long long) c * p.d_nb1) + row) = s;
+            if (WIDE) {
+                if ((threadIdx.x & 31) == 0) part[warp][c] = s;
+            } else if (lane == 0 && c < p.n) {
+                *((float *) (dst + (long long) c * p.d_nb1) + row) = s;
+            }
+        }
+        if (WIDE) {
+            __syncthreads();
+            if (threadIdx.x < NC && (int) threadIdx.x < p.n) {
+                float s = part[0][threadIdx.x];
+#pragma unroll
+                for (int q = 1; q < GV_WARPS; ++q) s += part[q][threadIdx.x];
+                *((float *) (dst + (long long) threadIdx.x * p.d_nb1) + row) = s;
+            }
+            __syncthreads();
         }
     }
 }
@@ -174,11 +192,18 @@ template <int T> __global__ void __launch_bounds__(256) dense_tile_kernel(const 
 template <int T> int launch_t(const DenseParams & p, cudaStream_t st) {
     const int nbatch = p.ne12 * p.ne13;
     if (p.n <= 8) {
-        const dim3 grid((unsigned) ((p.m + GV_WARPS - 1) / GV_WARPS), (unsigned) (nbatch < 65535 ? nbatch : 65535));
-        if (p.n == 1) launch_pdl(dense_gemv_kernel<T, 1>, dim3(grid), dim3(GV_WARPS * 32), 0, st, p);
-        else if (p.n == 2) launch_pdl(dense_gemv_kernel<T, 2>, dim3(grid), dim3(GV_WARPS * 32), 0, st, p);
-        else if (p.n <= 4) launch_pdl(dense_gemv_kernel<T, 4>, dim3(grid), dim3(GV_WARPS * 32), 0, st, p);
-        else launch_pdl(dense_gemv_kernel<T, 8>, dim3(grid), dim3(GV_WARPS * 32), 0, st, p);
+        const bool wide = (long long) p.m * nbatch <= 592 && p.k >= 1024;  // fewer rows than 4 warps per SM can take one each
+        const dim3 grid((unsigned) (wide ? p.m : (p.m + GV_WARPS - 1) / GV_WARPS), (unsigned) (nbatch < 65535 ? nbatch : 65535));
+        const dim3 block(GV_WARPS * 32);
+        if (wide) {
+            if (p.n == 1) launch_pdl(dense_gemv_kernel<T, 1, true>, grid, block, 0, st, p);
+            else if (p.n == 2) launch_pdl(dense_gemv_kernel<T, 2, true>, grid, block, 0, st, p);
+            else if (p.n <= 4) launch_pdl(dense_gemv_kernel<T, 4, true>, grid, block, 0, st, p);
+            else launch_pdl(dense_gemv_kernel<T, 8, true>, grid, block, 0, st, p);
+        } else if (p.n == 1) launch_pdl(dense_gemv_kernel<T, 1, false>, grid, block, 0, st, p);
+        else if (p.n == 2) launch_pdl(dense_gemv_kernel<T, 2, false>, grid, block, 0, st, p);
+        else if (p.n <= 4) launch_pdl(dense_gemv_kernel<T, 4, false>, grid, block, 0, st, p);
+        else launch_pdl(dense_gemv_kernel<T, 8, false>, grid, block, 0, st, p);
     } else {
         const long long gy = (p.n + TN - 1) / TN;
         if (gy > 65535) return B200Q_ENOTSUP;

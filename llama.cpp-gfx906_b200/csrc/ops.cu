@@ -610,6 +610,24 @@ __global__ void __launch_bounds__(256) scatter_rows_peers_kernel(const ScatterP 
     }
 }
 
+// ---- MoE combine: dst[i0, t] = sum_s e[i0, s, t] * w[s, t] — llama.cpp emits MUL(experts, weights), one VIEW per used expert and a
+// chain of ADDs (src/llama-graph.cpp build_moe_ffn: 4 launches per layer for top-4); same arithmetic and order: every product
+// rounded, then ((p0 + p1) + p2) + p3
+__global__ void __launch_bounds__(256) moe_weighted_sum_kernel(T4 e, T4 w, T4 d, long long n) {
+    pdl_grid_sync();
+    const int n_used = (int) e.ne[1];
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
+        const long long i0 = i % e.ne[0], t = i / e.ne[0];
+        const char * ep = e.data + i0 * 4 + t * e.nb[2];
+        const char * wp = w.data + t * w.nb[2];
+        float acc = __fmul_rn(*(const float *) ep, *(const float *) wp);
+        for (int s = 1; s < n_used; ++s) {
+            acc = __fadd_rn(acc, __fmul_rn(*(const float *) (ep + (long long) s * e.nb[1]), *(const float *) (wp + (long long) s * w.nb[1])));
+        }
+        *(float *) (d.data + i0 * 4 + t * d.nb[1]) = acc;
+    }
+}
+
 // ---- ADD_ID: dst[i0, i1, i2] = a[i0, i1, i2] + b[i0, ids[i1, i2]] (the per-expert bias of a MoE layer; add-id.cu) ----------------
 __global__ void __launch_bounds__(256) add_id_kernel(T4 a, T4 b, T4 ids, T4 d, long long n) {
     pdl_grid_sync();
@@ -940,6 +958,19 @@ int b200q_scatter_rows_peers(const float * src, const int32_t * row_index, float
     p.src = src; p.row_index = row_index; p.dst = dst; p.m = m; p.n_rows = n_rows; p.dst_row_stride = dst_row_stride; p.n_peers = n_peers;
     for (int q = 0; q < n_peers; ++q) p.peer_delta[q] = peer_delta[q];
     launch_pdl(scatter_rows_peers_kernel, dim3(grid_for(n_rows * m, 256)), dim3(256), 0, (cudaStream_t) stream, p);
+    return launched();
+}
+
+// experts f32 [n, n_used, n_tok] * weights f32 [1, n_used, n_tok], summed over the used experts -> dst f32 [n, n_tok]
+int b200q_op_moe_weighted_sum(const b200q_tensor * experts, const b200q_tensor * weights, const b200q_tensor * dst, void * stream) {
+    if (!experts || !weights || !dst || experts->type != B200Q_TYPE_F32 || weights->type != B200Q_TYPE_F32 || dst->type != B200Q_TYPE_F32 ||
+        experts->nb[0] != 4 || dst->nb[0] != 4 || experts->ne[3] != 1 || weights->ne[0] != 1 || weights->ne[1] != experts->ne[1] ||
+        weights->ne[2] != experts->ne[2] || weights->ne[3] != 1 || dst->ne[0] != experts->ne[0] || dst->ne[1] != experts->ne[2] || experts->ne[1] < 1) {
+        return ops_fail(B200Q_ENOTSUP, "moe_weighted_sum: experts f32 [n, n_used, n_tok], weights f32 [1, n_used, n_tok], dst f32 [n, n_tok]");
+    }
+    const long long n = experts->ne[0] * experts->ne[2];
+    if (n == 0) return 0;
+    launch_pdl(moe_weighted_sum_kernel, dim3(grid_for(n, 256)), dim3(256), 0, (cudaStream_t) stream, t4(experts), t4(weights), t4(dst), n);
     return launched();
 }
 

@@ -1238,6 +1238,45 @@ int try_fuse_attn(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int i, int n_nod
     return j4 + 1;
 }
 
+// The MoE combine — MUL(experts [n, n_used, n_tok], weights [1, n_used, n_tok]), one VIEW per used expert, a chain of n_used - 1
+// ADDs (src/llama-graph.cpp build_moe_ffn) — as ONE launch (b200q_op_moe_weighted_sum).  The MUL's result is never written: its
+// only consumers must be the n_used views, every view and every ADD but the last must have exactly one consumer.
+// Returns the index behind the run (i: no fusion).
+int try_fuse_moe_sum(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int i, int n_nodes, int * rc) {
+    if (!cgraph->use_counts) return i;
+    const ggml_tensor * mul = ggml_graph_node(cgraph, i);
+    const ggml_tensor * e = mul->src[0], * w = mul->src[1];
+    auto f32c = [](const ggml_tensor * t) { return t && t->type == GGML_TYPE_F32 && t->nb[0] == sizeof(float); };
+    if (!f32c(e) || !f32c(w) || !f32c(mul) || !ggml_are_same_shape(e, mul) || !ggml_is_contiguous(mul)) return i;
+    const int64_t n = e->ne[0], n_used = e->ne[1], n_tok = e->ne[2];
+    if (n_used < 2 || n_used > 16 || e->ne[3] != 1 || w->ne[0] != 1 || w->ne[1] != n_used || w->ne[2] != n_tok || w->ne[3] != 1) return i;
+    if (node_use_count(cgraph, mul) != (int32_t) n_used || (mul->flags & GGML_TENSOR_FLAG_OUTPUT)) return i;
+    // the views (in slot order, possibly interleaved with other no-op nodes), then the adds
+    std::vector<const ggml_tensor *> views;
+    int j = i + 1;
+    for (; j < n_nodes && (int64_t) views.size() < n_used; ++j) {
+        const ggml_tensor * t = ggml_graph_node(cgraph, j);
+        if (t->op != GGML_OP_VIEW) return i;
+        const size_t slot = views.size();
+        if (t->src[0] != mul || t->view_src != mul || t->view_offs != slot * mul->nb[1] || t->ne[0] != n || t->ne[1] != n_tok || t->ne[2] != 1 ||
+            t->nb[1] != mul->nb[2] || node_use_count(cgraph, t) != 1) return i;
+        views.push_back(t);
+    }
+    if ((int64_t) views.size() != n_used) return i;
+    const ggml_tensor * prev = views[0];
+    for (int64_t sidx = 1; sidx < n_used; ++sidx, ++j) {
+        if (j >= n_nodes) return i;
+        const ggml_tensor * a = ggml_graph_node(cgraph, j);
+        if (a->op != GGML_OP_ADD || a->src[0] != prev || a->src[1] != views[(size_t) sidx] || !f32c(a) || !ggml_is_contiguous(a) ||
+            a->ne[0] != n || a->ne[1] != n_tok) return i;
+        if (sidx < n_used - 1 && (node_use_count(cgraph, a) != 1 || (a->flags & GGML_TENSOR_FLAG_OUTPUT) || a->view_src)) return i;
+        prev = a;
+    }
+    const b200q_tensor te = bt(e), tw = bt(w), td = bt(prev);
+    *rc = b200q_op_moe_weighted_sum(&te, &tw, &td, ctx->stream);
+    return j;
+}
+
 ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
     const int  n_nodes  = ggml_graph_n_nodes(cgraph);
     const bool no_fuse  = getenv("GGML_B200_NO_FUSE") != nullptr;
@@ -1280,6 +1319,17 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
                     return GGML_STATUS_FAILED;
                 }
                 i += used - 1;
+                continue;
+            }
+        }
+        if (!no_fuse && node->op == GGML_OP_MUL && node->src[1] && node->src[1]->ne[0] == 1 && node->ne[1] > 1) {
+            const int behind = try_fuse_moe_sum(ctx, cgraph, i, n_nodes, &rc);
+            if (behind > i) {
+                if (rc != 0) {
+                    fprintf(stderr, "ggml-b200: fused MoE combine (%s) failed (%d): %s\n", node->name, rc, b200q_last_error());
+                    return GGML_STATUS_FAILED;
+                }
+                i = behind - 1;
                 continue;
             }
         }
