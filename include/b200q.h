@@ -272,6 +272,13 @@ B200Q_API int    b200q_mul_mat_id(const b200q_mul_mat_id_args * a, const void * 
                                   const int32_t * ids, float * dst, void * workspace, size_t workspace_bytes,
                                   void * stream);
 
+/* MUL_MAT_ID + ADD_ID (dst[t][s][:] += bias[ids[t][s]][:], the experts' bias rows of gpt-oss) in one launch; decode only
+ * (n_tokens == 1: the ring kernel's epilogue adds the bias) — B200Q_ENOTSUP otherwise, the caller then runs the two operators.
+ * bias f32, bias_nb1 = bytes between the experts' rows. */
+B200Q_API int    b200q_mul_mat_id_bias(const b200q_mul_mat_id_args * a, const void * as, const float * b, const int32_t * ids,
+                                       const float * bias, size_t bias_nb1, float * dst, void * workspace, size_t workspace_bytes,
+                                       void * stream);
+
 /* ---- the operators around the matmuls of a decoder layer: they keep a layer's graph on the device.  Each one
  *      replaces the reference CUDA kernel named beside it (ggml/src/ggml-cuda/) and follows the arithmetic of the CPU operator
  *      (ggml/src/ggml-cpu/ops.cpp); tensors are described ggml's way.  B200Q_ENOTSUP = layout / type the kernel does not take

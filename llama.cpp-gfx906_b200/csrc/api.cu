@@ -1097,6 +1097,10 @@ size_t b200q_mul_mat_id_workspace(const b200q_mul_mat_id_args * a) {
     return mmq_moe_workspace_bytes(a->k, a->n_tokens, a->n_used, a->n_expert);
 }
 
+// b200q_mul_mat_id_bias hands the bias to the decode branch of b200q_mul_mat_id through these (same thread, same call)
+static thread_local const float * g_moe_bias        = nullptr;
+static thread_local long long     g_moe_bias_stride = 0;
+
 int b200q_mul_mat_id(const b200q_mul_mat_id_args * a, const void * as, const float * b, const int32_t * ids, float * dst,
                      void * workspace, size_t workspace_bytes, void * stream) {
     if (!a || !as || !b || !ids || !dst) return fail(B200Q_EINVAL, "mul_mat_id: null argument");
@@ -1160,9 +1164,11 @@ int b200q_mul_mat_id(const b200q_mul_mat_id_args * a, const void * as, const flo
         }
         if (plan_kq(kq, grid, smem, a->type, a->k, (int) a->n_used, wl, dl, ml, b, di, ids, (long long) a->nb02,
                     a->b_ne1 == 1 ? 0 : (long long) (a->nb11 / 4))) {
+            kq.bias = g_moe_bias; kq.bias_stride = g_moe_bias_stride;
             return launch_kq(kq, grid, smem, a->type, a->flags, (cudaStream_t) stream);
         }
     }
+    if (g_moe_bias) return fail(B200Q_ENOTSUP, "mul_mat_id_bias: only the one-token ring-kernel path adds the bias");
 
     // one GEMV channel per (token, slot); expert ids are read on the device (no host round trip, cf. mmq.cu:161)
     GemvPlan plan{};
@@ -1180,6 +1186,18 @@ int b200q_mul_mat_id(const b200q_mul_mat_id_args * a, const void * as, const flo
     p.act_vec4 = aligned16(b, p.a_nb1) && (p.a_nb2 & 15) == 0;
     if (!plan_gemv(plan, a->type, 1, di)) return fail(B200Q_ENOTSUP, "mul_mat_id: k too large");
     return launch_gemv(plan, a->type, 1, a->flags, (cudaStream_t) stream);
+}
+
+// MUL_MAT_ID followed by ADD_ID (the experts' bias rows) in one launch: decode only (one token, the ring kernel's epilogue adds
+// bias[ids[g]][row]); B200Q_ENOTSUP otherwise — the caller then runs the two operators
+int b200q_mul_mat_id_bias(const b200q_mul_mat_id_args * a, const void * as, const float * b, const int32_t * ids, const float * bias,
+                          size_t bias_nb1, float * dst, void * workspace, size_t workspace_bytes, void * stream) {
+    if (!a || !bias || bias_nb1 % 4) return fail(B200Q_EINVAL, "mul_mat_id_bias: null / unaligned bias");
+    if (a->n_tokens != 1 || moe_use_mxf(a) || moe_use_mmq(a)) return fail(B200Q_ENOTSUP, "mul_mat_id_bias: one token only");
+    g_moe_bias = bias; g_moe_bias_stride = (long long) (bias_nb1 / 4);
+    const int rc = b200q_mul_mat_id(a, as, b, ids, dst, workspace, workspace_bytes, stream);
+    g_moe_bias = nullptr; g_moe_bias_stride = 0;
+    return rc;
 }
 
 // ---- persistent decode list --------------------------------------------------------------------------------------------

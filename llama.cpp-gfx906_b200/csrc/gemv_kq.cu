@@ -137,9 +137,13 @@ template <int T, bool MOE> __global__ void __launch_bounds__(NTHREADS, 2) gemv_k
     // producer hop: the warp that finishes a slot refills it at once.
     // MoE: the experts are chosen by ids[] (written by an earlier kernel of the stream: read only after the wait)
     const uint8_t * segw[KQ_MAX_SEG];
+    long long       eoff[KQ_MAX_SEG];  // MoE with a bias: the segment's expert * bias_stride
     if (MOE) {
 #pragma unroll
-        for (int g = 0; g < KQ_MAX_SEG; ++g) segw[g] = p.seg[g].w;
+        for (int g = 0; g < KQ_MAX_SEG; ++g) {
+            segw[g] = p.seg[g].w;
+            eoff[g] = 0;
+        }
     }
     auto seg_w = [&](int g) -> const uint8_t * { return MOE ? seg_ptr(segw, g) : p.seg[g].w; };
     const uint64_t pol    = policy_evict_first();
@@ -163,7 +167,11 @@ template <int T, bool MOE> __global__ void __launch_bounds__(NTHREADS, 2) gemv_k
     if (MOE && p.ids) {
 #pragma unroll
         for (int g = 0; g < KQ_MAX_SEG; ++g) {
-            if (g < p.nseg) segw[g] = p.seg[g].w + (long long) __ldg(p.ids + g) * p.expert_stride;
+            if (g < p.nseg) {
+                const long long e = (long long) __ldg(p.ids + g);
+                segw[g] = p.seg[g].w + e * p.expert_stride;
+                eoff[g] = e * p.bias_stride;
+            }
         }
     }
     if (!p.early_prefetch && lane == 0) {
@@ -203,6 +211,16 @@ template <int T, bool MOE> __global__ void __launch_bounds__(NTHREADS, 2) gemv_k
         }
         if (sub == 0 && lrow < si.nrows) {
             float * d = p.seg[si.g].dst + si.r0 + lrow;
+            if (MOE) {
+                if (p.bias) {  // the expert's bias row (ggml_add_id behind ggml_mul_mat_id): one f32 add, as the separate operator
+                    long long eo = eoff[0];
+#pragma unroll
+                    for (int q = 1; q < KQ_MAX_SEG; ++q) {
+                        if (si.g == q) eo = eoff[q];
+                    }
+                    acc = acc + __ldg(p.bias + eo + si.r0 + lrow);
+                }
+            }
             *d = acc;
             for (int r = 0; r < p.n_peers; ++r) {  // fire-and-forget stores over NVLink (visible at kernel completion)
                 *(float *) ((char *) d + p.peer_delta[r]) = acc;

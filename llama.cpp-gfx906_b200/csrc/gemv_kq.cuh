@@ -37,6 +37,8 @@ struct KqParams {
     const int32_t * ids;           // nullptr: plain segments
     long long       expert_stride; // bytes between expert matrices (seg[g].w holds the base of expert 0)
     long long       act_seg_stride;  // floats between the segments' activation vectors (0: shared)
+    const float *   bias;          // MoE only, may be nullptr: dst += bias[ids[g] * bias_stride + row] (the ADD_ID behind the matmul)
+    long long       bias_stride;   // floats between the experts' bias rows
     int             act_smem_stride; // bytes between the segments' quantized activation images (0: shared)
 };
 

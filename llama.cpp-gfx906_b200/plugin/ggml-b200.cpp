@@ -808,7 +808,9 @@ int compute_mul_mat(b200_backend_ctx * ctx, const ggml_tensor * op) {
     }
     return b200q_mul_mat(&q, a->data, act, (float *) op->data, need ? ws + conv : nullptr, need ? ctx->ws_bytes - conv : 0, ctx->stream);
 }
-int compute_mul_mat_id(b200_backend_ctx * ctx, const ggml_tensor * op) {
+// `bias_node` != nullptr: the ADD_ID node behind this MUL_MAT_ID (same ids, the matmul's only consumer) — try both in one launch,
+// writing into the ADD_ID's result; returns 1 when the pair has to go out separately
+int compute_mul_mat_id(b200_backend_ctx * ctx, const ggml_tensor * op, const ggml_tensor * bias_node = nullptr) {
     const ggml_tensor *   as  = op->src[0];
     const ggml_tensor *   b   = op->src[1];
     const ggml_tensor *   ids = op->src[2];
@@ -823,6 +825,13 @@ int compute_mul_mat_id(b200_backend_ctx * ctx, const ggml_tensor * op) {
     q.flags = weight_flags(as);
     const size_t need = b200q_mul_mat_id_workspace(&q);
     void *       ws   = need ? backend_workspace(ctx, need) : nullptr;
+    if (bias_node) {
+        const ggml_tensor * bias = bias_node->src[1];
+        q.nb1 = bias_node->nb[1]; q.nb2 = bias_node->nb[2];
+        const int rc = b200q_mul_mat_id_bias(&q, as->data, (const float *) b->data, (const int32_t *) ids->data, (const float *) bias->data,
+                                             bias->nb[1], (float *) bias_node->data, ws, ctx->ws_bytes, ctx->stream);
+        return rc == B200Q_ENOTSUP ? 1 : rc;
+    }
     return b200q_mul_mat_id(&q, as->data, (const float *) b->data, (const int32_t *) ids->data, (float *) op->data, ws,
                             ctx->ws_bytes, ctx->stream);
 }
@@ -1320,6 +1329,24 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
                 }
                 i += used - 1;
                 continue;
+            }
+        }
+        if (!no_fuse && node->op == GGML_OP_MUL_MAT_ID && i + 1 < n_nodes && node->src[2]->ne[1] == 1 && cgraph->use_counts) {
+            // decode: the experts' bias rows (ADD_ID behind the matmul, gpt-oss) go into the matmul's epilogue
+            const ggml_tensor * nx = ggml_graph_node(cgraph, i + 1);
+            if (nx->op == GGML_OP_ADD_ID && nx->src[0] == node && nx->src[2] == node->src[2] && supports_elementwise(nx) &&
+                ggml_is_contiguous(nx) && ggml_is_contiguous(node) && nx->src[1]->nb[0] == 4 && nx->src[1]->ne[0] == node->ne[0] &&
+                node_use_count(cgraph, node) == 1 && !(node->flags & GGML_TENSOR_FLAG_OUTPUT) && !node->view_src) {
+                rc = compute_mul_mat_id(ctx, node, nx);
+                if (rc == 0) {
+                    ++i;
+                    continue;
+                }
+                if (rc != 1) {
+                    fprintf(stderr, "ggml-b200: MUL_MAT_ID + ADD_ID (%s) failed (%d): %s\n", node->name, rc, b200q_last_error());
+                    return GGML_STATUS_FAILED;
+                }
+                rc = 0;  // not this shape: the two nodes go out one by one
             }
         }
         if (!no_fuse && node->op == GGML_OP_MUL && node->src[1] && node->src[1]->ne[0] == 1 && node->ne[1] > 1) {
