@@ -109,6 +109,8 @@ struct b200_backend_ctx {
     bool   hoist_ok   = false;
     struct hoist_copy { const void * src = nullptr; size_t bytes = 0; };
     std::vector<hoist_copy> hoist_copies;  // per node of the graph being dispatched
+    // a scratch result whose ONLY reader is a ROPE / SET_ROWS a few nodes on is not copied at all: that operator reads the scratch
+    std::vector<std::pair<const void *, const void *>> redirect;  // (the node's own address, where its values are)
 };
 constexpr size_t HOIST_BYTES = 1u << 20;
 constexpr size_t MAX_CACHED_GRAPHS = 256;
@@ -598,10 +600,22 @@ bool supports_elementwise(const ggml_tensor * op) {
             return false;
     }
 }
+// bt() of an operator's source, following a pending scratch redirect (see b200_backend_ctx::redirect)
+b200q_tensor bt_src(b200_backend_ctx * ctx, const ggml_tensor * t) {
+    b200q_tensor r = bt(t);
+    for (size_t q = ctx->redirect.size(); q-- > 0;) {  // newest first; an entry serves its one reader and goes
+        if (ctx->redirect[q].first == r.data) {
+            r.data = (void *) ctx->redirect[q].second;
+            ctx->redirect.erase(ctx->redirect.begin() + (long) q);
+            break;
+        }
+    }
+    return r;
+}
 int compute_elementwise(b200_backend_ctx * ctx, const ggml_tensor * op) {
     const ggml_tensor * a = op->src[0];
     const ggml_tensor * b = op->src[1];
-    const b200q_tensor  ta = bt(a), td = bt(op);
+    const b200q_tensor  ta = (op->op == GGML_OP_ROPE || op->op == GGML_OP_SET_ROWS) ? bt_src(ctx, a) : bt(a), td = bt(op);
     b200q_tensor        tb{}, tc{};
     if (b) tb = bt(b);
     if (op->src[2]) tc = bt(op->src[2]);
@@ -1286,12 +1300,39 @@ int try_fuse_moe_sum(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int i, int n_
     return j;
 }
 
+// Is the result of node i read by exactly one operator, a ROPE or SET_ROWS within the next nodes, through a chain of
+// single-use views that keep its address (RESHAPE / VIEW at offset 0)?  Then that operator can read the values from the
+// scratch they were computed into and the delivery copy is dropped.
+bool sole_reader_takes_scratch(const ggml_cgraph * cgraph, int i, int n_nodes) {
+    if (!cgraph->use_counts) return false;
+    const ggml_tensor * cur = ggml_graph_node((ggml_cgraph *) cgraph, i);
+    const void *        data = cur->data;
+    if (cur->flags & GGML_TENSOR_FLAG_OUTPUT) return false;
+    for (int hops = 0; hops < 6; ++hops) {
+        if (node_use_count(cgraph, cur) != 1) return false;
+        const ggml_tensor * user = nullptr;
+        for (int j = i + 1; j < n_nodes && j < i + 32 && !user; ++j) {
+            const ggml_tensor * t = ggml_graph_node((ggml_cgraph *) cgraph, j);
+            for (int q = 0; q < GGML_MAX_SRC; ++q) if (t->src[q] == cur) user = t;
+        }
+        if (!user) return false;
+        if (user->op == GGML_OP_RESHAPE || user->op == GGML_OP_VIEW) {
+            if (user->data != data || (user->flags & GGML_TENSOR_FLAG_OUTPUT)) return false;
+            cur = user;
+            continue;
+        }
+        return (user->op == GGML_OP_ROPE || user->op == GGML_OP_SET_ROWS) && user->src[0] == cur && supports_elementwise(user);
+    }
+    return false;
+}
+
 ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
     const int  n_nodes  = ggml_graph_n_nodes(cgraph);
     const bool no_fuse  = getenv("GGML_B200_NO_FUSE") != nullptr;
     std::vector<char> done((size_t) n_nodes, 0);  // nodes that already went out with an earlier list (2: result waits in scratch)
     ctx->packed_act = nullptr;
     ctx->hoist_used = 0;
+    ctx->redirect.clear();
     ctx->hoist_copies.assign((size_t) n_nodes, b200_backend_ctx::hoist_copy{});
     // scratch results live in the head of the workspace: only in graphs where no node needs the workspace for itself (the
     // tensor-core kernel's packed activations, MoE tables, the f32 copy of f16 activations) — decode graphs
@@ -1308,6 +1349,10 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
         if (done[(size_t) i] == 2) {
             const auto & hc = ctx->hoist_copies[(size_t) i];
             if (ctx->packed_act && ranges_overlap(node, ctx->packed_act)) ctx->packed_act = nullptr;
+            if (!no_fuse && sole_reader_takes_scratch(cgraph, i, n_nodes)) {
+                ctx->redirect.emplace_back(node->data, hc.src);
+                continue;
+            }
             B200_CHECK(b200q_memcpy(node->data, hc.src, hc.bytes, B200Q_D2D, ctx->stream));
             continue;
         }
@@ -1366,7 +1411,7 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
             const ggml_tensor * o = j < n_nodes ? ggml_graph_node(cgraph, j) : nullptr;
             if (o && o->op == GGML_OP_SET_ROWS && !done[(size_t) j] && supports_elementwise(node) && supports_elementwise(o) && o->type == node->type &&
                 !touches(o, node) && !ranges_overlap(node, o)) {
-                const b200q_tensor s0 = bt(node->src[0]), x0 = bt(node->src[1]), d0 = bt(node), s1 = bt(o->src[0]), x1 = bt(o->src[1]), d1 = bt(o);
+                const b200q_tensor s0 = bt_src(ctx, node->src[0]), x0 = bt(node->src[1]), d0 = bt(node), s1 = bt_src(ctx, o->src[0]), x1 = bt(o->src[1]), d1 = bt(o);
                 rc = b200q_op_set_rows_pair(&s0, &x0, &d0, &s1, &x1, &d1, ctx->stream);
                 if (rc != 0) {
                     fprintf(stderr, "ggml-b200: set_rows pair (%s) failed (%d): %s\n", node->name, rc, b200q_last_error());

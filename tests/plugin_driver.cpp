@@ -396,10 +396,15 @@ int run_layer(ggml_backend_t be, int type, int n_tokens, int n_past, std::vector
     ggml_tensor * wd = ggml_new_tensor_2d(wc.ctx, wt, D.n_ff, D.n_embd);
     ggml_tensor * an = ggml_new_tensor_1d(wc.ctx, GGML_TYPE_F32, D.n_embd);
     ggml_tensor * fn = ggml_new_tensor_1d(wc.ctx, GGML_TYPE_F32, D.n_embd);
-    ggml_tensor * kc = ggml_new_tensor_2d(wc.ctx, GGML_TYPE_F16, kv_dim, D.n_ctx);
-    ggml_tensor * vc = ggml_new_tensor_2d(wc.ctx, GGML_TYPE_F16, kv_dim, D.n_ctx);
+    ctx_scope kvc(4);  // the KV cache lives in its own buffer: the weights' buffer is marked immutable, as llama.cpp's is
+    ggml_tensor * kc = ggml_new_tensor_2d(kvc.ctx, GGML_TYPE_F16, kv_dim, D.n_ctx);
+    ggml_tensor * vc = ggml_new_tensor_2d(kvc.ctx, GGML_TYPE_F16, kv_dim, D.n_ctx);
     ggml_backend_buffer_t wbuf = ggml_backend_alloc_ctx_tensors(wc.ctx, be);
     if (!wbuf) return -3;
+    ggml_backend_buffer_set_usage(wbuf, GGML_BACKEND_BUFFER_USAGE_WEIGHTS);
+    ggml_backend_buffer_t kvbuf = ggml_backend_alloc_ctx_tensors(kvc.ctx, be);
+    if (!kvbuf) { ggml_backend_buffer_free(wbuf); return -3; }
+    struct kv_guard { ggml_backend_buffer_t b; ~kv_guard() { ggml_backend_buffer_free(b); } } kv_free{ kvbuf };
     lcg rng{ 12345u };
     auto fill_q = [&](ggml_tensor * t, float amp) {
         const int64_t n = ggml_nelements(t);
@@ -440,11 +445,21 @@ int run_layer(ggml_backend_t be, int type, int n_tokens, int n_past, std::vector
     cur = ggml_swiglu_split(c, ggml_mul_mat(c, wg, cur), ggml_mul_mat(c, wu, cur));
     ggml_tensor * res = ggml_add(c, ggml_mul_mat(c, wd, cur), ffn_inp);
     ggml_cgraph * gf = ggml_new_graph(c);
+    // node order as llama.cpp produces it (build_attn: q_cur, k_cur, v_cur are expanded first, then the cache writes,
+    // src/llama-graph.cpp:1451-1463): q, rope(q), k, rope(k), v, set_rows k, set_rows v — the order the plugin's list hoisting,
+    // scratch results and SET_ROWS pair are written for
+    ggml_build_forward_expand(gf, Q);
+    ggml_build_forward_expand(gf, K);
+    ggml_build_forward_expand(gf, V);
     ggml_build_forward_expand(gf, k_store);
     ggml_build_forward_expand(gf, v_store);
     ggml_build_forward_expand(gf, res);
-    ggml_backend_buffer_t cbuf = ggml_backend_alloc_ctx_tensors(cc.ctx, be);
-    int rc = cbuf ? 0 : -4;
+    // intermediate results are placed by ggml-alloc, as in llama.cpp: buffers are REUSED along the graph (a matmul's result may
+    // take the place of a tensor that died a few nodes earlier), which is what the plugin's reordering has to respect
+    for (ggml_tensor * t : { x, pos, idx, mask }) ggml_set_input(t);
+    ggml_set_output(res);
+    ggml_gallocr_t ga = ggml_gallocr_new(ggml_backend_get_default_buffer_type(be));
+    int rc = ga && ggml_gallocr_alloc_graph(ga, gf) ? 0 : -4;
     if (rc == 0) {
         if (unsupported) {
             *unsupported = 0;
@@ -475,7 +490,7 @@ int run_layer(ggml_backend_t be, int type, int n_tokens, int n_past, std::vector
             if (rc == 0) ggml_backend_tensor_get(res, out.data(), 0, ggml_nbytes(res));
         }
     }
-    if (cbuf) ggml_backend_buffer_free(cbuf);
+    if (ga) ggml_gallocr_free(ga);
     ggml_backend_buffer_free(wbuf);
     return rc;
 }
@@ -530,8 +545,12 @@ int run_moe(ggml_backend_t be, int n_tokens, std::vector<float> & out, int * uns
     ggml_tensor * res = parts[0];
     for (int i = 1; i < (int) n_used; ++i) res = ggml_add(c, res, parts[i]);
     ggml_build_forward_expand(gf, res);
-    ggml_backend_buffer_t cbuf = ggml_backend_alloc_ctx_tensors(cc.ctx, be);
-    int rc = cbuf ? 0 : -4;
+    // intermediate results are placed by ggml-alloc, as in llama.cpp: buffers are REUSED along the graph (a matmul's result may
+    // take the place of a tensor that died a few nodes earlier), which is what the plugin's reordering has to respect
+    for (ggml_tensor * t : { x }) ggml_set_input(t);
+    ggml_set_output(res);
+    ggml_gallocr_t ga = ggml_gallocr_new(ggml_backend_get_default_buffer_type(be));
+    int rc = ga && ggml_gallocr_alloc_graph(ga, gf) ? 0 : -4;
     if (rc == 0) {
         if (unsupported) {
             *unsupported = 0;
@@ -551,7 +570,7 @@ int run_moe(ggml_backend_t be, int n_tokens, std::vector<float> & out, int * uns
             if (rc == 0) ggml_backend_tensor_get(res, out.data(), 0, ggml_nbytes(res));
         }
     }
-    if (cbuf) ggml_backend_buffer_free(cbuf);
+    if (ga) ggml_gallocr_free(ga);
     ggml_backend_buffer_free(wbuf);
     return rc;
 }
