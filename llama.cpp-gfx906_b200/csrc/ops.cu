@@ -486,6 +486,20 @@ struct RopeP {
     int   n_dims, neox;
     float theta_scale, freq_scale, ext_factor, attn_factor, corr0, corr1;
 };
+// rope_yarn (ops.cpp:6056-6071) on theta = pos * theta_scale^(i0/2) / freq_factor: cosine and sine of pair ip at position pos
+__device__ __forceinline__ void rope_cos_sin(const RopeP & p, int pos, long long ip, const float * ff, float & c, float & s) {
+    const float theta_extrap = (float) pos * powf(p.theta_scale, (float) ip) / (ff ? ff[ip] : 1.0f);
+    const float theta_interp = p.freq_scale * theta_extrap;
+    float theta = theta_interp, mscale = p.attn_factor;
+    if (p.ext_factor != 0.0f) {
+        const float y    = ((float) ip - p.corr0) / fmaxf(0.001f, p.corr1 - p.corr0);
+        const float ramp = (1.0f - fminf(1.0f, fmaxf(0.0f, y))) * p.ext_factor;
+        theta            = theta_interp * (1.0f - ramp) + theta_extrap * ramp;
+        mscale *= 1.0f + 0.1f * logf(1.0f / p.freq_scale);
+    }
+    c = cosf(theta) * mscale;
+    s = sinf(theta) * mscale;
+}
 template <int TYPE> __global__ void __launch_bounds__(256) rope_kernel(T4 x, const int * pos, const float * ff, T4 d, RopeP p) {
     pdl_grid_sync();
     const long long half = x.ne[0] / 2, n = half * x.ne[1] * x.ne[2] * x.ne[3];
@@ -501,17 +515,8 @@ template <int TYPE> __global__ void __launch_bounds__(256) rope_kernel(T4 x, con
             Elem<TYPE>::st(ds + (i0 + 1) * es, Elem<TYPE>::ld(xs + (i0 + 1) * es));
             continue;
         }
-        // rope_yarn (ops.cpp:6056-6071) on theta = pos * theta_scale^(i0/2) / freq_factor
-        const float theta_extrap = (float) pos[i2] * powf(p.theta_scale, (float) ip) / (ff ? ff[ip] : 1.0f);
-        const float theta_interp = p.freq_scale * theta_extrap;
-        float theta = theta_interp, mscale = p.attn_factor;
-        if (p.ext_factor != 0.0f) {
-            const float y    = ((float) ip - p.corr0) / fmaxf(0.001f, p.corr1 - p.corr0);
-            const float ramp = (1.0f - fminf(1.0f, fmaxf(0.0f, y))) * p.ext_factor;
-            theta            = theta_interp * (1.0f - ramp) + theta_extrap * ramp;
-            mscale *= 1.0f + 0.1f * logf(1.0f / p.freq_scale);
-        }
-        const float c = cosf(theta) * mscale, s = sinf(theta) * mscale;
+        float c, s;
+        rope_cos_sin(p, pos[i2], ip, ff, c, s);
         const long long a0 = p.neox ? ip : i0, a1 = p.neox ? ip + p.n_dims / 2 : i0 + 1;
         const float x0 = Elem<TYPE>::ld(xs + a0 * es), x1 = Elem<TYPE>::ld(xs + a1 * es);
         Elem<TYPE>::st(ds + a0 * es, x0 * c - x1 * s);
@@ -584,6 +589,51 @@ template <int TD> __global__ void __launch_bounds__(256) set_rows_pair_kernel(T4
         const long long row = *(const long long *) (idx.data + i1 * idx.nb[0] + (i2 % idx.ne[1]) * idx.nb[1] + (i3 % idx.ne[2]) * idx.nb[2]);
         const float v = *(const float *) (s.data + i0 * s.nb[0] + i1 * s.nb[1] + i2 * s.nb[2] + i3 * s.nb[3]);
         Elem<TD>::st(d.data + i0 * d.nb[0] + row * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3], v);
+    }
+}
+
+// what follows a decode step's q / k / v matmuls, in one launch (blockIdx.y picks the part): ROPE of q into its own result,
+// ROPE of k stored straight into the K cache rows (the rotated k has no other reader), v stored into the V cache rows.
+// Arithmetic and rounding are those of rope_kernel followed by set_rows_kernel (rotate in f32, one conversion at the store).
+template <int TD> __global__ void __launch_bounds__(256) rope_store_kernel(T4 q, T4 qd, T4 k, const int * pos, const float * ff, RopeP p,
+                                                                            T4 kidx, T4 kd, T4 v, T4 vidx, T4 vd, long long nv) {
+    pdl_grid_sync();
+    if (blockIdx.y == 2) {  // v: a plain SET_ROWS
+        for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (long long) gridDim.x * blockDim.x) {
+            const long long i0 = i % v.ne[0], i1 = i / v.ne[0];
+            const long long row = *(const long long *) (vidx.data + i1 * vidx.nb[0]);
+            Elem<TD>::st(vd.data + i0 * vd.nb[0] + row * vd.nb[1], *(const float *) (v.data + i0 * v.nb[0] + i1 * v.nb[1]));
+        }
+        return;
+    }
+    const bool      store = blockIdx.y == 1;
+    const T4 &      x     = store ? k : q;
+    const long long half = x.ne[0] / 2, n = half * x.ne[1] * x.ne[2];
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
+        const long long ip = i % half, r = i / half, i1 = r % x.ne[1], i2 = r / x.ne[1], i0 = 2 * ip;
+        const char * xs = x.data + i1 * x.nb[1] + i2 * x.nb[2];
+        long long a0 = i0, a1 = i0 + 1;
+        float     y0, y1;
+        if (i0 >= p.n_dims) {
+            y0 = *(const float *) (xs + a0 * 4);
+            y1 = *(const float *) (xs + a1 * 4);
+        } else {
+            float c, s;
+            rope_cos_sin(p, pos[i2], ip, ff, c, s);
+            if (p.neox) { a0 = ip; a1 = ip + p.n_dims / 2; }
+            const float x0 = *(const float *) (xs + a0 * 4), x1 = *(const float *) (xs + a1 * 4);
+            y0 = x0 * c - x1 * s;
+            y1 = x0 * s + x1 * c;
+        }
+        if (store) {  // element (a, head i1) of token i2 is element i1 * ne0 + a of the cache row idx[i2]
+            char * ds = kd.data + *(const long long *) (kidx.data + i2 * kidx.nb[0]) * kd.nb[1] + i1 * x.ne[0] * kd.nb[0];
+            Elem<TD>::st(ds + a0 * kd.nb[0], y0);
+            Elem<TD>::st(ds + a1 * kd.nb[0], y1);
+        } else {
+            char * ds = qd.data + i1 * qd.nb[1] + i2 * qd.nb[2];
+            *(float *) (ds + a0 * 4) = y0;
+            *(float *) (ds + a1 * 4) = y1;
+        }
     }
 }
 
@@ -945,6 +995,52 @@ int b200q_op_set_rows_pair(const b200q_tensor * src0, const b200q_tensor * idx0,
         case B200Q_TYPE_BF16: launch_pdl(set_rows_pair_kernel<B200Q_TYPE_BF16>, g, dim3(256), 0, st, t4(src0), t4(idx0), t4(dst0), n0, t4(src1), t4(idx1), t4(dst1), n1); break;
         default: return ops_fail(B200Q_ENOTSUP, "set_rows_pair: destination type");
     }
+    return launched();
+}
+
+int b200q_op_rope_store(const b200q_tensor * q_src, const b200q_tensor * q_dst, const b200q_tensor * k_src, const b200q_tensor * pos,
+                        const b200q_tensor * freq_factors, const b200q_rope_params * rp, const b200q_tensor * k_idx, const b200q_tensor * k_dst,
+                        const b200q_tensor * v_src, const b200q_tensor * v_idx, const b200q_tensor * v_dst, void * stream) {
+    auto rope_ok = [&](const b200q_tensor * x) {
+        return x && x->type == B200Q_TYPE_F32 && x->nb[0] == 4 && x->ne[0] % 2 == 0 && x->ne[3] == 1 && pos && pos->ne[0] >= x->ne[2];
+    };
+    auto store_ok = [&](long long width, long long rows, const b200q_tensor * idx, const b200q_tensor * d) {
+        return idx && d && idx->type == B200Q_TYPE_I64 && idx->ne[0] == rows && idx->ne[1] == 1 && idx->ne[2] == 1 && d->ne[0] == width &&
+               d->ne[2] == 1 && d->ne[3] == 1;
+    };
+    if (!rp || !rope_ok(q_src) || !rope_ok(k_src) || !q_dst || q_dst->type != B200Q_TYPE_F32 || q_dst->nb[0] != 4 || !same_shape(q_src, q_dst) ||
+        pos->type != B200Q_TYPE_I32 || pos->nb[0] != 4 || q_src->ne[2] != k_src->ne[2] || q_src->ne[0] != k_src->ne[0] ||
+        !store_ok(k_src->ne[0] * k_src->ne[1], k_src->ne[2], k_idx, k_dst) || !v_src || v_src->type != B200Q_TYPE_F32 || v_src->ne[2] != 1 ||
+        v_src->ne[3] != 1 || !store_ok(v_src->ne[0], v_src->ne[1], v_idx, v_dst) || k_dst->type != v_dst->type) {
+        return ops_fail(B200Q_ENOTSUP, "rope_store: f32 q / k [head dim, heads, tokens], f32 v [width, tokens], i64 row indices, caches of one type");
+    }
+    if (rp->mode != B200Q_ROPE_NORMAL && rp->mode != B200Q_ROPE_NEOX) return ops_fail(B200Q_ENOTSUP, "rope_store: only the normal and NeoX modes");
+    if (rp->n_dims <= 0 || rp->n_dims % 2 || rp->n_dims > q_src->ne[0]) return ops_fail(B200Q_EINVAL, "rope_store: n_dims");
+    if (freq_factors && (freq_factors->type != B200Q_TYPE_F32 || freq_factors->ne[0] < rp->n_dims / 2 || freq_factors->nb[0] != 4)) {
+        return ops_fail(B200Q_ENOTSUP, "rope_store: frequency factors");
+    }
+    const long long nq = nelem(q_src) / 2, nk = nelem(k_src) / 2, nv = nelem(v_src);
+    long long most = nq > nk ? nq : nk;
+    if (nv > most) most = nv;
+    if (most == 0) return 0;
+    RopeP p;
+    p.n_dims = rp->n_dims; p.neox = rp->mode == B200Q_ROPE_NEOX;
+    p.theta_scale = powf(rp->freq_base, -2.0f / rp->n_dims);
+    p.freq_scale = rp->freq_scale; p.ext_factor = rp->ext_factor; p.attn_factor = rp->attn_factor;
+    p.corr0 = rp->corr_dims[0]; p.corr1 = rp->corr_dims[1];
+    const float * ff = freq_factors ? (const float *) freq_factors->data : nullptr;
+    const dim3    g((unsigned) grid_for(most, 256), 3);
+    cudaStream_t  st = (cudaStream_t) stream;
+#define B200Q_ROPE_STORE(TD)                                                                                                               \
+    launch_pdl(rope_store_kernel<TD>, g, dim3(256), 0, st, t4(q_src), t4(q_dst), t4(k_src), (const int *) pos->data, ff, p, t4(k_idx), t4(k_dst), \
+               t4(v_src), t4(v_idx), t4(v_dst), nv)
+    switch (k_dst->type) {
+        case B200Q_TYPE_F32:  B200Q_ROPE_STORE(B200Q_TYPE_F32); break;
+        case B200Q_TYPE_F16:  B200Q_ROPE_STORE(B200Q_TYPE_F16); break;
+        case B200Q_TYPE_BF16: B200Q_ROPE_STORE(B200Q_TYPE_BF16); break;
+        default: return ops_fail(B200Q_ENOTSUP, "rope_store: cache type");
+    }
+#undef B200Q_ROPE_STORE
     return launched();
 }
 

@@ -612,6 +612,17 @@ b200q_tensor bt_src(b200_backend_ctx * ctx, const ggml_tensor * t) {
     }
     return r;
 }
+b200q_rope_params rope_params_of(const ggml_tensor * op) {
+    const int32_t *   ip = (const int32_t *) op->op_params;
+    b200q_rope_params rp{};
+    rp.n_dims = ip[1]; rp.mode = ip[2];
+    const int n_ctx_orig = ip[4];
+    float beta_fast, beta_slow;
+    memcpy(&rp.freq_base, ip + 5, 4); memcpy(&rp.freq_scale, ip + 6, 4); memcpy(&rp.ext_factor, ip + 7, 4);
+    memcpy(&rp.attn_factor, ip + 8, 4); memcpy(&beta_fast, ip + 9, 4); memcpy(&beta_slow, ip + 10, 4);
+    ggml_rope_yarn_corr_dims(rp.n_dims, n_ctx_orig, rp.freq_base, beta_fast, beta_slow, rp.corr_dims);
+    return rp;
+}
 int compute_elementwise(b200_backend_ctx * ctx, const ggml_tensor * op) {
     const ggml_tensor * a = op->src[0];
     const ggml_tensor * b = op->src[1];
@@ -631,13 +642,7 @@ int compute_elementwise(b200_backend_ctx * ctx, const ggml_tensor * op) {
         case GGML_OP_SOFT_MAX:
             return b200q_op_soft_max(&ta, b ? &tb : nullptr, op->src[2] ? &tc : nullptr, &td, fp[0], fp[1], ctx->stream);
         case GGML_OP_ROPE: {
-            b200q_rope_params rp{};
-            rp.n_dims = ip[1]; rp.mode = ip[2];
-            const int n_ctx_orig = ip[4];
-            float beta_fast, beta_slow;
-            memcpy(&rp.freq_base, ip + 5, 4); memcpy(&rp.freq_scale, ip + 6, 4); memcpy(&rp.ext_factor, ip + 7, 4);
-            memcpy(&rp.attn_factor, ip + 8, 4); memcpy(&beta_fast, ip + 9, 4); memcpy(&beta_slow, ip + 10, 4);
-            ggml_rope_yarn_corr_dims(rp.n_dims, n_ctx_orig, rp.freq_base, beta_fast, beta_slow, rp.corr_dims);
+            const b200q_rope_params rp = rope_params_of(op);
             return b200q_op_rope(&ta, &tb, op->src[2] ? &tc : nullptr, &td, &rp, ctx->stream);
         }
         case GGML_OP_CPY: case GGML_OP_CONT: case GGML_OP_DUP: return b200q_op_cpy(&ta, &td, ctx->stream);
@@ -1074,6 +1079,13 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph);
 // statistics for tests and tuning (get_proc_address "ggml_backend_b200_graph_stats"): graphs recorded, graphs replayed
 int64_t g_graph_stats[2] = { 0, 0 };
 void    graph_stats(int64_t * recorded, int64_t * replayed) { *recorded = g_graph_stats[0]; *replayed = g_graph_stats[1]; }
+// how often each fusion of graph_dispatch fired ("ggml_backend_b200_fusion_stats": copies up to n counters, returns how many exist)
+enum { FUSE_NORM, FUSE_ATTN, FUSE_ROPE_STORE, FUSE_SET_ROWS_PAIR, FUSE_MOE_SUM, FUSE_ID_BIAS, FUSE_LIST, FUSE_SCRATCH_READ, FUSE_SCRATCH_COPY, FUSE_N };
+int64_t g_fusion_stats[FUSE_N] = {};
+int     fusion_stats(int64_t * out, int n) {
+    for (int i = 0; i < n && i < FUSE_N; ++i) out[i] = g_fusion_stats[i];
+    return FUSE_N;
+}
 
 // everything a launch bakes into its arguments: op, types, shapes, strides, addresses, parameters of every node and source
 void graph_fingerprint(const ggml_cgraph * cgraph, std::vector<uint64_t> & key, bool * capturable) {
@@ -1326,6 +1338,83 @@ bool sole_reader_takes_scratch(const ggml_cgraph * cgraph, int i, int n_nodes) {
     return false;
 }
 
+// ROPE(q) at node i, followed — with nothing in between but views and matmuls that already ran with an earlier list — by
+// ROPE(k) whose only reader is a SET_ROWS (the K cache write) and a second SET_ROWS (the V cache write): llama.cpp's decode
+// step behind the q / k / v matmuls.  All of it goes out as one launch (b200q_op_rope_store) at ROPE(q)'s position: every
+// source is already computed, and the cache rows are written a few nodes early past nodes that do not execute.  Matmul
+// results that wait in the scratch are read from there.  Returns the index behind the group, or 0.
+int try_fuse_rope_store(b200_backend_ctx * ctx, const ggml_cgraph * cgraph, int i, int n_nodes, const std::vector<char> & done, int * rc) {
+    if (!cgraph->use_counts) return 0;
+    const ggml_tensor * rq = ggml_graph_node((ggml_cgraph *) cgraph, i);
+    if (rq->op != GGML_OP_ROPE || !is_f32(rq) || rq->ne[3] != 1 || !supports_elementwise(rq)) return 0;
+    const ggml_tensor * rk = nullptr, * s[2] = { nullptr, nullptr };
+    int hoisted[4], n_hoisted = 0, last = -1;
+    for (int j = i + 1; j < n_nodes && j < i + 24 && last < 0; ++j) {
+        const ggml_tensor * t = ggml_graph_node((ggml_cgraph *) cgraph, j);
+        if (done[(size_t) j] == 2) {
+            if (n_hoisted == 4) return 0;
+            hoisted[n_hoisted++] = j;
+            continue;
+        }
+        if (done[(size_t) j] || noop_node(t)) continue;
+        if (t->op == GGML_OP_ROPE && !rk && !s[0]) { rk = t; continue; }
+        if (t->op == GGML_OP_SET_ROWS && rk && !s[0]) { s[0] = t; continue; }
+        if (t->op == GGML_OP_SET_ROWS && s[0]) { s[1] = t; last = j; continue; }
+        return 0;
+    }
+    if (last < 0) return 0;
+    // which of the two stores takes the rotated k (through single-use views at the same address)?
+    auto reads_rk = [&](const ggml_tensor * st) {
+        const ggml_tensor * t = st->src[0];
+        for (int hops = 0; hops < 4 && t; ++hops) {
+            if (t == rk) return true;
+            if ((t->op != GGML_OP_RESHAPE && t->op != GGML_OP_VIEW) || t->data != rk->data || node_use_count(cgraph, t) != 1 ||
+                (t->flags & GGML_TENSOR_FLAG_OUTPUT)) return false;
+            t = t->src[0];
+        }
+        return false;
+    };
+    const ggml_tensor * sk = reads_rk(s[0]) ? s[0] : reads_rk(s[1]) ? s[1] : nullptr;
+    if (!sk) return 0;
+    const ggml_tensor * sv = sk == s[0] ? s[1] : s[0];
+    if (reads_rk(sv) || node_use_count(cgraph, rk) != 1 || (rk->flags & GGML_TENSOR_FLAG_OUTPUT)) return 0;
+    if (!is_f32(rk) || !supports_elementwise(rk) || !ggml_is_contiguous(rk) || rk->ne[3] != 1 || rk->ne[0] != rq->ne[0] || rk->ne[2] != rq->ne[2] ||
+        memcmp(rk->op_params, rq->op_params, sizeof(rq->op_params)) != 0 || rk->src[1] != rq->src[1] || rk->src[2] != rq->src[2]) return 0;
+    auto store_ok = [&](const ggml_tensor * st, int64_t width, int64_t rows) {
+        const ggml_tensor * a = st->src[0], * x = st->src[1];
+        return supports_elementwise(st) && a->ne[0] == width && a->ne[1] == rows && a->ne[2] == 1 && a->ne[3] == 1 && a->nb[0] == 4 &&
+               x->ne[0] == rows && x->ne[1] == 1 && x->ne[2] == 1 && st->ne[2] == 1 && st->ne[3] == 1;
+    };
+    if (!store_ok(sk, rk->ne[0] * rk->ne[1], rk->ne[2]) || !ggml_is_contiguous(sk->src[0]) || !store_ok(sv, sv->src[0]->ne[0], sv->src[0]->ne[1]) ||
+        sk->type != sv->type || ranges_overlap(sk, sv) || ranges_overlap(rq, sk) || ranges_overlap(rq, sv)) return 0;
+    // where the sources really are: a hoisted matmul of this group whose result still waits in the scratch (k, v)
+    auto producer = [&](const ggml_tensor * t) {  // the node behind views that keep its address
+        for (int hops = 0; hops < 4 && (t->op == GGML_OP_RESHAPE || t->op == GGML_OP_VIEW) && t->src[0] && t->src[0]->data == t->data; ++hops) t = t->src[0];
+        return t;
+    };
+    b200q_tensor tk = bt(rk->src[0]), tv = bt(sv->src[0]);
+    for (int h = 0; h < n_hoisted; ++h) {
+        const ggml_tensor * m  = ggml_graph_node((ggml_cgraph *) cgraph, hoisted[h]);
+        const auto &        hc = ctx->hoist_copies[(size_t) hoisted[h]];
+        if (!sole_reader_takes_scratch(cgraph, hoisted[h], n_nodes)) return 0;  // somebody else waits for it: it needs its delivery copy
+        if (m == producer(rk->src[0])) tk.data = (void *) hc.src;
+        else if (m == producer(sv->src[0])) tv.data = (void *) hc.src;
+        else return 0;
+    }
+    auto hits_q = [&](const b200q_tensor & t, const ggml_tensor * g) {
+        const char * a0 = (const char *) t.data, * a1 = a0 + ggml_nbytes(g), * b0 = (const char *) rq->data, * b1 = b0 + ggml_nbytes(rq);
+        return a0 < b1 && b0 < a1;
+    };
+    if (hits_q(tk, rk->src[0]) || hits_q(tv, sv->src[0])) return 0;
+    const b200q_tensor      tq = bt_src(ctx, rq->src[0]);  // q itself may be behind a redirect of an earlier list
+    const b200q_tensor      td = bt(rq), tp = bt(rq->src[1]), kx = bt(sk->src[1]), kd = bt(sk), vx = bt(sv->src[1]), vd = bt(sv);
+    b200q_tensor            tf{};
+    if (rq->src[2]) tf = bt(rq->src[2]);
+    const b200q_rope_params rp = rope_params_of(rq);
+    *rc = b200q_op_rope_store(&tq, &td, &tk, &tp, rq->src[2] ? &tf : nullptr, &rp, &kx, &kd, &tv, &vx, &vd, ctx->stream);
+    return last + 1;
+}
+
 ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
     const int  n_nodes  = ggml_graph_n_nodes(cgraph);
     const bool no_fuse  = getenv("GGML_B200_NO_FUSE") != nullptr;
@@ -1351,9 +1440,11 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
             if (ctx->packed_act && ranges_overlap(node, ctx->packed_act)) ctx->packed_act = nullptr;
             if (!no_fuse && sole_reader_takes_scratch(cgraph, i, n_nodes)) {
                 ctx->redirect.emplace_back(node->data, hc.src);
+                ++g_fusion_stats[FUSE_SCRATCH_READ];
                 continue;
             }
             B200_CHECK(b200q_memcpy(node->data, hc.src, hc.bytes, B200Q_D2D, ctx->stream));
+            ++g_fusion_stats[FUSE_SCRATCH_COPY];
             continue;
         }
         if (ggml_is_empty(node) || done[(size_t) i]) continue;
@@ -1362,7 +1453,10 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
             ctx->packed_act = nullptr;
         }
         if (!no_lists && list_candidate(node)) {
-            if (compute_list_run(ctx, cgraph, i, n_nodes, done) > 0) continue;
+            if (compute_list_run(ctx, cgraph, i, n_nodes, done) > 0) {
+                ++g_fusion_stats[FUSE_LIST];
+                continue;
+            }
         }
         int rc = 0;
         if (!no_fuse && (node->op == GGML_OP_ADD || node->op == GGML_OP_RMS_NORM)) {
@@ -1372,6 +1466,7 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
                     fprintf(stderr, "ggml-b200: fused norm (%s) failed (%d): %s\n", node->name, rc, b200q_last_error());
                     return GGML_STATUS_FAILED;
                 }
+                ++g_fusion_stats[FUSE_NORM];
                 i += used - 1;
                 continue;
             }
@@ -1384,6 +1479,7 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
                 node_use_count(cgraph, node) == 1 && !(node->flags & GGML_TENSOR_FLAG_OUTPUT) && !node->view_src) {
                 rc = compute_mul_mat_id(ctx, node, nx);
                 if (rc == 0) {
+                    ++g_fusion_stats[FUSE_ID_BIAS];
                     ++i;
                     continue;
                 }
@@ -1401,6 +1497,19 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
                     fprintf(stderr, "ggml-b200: fused MoE combine (%s) failed (%d): %s\n", node->name, rc, b200q_last_error());
                     return GGML_STATUS_FAILED;
                 }
+                ++g_fusion_stats[FUSE_MOE_SUM];
+                i = behind - 1;
+                continue;
+            }
+        }
+        if (!no_fuse && node->op == GGML_OP_ROPE) {
+            const int behind = try_fuse_rope_store(ctx, cgraph, i, n_nodes, done, &rc);
+            if (behind > i) {
+                if (rc != 0) {
+                    fprintf(stderr, "ggml-b200: fused rope + cache store (%s) failed (%d): %s\n", node->name, rc, b200q_last_error());
+                    return GGML_STATUS_FAILED;
+                }
+                ++g_fusion_stats[FUSE_ROPE_STORE];
                 i = behind - 1;
                 continue;
             }
@@ -1417,6 +1526,7 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
                     fprintf(stderr, "ggml-b200: set_rows pair (%s) failed (%d): %s\n", node->name, rc, b200q_last_error());
                     return GGML_STATUS_FAILED;
                 }
+                ++g_fusion_stats[FUSE_SET_ROWS_PAIR];
                 i = j;
                 continue;
             }
@@ -1428,6 +1538,7 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
                     fprintf(stderr, "ggml-b200: fused attention (%s) failed (%d): %s\n", node->name, rc, b200q_last_error());
                     return GGML_STATUS_FAILED;
                 }
+                ++g_fusion_stats[FUSE_ATTN];
                 ctx->packed_act = nullptr;
                 i = behind - 1;
                 continue;
@@ -1580,6 +1691,7 @@ void * reg_get_proc_address(ggml_backend_reg_t, const char * name) {
     if (strcmp(name, "ggml_backend_get_features") == 0) return (void *) get_features;
     if (strcmp(name, "ggml_backend_split_buffer_type") == 0) return (void *) split_buffer_type;  // llama's -sm row
     if (strcmp(name, "ggml_backend_b200_graph_stats") == 0) return (void *) graph_stats;
+    if (strcmp(name, "ggml_backend_b200_fusion_stats") == 0) return (void *) fusion_stats;
     return nullptr;
 }
 

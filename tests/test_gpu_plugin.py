@@ -305,10 +305,28 @@ def test_inprocess_llama_layer_stays_on_device(t, n_tokens, n_past):
     CPU backend's on the same weights, inputs and pre-filled cache (decode, small batch and prompt shapes)."""
     L = _driver()
     nmse, unsup = C.c_double(-1.0), C.c_int(-1)
+    before = _fusion_stats(L)
     rc = L.pd_llama_layer(0, t, n_tokens, n_past, C.byref(nmse), C.byref(unsup))
     assert rc == 0 and unsup.value == 0, (rc, unsup.value)
-    print(f"\n[llama layer] {refs.NAMES[t]} n_tokens={n_tokens} n_past={n_past}: nmse vs CPU backend {nmse.value:.2e}")
+    fired = {k: v - before[k] for k, v in _fusion_stats(L).items()}
+    print(f"\n[llama layer] {refs.NAMES[t]} n_tokens={n_tokens} n_past={n_past}: nmse vs CPU backend {nmse.value:.2e}; fusions {fired}")
     assert 0.0 <= nmse.value <= 1e-3
+    if n_tokens == 1 and not any(os.environ.get(k) for k in ("GGML_B200_NO_FUSE", "GGML_B200_NO_LIST", "GGML_B200_NO_HOIST", "GGML_B200_NO_SCRATCH")):
+        # the decode step is what the fusions are for: they must have fired on the graph the CPU backend was compared with
+        # (two norms, the attention core, q / k / v and gate / up as lists, rope + both cache stores as one launch)
+        assert fired["norm"] >= 2 and fired["attn"] >= 1 and fired["list"] >= 2 and fired["rope_store"] >= 1, fired
+
+
+FUSIONS = ("norm", "attn", "rope_store", "set_rows_pair", "moe_sum", "id_bias", "list", "scratch_read", "scratch_copy")
+
+
+def _fusion_stats(L):
+    """the plugin's counters of how often each graph_dispatch fusion fired (proc address ggml_backend_b200_fusion_stats)"""
+    L.pd_proc_address.restype = C.c_void_p
+    fn = C.CFUNCTYPE(C.c_int, C.POINTER(C.c_int64), C.c_int)(L.pd_proc_address(b"ggml_backend_b200_fusion_stats"))
+    buf = (C.c_int64 * len(FUSIONS))()
+    assert fn(buf, len(FUSIONS)) == len(FUSIONS)
+    return dict(zip(FUSIONS, buf))
 
 
 @pytest.mark.parametrize("n_tokens", [1, 7, 40, 200])
