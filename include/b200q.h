@@ -225,6 +225,13 @@ B200Q_API int b200q_ipc_close(void * dev_ptr);
  *      unless a B200Q_LIST_DEP op lies between them.  Results are bit-reproducible and do not depend on how a list is
  *      composed, launched or sharded (fixed summation order per (type, k)). */
 #define B200Q_LIST_DEP 1u
+/* B200Q_LIST_SWIGLU: the vector this op multiplies is silu(act[i]) * act2[i] (ggml's SWIGLU of two tensors, unary-ops / glu.cu),
+ * computed while the activations are quantized: ffn_gate, ffn_up and ffn_down of a layer are ONE launch with one barrier point
+ * and the GLU node's own result is never written.  Normally together with B200Q_LIST_DEP (act and act2 are results of earlier
+ * ops of the list).  The op's dst must not overlap act or act2.  silu uses the approximate exp and division (2^-21 relative,
+ * far below the int8 step of the quantized vector).  Measured: every CTA evaluates the whole vector behind the barrier point,
+ * which costs more (4.8 us at k = 14336) than a separate GLU launch — the plugin uses it only with GGML_B200_GLU_LIST=1. */
+#define B200Q_LIST_SWIGLU 2u
 typedef struct b200q_list_op {
     int           type;
     int64_t       m, k;   /* dst[m] = W[m][k] . act[k];  m may be 0 (a rank without rows of a small matrix) */
@@ -232,6 +239,7 @@ typedef struct b200q_list_op {
     const float * act;
     float *       dst;
     uint32_t      flags;
+    const float * act2;   /* B200Q_LIST_SWIGLU only, else ignored (NULL) */
 } b200q_list_op;
 /* row split: every result row is also stored into the same place of each peer's dst buffer (peer_delta[i] = this
  * process's mapping of the i-th OTHER rank's dst buffer minus this GPU's own, ascending rank order), and every barrier

@@ -69,7 +69,7 @@ class MulMatIdArgs(C.Structure):
 
 class ListOp(C.Structure):
     _fields_ = [("type", C.c_int), ("m", C.c_int64), ("k", C.c_int64), ("w", C.c_void_p), ("act", C.c_void_p),
-                ("dst", C.c_void_p), ("flags", C.c_uint32)]
+                ("dst", C.c_void_p), ("flags", C.c_uint32), ("act2", C.c_void_p)]
 
 
 class ListPeers(C.Structure):
@@ -77,6 +77,7 @@ class ListPeers(C.Structure):
 
 
 LIST_DEP = 1
+LIST_SWIGLU = 2
 
 
 class GetRowsArgs(C.Structure):
@@ -356,19 +357,24 @@ class MatmulList:
     """A run of n = 1 ggml_mul_mat nodes executed by ONE persistent kernel launch (b200q_list_*): ``ops`` is a sequence of
     (w: QTensor [m, k], act: f32 cuda tensor [k], dst: f32 cuda tensor [m] or a raw device address, dep: bool).  ``dep``
     = the op's activations are produced by earlier ops of the list (the kernel waits for all of them, on every GPU of a
-    row split).  ``peers`` = (rank, world, peer_deltas, sync_ptrs) for row split (see include/b200q.h)."""
+    row split).  A fifth member ``act2`` makes the op read silu(act) * act2 (B200Q_LIST_SWIGLU: ffn_down behind ffn_gate and
+    ffn_up).  ``peers`` = (rank, world, peer_deltas, sync_ptrs) for row split (see include/b200q.h)."""
 
     def __init__(self, ops, peers=None):
         torch = _torch()
         self._keep = []
         arr = (ListOp * len(ops))()
-        for i, (w, act, dst, dep) in enumerate(ops):
+        for i, op in enumerate(ops):
+            w, act, dst, dep = op[:4]
+            act2 = op[4] if len(op) > 4 else None
+            assert act2 is None or (act2.dtype == torch.float32 and act2.is_cuda and act2.is_contiguous() and act2.numel() == w.k)
             assert act.dtype == torch.float32 and act.is_cuda and act.is_contiguous() and act.numel() == w.k
             dptr = dst if isinstance(dst, int) else dst.data_ptr()
             if not isinstance(dst, int):
                 assert dst.dtype == torch.float32 and dst.is_cuda and dst.is_contiguous() and dst.numel() == w.m
-            arr[i] = ListOp(w.qtype, w.m, w.k, w.data.data_ptr() if w.m else None, act.data_ptr(), dptr, LIST_DEP if dep else 0)
-            self._keep.append((w, act, dst))
+            arr[i] = ListOp(w.qtype, w.m, w.k, w.data.data_ptr() if w.m else None, act.data_ptr(), dptr,
+                            (LIST_DEP if dep else 0) | (LIST_SWIGLU if act2 is not None else 0), act2.data_ptr() if act2 is not None else None)
+            self._keep.append((w, act, dst, act2))
         pp = None
         if peers is not None:
             rank, world, deltas, syncs = peers

@@ -508,7 +508,7 @@ struct ListSegment {
 int list_smem_plan(int n_ops, int n_gens, long long act_stride, int max_smem, ListParams & p) {
     p.off_ops    = 8 * LIST_MAX_SLOTS + 16;  // behind the ring barriers and the barrier-point counters (gemv_list.cu)
     p.off_gens   = p.off_ops + n_ops * (int) sizeof(ListOp);
-    p.off_act    = round_up(p.off_gens + n_gens * 16, 128);
+    p.off_act    = round_up(p.off_gens + n_gens * (int) sizeof(ListGen), 128);
     p.act_stride = (int) act_stride;
     const long long ring0 = round_up(p.off_act + 2 * (int) act_stride, 128);
     p.off_ring   = (int) ring0;
@@ -1220,7 +1220,7 @@ int list_plan(const b200q_list_op * ops, int n_ops, int world, int sms, int max_
     ListSegment  cur;
     long long    cur_stride = 0;
     long long    units      = 0;
-    const float * prev_act  = nullptr;
+    const float * prev_act  = nullptr, * prev_act2 = nullptr;
     int           prev_q    = -1;
     std::vector<long long> op_units;  // units of every op of the current launch
     auto close = [&]() {
@@ -1247,7 +1247,7 @@ int list_plan(const b200q_list_op * ops, int n_ops, int world, int sms, int max_
         segs.push_back(std::move(cur));
         cur = ListSegment{};
         op_units.clear();
-        cur_stride = 0; units = 0; prev_act = nullptr; prev_q = -1;
+        cur_stride = 0; units = 0; prev_act = prev_act2 = nullptr; prev_q = -1;
     };
     for (int i = 0; i < n_ops; ++i) {
         const b200q_list_op & o = ops[i];
@@ -1256,7 +1256,9 @@ int list_plan(const b200q_list_op * ops, int n_ops, int world, int sms, int max_
         if (o.m < 0 || o.m > (1 << 30) || !o.act || ((uintptr_t) o.act & 15) || ((uintptr_t) o.w & 15) || (o.m && (!o.w || !o.dst))) {
             return fail(B200Q_EINVAL, "list: op %d: bad pointer / alignment / m", i);
         }
-        const bool new_gen = o.act != prev_act || g.qmode != prev_q || (o.flags & B200Q_LIST_DEP) || cur.gens.empty();
+        const float * act2 = (o.flags & B200Q_LIST_SWIGLU) ? o.act2 : nullptr;
+        if ((o.flags & B200Q_LIST_SWIGLU) && (!act2 || ((uintptr_t) act2 & 15))) return fail(B200Q_EINVAL, "list: op %d: B200Q_LIST_SWIGLU needs an aligned act2", i);
+        const bool new_gen = o.act != prev_act || act2 != prev_act2 || g.qmode != prev_q || (o.flags & B200Q_LIST_DEP) || cur.gens.empty();
         // does the op still fit this launch (tables + two activation images + >= LIST_MIN_SLOTS ring slots)?
         const long long stride = std::max<long long>(cur_stride, round_up((int) g.image_bytes, 128));
         ListParams      probe{};
@@ -1274,6 +1276,8 @@ int list_plan(const b200q_list_op * ops, int n_ops, int world, int sms, int max_
             gg.act   = o.act;
             gg.nsb   = (uint16_t) g.nsb;
             gg.qmode = (uint8_t) g.qmode;
+            gg.xform = act2 ? 1 : 0;
+            gg.act2  = act2;
             // the first generation of a launch follows a kernel boundary (and, in a row split, the previous launch's final
             // barrier point): no wait needed
             gg.wait  = (o.flags & B200Q_LIST_DEP) && !first_of_launch ? 1 : 0;
@@ -1288,7 +1292,7 @@ int list_plan(const b200q_list_op * ops, int n_ops, int world, int sms, int max_
         cur.ops.push_back(r);
         op_units.push_back((o.m + (1ll << g.rps_log2) - 1) >> g.rps_log2);
         units += op_units.back();
-        prev_act = o.act; prev_q = g.qmode;
+        prev_act = o.act; prev_act2 = act2; prev_q = g.qmode;
     }
     close();
     return 0;

@@ -158,7 +158,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
             asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(tab + 16u * i), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
         }
         const int4 * sg = (const int4 *) p.gens;
-        for (int i = threadIdx.x; i < p.n_gens; i += NTHREADS) {
+        for (int i = threadIdx.x; i < p.n_gens * 2; i += NTHREADS) {
             const int4 v = __ldg(sg + i);
             asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(gtab + 16u * i), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
         }
@@ -266,7 +266,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
     ActLayout al{};
     uint32_t  abase = 0;
     auto gen_layout = [&](int g, const float *& act, int & qmode, int & wait, int & bp) {
-        const int4 gi  = lds128(gtab + 16u * (uint32_t) g);
+        const int4 gi  = lds128(gtab + 32u * (uint32_t) g);
         act            = (const float *) (((unsigned long long) (uint32_t) gi.y << 32) | (uint32_t) gi.x);
         const int nsb  = (int) ((uint32_t) gi.z & 0xffffu);
         qmode          = (int) (((uint32_t) gi.z >> 16) & 0xffu);
@@ -295,7 +295,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
             gen_layout(g, act, qmode, wait, bp);
             if (g >= 2) named_bar_sync(BAR_FREE + (g & 1), NTHREADS);  // the compute warps are done with generation g - 2
             if (wait) named_bar_sync(BAR_BPDONE, NTHREADS);            // ... and have passed the barrier point in front of g
-            if (qmode == 0) quantize_act<LIST_QWARPS>(al, act, abase, qw, lane);
+            const int4 gx = lds128(gtab + 32u * (uint32_t) g + 16u);  // xform (upper half of the record's last word) and its second vector
+            if (((uint32_t) lds32(gtab + 32u * (uint32_t) g + 12u) >> 16) == 1u) {
+                const ActSwiglu src{ act, (const float *) (((unsigned long long) (uint32_t) gx.y << 32) | (uint32_t) gx.x) };
+                if (qmode == 0) quantize_act_from<LIST_QWARPS>(al, src, abase, qw, lane);
+                else if (qmode == 1) quantize_act32_from<false, LIST_QWARPS>(al, src, abase, qw, lane);
+                else quantize_act32_from<true, LIST_QWARPS>(al, src, abase, qw, lane);
+            } else if (qmode == 0) quantize_act<LIST_QWARPS>(al, act, abase, qw, lane);
             else if (qmode == 1) quantize_act32<false, LIST_QWARPS>(al, act, abase, qw, lane);
             else quantize_act32<true, LIST_QWARPS>(al, act, abase, qw, lane);
             named_bar_arrive(BAR_FULL + (g & 1), NTHREADS);

@@ -41,15 +41,17 @@ struct ListOp {  // 48 bytes; the table lives in shared memory during the launch
 };
 static_assert(sizeof(ListOp) == 48, "ListOp is 48 bytes");
 
-struct ListGen {         // 16 bytes: one activation vector, quantized once per CTA into shared memory
+struct ListGen {         // 32 bytes: one activation vector, quantized once per CTA into shared memory
     const float * act;   // [k] f32, 16-byte aligned
     uint16_t      nsb;   // k / (256 | 32)
     uint8_t       qmode; // 0: per-256 (K-quant partners), 1: per-32, 2: per-32 interleaved (mxfp4)
     uint8_t       wait;  // 1: barrier point before this generation (every earlier op complete on every CTA and GPU)
     uint16_t      bp;    // 1-based index of that barrier point within the launch
-    uint16_t      pad;
+    uint16_t      xform; // 0: the vector is act; 1: silu(act[i]) * act2[i] (B200Q_LIST_SWIGLU)
+    const float * act2;
+    uint64_t      pad;
 };
-static_assert(sizeof(ListGen) == 16, "ListGen is 16 bytes");
+static_assert(sizeof(ListGen) == 32, "ListGen is 32 bytes");
 
 // words of the 256-byte sync block (device memory, zero-initialised once)
 // PROGRESS / EXIT: CTAs of this launch that passed the current barrier point / left (re-armed by the last one);

@@ -59,7 +59,33 @@ __device__ __forceinline__ int dp2a_hi_ss(int a, int b, int c) {
 //   bs16: 16 x int16 at off_bs16 + 32 s              (sums of q over 16 values)
 //   bs32:  8 x int16 at off_bs32 + 16 s              (sums over 32 values)
 // One warp per super-block per step; lane l holds values 8l .. 8l+7 (coalesced 1 KB per warp).
+// where the eight values of a lane come from: the vector itself, or silu(a) * b of two vectors (the SWIGLU in front of ffn_down
+// folded into the quantization, same expression as ops.cu's glu_kernel)
+struct ActPlain {
+    const float * a;
+    __device__ __forceinline__ void operator()(size_t i, float4 & x0, float4 & x1) const {
+        const float4 * src = (const float4 *) (a + i);
+        x0 = __ldcg(src);
+        x1 = __ldcg(src + 1);
+    }
+};
+struct ActSwiglu {
+    const float * a, * b;
+    // every CTA evaluates the whole vector with its four quantizer warps, nothing to overlap with behind the barrier point: the
+    // IEEE division and expf cost 9.5 us per 14336 values, the approximate forms (2^-21 relative, far below the int8 step) 2 us
+    static __device__ __forceinline__ float f(float x, float g) { return __fdividef(x, 1.0f + __expf(-x)) * g; }
+    __device__ __forceinline__ void operator()(size_t i, float4 & x0, float4 & x1) const {
+        const float4 * sa = (const float4 *) (a + i), * sg = (const float4 *) (b + i);
+        const float4   a0 = __ldcg(sa), a1 = __ldcg(sa + 1), g0 = __ldcg(sg), g1 = __ldcg(sg + 1);
+        x0 = make_float4(f(a0.x, g0.x), f(a0.y, g0.y), f(a0.z, g0.z), f(a0.w, g0.w));
+        x1 = make_float4(f(a1.x, g1.x), f(a1.y, g1.y), f(a1.z, g1.z), f(a1.w, g1.w));
+    }
+};
+template <int NWQ = NW, class P, class L> __device__ __forceinline__ void quantize_act_from(const P & p, const L & load, uint32_t sb, int warp, int lane);
 template <int NWQ = NW, class P> __device__ __forceinline__ void quantize_act(const P & p, const float * act, uint32_t sb, int warp, int lane) {
+    quantize_act_from<NWQ>(p, ActPlain{ act }, sb, warp, lane);
+}
+template <int NWQ, class P, class L> __device__ __forceinline__ void quantize_act_from(const P & p, const L & load, uint32_t sb, int warp, int lane) {
     constexpr int QB = 4;
     for (int s0 = warp; s0 < p.nsb; s0 += NWQ * QB) {
         float4 x[QB][2];
@@ -67,9 +93,7 @@ template <int NWQ = NW, class P> __device__ __forceinline__ void quantize_act(co
         for (int b = 0; b < QB; ++b) {
             const int s = s0 + b * NWQ;
             if (s < p.nsb) {
-                const float4 * src = (const float4 *) (act + (size_t) s * 256 + lane * 8);
-                x[b][0] = __ldcg(src);
-                x[b][1] = __ldcg(src + 1);
+                load((size_t) s * 256 + lane * 8, x[b][0], x[b][1]);
             } else {
                 x[b][0] = x[b][1] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
@@ -336,17 +360,17 @@ template <> struct SbDot<T_Q6_K> {
 // One warp per 256 values per step; lane l holds values 8l .. 8l+7, 4 lanes per block.
 // ILV (mxfp4): the 8 words of a block are stored as (e, e+16, e+1, e+17) for e = 0, 2, .. 14 — the order in which a 16-bit
 // slice of the packed nibbles (lo(qs[e]), hi(qs[e]), lo(qs[e+1]), hi(qs[e+1])) indexes a PRMT table look-up
+template <bool ILV, int NWQ = NW, class P, class L> __device__ __forceinline__ void quantize_act32_from(const P & p, const L & load, uint32_t sb, int warp, int lane);
 template <bool ILV, int NWQ = NW, class P> __device__ __forceinline__ void quantize_act32(const P & p, const float * act, uint32_t sb, int warp, int lane) {
+    quantize_act32_from<ILV, NWQ>(p, ActPlain{ act }, sb, warp, lane);
+}
+template <bool ILV, int NWQ, class P, class L> __device__ __forceinline__ void quantize_act32_from(const P & p, const L & load, uint32_t sb, int warp, int lane) {
     const int nb = p.nsb;  // 32-element blocks per row
     for (int g = warp; g * 8 < nb; g += NWQ) {
         const int  b     = g * 8 + (lane >> 2);
         const bool valid = b < nb;  // uniform over the 4 lanes of a block
         float4     x0 = make_float4(0.f, 0.f, 0.f, 0.f), x1 = x0;
-        if (valid) {
-            const float4 * src = (const float4 *) (act + (size_t) g * 256 + lane * 8);
-            x0 = __ldcg(src);
-            x1 = __ldcg(src + 1);
-        }
+        if (valid) load((size_t) g * 256 + lane * 8, x0, x1);
         const float v[8] = { x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w };
         float amax = 0.0f;
 #pragma unroll

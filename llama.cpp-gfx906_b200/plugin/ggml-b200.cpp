@@ -985,10 +985,21 @@ bool touches(const ggml_tensor * node, const ggml_tensor * t) {  // does `node` 
     for (int j = 0; j < GGML_MAX_SRC; ++j) if (node->src[j] && ranges_overlap(node->src[j], t)) return true;
     return false;
 }
+int32_t node_use_count(const ggml_cgraph * cgraph, const ggml_tensor * t);
+// how often each fusion of graph_dispatch fired ("ggml_backend_b200_fusion_stats": copies up to n counters, returns how many exist)
+enum { FUSE_NORM, FUSE_ATTN, FUSE_ROPE_STORE, FUSE_SET_ROWS_PAIR, FUSE_MOE_SUM, FUSE_ID_BIAS, FUSE_LIST, FUSE_SCRATCH_READ, FUSE_SCRATCH_COPY, FUSE_GLU_LIST, FUSE_N };
+int64_t g_fusion_stats[FUSE_N] = {};
+int     fusion_stats(int64_t * out, int n) {
+    for (int i = 0; i < n && i < FUSE_N; ++i) out[i] = g_fusion_stats[i];
+    return FUSE_N;
+}
 int compute_list_run(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int first, int n_nodes, std::vector<char> & done) {
     std::vector<b200q_list_op> ops;
-    std::vector<int>           members, skipped;
+    std::vector<int>           members, skipped, absorbed;
     std::vector<void *>        scratch_of;
+    // measured (tools/ffn_list_bench.py, llama-bench): every CTA evaluating the whole 14336-value SWIGLU behind the barrier point costs
+    // 4.8 us per layer, a separate GLU launch overlapped by programmatic dependent launch 3: tg128 409 -> 392 t/s.  Opt-in only.
+    static const bool glu_list = getenv("GGML_B200_GLU_LIST") != nullptr && getenv("GGML_B200_NO_FUSE") == nullptr;
     const size_t               hoist_mark = ctx->hoist_used;
     static const bool no_hoist   = getenv("GGML_B200_NO_HOIST") != nullptr;
     static const bool no_scratch = getenv("GGML_B200_NO_SCRATCH") != nullptr;
@@ -1000,9 +1011,28 @@ int compute_list_run(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int first, in
             skipped.push_back(i);
             continue;
         }
+        // ffn_down behind SWIGLU(ffn_gate, ffn_up), both of them members of this run: the GLU is computed while the activations
+        // are quantized (B200Q_LIST_SWIGLU) and its node, which nobody else reads, never runs
+        const ggml_tensor * glu = nullptr;
+        if (glu_list && !skipped.empty() && cgraph->use_counts) {
+            const ggml_tensor * g = ggml_graph_node(cgraph, skipped.back());
+            const auto member_result = [&](const ggml_tensor * x) {
+                for (size_t q = 0; x && q < members.size(); ++q) if (ggml_graph_node(cgraph, members[q]) == x && !scratch_of[q]) return true;
+                return false;
+            };
+            if (g->op == GGML_OP_GLU && ggml_get_glu_op(g) == GGML_GLU_OP_SWIGLU && g->src[1] && t->src[1] == g && supports_elementwise(g) &&
+                member_result(g->src[0]) && member_result(g->src[1]) && ggml_is_contiguous(g->src[0]) && ggml_is_contiguous(g->src[1]) &&
+                node_use_count(cgraph, g) == 1 && !(g->flags & GGML_TENSOR_FLAG_OUTPUT) && !ranges_overlap(t, g->src[0]) && !ranges_overlap(t, g->src[1]) &&
+                !(((uintptr_t) g->src[0]->data | (uintptr_t) g->src[1]->data) & 15)) {
+                glu = g;
+                absorbed.push_back(skipped.back());
+                skipped.pop_back();
+            }
+        }
         void * scratch = nullptr;
         if (!skipped.empty()) {
             bool ok = false, aliased = false;
+            ok = glu != nullptr;
             for (int mi : members) ok = ok || ggml_graph_node(cgraph, mi)->src[1]->data == t->src[1]->data;  // the vector is ready
             for (int si : skipped) ok = ok && !ranges_overlap(ggml_graph_node(cgraph, si), t->src[1]);      // ... and stays untouched
             for (int si : skipped) aliased = aliased || touches(ggml_graph_node(cgraph, si), t);
@@ -1018,6 +1048,10 @@ int compute_list_run(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int first, in
         b200q_list_op o{};
         o.type = (int) t->src[0]->type; o.m = t->src[0]->ne[1]; o.k = t->src[0]->ne[0];
         o.w = t->src[0]->data; o.act = (const float *) t->src[1]->data; o.dst = scratch ? (float *) scratch : (float *) t->data;
+        if (glu) {
+            o.act = (const float *) glu->src[0]->data; o.act2 = (const float *) glu->src[1]->data;
+            o.flags |= B200Q_LIST_SWIGLU;
+        }
         scratch_of.push_back(scratch);
         const char * a0 = (const char *) o.act, * a1 = a0 + o.k * 4;
         for (const b200q_list_op & e : ops) {  // reads what an earlier op of the run writes?
@@ -1037,6 +1071,7 @@ int compute_list_run(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int first, in
         key.push_back(o.type); key.push_back(o.m); key.push_back(o.k);
         key.push_back((int64_t) (uintptr_t) o.w); key.push_back((int64_t) (uintptr_t) o.act);
         key.push_back((int64_t) (uintptr_t) o.dst * 2 + (o.flags & B200Q_LIST_DEP ? 1 : 0));
+        if (o.flags & B200Q_LIST_SWIGLU) key.push_back((int64_t) (uintptr_t) o.act2);
     }
     auto it = ctx->lists.find(key);
     if (it == ctx->lists.end()) {
@@ -1072,6 +1107,8 @@ int compute_list_run(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int first, in
             ctx->hoist_copies[(size_t) mi].bytes = (size_t) ggml_graph_node(cgraph, mi)->src[0]->ne[1] * sizeof(float);
         }
     }
+    for (int ai : absorbed) done[(size_t) ai] = 1;
+    g_fusion_stats[FUSE_GLU_LIST] += (int64_t) absorbed.size();
     return (int) members.size();
 }
 
@@ -1079,13 +1116,6 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph);
 // statistics for tests and tuning (get_proc_address "ggml_backend_b200_graph_stats"): graphs recorded, graphs replayed
 int64_t g_graph_stats[2] = { 0, 0 };
 void    graph_stats(int64_t * recorded, int64_t * replayed) { *recorded = g_graph_stats[0]; *replayed = g_graph_stats[1]; }
-// how often each fusion of graph_dispatch fired ("ggml_backend_b200_fusion_stats": copies up to n counters, returns how many exist)
-enum { FUSE_NORM, FUSE_ATTN, FUSE_ROPE_STORE, FUSE_SET_ROWS_PAIR, FUSE_MOE_SUM, FUSE_ID_BIAS, FUSE_LIST, FUSE_SCRATCH_READ, FUSE_SCRATCH_COPY, FUSE_N };
-int64_t g_fusion_stats[FUSE_N] = {};
-int     fusion_stats(int64_t * out, int n) {
-    for (int i = 0; i < n && i < FUSE_N; ++i) out[i] = g_fusion_stats[i];
-    return FUSE_N;
-}
 
 // everything a launch bakes into its arguments: op, types, shapes, strides, addresses, parameters of every node and source
 void graph_fingerprint(const ggml_cgraph * cgraph, std::vector<uint64_t> & key, bool * capturable) {

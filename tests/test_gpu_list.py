@@ -186,3 +186,49 @@ def test_long_list_is_cut_into_several_launches():
     short.launch()
     torch.cuda.synchronize()
     assert torch.equal(a, d1)
+
+
+@pytest.mark.parametrize("t,td", [(refs.Q4_K, refs.Q4_K), (refs.Q4_K, refs.Q6_K), (refs.Q8_0, refs.Q8_0), (refs.MXFP4, refs.MXFP4)],
+                         ids=lambda t: refs.NAMES[t])
+@pytest.mark.parametrize("dim,ff", [(1024, 2816), (4096, 14336)])
+def test_ffn_as_one_list_with_swiglu(t, td, dim, ff):
+    """ffn_gate, ffn_up and ffn_down of a layer as ONE launch: the third op reads silu(gate) * up (B200Q_LIST_SWIGLU, computed
+    while the activations are quantized, behind one barrier point).  Equals gate / up as a list, torch's f32 silu(g) * u written
+    out, and down as its own list — to the last ulp of expf (the separate path goes through torch here; the plugin's GLU kernel
+    uses the same expression) — and the CPU path on the same intermediate vector; repeated launches and graph replay agree."""
+    import b200q
+    import torch
+    if ff % refs.BLCK[td][0] or dim % refs.BLCK[t][0]:
+        pytest.skip("k not a multiple of the block size")
+    wg, wgt = _mk(t, ff, dim, seed=901)
+    wu, wut = _mk(t, ff, dim, seed=902)
+    wd, wdt = _mk(td, dim, ff, seed=903)
+    x = torch.from_numpy(refs.uniform_weights(1, dim, seed=904)).cuda().view(-1)
+    g, u, out = torch.zeros(ff, device="cuda"), torch.zeros(ff, device="cuda"), torch.zeros(dim, device="cuda")
+    lst = b200q.MatmulList([(wgt, x, g, False), (wut, x, u, False), (wdt, g, out, True, u)])
+    assert lst.n_launches == 1 and lst.n_barrier_points == 1
+    lst.launch()
+    torch.cuda.synchronize()
+    # the separate path
+    g2, u2, out2 = torch.zeros(ff, device="cuda"), torch.zeros(ff, device="cuda"), torch.zeros(dim, device="cuda")
+    _run_list([(wgt, x, g2, False), (wut, x, u2, False)])
+    assert torch.equal(g, g2) and torch.equal(u, u2)
+    h = (g2 / (1.0 + torch.exp(-g2)) * u2).contiguous()
+    _run_list([(wdt, h, out2, False)])
+    # (the fused silu uses the approximate exp / division: an int8 step of the quantized vector may flip here and there)
+    assert refs.nmse(out.cpu().numpy().reshape(1, -1), out2.cpu().numpy().reshape(1, -1)) <= 1e-6
+    want = _cpu(td, wd, h.cpu().numpy().reshape(1, ff))
+    assert refs.nmse(out.cpu().numpy().reshape(1, -1), want) <= MAX_NMSE
+    first = out.clone()
+    for it in range(5):
+        g.fill_(float(it)); u.fill_(-1.0); out.fill_(float("nan"))
+        lst.launch()
+        torch.cuda.synchronize()
+        assert torch.equal(out, first), it
+    gr = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(gr):
+        lst.launch()
+    out.fill_(float("nan"))
+    gr.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, first)

@@ -317,7 +317,7 @@ def test_inprocess_llama_layer_stays_on_device(t, n_tokens, n_past):
         assert fired["norm"] >= 2 and fired["attn"] >= 1 and fired["list"] >= 2 and fired["rope_store"] >= 1, fired
 
 
-FUSIONS = ("norm", "attn", "rope_store", "set_rows_pair", "moe_sum", "id_bias", "list", "scratch_read", "scratch_copy")
+FUSIONS = ("norm", "attn", "rope_store", "set_rows_pair", "moe_sum", "id_bias", "list", "scratch_read", "scratch_copy", "glu_list")
 
 
 def _fusion_stats(L):
