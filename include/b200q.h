@@ -349,12 +349,14 @@ B200Q_API int b200q_op_set_rows_pair(const b200q_tensor * src0, const b200q_tens
 /* what follows the q / k / v matmuls of a decode step, in one launch: ROPE(q_src) -> q_dst; ROPE(k_src) stored into the rows
  * k_idx of the K cache k_dst (the rotated k has no other reader: llama.cpp emits ROPE, RESHAPE to 2-D, SET_ROWS); v_src stored into
  * the rows v_idx of v_dst.  q / k f32 [head dim, heads, tokens], v f32 [width, tokens], both ROPEs with the same positions,
- * frequency factors and parameters; i64 indices [tokens]; caches [width, rows] of one type (f32 / f16 / bf16).  Values and
- * rounding are those of b200q_op_rope followed by b200q_op_set_rows (rope.cu, set-rows.cu). */
+ * frequency factors and parameters; i64 indices [tokens]; caches [width, rows] of one type (f32 / f16 / bf16).  q_bias / k_bias /
+ * v_bias (NULL: none): f32 vectors of a token's width added to the source first — the ADD nodes models with attention biases
+ * (gpt-oss, Qwen2) put between the matmul and the ROPE / the store.  Values and rounding are those of the separate operators
+ * (binbcast.cu, rope.cu, set-rows.cu). */
 B200Q_API int b200q_op_rope_store(const b200q_tensor * q_src, const b200q_tensor * q_dst, const b200q_tensor * k_src, const b200q_tensor * pos,
                                   const b200q_tensor * freq_factors, const b200q_rope_params * rp, const b200q_tensor * k_idx,
                                   const b200q_tensor * k_dst, const b200q_tensor * v_src, const b200q_tensor * v_idx, const b200q_tensor * v_dst,
-                                  void * stream);
+                                  const b200q_tensor * q_bias, const b200q_tensor * k_bias, const b200q_tensor * v_bias, void * stream);
 
 /* ---- expert-parallel MUL_MAT_ID across the GPUs of one box (NOT in the reference, which asserts that expert tensors are
  *      never split, ggml-cuda.cu:2094).  Experts are sharded by id, activations and routing are replicated: every rank runs

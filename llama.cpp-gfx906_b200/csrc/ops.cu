@@ -596,32 +596,37 @@ template <int TD> __global__ void __launch_bounds__(256) set_rows_pair_kernel(T4
 // ROPE of k stored straight into the K cache rows (the rotated k has no other reader), v stored into the V cache rows.
 // Arithmetic and rounding are those of rope_kernel followed by set_rows_kernel (rotate in f32, one conversion at the store).
 template <int TD> __global__ void __launch_bounds__(256) rope_store_kernel(T4 q, T4 qd, T4 k, const int * pos, const float * ff, RopeP p,
-                                                                            T4 kidx, T4 kd, T4 v, T4 vidx, T4 vd, long long nv) {
+                                                                            T4 kidx, T4 kd, T4 v, T4 vidx, T4 vd, long long nv,
+                                                                            const float * qb, const float * kb, const float * vb, long long vb_len) {
     pdl_grid_sync();
-    if (blockIdx.y == 2) {  // v: a plain SET_ROWS
+    if (blockIdx.y == 2) {  // v: a plain SET_ROWS (+ the bias row: element e of a token is element (flat index % width) of the bias)
         for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (long long) gridDim.x * blockDim.x) {
             const long long i0 = i % v.ne[0], i1 = i / v.ne[0];
             const long long row = *(const long long *) (vidx.data + i1 * vidx.nb[0]);
-            Elem<TD>::st(vd.data + i0 * vd.nb[0] + row * vd.nb[1], *(const float *) (v.data + i0 * v.nb[0] + i1 * v.nb[1]));
+            float x = *(const float *) (v.data + i0 * v.nb[0] + i1 * v.nb[1]);
+            if (vb) x += vb[i % vb_len];
+            Elem<TD>::st(vd.data + i0 * vd.nb[0] + row * vd.nb[1], x);
         }
         return;
     }
     const bool      store = blockIdx.y == 1;
     const T4 &      x     = store ? k : q;
+    const float *   bias  = store ? kb : qb;
     const long long half = x.ne[0] / 2, n = half * x.ne[1] * x.ne[2];
     for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long) gridDim.x * blockDim.x) {
         const long long ip = i % half, r = i / half, i1 = r % x.ne[1], i2 = r / x.ne[1], i0 = 2 * ip;
         const char * xs = x.data + i1 * x.nb[1] + i2 * x.nb[2];
         long long a0 = i0, a1 = i0 + 1;
-        float     y0, y1;
-        if (i0 >= p.n_dims) {
-            y0 = *(const float *) (xs + a0 * 4);
-            y1 = *(const float *) (xs + a1 * 4);
-        } else {
+        if (i0 < p.n_dims && p.neox) { a0 = ip; a1 = ip + p.n_dims / 2; }
+        float x0 = *(const float *) (xs + a0 * 4), x1 = *(const float *) (xs + a1 * 4);
+        if (bias) {  // the ADD in front of the ROPE (q / k / v biases): one rounding, as the separate operator
+            x0 += bias[i1 * x.ne[0] + a0];
+            x1 += bias[i1 * x.ne[0] + a1];
+        }
+        float y0 = x0, y1 = x1;
+        if (i0 < p.n_dims) {
             float c, s;
             rope_cos_sin(p, pos[i2], ip, ff, c, s);
-            if (p.neox) { a0 = ip; a1 = ip + p.n_dims / 2; }
-            const float x0 = *(const float *) (xs + a0 * 4), x1 = *(const float *) (xs + a1 * 4);
             y0 = x0 * c - x1 * s;
             y1 = x0 * s + x1 * c;
         }
@@ -1000,7 +1005,11 @@ int b200q_op_set_rows_pair(const b200q_tensor * src0, const b200q_tensor * idx0,
 
 int b200q_op_rope_store(const b200q_tensor * q_src, const b200q_tensor * q_dst, const b200q_tensor * k_src, const b200q_tensor * pos,
                         const b200q_tensor * freq_factors, const b200q_rope_params * rp, const b200q_tensor * k_idx, const b200q_tensor * k_dst,
-                        const b200q_tensor * v_src, const b200q_tensor * v_idx, const b200q_tensor * v_dst, void * stream) {
+                        const b200q_tensor * v_src, const b200q_tensor * v_idx, const b200q_tensor * v_dst, const b200q_tensor * q_bias,
+                        const b200q_tensor * k_bias, const b200q_tensor * v_bias, void * stream) {
+    auto bias_ok = [](const b200q_tensor * b, long long width) {
+        return !b || (b->type == B200Q_TYPE_F32 && b->nb[0] == 4 && b->ne[0] == width && b->ne[1] == 1 && b->ne[2] == 1 && b->ne[3] == 1);
+    };
     auto rope_ok = [&](const b200q_tensor * x) {
         return x && x->type == B200Q_TYPE_F32 && x->nb[0] == 4 && x->ne[0] % 2 == 0 && x->ne[3] == 1 && pos && pos->ne[0] >= x->ne[2];
     };
@@ -1013,6 +1022,11 @@ int b200q_op_rope_store(const b200q_tensor * q_src, const b200q_tensor * q_dst, 
         !store_ok(k_src->ne[0] * k_src->ne[1], k_src->ne[2], k_idx, k_dst) || !v_src || v_src->type != B200Q_TYPE_F32 || v_src->ne[2] != 1 ||
         v_src->ne[3] != 1 || !store_ok(v_src->ne[0], v_src->ne[1], v_idx, v_dst) || k_dst->type != v_dst->type) {
         return ops_fail(B200Q_ENOTSUP, "rope_store: f32 q / k [head dim, heads, tokens], f32 v [width, tokens], i64 row indices, caches of one type");
+    }
+    if (!bias_ok(q_bias, q_src->ne[0] * q_src->ne[1]) || !bias_ok(k_bias, k_src->ne[0] * k_src->ne[1]) ||
+        (v_bias && (v_bias->type != B200Q_TYPE_F32 || v_bias->nb[0] != 4 || v_bias->ne[0] < 1 || v_bias->ne[1] != 1 || v_bias->ne[2] != 1 || v_bias->ne[3] != 1 ||
+                    (v_src->ne[0] * v_src->ne[1]) % v_bias->ne[0] || v_src->nb[1] != v_src->ne[0] * 4))) {
+        return ops_fail(B200Q_ENOTSUP, "rope_store: biases are f32 vectors of a token's width (v: contiguous rows)");
     }
     if (rp->mode != B200Q_ROPE_NORMAL && rp->mode != B200Q_ROPE_NEOX) return ops_fail(B200Q_ENOTSUP, "rope_store: only the normal and NeoX modes");
     if (rp->n_dims <= 0 || rp->n_dims % 2 || rp->n_dims > q_src->ne[0]) return ops_fail(B200Q_EINVAL, "rope_store: n_dims");
@@ -1033,7 +1047,8 @@ int b200q_op_rope_store(const b200q_tensor * q_src, const b200q_tensor * q_dst, 
     cudaStream_t  st = (cudaStream_t) stream;
 #define B200Q_ROPE_STORE(TD)                                                                                                               \
     launch_pdl(rope_store_kernel<TD>, g, dim3(256), 0, st, t4(q_src), t4(q_dst), t4(k_src), (const int *) pos->data, ff, p, t4(k_idx), t4(k_dst), \
-               t4(v_src), t4(v_idx), t4(v_dst), nv)
+               t4(v_src), t4(v_idx), t4(v_dst), nv, q_bias ? (const float *) q_bias->data : nullptr, k_bias ? (const float *) k_bias->data : nullptr, \
+               v_bias ? (const float *) v_bias->data : nullptr, v_bias ? (long long) v_bias->ne[0] : 1ll)
     switch (k_dst->type) {
         case B200Q_TYPE_F32:  B200Q_ROPE_STORE(B200Q_TYPE_F32); break;
         case B200Q_TYPE_F16:  B200Q_ROPE_STORE(B200Q_TYPE_F16); break;

@@ -626,7 +626,7 @@ b200q_rope_params rope_params_of(const ggml_tensor * op) {
 int compute_elementwise(b200_backend_ctx * ctx, const ggml_tensor * op) {
     const ggml_tensor * a = op->src[0];
     const ggml_tensor * b = op->src[1];
-    const b200q_tensor  ta = (op->op == GGML_OP_ROPE || op->op == GGML_OP_SET_ROWS) ? bt_src(ctx, a) : bt(a), td = bt(op);
+    const b200q_tensor  ta = (op->op == GGML_OP_ROPE || op->op == GGML_OP_SET_ROWS || op->op == GGML_OP_ADD) ? bt_src(ctx, a) : bt(a), td = bt(op);
     b200q_tensor        tb{}, tc{};
     if (b) tb = bt(b);
     if (op->src[2]) tc = bt(op->src[2]);
@@ -695,7 +695,10 @@ void drop_graphs(b200_backend_ctx * ctx) {
     ctx->graph_order.swap(keep);
 }
 
+// The first HOIST_BYTES of the workspace are the scratch of hoisted matmul results (compute_list_run) for the whole graph; what
+// operators ask for (packed activations, MoE tables, f32 copies of f16 activations) starts behind it: ws_avail() bytes.
 void * backend_workspace(b200_backend_ctx * ctx, size_t need) {
+    need += HOIST_BYTES;
     if (need > ctx->ws_bytes) {
         drop_graphs(ctx);
         if (ctx->workspace) {
@@ -706,8 +709,9 @@ void * backend_workspace(b200_backend_ctx * ctx, size_t need) {
         B200_CHECK(b200q_malloc(&ctx->workspace, bytes));
         ctx->ws_bytes = bytes;
     }
-    return ctx->workspace;
+    return (char *) ctx->workspace + HOIST_BYTES;
 }
+size_t ws_avail(const b200_backend_ctx * ctx) { return ctx->ws_bytes > HOIST_BYTES ? ctx->ws_bytes - HOIST_BYTES : 0; }
 
 uint32_t weight_flags(const ggml_tensor * w) {
     const ggml_tensor * root = w->view_src ? w->view_src : w;
@@ -783,7 +787,7 @@ int compute_mul_mat_split(b200_backend_ctx * ctx, const ggml_tensor * op) {
         q.m = nr; q.nb02 = q.nb03 = q.nb01 * nr; q.nb12 = q.nb13 = q.nb11 * q.n; q.nb2 = q.nb3 = q.nb1 * q.n;
         const size_t need = b200q_mul_mat_workspace(&q);
         void *       ws   = need ? backend_workspace(ctx, need) : nullptr;
-        if (int rc = b200q_mul_mat(&q, ext->data[main_index], (const float *) b->data, (float *) op->data + lo, ws, ctx->ws_bytes, ctx->stream)) return rc;
+        if (int rc = b200q_mul_mat(&q, ext->data[main_index], (const float *) b->data, (float *) op->data + lo, ws, ws_avail(ctx), ctx->stream)) return rc;
     }
     for (int id = 0; id < n_dev; ++id) {
         if (id != main_index && ext->row_high[id] > ext->row_low[id]) B200_CHECK(b200q_stream_wait_event(ctx->stream, ctx->peers[id].done));
@@ -825,7 +829,7 @@ int compute_mul_mat(b200_backend_ctx * ctx, const ggml_tensor * op) {
         if (int rc = b200q_op_cpy(&src, &dst, ctx->stream)) return rc;
         act = (const float *) ws;
     }
-    return b200q_mul_mat(&q, a->data, act, (float *) op->data, need ? ws + conv : nullptr, need ? ctx->ws_bytes - conv : 0, ctx->stream);
+    return b200q_mul_mat(&q, a->data, act, (float *) op->data, need ? ws + conv : nullptr, need ? ws_avail(ctx) - conv : 0, ctx->stream);
 }
 // `bias_node` != nullptr: the ADD_ID node behind this MUL_MAT_ID (same ids, the matmul's only consumer) — try both in one launch,
 // writing into the ADD_ID's result; returns 1 when the pair has to go out separately
@@ -848,11 +852,11 @@ int compute_mul_mat_id(b200_backend_ctx * ctx, const ggml_tensor * op, const ggm
         const ggml_tensor * bias = bias_node->src[1];
         q.nb1 = bias_node->nb[1]; q.nb2 = bias_node->nb[2];
         const int rc = b200q_mul_mat_id_bias(&q, as->data, (const float *) b->data, (const int32_t *) ids->data, (const float *) bias->data,
-                                             bias->nb[1], (float *) bias_node->data, ws, ctx->ws_bytes, ctx->stream);
+                                             bias->nb[1], (float *) bias_node->data, ws, ws_avail(ctx), ctx->stream);
         return rc == B200Q_ENOTSUP ? 1 : rc;
     }
     return b200q_mul_mat_id(&q, as->data, (const float *) b->data, (const int32_t *) ids->data, (float *) op->data, ws,
-                            ctx->ws_bytes, ctx->stream);
+                            ws_avail(ctx), ctx->stream);
 }
 int compute_get_rows(b200_backend_ctx * ctx, const ggml_tensor * op) {
     const ggml_tensor * a = op->src[0];
@@ -989,6 +993,12 @@ int32_t node_use_count(const ggml_cgraph * cgraph, const ggml_tensor * t);
 // how often each fusion of graph_dispatch fired ("ggml_backend_b200_fusion_stats": copies up to n counters, returns how many exist)
 enum { FUSE_NORM, FUSE_ATTN, FUSE_ROPE_STORE, FUSE_SET_ROWS_PAIR, FUSE_MOE_SUM, FUSE_ID_BIAS, FUSE_LIST, FUSE_SCRATCH_READ, FUSE_SCRATCH_COPY, FUSE_GLU_LIST, FUSE_N };
 int64_t g_fusion_stats[FUSE_N] = {};
+void    print_fusion_stats() {  // GGML_B200_STATS=1: at exit, what graph_dispatch did with the graphs of this process
+    static const char * names[FUSE_N] = { "norm", "attn", "rope_store", "set_rows_pair", "moe_sum", "id_bias", "list", "scratch_read", "scratch_copy", "glu_list" };
+    fprintf(stderr, "ggml-b200 fusions:");
+    for (int i = 0; i < FUSE_N; ++i) fprintf(stderr, " %s=%lld", names[i], (long long) g_fusion_stats[i]);
+    fprintf(stderr, "\n");
+}
 int     fusion_stats(int64_t * out, int n) {
     for (int i = 0; i < n && i < FUSE_N; ++i) out[i] = g_fusion_stats[i];
     return FUSE_N;
@@ -1203,6 +1213,7 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) 
 // [ADD ->] RMS_NORM -> MUL as one launch (b200q_op_norm_fused; the reference fuses the same run, ggml-cuda.cu:2811-2845,
 // 3000-3040).  Returns the number of nodes consumed (0: no fusion here).  The norm's own output is never written, so it
 // must have the MUL as its only consumer and be neither a view source nor a graph output (ggml_node_has_n_uses).
+b200q_tensor bt_src(b200_backend_ctx * ctx, const ggml_tensor * t);
 int try_fuse_norm(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int i, int n_nodes, int * rc) {
     auto f32row = [](const ggml_tensor * t) { return t && t->type == GGML_TYPE_F32 && t->nb[0] == sizeof(float); };
     const ggml_tensor * add = nullptr;
@@ -1231,7 +1242,7 @@ int try_fuse_norm(b200_backend_ctx * ctx, ggml_cgraph * cgraph, int i, int n_nod
         const ggml_tensor * a = add->src[0];
         const ggml_tensor * b = add->src[1];
         if (!f32row(a) || !f32row(b) || !f32row(add) || !ggml_are_same_shape(a, add) || !ggml_are_same_shape(b, add)) return 0;
-        const b200q_tensor ta = bt(a), tb = bt(b), ts = bt(add);
+        const b200q_tensor ta = bt_src(ctx, a), tb = bt(b), ts = bt(add);  // a: possibly a hoisted matmul's result still in the scratch
         *rc = b200q_op_norm_fused(&ta, &tb, &ts, &tw, &td, eps, ctx->stream);
         return 3;
     }
@@ -1363,53 +1374,72 @@ bool sole_reader_takes_scratch(const ggml_cgraph * cgraph, int i, int n_nodes) {
             cur = user;
             continue;
         }
-        return (user->op == GGML_OP_ROPE || user->op == GGML_OP_SET_ROWS) && user->src[0] == cur && supports_elementwise(user);
+        return (user->op == GGML_OP_ROPE || user->op == GGML_OP_SET_ROWS || user->op == GGML_OP_ADD) && user->src[0] == cur && user->src[1] != cur &&
+               supports_elementwise(user);
     }
     return false;
 }
 
-// ROPE(q) at node i, followed — with nothing in between but views and matmuls that already ran with an earlier list — by
-// ROPE(k) whose only reader is a SET_ROWS (the K cache write) and a second SET_ROWS (the V cache write): llama.cpp's decode
-// step behind the q / k / v matmuls.  All of it goes out as one launch (b200q_op_rope_store) at ROPE(q)'s position: every
-// source is already computed, and the cache rows are written a few nodes early past nodes that do not execute.  Matmul
-// results that wait in the scratch are read from there.  Returns the index behind the group, or 0.
+// [ADD(bias) ->] ROPE(q) at node i, followed — with nothing in between but views and matmuls that already ran with an earlier
+// list — by [ADD(bias) ->] ROPE(k) whose only reader is a SET_ROWS (the K cache write) and [ADD(bias) ->] a second SET_ROWS (the V
+// cache write): llama.cpp's decode step behind the q / k / v matmuls (src/models/*.cpp: with biases in gpt-oss / Qwen2).  All of
+// it goes out as one launch (b200q_op_rope_store) at the first node's position: every source is already computed, and the cache
+// rows are written a few nodes early past nodes that do not execute.  Matmul results that wait in the scratch are read from
+// there; the ADD results and the rotated k are never written (each has the next node of the run as its only reader).
+// Returns the index behind the group, or 0.
 int try_fuse_rope_store(b200_backend_ctx * ctx, const ggml_cgraph * cgraph, int i, int n_nodes, const std::vector<char> & done, int * rc) {
     if (!cgraph->use_counts) return 0;
-    const ggml_tensor * rq = ggml_graph_node((ggml_cgraph *) cgraph, i);
-    if (rq->op != GGML_OP_ROPE || !is_f32(rq) || rq->ne[3] != 1 || !supports_elementwise(rq)) return 0;
-    const ggml_tensor * rk = nullptr, * s[2] = { nullptr, nullptr };
+    auto producer = [&](const ggml_tensor * t) {  // the node behind views that keep its address
+        for (int hops = 0; hops < 4 && (t->op == GGML_OP_RESHAPE || t->op == GGML_OP_VIEW) && t->src[0] && t->src[0]->data == t->data; ++hops) {
+            if (node_use_count(cgraph, t) != 1 || (t->flags & GGML_TENSOR_FLAG_OUTPUT)) return (const ggml_tensor *) nullptr;
+            t = t->src[0];
+        }
+        return t;
+    };
+    auto bias_add = [&](const ggml_tensor * t) {  // [width, tokens] + [width]: its result has one reader and is not a graph output
+        const ggml_tensor * a = t->src[0], * b = t->src[1];
+        return t->op == GGML_OP_ADD && is_f32(t) && is_f32(a) && is_f32(b) && ggml_is_contiguous(a) && ggml_is_contiguous(t) && ggml_are_same_shape(a, t) &&
+               ggml_is_contiguous(b) && b->ne[0] == a->ne[0] && b->ne[1] == 1 && b->ne[2] == 1 && b->ne[3] == 1 && a->ne[2] == 1 && a->ne[3] == 1 &&
+               node_use_count(cgraph, t) == 1 && !(t->flags & GGML_TENSOR_FLAG_OUTPUT) && !tensor_is_split(b);
+    };
+    const ggml_tensor * rq = nullptr, * rk = nullptr, * s[2] = { nullptr, nullptr }, * adds[3] = { nullptr, nullptr, nullptr };
+    const ggml_tensor * pending = nullptr;  // an ADD whose reader has not turned up yet
     int hoisted[4], n_hoisted = 0, last = -1;
-    for (int j = i + 1; j < n_nodes && j < i + 24 && last < 0; ++j) {
+    for (int j = i; j < n_nodes && j < i + 28 && last < 0; ++j) {
         const ggml_tensor * t = ggml_graph_node((ggml_cgraph *) cgraph, j);
-        if (done[(size_t) j] == 2) {
+        if (j > i && done[(size_t) j] == 2) {
             if (n_hoisted == 4) return 0;
             hoisted[n_hoisted++] = j;
             continue;
         }
-        if (done[(size_t) j] || noop_node(t)) continue;
-        if (t->op == GGML_OP_ROPE && !rk && !s[0]) { rk = t; continue; }
+        if ((j > i && done[(size_t) j]) || noop_node(t)) continue;
+        if (t->op == GGML_OP_ADD && !pending && !s[0] && bias_add(t)) { pending = t; continue; }
+        if (t->op == GGML_OP_ROPE && !s[0] && (!rq || !rk)) {
+            if (pending && producer(t->src[0]) != pending) return 0;
+            adds[rq ? 1 : 0] = pending;
+            pending = nullptr;
+            (rq ? rk : rq) = t;
+            continue;
+        }
         if (t->op == GGML_OP_SET_ROWS && rk && !s[0]) { s[0] = t; continue; }
         if (t->op == GGML_OP_SET_ROWS && s[0]) { s[1] = t; last = j; continue; }
         return 0;
     }
-    if (last < 0) return 0;
-    // which of the two stores takes the rotated k (through single-use views at the same address)?
-    auto reads_rk = [&](const ggml_tensor * st) {
-        const ggml_tensor * t = st->src[0];
-        for (int hops = 0; hops < 4 && t; ++hops) {
-            if (t == rk) return true;
-            if ((t->op != GGML_OP_RESHAPE && t->op != GGML_OP_VIEW) || t->data != rk->data || node_use_count(cgraph, t) != 1 ||
-                (t->flags & GGML_TENSOR_FLAG_OUTPUT)) return false;
-            t = t->src[0];
-        }
-        return false;
-    };
-    const ggml_tensor * sk = reads_rk(s[0]) ? s[0] : reads_rk(s[1]) ? s[1] : nullptr;
+    if (last < 0 || !rq || !rk) return 0;
+    if (!is_f32(rq) || rq->ne[3] != 1 || !supports_elementwise(rq)) return 0;
+    // which of the two stores takes the rotated k?
+    const ggml_tensor * sk = producer(s[0]->src[0]) == rk ? s[0] : producer(s[1]->src[0]) == rk ? s[1] : nullptr;
     if (!sk) return 0;
     const ggml_tensor * sv = sk == s[0] ? s[1] : s[0];
-    if (reads_rk(sv) || node_use_count(cgraph, rk) != 1 || (rk->flags & GGML_TENSOR_FLAG_OUTPUT)) return 0;
+    const ggml_tensor * vp = producer(sv->src[0]);
+    if (!vp || vp == rk || node_use_count(cgraph, rk) != 1 || (rk->flags & GGML_TENSOR_FLAG_OUTPUT)) return 0;
+    if (pending) {  // the ADD in front of the V store
+        if (vp != pending || !ggml_is_contiguous(sv->src[0])) return 0;
+        adds[2] = pending;
+    }
     if (!is_f32(rk) || !supports_elementwise(rk) || !ggml_is_contiguous(rk) || rk->ne[3] != 1 || rk->ne[0] != rq->ne[0] || rk->ne[2] != rq->ne[2] ||
         memcmp(rk->op_params, rq->op_params, sizeof(rq->op_params)) != 0 || rk->src[1] != rq->src[1] || rk->src[2] != rq->src[2]) return 0;
+    if ((adds[0] && !ggml_is_contiguous(rq->src[0])) || (adds[1] && !ggml_is_contiguous(rk->src[0]))) return 0;
     auto store_ok = [&](const ggml_tensor * st, int64_t width, int64_t rows) {
         const ggml_tensor * a = st->src[0], * x = st->src[1];
         return supports_elementwise(st) && a->ne[0] == width && a->ne[1] == rows && a->ne[2] == 1 && a->ne[3] == 1 && a->nb[0] == 4 &&
@@ -1417,31 +1447,32 @@ int try_fuse_rope_store(b200_backend_ctx * ctx, const ggml_cgraph * cgraph, int 
     };
     if (!store_ok(sk, rk->ne[0] * rk->ne[1], rk->ne[2]) || !ggml_is_contiguous(sk->src[0]) || !store_ok(sv, sv->src[0]->ne[0], sv->src[0]->ne[1]) ||
         sk->type != sv->type || ranges_overlap(sk, sv) || ranges_overlap(rq, sk) || ranges_overlap(rq, sv)) return 0;
-    // where the sources really are: a hoisted matmul of this group whose result still waits in the scratch (k, v)
-    auto producer = [&](const ggml_tensor * t) {  // the node behind views that keep its address
-        for (int hops = 0; hops < 4 && (t->op == GGML_OP_RESHAPE || t->op == GGML_OP_VIEW) && t->src[0] && t->src[0]->data == t->data; ++hops) t = t->src[0];
-        return t;
-    };
-    b200q_tensor tk = bt(rk->src[0]), tv = bt(sv->src[0]);
+    // where the values really are: behind an ADD, the ADD's first source; a hoisted matmul of this group still in the scratch
+    const ggml_tensor * qs = adds[0] ? adds[0]->src[0] : rq->src[0], * ks = adds[1] ? adds[1]->src[0] : rk->src[0], * vs = adds[2] ? adds[2]->src[0] : sv->src[0];
+    b200q_tensor tq = bt(rq->src[0]), tk = bt(rk->src[0]), tv = bt(sv->src[0]);  // shapes and strides of the readers' views
+    tq.data = qs->data; tk.data = ks->data; tv.data = vs->data;
     for (int h = 0; h < n_hoisted; ++h) {
         const ggml_tensor * m  = ggml_graph_node((ggml_cgraph *) cgraph, hoisted[h]);
         const auto &        hc = ctx->hoist_copies[(size_t) hoisted[h]];
         if (!sole_reader_takes_scratch(cgraph, hoisted[h], n_nodes)) return 0;  // somebody else waits for it: it needs its delivery copy
-        if (m == producer(rk->src[0])) tk.data = (void *) hc.src;
-        else if (m == producer(sv->src[0])) tv.data = (void *) hc.src;
+        if (m == producer(qs)) tq.data = (void *) hc.src;
+        else if (m == producer(ks)) tk.data = (void *) hc.src;
+        else if (m == producer(vs)) tv.data = (void *) hc.src;
         else return 0;
     }
     auto hits_q = [&](const b200q_tensor & t, const ggml_tensor * g) {
         const char * a0 = (const char *) t.data, * a1 = a0 + ggml_nbytes(g), * b0 = (const char *) rq->data, * b1 = b0 + ggml_nbytes(rq);
         return a0 < b1 && b0 < a1;
     };
-    if (hits_q(tk, rk->src[0]) || hits_q(tv, sv->src[0])) return 0;
-    const b200q_tensor      tq = bt_src(ctx, rq->src[0]);  // q itself may be behind a redirect of an earlier list
+    if (hits_q(tk, ks) || hits_q(tv, vs)) return 0;
+    if (tq.data == qs->data) tq.data = bt_src(ctx, qs).data;  // q itself may be behind a redirect of an earlier position
     const b200q_tensor      td = bt(rq), tp = bt(rq->src[1]), kx = bt(sk->src[1]), kd = bt(sk), vx = bt(sv->src[1]), vd = bt(sv);
-    b200q_tensor            tf{};
+    b200q_tensor            tf{}, tb[3]{};
     if (rq->src[2]) tf = bt(rq->src[2]);
+    for (int q = 0; q < 3; ++q) if (adds[q]) tb[q] = bt(adds[q]->src[1]);
     const b200q_rope_params rp = rope_params_of(rq);
-    *rc = b200q_op_rope_store(&tq, &td, &tk, &tp, rq->src[2] ? &tf : nullptr, &rp, &kx, &kd, &tv, &vx, &vd, ctx->stream);
+    *rc = b200q_op_rope_store(&tq, &td, &tk, &tp, rq->src[2] ? &tf : nullptr, &rp, &kx, &kd, &tv, &vx, &vd, adds[0] ? &tb[0] : nullptr,
+                              adds[1] ? &tb[1] : nullptr, adds[2] ? &tb[2] : nullptr, ctx->stream);
     return last + 1;
 }
 
@@ -1453,15 +1484,11 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
     ctx->hoist_used = 0;
     ctx->redirect.clear();
     ctx->hoist_copies.assign((size_t) n_nodes, b200_backend_ctx::hoist_copy{});
-    // scratch results live in the head of the workspace: only in graphs where no node needs the workspace for itself (the
-    // tensor-core kernel's packed activations, MoE tables, the f32 copy of f16 activations) — decode graphs
+    // scratch results live in the head of the workspace, which no operator is given (backend_workspace)
     ctx->hoist_ok = getenv("GGML_B200_NO_LIST") == nullptr;
-    for (int i = 0; i < n_nodes && ctx->hoist_ok; ++i) {
-        const ggml_tensor * t = ggml_graph_node(cgraph, i);
-        if (t->op == GGML_OP_MUL_MAT_ID) ctx->hoist_ok = false;
-        if (t->op == GGML_OP_MUL_MAT && (t->src[1]->ne[1] > 8 || t->src[1]->type != GGML_TYPE_F32 || tensor_is_split(t->src[0]))) ctx->hoist_ok = false;
-    }
-    if (ctx->hoist_ok) backend_workspace(ctx, HOIST_BYTES);
+    static const bool stats_hook = getenv("GGML_B200_STATS") != nullptr && atexit(print_fusion_stats) == 0;
+    (void) stats_hook;
+    if (ctx->hoist_ok) backend_workspace(ctx, 0);
     const bool no_lists = getenv("GGML_B200_NO_LIST") != nullptr;
     for (int i = 0; i < n_nodes; ++i) {
         ggml_tensor * node = ggml_graph_node(cgraph, i);
@@ -1532,7 +1559,7 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
                 continue;
             }
         }
-        if (!no_fuse && node->op == GGML_OP_ROPE) {
+        if (!no_fuse && (node->op == GGML_OP_ROPE || node->op == GGML_OP_ADD)) {
             const int behind = try_fuse_rope_store(ctx, cgraph, i, n_nodes, done, &rc);
             if (behind > i) {
                 if (rc != 0) {

@@ -381,11 +381,12 @@ namespace {
 struct lcg { uint32_t s; float next() { s = s * 1664525u + 1013904223u; return ((s >> 8) * (1.0f / 8388608.0f)) - 1.0f; } };
 struct layer_dims { int64_t n_embd = 512, n_head = 8, n_head_kv = 2, hd = 64, n_ff = 1024, n_ctx = 256; };
 
+bool g_layer_bias = false;  // q / k / v / o biases as gpt-oss and Qwen2 have them (an ADD behind each of the four matmuls)
 int run_layer(ggml_backend_t be, int type, int n_tokens, int n_past, std::vector<float> & out, int * unsupported) {
     const layer_dims D;
     const int64_t n_kv   = ((n_past + n_tokens + 31) / 32) * 32;
     const int64_t kv_dim = D.hd * D.n_head_kv;
-    ctx_scope wc(16), cc(96);
+    ctx_scope wc(24), cc(112);
     const ggml_type wt = (ggml_type) type;
     ggml_tensor * wq = ggml_new_tensor_2d(wc.ctx, wt, D.n_embd, D.n_embd);
     ggml_tensor * wk = ggml_new_tensor_2d(wc.ctx, wt, D.n_embd, kv_dim);
@@ -396,6 +397,10 @@ int run_layer(ggml_backend_t be, int type, int n_tokens, int n_past, std::vector
     ggml_tensor * wd = ggml_new_tensor_2d(wc.ctx, wt, D.n_ff, D.n_embd);
     ggml_tensor * an = ggml_new_tensor_1d(wc.ctx, GGML_TYPE_F32, D.n_embd);
     ggml_tensor * fn = ggml_new_tensor_1d(wc.ctx, GGML_TYPE_F32, D.n_embd);
+    ggml_tensor * bq = ggml_new_tensor_1d(wc.ctx, GGML_TYPE_F32, D.n_embd);
+    ggml_tensor * bk = ggml_new_tensor_1d(wc.ctx, GGML_TYPE_F32, kv_dim);
+    ggml_tensor * bv = ggml_new_tensor_1d(wc.ctx, GGML_TYPE_F32, kv_dim);
+    ggml_tensor * bo = ggml_new_tensor_1d(wc.ctx, GGML_TYPE_F32, D.n_embd);
     ctx_scope kvc(4);  // the KV cache lives in its own buffer: the weights' buffer is marked immutable, as llama.cpp's is
     ggml_tensor * kc = ggml_new_tensor_2d(kvc.ctx, GGML_TYPE_F16, kv_dim, D.n_ctx);
     ggml_tensor * vc = ggml_new_tensor_2d(kvc.ctx, GGML_TYPE_F16, kv_dim, D.n_ctx);
@@ -417,6 +422,7 @@ int run_layer(ggml_backend_t be, int type, int n_tokens, int n_past, std::vector
     };
     for (ggml_tensor * t : { wq, wk, wv, wo, wg, wu, wd }) fill_q(t, 0.06f);
     for (ggml_tensor * t : { an, fn }) fill_q(t, 1.0f);
+    for (ggml_tensor * t : { bq, bk, bv, bo }) fill_q(t, 0.3f);
     for (ggml_tensor * t : { kc, vc }) fill_q(t, 0.5f);  // positions < n_past hold earlier tokens; the rest is masked out
 
     ggml_tensor * x    = ggml_new_tensor_2d(cc.ctx, GGML_TYPE_F32, D.n_embd, n_tokens);
@@ -425,9 +431,10 @@ int run_layer(ggml_backend_t be, int type, int n_tokens, int n_past, std::vector
     ggml_tensor * mask = ggml_new_tensor_2d(cc.ctx, GGML_TYPE_F32, n_kv, n_tokens);
     ggml_context * c = cc.ctx;
     ggml_tensor * cur = ggml_mul(c, ggml_rms_norm(c, x, 1e-5f), an);
-    ggml_tensor * Q = ggml_reshape_3d(c, ggml_mul_mat(c, wq, cur), D.hd, D.n_head, n_tokens);
-    ggml_tensor * K = ggml_reshape_3d(c, ggml_mul_mat(c, wk, cur), D.hd, D.n_head_kv, n_tokens);
-    ggml_tensor * V = ggml_mul_mat(c, wv, cur);
+    auto biased = [&](ggml_tensor * t, ggml_tensor * b) { return g_layer_bias ? ggml_add(c, t, b) : t; };
+    ggml_tensor * Q = ggml_reshape_3d(c, biased(ggml_mul_mat(c, wq, cur), bq), D.hd, D.n_head, n_tokens);
+    ggml_tensor * K = ggml_reshape_3d(c, biased(ggml_mul_mat(c, wk, cur), bk), D.hd, D.n_head_kv, n_tokens);
+    ggml_tensor * V = biased(ggml_mul_mat(c, wv, cur), bv);
     Q = ggml_rope_ext(c, Q, pos, nullptr, (int) D.hd, 0, 8192, 500000.0f, 1.0f, 0.0f, 1.0f, 32.0f, 1.0f);
     K = ggml_rope_ext(c, K, pos, nullptr, (int) D.hd, 0, 8192, 500000.0f, 1.0f, 0.0f, 1.0f, 32.0f, 1.0f);
     ggml_tensor * k_store = ggml_set_rows(c, kc, ggml_reshape_2d(c, K, kv_dim, n_tokens), idx);
@@ -440,7 +447,7 @@ int run_layer(ggml_backend_t be, int type, int n_tokens, int n_past, std::vector
     v = ggml_cont(c, ggml_transpose(c, v));
     ggml_tensor * kqv = ggml_mul_mat(c, v, kq);
     cur = ggml_cont_2d(c, ggml_permute(c, kqv, 0, 2, 1, 3), D.n_embd, n_tokens);
-    ggml_tensor * ffn_inp = ggml_add(c, ggml_mul_mat(c, wo, cur), x);
+    ggml_tensor * ffn_inp = ggml_add(c, biased(ggml_mul_mat(c, wo, cur), bo), x);
     cur = ggml_mul(c, ggml_rms_norm(c, ffn_inp, 1e-5f), fn);
     cur = ggml_swiglu_split(c, ggml_mul_mat(c, wg, cur), ggml_mul_mat(c, wu, cur));
     ggml_tensor * res = ggml_add(c, ggml_mul_mat(c, wd, cur), ffn_inp);
@@ -599,6 +606,13 @@ int pd_moe_block(int dev, int n_tokens, double * nmse, int * unsupported) {
     return rc;
 }
 
+int pd_llama_layer(int dev, int type, int n_tokens, int n_past, double * nmse, int * unsupported);
+int pd_llama_layer_bias(int dev, int type, int n_tokens, int n_past, double * nmse, int * unsupported) {
+    g_layer_bias = true;
+    const int rc = pd_llama_layer(dev, type, n_tokens, n_past, nmse, unsupported);
+    g_layer_bias = false;
+    return rc;
+}
 int pd_llama_layer(int dev, int type, int n_tokens, int n_past, double * nmse, int * unsupported) {
     if (!g_reg) return -1;
     ggml_backend_t be  = ggml_backend_dev_init(ggml_backend_reg_dev_get(g_reg, dev), nullptr);

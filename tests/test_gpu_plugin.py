@@ -96,6 +96,7 @@ def _driver():
         L.pd_layer_replay.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.pd_last_us.restype = C.c_double
         L.pd_llama_layer.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
+        L.pd_llama_layer_bias.argtypes = L.pd_llama_layer.argtypes
         L.pd_moe_block.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         n = L.pd_load(PLUGIN.encode())
         assert n >= 1, f"ggml_backend_load({PLUGIN}) registered {n} devices"
@@ -315,6 +316,24 @@ def test_inprocess_llama_layer_stays_on_device(t, n_tokens, n_past):
         # the decode step is what the fusions are for: they must have fired on the graph the CPU backend was compared with
         # (two norms, the attention core, q / k / v and gate / up as lists, rope + both cache stores as one launch)
         assert fired["norm"] >= 2 and fired["attn"] >= 1 and fired["list"] >= 2 and fired["rope_store"] >= 1, fired
+
+
+@pytest.mark.parametrize("n_tokens,n_past", [(1, 37), (1, 0), (5, 60), (40, 0)])
+@pytest.mark.parametrize("t", [refs.Q8_0, refs.Q4_K], ids=lambda t: refs.NAMES[t])
+def test_inprocess_layer_with_attention_biases(t, n_tokens, n_past):
+    """the same layer with q / k / v / o biases (gpt-oss, Qwen2: an ADD behind each matmul).  At decode the ADDs in front of the
+    ROPEs and of the V store are part of the one launch behind the q / k / v list (b200q_op_rope_store with biases) and read
+    hoisted results from the scratch; the output equals the reference CPU backend's."""
+    L = _driver()
+    nmse, unsup = C.c_double(-1.0), C.c_int(-1)
+    before = _fusion_stats(L)
+    rc = L.pd_llama_layer_bias(0, t, n_tokens, n_past, C.byref(nmse), C.byref(unsup))
+    assert rc == 0 and unsup.value == 0, (rc, unsup.value)
+    fired = {k: v - before[k] for k, v in _fusion_stats(L).items()}
+    print(f"\n[llama layer + biases] {refs.NAMES[t]} n_tokens={n_tokens} n_past={n_past}: nmse vs CPU backend {nmse.value:.2e}; fusions {fired}")
+    assert 0.0 <= nmse.value <= 1e-3
+    if n_tokens == 1 and not any(os.environ.get(k) for k in ("GGML_B200_NO_FUSE", "GGML_B200_NO_LIST", "GGML_B200_NO_HOIST", "GGML_B200_NO_SCRATCH")):
+        assert fired["rope_store"] >= 1 and fired["list"] >= 2, fired
 
 
 FUSIONS = ("norm", "attn", "rope_store", "set_rows_pair", "moe_sum", "id_bias", "list", "scratch_read", "scratch_copy", "glu_list")
