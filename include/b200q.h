@@ -342,6 +342,17 @@ B200Q_API int b200q_op_set_rows(const b200q_tensor * src, const b200q_tensor * i
  * chain of ADDs, src/llama-graph.cpp build_moe_ffn); products rounded separately and added in slot order, as the separate operators do */
 B200Q_API int b200q_op_moe_weighted_sum(const b200q_tensor * experts, const b200q_tensor * weights, const b200q_tensor * dst, void * stream);
 
+/* the MoE router behind the logits matmul, as gpt-oss gates (src/llama-graph.cpp build_moe_ffn: router bias, top-k, soft_max over
+ * the selected logits): biased = logits + bias; sorted = argsort(biased, descending) per token; weights (may be NULL)[s, t] =
+ * soft_max over the first weights->ne[0] entries of sorted of biased — the nodes ADD, ARGSORT, (top-k view,) GET_ROWS, SOFT_MAX in
+ * one launch.  logits / biased f32 [experts <= 1024, tokens], bias f32 [experts] or NULL, sorted i32 [experts, tokens], weights f32
+ * [used, tokens].  llama.cpp's node order puts the expert matmuls between the top-k and the GET_ROWS, so the plugin runs the
+ * first half here (weights = NULL) and the second half with b200q_op_moe_gate_weights: weights[q, t] = soft_max over q of
+ * probs[0, ids[q, t], t] (GET_ROWS of single values + SOFT_MAX); probs f32 [1, experts, tokens], ids i32 [used, tokens]. */
+B200Q_API int b200q_op_moe_route(const b200q_tensor * logits, const b200q_tensor * bias, const b200q_tensor * biased, const b200q_tensor * sorted,
+                                 const b200q_tensor * weights, void * stream);
+B200Q_API int b200q_op_moe_gate_weights(const b200q_tensor * probs, const b200q_tensor * ids, const b200q_tensor * weights, void * stream);
+
 /* two independent SET_ROWS with one destination type in one launch (a layer's K and V cache writes are consecutive nodes) */
 B200Q_API int b200q_op_set_rows_pair(const b200q_tensor * src0, const b200q_tensor * idx0, const b200q_tensor * dst0,
                                      const b200q_tensor * src1, const b200q_tensor * idx1, const b200q_tensor * dst1, void * stream);

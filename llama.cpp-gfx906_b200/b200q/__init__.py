@@ -44,7 +44,7 @@ EXPORTS = [
     "b200q_enable_peer_access", "b200q_memcpy_peer", "b200q_max_k",
     "b200q_op_rms_norm", "b200q_op_bin", "b200q_op_scale", "b200q_op_unary", "b200q_op_glu", "b200q_op_soft_max", "b200q_op_rope",
     "b200q_graph_begin", "b200q_graph_end", "b200q_graph_launch", "b200q_graph_destroy",
-    "b200q_op_cpy", "b200q_op_add_id", "b200q_op_argsort", "b200q_op_norm_fused", "b200q_op_attn_decode", "b200q_op_set_rows_pair", "b200q_op_rope_store", "b200q_scatter_rows_peers", "b200q_op_moe_weighted_sum", "b200q_mul_mat_id_bias", "b200q_op_set_rows", "b200q_mxf_probe",
+    "b200q_op_cpy", "b200q_op_add_id", "b200q_op_argsort", "b200q_op_norm_fused", "b200q_op_attn_decode", "b200q_op_set_rows_pair", "b200q_op_rope_store", "b200q_op_moe_route", "b200q_op_moe_gate_weights", "b200q_scatter_rows_peers", "b200q_op_moe_weighted_sum", "b200q_mul_mat_id_bias", "b200q_op_set_rows", "b200q_mxf_probe",
 ]
 
 

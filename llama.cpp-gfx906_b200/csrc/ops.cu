@@ -729,6 +729,76 @@ __global__ void __launch_bounds__(1024) argsort_kernel(T4 s, T4 d, int npad, int
     if (t < n) *(int *) (d.data + (long long) t * 4 + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = as_idx[t];
 }
 
+// ---- MoE router behind the logits matmul (gpt-oss gating: src/llama-graph.cpp build_moe_ffn with a router bias and
+// LLAMA_EXPERT_GATING_FUNC_TYPE_SOFTMAX_WEIGHT): ADD(bias) -> ARGSORT(desc) -> top-k view -> GET_ROWS -> SOFT_MAX as one launch.
+// One CTA per token; the comparisons are argsort_kernel's (same order, ties included), the soft_max is max / expf / sum / scale
+// by the reciprocal over the n_used selected logits in slot order.
+__global__ void __launch_bounds__(1024) moe_route_kernel(T4 lg, const float * bias, T4 biased, T4 sorted, T4 wout, int npad, int n_used) {
+    pdl_grid_sync();
+    extern __shared__ int rt_smem[];
+    int *   idx = rt_smem;
+    float * v   = (float *) (rt_smem + npad);
+    const long long tok = blockIdx.x;
+    const int n = (int) lg.ne[0], t = threadIdx.x;
+    if (t < n) {
+        float x = *(const float *) (lg.data + (long long) t * 4 + tok * lg.nb[1]);
+        if (bias) x += bias[t];
+        v[t] = x;
+        *(float *) (biased.data + (long long) t * 4 + tok * biased.nb[1]) = x;
+    }
+    if (t < npad) idx[t] = t;
+    __syncthreads();
+    for (int k = 2; k <= npad; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const int o = t ^ j;
+            if (t < npad && o > t) {
+                const int a = idx[t], b = idx[o];
+                const bool after  = a >= n ? b < n : (b < n && v[a] < v[b]);
+                const bool before = b >= n ? a < n : (a < n && v[b] < v[a]);
+                const bool up = (t & k) == 0;
+                if (up ? after : before) {
+                    idx[t] = b;
+                    idx[o] = a;
+                }
+            }
+            __syncthreads();
+        }
+    }
+    if (t < n) *(int *) (sorted.data + (long long) t * 4 + tok * sorted.nb[1]) = idx[t];
+    if (t == 0 && n_used > 0) {
+        float mx = -INFINITY, sum = 0.0f;
+        for (int q = 0; q < n_used; ++q) mx = fmaxf(mx, v[idx[q]]);
+        float * wp = (float *) (wout.data + tok * wout.nb[1]);
+        for (int q = 0; q < n_used; ++q) {
+            const float e = expf(v[idx[q]] - mx);
+            wp[q] = e;
+            sum += e;
+        }
+        const float inv = 1.0f / sum;
+        for (int q = 0; q < n_used; ++q) wp[q] *= inv;
+    }
+}
+
+// GET_ROWS of single logits by the selected expert ids + SOFT_MAX over them (the second half of the router: llama.cpp's graph
+// order puts the expert matmuls between the top-k and this): weights[q, t] = soft_max_q(probs[ids[q, t], t]); a thread per token
+__global__ void __launch_bounds__(128) moe_gate_weights_kernel(T4 probs, T4 ids, T4 wout, long long n_tok, int n_used) {
+    pdl_grid_sync();
+    const long long tok = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (tok >= n_tok) return;
+    const char * ip = ids.data + tok * ids.nb[1];
+    const char * pp = probs.data + tok * probs.nb[2];
+    float *      wp = (float *) (wout.data + tok * wout.nb[1]);
+    float mx = -INFINITY, sum = 0.0f;
+    for (int q = 0; q < n_used; ++q) mx = fmaxf(mx, *(const float *) (pp + (long long) *(const int *) (ip + q * ids.nb[0]) * probs.nb[1]));
+    for (int q = 0; q < n_used; ++q) {
+        const float e = expf(*(const float *) (pp + (long long) *(const int *) (ip + q * ids.nb[0]) * probs.nb[1]) - mx);
+        wp[q] = e;
+        sum += e;
+    }
+    const float inv = 1.0f / sum;
+    for (int q = 0; q < n_used; ++q) wp[q] *= inv;
+}
+
 template <int TS> int cpy_to(const b200q_tensor * s, const b200q_tensor * d, long long n, cudaStream_t st) {
     if (TS == B200Q_TYPE_F32 && d->type == B200Q_TYPE_F32 && s->nb[0] == 4 && d->nb[0] == 4 && s->ne[0] % 4 == 0 && d->ne[0] % 4 == 0) {
         bool al = true;
@@ -976,6 +1046,37 @@ int b200q_op_argsort(const b200q_tensor * src, const b200q_tensor * dst, int des
     int npad = 1;
     while (npad < src->ne[0]) npad <<= 1;
     launch_pdl(argsort_kernel, dim3((unsigned) rows), dim3(npad < 32 ? 32 : npad), npad * sizeof(int), (cudaStream_t) stream, t4(src), t4(dst), npad, descending ? 1 : 0);
+    return launched();
+}
+
+int b200q_op_moe_route(const b200q_tensor * logits, const b200q_tensor * bias, const b200q_tensor * biased, const b200q_tensor * sorted,
+                       const b200q_tensor * weights, void * stream) {
+    if (!logits || !biased || !sorted || logits->type != B200Q_TYPE_F32 || biased->type != B200Q_TYPE_F32 || sorted->type != B200Q_TYPE_I32 ||
+        logits->nb[0] != 4 || biased->nb[0] != 4 || sorted->nb[0] != 4 || logits->ne[0] < 1 ||
+        logits->ne[0] > 1024 || logits->ne[2] != 1 || logits->ne[3] != 1 || !same_shape(logits, biased) || !same_shape(logits, sorted) ||
+        (weights && (weights->type != B200Q_TYPE_F32 || weights->nb[0] != 4 || weights->ne[0] < 1 || weights->ne[0] > logits->ne[0] ||
+                     weights->ne[1] != logits->ne[1] || weights->ne[2] != 1 || weights->ne[3] != 1)) ||
+        (bias && (bias->type != B200Q_TYPE_F32 || bias->nb[0] != 4 || bias->ne[0] != logits->ne[0] || bias->ne[1] != 1 || bias->ne[2] != 1 || bias->ne[3] != 1))) {
+        return ops_fail(B200Q_ENOTSUP, "moe_route: f32 logits [experts <= 1024, tokens], f32 bias [experts], i32 order, f32 weights [used, tokens]");
+    }
+    if (logits->ne[1] == 0) return 0;
+    if (logits->ne[1] > 0x7fffffffll) return ops_fail(B200Q_ENOTSUP, "moe_route: too many tokens");
+    int npad = 1;
+    while (npad < logits->ne[0]) npad <<= 1;
+    launch_pdl(moe_route_kernel, dim3((unsigned) logits->ne[1]), dim3(npad < 32 ? 32 : npad), npad * 8, (cudaStream_t) stream, t4(logits),
+               bias ? (const float *) bias->data : nullptr, t4(biased), t4(sorted), weights ? t4(weights) : t4(biased), npad, weights ? (int) weights->ne[0] : 0);
+    return launched();
+}
+
+int b200q_op_moe_gate_weights(const b200q_tensor * probs, const b200q_tensor * ids, const b200q_tensor * weights, void * stream) {
+    if (!probs || !ids || !weights || probs->type != B200Q_TYPE_F32 || ids->type != B200Q_TYPE_I32 || weights->type != B200Q_TYPE_F32 ||
+        probs->ne[0] != 1 || probs->ne[3] != 1 || ids->ne[2] != 1 || ids->ne[3] != 1 || ids->ne[1] != probs->ne[2] || ids->ne[0] < 1 || ids->ne[0] > 1024 ||
+        weights->nb[0] != 4 || weights->ne[0] != ids->ne[0] || weights->ne[1] != ids->ne[1] || weights->ne[2] != 1 || weights->ne[3] != 1) {
+        return ops_fail(B200Q_ENOTSUP, "moe_gate_weights: f32 probs [1, experts, tokens], i32 ids [used, tokens], f32 weights [used, tokens]");
+    }
+    const long long n_tok = ids->ne[1];
+    if (n_tok == 0) return 0;
+    launch_pdl(moe_gate_weights_kernel, dim3(grid_for(n_tok, 128)), dim3(128), 0, (cudaStream_t) stream, t4(probs), t4(ids), t4(weights), n_tok, (int) ids->ne[0]);
     return launched();
 }
 

@@ -991,10 +991,10 @@ bool touches(const ggml_tensor * node, const ggml_tensor * t) {  // does `node` 
 }
 int32_t node_use_count(const ggml_cgraph * cgraph, const ggml_tensor * t);
 // how often each fusion of graph_dispatch fired ("ggml_backend_b200_fusion_stats": copies up to n counters, returns how many exist)
-enum { FUSE_NORM, FUSE_ATTN, FUSE_ROPE_STORE, FUSE_SET_ROWS_PAIR, FUSE_MOE_SUM, FUSE_ID_BIAS, FUSE_LIST, FUSE_SCRATCH_READ, FUSE_SCRATCH_COPY, FUSE_GLU_LIST, FUSE_N };
+enum { FUSE_NORM, FUSE_ATTN, FUSE_ROPE_STORE, FUSE_SET_ROWS_PAIR, FUSE_MOE_SUM, FUSE_ID_BIAS, FUSE_LIST, FUSE_SCRATCH_READ, FUSE_SCRATCH_COPY, FUSE_GLU_LIST, FUSE_ROUTE, FUSE_N };
 int64_t g_fusion_stats[FUSE_N] = {};
 void    print_fusion_stats() {  // GGML_B200_STATS=1: at exit, what graph_dispatch did with the graphs of this process
-    static const char * names[FUSE_N] = { "norm", "attn", "rope_store", "set_rows_pair", "moe_sum", "id_bias", "list", "scratch_read", "scratch_copy", "glu_list" };
+    static const char * names[FUSE_N] = { "norm", "attn", "rope_store", "set_rows_pair", "moe_sum", "id_bias", "list", "scratch_read", "scratch_copy", "glu_list", "route" };
     fprintf(stderr, "ggml-b200 fusions:");
     for (int i = 0; i < FUSE_N; ++i) fprintf(stderr, " %s=%lld", names[i], (long long) g_fusion_stats[i]);
     fprintf(stderr, "\n");
@@ -1380,6 +1380,54 @@ bool sole_reader_takes_scratch(const ggml_cgraph * cgraph, int i, int n_nodes) {
     return false;
 }
 
+// The MoE router behind the logits matmul as gpt-oss gates (src/llama-graph.cpp build_moe_ffn, router bias +
+// LLAMA_EXPERT_GATING_FUNC_TYPE_SOFTMAX_WEIGHT) is ADD(logits, bias) -> ARGSORT(desc) -> VIEW (top-k) ... GET_ROWS(RESHAPE(biased),
+// top-k) -> RESHAPE -> SOFT_MAX, with the expert matmuls between the two halves in graph order.  Each half is one launch:
+// ADD + ARGSORT (both results written), and GET_ROWS + SOFT_MAX (the GET_ROWS result, which only the SOFT_MAX reads, is not).
+// Both return the index behind the run, or 0.
+int try_fuse_moe_route(b200_backend_ctx * ctx, const ggml_cgraph * cgraph, int i, int n_nodes, int * rc) {
+    const ggml_tensor * add = ggml_graph_node((ggml_cgraph *) cgraph, i);
+    const ggml_tensor * lg = add->src[0], * bias = add->src[1];
+    if (add->op != GGML_OP_ADD || !is_f32(add) || !is_f32(lg) || !is_f32(bias) || !ggml_is_contiguous(add) || !ggml_is_contiguous(lg) ||
+        !ggml_is_contiguous(bias) || !ggml_are_same_shape(add, lg) || add->ne[0] > 1024 || add->ne[2] != 1 || add->ne[3] != 1 || bias->ne[0] != add->ne[0] ||
+        ggml_nelements(bias) != bias->ne[0] || tensor_is_split(bias)) return 0;
+    int j = i + 1;
+    while (j < n_nodes && noop_node(ggml_graph_node((ggml_cgraph *) cgraph, j))) ++j;
+    if (j >= n_nodes) return 0;
+    const ggml_tensor * srt = ggml_graph_node((ggml_cgraph *) cgraph, j);
+    if (srt->op != GGML_OP_ARGSORT || srt->src[0] != add || ((const int32_t *) srt->op_params)[0] != GGML_SORT_ORDER_DESC || !supports_elementwise(srt) ||
+        !ggml_is_contiguous(srt) || ranges_overlap(srt, lg) || ranges_overlap(srt, add)) return 0;
+    const b200q_tensor tl = bt_src(ctx, lg), tb = bt(bias), ta = bt(add), ts = bt(srt);
+    *rc = b200q_op_moe_route(&tl, &tb, &ta, &ts, nullptr, ctx->stream);
+    return j + 1;
+}
+int try_fuse_gate_weights(b200_backend_ctx * ctx, const ggml_cgraph * cgraph, int i, int n_nodes, int * rc) {
+    if (!cgraph->use_counts) return 0;
+    const ggml_tensor * gr = ggml_graph_node((ggml_cgraph *) cgraph, i);
+    const ggml_tensor * probs = gr->src[0], * ids = gr->src[1];
+    if (gr->op != GGML_OP_GET_ROWS || !is_f32(gr) || !is_f32(probs) || !ids || ids->type != GGML_TYPE_I32 || probs->ne[0] != 1 || probs->ne[3] != 1 ||
+        ids->ne[2] != 1 || ids->ne[3] != 1 || ids->ne[1] != probs->ne[2] || ids->ne[0] > 1024 || gr->ne[0] != 1 || gr->ne[1] != ids->ne[0] ||
+        gr->ne[2] != ids->ne[1] || node_use_count(cgraph, gr) != 1 || (gr->flags & GGML_TENSOR_FLAG_OUTPUT) || tensor_is_split(probs)) return 0;
+    int j = i + 1;
+    const ggml_tensor * view = nullptr;
+    while (j < n_nodes && noop_node(ggml_graph_node((ggml_cgraph *) cgraph, j))) {
+        const ggml_tensor * t = ggml_graph_node((ggml_cgraph *) cgraph, j);
+        if (t->src[0] == gr) view = t;
+        ++j;
+    }
+    if (j >= n_nodes || !view) return 0;
+    const ggml_tensor * sm = ggml_graph_node((ggml_cgraph *) cgraph, j);
+    float scale, max_bias;
+    memcpy(&scale, sm->op_params, 4); memcpy(&max_bias, (const char *) sm->op_params + 4, 4);
+    if (view->op != GGML_OP_RESHAPE || view->data != gr->data || node_use_count(cgraph, view) != 1 || (view->flags & GGML_TENSOR_FLAG_OUTPUT)) return 0;
+    if (sm->op != GGML_OP_SOFT_MAX || sm->src[0] != view || sm->src[1] || sm->src[2] || scale != 1.0f || max_bias != 0.0f || !is_f32(sm) ||
+        !ggml_is_contiguous(sm) || sm->ne[0] != ids->ne[0] || sm->ne[1] != ids->ne[1] || sm->ne[2] != 1 || sm->ne[3] != 1 || ranges_overlap(sm, probs) ||
+        ranges_overlap(sm, ids)) return 0;
+    const b200q_tensor tp = bt(probs), ti = bt(ids), tw = bt(sm);
+    *rc = b200q_op_moe_gate_weights(&tp, &ti, &tw, ctx->stream);
+    return j + 1;
+}
+
 // [ADD(bias) ->] ROPE(q) at node i, followed — with nothing in between but views and matmuls that already ran with an earlier
 // list — by [ADD(bias) ->] ROPE(k) whose only reader is a SET_ROWS (the K cache write) and [ADD(bias) ->] a second SET_ROWS (the V
 // cache write): llama.cpp's decode step behind the q / k / v matmuls (src/models/*.cpp: with biases in gpt-oss / Qwen2).  All of
@@ -1555,6 +1603,18 @@ ggml_status graph_dispatch(b200_backend_ctx * ctx, ggml_cgraph * cgraph) {
                     return GGML_STATUS_FAILED;
                 }
                 ++g_fusion_stats[FUSE_MOE_SUM];
+                i = behind - 1;
+                continue;
+            }
+        }
+        if (!no_fuse && (node->op == GGML_OP_ADD || node->op == GGML_OP_GET_ROWS)) {
+            const int behind = node->op == GGML_OP_ADD ? try_fuse_moe_route(ctx, cgraph, i, n_nodes, &rc) : try_fuse_gate_weights(ctx, cgraph, i, n_nodes, &rc);
+            if (behind > i) {
+                if (rc != 0) {
+                    fprintf(stderr, "ggml-b200: fused MoE router (%s) failed (%d): %s\n", node->name, rc, b200q_last_error());
+                    return GGML_STATUS_FAILED;
+                }
+                ++g_fusion_stats[FUSE_ROUTE];
                 i = behind - 1;
                 continue;
             }

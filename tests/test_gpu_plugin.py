@@ -336,7 +336,7 @@ def test_inprocess_layer_with_attention_biases(t, n_tokens, n_past):
         assert fired["rope_store"] >= 1 and fired["list"] >= 2, fired
 
 
-FUSIONS = ("norm", "attn", "rope_store", "set_rows_pair", "moe_sum", "id_bias", "list", "scratch_read", "scratch_copy", "glu_list")
+FUSIONS = ("norm", "attn", "rope_store", "set_rows_pair", "moe_sum", "id_bias", "list", "scratch_read", "scratch_copy", "glu_list", "route")
 
 
 def _fusion_stats(L):
@@ -356,10 +356,14 @@ def test_inprocess_gpt_oss_moe_block_stays_on_device(n_tokens):
     reference CPU backend's (the routing is discrete: equal selections are part of what the NMSE checks)."""
     L = _driver()
     nmse, unsup = C.c_double(-1.0), C.c_int(-1)
+    before = _fusion_stats(L)
     rc = L.pd_moe_block(0, n_tokens, C.byref(nmse), C.byref(unsup))
     assert rc == 0 and unsup.value == 0, (rc, unsup.value)
-    print(f"\n[gpt-oss moe block] n_tokens={n_tokens}: nmse vs CPU backend {nmse.value:.2e}")
+    fired = {k: v - before[k] for k, v in _fusion_stats(L).items()}
+    print(f"\n[gpt-oss moe block] n_tokens={n_tokens}: nmse vs CPU backend {nmse.value:.2e}; fusions {fired}")
     assert 0.0 <= nmse.value <= 1e-3
+    if not os.environ.get("GGML_B200_NO_FUSE"):  # router (bias, top-k, soft_max over the selection) and combine as one launch each
+        assert fired["route"] >= 2 and fired["moe_sum"] >= 1, fired  # both halves: ADD + ARGSORT, GET_ROWS + SOFT_MAX
 
 
 def test_inprocess_split_buffer_only_serves_mul_mat():
