@@ -453,7 +453,7 @@ struct ListGeo {
 // stage geometry of one op: a function of (type, k) only (gemv_list.cuh)
 bool list_geometry(int type, int64_t k, ListGeo & g) {
     if (!list_type_ok(type)) return false;
-    const bool kquant = type == T_Q4_K || type == T_Q6_K;
+    const bool kquant = type == T_Q4_K || type == T_Q5_K || type == T_Q6_K;
     g.unit = kquant ? 256 : 32;
     if (k <= 0 || k % g.unit || k / g.unit > 65535) return false;
     g.nsb   = (int) (k / g.unit);
@@ -461,7 +461,7 @@ bool list_geometry(int type, int64_t k, ListGeo & g) {
     g.qmode = kquant ? 0 : type == T_MXFP4 ? 2 : 1;
     const long long rb   = (long long) g.nsb * g.bb;
     int             rps;
-    if (kquant && g.nsb <= LIST_REG_ACT_NSB) {
+    if (kquant && type != T_Q5_K && g.nsb <= LIST_REG_ACT_NSB) {
         // column-owning lanes (gemv_list.cuh): 32 / lpr rows side by side, up to 4 rows per lane in sequence
         int lpr = 1;
         while (lpr < 32 && lpr < g.nsb) lpr *= 2;
@@ -1386,12 +1386,14 @@ int b200q_list_create(const b200q_list_op * ops, int n_ops, const b200q_list_pee
 
 int b200q_list_launch(b200q_list * L, void * stream) {
     if (!L) return fail(B200Q_EINVAL, "list_launch: null list");
-    list_kernel_t fn = list_kernel();
     const DevInfo & di = dev_info();
-    if (int rc = ensure_smem_attr((const void *) fn, di.max_smem)) return rc;
     static const bool debug = getenv("B200Q_DEBUG") != nullptr;
     for (auto & sg : L->segs) {
         if (sg.total_units == 0 && sg.p.world == 1) continue;
+        bool q5k = false;
+        for (const ListOp & o : sg.ops) q5k = q5k || o.type == T_Q5_K;
+        list_kernel_t fn = list_kernel(q5k);
+        if (int rc = ensure_smem_attr((const void *) fn, di.max_smem)) return rc;
         if (debug) {
             fprintf(stderr, "[b200q] gemv_list ops=%d gens=%d units=%d bp=%d slots=%d smem=%d grid=%d world=%d\n", sg.p.n_ops, sg.p.n_gens,
                     (int) sg.total_units, sg.p.n_bp, sg.p.nslots, sg.smem, sg.grid, sg.p.world);

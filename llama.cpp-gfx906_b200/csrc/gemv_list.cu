@@ -116,7 +116,7 @@ struct Walk {
 template <int T> __device__ __forceinline__ float dot_units(const ActLayout & al, uint32_t abase, uint32_t row, int s0, int s1, int step) {
     float acc = 0.0f;
     for (int s = s0; s < s1; s += step) {
-        if constexpr (T == T_Q4_K || T == T_Q6_K) acc += SbDot<T>::run(al, abase, row, s);
+        if constexpr (T == T_Q4_K || T == T_Q5_K || T == T_Q6_K) acc += SbDot<T>::run(al, abase, row, s);
         else acc += B32Dot<T>::run(al, abase, row, s);
     }
     return acc;
@@ -139,7 +139,9 @@ constexpr int LIST_TRACE_EVENTS = 4096;
 #define EV(tag_, val_) do { } while (0)
 #endif
 
-__global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams p) {
+// Q5K: the instantiation that also serves q5_K ops.  Kept apart because its extra case costs the common instantiation two
+// spilled registers and 5 % of the headline pass (5.39 -> 5.10 TB/s); lists without q5_K launch the kernel without it.
+template <bool Q5K> __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams p) {
     const uint32_t sb   = smem_u32(list_smem);
     const int      warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int      G    = (int) gridDim.x;
@@ -354,7 +356,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
             cur_op = wc.op;
             r      = op_load(tab, cur_op);
             while (g < r.gen) gen_switch(++g);
-            const bool kq = r.type == T_Q4_K || r.type == T_Q6_K;
+            const bool kq = r.type == T_Q4_K || r.type == T_Q6_K;  // q5_K (Q5_K_M files) walks its rows with activations in shared memory
             regs          = kq && r.nsb <= LIST_REG_ACT_NSB;
             // lanes per row: column-owning lanes cover the columns; row-owning lanes split a row 32 / rps ways
             lpr_log2 = regs ? (r.nsb == 1 ? 0 : 32 - __clz(r.nsb - 1)) : 5 - r.rps_log2;
@@ -441,6 +443,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
                 const uint32_t row = row0 + (uint32_t) lrow * (uint32_t) rb;
                 switch (r.type) {
                     case T_Q4_K:  acc += dot_units<T_Q4_K>(al, abase, row, s0 + sub, s1, lpr); break;
+                    case T_Q5_K:  if constexpr (Q5K) acc += dot_units<T_Q5_K>(al, abase, row, s0 + sub, s1, lpr); break;
                     case T_Q6_K:  acc += dot_units<T_Q6_K>(al, abase, row, s0 + sub, s1, lpr); break;
                     case T_Q8_0:  acc += dot_units<T_Q8_0>(al, abase, row, s0 + sub, s1, lpr); break;
                     case T_Q4_0:  acc += dot_units<T_Q4_0>(al, abase, row, s0 + sub, s1, lpr); break;
@@ -486,11 +489,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemv_list_kernel(const ListParams
 
 }  // namespace
 
-list_kernel_t list_kernel() { return gemv_list_kernel; }
+list_kernel_t list_kernel(bool with_q5k) { return with_q5k ? gemv_list_kernel<true> : gemv_list_kernel<false>; }
 int           list_threads() { return NTHREADS; }
 bool          list_type_ok(int type) {
     switch (type) {
-        case T_Q4_K: case T_Q6_K: case T_Q8_0: case T_Q4_0: case T_Q4_1: case T_Q5_0: case T_Q5_1: case T_MXFP4: return true;
+        case T_Q4_K: case T_Q5_K: case T_Q6_K: case T_Q8_0: case T_Q4_0: case T_Q4_1: case T_Q5_0: case T_Q5_1: case T_MXFP4: return true;
         default: return false;
     }
 }

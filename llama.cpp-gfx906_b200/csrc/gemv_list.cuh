@@ -77,7 +77,7 @@ struct ListParams {
 };
 
 typedef void (*list_kernel_t)(const ListParams);
-list_kernel_t list_kernel();
+list_kernel_t list_kernel(bool with_q5k);  // with_q5k: some op of the launch is q5_K
 int           list_threads();
 bool          list_type_ok(int type);
 

@@ -17,7 +17,7 @@ import refs
 
 pytestmark = pytest.mark.gpu
 MAX_NMSE = 5e-4
-LIST_TYPES = [refs.Q4_K, refs.Q6_K, refs.Q8_0, refs.Q4_0, refs.Q4_1, refs.Q5_0, refs.Q5_1, refs.MXFP4]
+LIST_TYPES = [refs.Q4_K, refs.Q5_K, refs.Q6_K, refs.Q8_0, refs.Q4_0, refs.Q4_1, refs.Q5_0, refs.Q5_1, refs.MXFP4]
 
 
 def _cpu(t, w, act):

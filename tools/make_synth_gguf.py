@@ -3,7 +3,7 @@ reference's llama-bench.  Our own minimal GGUF v3 writer (the format is document
 docs; nothing is imported from the reference, so this runs on the GPU box).  Weights are valid random blocks
 (tests/refs.random_blocks) tiled over each matrix — throughput does not depend on the values.
 
-python tools/make_synth_gguf.py --out /tmp/synth-8b-q4_k_m.gguf [--layers 32] [--ftype q4_k_m|q8_0|q4_0]"""
+python tools/make_synth_gguf.py --out /tmp/synth-8b-q4_k_m.gguf [--layers 32] [--ftype q4_k_m|q5_k_m|q8_0|q4_0]"""
 import argparse
 import os
 import struct
@@ -120,8 +120,8 @@ def main():
         return gpt_oss(a)
     a.vocab = a.vocab or 128256
     n_embd, n_ff, n_head, n_head_kv, hd = 4096, 14336, 32, 8, 128
-    base = {"q4_k_m": refs.Q4_K, "q8_0": refs.Q8_0, "q4_0": refs.Q4_0}[a.ftype]
-    wide = refs.Q6_K if a.ftype == "q4_k_m" else base
+    base = {"q4_k_m": refs.Q4_K, "q5_k_m": refs.Q5_K, "q8_0": refs.Q8_0, "q4_0": refs.Q4_0}[a.ftype]
+    wide = refs.Q6_K if a.ftype in ("q4_k_m", "q5_k_m") else base
     tensors = []  # (name, ne (ggml order), type)
     tensors.append(("token_embd.weight", (n_embd, a.vocab), base))
     for i in range(a.layers):
