@@ -325,6 +325,88 @@ template <> struct Dq<T_Q4_K> {
         }
     }
 };
+template <> struct Dq<T_Q5_K> {  // q4_K's layout with 32 bytes of fifth bits behind the scales: element l of sub-block b32 takes bit b32 of qh[l]
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        uint32_t h[4];  // [d dmin] [scales x3]
+        ldu32_n<4>(piece, h);
+        const float d = half_bits_to_float((uint16_t) (h[0] & 0xffffu)), dmin = half_bits_to_float((uint16_t) (h[0] >> 16));
+        int sc, mn;
+        if (b32 < 4) {
+            sc = (int) ((h[1] >> (8 * b32)) & 63);
+            mn = (int) ((h[2] >> (8 * b32)) & 63);
+        } else {
+            const int      jj = b32 - 4;
+            const uint32_t hi = (h[3] >> (8 * jj)) & 0xff;
+            sc                = (int) ((hi & 0xF) | (((h[1] >> (8 * jj + 6)) & 3) << 4));
+            mn                = (int) ((hi >> 4) | (((h[2] >> (8 * jj + 6)) & 3) << 4));
+        }
+        const float dsc = d * (float) sc, dm = -dmin * (float) mn;
+        const int   sh  = 4 * (b32 & 1);
+        uint32_t    q[8], fh[8];
+        ldu32_n<8>(piece + 48 + 32 * (b32 >> 1), q);
+        ldu32_n<8>(piece + 16, fh);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t w = ((q[i] >> sh) & 0x0F0F0F0Fu) | (((fh[i] >> b32) & 0x01010101u) << 4);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[4 * i + j] = fmaf(magic_u8(w, j) - MAGIC, dsc, dm);
+        }
+    }
+};
+// the 32-element formats with a minimum and / or a fifth bit (dequantize_row_q4_1 / q5_0 / q5_1, ggml-quants.c): bit l of the
+// 32-bit qh belongs to element l; four of them are spread to bit 4 of four bytes by one multiplication (bit k lands on 8 k)
+__device__ __forceinline__ uint32_t spread4(uint32_t qh, int first) { return ((((qh >> first) & 0xFu) * 0x00204081u) & 0x01010101u) << 4; }
+template <> struct Dq<T_Q4_1> {
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        uint32_t w[5];  // [d m] [qs x4]
+        ldu32_n<5>(piece + b32 * 20, w);
+        const float d = half_bits_to_float((uint16_t) (w[0] & 0xffffu)), m = half_bits_to_float((uint16_t) (w[0] >> 16));
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t lo = w[1 + i] & 0x0F0F0F0Fu, hi = (w[1 + i] >> 4) & 0x0F0F0F0Fu;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                v[4 * i + j]      = fmaf(magic_u8(lo, j) - MAGIC, d, m);
+                v[16 + 4 * i + j] = fmaf(magic_u8(hi, j) - MAGIC, d, m);
+            }
+        }
+    }
+};
+template <> struct Dq<T_Q5_0> {
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        uint32_t w[6];  // [d | qh0 qh1] [qh2 qh3 | qs0 qs1] [qs2..5] [qs6..9] [qs10..13] [qs14 qs15 | next]
+        ldu32_n<6>(piece + b32 * 22, w);
+        const float    d  = half_bits_to_float((uint16_t) (w[0] & 0xffffu));
+        const uint32_t qh = __funnelshift_r(w[0], w[1], 16);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t q  = __funnelshift_r(w[1 + i], w[2 + i], 16);
+            const uint32_t lo = (q & 0x0F0F0F0Fu) | spread4(qh, 4 * i), hi = ((q >> 4) & 0x0F0F0F0Fu) | spread4(qh, 16 + 4 * i);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                v[4 * i + j]      = d * (magic_u8(lo, j) - (MAGIC + 16.0f));
+                v[16 + 4 * i + j] = d * (magic_u8(hi, j) - (MAGIC + 16.0f));
+            }
+        }
+    }
+};
+template <> struct Dq<T_Q5_1> {
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        uint32_t w[6];  // [d m] [qh] [qs x4]
+        ldu32_n<6>(piece + b32 * 24, w);
+        const float    d  = half_bits_to_float((uint16_t) (w[0] & 0xffffu)), m = half_bits_to_float((uint16_t) (w[0] >> 16));
+        const uint32_t qh = w[1];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t lo = (w[2 + i] & 0x0F0F0F0Fu) | spread4(qh, 4 * i), hi = ((w[2 + i] >> 4) & 0x0F0F0F0Fu) | spread4(qh, 16 + 4 * i);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                v[4 * i + j]      = fmaf(magic_u8(lo, j) - MAGIC, d, m);
+                v[16 + 4 * i + j] = fmaf(magic_u8(hi, j) - MAGIC, d, m);
+            }
+        }
+    }
+};
 template <> struct Dq<T_Q6_K> {
     static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
         const int n128 = b32 >> 2, quad = b32 & 3;
