@@ -407,6 +407,93 @@ template <> struct Dq<T_Q5_1> {
         }
     }
 };
+// kvalues_iq4nl (ggml-common.h:1088-1090) + 128 as a 16-byte table in four words; four nibbles (one per byte of `nibs`) are looked
+// up with three PRMTs: entries 0..7 and 8..15 by the low three bits, then bit 3 picks per byte
+__device__ __forceinline__ uint32_t iq4_lut4(uint32_t nibs) {
+    const uint32_t sel = (nibs & 0xFu) | ((nibs >> 4) & 0xF0u) | ((nibs >> 8) & 0xF00u) | ((nibs >> 12) & 0xF000u);
+    const uint32_t lo  = __byte_perm(0x3F2D1801u, 0x766A5D4Fu, sel & 0x7777u);
+    const uint32_t hi  = __byte_perm(0xA6998D81u, 0xF1D9C5B5u, sel & 0x7777u);
+    return __byte_perm(lo, hi, 0x3210u | ((sel & 0x8888u) >> 1));
+}
+template <> struct Dq<T_IQ4_NL> {
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        uint32_t w[5];  // [d | qs0 qs1] [qs2..5] [qs6..9] [qs10..13] [qs14 qs15 | next]
+        ldu32_n<5>(piece + b32 * 18, w);
+        const float d = half_bits_to_float((uint16_t) (w[0] & 0xffffu));
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t q  = __funnelshift_r(w[i], w[i + 1], 16);
+            const uint32_t lo = iq4_lut4(q & 0x0F0F0F0Fu), hi = iq4_lut4((q >> 4) & 0x0F0F0F0Fu);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                v[4 * i + j]      = d * (magic_u8(lo, j) - (MAGIC + 128.0f));
+                v[16 + 4 * i + j] = d * (magic_u8(hi, j) - (MAGIC + 128.0f));
+            }
+        }
+    }
+};
+template <> struct Dq<T_IQ4_XS> {  // d:0 scales_h:2 scales_l:4 qs:8 (136 bytes per 256 values); sub-block b32 has a 6-bit scale
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        uint32_t h[2], q[4];
+        ldu32_n<2>(piece, h);  // [d | scales_h] [scales_l x4]
+        ldu32_n<4>(piece + 8 + 16 * b32, q);
+        const int   ls = (int) (((h[1] >> (4 * b32)) & 0xFu) | ((((h[0] >> 16) >> (2 * b32)) & 3u) << 4));
+        const float dl = half_bits_to_float((uint16_t) (h[0] & 0xffffu)) * (float) (ls - 32);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t lo = iq4_lut4(q[i] & 0x0F0F0F0Fu), hi = iq4_lut4((q[i] >> 4) & 0x0F0F0F0Fu);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                v[4 * i + j]      = dl * (magic_u8(lo, j) - (MAGIC + 128.0f));
+                v[16 + 4 * i + j] = dl * (magic_u8(hi, j) - (MAGIC + 128.0f));
+            }
+        }
+    }
+};
+// q2_K (scales:0 qs:16 d:80 dmin:82) and q3_K (hmask:0 qs:32 scales:96 d:108): 32 values = 2-bit field j of 32 consecutive qs
+// bytes of 128-value half n, two 16-value halves with a scale each (dequantize_row_q2_K / _q3_K, ggml-quants.c:784-814, 1128-1176)
+template <> struct Dq<T_Q2_K> {
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        const int n = b32 >> 2, j = b32 & 3;
+        uint32_t  q[8];
+        ldu32_n<8>(piece + 16 + 32 * n, q);
+        const uint32_t dd = ldu32(piece + 80), sc = ldu32(piece + 8 * n + 2 * j);  // [d dmin]; scale bytes of the two halves
+        const float    d = half_bits_to_float((uint16_t) (dd & 0xffffu)), dmin = half_bits_to_float((uint16_t) (dd >> 16));
+        const float    dl0 = d * (float) (sc & 0xFu), ml0 = -dmin * (float) ((sc >> 4) & 0xFu);
+        const float    dl1 = d * (float) ((sc >> 8) & 0xFu), ml1 = -dmin * (float) ((sc >> 12) & 0xFu);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t w  = (q[i] >> (2 * j)) & 0x03030303u;
+            const float    dl = i < 4 ? dl0 : dl1, ml = i < 4 ? ml0 : ml1;
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) v[4 * i + jj] = fmaf(magic_u8(w, jj) - MAGIC, dl, ml);
+        }
+    }
+};
+template <> struct Dq<T_Q3_K> {
+    static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
+        const int n = b32 >> 2, j = b32 & 3;
+        uint32_t  q[8], hm[8], scw[3];
+        ldu32_n<8>(piece + 32 + 32 * n, q);
+        ldu32_n<8>(piece, hm);
+        ldu32_n<3>(piece + 96, scw);
+        const float d = ldh(piece + 108);
+        auto byte = [&](int k) { return ((k < 4 ? scw[0] : k < 8 ? scw[1] : scw[2]) >> (8 * (k & 3))) & 0xffu; };
+        auto scale = [&](int s) {  // the aux[] shuffle of dequantize_row_q3_K: low 4 bits in bytes 0..7, high 2 bits in bytes 8..11
+            const uint32_t lo = s < 8 ? (byte(s) & 0xFu) : (byte(s - 8) >> 4);
+            const uint32_t hi = (byte(8 + (s & 3)) >> (2 * (s >> 2))) & 3u;
+            return (int) (lo | (hi << 4)) - 32;
+        };
+        const float dl0 = d * (float) scale(8 * n + 2 * j), dl1 = d * (float) scale(8 * n + 2 * j + 1);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t w  = ((q[i] >> (2 * j)) & 0x03030303u) | (((hm[i] >> (4 * n + j)) & 0x01010101u) << 2);
+            const float    dl = i < 4 ? dl0 : dl1;
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) v[4 * i + jj] = dl * (magic_u8(w, jj) - (MAGIC + 4.0f));
+        }
+    }
+};
 template <> struct Dq<T_Q6_K> {
     static __device__ __forceinline__ void run(uint32_t piece, int b32, float (&v)[32]) {
         const int n128 = b32 >> 2, quad = b32 & 3;
@@ -967,7 +1054,7 @@ mmq_kernel_t mmq_kernel_for(int type) {
         case T_F16:   return mmq_kernel<T_F16>;
         case T_BF16:  return mmq_kernel<T_BF16>;
         case T_F32W:  return mmq_kernel<T_F32W>;
-        case T_Q2_K:  return mmq_kernel<T_Q2_K>;    // these four dequantize through the scalar decoders of blocks.cuh
+        case T_Q2_K:  return mmq_kernel<T_Q2_K>;
         case T_Q3_K:  return mmq_kernel<T_Q3_K>;
         case T_IQ4_NL: return mmq_kernel<T_IQ4_NL>;
         case T_IQ4_XS: return mmq_kernel<T_IQ4_XS>;
