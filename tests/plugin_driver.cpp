@@ -381,6 +381,8 @@ namespace {
 struct lcg { uint32_t s; float next() { s = s * 1664525u + 1013904223u; return ((s >> 8) * (1.0f / 8388608.0f)) - 1.0f; } };
 struct layer_dims { int64_t n_embd = 512, n_head = 8, n_head_kv = 2, hd = 64, n_ff = 1024, n_ctx = 256; };
 
+bool g_layer_vtrans = false;  // the V cache transposed as llama.cpp keeps it without flash attention (llama-kv-cache.cpp cpy_v / get_v,
+                              // v_trans): element e of position p at (e * n_ctx + p); written by a SET_ROWS of one-element rows
 bool g_layer_bias = false;  // q / k / v / o biases as gpt-oss and Qwen2 have them (an ADD behind each of the four matmuls)
 int run_layer(ggml_backend_t be, int type, int n_tokens, int n_past, std::vector<float> & out, int * unsupported) {
     const layer_dims D;
@@ -429,6 +431,7 @@ int run_layer(ggml_backend_t be, int type, int n_tokens, int n_past, std::vector
     ggml_tensor * pos  = ggml_new_tensor_1d(cc.ctx, GGML_TYPE_I32, n_tokens);
     ggml_tensor * idx  = ggml_new_tensor_1d(cc.ctx, GGML_TYPE_I64, n_tokens);
     ggml_tensor * mask = ggml_new_tensor_2d(cc.ctx, GGML_TYPE_F32, n_kv, n_tokens);
+    ggml_tensor * idxv = ggml_new_tensor_1d(cc.ctx, GGML_TYPE_I64, g_layer_vtrans ? kv_dim * n_tokens : 1);
     ggml_context * c = cc.ctx;
     ggml_tensor * cur = ggml_mul(c, ggml_rms_norm(c, x, 1e-5f), an);
     auto biased = [&](ggml_tensor * t, ggml_tensor * b) { return g_layer_bias ? ggml_add(c, t, b) : t; };
@@ -438,13 +441,15 @@ int run_layer(ggml_backend_t be, int type, int n_tokens, int n_past, std::vector
     Q = ggml_rope_ext(c, Q, pos, nullptr, (int) D.hd, 0, 8192, 500000.0f, 1.0f, 0.0f, 1.0f, 32.0f, 1.0f);
     K = ggml_rope_ext(c, K, pos, nullptr, (int) D.hd, 0, 8192, 500000.0f, 1.0f, 0.0f, 1.0f, 32.0f, 1.0f);
     ggml_tensor * k_store = ggml_set_rows(c, kc, ggml_reshape_2d(c, K, kv_dim, n_tokens), idx);
-    ggml_tensor * v_store = ggml_set_rows(c, vc, V, idx);
+    ggml_tensor * v_store = g_layer_vtrans ? ggml_set_rows(c, ggml_reshape_2d(c, vc, 1, ggml_nelements(vc)), ggml_reshape_2d(c, V, 1, ggml_nelements(V)), idxv)
+                                           : ggml_set_rows(c, vc, V, idx);
     ggml_tensor * q = ggml_permute(c, Q, 0, 2, 1, 3);
     ggml_tensor * k = ggml_view_3d(c, kc, D.hd, n_kv, D.n_head_kv, kc->nb[1], ggml_row_size(kc->type, D.hd), 0);
     ggml_tensor * v = ggml_view_3d(c, vc, D.hd, n_kv, D.n_head_kv, vc->nb[1], ggml_row_size(vc->type, D.hd), 0);
     ggml_tensor * kq = ggml_mul_mat(c, k, q);
     kq = ggml_soft_max_ext(c, kq, mask, 1.0f / 8.0f, 0.0f);
-    v = ggml_cont(c, ggml_transpose(c, v));
+    if (g_layer_vtrans) v = ggml_view_3d(c, vc, n_kv, D.hd, D.n_head_kv, ggml_row_size(vc->type, D.n_ctx), ggml_row_size(vc->type, D.n_ctx * D.hd), 0);
+    else v = ggml_cont(c, ggml_transpose(c, v));
     ggml_tensor * kqv = ggml_mul_mat(c, v, kq);
     cur = ggml_cont_2d(c, ggml_permute(c, kqv, 0, 2, 1, 3), D.n_embd, n_tokens);
     ggml_tensor * ffn_inp = ggml_add(c, biased(ggml_mul_mat(c, wo, cur), bo), x);
@@ -463,7 +468,7 @@ int run_layer(ggml_backend_t be, int type, int n_tokens, int n_past, std::vector
     ggml_build_forward_expand(gf, res);
     // intermediate results are placed by ggml-alloc, as in llama.cpp: buffers are REUSED along the graph (a matmul's result may
     // take the place of a tensor that died a few nodes earlier), which is what the plugin's reordering has to respect
-    for (ggml_tensor * t : { x, pos, idx, mask }) ggml_set_input(t);
+    for (ggml_tensor * t : { x, pos, idx, mask, idxv }) ggml_set_input(t);
     ggml_set_output(res);
     ggml_gallocr_t ga = ggml_gallocr_new(ggml_backend_get_default_buffer_type(be));
     int rc = ga && ggml_gallocr_alloc_graph(ga, gf) ? 0 : -4;
@@ -491,6 +496,11 @@ int run_layer(ggml_backend_t be, int type, int n_tokens, int n_past, std::vector
         ggml_backend_tensor_set(pos, ps.data(), 0, ggml_nbytes(pos));
         ggml_backend_tensor_set(idx, is.data(), 0, ggml_nbytes(idx));
         ggml_backend_tensor_set(mask, ms.data(), 0, ggml_nbytes(mask));
+        if (g_layer_vtrans) {
+            std::vector<int64_t> iv((size_t) (kv_dim * n_tokens));
+            for (int t = 0; t < n_tokens; ++t) for (int64_t e = 0; e < kv_dim; ++e) iv[(size_t) (t * kv_dim + e)] = e * D.n_ctx + n_past + t;
+            ggml_backend_tensor_set(idxv, iv.data(), 0, ggml_nbytes(idxv));
+        }
         if (!unsupported || *unsupported == 0) {
             if (ggml_backend_graph_compute(be, gf) != GGML_STATUS_SUCCESS) rc = -5;
             out.resize((size_t) (D.n_embd * n_tokens));
@@ -607,6 +617,13 @@ int pd_moe_block(int dev, int n_tokens, double * nmse, int * unsupported) {
 }
 
 int pd_llama_layer(int dev, int type, int n_tokens, int n_past, double * nmse, int * unsupported);
+int pd_llama_layer_vtrans(int dev, int type, int n_tokens, int n_past, int bias, double * nmse, int * unsupported) {
+    g_layer_vtrans = true;
+    g_layer_bias   = bias != 0;
+    const int rc = pd_llama_layer(dev, type, n_tokens, n_past, nmse, unsupported);
+    g_layer_vtrans = g_layer_bias = false;
+    return rc;
+}
 int pd_llama_layer_bias(int dev, int type, int n_tokens, int n_past, double * nmse, int * unsupported) {
     g_layer_bias = true;
     const int rc = pd_llama_layer(dev, type, n_tokens, n_past, nmse, unsupported);

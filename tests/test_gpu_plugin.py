@@ -97,6 +97,7 @@ def _driver():
         L.pd_last_us.restype = C.c_double
         L.pd_llama_layer.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.pd_llama_layer_bias.argtypes = L.pd_llama_layer.argtypes
+        L.pd_llama_layer_vtrans.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.pd_moe_block.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         n = L.pd_load(PLUGIN.encode())
         assert n >= 1, f"ggml_backend_load({PLUGIN}) registered {n} devices"
@@ -334,6 +335,25 @@ def test_inprocess_layer_with_attention_biases(t, n_tokens, n_past):
     assert 0.0 <= nmse.value <= 1e-3
     if n_tokens == 1 and not any(os.environ.get(k) for k in ("GGML_B200_NO_FUSE", "GGML_B200_NO_LIST", "GGML_B200_NO_HOIST", "GGML_B200_NO_SCRATCH")):
         assert fired["rope_store"] >= 1 and fired["list"] >= 2, fired
+
+
+@pytest.mark.parametrize("bias", [0, 1])
+@pytest.mark.parametrize("n_tokens,n_past", [(1, 37), (1, 0), (5, 60), (40, 0)])
+def test_inprocess_layer_with_transposed_v_cache(n_tokens, n_past, bias):
+    """the layer as llama-bench -fa 0 really runs it: the V cache is kept transposed (llama-kv-cache.cpp v_trans: a SET_ROWS of
+    one-element rows with an index per element writes it, the attention reads it through a strided view, no CONT).  This is the
+    layout the fused rope + cache stores launch and the fused attention core meet in the benchmark; checked against the CPU
+    backend with and without attention biases."""
+    L = _driver()
+    nmse, unsup = C.c_double(-1.0), C.c_int(-1)
+    before = _fusion_stats(L)
+    rc = L.pd_llama_layer_vtrans(0, refs.Q4_K, n_tokens, n_past, bias, C.byref(nmse), C.byref(unsup))
+    assert rc == 0 and unsup.value == 0, (rc, unsup.value)
+    fired = {k: v - before[k] for k, v in _fusion_stats(L).items()}
+    print(f"\n[llama layer, transposed V] n_tokens={n_tokens} n_past={n_past} bias={bias}: nmse vs CPU backend {nmse.value:.2e}; fusions {fired}")
+    assert 0.0 <= nmse.value <= 1e-3
+    if n_tokens == 1 and not any(os.environ.get(k) for k in ("GGML_B200_NO_FUSE", "GGML_B200_NO_LIST", "GGML_B200_NO_HOIST", "GGML_B200_NO_SCRATCH")):
+        assert fired["rope_store"] >= 1 and fired["attn"] >= 1, fired
 
 
 FUSIONS = ("norm", "attn", "rope_store", "set_rows_pair", "moe_sum", "id_bias", "list", "scratch_read", "scratch_copy", "glu_list", "route")
