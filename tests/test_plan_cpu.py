@@ -171,11 +171,11 @@ def test_list_plan_llama3_70b_splits_and_chunks():
     assert down and all(p["nch"] == 2 and p["rps"] == 1 for p in down)
 
 
-@pytest.mark.parametrize("t", [refs.Q4_K, refs.Q6_K, refs.Q8_0, refs.Q4_0, refs.Q4_1, refs.Q5_0, refs.Q5_1, refs.MXFP4],
+@pytest.mark.parametrize("t", [refs.Q4_K, refs.Q5_K, refs.Q6_K, refs.Q8_0, refs.Q4_0, refs.Q4_1, refs.Q5_0, refs.Q5_1, refs.MXFP4],
                          ids=lambda t: refs.NAMES[t])
 def test_list_geometry_depends_on_type_and_k_only(t):
     """the same (type, k) gets the same stage geometry whatever the list looks like (results must not depend on it)"""
-    unit = 256 if t in (refs.Q4_K, refs.Q6_K) else 32
+    unit = 256 if t in (refs.Q4_K, refs.Q5_K, refs.Q6_K) else 32
     for k in (unit, 4 * unit, 2880 // 32 * 32 if unit == 32 else 1024, 4096, 14336 // unit * unit, 28672):
         if k % unit:
             continue
@@ -183,6 +183,15 @@ def test_list_geometry_depends_on_type_and_k_only(t):
         b, _ = plan_list([(refs.Q4_K, 4096, 4096, False, False), (t, 5000, k, True, False), (refs.Q6_K, 128, 14336, False, False)])
         for f in ("rps", "nch", "csb", "nsb"):
             assert a[0][f] == b[1][f], (k, f)
+
+
+def test_list_q5_k_rows_are_walked_by_lanes_not_columns():
+    """q5_K keeps its activations in shared memory (gemv_list.cu: the register-resident column scheme is q4_K / q6_K only), so a
+    stage must never hold more than 32 rows — one lane per row at most — however short the rows are"""
+    for k in (256, 512, 1024, 4096, 14336):
+        p, segs = plan_list([(refs.Q5_K, 300, k, False, False)])
+        assert 1 <= p[0]["rps"] <= 32 and p[0]["rps"] * refs.row_size(refs.Q5_K, k) <= LIST_PAYLOAD or p[0]["nch"] > 1, (k, p[0])
+        assert p[0]["nsb"] == k // 256 and segs[0]["nslots"] >= LIST_MIN_SLOTS
 
 
 def test_list_walk_covers_every_unit_exactly_once():
